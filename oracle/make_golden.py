@@ -1,0 +1,208 @@
+"""Generate tests/golden/*.pt by running the REAL reference python sources.
+
+TEST INFRASTRUCTURE, build container only (needs /root/reference; the GPU box does not have
+it - the committed fixtures travel instead).  Usage:  python -m oracle.make_golden
+
+How the reference is made importable here: its third-party imports (pytorch3d,
+torch_geometric, torch_scatter, torch_sparse, torch_cluster, frnn) resolve to oracle/shims/*
+(the oracle's restatement of that arithmetic).  Two documented deviations from stock:
+  * `point_ops.fast_knn` raises on CPU tensors (point_ops.py:439-440); it is replaced by the
+    same call without the `is_cuda` check so the nuScenes/KITTI/A2D2 step lists run on CPU;
+  * `SemNuScenes._get_curves` is compiled from its own source text (ast) because importing
+    src/data/nuscenes_dataset.py needs nuscenes-devkit/cv2/mitsuba.
+So the fixtures pin the reference's OWN code (base.py, modules/*, point_ops.py, fps_ops.py,
+_get_curves); the third-party arithmetic under the shims stays "parity unpinned".
+"""
+from __future__ import annotations
+
+import ast
+import os
+import sys
+import textwrap
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def _import_reference():
+    for p in (ROOT, os.path.join(ROOT, "oracle", "shims"), REF):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import frnn
+    import src.models.utils.point_ops as rpo
+
+    def fast_knn_no_cuda_check(points1, points2, lengths1, lengths2, K, r, return_nn=False):
+        return frnn.frnn_grid_points(points1.contiguous(), points2.contiguous(), lengths1, lengths2, K, r)[1]
+
+    rpo.fast_knn = fast_knn_no_cuda_check
+    import src.models.base as rbase
+    import src.models.modules.fast_conv1d as rconv
+    import src.models.modules.fps_ops as rfps
+    return rpo, rbase, rconv, rfps
+
+
+def _reference_get_curves():
+    """Compile SemNuScenes._get_curves from its source text (nuscenes_dataset.py:91-118)."""
+    src = open(os.path.join(REF, "src/data/nuscenes_dataset.py")).read()
+    tree = ast.parse(src)
+    for node in ast.walk(tree):
+        if isinstance(node, ast.FunctionDef) and node.name == "_get_curves":
+            code = textwrap.dedent(ast.get_source_segment(src, node))
+            ns = {"torch": torch}
+            exec(compile(code, "nuscenes_dataset.py:_get_curves", "exec"), ns)
+            return ns["_get_curves"]
+    raise RuntimeError("_get_curves not found")
+
+
+def _cases():
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch
+    return {
+        "driving_b2": driving_scan_batch([11, 12], subsample=1500),
+        "driving_b1": driving_scan_batch([13], subsample=2500),
+        "object_b2": object_scan_batch([21, 22], n_points=768),
+    }
+
+
+def make_ops(rpo, rconv, rfps):
+    out = {}
+    for cname, data in _cases().items():
+        pos, batch, curve = data.pos, data.batch, data.curve_idxs
+        g = {"pos": pos, "x": data.x, "batch": batch, "curve": curve}
+        driving = cname.startswith("driving")
+        arclen = 0.007 if driving else 0.04
+        r_geo = 0.02 if driving else 0.075
+        g["glob"] = rpo.curveidx_local2global(curve.clone(), batch)
+        g["ptr"] = rpo.batch2ptr(batch)
+        g["ptr_ends"] = rpo.batch2ptr(batch, with_ends=True)
+        padded, mask = rpo.to_batch_padded(pos.clone(), batch.clone())
+        g["padded_sum"], g["padded_mask"] = padded.sum(dim=1), mask
+
+        torch.manual_seed(100)
+        g["curvefps_u"] = torch.rand(1)
+        torch.manual_seed(100)
+        idx = rfps.CurveFPS(arclen)(pos.clone(), batch.clone(), curve.clone())
+        g["curvefps_arclen"], g["curvefps_idx"] = arclen, idx
+
+        vox = 0.03 if driving else 0.08
+        torch.manual_seed(101)
+        g["voxel_noise"] = torch.rand(pos.shape[0])
+        torch.manual_seed(101)
+        g["voxel_size"], g["voxel_idx"] = vox, rfps.VoxelFPS(vox)(pos.clone(), batch.clone())
+
+        torch.manual_seed(102)
+        lengths = torch.bincount(batch)
+        g["fps_starts"] = torch.tensor([int(torch.randint(high=int(l), size=(1,)).item()) for l in lengths])
+        torch.manual_seed(102)
+        g["fps_ratio"], g["fps_idx"] = 0.25, rpo.fps_pytorch3d(pos, batch, 0.25)
+
+        row, col = rpo.radius_1d_group_subset(pos, idx, curve, batch, r_geo)
+        g["r1d_radius"], g["r1d_row"], g["r1d_col"] = r_geo, row, col
+        row, col = rpo.knn_1d_group_superset(pos, idx, curve, batch, 3)
+        g["s1d_row"], g["s1d_col"] = row, col
+
+        r_knn = 0.04 if driving else 0.2
+        g["knn_radius"] = r_knn
+        sub = g["voxel_idx"]
+        dense, l2, m1 = rpo.knn_ball_group_pytorch3d(pos[sub].clone(), pos, batch[sub].clone(), batch, operation="knn",
+                                                     knn=16, radius=r_knn, return_dense=True)
+        g["frnn_dense"] = dense
+        row, col = rpo.knn_ball_group_pytorch3d(pos[sub].clone(), pos, batch[sub].clone(), batch, operation="knn",
+                                                knn=16, radius=r_knn)
+        g["frnn_row"], g["frnn_col"] = row, col
+        row, col = rpo.knn_ball_group_pytorch3d(pos[sub].clone(), pos, batch[sub].clone(), batch,
+                                                operation="ball-group", radius=r_knn)
+        g["ball_row"], g["ball_col"] = row, col
+        row, col = rpo.knn_ball_group_pytorch3d(pos, pos[sub].clone(), batch, batch[sub].clone(), operation="knn",
+                                                knn=3, accel_knn=False)
+        g["knn3_row"], g["knn3_col"] = row, col
+
+        gen = torch.Generator().manual_seed(7)
+        feat = torch.randn(pos.shape[0], 6, generator=gen)
+        g["feat"] = feat
+        g["feat_diffs"] = rconv.compute_feature_diffs(feat, curve, batch)
+        fsub = torch.randn(sub.shape[0], 8, generator=gen)
+        g["feat_sub"] = fsub
+        g["interp3"] = rpo.knn_interpolate_pytorch3d(fsub, pos[sub], pos, batch[sub], batch, k=3)
+        fidx = torch.randn(idx.shape[0], 8, generator=gen)
+        g["feat_idx"] = fidx
+        g["interp1d"] = rpo.knn_interpolate_1D_pytorch3d(fidx, idx, pos, batch, curve, 3)
+
+        from curvecloudnet_b200.synthetic import randomize_model_
+        for ver, cls, k in (("v2", rconv.SymmetricCurve1DConvV2, 5), ("v1", rconv.SymmetricCurve1DConvFastV1, 7)):
+            torch.manual_seed(3)
+            mod = cls([9, 16, 12], k, with_xyz=True, with_diff=True)
+            randomize_model_(mod, 55)
+            mod.eval()
+            with torch.no_grad():
+                g["conv_%s_out" % ver] = mod(feat, pos, batch, curve)[0]
+            g["conv_%s_k" % ver] = k
+        out[cname] = g
+
+    # a3: curve grouping of raw sweeps
+    from curvecloudnet_b200.synthetic import raycast_driving_scan
+    gc = _reference_get_curves()
+    raw = raycast_driving_scan(31)
+    n = 6000
+    pts = torch.from_numpy(raw.points[:n])
+    beam = torch.from_numpy(raw.beam_ids[:n])
+
+    class _Self:
+        CURVE_THRESH = 0.08
+    labels = torch.zeros(n, 1, dtype=torch.uint8)
+    refl = torch.from_numpy(raw.reflectance[:n])[:, None]
+    p2, cid, _, _, inv = gc(_Self(), pts.clone(), beam.clone(), labels, refl)
+    out["get_curves"] = {"points": pts, "beam": beam, "sorted_points": p2, "curve_idxs": cid, "inv_reorder": inv}
+    return out
+
+
+def make_models(rbase):
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch, randomize_model_
+    out = {}
+    specs = {
+        "nuscenes": lambda: driving_scan_batch([41, 42], subsample=1500),
+        "shapenet-class": lambda: object_scan_batch([43, 44], n_points=768),
+        "shapenet-seg": lambda: object_scan_batch([45, 46], n_points=768),
+    }
+    for name, mk in specs.items():
+        data = mk()
+        if name == "shapenet-class":
+            del data.labels          # shapenet_classification.py:24-25 deletes it before the call
+        model = build_model(rbase.ModelBase, name)
+        randomize_model_(model, 1234)
+        model.eval()
+        torch.manual_seed(77)
+        with torch.no_grad():
+            logits = model(data, labels=data.y)
+        out[name] = {"data_seeds": {"nuscenes": [41, 42], "shapenet-class": [43, 44], "shapenet-seg": [45, 46]}[name],
+                     "pos": data.pos, "x": data.x, "batch": data.batch, "curve": data.curve_idxs,
+                     "labels": getattr(data, "labels", None), "weight_seed": 1234, "rng_seed": 77,
+                     "logits": logits}
+        print(name, tuple(logits.shape), float(logits.abs().max()))
+    return out
+
+
+def _compact(obj):
+    """int64 -> int32 (all values are small indices) to keep the committed fixtures small;
+    tests/golden_utils.load() widens them again."""
+    if torch.is_tensor(obj):
+        return obj.to(torch.int32) if obj.dtype == torch.int64 else obj
+    if isinstance(obj, dict):
+        return {k: _compact(v) for k, v in obj.items()}
+    return obj
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    rpo, rbase, rconv, rfps = _import_reference()
+    torch.save(_compact(make_ops(rpo, rconv, rfps)), os.path.join(OUT, "ops.pt"))
+    torch.save(_compact(make_models(rbase)), os.path.join(OUT, "models.pt"))
+    for f in ("ops.pt", "models.pt"):
+        print(f, os.path.getsize(os.path.join(OUT, f)) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,97 @@
+"""The oracle's restatement of the reference's own python against the golden vectors that
+oracle/make_golden.py produced by running the REAL reference sources (CPU, not gpu)."""
+import pytest
+import torch
+
+from golden_utils import FixedDraws, load, rel_err
+from oracle import ccn_modules as M
+from oracle import ccn_point_ops as po
+
+OPS = load("ops.pt")
+CASES = [c for c in OPS if c != "get_curves"]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_csr_helpers(case):
+    g = OPS[case]
+    assert torch.equal(po.curve_ids_global(g["curve"], g["batch"]), g["glob"])
+    assert torch.equal(po.batch_to_ptr(g["batch"]), g["ptr"])
+    assert torch.equal(po.batch_to_ptr(g["batch"], True), g["ptr_ends"])
+    padded, mask = po.pad_by_batch(g["pos"], g["batch"])
+    assert torch.equal(mask, g["padded_mask"])
+    assert torch.allclose(padded.sum(dim=1), g["padded_sum"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_samplers(case):
+    g = OPS[case]
+    assert torch.equal(po.curve_fps(g["pos"], g["batch"], g["curve"], g["curvefps_arclen"], g["curvefps_u"]),
+                       g["curvefps_idx"])
+    assert torch.equal(po.voxel_fps(g["pos"], g["batch"], g["voxel_size"], g["voxel_noise"]), g["voxel_idx"])
+    d = FixedDraws(starts=g["fps_starts"].tolist())
+    assert torch.equal(po.fps_sorted(g["pos"], g["batch"], g["fps_ratio"], d), g["fps_idx"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_groupings(case):
+    g = OPS[case]
+    pos, batch, curve, idx, sub = g["pos"], g["batch"], g["curve"], g["curvefps_idx"], g["voxel_idx"]
+    row, col = po.radius_1d_group_subset(pos, idx, curve, batch, g["r1d_radius"])
+    assert torch.equal(row, g["r1d_row"]) and torch.equal(col, g["r1d_col"])
+    row, col = po.knn_1d_group_superset(pos, idx, curve, batch, 3)
+    assert torch.equal(row, g["s1d_row"]) and torch.equal(col, g["s1d_col"])
+    r = g["knn_radius"]
+    dense, _, _ = po.knn_ball_group(pos[sub], pos, batch[sub], batch, "knn", radius=r, knn=16, return_dense=True)
+    assert torch.equal(dense, g["frnn_dense"])
+    row, col = po.knn_ball_group(pos[sub], pos, batch[sub], batch, "knn", radius=r, knn=16)
+    assert torch.equal(row, g["frnn_row"]) and torch.equal(col, g["frnn_col"])
+    row, col = po.knn_ball_group(pos[sub], pos, batch[sub], batch, "ball-group", radius=r)
+    assert torch.equal(row, g["ball_row"]) and torch.equal(col, g["ball_col"])
+    row, col = po.knn_ball_group(pos, pos[sub], batch, batch[sub], "knn", knn=3, accel_knn=False)
+    assert torch.equal(row, g["knn3_row"]) and torch.equal(col, g["knn3_col"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_float_ops(case):
+    from curvecloudnet_b200.synthetic import randomize_model_
+    g = OPS[case]
+    pos, batch, curve, idx, sub = g["pos"], g["batch"], g["curve"], g["curvefps_idx"], g["voxel_idx"]
+    assert torch.equal(M.feature_diffs(g["feat"], curve, batch), g["feat_diffs"])
+    y = po.knn_interpolate(g["feat_sub"], pos[sub], pos, batch[sub], batch, k=3)
+    assert rel_err(y, g["interp3"]) < 1e-6
+    y = po.knn_interpolate_1d(g["feat_idx"], idx, pos, batch, curve, 3)
+    assert rel_err(y, g["interp1d"]) < 1e-6
+    for ver, cls in (("v2", M.SymmetricCurve1DConvV2), ("v1", M.SymmetricCurve1DConvFastV1)):
+        mod = cls([9, 16, 12], g["conv_%s_k" % ver], with_xyz=True, with_diff=True)
+        randomize_model_(mod, 55)
+        mod.eval()
+        with torch.no_grad():
+            out = mod(g["feat"], pos, batch, curve)[0]
+        assert rel_err(out, g["conv_%s_out" % ver]) < 1e-6
+
+
+def test_get_curves():
+    g = OPS["get_curves"]
+    reorder, inv, cid = po.get_curves(g["points"], g["beam"], 0.08)
+    assert torch.equal(inv, g["inv_reorder"])
+    assert torch.equal(cid, g["curve_idxs"])
+    assert torch.equal(g["points"][reorder], g["sorted_points"])
+
+
+@pytest.mark.parametrize("name", ["nuscenes", "shapenet-class", "shapenet-seg"])
+def test_model_logits(name):
+    """End to end: oracle ModelBase == the reference's ModelBase (run over the shims) on the same
+    seeded weights, inputs and RNG draws."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import ScanBatch, randomize_model_
+    from oracle.ccn_model import ModelBase
+    g = load("models.pt")[name]
+    data = ScanBatch(g["x"], g["pos"], g["batch"], g["curve"], None, g["labels"])
+    model = build_model(ModelBase, name)
+    randomize_model_(model, g["weight_seed"])
+    model.eval()
+    torch.manual_seed(g["rng_seed"])
+    with torch.no_grad():
+        logits = model(data)
+    assert logits.shape == g["logits"].shape
+    assert rel_err(logits, g["logits"]) < 2e-6
