@@ -1,0 +1,284 @@
+// Gather / segmented aggregation kernels around the shared MLPs.
+// They replace the reference's materialised x[col] gathers, torch_scatter atomics
+// (scatter_max/add/mean, reference src/models/modules/point_conv.py:71-93), torch_geometric
+// segment softmax, frnn_gather (third_party/FRNN/frnn/frnn.py:351-397) and the dense masked max of
+// StaticEdgeConv.forward_fast (src/models/modules/dgcnn.py:158-207).  All sums run in edge order
+// (deterministic), one thread per (segment, channel) with channels on the fast axis.
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float apply_act(float y, int act, float slope) {
+    if (act == CCN_ACT_RELU) return fmaxf(y, 0.f);
+    if (act == CCN_ACT_LEAKY) return y > 0.f ? y : y * slope;
+    return y;
+}
+
+__global__ void gather_rows_kernel(const float* __restrict__ src, int64_t lds, const int64_t* __restrict__ idx,
+                                   int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
+    const int64_t total = n * (int64_t)c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / c;
+        const int k = (int)(t - i * c);
+        const int64_t s = idx ? idx[i] : i;
+        dst[i * ldd + k] = src[s * lds + k];
+    }
+}
+
+__global__ void gather_i64_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ idx, int64_t n,
+                                  int64_t* __restrict__ dst) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+
+// CSR from a dense (nq, K) neighbour table whose valid entries lead every row.
+__global__ void dense_to_csr_kernel(const int32_t* __restrict__ idx, const int32_t* __restrict__ row_ptr, int64_t nq,
+                                    int K, int32_t* __restrict__ erow, int32_t* __restrict__ ecol) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= nq * K) return;
+    const int64_t q = t / K;
+    const int k = (int)(t - q * K);
+    const int b = row_ptr[q], cnt = row_ptr[q + 1] - b;
+    if (k < cnt) {
+        erow[b + k] = (int32_t)q;
+        ecol[b + k] = idx[t];
+    }
+}
+
+__global__ void csr_rows_kernel(const int32_t* __restrict__ row_ptr, int64_t nq, int32_t* __restrict__ erow) {
+    const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    for (int e = row_ptr[q]; e < row_ptr[q + 1]; ++e) erow[e] = (int32_t)q;
+}
+
+// First layer of PointNetConv2's local_nn, decomposed (point_conv.py:60-69):
+//   W [x_j ; (pos_j - pos_i)/r] + b = H[j] + Wp (pos_j - pos_i)/r + b,   H = x W_x^T computed per SOURCE point.
+__global__ void edge_layer1_kernel(const float* __restrict__ H, int64_t ldh, const float* __restrict__ wp,
+                                   const float* __restrict__ bias, const float* __restrict__ pos_src,
+                                   const float* __restrict__ pos_dst, const int32_t* __restrict__ erow,
+                                   const int32_t* __restrict__ ecol, int64_t E, int c, float inv_norm_is_div,
+                                   float radius, int act, float slope, float* __restrict__ out, int64_t ldo) {
+    const int64_t total = E * (int64_t)c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = t / c;
+        const int k = (int)(t - e * c);
+        const int j = ecol[e], i = erow[e];
+        float rx = __fsub_rn(pos_src[3 * j], pos_dst[3 * i]);
+        float ry = __fsub_rn(pos_src[3 * j + 1], pos_dst[3 * i + 1]);
+        float rz = __fsub_rn(pos_src[3 * j + 2], pos_dst[3 * i + 2]);
+        if (inv_norm_is_div != 0.f) { rx = __fdiv_rn(rx, radius); ry = __fdiv_rn(ry, radius); rz = __fdiv_rn(rz, radius); }
+        float y = bias ? bias[k] : 0.f;
+        if (H) y += H[(int64_t)j * ldh + k];
+        y = fmaf(wp[k], rx, y);
+        y = fmaf(wp[c + k], ry, y);
+        y = fmaf(wp[2 * c + k], rz, y);
+        out[e * ldo + k] = apply_act(y, act, slope);
+    }
+}
+
+// Segmented aggregation over CSR rows.  mode: 0 max (empty -> 0), 1 mean, 2 sum sigmoid(att)*msg,
+// 3 sum softmax_row(att)*msg with exp(a - max)/(sum + 1e-16) (torch_geometric.utils.softmax).
+__global__ void seg_aggregate_kernel(const float* __restrict__ msg, int64_t ldm, const float* __restrict__ att,
+                                     int64_t lda, const int32_t* __restrict__ row_ptr, int64_t nq, int c, int mode,
+                                     float* __restrict__ out, int64_t ldo) {
+    const int64_t total = nq * (int64_t)c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t q = t / c;
+        const int k = (int)(t - q * c);
+        const int b = row_ptr[q], e = row_ptr[q + 1];
+        float r = 0.f;
+        if (mode == CCN_AGG_MAX) {
+            if (e > b) {
+                r = msg[(int64_t)b * ldm + k];
+                for (int j = b + 1; j < e; ++j) r = fmaxf(r, msg[(int64_t)j * ldm + k]);
+            }
+        } else if (mode == CCN_AGG_MEAN) {
+            for (int j = b; j < e; ++j) r += msg[(int64_t)j * ldm + k];
+            r = r / fmaxf((float)(e - b), 1.f);
+        } else if (mode == CCN_AGG_WSUM) {
+            for (int j = b; j < e; ++j) {
+                const float a = att[(int64_t)j * lda + k];
+                r += msg[(int64_t)j * ldm + k] * (1.f / (1.f + expf(-a)));
+            }
+        } else {
+            float m = -INFINITY;
+            for (int j = b; j < e; ++j) m = fmaxf(m, att[(int64_t)j * lda + k]);
+            float s = 0.f;
+            for (int j = b; j < e; ++j) s += expf(att[(int64_t)j * lda + k] - m);
+            const float inv = 1.f / (s + 1e-16f);
+            for (int j = b; j < e; ++j) r += msg[(int64_t)j * ldm + k] * (expf(att[(int64_t)j * lda + k] - m) * inv);
+        }
+        out[q * ldo + k] = r;
+    }
+}
+
+// StaticEdgeConv.forward_fast first layer, decomposed (dgcnn.py:166-173):
+//   W [x_j ; x_i - x_j] + b = (Wa - Wb) x_j + (Wb x_i + b) = P[j] + Q[i];  x_j = 0 for missing neighbours.
+// Row layout: (i, 0) = self loop, (i, 1+k) = idx[i][k].
+__global__ void sgcnn_layer1_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ idx,
+                                    int64_t n, int K, int c, int act, float slope, float* __restrict__ out,
+                                    int64_t ldo) {
+    const int G = K + 1;
+    const int64_t total = n * (int64_t)G * c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = t / c;
+        const int k = (int)(t - row * c);
+        const int64_t i = row / G;
+        const int g = (int)(row - i * G);
+        const int j = g == 0 ? (int)i : idx[i * K + g - 1];
+        float y = PQ[i * ldpq + c + k];
+        if (j >= 0) y += PQ[(int64_t)j * ldpq + k];
+        out[row * ldo + k] = apply_act(y, act, slope);
+    }
+}
+
+__global__ void edge_pair_layer1_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ erow,
+                                        const int32_t* __restrict__ ecol, int64_t E, int c, int act, float slope,
+                                        float* __restrict__ out, int64_t ldo) {
+    const int64_t total = E * (int64_t)c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = t / c;
+        const int k = (int)(t - e * c);
+        const float y = PQ[(int64_t)ecol[e] * ldpq + k] + PQ[(int64_t)erow[e] * ldpq + c + k];
+        out[e * ldo + k] = apply_act(y, act, slope);
+    }
+}
+
+// max over the K+1 rows of every point, invalid rows count as -100 (dgcnn.py:187-189).
+__global__ void group_max_dense_kernel(const float* __restrict__ feat, int64_t ldf, const int32_t* __restrict__ idx,
+                                       int64_t n, int K, int c, float* __restrict__ out, int64_t ldo) {
+    const int G = K + 1;
+    const int64_t total = n * (int64_t)c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / c;
+        const int k = (int)(t - i * c);
+        float r = feat[(i * G) * ldf + k];
+        for (int g = 1; g < G; ++g) {
+            const float v = idx[i * K + g - 1] >= 0 ? feat[(i * G + g) * ldf + k] : -100.f;
+            r = fmaxf(r, v);
+        }
+        out[i * ldo + k] = r;
+    }
+}
+
+// y[i] = sum_k w x[nbr] / sum_k w   (point_ops.py:336-341, 350-355); w = 1/clamp(d2, 1e-16) when from_d2.
+__global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, const int32_t* __restrict__ nbr,
+                                    const float* __restrict__ wgt, int from_d2, int64_t n, int knn, int c,
+                                    float* __restrict__ out, int64_t ldo) {
+    const int64_t total = n * (int64_t)c;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / c;
+        const int k = (int)(t - i * c);
+        float num = 0.f, den = 0.f;
+        for (int s = 0; s < knn; ++s) {
+            const int j = nbr[i * knn + s];
+            if (j < 0) continue;
+            float w = wgt[i * knn + s];
+            if (from_d2) w = __fdiv_rn(1.f, fmaxf(w, 1e-16f));
+            num = __fadd_rn(num, __fmul_rn(x[(int64_t)j * ldx + k], w));
+            den = __fadd_rn(den, w);
+        }
+        out[i * ldo + k] = __fdiv_rn(num, den);
+    }
+}
+
+}  // namespace
+
+#define CCN_ELT_GRID(total) ccn_grid((total), 256, 148LL * 32)
+
+extern "C" int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t* idx, int64_t n, int32_t c,
+                                   float* dst, int64_t ldd, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && c > 0 && src && dst && lds >= c && ldd >= c);
+    if (n == 0) return CCN_OK;
+    gather_rows_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, n, c, dst, ldd);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_gather_i64(const int64_t* src, const int64_t* idx, int64_t n, int64_t* dst, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && src && idx && dst);
+    if (n == 0) return CCN_OK;
+    gather_i64_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(src, idx, n, dst);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int64_t nq, int32_t K, int32_t* erow,
+                                int32_t* ecol, ccn_stream_t stream) {
+    CCN_REQUIRE(nq >= 0 && K >= 1 && idx && row_ptr && erow && ecol);
+    if (nq == 0) return CCN_OK;
+    dense_to_csr_kernel<<<ccn_blocks_exact(nq * K, 256), 256, 0, (cudaStream_t)stream>>>(idx, row_ptr, nq, K, erow, ecol);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_csr_rows(const int32_t* row_ptr, int64_t nq, int32_t* erow, ccn_stream_t stream) {
+    CCN_REQUIRE(nq >= 0 && row_ptr && erow);
+    if (nq == 0) return CCN_OK;
+    csr_rows_kernel<<<ccn_blocks_exact(nq, 256), 256, 0, (cudaStream_t)stream>>>(row_ptr, nq, erow);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_edge_layer1(const float* H, int64_t ldh, const float* wp, const float* bias, const float* pos_src,
+                               const float* pos_dst, const int32_t* erow, const int32_t* ecol, int64_t E, int32_t c,
+                               float normalize_radius, int32_t act, float slope, float* out, int64_t ldo,
+                               ccn_stream_t stream) {
+    CCN_REQUIRE(E >= 0 && c > 0 && wp && pos_src && pos_dst && erow && ecol && out && ldo >= c);
+    if (E == 0) return CCN_OK;
+    edge_layer1_kernel<<<CCN_ELT_GRID(E * c), 256, 0, (cudaStream_t)stream>>>(
+        H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
+        slope, out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_edge_pair_layer1(const float* PQ, int64_t ldpq, const int32_t* erow, const int32_t* ecol, int64_t E,
+                                    int32_t c, int32_t act, float slope, float* out, int64_t ldo, ccn_stream_t stream) {
+    CCN_REQUIRE(E >= 0 && c > 0 && PQ && erow && ecol && out && ldpq >= 2 * c && ldo >= c);
+    if (E == 0) return CCN_OK;
+    edge_pair_layer1_kernel<<<CCN_ELT_GRID(E * c), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, erow, ecol, E, c, act,
+                                                                                   slope, out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
+                                 int64_t nq, int32_t c, int32_t mode, float* out, int64_t ldo, ccn_stream_t stream) {
+    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 3);
+    CCN_REQUIRE(mode < 2 || att);
+    if (nq == 0) return CCN_OK;
+    seg_aggregate_kernel<<<CCN_ELT_GRID(nq * c), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq, c,
+                                                                                 mode, out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_sgcnn_layer1(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c,
+                                int32_t act, float slope, float* out, int64_t ldo, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && PQ && out && ldpq >= 2 * c && ldo >= c && (K == 0 || idx));
+    if (n == 0) return CCN_OK;
+    sgcnn_layer1_kernel<<<CCN_ELT_GRID(n * (K + 1) * c), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, idx, n, K, c, act,
+                                                                                        slope, out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_group_max_dense(const float* feat, int64_t ldf, const int32_t* idx, int64_t n, int32_t K,
+                                   int32_t c, float* out, int64_t ldo, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && feat && out);
+    if (n == 0) return CCN_OK;
+    group_max_dense_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(feat, ldf, idx, n, K, c, out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr, const float* wgt, int32_t from_d2,
+                                int64_t n, int32_t knn, int32_t c, float* out, int64_t ldo, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && knn >= 1 && c > 0 && x && nbr && wgt && out);
+    if (n == 0) return CCN_OK;
+    interp_blend_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn, c,
+                                                                               out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}

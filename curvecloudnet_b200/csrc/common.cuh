@@ -1,0 +1,84 @@
+// Shared device/host helpers for libccn_b200 (sm_100a).  See include/ccn_b200.h for the C-ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ccn_b200.h"
+
+#define CCN_CHECK_LAUNCH()                                 \
+    do {                                                   \
+        cudaError_t e__ = cudaGetLastError();              \
+        if (e__ != cudaSuccess) return (int)e__;           \
+    } while (0)
+
+#define CCN_REQUIRE(cond)                 \
+    do {                                  \
+        if (!(cond)) return CCN_EINVAL;   \
+    } while (0)
+
+static inline unsigned ccn_grid(int64_t work, int threads, int64_t cap = 148LL * 64) {
+    int64_t b = (work + threads - 1) / threads;
+    if (b < 1) b = 1;
+    if (b > cap) b = cap;
+    return (unsigned)b;
+}
+
+static inline unsigned ccn_blocks_exact(int64_t work, int threads) {
+    int64_t b = (work + threads - 1) / threads;
+    return (unsigned)(b < 1 ? 1 : b);
+}
+
+// ((dx*dx)+(dy*dy))+(dz*dz), every operation rounded separately (no FMA contraction): the total
+// order (d2, index) that decides every neighbour index is defined on exactly this value
+// (oracle/tp_ops.py sqdist3).
+__device__ __forceinline__ float ccn_sqdist3(float ax, float ay, float az, float bx, float by, float bz) {
+    float dx = __fsub_rn(ax, bx), dy = __fsub_rn(ay, by), dz = __fsub_rn(az, bz);
+    return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+
+// |v| as torch.linalg.norm(v, dim=-1) computes it for (N,3) f32 on CPU:
+// sqrt(fma(z,z,fma(y,y,x*x))) with a correctly rounded sqrt (oracle/ccn_point_ops.py norm3).
+__device__ __forceinline__ float ccn_norm3(float x, float y, float z) {
+    return __fsqrt_rn(__fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x))));
+}
+
+// (d2, idx) packed so that unsigned 64-bit order == lexicographic (d2, idx) order for d2 >= 0.
+__device__ __forceinline__ unsigned long long ccn_pack_key(float d2, int idx) {
+    return ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)idx;
+}
+
+__device__ __forceinline__ int ccn_lane() { return threadIdx.x & 31; }
+__device__ __forceinline__ int ccn_warp() { return threadIdx.x >> 5; }
+
+// ------------------------------------------------------------------------------------------
+// Block-wide exclusive scan (blockDim.x a multiple of 32, <= 1024).  `smem` holds 33 T's.
+// Returns the exclusive prefix of `v`; *total receives the block sum (same in every thread).
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ T ccn_block_excl_scan(T v, T* smem, T* total) {
+    const int lane = ccn_lane(), warp = ccn_warp(), nwarp = (blockDim.x + 31) >> 5;
+    T incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        T t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) smem[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        T w = lane < nwarp ? smem[lane] : T(0);
+        T wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            T t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        smem[lane] = wi - w;                 // exclusive prefix of the warp sums
+        if (lane == 31) smem[32] = wi;       // block total
+    }
+    __syncthreads();
+    T res = smem[warp] + (incl - v);
+    *total = smem[32];
+    __syncthreads();                         // smem may be reused by the caller's next round
+    return res;
+}

@@ -1,0 +1,405 @@
+"""Step modules with the reference's class names, constructor arguments, forward signatures and
+parameter names (reference src/models/modules/{fast_conv1d,pointnet2,point_conv,dgcnn,mlp,skip_connect}.py),
+so `ModelBase` configs and checkpoints drop in.  Bodies call the sm_100a kernels through `ops`;
+there is no torch arithmetic on the per-scan path.
+
+Inference (eval) path only in this round: BatchNorm uses running statistics folded into the weights.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .nn import DEFAULT_DRAWS, MLP, Draws, fold_batchnorm, get_cache
+
+
+def _cat_xyz(x, pos, with_xyz):
+    if not with_xyz:
+        return x
+    return pos if x is None else ops.concat_cols([x, pos])
+
+
+# ----------------------------------------------------------------------------------------------
+# fast_conv1d.py
+# ----------------------------------------------------------------------------------------------
+class SymmetricConv1d(nn.Module):
+    """Parameter holder of fast_conv1d.py:148-187: weight (C_out, C_in, k//2+1) mirrored around tap 0."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, bias=True):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, kernel_size))
+        self.bias = nn.Parameter(torch.empty(out_channels)) if bias else None
+        nn.init.kaiming_uniform_(self.weight, a=5 ** 0.5)
+        if bias:
+            bound = 1.0 / (in_channels * kernel_size) ** 0.5
+            nn.init.uniform_(self.bias, -bound, bound)
+
+    def full_weight(self):
+        w = self.weight
+        if w.shape[2] > 1:
+            w = torch.cat([torch.flip(w[:, :, 1:], dims=[2]), w], dim=2)   # fast_conv1d.py:175-178
+        return w
+
+
+class _CurveConvBase(nn.Module):
+    def __init__(self, feat_dims, kernel_size, bias, with_xyz, with_diff, diff_every_layer):
+        super().__init__()
+        self.kernel_size, self.feat_dims = kernel_size, list(feat_dims)
+        self.with_xyz, self.with_diff = with_xyz, with_diff
+        ku = kernel_size // 2 + 1
+        convs, norms = [], []
+        for i in range(1, len(feat_dims)):
+            doubled = with_diff and (diff_every_layer or i == 1)
+            convs.append(SymmetricConv1d(feat_dims[i - 1] * (2 if doubled else 1), feat_dims[i], ku, bias=bias))
+            norms.append(nn.BatchNorm1d(feat_dims[i]))
+        self.conv_modules = nn.ModuleList(convs)
+        self.norm_modules = nn.ModuleList(norms)
+        self._folded, self._folded_key = None, None
+
+    def _layers(self):
+        """[(w (k, C_in, C_out), b (C_out))]: mirrored kernel with BatchNorm(eval) folded."""
+        if self.training:
+            raise NotImplementedError("curvecloudnet_b200 round 1 implements the inference (eval) path")
+        key = tuple(c.weight._version + n.weight._version + n.running_mean._version + n.running_var._version
+                    for c, n in zip(self.conv_modules, self.norm_modules)) + (self.conv_modules[0].weight.data_ptr(),)
+        if self._folded is None or key != self._folded_key:
+            out = []
+            for conv, norm in zip(self.conv_modules, self.norm_modules):
+                w, b = fold_batchnorm(conv.full_weight(), conv.bias, norm)
+                out.append((w.permute(2, 1, 0).contiguous(), b))
+            self._folded, self._folded_key = out, key
+        return self._folded
+
+
+class SymmetricCurve1DConvV2(_CurveConvBase):
+    """fast_conv1d.py:11-75.  One zero-padded signal for the whole stack ((k//2)*L pad rows before every
+    curve and after the last); conv + BN + LeakyReLU run over pad rows too.  Here: layer 1 reads the
+    points through the pad-row map, middle layers work on the padded signal, the last layer writes
+    valid rows only."""
+
+    def __init__(self, feat_dims=(64, 64, 128), kernel_size=5, bias=True, device=None, dtype=None,
+                 with_xyz=False, with_diff=False):
+        super().__init__(feat_dims, kernel_size, bias, with_xyz, with_diff, diff_every_layer=False)
+
+    def forward(self, x, pos, batch, point2curveidx, **kwargs):
+        topo = get_cache(kwargs).topology(batch, point2curveidx)
+        n = pos.shape[0]
+        feats = ops.curve_feat_prep(x, pos, self.with_xyz, self.with_diff, topo.curve_ord)
+        layers = self._layers()
+        k = self.kernel_size
+        pad = (k // 2) * len(layers) if k > 1 else 0
+        row2pt = ops.curve_row_map(topo, pad)
+        rows = row2pt.shape[0]
+        sig = feats
+        for li, (w, b) in enumerate(layers):
+            first, last = li == 0, li == len(layers) - 1
+            sig = ops.curve_conv_layer(sig, w, b, row2pt, rows, n if last else rows, k, first, last)
+        return sig, pos, batch, point2curveidx
+
+
+class SymmetricCurve1DConvFastV1(_CurveConvBase):
+    """fast_conv1d.py:78-145.  Every layer: feature differences (C_in doubles each layer), fresh k//2
+    zero rows between curves, conv, BN over the valid rows, LeakyReLU."""
+
+    def __init__(self, feat_dims=(64, 64, 128), kernel_size=5, bias=True, device=None, dtype=None,
+                 with_xyz=False, with_diff=False):
+        super().__init__(feat_dims, kernel_size, bias, with_xyz, with_diff, diff_every_layer=True)
+
+    def forward(self, x, pos, batch, point2curveidx, **kwargs):
+        topo = get_cache(kwargs).topology(batch, point2curveidx)
+        n = pos.shape[0]
+        k = self.kernel_size
+        pad = k // 2 if k > 1 else 0
+        row2pt = ops.curve_row_map(topo, pad)
+        rows = row2pt.shape[0]
+        for li, (w, b) in enumerate(self._layers()):
+            feats = ops.curve_feat_prep(x, pos, self.with_xyz and li == 0, self.with_diff, topo.curve_ord)
+            x = ops.curve_conv_layer(feats, w, b, row2pt, rows, n, k, True, True)
+        return x, pos, batch, point2curveidx
+
+
+# ----------------------------------------------------------------------------------------------
+# point_conv.py
+# ----------------------------------------------------------------------------------------------
+class PointNetConv2(nn.Module):
+    """point_conv.py:12-93 over a CSR edge list (target-sorted, as every reference call site builds it).
+    message  = local_nn(cat[x_j, (pos_j - pos_i) / normalize_radius])            (:60-69)
+    aggregate = max | mean | sum sigmoid(attend_nn(m)) m | sum softmax_i(attend_nn(m)) m   (:71-93)
+    The first Linear of local_nn is decomposed: its x_j part is one GEMM over the SOURCE points
+    (N_src rows instead of E), its 3 positional columns are added per edge together with the folded
+    BatchNorm shift and the activation (ccn_edge_layer1); the remaining layers run per edge."""
+
+    def __init__(self, local_nn=None, global_nn=None, attend_nn=None, add_self_loops=True, aggr_type="max",
+                 normalize_radius=None, **kwargs):
+        super().__init__()
+        assert aggr_type in ["max", "attend", "mean", "weighted-sum"]
+        if add_self_loops:
+            raise NotImplementedError("every reference call site passes add_self_loops=False")
+        if local_nn is None:
+            raise NotImplementedError("PointNetConv2 without local_nn does not occur on the path")
+        self.local_nn, self.global_nn, self.attend_nn = local_nn, global_nn, attend_nn
+        self.aggr_type, self.normalize_radius = aggr_type, normalize_radius
+        self._dec, self._dec_src = None, None
+
+    def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR):
+        layers = self.local_nn.layers()
+        w0, b0, act0, slope0 = layers[0]
+        cx = 0 if x_src is None else x_src.shape[1]
+        assert w0.shape[1] == cx + 3, "local_nn input width %d != %d feature + 3 position columns" % (w0.shape[1], cx)
+        if self._dec is None or self._dec_src is not layers:   # weight preparation, once per weight version
+            self._dec, self._dec_src = (w0[:, :cx].contiguous(), w0[:, cx:].t().contiguous()), layers
+        wx, wp = self._dec                                     # (C1, cx), (3, C1)
+        H = ops.linear(x_src, wx, None) if cx > 0 else None
+        msg = ops.edge_layer1(H, wp, b0, pos_src, pos_dst, edges, self.normalize_radius, act0, slope0)
+        msg = self.local_nn.forward_from(msg, 1)
+        if self.aggr_type in ("max", "mean"):
+            out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, self.aggr_type)
+        else:
+            att = self.attend_nn(msg)
+            out = ops.seg_aggregate(msg, att, edges.row_ptr, edges.nq, self.aggr_type)
+        if self.global_nn is not None:
+            out = self.global_nn(out)
+        return out
+
+
+# ----------------------------------------------------------------------------------------------
+# pointnet2.py
+# ----------------------------------------------------------------------------------------------
+def _subset(x, pos, batch, curve, idx):
+    return (None if x is None else ops.gather_rows(x, idx), ops.gather_rows(pos, idx), ops.gather_i64(batch, idx),
+            None if curve is None else ops.gather_i64(curve, idx))
+
+
+class SAModule(nn.Module):
+    """pointnet2.py:33-78: down-sample ('random' | 'curve-fps' | 'voxel' | 'fps'), group with FRNN kNN
+    (use_fast_knn) or ball_query K=128, PointNetConv2."""
+
+    def __init__(self, ratio, r, nn, k, curve_fps_arclen=None, voxel_size=None, downsample_type="random",
+                 attend_nn=None, aggr_type="max", normalize_radius=False, use_fast_knn=True, **kwargs):
+        super().__init__()
+        assert downsample_type in ["curve-fps", "random", "fps", "voxel"]
+        self.ratio, self.r, self.knn = ratio, r, k
+        self.downsample_type, self.use_fast_knn = downsample_type, use_fast_knn
+        self.curve_fps_arclen, self.voxel_size = curve_fps_arclen, voxel_size
+        self.normalize_radius = r if normalize_radius else None
+        self.conv = PointNetConv2(nn, add_self_loops=False, aggr_type=aggr_type, attend_nn=attend_nn,
+                                  normalize_radius=self.normalize_radius)
+
+    def forward(self, x, pos, batch, point2curveidx=None, draws: Draws = DEFAULT_DRAWS, **kwargs):
+        cache = get_cache(kwargs)
+        sptr = cache.sample_ptr(batch)
+        n = pos.shape[0]
+        if self.downsample_type == "random":
+            perm = draws.randperm(n)[:int(n * self.ratio)].sort()[0]         # pointnet2.py:49-52
+            idx = perm.to(pos.device)
+            sptr_q = None
+        elif self.downsample_type == "curve-fps":
+            topo = cache.topology(batch, point2curveidx)
+            idx, sptr_q = ops.curve_fps(pos, topo, self.curve_fps_arclen, draws.curve_phase())
+        elif self.downsample_type == "voxel":
+            idx, sptr_q = ops.voxel_fps(pos, batch, self.voxel_size, draws.voxel_noise(n), sptr.n_samples)
+        else:
+            idx, sptr_q = fps_sorted(pos, sptr, self.ratio, draws)
+        xq, posq, batchq, curveq = _subset(x, pos, batch, point2curveidx, idx)
+        if sptr_q is not None:
+            cache.put_sample_ptr(batchq, sptr_q)
+        if self.use_fast_knn:
+            nbr, _, cnt = ops.frnn_knn(posq, batchq, pos, batch, sptr, self.knn, self.r, want_cnt=True)
+        else:
+            nbr, cnt = ops.ball_query(posq, batchq, pos, sptr, self.r, 128)
+        edges = ops.dense_to_csr(nbr, cnt)
+        out = self.conv.forward_edges(x, pos, posq, edges)
+        return out, posq, batchq, curveq
+
+
+def fps_sorted(pos, sptr: ops.SamplePtr, ratio, draws: Draws):
+    """fps_pytorch3d (point_ops.py:57-70): K = ceil(len*ratio) in f32, random start per cloud, sorted result."""
+    lens = sptr.lengths
+    ksel = ops.fps_count(lens, ratio)
+    starts = [draws.fps_start(l) for l in lens]
+    idx = ops.fps(pos, sptr, ksel, starts)
+    off, host = 0, [0]
+    for k, l in zip(ksel, lens):
+        off += min(k, l)
+        host.append(off)
+    dev = torch.tensor(host, dtype=torch.int32).to(pos.device, non_blocking=True)
+    return idx, ops.SamplePtr(dev, host)
+
+
+class GlobalSAModule(nn.Module):
+    """pointnet2.py:81-116: nn(cat[x,pos]) then per-sample max (or mean)."""
+
+    def __init__(self, nn, **kwargs):
+        super().__init__()
+        self.nn = nn
+        self.pooling = kwargs.get("pooling", "max")
+        if self.pooling not in ("max", "mean"):
+            raise NotImplementedError(self.pooling)
+
+    def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        sptr = get_cache(kwargs).sample_ptr(batch)
+        h = self.nn(ops.concat_cols([x, pos]))
+        out = ops.seg_aggregate(h, None, sptr.dev, sptr.n_samples, self.pooling)
+        first = torch.tensor(sptr.host[:-1], dtype=torch.int64).to(pos.device)
+        _, posf, batchf, curvef = _subset(None, pos, batch, point2curveidx, first)
+        return out, posf, batchf, curvef
+
+
+def _fp_concat(x, x_skip, pos_skip, with_xyz):
+    """pointnet2.py:132-139 / :194-201."""
+    parts = [x]
+    if x_skip is not None:
+        parts.append(x_skip)
+    if with_xyz:
+        parts.append(pos_skip[:, :3])
+    return ops.concat_cols(parts) if len(parts) > 1 else x
+
+
+class FPModule(nn.Module):
+    """pointnet2.py:119-143: exact 3-NN inverse-d2 interpolation onto the skip level, concat, MLP."""
+
+    def __init__(self, k, nn, with_xyz=False):
+        super().__init__()
+        self.k, self.nn, self.with_xyz = k, nn, with_xyz
+
+    def forward(self, x, pos, batch, x_skip, pos_skip, batch_skip, point2curveidx=None,
+                point2curveidx_skip=None, **kwargs):
+        sptr = get_cache(kwargs).sample_ptr(batch)
+        nbr, d2 = ops.knn_exact(pos_skip, batch_skip, pos, sptr, self.k, zero_fill=True, want_d2=True)
+        y = ops.interp_blend(x, nbr, d2, from_d2=True)
+        y = self.nn(_fp_concat(y, x_skip, pos_skip, self.with_xyz))
+        return y, pos_skip, batch_skip, point2curveidx_skip
+
+
+class CurveSAModule(nn.Module):
+    """pointnet2.py:146-181: CurveFPS (or FPS) -> radius_1d_group_subset -> PointNetConv2; the sampled
+    indices are the 6th output (consumed by fp-geo)."""
+
+    def __init__(self, ratio, r, nn, curve_fps_arclen=None, use_curve_fps=False, global_nn=None, attend_nn=None,
+                 with_xyz=False, aggr_type="max", normalize_radius=False, **kwargs):
+        super().__init__()
+        self.ratio, self.r = ratio, r
+        self.curve_fps_arclen, self.use_curve_fps, self.with_xyz = curve_fps_arclen, use_curve_fps, with_xyz
+        self.normalize_radius = r if normalize_radius else None
+        self.conv = PointNetConv2(nn, add_self_loops=False, global_nn=global_nn, aggr_type=aggr_type,
+                                  attend_nn=attend_nn, normalize_radius=self.normalize_radius)
+
+    def forward(self, x, pos, batch, point2curveidx, draws: Draws = DEFAULT_DRAWS, **kwargs):
+        cache = get_cache(kwargs)
+        topo = cache.topology(batch, point2curveidx)
+        if self.with_xyz:
+            x = pos if x is None else ops.concat_cols([x, pos])
+        if self.use_curve_fps:
+            idx, sptr_q = ops.curve_fps(pos, topo, self.curve_fps_arclen, draws.curve_phase())
+        else:
+            idx, sptr_q = fps_sorted(pos, topo.sptr, self.ratio, draws)
+        edges = ops.radius_1d_group(pos, topo, idx, self.r)
+        _, posq, batchq, curveq = _subset(None, pos, batch, point2curveidx, idx)
+        cache.put_sample_ptr(batchq, sptr_q)
+        out = self.conv.forward_edges(x, pos, posq, edges)
+        return out, posq, batchq, curveq, None, idx
+
+
+class CurveFPModule(FPModule):
+    """pointnet2.py:184-205: interpolation along the curve onto the fine points."""
+
+    def forward(self, x, idx, x_skip, pos_skip, batch_skip, point2curveidx_skip=None, **kwargs):
+        topo = get_cache(kwargs).topology(batch_skip, point2curveidx_skip)
+        nbr, wgt = ops.knn_1d_superset(pos_skip, topo.curve_ord, idx, self.k)
+        y = ops.interp_blend(x, nbr, wgt, from_d2=False)
+        y = self.nn(_fp_concat(y, x_skip, pos_skip, self.with_xyz))
+        return y, pos_skip, batch_skip, point2curveidx_skip
+
+
+# ----------------------------------------------------------------------------------------------
+# dgcnn.py (StaticEdgeConv / SGCNNLayer; the Dynamic* classes are reached by no shipped config)
+# ----------------------------------------------------------------------------------------------
+class SGCNNLayer(nn.Module):
+    """dgcnn.py:130-266.  kNN graph in xyz space.
+    dense path  (forward_fast :158-207): FRNN idx (N,K) + self loop; rows [x_j, x_i - x_j] (x_j = 0 for
+                missing neighbours); MLP; max with missing rows at -100.
+    sparse path (forward_slow :209-246): edge list from FRNN or exact kNN; nn([x_i, x_j - x_i]); scatter max
+                or softmax attention.
+    In both, the first Linear is decomposed into two per-POINT products P, Q (one GEMM with 2*C1
+    outputs over N rows instead of N*(K+1) rows of width 2C); the per-edge first layer is then
+    act(P[j] + Q[i]) (ccn_sgcnn_layer1 / ccn_edge_pair_layer1)."""
+
+    def __init__(self, nn, k, aggr="max", r=1.0, num_workers=1, with_xyz=False, attend_nn=None, aggr_type="max",
+                 use_sparse_feat_agg=False, use_fast_knn=True, **kwargs):
+        super().__init__()
+        assert aggr_type in ["max", "attend", "mean", "weighted-sum"]
+        self.nn, self.k, self.r, self.with_xyz = nn, k, r, with_xyz
+        self.attend_nn, self.aggr_type = attend_nn, aggr_type
+        self.use_fast_knn, self.use_sparse_feat_agg = use_fast_knn, use_sparse_feat_agg
+        self._dec, self._dec_src = None, None
+
+    def _decomposed(self):
+        layers = self.nn.layers()
+        if self._dec is None or self._dec_src is not layers:
+            w0, b0, act0, slope0 = layers[0]
+            c = w0.shape[1] // 2
+            wa, wb = w0[:, :c], w0[:, c:]
+            zero = torch.zeros_like(b0)
+            if self.use_sparse_feat_agg:     # [x_i, x_j - x_i]: P (per source j) = Wb, Q (per target i) = Wa - Wb
+                wpq, bpq = torch.cat([wb, wa - wb], dim=0), torch.cat([zero, b0])
+            else:                            # [x_j, x_i - x_j]: P (per neighbour j) = Wa - Wb, Q (per point i) = Wb
+                wpq, bpq = torch.cat([wa - wb, wb], dim=0), torch.cat([zero, b0])
+            self._dec, self._dec_src = (wpq.contiguous(), bpq.contiguous(), act0, slope0), layers
+        return self._dec
+
+    def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        sptr = get_cache(kwargs).sample_ptr(batch)
+        x = _cat_xyz(x, pos, self.with_xyz)
+        wpq, bpq, act0, slope0 = self._decomposed()
+        PQ = ops.linear(x, wpq, bpq)
+        if not self.use_sparse_feat_agg:
+            if self.aggr_type != "max":
+                raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
+            nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r)
+            h = ops.sgcnn_layer1(PQ, nbr, act0, slope0)
+            h = self.nn.forward_from(h, 1)
+            return ops.group_max_dense(h, nbr), pos, batch, point2curveidx
+        if self.use_fast_knn:
+            nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, want_cnt=True)
+        else:
+            nbr, _, cnt = ops.knn_exact(pos, batch, pos, sptr, self.k, zero_fill=True, want_d2=False, want_cnt=True)
+        edges = ops.dense_to_csr(nbr, cnt)
+        msg = ops.edge_pair_layer1(PQ, edges, act0, slope0)
+        msg = self.nn.forward_from(msg, 1)
+        if self.aggr_type == "max":
+            out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "max")
+        elif self.aggr_type == "attend":
+            out = ops.seg_aggregate(msg, self.attend_nn(msg), edges.row_ptr, edges.nq, "attend")
+        else:
+            raise NotImplementedError("sparse SGCNN path: aggregation %r" % self.aggr_type)
+        return out, pos, batch, point2curveidx
+
+
+# ----------------------------------------------------------------------------------------------
+# mlp.py / skip_connect.py
+# ----------------------------------------------------------------------------------------------
+class SharedMLP(nn.Module):
+    """mlp.py:5-22."""
+
+    def __init__(self, dims, use_bias=False, with_xyz=False, act="leaky_relu", **kwargs):
+        super().__init__()
+        self.mlp = MLP(dims, dropout=kwargs.get("dropout", 0.0), norm=kwargs.get("norm", "batch_norm"),
+                       plain_last=kwargs.get("plain_last", True), act=act, bias=use_bias)
+        self.with_xyz = with_xyz
+
+    def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        return self.mlp(_cat_xyz(x, pos, self.with_xyz)), pos, batch, point2curveidx
+
+
+class SkipConnect(nn.Module):
+    """skip_connect.py:6-15."""
+
+    def __init__(self, nn, num_skips=1):
+        super().__init__()
+        self.num_skips, self.nn = num_skips, nn
+
+    def forward(self, xs, pos, batch, point2curveidx=None, **kwargs):
+        return self.nn(ops.concat_cols(list(xs))), pos, batch, point2curveidx

@@ -1,0 +1,101 @@
+"""ctypes binding of libccn_b200.so (the C-ABI declared in include/ccn_b200.h).
+
+This is the whole "thin torch-extension": torch supplies device memory and the current CUDA
+stream, every piece of arithmetic happens in the library's sm_100a kernels.  There is NO
+fallback: if the library is missing, or a tensor is not a CUDA tensor, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libccn_b200.so")
+
+_c = {"p": ctypes.c_void_p, "q": ctypes.c_int64, "i": ctypes.c_int32, "f": ctypes.c_float}
+
+def _parse_header():
+    """Derive every entry point's ctypes signature from include/ccn_b200.h (single source of truth)."""
+    path = os.path.join(os.path.dirname(_HERE), "include", "ccn_b200.h")
+    src = re.sub(r"/\*.*?\*/", " ", open(path).read(), flags=re.S)
+    sigs, rets = {}, {}
+    for ret, name, args in re.findall(r"\b(int|int64_t)\s+(ccn_\w+)\s*\(([^)]*)\)\s*;", src):
+        codes = ""
+        for a in [a.strip() for a in args.split(",")]:
+            if a in ("", "void"):
+                continue
+            if "*" in a or "ccn_stream_t" in a:
+                codes += "p"
+            elif "int64_t" in a:
+                codes += "q"
+            elif "int32_t" in a:
+                codes += "i"
+            elif "float" in a:
+                codes += "f"
+            else:
+                raise RuntimeError("unparsed argument %r of %s" % (a, name))
+        sigs[name] = codes
+        rets[name] = ctypes.c_int64 if ret == "int64_t" else ctypes.c_int
+    return sigs, rets
+
+
+SIGNATURES, _RETURNS = _parse_header()
+
+_lib = None
+
+
+def load():
+    """Load libccn_b200.so (built by __graft_entry__.build()); raises if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "curvecloudnet_b200: %s not built - run `python -c 'import __graft_entry__ as g; g.build()'`; "
+            "there is no CPU fallback" % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, sig in SIGNATURES.items():
+        fn = getattr(lib, name)        # AttributeError here = the .so does not export a declared symbol
+        fn.argtypes = [_c[ch] for ch in sig]
+        fn.restype = _RETURNS[name]
+    _lib = lib
+    return lib
+
+
+class CcnError(RuntimeError):
+    pass
+
+
+launch_count = 0   # kernels-launching library calls made through this binding (bench.py reads it)
+
+
+def call(name, *args):
+    """Call a C-ABI entry point; torch tensors become device pointers, the current stream is appended."""
+    global launch_count
+    lib = load()
+    conv = []
+    for a in args:
+        if torch.is_tensor(a):
+            if not a.is_cuda:
+                raise CcnError("%s: tensor argument is not on a CUDA device (no CPU path exists)" % name)
+            conv.append(a.data_ptr())
+        else:
+            conv.append(a)
+    conv.append(torch.cuda.current_stream().cuda_stream)
+    rc = getattr(lib, name)(*conv)
+    launch_count += 1
+    if rc != 0:
+        if rc < 0:
+            raise CcnError("%s: invalid argument (code %d)" % (name, rc))
+        raise CcnError("%s: CUDA error %d" % (name, rc))
+
+
+def grid_num_cells(n2: int) -> int:
+    return int(load().ccn_grid_num_cells(int(n2)))
+
+
+def voxel_table_slots(n: int) -> int:
+    return int(load().ccn_voxel_table_slots(int(n)))

@@ -1,0 +1,194 @@
+"""Host-side building blocks: the shared MLP, random draws, the per-forward cache.
+
+`MLP` keeps torch_geometric.nn.MLP's constructor and parameter names
+(lins.{i}.{weight,bias}, norms.{i}.module.{weight,bias,running_mean,running_var,num_batches_tracked})
+- the `mlp_func` of the reference (src/models/base.py:32) - so reference checkpoints load with
+strict=True; its forward runs our Linear kernel with BatchNorm(eval) folded into the weights and the
+activation fused (ccn_linear_f32 / the tcgen05 path).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Union
+
+import torch
+
+from . import ops
+
+
+class Draws:
+    """The reference's random draws, taken from torch's GLOBAL CPU generator in the reference's call
+    order: CurveFPS `torch.rand(1)` (fps_ops.py:30), VoxelFPS `torch.rand(N)` (fps_ops.py:56),
+    pytorch3d's random FPS start `torch.randint(high=len, size=(1,))` per cloud (point_ops.py:64) and
+    SAModule's `torch.randperm` (pointnet2.py:51).  Seeding torch identically therefore reproduces the
+    reference's sampling; tests may substitute recorded values."""
+
+    def curve_phase(self) -> torch.Tensor:
+        return torch.rand(1)
+
+    def voxel_noise(self, n: int) -> torch.Tensor:
+        return torch.rand(n)
+
+    def fps_start(self, length: int) -> int:
+        return int(torch.randint(high=int(length), size=(1,)).item())
+
+    def randperm(self, n: int) -> torch.Tensor:
+        return torch.randperm(n)
+
+
+DEFAULT_DRAWS = Draws()
+
+
+class ForwardCache:
+    """Per-forward memo of the topology objects the reference recomputes in every step
+    (curveidx_local2global / batch2ptr, point_ops.py:20-54): keyed by the identity of the id tensors."""
+
+    def __init__(self):
+        self._sptr = {}
+        self._topo = {}
+
+    def sample_ptr(self, batch: torch.Tensor) -> ops.SamplePtr:
+        key = (batch.data_ptr(), batch.shape[0])
+        hit = self._sptr.get(key)
+        if hit is None:
+            hit = (ops.sample_ptr(batch), batch)      # keep the tensor alive: data_ptr stays unique
+            self._sptr[key] = hit
+        return hit[0]
+
+    def put_sample_ptr(self, batch: torch.Tensor, sptr: ops.SamplePtr):
+        self._sptr[(batch.data_ptr(), batch.shape[0])] = (sptr, batch)
+
+    def topology(self, batch: torch.Tensor, curve: torch.Tensor) -> ops.CurveTopology:
+        key = (batch.data_ptr(), curve.data_ptr(), batch.shape[0])
+        hit = self._topo.get(key)
+        if hit is None:
+            topo = ops.curve_csr(batch, curve)
+            hit = (topo, batch, curve)
+            self._topo[key] = hit
+            self.put_sample_ptr(batch, topo.sptr)
+        return hit[0]
+
+
+def get_cache(kwargs) -> ForwardCache:
+    c = kwargs.get("cache")
+    return c if c is not None else ForwardCache()
+
+
+_ACTS = {"relu": (ops.ACT_RELU, 0.0), "leaky_relu": (ops.ACT_LEAKY, 0.01), "leakyrelu": (ops.ACT_LEAKY, 0.01)}
+
+
+class BatchNorm(torch.nn.Module):
+    """torch_geometric.nn.norm.BatchNorm: BatchNorm1d held as `.module`."""
+
+    def __init__(self, channels: int, eps: float = 1e-5, momentum: float = 0.1):
+        super().__init__()
+        self.module = torch.nn.BatchNorm1d(channels, eps=eps, momentum=momentum)
+
+    def reset_parameters(self):
+        self.module.reset_parameters()
+
+
+def fold_batchnorm(weight: torch.Tensor, bias: Optional[torch.Tensor], bn: Optional[torch.nn.BatchNorm1d]):
+    """(W, b) of `BatchNorm_eval(x W^T + b)` as one affine map: W' = s W, b' = (b - mean) s + beta,
+    s = gamma / sqrt(var + eps).  Weight preparation, not part of the per-scan path."""
+    w = weight.detach().float()
+    b = bias.detach().float() if bias is not None else torch.zeros(w.shape[0], device=w.device)
+    if bn is not None:
+        s = bn.weight.detach() / torch.sqrt(bn.running_var.detach() + bn.eps)
+        w = w * s.view(-1, *([1] * (w.dim() - 1)))
+        b = (b - bn.running_mean.detach()) * s + bn.bias.detach()
+    return w.contiguous(), b.contiguous()
+
+
+class MLP(torch.nn.Module):
+    def __init__(self, channel_list: Sequence[int], *, dropout: Union[float, List[float]] = 0.0, act="relu",
+                 act_first: bool = False, norm: Optional[str] = "batch_norm", plain_last: bool = True,
+                 bias: Union[bool, List[bool]] = True, **kwargs):
+        super().__init__()
+        channel_list = list(channel_list)
+        assert len(channel_list) >= 2
+        if act_first:
+            raise NotImplementedError("act_first MLPs do not occur on the CurveCloudNet path")
+        if norm not in (None, "batch_norm", "BatchNorm"):
+            raise NotImplementedError("norm=%r" % (norm,))
+        if isinstance(act, str):
+            if act.lower() not in _ACTS:
+                raise NotImplementedError("activation %r" % act)
+            self.act_name = act.lower()
+        else:
+            raise NotImplementedError("activation must be 'relu' or 'leaky_relu'")
+        self.channel_list = channel_list
+        self.plain_last = plain_last
+        nl = len(channel_list) - 1
+        if isinstance(dropout, (float, int)):
+            dropout = [float(dropout)] * nl
+            if plain_last:
+                dropout[-1] = 0.0
+        self.dropout = dropout
+        if isinstance(bias, bool):
+            bias = [bias] * nl
+        self.lins = torch.nn.ModuleList(
+            torch.nn.Linear(i, o, bias=b) for i, o, b in zip(channel_list[:-1], channel_list[1:], bias))
+        hidden = channel_list[1:-1] if plain_last else channel_list[1:]
+        self.norms = torch.nn.ModuleList(BatchNorm(h) if norm is not None else torch.nn.Identity() for h in hidden)
+        self._folded = None
+        self._folded_key = None
+
+    @property
+    def in_channels(self):
+        return self.channel_list[0]
+
+    @property
+    def out_channels(self):
+        return self.channel_list[-1]
+
+    @property
+    def num_layers(self):
+        return len(self.lins)
+
+    def reset_parameters(self):
+        for lin in self.lins:
+            lin.reset_parameters()
+        for n in self.norms:
+            if hasattr(n, "reset_parameters"):
+                n.reset_parameters()
+
+    # ------------------------------------------------------------------ folded parameters
+    def _key(self):
+        k = [self.training]
+        for i, lin in enumerate(self.lins):
+            k.append(lin.weight._version)
+            k.append(lin.weight.data_ptr())
+            if i < len(self.norms) and isinstance(self.norms[i], BatchNorm):
+                m = self.norms[i].module
+                k.append(m.weight._version + m.running_mean._version + m.running_var._version + m.bias._version)
+        return tuple(k)
+
+    def layers(self):
+        """[(W', b', act code, slope)] with BatchNorm(eval) folded; cached until a parameter changes."""
+        if self.training:
+            raise NotImplementedError(
+                "curvecloudnet_b200 round 1 implements the inference (eval) path; call model.eval()")
+        key = self._key()
+        if self._folded is None or key != self._folded_key:
+            out = []
+            act, slope = _ACTS[self.act_name]
+            for i, lin in enumerate(self.lins):
+                bn = None
+                if i < len(self.norms) and isinstance(self.norms[i], BatchNorm):
+                    bn = self.norms[i].module
+                w, b = fold_batchnorm(lin.weight, lin.bias, bn)
+                hidden = i < len(self.lins) - 1 or not self.plain_last
+                out.append((w, b, act if hidden else ops.ACT_NONE, slope))
+            self._folded, self._folded_key = out, key
+        return self._folded
+
+    def forward(self, x, *args, **kwargs):
+        for w, b, act, slope in self.layers():
+            x = ops.linear(x, w, b, act, slope)
+        return x
+
+    def forward_from(self, x, first: int):
+        """Run layers first.. (the first layer(s) having been applied in a fused/decomposed form)."""
+        for w, b, act, slope in self.layers()[first:]:
+            x = ops.linear(x, w, b, act, slope)
+        return x

@@ -1,0 +1,428 @@
+"""Op layer: one python function per C-ABI kernel group (include/ccn_b200.h), torch tensors in/out.
+
+Everything here runs on the GPU through libccn_b200.so; torch is used only to allocate device
+buffers and to read back the few data-dependent sizes (marked "host sync").  Neighbour tables and
+CSR pointers are int32 on the device; reference-facing index vectors stay int64.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import List, Optional, Tuple
+
+import torch
+
+from . import native
+from .native import call
+
+ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
+AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3}
+MAX_SAMPLES = 4096
+TOPO_ERRORS = {1: "batch vector is not sorted", 2: "curve ids are not sorted within a sample",
+               4: "more than %d samples in a batch" % MAX_SAMPLES, 8: "batch ids are not 0..B-1"}
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        raise TypeError("expected float32, got %s" % t.dtype)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _i64(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.int64:
+        t = t.to(torch.int64)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _rows(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
+    """2-D fp32 tensor with unit inner stride -> (tensor, leading dimension)."""
+    if t.dtype != torch.float32 or t.dim() != 2:
+        raise TypeError("expected a 2-D float32 tensor")
+    if t.stride(1) != 1 or (t.shape[0] > 1 and t.stride(0) < t.shape[1]):
+        t = t.contiguous()
+    return t, (t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1))
+
+
+def _empty(shape, dtype, like):
+    return torch.empty(shape, dtype=dtype, device=like.device)
+
+
+def _raise_topo(flags: int):
+    msgs = [m for bit, m in TOPO_ERRORS.items() if flags & bit]
+    raise AssertionError("; ".join(msgs))   # the reference asserts sortedness (point_ops.py:31,49)
+
+
+# ----------------------------------------------------------------------------------------------
+# topology
+# ----------------------------------------------------------------------------------------------
+@dataclass
+class SamplePtr:
+    dev: torch.Tensor          # int32 (B+1) on the device
+    host: List[int]            # same on the host
+
+    @property
+    def n_samples(self) -> int:
+        return len(self.host) - 1
+
+    @property
+    def lengths(self) -> List[int]:
+        return [self.host[i + 1] - self.host[i] for i in range(self.n_samples)]
+
+
+@dataclass
+class CurveTopology:
+    n: int
+    n_curves: int
+    max_glob: int
+    curve_ord: torch.Tensor    # int32 (n)   dense global curve ordinal
+    curve_ptr: torch.Tensor    # int32 (n_curves+1)
+    curve_glob: torch.Tensor   # int64 (n)   reference curveidx_local2global
+    curve_local: torch.Tensor  # int64 (n)   as given
+    sptr: SamplePtr
+    batch: Optional[torch.Tensor] = None   # int64 (n)
+
+    @property
+    def dense(self) -> bool:
+        return self.max_glob == self.n_curves
+
+
+def curve_csr(batch: torch.Tensor, curve: torch.Tensor) -> CurveTopology:
+    """curveidx_local2global + batch2ptr in one pass (one host sync for {B, #curves})."""
+    batch, curve = _i64(batch), _i64(curve)
+    n = batch.shape[0]
+    ord_ = _empty((n,), torch.int32, batch)
+    cptr = _empty((n + 1,), torch.int32, batch)
+    tail = _empty((MAX_SAMPLES + 1 + 4,), torch.int32, batch)   # sample_ptr followed by counts
+    soff = _empty((MAX_SAMPLES + 1,), torch.int64, batch)
+    glob = _empty((n,), torch.int64, batch)
+    counts = tail[MAX_SAMPLES + 1:]
+    call("ccn_curve_csr", batch, curve, n, ord_, cptr, tail, soff, glob, counts, MAX_SAMPLES)
+    host = tail.tolist()                                         # host sync
+    B, n_curves, flags, max_glob = host[MAX_SAMPLES + 1:MAX_SAMPLES + 5]
+    if flags:
+        _raise_topo(flags)
+    sptr = SamplePtr(tail[:B + 1], host[:B + 1])
+    return CurveTopology(n, n_curves, max_glob, ord_, cptr[:n_curves + 1], glob, curve, sptr, batch)
+
+
+def sample_ptr(batch: torch.Tensor) -> SamplePtr:
+    """batch2ptr(batch, with_ends=True) (one host sync)."""
+    batch = _i64(batch)
+    n = batch.shape[0]
+    tail = _empty((MAX_SAMPLES + 1 + 4,), torch.int32, batch)
+    call("ccn_sample_ptr", batch, n, tail, tail[MAX_SAMPLES + 1:], MAX_SAMPLES)
+    host = tail.tolist()
+    B, _, flags, _ = host[MAX_SAMPLES + 1:MAX_SAMPLES + 5]
+    if flags:
+        _raise_topo(flags)
+    return SamplePtr(tail[:B + 1], host[:B + 1])
+
+
+def _finish_subset(parent_batch, idx_buf, count_dev, n_samples) -> Tuple[torch.Tensor, SamplePtr]:
+    """Read back {sample_ptr of the selected level, count} with ONE host sync; trims idx."""
+    out = _empty((n_samples + 1,), torch.int32, idx_buf)
+    call("ccn_subset_sample_ptr", parent_batch, idx_buf, count_dev, idx_buf.shape[0], n_samples, out)
+    host = out.tolist()                                          # host sync
+    return idx_buf[:host[-1]], SamplePtr(out, host)
+
+
+# ----------------------------------------------------------------------------------------------
+# curve convolution
+# ----------------------------------------------------------------------------------------------
+def curve_feat_prep(x: Optional[torch.Tensor], pos: torch.Tensor, with_xyz: bool, with_diff: bool,
+                    curve_ord: torch.Tensor) -> torch.Tensor:
+    pos = _f32(pos)
+    n = pos.shape[0]
+    cx = 0 if x is None else x.shape[1]
+    c_in = cx + (3 if with_xyz else 0)
+    out = _empty((n, c_in * (2 if with_diff else 1)), torch.float32, pos)
+    if x is not None:
+        x, ldx = _rows(x)
+    else:
+        ldx = 0
+    call("ccn_curve_feat_prep", x if x is not None else 0, ldx, cx, pos, int(with_xyz), int(with_diff), curve_ord, n,
+         out, out.shape[1])
+    return out
+
+
+def curve_row_map(topo: CurveTopology, pad: int) -> torch.Tensor:
+    rows = topo.n + (topo.n_curves + 1) * pad
+    row2pt = _empty((max(rows, 1),), torch.int32, topo.curve_ord)
+    call("ccn_curve_row_map", topo.curve_ord, topo.n, topo.n_curves, pad, row2pt)
+    return row2pt[:rows]
+
+
+def curve_conv_layer(inp: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, row2pt: torch.Tensor, rows: int,
+                     out_rows: int, ksize: int, in_mapped: bool, out_mapped: bool, slope: float = 0.01) -> torch.Tensor:
+    """w: (ksize, cin, cout) folded, bias: (cout) folded."""
+    inp, ld_in = _rows(inp)
+    cin, cout = w.shape[1], w.shape[2]
+    out = _empty((out_rows, cout), torch.float32, inp)
+    call("ccn_curve_conv_layer", inp, ld_in, w, bias, out, cout, row2pt, rows, cin, cout, ksize, int(in_mapped),
+         int(out_mapped), float(slope))
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# sampling / grouping along curves
+# ----------------------------------------------------------------------------------------------
+def curve_fps(pos: torch.Tensor, topo: CurveTopology, arclen: float, u: torch.Tensor) -> Tuple[torch.Tensor, SamplePtr]:
+    """CurveFPS.forward -> (idx int64 ascending, sample ptr of the kept points)."""
+    pos = _f32(pos)
+    n = pos.shape[0]
+    run = _empty((max(n, 1),), torch.float32, pos)
+    idx = _empty((max(n, 1),), torch.int64, pos)
+    cnt = _empty((1,), torch.int32, pos)
+    u = u.to(device=pos.device, dtype=torch.float32).reshape(1)
+    call("ccn_curve_fps", pos, topo.curve_ord, topo.curve_ptr, n, u, float(arclen), run, idx, cnt)
+    return _finish_subset(topo.batch, idx, cnt, topo.sptr.n_samples)
+
+
+@dataclass
+class EdgeCSR:
+    row_ptr: torch.Tensor      # int32 (nq+1)
+    erow: torch.Tensor         # int32 (E) target / query ordinal of every edge
+    ecol: torch.Tensor         # int32 (E) source point index
+    n_edges: int
+    nq: int
+
+
+def radius_1d_group(pos: torch.Tensor, topo: CurveTopology, idxs: torch.Tensor, radius: float) -> EdgeCSR:
+    """radius_1d_group_subset as CSR over the queries (one host sync for E)."""
+    if not topo.dense:
+        raise NotImplementedError("radius_1d_group: curve ids with gaps inside a sample are not supported")
+    pos, idxs = _f32(pos), _i64(idxs)
+    nq = idxs.shape[0]
+    kc = _empty((max(topo.n_curves, 1),), torch.float32, pos)
+    stats = _empty((2,), torch.int32, pos)
+    row_ptr = _empty((nq + 2,), torch.int32, pos)
+    total = row_ptr[nq + 1:]
+    call("ccn_radius_1d_group_count", pos, topo.curve_ord, topo.curve_ptr, topo.curve_local, topo.n, topo.n_curves,
+         idxs, nq, float(radius), kc, stats, row_ptr, total)
+    E = int(total.item())                                        # host sync
+    col = _empty((max(E, 1),), torch.int32, pos)
+    call("ccn_radius_1d_group_fill", topo.curve_ord, topo.curve_local, topo.n, topo.n_curves, idxs, nq, kc, stats,
+         row_ptr, col)
+    erow = _empty((max(E, 1),), torch.int32, pos)
+    call("ccn_csr_rows", row_ptr, nq, erow)
+    return EdgeCSR(row_ptr[:nq + 1], erow[:E], col[:E], E, nq)
+
+
+def knn_1d_superset(pos: torch.Tensor, curve_ord: torch.Tensor, idxs: torch.Tensor, knn: int):
+    pos, idxs = _f32(pos), _i64(idxs)
+    n = pos.shape[0]
+    nbr = _empty((n, knn), torch.int32, pos)
+    wgt = _empty((n, knn), torch.float32, pos)
+    call("ccn_knn_1d_superset", pos, curve_ord, n, idxs, idxs.shape[0], knn, nbr, wgt)
+    return nbr, wgt
+
+
+# ----------------------------------------------------------------------------------------------
+# point down-sampling
+# ----------------------------------------------------------------------------------------------
+def voxel_fps(pos: torch.Tensor, batch: torch.Tensor, voxel: float, noise: torch.Tensor,
+              n_samples: int) -> Tuple[torch.Tensor, SamplePtr]:
+    """VoxelFPS.forward -> (idx int64 in voxel-key order, sample ptr of the kept points)."""
+    pos, batch = _f32(pos), _i64(batch)
+    n = pos.shape[0]
+    slots = native.voxel_table_slots(n)
+    table = _empty((2 * slots + max(n, 1),), torch.int64, pos)
+    ints = _empty((2 * max(n, 1) + 2,), torch.int32, pos)
+    idx = _empty((max(n, 1),), torch.int64, pos)
+    noise = noise.to(device=pos.device, dtype=torch.float32).contiguous()
+    counts = ints[2 * max(n, 1):]
+    call("ccn_voxel_fps", pos, batch, n, float(voxel), noise, slots, table, table[slots:], table[2 * slots:],
+         ints, ints[max(n, 1):], idx, counts)
+    idx, sptr = _finish_subset(batch, idx, counts, n_samples)
+    if int(counts[1].item()):
+        raise native.CcnError("voxel_fps: voxel coordinates out of the supported range (|ix| < 2^17, B <= 1024)")
+    return idx, sptr
+
+
+def fps_count(lengths: List[int], ratio: float) -> List[int]:
+    """K = ceil(len * ratio) evaluated in float32 like the reference (point_ops.py:63)."""
+    t = torch.ceil(torch.tensor(lengths, dtype=torch.int64) * ratio).to(torch.int64)
+    return [int(v) for v in t.tolist()]
+
+
+def fps(pos: torch.Tensor, sptr: SamplePtr, ksel: List[int], starts: List[int]) -> torch.Tensor:
+    """sample_farthest_points per cloud from explicit start points; returns the selected global
+    indices sorted ascending (what fps_pytorch3d returns, point_ops.py:69).  No host sync."""
+    pos = _f32(pos)
+    n = pos.shape[0]
+    B = sptr.n_samples
+    lens = sptr.lengths
+    total = sum(min(k, l) for k, l in zip(ksel, lens))
+    meta = torch.tensor(list(ksel) + list(starts), dtype=torch.int32).to(pos.device, non_blocking=True)
+    max_len = max(lens) if lens else 0
+    closest = _empty((max(n, 1),), torch.float32, pos) if max_len > 512 * 16 else None
+    sel = _empty((max(n, 1),), torch.int32, pos)
+    idx = _empty((max(total, 1),), torch.int64, pos)
+    call("ccn_fps", pos, sptr.dev, B, n, meta, meta[B:], max_len, closest if closest is not None else 0, sel, idx, 0)
+    return idx[:total]
+
+
+# ----------------------------------------------------------------------------------------------
+# neighbour search
+# ----------------------------------------------------------------------------------------------
+def frnn_knn(pos1, batch1, pos2, batch2, sptr2: SamplePtr, K: int, radius: float, want_d2=False, want_cnt=False):
+    """Fixed-radius kNN -> idx int32 (n1, K) GLOBAL rows of pos2, -1 padded, ascending by (d2, index)."""
+    pos1, pos2, batch1, batch2 = _f32(pos1), _f32(pos2), _i64(batch1), _i64(batch2)
+    n1, n2 = pos1.shape[0], pos2.shape[0]
+    cells = native.grid_num_cells(n2)
+    cell_off = _empty((cells + 1,), torch.int32, pos1)
+    slot = _empty((max(n2, 1),), torch.int32, pos1)
+    sorted_ = _empty((max(n2, 1), 4), torch.float32, pos1)
+    call("ccn_grid_build", pos2, batch2, n2, float(radius), cells, cell_off, slot, sorted_)
+    idx = _empty((n1, K), torch.int32, pos1)
+    d2 = _empty((n1, K), torch.float32, pos1) if want_d2 else None
+    cnt = _empty((n1 + 2,), torch.int32, pos1) if want_cnt else None
+    call("ccn_frnn_knn", pos1, batch1, n1, sorted_, cell_off, cells, sptr2.dev, float(radius), K, idx,
+         d2 if want_d2 else 0, cnt if want_cnt else 0)
+    return idx, d2, cnt
+
+
+def knn_exact(pos1, batch1, pos2, sptr2: SamplePtr, K: int, zero_fill=True, want_d2=True, want_cnt=False):
+    pos1, pos2, batch1 = _f32(pos1), _f32(pos2), _i64(batch1)
+    n1 = pos1.shape[0]
+    idx = _empty((n1, K), torch.int32, pos1)
+    d2 = _empty((n1, K), torch.float32, pos1) if want_d2 else None
+    cnt = _empty((n1 + 2,), torch.int32, pos1) if want_cnt else None
+    call("ccn_knn_exact", pos1, batch1, n1, pos2, sptr2.dev, K, int(zero_fill), idx, d2 if want_d2 else 0,
+         cnt if want_cnt else 0)
+    if want_cnt:
+        return idx, d2, cnt
+    return idx, d2
+
+
+def ball_query(pos1, batch1, pos2, sptr2: SamplePtr, radius: float, K: int = 128):
+    pos1, pos2, batch1 = _f32(pos1), _f32(pos2), _i64(batch1)
+    n1 = pos1.shape[0]
+    idx = _empty((n1, K), torch.int32, pos1)
+    cnt = _empty((n1 + 2,), torch.int32, pos1)
+    call("ccn_ball_query", pos1, batch1, n1, pos2, sptr2.dev, float(radius), K, idx, cnt)
+    return idx, cnt
+
+
+def dense_to_csr(idx: torch.Tensor, cnt: torch.Tensor) -> EdgeCSR:
+    """(nq, K) table with leading valid entries + per-row counts (nq+2 buffer) -> CSR (one host sync for E)."""
+    nq, K = idx.shape
+    call("ccn_excl_scan_i32", cnt, nq, cnt[nq + 1:])
+    E = int(cnt[nq + 1].item())                                  # host sync
+    erow = _empty((max(E, 1),), torch.int32, idx)
+    ecol = _empty((max(E, 1),), torch.int32, idx)
+    call("ccn_dense_to_csr", idx, cnt, nq, K, erow, ecol)
+    return EdgeCSR(cnt[:nq + 1], erow[:E], ecol[:E], E, nq)
+
+
+# ----------------------------------------------------------------------------------------------
+# gathers, aggregation, MLP layer
+# ----------------------------------------------------------------------------------------------
+def gather_rows(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    src, lds = _rows(src)
+    idx = _i64(idx)
+    out = _empty((idx.shape[0], src.shape[1]), torch.float32, src)
+    call("ccn_gather_rows_f32", src, lds, idx, idx.shape[0], src.shape[1], out, src.shape[1])
+    return out
+
+
+def gather_i64(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    src, idx = _i64(src), _i64(idx)
+    out = _empty((idx.shape[0],), torch.int64, src)
+    call("ccn_gather_i64", src, idx, idx.shape[0], out)
+    return out
+
+
+def concat_cols(parts: List[torch.Tensor]) -> torch.Tensor:
+    """torch.cat(parts, dim=1) with our copy kernel (column-offset strided writes)."""
+    n = parts[0].shape[0]
+    c = sum(p.shape[1] for p in parts)
+    out = _empty((n, c), torch.float32, parts[0])
+    off = 0
+    for p in parts:
+        p, ld = _rows(p)
+        call("ccn_gather_rows_f32", p, ld, 0, n, p.shape[1], out[:, off:], c)
+        off += p.shape[1]
+    return out
+
+
+def linear(A: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], act: int = ACT_NONE,
+           slope: float = 0.01) -> torch.Tensor:
+    """Y = act(A W^T + bias), fp32."""
+    A, lda = _rows(A)
+    W, ldw = _rows(W)
+    M, K = A.shape
+    N = W.shape[0]
+    assert W.shape[1] == K, (A.shape, W.shape)
+    Y = _empty((M, N), torch.float32, A)
+    call("ccn_linear_f32", A, lda, W, ldw, bias if bias is not None else 0, Y, N, M, N, K, act, float(slope))
+    return Y
+
+
+def edge_layer1(H: Optional[torch.Tensor], wp: torch.Tensor, bias: Optional[torch.Tensor], pos_src, pos_dst,
+                edges: EdgeCSR, normalize_radius: Optional[float], act: int, slope: float = 0.01) -> torch.Tensor:
+    c = wp.shape[1]
+    out = _empty((edges.n_edges, c), torch.float32, wp)
+    if H is not None:
+        H, ldh = _rows(H)
+    else:
+        ldh = 0
+    call("ccn_edge_layer1", H if H is not None else 0, ldh, wp, bias if bias is not None else 0, _f32(pos_src),
+         _f32(pos_dst), edges.erow, edges.ecol, edges.n_edges, c, float(normalize_radius or 0.0), act, float(slope),
+         out, c)
+    return out
+
+
+def edge_pair_layer1(PQ: torch.Tensor, edges: EdgeCSR, act: int, slope: float = 0.01) -> torch.Tensor:
+    PQ, ld = _rows(PQ)
+    c = PQ.shape[1] // 2
+    out = _empty((edges.n_edges, c), torch.float32, PQ)
+    call("ccn_edge_pair_layer1", PQ, ld, edges.erow, edges.ecol, edges.n_edges, c, act, float(slope), out, c)
+    return out
+
+
+def seg_aggregate(msg: torch.Tensor, att: Optional[torch.Tensor], row_ptr: torch.Tensor, nq: int, mode: str):
+    msg, ldm = _rows(msg)
+    c = msg.shape[1]
+    if att is not None:
+        att, lda = _rows(att)
+    else:
+        lda = 0
+    out = _empty((nq, c), torch.float32, msg)
+    call("ccn_seg_aggregate", msg, ldm, att if att is not None else 0, lda, row_ptr, nq, c, AGG[mode], out, c)
+    return out
+
+
+def sgcnn_layer1(PQ: torch.Tensor, idx: torch.Tensor, act: int, slope: float = 0.01) -> torch.Tensor:
+    PQ, ld = _rows(PQ)
+    n, K = idx.shape
+    c = PQ.shape[1] // 2
+    out = _empty((n * (K + 1), c), torch.float32, PQ)
+    call("ccn_sgcnn_layer1", PQ, ld, idx, n, K, c, act, float(slope), out, c)
+    return out
+
+
+def group_max_dense(feat: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    feat, ld = _rows(feat)
+    n, K = idx.shape
+    c = feat.shape[1]
+    out = _empty((n, c), torch.float32, feat)
+    call("ccn_group_max_dense", feat, ld, idx, n, K, c, out, c)
+    return out
+
+
+def interp_blend(x: torch.Tensor, nbr: torch.Tensor, wgt: torch.Tensor, from_d2: bool) -> torch.Tensor:
+    x, ldx = _rows(x)
+    n, knn = nbr.shape
+    c = x.shape[1]
+    out = _empty((n, c), torch.float32, x)
+    call("ccn_interp_blend", x, ldx, nbr, wgt, int(from_d2), n, knn, c, out, c)
+    return out
+
+
+def sample_ptr_any(ids: torch.Tensor) -> torch.Tensor:
+    """batch2ptr(ids, with_ends=True) for ANY sorted int64 id vector (run starts + [N]) as int64."""
+    ids = _i64(ids)
+    zeros = torch.zeros_like(ids)
+    topo = curve_csr(zeros, ids)
+    return topo.curve_ptr.to(torch.int64)

@@ -1,0 +1,179 @@
+/* libccn_b200.so - C-ABI of the B200-native (sm_100a) CurveCloudNet per-scan hot path.
+ *
+ * Every entry point is what the reference's FFI for this path would bind.  The reference reaches
+ * native code in two ways, and each function below names the interface it replaces:
+ *   (1) its vendored pybind module `frnn._C` (/root/reference/third_party/FRNN/frnn/csrc/ext.cpp:10-27:
+ *       insert_points_cuda, counting_sort_cuda, find_nbrs_cuda) and `prefix_sum.prefix_sum_cuda`
+ *       (third_party/FRNN/external/prefix_sum/prefix_sum.h:6-20);
+ *   (2) un-vendored python packages whose CUDA kernels it calls from src/models/utils/point_ops.py
+ *       and src/models/modules/{fast_conv1d,pointnet2,point_conv,dgcnn,fps_ops}.py (pytorch3d.ops, torch_scatter, torch_geometric.nn.MLP, cuDNN conv1d).
+ *
+ * Conventions (same as the reference's pybind functions: outputs pre-allocated by the caller,
+ * frnn.py:91-103):
+ *   - all pointers are DEVICE pointers; the library never allocates, never synchronises and never
+ *     touches the default stream: every launch goes to `stream` (the caller passes torch's current
+ *     stream, as find_nbrs.cu:596-618 does);
+ *   - features are fp32 row-major with an explicit leading dimension, positions are fp32 (n,3)
+ *     contiguous, reference-facing index vectors (`batch`, `curve_idxs`, sampled `idx`) are int64 as
+ *     in the reference API, internal neighbour tables / CSR pointers are int32;
+ *   - random draws the reference takes from torch's RNG (CurveFPS phase, VoxelFPS noise, FPS start)
+ *     are INPUTS;
+ *   - return 0 on success, a negative CCN_E* on bad arguments, a positive cudaError_t otherwise.
+ *   - data-dependent sizes are written to small device `counts` buffers the caller reads back.
+ */
+#ifndef CCN_B200_H
+#define CCN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* ccn_stream_t;
+
+#define CCN_OK 0
+#define CCN_EINVAL (-1)
+#define CCN_EUNSUPPORTED (-2)
+
+#define CCN_ACT_NONE 0
+#define CCN_ACT_RELU 1
+#define CCN_ACT_LEAKY 2
+
+#define CCN_AGG_MAX 0
+#define CCN_AGG_MEAN 1
+#define CCN_AGG_WSUM 2   /* sum sigmoid(att) * msg */
+#define CCN_AGG_ATTEND 3 /* sum softmax_target(att) * msg */
+
+#define CCN_TOPO_ERR_BATCH_UNSORTED 1
+#define CCN_TOPO_ERR_CURVE_UNSORTED 2
+#define CCN_TOPO_ERR_TOO_MANY_SAMPLES 4
+#define CCN_TOPO_ERR_BATCH_NOT_DENSE 8
+
+int ccn_version(void);
+
+/* ---- curve / sample topology -------------------------------------------------------------------
+ * replaces curveidx_local2global + batch2ptr + is_sorted asserts
+ * (src/models/utils/point_ops.py:20-54,464-465; fast_conv1d.py:41).
+ * curve_ord[i]  dense global curve ordinal of point i; curve_ptr[0..n_curves] CSR over points;
+ * sample_ptr[0..B] CSR over points; sample_curve_off[b] reference offset of sample b;
+ * curve_glob[i] = reference's global id; counts = {B, n_curves, CCN_TOPO_ERR_* flags, max glob id + 1}.
+ * curve_ptr needs n+1 entries, sample_ptr/sample_curve_off max_samples+1. */
+int ccn_curve_csr(const int64_t* batch, const int64_t* curve, int64_t n, int32_t* curve_ord, int32_t* curve_ptr,
+                  int32_t* sample_ptr, int64_t* sample_curve_off, int64_t* curve_glob, int32_t* counts,
+                  int32_t max_samples, ccn_stream_t stream);
+/* batch2ptr(batch, with_ends=True) for levels without curves; counts = {B, 0, flags, 0}. */
+int ccn_sample_ptr(const int64_t* batch, int64_t n, int32_t* sample_ptr, int32_t* counts, int32_t max_samples,
+                   ccn_stream_t stream);
+/* sample CSR of the level selected by idx[0..*count_ptr) out of a batch-sorted parent (the reference gets it by
+ * recomputing batch2ptr on batch[idx]); sptr_out[0..B], sptr_out[B] = *count_ptr.  capacity >= *count_ptr. */
+int ccn_subset_sample_ptr(const int64_t* batch, const int64_t* idx, const int32_t* count_ptr, int64_t capacity,
+                          int32_t n_samples, int32_t* sptr_out, ccn_stream_t stream);
+
+/* ---- symmetric curve convolution (src/models/modules/fast_conv1d.py:11-205; cuDNN F.conv1d :183) ---
+ * feat_prep: out[i] = [x[i] (cx), pos[i] (3 if with_xyz), |mean fwd/bwd difference along the curve| (if with_diff)]
+ *            (fast_conv1d.py:42-45,64-66 and compute_feature_diffs :190-205).
+ * row_map:   row2pt[r] = point of padded row r or -1; `pad` zero rows precede every curve and follow the
+ *            last one (fast_conv1d.py:48-61); rows = n + (n_curves+1)*pad.
+ * conv_layer: one layer over `rows` signal rows: out = leaky_relu(conv1d_same(in; w) + bias), w is
+ *            (ksize, cin, cout) = mirrored weight (fast_conv1d.py:173-184) with BatchNorm(eval) folded.
+ *            in_mapped: input rows are points addressed through row2pt (pad rows read zeros);
+ *            out_mapped: only rows with row2pt >= 0 are written, to out[row2pt[r]]. */
+int ccn_curve_feat_prep(const float* x, int64_t ldx, int32_t cx, const float* pos, int32_t with_xyz,
+                        int32_t with_diff, const int32_t* curve_ord, int64_t n, float* out, int64_t ldo,
+                        ccn_stream_t stream);
+int ccn_curve_row_map(const int32_t* curve_ord, int64_t n, int32_t n_curves, int32_t pad, int32_t* row2pt,
+                      ccn_stream_t stream);
+int ccn_curve_conv_layer(const float* in, int64_t ld_in, const float* w, const float* bias, float* out,
+                         int64_t ld_out, const int32_t* row2pt, int64_t rows, int32_t cin, int32_t cout,
+                         int32_t ksize, int32_t in_mapped, int32_t out_mapped, float slope, ccn_stream_t stream);
+
+/* ---- sampling / grouping along curves --------------------------------------------------------------
+ * curve_fps: CurveFPS.forward (src/models/modules/fps_ops.py:16-39); u = the torch.rand(1) draw (:30);
+ *            idx_out ascending (capacity n), *count_out = number kept; run_scratch n floats.
+ * radius_1d_group_{count,fill}: radius_1d_group_subset (point_ops.py:143-193) as CSR over queries:
+ *            count writes row_ptr[0..nq] and *total_out = E; fill writes col[E] (point indices, in the
+ *            reference's candidate order 0,-1,+1,...).  kc_scratch n_curves floats, stats_scratch 2 ints.
+ * knn_1d_superset: knn_1d_group_superset + weights of knn_interpolate_1D_pytorch3d (point_ops.py:196-260,
+ *            344-355): nbr (n,knn) sampled ORDINALS (-1 padded) by (distance, candidate order), wgt = 1/clamp(d^2,1e-16). */
+int ccn_curve_fps(const float* pos, const int32_t* curve_ord, const int32_t* curve_ptr, int64_t n, const float* u,
+                  float arclen, float* run_scratch, int64_t* idx_out, int32_t* count_out, ccn_stream_t stream);
+int ccn_radius_1d_group_count(const float* pos, const int32_t* curve_ord, const int32_t* curve_ptr,
+                              const int64_t* curve_local, int64_t n, int32_t n_curves, const int64_t* idxs, int64_t nq,
+                              float radius, float* kc_scratch, int32_t* stats_scratch, int32_t* row_ptr,
+                              int32_t* total_out, ccn_stream_t stream);
+int ccn_radius_1d_group_fill(const int32_t* curve_ord, const int64_t* curve_local, int64_t n, int32_t n_curves,
+                             const int64_t* idxs, int64_t nq, const float* kc_scratch, const int32_t* stats_scratch,
+                             const int32_t* row_ptr, int32_t* col, ccn_stream_t stream);
+int ccn_knn_1d_superset(const float* pos, const int32_t* curve_ord, int64_t n, const int64_t* idxs, int64_t nq,
+                        int32_t knn, int32_t* nbr, float* wgt, ccn_stream_t stream);
+/* in-place exclusive scan of a[0..n), a[n] = total (replaces prefix_sum.prefix_sum_cuda, prefix_sum.h:6-20). */
+int ccn_excl_scan_i32(int32_t* a, int64_t n, int32_t* total_out, ccn_stream_t stream);
+
+/* ---- point down-sampling ---------------------------------------------------------------------------
+ * voxel_fps: VoxelFPS.forward (fps_ops.py:51-60); noise = the torch.rand(n) draw (:56); idx_out in
+ *            lexicographic (batch, ix, iy, iz) voxel order; counts = {#voxels, error flag}.
+ *            slots = ccn_voxel_table_slots(n); scratch: table_keys/table_min slots u64, ukeys n u64, uwin/rank n i32.
+ * fps:       pytorch3d.ops.sample_farthest_points as called by fps_pytorch3d (point_ops.py:57-70):
+ *            per cloud ksel[b] picks from local start[b], ties -> lowest index; idx_out = the selected
+ *            global indices SORTED ascending (point_ops.py:69); *total_out = how many. */
+int64_t ccn_voxel_table_slots(int64_t n);
+int ccn_voxel_fps(const float* pos, const int64_t* batch, int64_t n, float voxel, const float* noise, int64_t slots,
+                  uint64_t* table_keys, uint64_t* table_min, uint64_t* ukeys, int32_t* uwin, int32_t* rank,
+                  int64_t* idx_out, int32_t* counts, ccn_stream_t stream);
+int ccn_fps(const float* pos, const int32_t* sample_ptr, int32_t n_samples, int64_t n, const int32_t* ksel,
+            const int32_t* start, int32_t max_len, float* closest_scratch, int32_t* sel_cnt_scratch, int64_t* idx_out,
+            int32_t* total_out, ccn_stream_t stream);
+
+/* ---- neighbour search ------------------------------------------------------------------------------
+ * grid_build + frnn_knn: frnn.frnn_grid_points (third_party/FRNN/frnn/frnn.py:210-347) = _C.insert_points_cuda +
+ *            prefix_sum_cuda + _C.counting_sort_cuda + _C.find_nbrs_cuda (ext.cpp:10-27): up to K points of cloud
+ *            batch1[q] with d2 <= r*r, ascending by (d2, index), idx = GLOBAL row of pos2 (int32) or -1.
+ *            num_cells = ccn_grid_num_cells(n2); cell_off num_cells+1 ints; slot_scratch n2 ints; sorted_xyzi 4*n2 floats.
+ * knn_exact: pytorch3d.ops.knn_points (call site point_ops.py:91); zero_fill mimics its 0 padding.
+ * ball_query: pytorch3d.ops.ball_query (call site point_ops.py:81): first K in index order with d2 < r*r. */
+int64_t ccn_grid_num_cells(int64_t n2);
+int ccn_grid_build(const float* pos2, const int64_t* batch2, int64_t n2, float radius, int64_t num_cells,
+                   int32_t* cell_off, int32_t* slot_scratch, float* sorted_xyzi, ccn_stream_t stream);
+int ccn_frnn_knn(const float* pos1, const int64_t* batch1, int64_t n1, const float* sorted_xyzi,
+                 const int32_t* cell_off, int64_t num_cells, const int32_t* sample_ptr2, float radius, int32_t K,
+                 int32_t* idx_out, float* d2_out, int32_t* cnt_out, ccn_stream_t stream);
+int ccn_knn_exact(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const int32_t* sample_ptr2,
+                  int32_t K, int32_t zero_fill, int32_t* idx_out, float* d2_out, int32_t* cnt_out, ccn_stream_t stream);
+int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const int32_t* sample_ptr2,
+                   float radius, int32_t K, int32_t* idx_out, int32_t* cnt_out, ccn_stream_t stream);
+
+/* ---- gathers and segmented aggregation ---------------------------------------------------------------
+ * replace x[idx] / torch_scatter / torch_geometric.utils.softmax / frnn_gather on the path
+ * (point_conv.py:60-93, dgcnn.py:166-206, pointnet2.py:95-99, point_ops.py:336-355). */
+int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t* idx, int64_t n, int32_t c, float* dst,
+                        int64_t ldd, ccn_stream_t stream);
+int ccn_gather_i64(const int64_t* src, const int64_t* idx, int64_t n, int64_t* dst, ccn_stream_t stream);
+int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int64_t nq, int32_t K, int32_t* erow, int32_t* ecol,
+                     ccn_stream_t stream);
+int ccn_csr_rows(const int32_t* row_ptr, int64_t nq, int32_t* erow, ccn_stream_t stream);
+int ccn_edge_layer1(const float* H, int64_t ldh, const float* wp, const float* bias, const float* pos_src,
+                    const float* pos_dst, const int32_t* erow, const int32_t* ecol, int64_t E, int32_t c,
+                    float normalize_radius, int32_t act, float slope, float* out, int64_t ldo, ccn_stream_t stream);
+/* first layer of StaticEdgeConv.forward_slow's message nn([x_i, x_j - x_i]) (dgcnn.py:227-228), decomposed:
+ * out[e] = act(PQ[ecol[e], 0:c] + PQ[erow[e], c:2c]),  PQ = x [Wb ; Wa - Wb]^T (+ bias on the second half). */
+int ccn_edge_pair_layer1(const float* PQ, int64_t ldpq, const int32_t* erow, const int32_t* ecol, int64_t E, int32_t c,
+                         int32_t act, float slope, float* out, int64_t ldo, ccn_stream_t stream);
+int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr, int64_t nq,
+                      int32_t c, int32_t mode, float* out, int64_t ldo, ccn_stream_t stream);
+int ccn_sgcnn_layer1(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c, int32_t act,
+                     float slope, float* out, int64_t ldo, ccn_stream_t stream);
+int ccn_group_max_dense(const float* feat, int64_t ldf, const int32_t* idx, int64_t n, int32_t K, int32_t c, float* out,
+                        int64_t ldo, ccn_stream_t stream);
+int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr, const float* wgt, int32_t from_d2, int64_t n,
+                     int32_t knn, int32_t c, float* out, int64_t ldo, ccn_stream_t stream);
+
+/* ---- shared MLP layer (torch_geometric.nn.MLP -> nn.Linear/BatchNorm1d/act; base.py:32, mlp.py:16-22) ----
+ * Y = act(A W^T + bias), W is (N, K) row-major with BatchNorm(eval) folded by the caller. */
+int ccn_linear_f32(const float* A, int64_t lda, const float* W, int64_t ldw, const float* bias, float* Y, int64_t ldy,
+                   int64_t M, int32_t N, int32_t K, int32_t act, float slope, ccn_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCN_B200_H */

@@ -1,0 +1,169 @@
+"""GPU parity of the op-level kernels (through the C-ABI) against the golden vectors produced by the real
+reference sources (oracle/make_golden.py) and against the CPU oracle on fresh seeded inputs.
+Integer / index results: bit-exact.  Float results: relative 1e-4 (BASELINE.json north_star)."""
+import pytest
+import torch
+
+from golden_utils import FixedDraws, load, rel_err
+
+pytestmark = pytest.mark.gpu
+
+OPS = load("ops.pt")
+CASES = [c for c in OPS if c != "get_curves"]
+TOL = 1e-4
+
+
+def dev(t):
+    return None if t is None else t.cuda()
+
+
+def _local_dense(po, case):
+    g = OPS[case]
+    return g, dev(g["pos"]), dev(g["batch"]), dev(g["curve"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_csr_helpers(case):
+    from curvecloudnet_b200 import point_ops as po
+    g, pos, batch, curve = _local_dense(po, case)
+    assert torch.equal(po.curveidx_local2global(curve, batch).cpu(), g["glob"])
+    assert torch.equal(po.batch2ptr(batch).cpu(), g["ptr"])
+    assert torch.equal(po.batch2ptr(batch, True).cpu(), g["ptr_ends"])
+    padded, mask = po.to_batch_padded(pos, batch)
+    assert torch.equal(mask.cpu(), g["padded_mask"])
+    assert torch.allclose(padded.sum(dim=1).cpu(), g["padded_sum"], rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_samplers(case):
+    from curvecloudnet_b200 import point_ops as po
+    g, pos, batch, curve = _local_dense(po, case)
+    idx = po.CurveFPS(g["curvefps_arclen"])(pos, batch, curve, draws=FixedDraws(u=g["curvefps_u"]))
+    assert torch.equal(idx.cpu(), g["curvefps_idx"])
+    idx = po.VoxelFPS(g["voxel_size"])(pos, batch, draws=FixedDraws(noise=g["voxel_noise"]))
+    assert torch.equal(idx.cpu(), g["voxel_idx"])
+    idx = po.fps_pytorch3d(pos, batch, g["fps_ratio"], draws=FixedDraws(starts=g["fps_starts"].tolist()))
+    assert torch.equal(idx.cpu(), g["fps_idx"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_groupings(case):
+    from curvecloudnet_b200 import point_ops as po
+    g, pos, batch, curve = _local_dense(po, case)
+    idx, sub = dev(g["curvefps_idx"]), dev(g["voxel_idx"])
+    row, col = po.radius_1d_group_subset(pos, idx, curve, batch, g["r1d_radius"])
+    assert torch.equal(row.cpu(), g["r1d_row"]) and torch.equal(col.cpu(), g["r1d_col"])
+    row, col = po.knn_1d_group_superset(pos, idx, curve, batch, 3)
+    assert torch.equal(row.cpu(), g["s1d_row"]) and torch.equal(col.cpu(), g["s1d_col"])
+    r = g["knn_radius"]
+    psub, bsub = pos[sub].contiguous(), batch[sub].contiguous()
+    dense, _, _ = po.knn_ball_group_pytorch3d(psub, pos, bsub, batch, "knn", radius=r, knn=16, return_dense=True)
+    assert torch.equal(dense.cpu(), g["frnn_dense"])
+    row, col = po.knn_ball_group_pytorch3d(psub, pos, bsub, batch, "knn", radius=r, knn=16)
+    assert torch.equal(row.cpu(), g["frnn_row"]) and torch.equal(col.cpu(), g["frnn_col"])
+    row, col = po.knn_ball_group_pytorch3d(psub, pos, bsub, batch, "ball-group", radius=r)
+    assert torch.equal(row.cpu(), g["ball_row"]) and torch.equal(col.cpu(), g["ball_col"])
+    row, col = po.knn_ball_group_pytorch3d(pos, psub, batch, bsub, "knn", knn=3, accel_knn=False)
+    assert torch.equal(row.cpu(), g["knn3_row"]) and torch.equal(col.cpu(), g["knn3_col"])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_float_ops(case):
+    from curvecloudnet_b200 import modules as M
+    from curvecloudnet_b200 import point_ops as po
+    from curvecloudnet_b200.synthetic import randomize_model_
+    g, pos, batch, curve = _local_dense(po, case)
+    idx, sub = dev(g["curvefps_idx"]), dev(g["voxel_idx"])
+    feat = dev(g["feat"])
+    assert rel_err(po.compute_feature_diffs(feat, curve, batch).cpu(), g["feat_diffs"]) <= 1e-6
+    psub, bsub = pos[sub].contiguous(), batch[sub].contiguous()
+    y = po.knn_interpolate_pytorch3d(dev(g["feat_sub"]), psub, pos, bsub, batch, k=3)
+    assert rel_err(y.cpu(), g["interp3"]) <= TOL
+    y = po.knn_interpolate_1D_pytorch3d(dev(g["feat_idx"]), idx, pos, batch, curve, 3)
+    assert rel_err(y.cpu(), g["interp1d"]) <= TOL
+    for ver, cls in (("v2", M.SymmetricCurve1DConvV2), ("v1", M.SymmetricCurve1DConvFastV1)):
+        torch.manual_seed(3)
+        mod = cls([9, 16, 12], g["conv_%s_k" % ver], with_xyz=True, with_diff=True)
+        randomize_model_(mod, 55)
+        mod = mod.cuda().eval()
+        out = mod(feat, pos, batch, curve)[0]
+        assert rel_err(out.cpu(), g["conv_%s_out" % ver]) <= TOL, ver
+
+
+def test_linear_matches_torch_fp32():
+    """The fp32 Linear kernel against plain torch fp32 (float64 accumulation as the yardstick)."""
+    from curvecloudnet_b200 import ops
+    gen = torch.Generator().manual_seed(0)
+    for (m, n, k, act) in [(1, 5, 3, 0), (130, 64, 67, 1), (777, 129, 259, 2), (40000, 64, 38, 1),
+                           (300, 1024, 2051, 1), (5000, 256, 256, 0)]:
+        a = torch.randn(m, k, generator=gen)
+        w = torch.randn(n, k, generator=gen) / k ** 0.5
+        b = torch.randn(n, generator=gen)
+        ref = a.double() @ w.double().t() + b.double()
+        if act == 1:
+            ref = ref.clamp(min=0)
+        elif act == 2:
+            ref = torch.where(ref > 0, ref, ref * 0.01)
+        y = ops.linear(a.cuda(), w.cuda(), b.cuda(), act, 0.01).cpu()
+        assert rel_err(y, ref.float()) <= 2e-6, (m, n, k, act)
+        # strided A (a column slice) and no bias
+        a2 = torch.randn(m, k + 5, generator=gen)
+        y2 = ops.linear(a2.cuda()[:, 2:2 + k], w.cuda(), None).cpu()
+        assert rel_err(y2, (a2[:, 2:2 + k].double() @ w.double().t()).float()) <= 2e-6
+
+
+def test_random_clouds_against_oracle():
+    """Fresh seeded inputs (not in the fixtures): neighbour search and samplers vs the CPU oracle, incl.
+    duplicate points (distance ties -> lowest index), K larger than the cloud and ragged batches."""
+    from curvecloudnet_b200 import ops
+    from oracle import tp_ops as tp
+    gen = torch.Generator().manual_seed(5)
+    lens2, lens1 = [700, 1, 333, 40], [50, 3, 120, 7]
+    p2 = torch.rand(sum(lens2), 3, generator=gen)
+    p2[10:20] = p2[0:10]                      # exact duplicates
+    p2 = (p2 * 64).round() / 64                 # many exact distance ties
+    p1 = (torch.rand(sum(lens1), 3, generator=gen) * 64).round() / 64
+    b2 = torch.cat([torch.full((l,), i, dtype=torch.int64) for i, l in enumerate(lens2)])
+    b1 = torch.cat([torch.full((l,), i, dtype=torch.int64) for i, l in enumerate(lens1)])
+    s2 = ops.sample_ptr(b2.cuda())
+    off2 = [0] + list(torch.tensor(lens2).cumsum(0))
+    P1, P2 = max(lens1), max(lens2)
+    pp1, pp2 = torch.zeros(4, P1, 3), torch.zeros(4, P2, 3)
+    o1 = 0
+    for b in range(4):
+        pp1[b, :lens1[b]] = p1[o1:o1 + lens1[b]]
+        pp2[b, :lens2[b]] = p2[off2[b]:off2[b] + lens2[b]]
+        o1 += lens1[b]
+    l1t, l2t = torch.tensor(lens1), torch.tensor(lens2)
+
+    def flat(dense, fill_local):
+        rows = []
+        for b in range(4):
+            blk = dense[b, :lens1[b]].clone()
+            blk = torch.where(blk >= 0, blk + off2[b], blk) if fill_local else blk + off2[b]
+            rows.append(blk)
+        return torch.cat(rows)
+
+    for K, r in [(8, 0.25), (32, 0.11), (1, 0.5)]:
+        _, want = tp.frnn_grid_points(pp1, pp2, l1t, l2t, K, r)
+        got, _, cnt = ops.frnn_knn(p1.cuda(), b1.cuda(), p2.cuda(), b2.cuda(), s2, K, r, want_cnt=True)
+        assert torch.equal(got.cpu().long(), flat(want, True)), (K, r)
+        assert torch.equal(cnt[:p1.shape[0]].cpu().long(), (flat(want, True) >= 0).sum(1))
+    for K in (3, 20):
+        _, want = tp.knn_points(pp1, pp2, l1t, l2t, K)
+        got, _ = ops.knn_exact(p1.cuda(), b1.cuda(), p2.cuda(), s2, K, zero_fill=True)
+        assert torch.equal(got.cpu().long(), flat(want, False)), K
+    want = tp.ball_query(pp1, pp2, l1t, l2t, 16, 0.2)
+    got, _ = ops.ball_query(p1.cuda(), b1.cuda(), p2.cuda(), s2, 0.2, 16)
+    assert torch.equal(got.cpu().long(), flat(want, True))
+    # FPS with ties, every start, K > len
+    idx = tp.sample_farthest_points(pp2, l2t, torch.tensor([70, 5, 333, 13]), [3, 0, 100, 39])
+    want = torch.cat([idx[b][idx[b] >= 0] + off2[b] for b in range(4)]).sort()[0]
+    got = ops.fps(p2.cuda(), s2, [70, 5, 333, 13], [3, 0, 100, 39])
+    assert torch.equal(got.cpu(), want)
+
+
+def test_no_cpu_path():
+    from curvecloudnet_b200 import native, ops
+    with pytest.raises((native.CcnError, TypeError, RuntimeError)):
+        ops.linear(torch.zeros(4, 4), torch.zeros(4, 4), None)
