@@ -1,0 +1,248 @@
+"""bench.py - CurveCloudNet nuScenes-shape segmentation forward (BASELINE.json configs[3]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one forward of the 33-step nuScenes CurveCloudNet over one synthetic 32-beam scan
+(~33 k points, B=1, eval semantics of the reference's val loop).  Per rank: S distinct scans are
+cycled; ranks shard scans, no data-path collective (per-scan inference has no cross-GPU dependency).
+
+One JSON line on stdout (rank 0):
+  value      points/s, whole job, inputs resident in HBM when a step starts (device-event time, max over ranks)
+  e2e        points/s through the public API (ModelBase.forward) from PINNED HOST buffers, H2D of the
+             scan and D2H of the logits inside the timed region
+  roofline   the dominant kernel family (the shared-MLP Linear kernel): algorithmic FLOPs / CUDA-event
+             time of its launches inside the timed steps, against the measured bf16 tensor peak
+  cpu_baseline  the CPU oracle (port of the reference, oracle/) timed on this host on a bounded sample
+--impl reference: the reference's CPU path = the oracle port (the reference itself cannot be imported
+  on this image), all host threads, bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "points/sec fwd seg (nuScenes-shape CurveCloudNet)"
+WORKLOAD = "nuScenes-shape CurveCloudNet segmentation forward, 32-beam synthetic scan, B=1 scan/step"
+CPU_SAMPLE_POINTS = 8000
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    def __init__(self, device_index):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device_index), "--query-gpu=" + q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [t.strip() for t in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def cpu_reference_points_per_s(sample_points, iters, warmup, threads):
+    """Times the CPU oracle (port of the reference) on a bounded azimuth sector of the same scan."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    torch.set_num_threads(threads)
+    data = driving_scan_batch([0], subsample=sample_points)
+    model = build_model(OracleModel, "nuscenes")
+    randomize_model_(model, 1234)
+    model.eval()
+    n = data.pos.shape[0]
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + iters):
+            torch.manual_seed(i)
+            t0 = time.perf_counter()
+            model(data)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    total = sum(times)
+    return n * len(times) / total, n, total / len(times)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    steps, warmup = max(args.steps, 1), max(min(args.warmup, 2), 1)
+    pps, n, sec = cpu_reference_points_per_s(CPU_SAMPLE_POINTS, steps, warmup, threads)
+    sample = "oracle port on a %d-point azimuth sector of scan seed 0 per step, %d threads" % (n, threads)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": pps, "unit": "points/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": pps, "unit": "points/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": pps, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scans", type=int, default=4, help="distinct synthetic scans cycled per rank")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    from curvecloudnet_b200 import native
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    native.load()
+    W, K = max(args.warmup, 3), max(args.steps, 1)
+
+    model = build_model(ModelBase, "nuscenes")
+    randomize_model_(model, 1234)
+    model = model.cuda().eval()
+    host_scans = [driving_scan_batch([1000 * rank + s]).pin_memory() for s in range(args.scans)]
+    dev_scans = [s.to("cuda") for s in host_scans]
+    pts = [s.num_points for s in host_scans]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_pass(steps, from_host, profile):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        outs, npts = [], 0
+        native.profile_begin(("ccn_linear_f32",) if profile else None)
+        barrier()
+        l0 = native.kernel_launches()
+        with torch.no_grad():
+            for i in range(steps):
+                flush.zero_()                                              # L2 flush, outside the timed span
+                j = i % args.scans
+                torch.manual_seed(i)
+                ev[i][0].record()
+                data = host_scans[j].to("cuda", non_blocking=True) if from_host else dev_scans[j]
+                logits = model(data)
+                if from_host:
+                    outs.append(logits.to("cpu", non_blocking=False))
+                ev[i][1].record()
+                npts += pts[j]
+        barrier()
+        launches = native.kernel_launches() - l0
+        prof = native.profile_end()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        return ms, npts, launches, prof, (logits.shape if steps else None)
+
+    timed_pass(W, False, False)                                            # warm-up
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, npts, launches, prof, oshape = timed_pass(K, False, True)
+    clocks = sampler.stop() if sampler else None
+    ms_e2e, npts_e2e, _, _, _ = timed_pass(K, True, False)
+
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([npts, npts_e2e], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_max, ms_e2e_max = [float(v) for v in t.tolist()]
+    tot_pts, tot_pts_e2e = [float(v) for v in tot.tolist()]
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peaks, peak_src = _peaks()
+    lin = prof.get("ccn_linear_f32", {"ms": 0.0, "calls": 0, "work": 0.0})
+    # the Linear kernel ran inside a long step: compare with the sustained GEMM figure
+    peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+    ach_tf = (lin["work"] / (lin["ms"] * 1e-3) / 1e12) if lin["ms"] > 0 else 0.0
+    roofline = {"bound": "tensor", "kernel": "linear_f32_kernel (ccn_linear_f32)", "achieved": ach_tf, "peak": peak_tf,
+                "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None, "traffic": None,
+                "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": lin["calls"],
+                "avg_launch_us": (lin["ms"] * 1e3 / lin["calls"]) if lin["calls"] else None,
+                "share_of_step": lin["ms"] / ms if ms else None,
+                "flops_per_step": lin["work"] / K}
+    mean_pts = tot_pts / (K * world)
+    h2d = sum(s.input_bytes() for s in host_scans) / len(host_scans)
+    d2h = mean_pts * (oshape[1] if oshape else 17) * 4
+    line = {
+        "metric": METRIC, "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "scans_per_s": (K * world) / (ms_max * 1e-3),
+        "config": {"workload": WORKLOAD, "points_per_scan": mean_pts, "scans_per_rank": args.scans,
+                   "parallelism": "scan-sharded dp%d, no collective" % world,
+                   "l2": "256 MiB buffer written between timed steps (L2 flush)"},
+        "e2e": {"value": tot_pts_e2e / (ms_e2e_max * 1e-3), "unit": "points/s", "h2d_bytes_per_step": int(h2d),
+                "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e_max / K},
+        "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        pps, n, sec = cpu_reference_points_per_s(CPU_SAMPLE_POINTS, 3, 1, threads)
+        line["cpu_baseline"] = {"value": pps, "unit": "points/s", "cores": threads, "kind": "port",
+                                "sample": "oracle port, %d-point azimuth sector of scan seed 0, 3 timed forwards, %.2f s each"
+                                          % (n, sec)}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -5,10 +5,13 @@
 
 #include "../../include/ccn_b200.h"
 
+extern unsigned long long g_ccn_kernel_launches;   // version.cu; one increment per <<<>>> (bench.py's gpu_launches)
+
 #define CCN_CHECK_LAUNCH()                                 \
     do {                                                   \
         cudaError_t e__ = cudaGetLastError();              \
         if (e__ != cudaSuccess) return (int)e__;           \
+        ++g_ccn_kernel_launches;                           \
     } while (0)
 
 #define CCN_REQUIRE(cond)                 \

@@ -86,16 +86,24 @@ __global__ void __launch_bounds__(1024) curve_fps_kernel(
     if (threadIdx.x == 0) *count_out = icarry;
 }
 
-// Per-curve statistics for radius_1d_group_subset (point_ops.py:149-167): one thread per curve,
-// f32 sums in index order.  stats[0] = max k_c (float bits), stats[1] = max #points (float bits).
-__global__ void radius_1d_curve_stats_kernel(const float* __restrict__ pos, const int32_t* __restrict__ ord,
-                                             const int32_t* __restrict__ cptr, int32_t n_curves, float radius,
-                                             float* __restrict__ kc, int32_t* __restrict__ stats) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// Per-curve statistics for radius_1d_group_subset (point_ops.py:149-167): one WARP per curve.  Lanes
+// load 32 edge norms at a time; the f32 sum still runs strictly in index order (shuffle broadcast of
+// lane 0, 1, 2, ...), as the oracle's scatter_add does.  stats[0] = max k_c, stats[1] = max #points (float bits).
+__global__ void __launch_bounds__(256) radius_1d_curve_stats_kernel(
+    const float* __restrict__ pos, const int32_t* __restrict__ ord, const int32_t* __restrict__ cptr,
+    int32_t n_curves, float radius, float* __restrict__ kc, int32_t* __restrict__ stats) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (c >= n_curves) return;
+    const int lane = ccn_lane();
     const int32_t b = cptr[c], e = cptr[c + 1];
     float len = 0.f;
-    for (int32_t i = b + 1; i < e; ++i) len = __fadd_rn(len, edge_to_prev(pos, ord, i));
+    for (int32_t i0 = b + 1; i0 < e; i0 += 32) {
+        const int32_t i = i0 + lane;
+        const float en = i < e ? edge_to_prev(pos, ord, i) : 0.f;
+        const int m = min(32, e - i0);
+        for (int l = 0; l < m; ++l) len = __fadd_rn(len, __shfl_sync(0xffffffffu, en, l));
+    }
+    if (lane != 0) return;
     const float cnt = (float)(e - b);
     const float avg = __fdiv_rn(len, cnt);
     float k = ceilf(__fmul_rn(__frcp_rn(avg), radius));
@@ -253,9 +261,8 @@ extern "C" int ccn_radius_1d_group_count(const float* pos, const int32_t* curve_
     cudaError_t e = cudaMemsetAsync(stats_scratch, 0, 2 * sizeof(int32_t), s);
     if (e != cudaSuccess) return (int)e;
     if (n_curves > 0) {
-        radius_1d_curve_stats_kernel<<<ccn_blocks_exact(n_curves, 128), 128, 0, s>>>(pos, curve_ord, curve_ptr,
-                                                                                    n_curves, radius, kc_scratch,
-                                                                                    stats_scratch);
+        radius_1d_curve_stats_kernel<<<ccn_blocks_exact((int64_t)n_curves * 32, 256), 256, 0, s>>>(
+            pos, curve_ord, curve_ptr, n_curves, radius, kc_scratch, stats_scratch);
         CCN_CHECK_LAUNCH();
     }
     if (nq > 0) {

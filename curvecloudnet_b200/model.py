@@ -12,7 +12,7 @@ import torch
 
 from . import modules as M
 from . import ops
-from .nn import MLP, Draws, ForwardCache
+from .nn import MLP, Draws, ForwardCache, get_precision, set_precision
 
 _DOWN_STEPS = ("sa", "sa-geo", "sa-global", "pt-transition-down")
 
@@ -72,6 +72,8 @@ class ModelBase(torch.nn.Module):
         self.in_dim, self.n_out = in_dim, n_out
         self.use_bias = kwargs.get("use_bias", False)
         self.version = kwargs.get("version", 2.0)
+        # arithmetic of the shared-MLP Linear layers: "fp32" | "bf16x3" | "bf16" (nn.set_precision); not a reference kwarg
+        self.precision = kwargs.pop("precision", "fp32")
         self.mlp_func = MLP
         self.step_names = list(steps)
         self.skip_connect_state_store = list(kwargs.get("skip_connect_state_store", []))
@@ -144,6 +146,14 @@ class ModelBase(torch.nn.Module):
 
     # ------------------------------------------------------------------------------ forward
     def forward(self, data, draws: Draws = None, **kwargs):
+        prev = get_precision()
+        set_precision(self.precision)
+        try:
+            return self._forward(data, draws, **kwargs)
+        finally:
+            set_precision(prev)
+
+    def _forward(self, data, draws: Draws = None, **kwargs):
         """base.py:133-175.  hist[k][i] is the INPUT of step i (the lists start with the raw input)."""
         if isinstance(data, list):
             data = Batch.from_data_list(data)

@@ -13,7 +13,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .nn import DEFAULT_DRAWS, MLP, Draws, fold_batchnorm, get_cache
+from .nn import DEFAULT_DRAWS, MLP, Draws, PreparedLinear, fold_batchnorm, get_cache
 
 
 def _cat_xyz(x, pos, with_xyz):
@@ -146,14 +146,15 @@ class PointNetConv2(nn.Module):
 
     def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR):
         layers = self.local_nn.layers()
-        w0, b0, act0, slope0 = layers[0]
+        l0 = layers[0]
         cx = 0 if x_src is None else x_src.shape[1]
-        assert w0.shape[1] == cx + 3, "local_nn input width %d != %d feature + 3 position columns" % (w0.shape[1], cx)
+        assert l0.in_features == cx + 3, "local_nn input width %d != %d feature + 3 position columns" % (l0.in_features, cx)
         if self._dec is None or self._dec_src is not layers:   # weight preparation, once per weight version
-            self._dec, self._dec_src = (w0[:, :cx].contiguous(), w0[:, cx:].t().contiguous()), layers
-        wx, wp = self._dec                                     # (C1, cx), (3, C1)
-        H = ops.linear(x_src, wx, None) if cx > 0 else None
-        msg = ops.edge_layer1(H, wp, b0, pos_src, pos_dst, edges, self.normalize_radius, act0, slope0)
+            lin_x = PreparedLinear(l0.w[:, :cx].contiguous(), None) if cx > 0 else None
+            self._dec, self._dec_src = (lin_x, l0.w[:, cx:].t().contiguous()), layers
+        lin_x, wp = self._dec                                  # x part (C1, cx) and positional part (3, C1)
+        H = lin_x(x_src) if lin_x is not None else None
+        msg = ops.edge_layer1(H, wp, l0.b, pos_src, pos_dst, edges, self.normalize_radius, l0.act, l0.slope)
         msg = self.local_nn.forward_from(msg, 1)
         if self.aggr_type in ("max", "mean"):
             out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, self.aggr_type)
@@ -339,22 +340,22 @@ class SGCNNLayer(nn.Module):
     def _decomposed(self):
         layers = self.nn.layers()
         if self._dec is None or self._dec_src is not layers:
-            w0, b0, act0, slope0 = layers[0]
-            c = w0.shape[1] // 2
-            wa, wb = w0[:, :c], w0[:, c:]
-            zero = torch.zeros_like(b0)
+            l0 = layers[0]
+            c = l0.in_features // 2
+            wa, wb = l0.w[:, :c], l0.w[:, c:]
+            zero = torch.zeros_like(l0.b)
             if self.use_sparse_feat_agg:     # [x_i, x_j - x_i]: P (per source j) = Wb, Q (per target i) = Wa - Wb
-                wpq, bpq = torch.cat([wb, wa - wb], dim=0), torch.cat([zero, b0])
+                wpq, bpq = torch.cat([wb, wa - wb], dim=0), torch.cat([zero, l0.b])
             else:                            # [x_j, x_i - x_j]: P (per neighbour j) = Wa - Wb, Q (per point i) = Wb
-                wpq, bpq = torch.cat([wa - wb, wb], dim=0), torch.cat([zero, b0])
-            self._dec, self._dec_src = (wpq.contiguous(), bpq.contiguous(), act0, slope0), layers
+                wpq, bpq = torch.cat([wa - wb, wb], dim=0), torch.cat([zero, l0.b])
+            self._dec, self._dec_src = (PreparedLinear(wpq.contiguous(), bpq.contiguous()), l0.act, l0.slope), layers
         return self._dec
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
         sptr = get_cache(kwargs).sample_ptr(batch)
         x = _cat_xyz(x, pos, self.with_xyz)
-        wpq, bpq, act0, slope0 = self._decomposed()
-        PQ = ops.linear(x, wpq, bpq)
+        lin_pq, act0, slope0 = self._decomposed()
+        PQ = lin_pq(x)
         if not self.use_sparse_feat_agg:
             if self.aggr_type != "max":
                 raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")

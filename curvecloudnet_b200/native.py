@@ -69,13 +69,41 @@ class CcnError(RuntimeError):
     pass
 
 
-launch_count = 0   # kernels-launching library calls made through this binding (bench.py reads it)
+# ---- optional per-entry-point device timing (bench.py's roofline leg) -------------------------------
+_prof_names = None
+_prof_events = []          # (name, start event, end event, algorithmic work of the call)
+
+# algorithmic work of one call: FLOPs for the Linear kernels (2 M N K)
+_WORK = {
+    "ccn_linear_f32": lambda a: 2.0 * a[7] * a[8] * a[9],
+    "ccn_linear_tc": lambda a: 2.0 * a[7] * a[8] * a[9],
+}
+
+
+def profile_begin(names):
+    global _prof_names, _prof_events
+    _prof_names = set(names) if names else None
+    _prof_events = []
+
+
+def profile_end():
+    """-> {name: {"ms": device time, "calls": n, "work": summed algorithmic work}} (synchronises)."""
+    global _prof_names
+    out = {}
+    if _prof_events:
+        torch.cuda.synchronize()
+    for name, a, b, work in _prof_events:
+        d = out.setdefault(name, {"ms": 0.0, "calls": 0, "work": 0.0})
+        d["ms"] += a.elapsed_time(b)
+        d["calls"] += 1
+        d["work"] += work
+    _prof_names = None
+    return out
 
 
 def call(name, *args):
     """Call a C-ABI entry point; torch tensors become device pointers, the current stream is appended."""
-    global launch_count
-    lib = load()
+    lib = _lib if _lib is not None else load()
     conv = []
     for a in args:
         if torch.is_tensor(a):
@@ -85,12 +113,22 @@ def call(name, *args):
         else:
             conv.append(a)
     conv.append(torch.cuda.current_stream().cuda_stream)
+    timed = _prof_names is not None and name in _prof_names
+    if timed:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     rc = getattr(lib, name)(*conv)
-    launch_count += 1
+    if timed:
+        e1.record()
+        _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
     if rc != 0:
         if rc < 0:
             raise CcnError("%s: invalid argument (code %d)" % (name, rc))
         raise CcnError("%s: CUDA error %d" % (name, rc))
+
+
+def kernel_launches() -> int:
+    return int(load().ccn_kernel_launches())
 
 
 def grid_num_cells(n2: int) -> int:

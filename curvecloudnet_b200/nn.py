@@ -99,6 +99,53 @@ def fold_batchnorm(weight: torch.Tensor, bias: Optional[torch.Tensor], bn: Optio
     return w.contiguous(), b.contiguous()
 
 
+_PRECISION = {"mode": "fp32"}
+PRECISIONS = ("fp32", "bf16x3", "bf16")
+
+
+def set_precision(mode: str):
+    """Arithmetic of the shared-MLP Linear layers:
+       "fp32"    FP32-pipe kernel (ccn_linear_f32), the 1e-4 reference path;
+       "bf16x3"  tcgen05 tensor cores, split-bf16 x3 (fp32-class accuracy, 1e-4 budget);
+       "bf16"    tcgen05 tensor cores, plain bf16 operands, fp32 accumulation (2e-2 budget)."""
+    if mode not in PRECISIONS:
+        raise ValueError("precision must be one of %s" % (PRECISIONS,))
+    _PRECISION["mode"] = mode
+
+
+def get_precision() -> str:
+    return _PRECISION["mode"]
+
+
+class PreparedLinear:
+    """One Linear layer ready for the kernels: fp32 (W, b) with BatchNorm folded, activation, and (lazily)
+    the bf16 hi/lo copies + TMA descriptors of the tensor-core path.  Weight preparation only."""
+
+    __slots__ = ("w", "b", "act", "slope", "_tc")
+
+    def __init__(self, w, b, act=ops.ACT_NONE, slope=0.01):
+        self.w, self.b, self.act, self.slope, self._tc = w.contiguous(), b, act, slope, None
+
+    @property
+    def out_features(self):
+        return self.w.shape[0]
+
+    @property
+    def in_features(self):
+        return self.w.shape[1]
+
+    def tc(self):
+        if self._tc is None:
+            self._tc = ops.prepare_tc_weight(self.w)
+        return self._tc
+
+    def __call__(self, x):
+        mode = _PRECISION["mode"]
+        if mode == "fp32":
+            return ops.linear(x, self.w, self.b, self.act, self.slope)
+        return ops.linear_tc(x, self.tc(), self.b, self.act, self.slope, 3 if mode == "bf16x3" else 1)
+
+
 class MLP(torch.nn.Module):
     def __init__(self, channel_list: Sequence[int], *, dropout: Union[float, List[float]] = 0.0, act="relu",
                  act_first: bool = False, norm: Optional[str] = "batch_norm", plain_last: bool = True,
@@ -164,7 +211,7 @@ class MLP(torch.nn.Module):
         return tuple(k)
 
     def layers(self):
-        """[(W', b', act code, slope)] with BatchNorm(eval) folded; cached until a parameter changes."""
+        """[PreparedLinear] with BatchNorm(eval) folded; cached until a parameter changes."""
         if self.training:
             raise NotImplementedError(
                 "curvecloudnet_b200 round 1 implements the inference (eval) path; call model.eval()")
@@ -178,17 +225,17 @@ class MLP(torch.nn.Module):
                     bn = self.norms[i].module
                 w, b = fold_batchnorm(lin.weight, lin.bias, bn)
                 hidden = i < len(self.lins) - 1 or not self.plain_last
-                out.append((w, b, act if hidden else ops.ACT_NONE, slope))
+                out.append(PreparedLinear(w, b, act if hidden else ops.ACT_NONE, slope))
             self._folded, self._folded_key = out, key
         return self._folded
 
     def forward(self, x, *args, **kwargs):
-        for w, b, act, slope in self.layers():
-            x = ops.linear(x, w, b, act, slope)
+        for lin in self.layers():
+            x = lin(x)
         return x
 
     def forward_from(self, x, first: int):
         """Run layers first.. (the first layer(s) having been applied in a fused/decomposed form)."""
-        for w, b, act, slope in self.layers()[first:]:
-            x = ops.linear(x, w, b, act, slope)
+        for lin in self.layers()[first:]:
+            x = lin(x)
         return x

@@ -426,3 +426,45 @@ def sample_ptr_any(ids: torch.Tensor) -> torch.Tensor:
     zeros = torch.zeros_like(ids)
     topo = curve_csr(zeros, ids)
     return topo.curve_ptr.to(torch.int64)
+
+
+# ----------------------------------------------------------------------------------------------
+# tensor-core Linear (tcgen05): weight preparation + launch
+# ----------------------------------------------------------------------------------------------
+class TcWeight:
+    """bf16 hi/lo copies of a folded fp32 weight (N, K), K padded to 64, and their host-side TMA descriptors."""
+
+    def __init__(self, w: torch.Tensor):
+        import ctypes
+        w, ldw = _rows(w)
+        n, k = w.shape
+        self.n, self.k = n, k
+        self.kpad = (k + 63) // 64 * 64
+        self.box_n = 32 if n <= 32 else 64 if n <= 64 else 128
+        buf = torch.empty((2, n, self.kpad), dtype=torch.bfloat16, device=w.device)
+        self.hi, self.lo = buf[0], buf[1]
+        call("ccn_split_bf16", w, ldw, n, k, self.kpad, self.hi, self.lo)
+        self.map_hi = ctypes.create_string_buffer(128 + 64)
+        self.map_lo = ctypes.create_string_buffer(128 + 64)
+        lib = native.load()
+        self.p_hi = (ctypes.addressof(self.map_hi) + 63) & ~63          # CUtensorMap wants 64-byte alignment
+        self.p_lo = (ctypes.addressof(self.map_lo) + 63) & ~63
+        for ptr, t in ((self.p_hi, self.hi), (self.p_lo, self.lo)):
+            rc = lib.ccn_weight_tensor_map(ptr, t.data_ptr(), n, self.kpad, self.box_n)
+            if rc:
+                raise native.CcnError("ccn_weight_tensor_map failed (code %d)" % rc)
+
+
+def prepare_tc_weight(w: torch.Tensor) -> TcWeight:
+    return TcWeight(w)
+
+
+def linear_tc(A: torch.Tensor, tw: TcWeight, bias: Optional[torch.Tensor], act: int, slope: float, mode: int):
+    """Y = act(A W^T + bias) on tcgen05; mode 1 = bf16, 3 = split-bf16 x3."""
+    A, lda = _rows(A)
+    M, K = A.shape
+    assert K == tw.k, (A.shape, tw.k)
+    Y = _empty((M, tw.n), torch.float32, A)
+    call("ccn_linear_tc", A, lda, tw.p_hi, tw.p_lo, bias if bias is not None else 0, Y, tw.n, M, tw.n, K, tw.box_n,
+         mode, act, float(slope))
+    return Y

@@ -51,6 +51,8 @@ typedef struct CUstream_st* ccn_stream_t;
 #define CCN_TOPO_ERR_BATCH_NOT_DENSE 8
 
 int ccn_version(void);
+/* number of kernels this library has launched in this process (bench.py reports it as gpu_launches). */
+int64_t ccn_kernel_launches(void);
 
 /* ---- curve / sample topology -------------------------------------------------------------------
  * replaces curveidx_local2global + batch2ptr + is_sorted asserts
@@ -172,6 +174,19 @@ int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr, const floa
  * Y = act(A W^T + bias), W is (N, K) row-major with BatchNorm(eval) folded by the caller. */
 int ccn_linear_f32(const float* A, int64_t lda, const float* W, int64_t ldw, const float* bias, float* Y, int64_t ldy,
                    int64_t M, int32_t N, int32_t K, int32_t act, float slope, ccn_stream_t stream);
+
+
+/* Tensor-core path of the same layer (tcgen05.mma kind::f16, fp32 accumulation in TMEM, weights by TMA):
+ *   ccn_split_bf16         W fp32 (n,k) -> bf16 hi (n,kpad) [+ residual lo], kpad % 64 == 0, zero padded;
+ *   ccn_weight_tensor_map  HOST call: fills a 128-byte CUtensorMap (host memory) for such a weight, box = 64 x box_n;
+ *   ccn_linear_tc          mode 1: bf16 (2e-2 budget); mode 3: split-bf16 x3 (A_hi W_hi + A_lo W_hi + A_hi W_lo, fp32-class
+ *                          accuracy for the 1e-4 budget).  A and Y stay fp32 in HBM; box_n in {32, 64, 128, 256}. */
+int ccn_split_bf16(const float* w, int64_t ldw, int32_t n, int32_t k, int32_t kpad, void* hi, void* lo,
+                   ccn_stream_t stream);
+int ccn_weight_tensor_map(void* tmap_out_host, const void* w_bf16, int32_t n, int32_t kpad, int32_t box_n);
+int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_host, const void* w_lo_tmap_host,
+                  const float* bias, float* Y, int64_t ldy, int64_t M, int32_t N, int32_t K, int32_t box_n, int32_t mode,
+                  int32_t act, float slope, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -167,3 +167,28 @@ def test_no_cpu_path():
     from curvecloudnet_b200 import native, ops
     with pytest.raises((native.CcnError, TypeError, RuntimeError)):
         ops.linear(torch.zeros(4, 4), torch.zeros(4, 4), None)
+
+
+@pytest.mark.parametrize("mode,tol", [(3, 2e-5), (1, 1e-2)])
+def test_linear_tensor_core(mode, tol):
+    """tcgen05 Linear (ccn_linear_tc) vs float64: x3 split-bf16 is fp32-class, plain bf16 within its budget."""
+    from curvecloudnet_b200 import ops
+    gen = torch.Generator().manual_seed(1)
+    shapes = [(1, 5, 3, 0), (130, 64, 67, 1), (777, 129, 259, 2), (40000, 64, 38, 1), (300, 1024, 2051, 1),
+              (5000, 256, 256, 0), (129, 17, 64, 0), (4096, 192, 128, 2), (257, 32, 640, 1)]
+    for (m, n, k, act) in shapes:
+        a = torch.randn(m, k, generator=gen)
+        w = torch.randn(n, k, generator=gen) / k ** 0.5
+        b = torch.randn(n, generator=gen)
+        ref = a.double() @ w.double().t() + b.double()
+        if act == 1:
+            ref = ref.clamp(min=0)
+        elif act == 2:
+            ref = torch.where(ref > 0, ref, ref * 0.01)
+        tw = ops.prepare_tc_weight(w.cuda())
+        y = ops.linear_tc(a.cuda(), tw, b.cuda(), act, 0.01, mode).cpu()
+        assert torch.isfinite(y).all(), (m, n, k, act)
+        assert rel_err(y, ref.float()) <= tol, (m, n, k, act, rel_err(y, ref.float()))
+        a2 = torch.randn(m, k + 5, generator=gen)          # unaligned, strided A; no bias
+        y2 = ops.linear_tc(a2.cuda()[:, 2:2 + k], tw, None, 0, 0.01, mode).cpu()
+        assert rel_err(y2, (a2[:, 2:2 + k].double() @ w.double().t()).float()) <= tol, (m, n, k, "strided")
