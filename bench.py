@@ -130,6 +130,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scans", type=int, default=4, help="distinct synthetic scans cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch", type=int, default=1, help="scans per step (one ModelBase.forward call)")
+    ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"],
+                    help="shared-MLP Linear arithmetic: fp32 pipe | tcgen05 split-bf16 x3 (1e-4 budget) | tcgen05 bf16 (2e-2 budget)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -152,10 +155,12 @@ def main():
     native.load()
     W, K = max(args.warmup, 3), max(args.steps, 1)
 
-    model = build_model(ModelBase, "nuscenes")
+    model = build_model(ModelBase, "nuscenes", precision=args.precision)
     randomize_model_(model, 1234)
     model = model.cuda().eval()
-    host_scans = [driving_scan_batch([1000 * rank + s]).pin_memory() for s in range(args.scans)]
+    lin_name = "ccn_linear_f32" if args.precision == "fp32" else "ccn_linear_tc"
+    host_scans = [driving_scan_batch([1000 * rank + args.batch * s + b for b in range(args.batch)]).pin_memory()
+                  for s in range(args.scans)]
     dev_scans = [s.to("cuda") for s in host_scans]
     pts = [s.num_points for s in host_scans]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
@@ -169,7 +174,7 @@ def main():
     def timed_pass(steps, from_host, profile):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         outs, npts = [], 0
-        native.profile_begin(("ccn_linear_f32",) if profile else None)
+        native.profile_begin((lin_name,) if profile else None)
         barrier()
         l0 = native.kernel_launches()
         with torch.no_grad():
@@ -209,11 +214,12 @@ def main():
         return
 
     peaks, peak_src = _peaks()
-    lin = prof.get("ccn_linear_f32", {"ms": 0.0, "calls": 0, "work": 0.0})
+    lin = prof.get(lin_name, {"ms": 0.0, "calls": 0, "work": 0.0})
     # the Linear kernel ran inside a long step: compare with the sustained GEMM figure
     peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
     ach_tf = (lin["work"] / (lin["ms"] * 1e-3) / 1e12) if lin["ms"] > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "linear_f32_kernel (ccn_linear_f32)", "achieved": ach_tf, "peak": peak_tf,
+    roofline = {"bound": "tensor", "kernel": "linear_f32_kernel (ccn_linear_f32)" if args.precision == "fp32" else
+                "linear_tc_kernel<%d> (ccn_linear_tc, tcgen05)" % (3 if args.precision == "bf16x3" else 1), "achieved": ach_tf, "peak": peak_tf,
                 "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None, "traffic": None,
                 "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": lin["calls"],
                 "avg_launch_us": (lin["ms"] * 1e3 / lin["calls"]) if lin["calls"] else None,
@@ -224,9 +230,12 @@ def main():
     d2h = mean_pts * (oshape[1] if oshape else 17) * 4
     line = {
         "metric": METRIC, "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "scans_per_s": (K * world) / (ms_max * 1e-3),
-        "config": {"workload": WORKLOAD, "points_per_scan": mean_pts, "scans_per_rank": args.scans,
+        "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (split-bf16 tensor-core MLPs, fp32-class accuracy; all else f32)",
+                  "bf16": "bf16 (tensor-core MLPs, fp32 accumulate; all else f32)"}[args.precision],
+        "data": "synthetic", "scans_per_s": (K * world * args.batch) / (ms_max * 1e-3),
+        "config": {"workload": WORKLOAD.replace("B=1", "B=%d" % args.batch), "points_per_step": mean_pts,
+                   "scans_per_step": args.batch, "distinct_batches_per_rank": args.scans,
                    "parallelism": "scan-sharded dp%d, no collective" % world,
                    "l2": "256 MiB buffer written between timed steps (L2 flush)"},
         "e2e": {"value": tot_pts_e2e / (ms_e2e_max * 1e-3), "unit": "points/s", "h2d_bytes_per_step": int(h2d),

@@ -303,8 +303,13 @@ extern "C" int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_
     CCN_REQUIRE(box_n == 32 || box_n == 64 || box_n == 128 || box_n == 256);
     if (M == 0) return CCN_OK;
     const int per_stage = (mode == 3 ? 2 : 1) * (kABytes + box_n * kBK * 2);
-    int stages = 3;
-    while (stages > 2 && stages * per_stage + 1024 > 200 * 1024) --stages;
+    // large grids: keep two CTAs per SM resident (epilogue of one overlaps the main loop of the other);
+    // skinny problems (at most one CTA per SM anyway): spend the shared memory on a deeper pipeline
+    const int64_t tiles = ((M + kBM - 1) / kBM) * ((N + box_n - 1) / box_n);
+    const int budget = (tiles > 148 ? 100 : 200) * 1024;
+    int stages = (budget - 1024) / per_stage;
+    if (stages > 8) stages = 8;
+    if (stages < 2) stages = 2;
     const int nk = (K + kBK - 1) / kBK;
     if (stages > nk) stages = nk < 2 ? 2 : nk;
     const int smem = stages * per_stage + 1024;

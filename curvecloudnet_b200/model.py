@@ -11,7 +11,7 @@ import copy
 import torch
 
 from . import modules as M
-from . import ops
+from . import native, ops
 from .nn import MLP, Draws, ForwardCache, get_precision, set_precision
 
 _DOWN_STEPS = ("sa", "sa-geo", "sa-global", "pt-transition-down")
@@ -148,9 +148,11 @@ class ModelBase(torch.nn.Module):
     def forward(self, data, draws: Draws = None, **kwargs):
         prev = get_precision()
         set_precision(self.precision)
+        native.pin_stream(True)
         try:
             return self._forward(data, draws, **kwargs)
         finally:
+            native.pin_stream(False)
             set_precision(prev)
 
     def _forward(self, data, draws: Draws = None, **kwargs):

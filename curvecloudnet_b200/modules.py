@@ -208,7 +208,7 @@ class SAModule(nn.Module):
         if sptr_q is not None:
             cache.put_sample_ptr(batchq, sptr_q)
         if self.use_fast_knn:
-            nbr, _, cnt = ops.frnn_knn(posq, batchq, pos, batch, sptr, self.knn, self.r, want_cnt=True)
+            nbr, _, cnt = ops.frnn_knn(posq, batchq, pos, batch, sptr, self.knn, self.r, want_cnt=True, cache=cache)
         else:
             nbr, cnt = ops.ball_query(posq, batchq, pos, sptr, self.r, 128)
         edges = ops.dense_to_csr(nbr, cnt)
@@ -352,19 +352,20 @@ class SGCNNLayer(nn.Module):
         return self._dec
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
-        sptr = get_cache(kwargs).sample_ptr(batch)
+        cache = get_cache(kwargs)
+        sptr = cache.sample_ptr(batch)
         x = _cat_xyz(x, pos, self.with_xyz)
         lin_pq, act0, slope0 = self._decomposed()
         PQ = lin_pq(x)
         if not self.use_sparse_feat_agg:
             if self.aggr_type != "max":
                 raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
-            nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r)
+            nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, cache=cache)
             h = ops.sgcnn_layer1(PQ, nbr, act0, slope0)
             h = self.nn.forward_from(h, 1)
             return ops.group_max_dense(h, nbr), pos, batch, point2curveidx
         if self.use_fast_knn:
-            nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, want_cnt=True)
+            nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, want_cnt=True, cache=cache)
         else:
             nbr, _, cnt = ops.knn_exact(pos, batch, pos, sptr, self.k, zero_fill=True, want_d2=False, want_cnt=True)
         edges = ops.dense_to_csr(nbr, cnt)

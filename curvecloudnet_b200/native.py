@@ -71,6 +71,7 @@ class CcnError(RuntimeError):
 
 # ---- optional per-entry-point device timing (bench.py's roofline leg) -------------------------------
 _prof_names = None
+_prof_shapes = []          # (M, N, K) of every timed Linear call (tools/profile_forward.py)
 _prof_events = []          # (name, start event, end event, algorithmic work of the call)
 
 # algorithmic work of one call: FLOPs for the Linear kernels (2 M N K)
@@ -84,6 +85,7 @@ def profile_begin(names):
     global _prof_names, _prof_events
     _prof_names = set(names) if names else None
     _prof_events = []
+    del _prof_shapes[:]
 
 
 def profile_end():
@@ -101,6 +103,16 @@ def profile_end():
     return out
 
 
+_stream_handle = None      # set for the duration of a forward (ModelBase.forward) to skip the per-call lookup
+
+
+def pin_stream(on: bool):
+    """Cache torch's current CUDA stream handle for subsequent calls (the caller must not switch streams
+    while pinned); pin_stream(False) returns to per-call lookup."""
+    global _stream_handle
+    _stream_handle = torch.cuda.current_stream().cuda_stream if on else None
+
+
 def call(name, *args):
     """Call a C-ABI entry point; torch tensors become device pointers, the current stream is appended."""
     lib = _lib if _lib is not None else load()
@@ -112,7 +124,7 @@ def call(name, *args):
             conv.append(a.data_ptr())
         else:
             conv.append(a)
-    conv.append(torch.cuda.current_stream().cuda_stream)
+    conv.append(_stream_handle if _stream_handle is not None else torch.cuda.current_stream().cuda_stream)
     timed = _prof_names is not None and name in _prof_names
     if timed:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -121,6 +133,8 @@ def call(name, *args):
     if timed:
         e1.record()
         _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
+        if name in _WORK:
+            _prof_shapes.append((args[7], args[8], args[9]))
     if rc != 0:
         if rc < 0:
             raise CcnError("%s: invalid argument (code %d)" % (name, rc))

@@ -45,6 +45,8 @@ class ForwardCache:
     def __init__(self):
         self._sptr = {}
         self._topo = {}
+        self.grids = {}     # (pos2 ptr, n2, radius) -> hashed grid          (ops.frnn_knn)
+        self.knn = {}       # (pos1 ptr, pos2 ptr, n1, n2, K, radius) -> idx  (ops.frnn_knn)
 
     def sample_ptr(self, batch: torch.Tensor) -> ops.SamplePtr:
         key = (batch.data_ptr(), batch.shape[0])

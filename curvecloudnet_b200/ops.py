@@ -265,20 +265,39 @@ def fps(pos: torch.Tensor, sptr: SamplePtr, ksel: List[int], starts: List[int]) 
 # ----------------------------------------------------------------------------------------------
 # neighbour search
 # ----------------------------------------------------------------------------------------------
-def frnn_knn(pos1, batch1, pos2, batch2, sptr2: SamplePtr, K: int, radius: float, want_d2=False, want_cnt=False):
-    """Fixed-radius kNN -> idx int32 (n1, K) GLOBAL rows of pos2, -1 padded, ascending by (d2, index)."""
+def frnn_knn(pos1, batch1, pos2, batch2, sptr2: SamplePtr, K: int, radius: float, want_d2=False, want_cnt=False,
+             cache=None):
+    """Fixed-radius kNN -> idx int32 (n1, K) GLOBAL rows of pos2, -1 padded, ascending by (d2, index).
+    `cache` (nn.ForwardCache): the hashed grid of (pos2, radius) and, for plain index queries, the whole
+    result are memoised for the forward - the reference rebuilds both at every step that searches the
+    same level with the same (K, r)."""
     pos1, pos2, batch1, batch2 = _f32(pos1), _f32(pos2), _i64(batch1), _i64(batch2)
     n1, n2 = pos1.shape[0], pos2.shape[0]
-    cells = native.grid_num_cells(n2)
-    cell_off = _empty((cells + 1,), torch.int32, pos1)
-    slot = _empty((max(n2, 1),), torch.int32, pos1)
-    sorted_ = _empty((max(n2, 1), 4), torch.float32, pos1)
-    call("ccn_grid_build", pos2, batch2, n2, float(radius), cells, cell_off, slot, sorted_)
+    radius = float(radius)
+    rkey = (pos1.data_ptr(), pos2.data_ptr(), n1, n2, K, radius)
+    if cache is not None and not (want_d2 or want_cnt):
+        hit = cache.knn.get(rkey)
+        if hit is not None:
+            return hit[0], None, None
+    gkey = (pos2.data_ptr(), n2, radius)
+    grid = cache.grids.get(gkey) if cache is not None else None
+    if grid is None:
+        cells = native.grid_num_cells(n2)
+        cell_off = _empty((cells + 1,), torch.int32, pos1)
+        slot = _empty((max(n2, 1),), torch.int32, pos1)
+        sorted_ = _empty((max(n2, 1), 4), torch.float32, pos1)
+        call("ccn_grid_build", pos2, batch2, n2, radius, cells, cell_off, slot, sorted_)
+        grid = (cells, cell_off, sorted_, pos2)
+        if cache is not None:
+            cache.grids[gkey] = grid
+    cells, cell_off, sorted_, _ = grid
     idx = _empty((n1, K), torch.int32, pos1)
     d2 = _empty((n1, K), torch.float32, pos1) if want_d2 else None
     cnt = _empty((n1 + 2,), torch.int32, pos1) if want_cnt else None
-    call("ccn_frnn_knn", pos1, batch1, n1, sorted_, cell_off, cells, sptr2.dev, float(radius), K, idx,
+    call("ccn_frnn_knn", pos1, batch1, n1, sorted_, cell_off, cells, sptr2.dev, radius, K, idx,
          d2 if want_d2 else 0, cnt if want_cnt else 0)
+    if cache is not None and not (want_d2 or want_cnt):
+        cache.knn[rkey] = (idx, pos1, pos2)
     return idx, d2, cnt
 
 
@@ -432,27 +451,45 @@ def sample_ptr_any(ids: torch.Tensor) -> torch.Tensor:
 # tensor-core Linear (tcgen05): weight preparation + launch
 # ----------------------------------------------------------------------------------------------
 class TcWeight:
-    """bf16 hi/lo copies of a folded fp32 weight (N, K), K padded to 64, and their host-side TMA descriptors."""
+    """bf16 hi/lo copies of a folded fp32 weight (N, K), K padded to 64, and their host-side TMA descriptors
+    (one pair per N-tile width)."""
 
     def __init__(self, w: torch.Tensor):
-        import ctypes
         w, ldw = _rows(w)
         n, k = w.shape
         self.n, self.k = n, k
         self.kpad = (k + 63) // 64 * 64
-        self.box_n = 32 if n <= 32 else 64 if n <= 64 else 128
+        self.max_box = 32 if n <= 32 else 64 if n <= 64 else 128
         buf = torch.empty((2, n, self.kpad), dtype=torch.bfloat16, device=w.device)
         self.hi, self.lo = buf[0], buf[1]
         call("ccn_split_bf16", w, ldw, n, k, self.kpad, self.hi, self.lo)
-        self.map_hi = ctypes.create_string_buffer(128 + 64)
-        self.map_lo = ctypes.create_string_buffer(128 + 64)
-        lib = native.load()
-        self.p_hi = (ctypes.addressof(self.map_hi) + 63) & ~63          # CUtensorMap wants 64-byte alignment
-        self.p_lo = (ctypes.addressof(self.map_lo) + 63) & ~63
-        for ptr, t in ((self.p_hi, self.hi), (self.p_lo, self.lo)):
-            rc = lib.ccn_weight_tensor_map(ptr, t.data_ptr(), n, self.kpad, self.box_n)
-            if rc:
-                raise native.CcnError("ccn_weight_tensor_map failed (code %d)" % rc)
+        self._maps = {}
+
+    def maps(self, box_n: int):
+        hit = self._maps.get(box_n)
+        if hit is None:
+            import ctypes
+            lib = native.load()
+            bufs, ptrs = [], []
+            for t in (self.hi, self.lo):
+                b = ctypes.create_string_buffer(128 + 64)
+                p = (ctypes.addressof(b) + 63) & ~63                     # CUtensorMap wants 64-byte alignment
+                rc = lib.ccn_weight_tensor_map(p, t.data_ptr(), self.n, self.kpad, box_n)
+                if rc:
+                    raise native.CcnError("ccn_weight_tensor_map failed (code %d)" % rc)
+                bufs.append(b)
+                ptrs.append(p)
+            hit = (ptrs[0], ptrs[1], bufs)
+            self._maps[box_n] = hit
+        return hit
+
+    def pick_box(self, m: int) -> int:
+        """Widest N tile that still yields >= one wave of CTAs (148 SMs); skinny problems get narrow tiles."""
+        box = self.max_box
+        mt = (m + 127) // 128
+        while box > 32 and mt * ((self.n + box - 1) // box) < 148:
+            box //= 2
+        return box
 
 
 def prepare_tc_weight(w: torch.Tensor) -> TcWeight:
@@ -465,6 +502,8 @@ def linear_tc(A: torch.Tensor, tw: TcWeight, bias: Optional[torch.Tensor], act: 
     M, K = A.shape
     assert K == tw.k, (A.shape, tw.k)
     Y = _empty((M, tw.n), torch.float32, A)
-    call("ccn_linear_tc", A, lda, tw.p_hi, tw.p_lo, bias if bias is not None else 0, Y, tw.n, M, tw.n, K, tw.box_n,
-         mode, act, float(slope))
+    box = tw.pick_box(M)
+    p_hi, p_lo, _ = tw.maps(box)
+    call("ccn_linear_tc", A, lda, p_hi, p_lo, bias if bias is not None else 0, Y, tw.n, M, tw.n, K, box, mode, act,
+         float(slope))
     return Y

@@ -1,0 +1,44 @@
+"""Dev tool: per-entry-point device time of one nuScenes-shape forward (CUDA events around every C-ABI call)."""
+import sys, os, collections
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from curvecloudnet_b200 import native
+from curvecloudnet_b200.configs import build_model
+from curvecloudnet_b200.model import ModelBase
+from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+
+prec = sys.argv[1] if len(sys.argv) > 1 else "bf16"
+model = build_model(ModelBase, "nuscenes", precision=prec)
+randomize_model_(model, 1234)
+model = model.cuda().eval()
+data = driving_scan_batch([0]).to("cuda")
+with torch.no_grad():
+    for _ in range(3):
+        torch.manual_seed(0); model(data)
+torch.cuda.synchronize()
+native.profile_begin(list(native.SIGNATURES))
+native._prof_detail = True
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+import time
+t0 = time.perf_counter()
+e0.record()
+with torch.no_grad():
+    torch.manual_seed(0); model(data)
+e1.record()
+torch.cuda.synchronize()
+wall = time.perf_counter() - t0
+ev = list(native._prof_events)
+prof = native.profile_end()
+print("forward: %.3f ms device span, %.3f ms wall (with event overhead)" % (e0.elapsed_time(e1), wall * 1e3))
+tot = sum(d["ms"] for d in prof.values())
+print("sum of per-call device times: %.3f ms over %d calls" % (tot, sum(d["calls"] for d in prof.values())))
+for k, d in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]):
+    print("  %-28s calls %4d  %8.3f ms  %5.1f%%" % (k, d["calls"], d["ms"], 100 * d["ms"] / tot))
+print("linear calls (M, N, K) us TFLOP/s:")
+rows = []
+for name, a, b, work in ev:
+    if name.startswith("ccn_linear"):
+        rows.append((a.elapsed_time(b) * 1e3, work))
+shapes = native._prof_shapes
+for (us, work), shp in zip(rows, shapes):
+    print("   M=%7d N=%5d K=%5d  %8.1f us  %7.1f TF/s" % (shp[0], shp[1], shp[2], us, work / us / 1e6))
