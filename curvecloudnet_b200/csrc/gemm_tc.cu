@@ -288,10 +288,24 @@ extern "C" int ccn_weight_tensor_map(void* tmap_out_host, const void* w_bf16, in
     cuuint64_t strides[1] = {(cuuint64_t)kpad * 2};
     cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_n};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = cuTensorMapEncodeTiled((CUtensorMap*)tmap_out_host, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                                        const_cast<void*>(w_bf16), dims, strides, box, estr,
-                                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    // libcuda is resolved at run time through the runtime's driver entry point (the library must load, and
+    // export its symbols, on hosts without a driver; nothing here links -lcuda).
+    typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeTiled encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess) return (int)e;
+        if (q != cudaDriverEntryPointSuccess || !fn) return CCN_EUNSUPPORTED;
+        encode = (EncodeTiled)fn;
+    }
+    CUresult r = encode((CUtensorMap*)tmap_out_host, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(w_bf16), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? CCN_OK : 1000 + (int)r;
 }
 

@@ -1,0 +1,24 @@
+#!/bin/bash
+# One GPU-box pass: parity tests, bench lines (three precisions), per-entry-point timing, ncu launch list.
+# Usage (from the repo root, under gpurun):  bash tools/gpu_check.sh [tag]
+TAG=${1:-r01}
+O=gpurun_out
+mkdir -p $O
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/${TAG}_smi.txt 2>&1
+python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> $O/${TAG}_pytest_gpu.log
+tail -5 $O/${TAG}_pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; echo "smoke exit $?" >> $O/${TAG}_smoke.log
+tail -2 $O/${TAG}_smoke.log
+python bench.py --steps 20 --warmup 5 > $O/${TAG}_bench_bf16x3.json 2> $O/${TAG}_bench_bf16x3.err; echo "bench exit $?"
+cat $O/${TAG}_bench_bf16x3.json
+python bench.py --steps 20 --warmup 5 --precision bf16 --no-cpu-baseline > $O/${TAG}_bench_bf16.json 2> $O/${TAG}_bench_bf16.err
+cat $O/${TAG}_bench_bf16.json
+python bench.py --steps 10 --warmup 3 --precision fp32 --no-cpu-baseline > $O/${TAG}_bench_fp32.json 2> $O/${TAG}_bench_fp32.err
+cat $O/${TAG}_bench_fp32.json
+python tools/profile_forward.py bf16x3 > $O/${TAG}_entrypoints_bf16x3.txt 2>&1
+python tools/profile_forward.py bf16 > $O/${TAG}_entrypoints_bf16.txt 2>&1
+head -40 $O/${TAG}_entrypoints_bf16x3.txt
+python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${TAG}_plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/${TAG}_launches.csv \
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu.log 2>&1
+echo "ncu exit $?"
