@@ -1,0 +1,52 @@
+"""The C-ABI library loads on a GPU-less host and exports every entry point include/ccn_b200.h declares
+(no compute calls here).  Also: the product package never imports the oracle."""
+import os
+import re
+import subprocess
+
+import pytest
+
+from curvecloudnet_b200 import native
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(native.LIB_PATH):
+        import __graft_entry__ as g
+        g.build()
+    return native.load()
+
+
+def test_every_declared_symbol_is_exported(lib):
+    assert len(native.SIGNATURES) >= 30
+    for name in native.SIGNATURES:
+        assert hasattr(lib, name), name
+    assert lib.ccn_version() >= 1
+    assert native.grid_num_cells(1000) == 2048
+    assert native.kernel_launches() == 0 or native.kernel_launches() > 0
+
+
+def test_library_has_sm100a_code_only(lib):
+    out = subprocess.run(["cuobjdump", "--list-elf", native.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = set(re.findall(r"sm_\d+a?", out.stdout))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_cpu_tensors_are_rejected_not_emulated(lib):
+    import torch
+    with pytest.raises(native.CcnError):
+        native.call("ccn_gather_i64", torch.zeros(4, dtype=torch.int64), torch.zeros(4, dtype=torch.int64), 4,
+                    torch.zeros(4, dtype=torch.int64))
+
+
+def test_product_package_never_imports_oracle():
+    pkg = os.path.join(ROOT, "curvecloudnet_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), os.path.join(dirpath, f)
