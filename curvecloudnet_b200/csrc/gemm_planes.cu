@@ -1,0 +1,372 @@
+// Shared-MLP Linear layer on tcgen05 with BOTH operands delivered by TMA (sm_100a only).
+//   Y[M,N] = act(A[M,K] W[N,K]^T + bias)
+// (replaces torch_geometric.nn.MLP -> cuBLAS SGEMM + BatchNorm + activation
+//  kernels, reference src/models/base.py:32, src/models/modules/mlp.py:16-22.)
+//
+// Activation format between layers: "split-bf16 planes" - an (M, K) activation is stored as bf16 plane(s)
+// (planes, M, kpad), plane 0 = bf16(x), plane 1 = bf16(x - plane 0) (x3 mode only), kpad % 8 == 0 and pad
+// columns zero.  Both planes together cost the 4 bytes/element of fp32, but they are TMA-loadable straight
+// into the SWIZZLE_128B K-major UMMA layout: no conversion warps, no register staging, the load pipeline is
+// as deep as shared memory allows.  Producers (this kernel's epilogue, ccn_pack_planes, the edge-layer
+// kernels) write planes; the last layer of a chain writes fp32.
+//
+// One persistent CTA per SM, 192 threads:
+//   warp 0   lane 0: TMA producer.  Weights (bf16 hi [+ lo]) are loaded ONCE per CTA when the CTA's N-slice of W
+//            fits in shared memory next to a >= 3-stage ring ("resident": every big-M layer of the path), else
+//            they stream through the ring with A.  A tiles: 128 rows x 64 bf16 per plane per stage.
+//   warp 1   lane 0: tcgen05.mma kind::f16 issuer, fp32 accumulators in TMEM, DOUBLE-BUFFERED (2 x BN columns)
+//            so the epilogue of tile t overlaps the MMAs of tile t+1.  x3 mode: A_hi W_hi + A_lo W_hi + A_hi W_lo.
+//   warps 2-5 epilogue: tcgen05.ld (32 lanes x 32 columns), bias + activation, then fp32 rows and/or bf16 planes.
+// Tile order: tile t -> (m = t / tiles_n, n = t % tiles_n); the grid is a multiple of tiles_n in resident mode, so
+// a CTA keeps one N-slice and the CTAs sharing an A tile run concurrently (second read served by L2).
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace {
+
+using namespace ccn_tc;
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;
+constexpr int kATile = kBM * kBK * 2;     // 16 KB per plane per stage
+constexpr int kThreads = 192;
+constexpr int kMaxStages = 8;
+constexpr int kSmemLimit = 227 * 1024;
+
+struct PlanesParams {
+    const float* bias;
+    float* Y;               // fp32 output or null
+    int64_t ldy;
+    __nv_bfloat16* Yp;      // planes output or null
+    int64_t yp_ld;          // row stride (elements) of an output plane
+    int64_t yp_plane;       // plane stride (elements)
+    int yp_cols;            // columns to write per output plane row (N rounded up to 8)
+    int M, N, K;
+    int BN, tiles_m, tiles_n;
+    int stages, resident;
+    int act;
+    float slope;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
+    const __grid_constant__ CUtensorMap a_hi, const __grid_constant__ CUtensorMap a_lo,
+    const __grid_constant__ CUtensorMap w_hi, const __grid_constant__ CUtensorMap w_lo, const PlanesParams p) {
+    constexpr int P = MODE == 3 ? 2 : 1;
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 5];   // full[S], empty[S], wfull, tfull[2], tempty[2]
+    __shared__ uint32_t tmem_base_slot;
+    __shared__ float bias_s[256];                                // bias of the current N-slice (epilogue warps)
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int BN = p.BN, stages = p.stages;
+    const int nk = (p.K + kBK - 1) / kBK;
+    const int wtile = BN * kBK * 2;                      // bytes of one W tile (one plane, one K chunk)
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t w_res = smem0;                        // resident weights: [nk][P][BN x 64]
+    const uint32_t ring0 = smem0 + (p.resident ? (uint32_t)(nk * P * wtile) : 0u);
+    const int stage_bytes = P * kATile + (p.resident ? 0 : P * wtile);
+    const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[kMaxStages]);
+    const uint32_t wfull = smem_u32(&bars[2 * kMaxStages]);
+    const uint32_t tfull0 = smem_u32(&bars[2 * kMaxStages + 1]), tempty0 = smem_u32(&bars[2 * kMaxStages + 3]);
+    uint32_t tmem_cols = 32;
+    while ((int)tmem_cols < 2 * BN) tmem_cols <<= 1;
+
+    const int total_tiles = p.tiles_m * p.tiles_n;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        mbar_init(wfull, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull0 + 8 * b, 1);
+            mbar_init(tempty0 + 8 * b, 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(smem_u32(&tmem_base_slot), tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            if (p.resident) {
+                const int n0 = (blockIdx.x % p.tiles_n) * BN;
+                mbar_arrive_expect_tx(wfull, (uint32_t)(nk * P * wtile));
+                for (int kc = 0; kc < nk; ++kc) {
+                    tma_load_2d(w_res + (kc * P) * wtile, &w_hi, kc * kBK, n0, wfull);
+                    if (P == 2) tma_load_2d(w_res + (kc * P + 1) * wtile, &w_lo, kc * kBK, n0, wfull);
+                }
+            }
+            uint32_t cnt = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                const int m0 = (t / p.tiles_n) * kBM, n0 = (t % p.tiles_n) * BN;
+                for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                    const int s = cnt % stages;
+                    mbar_wait(empty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
+                    const uint32_t dst = ring0 + s * stage_bytes;
+                    mbar_arrive_expect_tx(full0 + 8 * s, (uint32_t)stage_bytes);
+                    tma_load_2d(dst, &a_hi, kc * kBK, m0, full0 + 8 * s);
+                    if (P == 2) tma_load_2d(dst + kATile, &a_lo, kc * kBK, m0, full0 + 8 * s);
+                    if (!p.resident) {
+                        tma_load_2d(dst + P * kATile, &w_hi, kc * kBK, n0, full0 + 8 * s);
+                        if (P == 2) tma_load_2d(dst + P * kATile + wtile, &w_lo, kc * kBK, n0, full0 + 8 * s);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            if (p.resident) {
+                mbar_wait(wfull, 0);
+                tc_fence_after();
+            }
+            uint32_t cnt = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+                const int n0 = (t % p.tiles_n) * BN;
+                const int mma_n = min(BN, ((p.N - n0) + 15) & ~15);
+                // instruction descriptor: D=f32, A=B=bf16, K-major both, N>>3 at bit 17, M>>4 at bit 24
+                const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(mma_n >> 3) << 17) |
+                                       ((uint32_t)(kBM >> 4) << 24);
+                const int buf = it & 1;
+                mbar_wait(tempty0 + 8 * buf, ((it >> 1) & 1) ^ 1);     // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t acc = tmem_base + (uint32_t)(buf * BN);
+                for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                    const int s = cnt % stages;
+                    mbar_wait(full0 + 8 * s, (cnt / stages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_hi_s = ring0 + s * stage_bytes;
+                    const uint32_t a_lo_s = a_hi_s + kATile;
+                    const uint32_t w_hi_s = p.resident ? w_res + (kc * P) * wtile : a_hi_s + P * kATile;
+                    const uint32_t w_lo_s = w_hi_s + wtile;
+#pragma unroll
+                    for (int k = 0; k < kBK / 16; ++k) {
+                        const uint32_t ko = k * 32;     // 16 bf16 = 32 bytes inside the 128-byte swizzle row
+                        umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), umma_desc_sw128(w_hi_s + ko), idesc, (kc | k) ? 1u : 0u);
+                        if (P == 2) {
+                            umma_bf16(acc, umma_desc_sw128(a_lo_s + ko), umma_desc_sw128(w_hi_s + ko), idesc, 1u);
+                            umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), umma_desc_sw128(w_lo_s + ko), idesc, 1u);
+                        }
+                    }
+                    umma_commit(empty0 + 8 * s);        // stage reusable once these MMAs have read it
+                }
+                umma_commit(tfull0 + 8 * buf);          // accumulator of this tile complete
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue (warps 2..5)
+        const int q = warp & 3;                         // TMEM lane quarter this warp may access
+        const bool vecy = p.Y && ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0);
+        int it = 0, bias_n0 = -1;
+        const float* bs = bias_s;
+        const int et = threadIdx.x - 64;                // 0..127 over the four epilogue warps
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            const int m0 = (t / p.tiles_n) * kBM, n0 = (t % p.tiles_n) * BN;
+            const int mma_n = min(BN, ((p.N - n0) + 15) & ~15);
+            const int buf = it & 1;
+            if (n0 != bias_n0) {                        // once per CTA in resident mode
+                asm volatile("bar.sync 1, 128;" ::: "memory");      // everyone is done with the previous slice
+                for (int j = et; j < BN; j += 128) bias_s[j] = (p.bias && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                bias_n0 = n0;
+            }
+            mbar_wait(tfull0 + 8 * buf, (it >> 1) & 1);
+            tc_fence_after();
+            const int row = m0 + q * 32 + lane;
+            const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
+            for (int c0 = 0; c0 < mma_n; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tbase + (uint32_t)c0, v);
+                float y[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    float o = __uint_as_float(v[j]) + bs[c0 + j];
+                    if (p.act == CCN_ACT_RELU) o = fmaxf(o, 0.f);
+                    else if (p.act == CCN_ACT_LEAKY) o = o > 0.f ? o : o * p.slope;
+                    y[j] = o;
+                }
+                if (row < p.M) {
+                    if (p.Y) {
+                        float* yrow = p.Y + (int64_t)row * p.ldy + n0 + c0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            const int n = n0 + c0 + j;
+                            if (vecy && n + 3 < p.N) {
+                                *reinterpret_cast<float4*>(yrow + j) = make_float4(y[j], y[j + 1], y[j + 2], y[j + 3]);
+                            } else {
+#pragma unroll
+                                for (int e = 0; e < 4; ++e)
+                                    if (n + e < p.N) yrow[j + e] = y[j + e];
+                            }
+                        }
+                    }
+                    if (p.Yp) {
+                        __nv_bfloat16* hrow = p.Yp + (int64_t)row * p.yp_ld + n0 + c0;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            if (n0 + c0 + j >= p.yp_cols) break;       // yp_cols % 8 == 0: whole groups only
+                            __nv_bfloat162 h[4], l[4];
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                h[e] = __floats2bfloat162_rn(y[j + 2 * e], y[j + 2 * e + 1]);
+                                if (P == 2) {
+                                    const float2 f = __bfloat1622float2(h[e]);
+                                    l[e] = __floats2bfloat162_rn(y[j + 2 * e] - f.x, y[j + 2 * e + 1] - f.y);
+                                }
+                            }
+                            *reinterpret_cast<uint4*>(hrow + j) = *reinterpret_cast<uint4*>(h);
+                            if (P == 2) *reinterpret_cast<uint4*>(hrow + p.yp_plane + j) = *reinterpret_cast<uint4*>(l);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, tmem_cols);
+    }
+}
+
+// Up to four fp32 column blocks (each optionally row-gathered through an int64 index) -> bf16 planes.
+// One thread per (row, group of 8 output columns); pad columns up to kpad are written as zeros.
+struct PackSrc {
+    const float* p[4];
+    const int64_t* idx[4];
+    int64_t ld[4];
+    int c[4];
+};
+
+__global__ void pack_planes_kernel(const PackSrc s, int64_t n, int ctot, __nv_bfloat16* __restrict__ planes,
+                                   int64_t kpad, int64_t plane_stride, int n_planes) {
+    const int groups = (int)(kpad >> 3);
+    const int64_t total = n * groups;
+    const int e0 = s.c[0], e1 = e0 + s.c[1], e2 = e1 + s.c[2];
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / groups;
+        const int g = (int)(t - i * groups);
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int c = g * 8 + e;
+            float x = 0.f;
+            if (c < ctot) {
+                const int k = c < e0 ? 0 : c < e1 ? 1 : c < e2 ? 2 : 3;
+                const int cc = c - (k == 0 ? 0 : k == 1 ? e0 : k == 2 ? e1 : e2);
+                const int64_t r = s.idx[k] ? s.idx[k][i] : i;
+                x = s.p[k][r * s.ld[k] + cc];
+            }
+            v[e] = x;
+        }
+        __nv_bfloat162 h[4], l[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+            const float2 f = __bfloat1622float2(h[e]);
+            l[e] = __floats2bfloat162_rn(v[2 * e] - f.x, v[2 * e + 1] - f.y);
+        }
+        __nv_bfloat16* o = planes + i * kpad + g * 8;
+        *reinterpret_cast<uint4*>(o) = *reinterpret_cast<uint4*>(h);
+        if (n_planes == 2) *reinterpret_cast<uint4*>(o + plane_stride) = *reinterpret_cast<uint4*>(l);
+    }
+}
+
+}  // namespace
+
+extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const int64_t* i0, const float* s1, int64_t ld1,
+                               int32_t c1, const int64_t* i1, const float* s2, int64_t ld2, int32_t c2,
+                               const int64_t* i2, const float* s3, int64_t ld3, int32_t c3, const int64_t* i3, int64_t n,
+                               void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    const int ctot = c0 + c1 + c2 + c3;
+    CCN_REQUIRE(n >= 0 && planes && c0 > 0 && s0 && c1 >= 0 && c2 >= 0 && c3 >= 0 && (c1 == 0 || s1) && (c2 == 0 || s2) &&
+                (c3 == 0 || s3));
+    CCN_REQUIRE(kpad >= ctot && (kpad & 7) == 0 && (n_planes == 1 || n_planes == 2) &&
+                (reinterpret_cast<uintptr_t>(planes) & 15) == 0 && (n_planes == 1 || (plane_stride & 7) == 0));
+    if (n == 0) return CCN_OK;
+    PackSrc s;
+    s.p[0] = s0; s.p[1] = s1; s.p[2] = s2; s.p[3] = s3;
+    s.idx[0] = i0; s.idx[1] = i1; s.idx[2] = i2; s.idx[3] = i3;
+    s.ld[0] = ld0; s.ld[1] = ld1; s.ld[2] = ld2; s.ld[3] = ld3;
+    s.c[0] = c0; s.c[1] = c1; s.c[2] = c2; s.c[3] = c3;
+    pack_planes_kernel<<<ccn_grid(n * (kpad >> 3), 256, 148LL * 32), 256, 0, (cudaStream_t)stream>>>(
+        s, n, ctot, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_linear_planes(const void* a_hi_tmap_host, const void* a_lo_tmap_host, const void* w_hi_tmap_host,
+                                 const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes,
+                                 int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N, int32_t K, int32_t box_n,
+                                 int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
+    CCN_REQUIRE(a_hi_tmap_host && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0 && K > 0);
+    CCN_REQUIRE((mode == 1 || (mode == 3 && a_lo_tmap_host && w_lo_tmap_host)) && act >= 0 && act <= 2);
+    CCN_REQUIRE(box_n == 32 || box_n == 64 || box_n == 128 || box_n == 256);
+    CCN_REQUIRE(!Y || ldy >= N);
+    const int yp_cols = (N + 7) & ~7;
+    CCN_REQUIRE(!y_planes || (yp_ld >= yp_cols && (yp_ld & 7) == 0 && (reinterpret_cast<uintptr_t>(y_planes) & 15) == 0 &&
+                              (mode == 1 || (yp_plane_stride & 7) == 0)));
+    if (M == 0) return CCN_OK;
+    const int P = mode == 3 ? 2 : 1;
+    PlanesParams p;
+    p.bias = bias; p.Y = Y; p.ldy = ldy; p.Yp = (__nv_bfloat16*)y_planes; p.yp_ld = yp_ld; p.yp_plane = yp_plane_stride;
+    p.yp_cols = yp_cols; p.M = (int)M; p.N = N; p.K = K; p.BN = box_n;
+    p.tiles_m = (int)((M + kBM - 1) / kBM);
+    p.tiles_n = (N + box_n - 1) / box_n;
+    p.act = act; p.slope = slope;
+    const int nk = (K + kBK - 1) / kBK;
+    const int wtile = box_n * kBK * 2;
+    const int64_t total = (int64_t)p.tiles_m * p.tiles_n;
+    const int budget = kSmemLimit - 2560;        // dynamic limit (kSmemLimit - 1536; 1.2 KB is static) minus the 1024-byte alignment slack
+    // resident weights when the CTA's N-slice fits next to a >= 3-stage A ring and a CTA sees more than one tile
+    const int64_t wres = (int64_t)nk * P * wtile;
+    int grid = (int)(total < 148 ? total : 148);
+    p.resident = 0;
+    if (total > 148 && p.tiles_n <= 148 && wres + 3 * P * kATile <= budget) {
+        p.resident = 1;
+        grid = (148 / p.tiles_n) * p.tiles_n;
+    }
+    const int stage_bytes = P * kATile + (p.resident ? 0 : P * wtile);
+    int stages = (int)((budget - (p.resident ? wres : 0)) / stage_bytes);
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages < 2) return CCN_EUNSUPPORTED;
+    p.stages = stages;
+    const int smem = (int)((p.resident ? wres : 0) + (int64_t)stages * stage_bytes + 1024);
+    const CUtensorMap* ahi = (const CUtensorMap*)a_hi_tmap_host;
+    const CUtensorMap* alo = mode == 3 ? (const CUtensorMap*)a_lo_tmap_host : ahi;
+    const CUtensorMap* whi = (const CUtensorMap*)w_hi_tmap_host;
+    const CUtensorMap* wlo = mode == 3 ? (const CUtensorMap*)w_lo_tmap_host : whi;
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e;
+    if (mode == 3) {
+        static bool attr3 = false;
+        if (!attr3) {
+            e = cudaFuncSetAttribute(linear_planes_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536);
+            if (e != cudaSuccess) return (int)e;
+            attr3 = true;
+        }
+        linear_planes_kernel<3><<<grid, kThreads, smem, s>>>(*ahi, *alo, *whi, *wlo, p);
+    } else {
+        static bool attr1 = false;
+        if (!attr1) {
+            e = cudaFuncSetAttribute(linear_planes_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536);
+            if (e != cudaSuccess) return (int)e;
+            attr1 = true;
+        }
+        linear_planes_kernel<1><<<grid, kThreads, smem, s>>>(*ahi, *alo, *whi, *wlo, p);
+    }
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}

@@ -75,10 +75,8 @@ _prof_shapes = []          # (M, N, K) of every timed Linear call (tools/profile
 _prof_events = []          # (name, start event, end event, algorithmic work of the call)
 
 # algorithmic work of one call: FLOPs for the Linear kernels (2 M N K)
-_WORK = {
-    "ccn_linear_f32": lambda a: 2.0 * a[7] * a[8] * a[9],
-    "ccn_linear_tc": lambda a: 2.0 * a[7] * a[8] * a[9],
-}
+_MNK = {"ccn_linear_f32": (7, 8, 9), "ccn_linear_tc": (7, 8, 9), "ccn_linear_planes": (10, 11, 12)}
+_WORK = {name: (lambda a, ix=ix: 2.0 * a[ix[0]] * a[ix[1]] * a[ix[2]]) for name, ix in _MNK.items()}
 
 
 def profile_begin(names):
@@ -134,7 +132,8 @@ def call(name, *args):
         e1.record()
         _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
         if name in _WORK:
-            _prof_shapes.append((args[7], args[8], args[9]))
+            ix = _MNK[name]
+            _prof_shapes.append((args[ix[0]], args[ix[1]], args[ix[2]]))
     if rc != 0:
         if rc < 0:
             raise CcnError("%s: invalid argument (code %d)" % (name, rc))

@@ -119,6 +119,22 @@ def get_precision() -> str:
     return _PRECISION["mode"]
 
 
+def n_planes() -> int:
+    """Activation planes of the current precision mode (0 = fp32 mode: no planes)."""
+    return {"fp32": 0, "bf16x3": 2, "bf16": 1}[_PRECISION["mode"]]
+
+
+def cat_features(parts, idxs=None):
+    """torch.cat(parts, dim=1) (block k row-gathered by idxs[k]) as the input of an MLP: activation planes on the
+    tensor-core modes (one pack kernel, no fp32 concat buffer), an fp32 matrix in fp32 mode."""
+    npl = n_planes()
+    if npl:
+        return ops.pack_planes(parts, npl, idxs)
+    if idxs is not None:
+        parts = [p if ix is None else ops.gather_rows(p, ix) for p, ix in zip(parts, idxs)]
+    return ops.concat_cols(list(parts)) if len(parts) > 1 else parts[0]
+
+
 class PreparedLinear:
     """One Linear layer ready for the kernels: fp32 (W, b) with BatchNorm folded, activation, and (lazily)
     the bf16 hi/lo copies + TMA descriptors of the tensor-core path.  Weight preparation only."""
@@ -141,11 +157,15 @@ class PreparedLinear:
             self._tc = ops.prepare_tc_weight(self.w)
         return self._tc
 
-    def __call__(self, x):
+    def __call__(self, x, out: str = "f32"):
+        """x: fp32 (M, K) tensor or ops.Planes.  out: "f32" | "planes" | "both" (planes only on the tensor-core modes)."""
         mode = _PRECISION["mode"]
         if mode == "fp32":
+            assert out == "f32" and torch.is_tensor(x)
             return ops.linear(x, self.w, self.b, self.act, self.slope)
-        return ops.linear_tc(x, self.tc(), self.b, self.act, self.slope, 3 if mode == "bf16x3" else 1)
+        if torch.is_tensor(x):
+            x = ops.pack_planes([x], n_planes())
+        return ops.linear_planes(x, self.tc(), self.b, self.act, self.slope, out)
 
 
 class MLP(torch.nn.Module):
@@ -231,13 +251,18 @@ class MLP(torch.nn.Module):
             self._folded, self._folded_key = out, key
         return self._folded
 
-    def forward(self, x, *args, **kwargs):
-        for lin in self.layers():
-            x = lin(x)
-        return x
+    def forward(self, x, *args, out: str = "f32", **kwargs):
+        return self.forward_from(x, 0, out)
 
-    def forward_from(self, x, first: int):
-        """Run layers first.. (the first layer(s) having been applied in a fused/decomposed form)."""
-        for lin in self.layers()[first:]:
-            x = lin(x)
-        return x
+    def forward_from(self, x, first: int, out: str = "f32"):
+        """Run layers first.. (the first layer(s) having been applied in a fused/decomposed form).  On the tensor-core
+        modes the activations between layers are bf16 planes; the last layer writes `out`."""
+        layers = self.layers()[first:]
+        if not layers:
+            if out != "f32" or not torch.is_tensor(x):
+                raise NotImplementedError("one-layer edge MLP on the planes path (no shipped config has one)")
+            return x
+        inner = "planes" if _PRECISION["mode"] != "fp32" else "f32"
+        for lin in layers[:-1]:
+            x = lin(x, inner)
+        return layers[-1](x, out)

@@ -483,6 +483,22 @@ class TcWeight:
             self._maps[box_n] = hit
         return hit
 
+    def pick_box_planes(self, m: int, n_planes: int) -> int:
+        """N-tile width for ccn_linear_planes.  Big M (>= one m-tile per SM): the widest tile whose weight slice stays
+        resident in shared memory next to a 3-stage A ring; otherwise the widest tile that still gives >= 148 tiles."""
+        cand = [b for b in (256, 128, 64, 32) if b == 32 or b // 2 < self.n]
+        tiles_m = (m + 127) // 128
+        nk = self.kpad // 64
+        if tiles_m >= 148:
+            for b in cand:
+                if nk * n_planes * b * 128 + 3 * n_planes * 16384 <= SMEM_BUDGET:
+                    return b
+            return cand[-1]
+        for b in cand:
+            if tiles_m * ((self.n + b - 1) // b) >= 148:
+                return b
+        return 32
+
     def pick_box(self, m: int) -> int:
         """Widest N tile that still yields >= one wave of CTAs (148 SMs); skinny problems get narrow tiles."""
         box = self.max_box
@@ -490,6 +506,90 @@ class TcWeight:
         while box > 32 and mt * ((self.n + box - 1) // box) < 148:
             box //= 2
         return box
+
+
+SMEM_BUDGET = 227 * 1024 - 2560
+
+
+def _tensor_map(base_ptr: int, rows: int, kpad: int, box_rows: int):
+    """Host-side CUtensorMap of a bf16 (rows, kpad) row-major matrix, box = 64 x box_rows, SWIZZLE_128B."""
+    import ctypes
+    b = ctypes.create_string_buffer(128 + 64)
+    p = (ctypes.addressof(b) + 63) & ~63
+    rc = native.load().ccn_weight_tensor_map(p, base_ptr, rows, kpad, box_rows)
+    if rc:
+        raise native.CcnError("ccn_weight_tensor_map failed (code %d)" % rc)
+    return p, b
+
+
+class Planes:
+    """Split-bf16 activation planes (n_planes, M, kpad): plane 0 = bf16(x), plane 1 = bf16(x - plane 0);
+    the inter-layer activation format of the tensor-core MLP path (TMA-loadable, csrc/gemm_planes.cu)."""
+
+    def __init__(self, buf: torch.Tensor, m: int, k: int):
+        self.buf, self.m, self.k = buf, m, k
+        self.n_planes, self.kpad = buf.shape[0], buf.shape[2]
+        self._maps = None
+
+    @property
+    def shape(self):
+        return (self.m, self.k)
+
+    @property
+    def plane_stride(self):
+        return self.buf.stride(0)
+
+    def maps(self):
+        if self._maps is None:
+            hi = _tensor_map(self.buf[0].data_ptr(), max(self.m, 1), self.kpad, 128)
+            lo = _tensor_map(self.buf[1].data_ptr(), max(self.m, 1), self.kpad, 128) if self.n_planes == 2 else hi
+            self._maps = (hi[0], lo[0], (hi, lo))
+        return self._maps
+
+    def to_f32(self) -> torch.Tensor:
+        """Debug/test helper (torch arithmetic, not on the product path)."""
+        x = self.buf[0, :self.m, :self.k].float()
+        return x + self.buf[1, :self.m, :self.k].float() if self.n_planes == 2 else x
+
+
+def alloc_planes(m: int, k: int, n_planes: int, like: torch.Tensor) -> Planes:
+    kpad = (k + 7) // 8 * 8
+    return Planes(torch.empty((n_planes, max(m, 1), kpad), dtype=torch.bfloat16, device=like.device), m, k)
+
+
+def pack_planes(parts, n_planes: int, idxs=None) -> Planes:
+    """torch.cat([p[idx] for p, idx in ...], dim=1) written directly as activation planes (up to four blocks)."""
+    assert 1 <= len(parts) <= 4
+    idxs = list(idxs) if idxs is not None else [None] * len(parts)
+    n = parts[0].shape[0] if idxs[0] is None else idxs[0].shape[0]
+    args, ctot = [], 0
+    for k in range(4):
+        if k < len(parts):
+            t, ld = _rows(parts[k])
+            ix = _i64(idxs[k]) if idxs[k] is not None else 0
+            args += [t, ld, t.shape[1], ix]
+            ctot += t.shape[1]
+        else:
+            args += [0, 0, 0, 0]
+    out = alloc_planes(n, ctot, n_planes, parts[0])
+    call("ccn_pack_planes", *args, n, out.buf, out.kpad, out.plane_stride, n_planes)
+    return out
+
+
+def linear_planes(A: Planes, tw: "TcWeight", bias: Optional[torch.Tensor], act: int, slope: float, out: str = "f32"):
+    """Y = act(A W^T + bias) with both operands by TMA.  out: "f32" -> tensor, "planes" -> Planes, "both" -> (tensor, Planes)."""
+    M, K = A.shape
+    assert K == tw.k, (A.shape, tw.k)
+    mode = 3 if A.n_planes == 2 else 1
+    Y = _empty((M, tw.n), torch.float32, A.buf) if out in ("f32", "both") else None
+    Yp = alloc_planes(M, tw.n, A.n_planes, A.buf) if out in ("planes", "both") else None
+    box = tw.pick_box_planes(M, A.n_planes)
+    w_hi, w_lo, _ = tw.maps(box)
+    a_hi, a_lo, _ = A.maps()
+    call("ccn_linear_planes", a_hi, a_lo, w_hi, w_lo, bias if bias is not None else 0, Y if Y is not None else 0, tw.n,
+         Yp.buf if Yp is not None else 0, Yp.kpad if Yp is not None else 0, Yp.plane_stride if Yp is not None else 0,
+         M, tw.n, K, box, mode, act, float(slope))
+    return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)
 
 
 def prepare_tc_weight(w: torch.Tensor) -> TcWeight:

@@ -1,0 +1,74 @@
+"""GPU parity of the TMA/tcgen05 Linear kernel (ccn_linear_planes) and the planes pack kernel against float64
+torch arithmetic.  Tolerances: split-bf16 x3 -> 1e-4 budget (we require 3e-5), bf16 -> 2e-2 (BASELINE.json)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [  # (M, N, K): resident big-M, streaming, ragged N/K, tiny M, one tile per CTA, wide K
+    (40000, 64, 64), (30000, 256, 256), (20011, 128, 67), (20000, 192, 128), (5695, 256, 131), (1933, 512, 259),
+    (174, 2048, 1027), (580, 1024, 2051), (33, 17, 64), (1, 64, 35), (129, 40, 8), (3654, 1024, 1024),
+]
+
+
+def _ref(x, w, b, act):
+    y = x.double() @ w.double().t() + (b.double() if b is not None else 0)
+    if act == 1:
+        y = y.clamp(min=0)
+    elif act == 2:
+        y = torch.where(y > 0, y, y * 0.01)
+    return y
+
+
+@pytest.mark.parametrize("mode", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("shape", SHAPES)
+def test_linear_planes_matches_float64(shape, mode):
+    from curvecloudnet_b200 import nn as cnn, ops
+    M, N, K = shape
+    g = torch.Generator().manual_seed(M + N + K)
+    x = torch.randn(M, K, generator=g).cuda()
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).cuda()
+    b = torch.randn(N, generator=g).cuda()
+    prev = cnn.get_precision()
+    cnn.set_precision(mode)
+    try:
+        npl = cnn.n_planes()
+        tol = 3e-5 if mode == "bf16x3" else 2e-2
+        lin = cnn.PreparedLinear(w, b, act=2, slope=0.01)
+        xp = ops.pack_planes([x], npl)
+        assert xp.buf.shape == (npl, M, (K + 7) // 8 * 8)
+        assert float(xp.buf[:, :, K:].float().abs().max() if xp.kpad > K else 0.0) == 0.0
+        back = xp.to_f32()
+        assert float((back - x).abs().max() / x.abs().max()) <= (2e-5 if npl == 2 else 8e-3)
+        want = _ref(x, w, b, 2)
+        scale = float(want.abs().max())
+        y, yp = lin(xp, "both")
+        torch.cuda.synchronize()
+        assert float((y.double() - want).abs().max()) / scale <= tol
+        assert float((yp.to_f32().double() - want).abs().max()) / scale <= tol * 1.5 + (8e-3 if npl == 1 else 0)
+        if yp.kpad > N:
+            assert float(yp.buf[:, :, N:].float().abs().max()) == 0.0
+        y2 = lin(x)                                   # fp32 in -> pack -> GEMM -> fp32 out
+        assert torch.equal(y2, y)
+        lin0 = cnn.PreparedLinear(w, None, act=0)
+        y3 = lin0(xp)
+        assert float((y3.double() - _ref(x, w, None, 0)).abs().max()) / scale <= tol
+    finally:
+        cnn.set_precision(prev)
+
+
+def test_pack_concat_and_gather():
+    from curvecloudnet_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    a = torch.randn(1000, 37, generator=g).cuda()
+    b = torch.randn(1000, 3, generator=g).cuda()
+    c = torch.randn(50, 64, generator=g).cuda()
+    ic = torch.randint(0, 50, (1000,), generator=g).cuda()
+    wide = torch.randn(1000, 80, generator=g).cuda()
+    pl = ops.pack_planes([a, wide[:, 5:17], b, c], 2, [None, None, None, ic])
+    want = torch.cat([a, wide[:, 5:17], b, c[ic]], dim=1)
+    assert pl.shape == (1000, 37 + 12 + 3 + 64)
+    assert float((pl.to_f32() - want).abs().max()) <= 2e-5 * float(want.abs().max())
+    sel = torch.randint(0, 1000, (321,), generator=g).cuda()
+    pl = ops.pack_planes([a, b], 1, [sel, sel])
+    assert float((pl.to_f32() - torch.cat([a, b], 1)[sel]).abs().max()) <= 8e-3 * float(a.abs().max())
