@@ -4,6 +4,8 @@
 // segment softmax, frnn_gather (third_party/FRNN/frnn/frnn.py:351-397) and the dense masked max of
 // StaticEdgeConv.forward_fast (src/models/modules/dgcnn.py:158-207).  All sums run in edge order
 // (deterministic), one thread per (segment, channel) with channels on the fast axis.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace {
@@ -182,6 +184,108 @@ __global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, co
     }
 }
 
+
+// ---- planes-output variants of the per-edge first layers (the consumer is always the next Linear of the MLP):
+// one thread per (row, 8 channels); requires c % 8 == 0 and 16-byte aligned fp32 rows.
+struct F8 { float v[8]; };
+__device__ __forceinline__ F8 ld8(const float* p) {
+    F8 r;
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    return r;
+}
+__device__ __forceinline__ void st_planes8(const F8& y, __nv_bfloat16* o, int64_t plane_stride, int n_planes) {
+    __nv_bfloat162 h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        h[e] = __floats2bfloat162_rn(y.v[2 * e], y.v[2 * e + 1]);
+        const float2 f = __bfloat1622float2(h[e]);
+        l[e] = __floats2bfloat162_rn(y.v[2 * e] - f.x, y.v[2 * e + 1] - f.y);
+    }
+    *reinterpret_cast<uint4*>(o) = *reinterpret_cast<uint4*>(h);
+    if (n_planes == 2) *reinterpret_cast<uint4*>(o + plane_stride) = *reinterpret_cast<uint4*>(l);
+}
+
+__global__ void sgcnn_layer1_planes_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ idx,
+                                           int64_t n, int K, int c, int act, float slope,
+                                           __nv_bfloat16* __restrict__ planes, int64_t kpad, int64_t plane_stride,
+                                           int n_planes) {
+    const int G = K + 1, cg = c >> 3;
+    const int64_t total = n * (int64_t)G * cg;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = t / cg;
+        const int k = (int)(t - row * cg) << 3;
+        const int64_t i = row / G;
+        const int g = (int)(row - i * G);
+        const int j = g == 0 ? (int)i : idx[i * K + g - 1];
+        F8 y = ld8(PQ + i * ldpq + c + k);
+        if (j >= 0) {
+            const F8 pj = ld8(PQ + (int64_t)j * ldpq + k);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) y.v[e] += pj.v[e];
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y.v[e] = apply_act(y.v[e], act, slope);
+        st_planes8(y, planes + row * kpad + k, plane_stride, n_planes);
+    }
+}
+
+__global__ void edge_pair_layer1_planes_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ erow,
+                                               const int32_t* __restrict__ ecol, int64_t E, int c, int act, float slope,
+                                               __nv_bfloat16* __restrict__ planes, int64_t kpad, int64_t plane_stride,
+                                               int n_planes) {
+    const int cg = c >> 3;
+    const int64_t total = E * (int64_t)cg;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = t / cg;
+        const int k = (int)(t - e * cg) << 3;
+        F8 y = ld8(PQ + (int64_t)ecol[e] * ldpq + k);
+        const F8 q = ld8(PQ + (int64_t)erow[e] * ldpq + c + k);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) y.v[u] = apply_act(y.v[u] + q.v[u], act, slope);
+        st_planes8(y, planes + e * kpad + k, plane_stride, n_planes);
+    }
+}
+
+__global__ void edge_layer1_planes_kernel(const float* __restrict__ H, int64_t ldh, const float* __restrict__ wp,
+                                          const float* __restrict__ bias, const float* __restrict__ pos_src,
+                                          const float* __restrict__ pos_dst, const int32_t* __restrict__ erow,
+                                          const int32_t* __restrict__ ecol, int64_t E, int c, float inv_norm_is_div,
+                                          float radius, int act, float slope, __nv_bfloat16* __restrict__ planes,
+                                          int64_t kpad, int64_t plane_stride, int n_planes) {
+    const int cg = c >> 3;
+    const int64_t total = E * (int64_t)cg;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = t / cg;
+        const int k = (int)(t - e * cg) << 3;
+        const int j = ecol[e], i = erow[e];
+        float rx = __fsub_rn(pos_src[3 * j], pos_dst[3 * i]);
+        float ry = __fsub_rn(pos_src[3 * j + 1], pos_dst[3 * i + 1]);
+        float rz = __fsub_rn(pos_src[3 * j + 2], pos_dst[3 * i + 2]);
+        if (inv_norm_is_div != 0.f) { rx = __fdiv_rn(rx, radius); ry = __fdiv_rn(ry, radius); rz = __fdiv_rn(rz, radius); }
+        F8 y;
+        if (bias) y = ld8(bias + k);
+        else {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) y.v[u] = 0.f;
+        }
+        if (H) {
+            const F8 h = ld8(H + (int64_t)j * ldh + k);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) y.v[u] += h.v[u];
+        }
+        const F8 wx = ld8(wp + k), wy = ld8(wp + c + k), wz = ld8(wp + 2 * c + k);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            float v = fmaf(wx.v[u], rx, y.v[u]);
+            v = fmaf(wy.v[u], ry, v);
+            v = fmaf(wz.v[u], rz, v);
+            y.v[u] = apply_act(v, act, slope);
+        }
+        st_planes8(y, planes + e * kpad + k, plane_stride, n_planes);
+    }
+}
+
 }  // namespace
 
 #define CCN_ELT_GRID(total) ccn_grid((total), 256, 148LL * 32)
@@ -279,6 +383,50 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
     if (n == 0) return CCN_OK;
     interp_blend_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn, c,
                                                                                out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+static inline bool ccn_al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+#define CCN_PLANES_OK(planes, kpad, pstride, npl, c) \
+    ((planes) && ccn_al16(planes) && ((kpad) & 7) == 0 && (kpad) >= (c) && ((c) & 7) == 0 && ((npl) == 1 || ((npl) == 2 && ((pstride) & 7) == 0)))
+
+extern "C" int ccn_sgcnn_layer1_planes(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c,
+                                       int32_t act, float slope, void* planes, int64_t kpad, int64_t plane_stride,
+                                       int32_t n_planes, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && PQ && ldpq >= 2 * c && (K == 0 || idx));
+    CCN_REQUIRE(CCN_PLANES_OK(planes, kpad, plane_stride, n_planes, c) && kpad == c && ccn_al16(PQ) && (ldpq & 3) == 0);
+    if (n == 0) return CCN_OK;
+    sgcnn_layer1_planes_kernel<<<CCN_ELT_GRID(n * (K + 1) * (c >> 3)), 256, 0, (cudaStream_t)stream>>>(
+        PQ, ldpq, idx, n, K, c, act, slope, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_edge_pair_layer1_planes(const float* PQ, int64_t ldpq, const int32_t* erow, const int32_t* ecol,
+                                           int64_t E, int32_t c, int32_t act, float slope, void* planes, int64_t kpad,
+                                           int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    CCN_REQUIRE(E >= 0 && c > 0 && PQ && erow && ecol && ldpq >= 2 * c);
+    CCN_REQUIRE(CCN_PLANES_OK(planes, kpad, plane_stride, n_planes, c) && kpad == c && ccn_al16(PQ) && (ldpq & 3) == 0);
+    if (E == 0) return CCN_OK;
+    edge_pair_layer1_planes_kernel<<<CCN_ELT_GRID(E * (c >> 3)), 256, 0, (cudaStream_t)stream>>>(
+        PQ, ldpq, erow, ecol, E, c, act, slope, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_edge_layer1_planes(const float* H, int64_t ldh, const float* wp, const float* bias,
+                                      const float* pos_src, const float* pos_dst, const int32_t* erow,
+                                      const int32_t* ecol, int64_t E, int32_t c, float normalize_radius, int32_t act,
+                                      float slope, void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes,
+                                      ccn_stream_t stream) {
+    CCN_REQUIRE(E >= 0 && c > 0 && wp && pos_src && pos_dst && erow && ecol);
+    CCN_REQUIRE(CCN_PLANES_OK(planes, kpad, plane_stride, n_planes, c) && kpad == c && ccn_al16(wp) &&
+                (!bias || ccn_al16(bias)) && (!H || (ccn_al16(H) && (ldh & 3) == 0)));
+    if (E == 0) return CCN_OK;
+    edge_layer1_planes_kernel<<<CCN_ELT_GRID(E * (c >> 3)), 256, 0, (cudaStream_t)stream>>>(
+        H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
+        slope, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

@@ -12,7 +12,7 @@ import torch
 
 from . import modules as M
 from . import native, ops
-from .nn import MLP, Draws, ForwardCache, get_precision, set_precision
+from .nn import MLP, Draws, ForwardCache, cat_features, get_precision, set_precision
 
 _DOWN_STEPS = ("sa", "sa-geo", "sa-global", "pt-transition-down")
 
@@ -203,7 +203,7 @@ class ModelBase(torch.nn.Module):
             onehot = torch.zeros((cats.shape[0], 16), dtype=torch.float32, device=feat.device)
             onehot[torch.arange(cats.shape[0], device=feat.device), cats] = 1.0   # input encoding (B x 16)
             cat_feat = self.lin_categorical(onehot)
-            feat = ops.concat_cols([feat, ops.gather_rows(cat_feat, batch0)])
+            feat = cat_features([feat, cat_feat], [None, batch0])
         if isinstance(self.mlp, torch.nn.Identity):
             return feat
         return self.mlp(feat)

@@ -13,13 +13,14 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .nn import DEFAULT_DRAWS, MLP, Draws, PreparedLinear, fold_batchnorm, get_cache
+from .nn import DEFAULT_DRAWS, MLP, Draws, PreparedLinear, cat_features, fold_batchnorm, get_cache, n_planes
 
 
 def _cat_xyz(x, pos, with_xyz):
+    """cat[x, pos] as the input of a Linear (activation planes on the tensor-core modes)."""
     if not with_xyz:
         return x
-    return pos if x is None else ops.concat_cols([x, pos])
+    return pos if x is None else cat_features([x, pos])
 
 
 # ----------------------------------------------------------------------------------------------
@@ -154,12 +155,17 @@ class PointNetConv2(nn.Module):
             self._dec, self._dec_src = (lin_x, l0.w[:, cx:].t().contiguous()), layers
         lin_x, wp = self._dec                                  # x part (C1, cx) and positional part (3, C1)
         H = lin_x(x_src) if lin_x is not None else None
-        msg = ops.edge_layer1(H, wp, l0.b, pos_src, pos_dst, edges, self.normalize_radius, l0.act, l0.slope)
-        msg = self.local_nn.forward_from(msg, 1)
+        npl = n_planes() if len(layers) > 1 else 0
+        msg = ops.edge_layer1(H, wp, l0.b, pos_src, pos_dst, edges, self.normalize_radius, l0.act, l0.slope, npl)
         if self.aggr_type in ("max", "mean"):
+            msg = self.local_nn.forward_from(msg, 1)
             out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, self.aggr_type)
         else:
-            att = self.attend_nn(msg)
+            # the message is needed twice: fp32 for the aggregation, planes as the input of attend_nn
+            both = npl > 0
+            msg = self.local_nn.forward_from(msg, 1, "both" if both else "f32")
+            msg, msg_in = msg if both else (msg, msg)
+            att = self.attend_nn(msg_in)
             out = ops.seg_aggregate(msg, att, edges.row_ptr, edges.nq, self.aggr_type)
         if self.global_nn is not None:
             out = self.global_nn(out)
@@ -242,7 +248,7 @@ class GlobalSAModule(nn.Module):
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
         sptr = get_cache(kwargs).sample_ptr(batch)
-        h = self.nn(ops.concat_cols([x, pos]))
+        h = self.nn(cat_features([x, pos]))
         out = ops.seg_aggregate(h, None, sptr.dev, sptr.n_samples, self.pooling)
         first = torch.tensor(sptr.host[:-1], dtype=torch.int64).to(pos.device)
         _, posf, batchf, curvef = _subset(None, pos, batch, point2curveidx, first)
@@ -256,7 +262,7 @@ def _fp_concat(x, x_skip, pos_skip, with_xyz):
         parts.append(x_skip)
     if with_xyz:
         parts.append(pos_skip[:, :3])
-    return ops.concat_cols(parts) if len(parts) > 1 else x
+    return cat_features(parts) if len(parts) > 1 else x
 
 
 class FPModule(nn.Module):
@@ -291,8 +297,7 @@ class CurveSAModule(nn.Module):
     def forward(self, x, pos, batch, point2curveidx, draws: Draws = DEFAULT_DRAWS, **kwargs):
         cache = get_cache(kwargs)
         topo = cache.topology(batch, point2curveidx)
-        if self.with_xyz:
-            x = pos if x is None else ops.concat_cols([x, pos])
+        x = _cat_xyz(x, pos, self.with_xyz)
         if self.use_curve_fps:
             idx, sptr_q = ops.curve_fps(pos, topo, self.curve_fps_arclen, draws.curve_phase())
         else:
@@ -361,7 +366,7 @@ class SGCNNLayer(nn.Module):
             if self.aggr_type != "max":
                 raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
             nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, cache=cache)
-            h = ops.sgcnn_layer1(PQ, nbr, act0, slope0)
+            h = ops.sgcnn_layer1(PQ, nbr, act0, slope0, n_planes() if self.nn.num_layers > 1 else 0)
             h = self.nn.forward_from(h, 1)
             return ops.group_max_dense(h, nbr), pos, batch, point2curveidx
         if self.use_fast_knn:
@@ -369,12 +374,16 @@ class SGCNNLayer(nn.Module):
         else:
             nbr, _, cnt = ops.knn_exact(pos, batch, pos, sptr, self.k, zero_fill=True, want_d2=False, want_cnt=True)
         edges = ops.dense_to_csr(nbr, cnt)
-        msg = ops.edge_pair_layer1(PQ, edges, act0, slope0)
-        msg = self.nn.forward_from(msg, 1)
+        npl = n_planes() if self.nn.num_layers > 1 else 0
+        msg = ops.edge_pair_layer1(PQ, edges, act0, slope0, npl)
         if self.aggr_type == "max":
+            msg = self.nn.forward_from(msg, 1)
             out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "max")
         elif self.aggr_type == "attend":
-            out = ops.seg_aggregate(msg, self.attend_nn(msg), edges.row_ptr, edges.nq, "attend")
+            both = npl > 0
+            msg = self.nn.forward_from(msg, 1, "both" if both else "f32")
+            msg, msg_in = msg if both else (msg, msg)
+            out = ops.seg_aggregate(msg, self.attend_nn(msg_in), edges.row_ptr, edges.nq, "attend")
         else:
             raise NotImplementedError("sparse SGCNN path: aggregation %r" % self.aggr_type)
         return out, pos, batch, point2curveidx
@@ -404,4 +413,4 @@ class SkipConnect(nn.Module):
         self.num_skips, self.nn = num_skips, nn
 
     def forward(self, xs, pos, batch, point2curveidx=None, **kwargs):
-        return self.nn(ops.concat_cols(list(xs))), pos, batch, point2curveidx
+        return self.nn(cat_features(list(xs))), pos, batch, point2curveidx

@@ -379,22 +379,34 @@ def linear(A: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], act: 
 
 
 def edge_layer1(H: Optional[torch.Tensor], wp: torch.Tensor, bias: Optional[torch.Tensor], pos_src, pos_dst,
-                edges: EdgeCSR, normalize_radius: Optional[float], act: int, slope: float = 0.01) -> torch.Tensor:
+                edges: EdgeCSR, normalize_radius: Optional[float], act: int, slope: float = 0.01, n_planes: int = 0):
+    """-> fp32 (E, c), or activation planes when n_planes > 0 (c % 8 == 0)."""
     c = wp.shape[1]
-    out = _empty((edges.n_edges, c), torch.float32, wp)
     if H is not None:
         H, ldh = _rows(H)
     else:
         ldh = 0
+    if n_planes and c % 8 == 0 and (H is None or ldh % 4 == 0):
+        out = alloc_planes(edges.n_edges, c, n_planes, wp)
+        call("ccn_edge_layer1_planes", H if H is not None else 0, ldh, wp, bias if bias is not None else 0, _f32(pos_src),
+             _f32(pos_dst), edges.erow, edges.ecol, edges.n_edges, c, float(normalize_radius or 0.0), act, float(slope),
+             out.buf, out.kpad, out.plane_stride, n_planes)
+        return out
+    out = _empty((edges.n_edges, c), torch.float32, wp)
     call("ccn_edge_layer1", H if H is not None else 0, ldh, wp, bias if bias is not None else 0, _f32(pos_src),
          _f32(pos_dst), edges.erow, edges.ecol, edges.n_edges, c, float(normalize_radius or 0.0), act, float(slope),
          out, c)
     return out
 
 
-def edge_pair_layer1(PQ: torch.Tensor, edges: EdgeCSR, act: int, slope: float = 0.01) -> torch.Tensor:
+def edge_pair_layer1(PQ: torch.Tensor, edges: EdgeCSR, act: int, slope: float = 0.01, n_planes: int = 0):
     PQ, ld = _rows(PQ)
     c = PQ.shape[1] // 2
+    if n_planes and c % 8 == 0 and ld % 4 == 0:
+        out = alloc_planes(edges.n_edges, c, n_planes, PQ)
+        call("ccn_edge_pair_layer1_planes", PQ, ld, edges.erow, edges.ecol, edges.n_edges, c, act, float(slope), out.buf,
+             out.kpad, out.plane_stride, n_planes)
+        return out
     out = _empty((edges.n_edges, c), torch.float32, PQ)
     call("ccn_edge_pair_layer1", PQ, ld, edges.erow, edges.ecol, edges.n_edges, c, act, float(slope), out, c)
     return out
@@ -412,10 +424,15 @@ def seg_aggregate(msg: torch.Tensor, att: Optional[torch.Tensor], row_ptr: torch
     return out
 
 
-def sgcnn_layer1(PQ: torch.Tensor, idx: torch.Tensor, act: int, slope: float = 0.01) -> torch.Tensor:
+def sgcnn_layer1(PQ: torch.Tensor, idx: torch.Tensor, act: int, slope: float = 0.01, n_planes: int = 0):
     PQ, ld = _rows(PQ)
     n, K = idx.shape
     c = PQ.shape[1] // 2
+    if n_planes and c % 8 == 0 and ld % 4 == 0:
+        out = alloc_planes(n * (K + 1), c, n_planes, PQ)
+        call("ccn_sgcnn_layer1_planes", PQ, ld, idx, n, K, c, act, float(slope), out.buf, out.kpad, out.plane_stride,
+             n_planes)
+        return out
     out = _empty((n * (K + 1), c), torch.float32, PQ)
     call("ccn_sgcnn_layer1", PQ, ld, idx, n, K, c, act, float(slope), out, c)
     return out

@@ -204,6 +204,19 @@ int ccn_linear_planes(const void* a_hi_tmap_host, const void* a_lo_tmap_host, co
                       int64_t yp_plane_stride, int64_t M, int32_t N, int32_t K, int32_t box_n, int32_t mode, int32_t act,
                       float slope, ccn_stream_t stream);
 
+/* Planes-output variants of the per-edge first layers (the consumer is the next Linear of the edge MLP); c % 8 == 0,
+ * kpad == c, fp32 inputs 16-byte aligned with leading dimensions % 4 == 0. */
+int ccn_sgcnn_layer1_planes(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c,
+                            int32_t act, float slope, void* planes, int64_t kpad, int64_t plane_stride,
+                            int32_t n_planes, ccn_stream_t stream);
+int ccn_edge_pair_layer1_planes(const float* PQ, int64_t ldpq, const int32_t* erow, const int32_t* ecol, int64_t E,
+                                int32_t c, int32_t act, float slope, void* planes, int64_t kpad, int64_t plane_stride,
+                                int32_t n_planes, ccn_stream_t stream);
+int ccn_edge_layer1_planes(const float* H, int64_t ldh, const float* wp, const float* bias, const float* pos_src,
+                           const float* pos_dst, const int32_t* erow, const int32_t* ecol, int64_t E, int32_t c,
+                           float normalize_radius, int32_t act, float slope, void* planes, int64_t kpad,
+                           int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
