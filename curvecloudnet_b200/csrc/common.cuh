@@ -7,6 +7,9 @@
 
 extern unsigned long long g_ccn_kernel_launches;   // version.cu; one increment per <<<>>> (bench.py's gpu_launches)
 
+// gemm_tc.cu: CUtensorMap (128 bytes, 64-byte aligned, HOST memory) of a bf16 (n, kpad) row-major matrix, box 64 x box_n
+int ccn_encode_bf16_map(void* tmap_out_host, const void* base, int64_t n, int64_t kpad, int32_t box_n);
+
 #define CCN_CHECK_LAUNCH()                                 \
     do {                                                   \
         cudaError_t e__ = cudaGetLastError();              \

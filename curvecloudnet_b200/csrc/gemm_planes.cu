@@ -307,12 +307,13 @@ extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const i
     return CCN_OK;
 }
 
-extern "C" int ccn_linear_planes(const void* a_hi_tmap_host, const void* a_lo_tmap_host, const void* w_hi_tmap_host,
+extern "C" int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_plane_stride, const void* w_hi_tmap_host,
                                  const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes,
                                  int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N, int32_t K, int32_t box_n,
                                  int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
-    CCN_REQUIRE(a_hi_tmap_host && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0 && K > 0);
-    CCN_REQUIRE((mode == 1 || (mode == 3 && a_lo_tmap_host && w_lo_tmap_host)) && act >= 0 && act <= 2);
+    CCN_REQUIRE(a_planes && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0 && K > 0);
+    CCN_REQUIRE((mode == 1 || (mode == 3 && w_lo_tmap_host && (a_plane_stride & 7) == 0)) && act >= 0 && act <= 2);
+    CCN_REQUIRE(a_ld >= K && (a_ld & 7) == 0 && (reinterpret_cast<uintptr_t>(a_planes) & 15) == 0);
     CCN_REQUIRE(box_n == 32 || box_n == 64 || box_n == 128 || box_n == 256);
     CCN_REQUIRE(!Y || ldy >= N);
     const int yp_cols = (N + 7) & ~7;
@@ -344,8 +345,13 @@ extern "C" int ccn_linear_planes(const void* a_hi_tmap_host, const void* a_lo_tm
     if (stages < 2) return CCN_EUNSUPPORTED;
     p.stages = stages;
     const int smem = (int)((p.resident ? wres : 0) + (int64_t)stages * stage_bytes + 1024);
-    const CUtensorMap* ahi = (const CUtensorMap*)a_hi_tmap_host;
-    const CUtensorMap* alo = mode == 3 ? (const CUtensorMap*)a_lo_tmap_host : ahi;
+    alignas(64) CUtensorMap amaps[2];
+    int rc = ccn_encode_bf16_map(&amaps[0], a_planes, M, a_ld, kBM);
+    if (rc == CCN_OK && mode == 3)
+        rc = ccn_encode_bf16_map(&amaps[1], (const __nv_bfloat16*)a_planes + a_plane_stride, M, a_ld, kBM);
+    if (rc != CCN_OK) return rc;
+    const CUtensorMap* ahi = &amaps[0];
+    const CUtensorMap* alo = mode == 3 ? &amaps[1] : ahi;
     const CUtensorMap* whi = (const CUtensorMap*)w_hi_tmap_host;
     const CUtensorMap* wlo = mode == 3 ? (const CUtensorMap*)w_lo_tmap_host : whi;
     cudaStream_t s = (cudaStream_t)stream;

@@ -226,15 +226,10 @@ extern "C" int ccn_split_bf16(const float* w, int64_t ldw, int32_t n, int32_t k,
     return CCN_OK;
 }
 
-// Host-side TMA descriptor of a bf16 (n, kpad) row-major weight: box = 64 (K) x box_n rows, SWIZZLE_128B.
-extern "C" int ccn_weight_tensor_map(void* tmap_out_host, const void* w_bf16, int32_t n, int32_t kpad, int32_t box_n) {
-    CCN_REQUIRE(tmap_out_host && w_bf16 && n > 0 && kpad > 0 && (kpad % 8) == 0 && box_n >= 16 && box_n <= 256);
-    cuuint64_t dims[2] = {(cuuint64_t)kpad, (cuuint64_t)n};
-    cuuint64_t strides[1] = {(cuuint64_t)kpad * 2};
-    cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_n};
-    cuuint32_t estr[2] = {1, 1};
-    // libcuda is resolved at run time through the runtime's driver entry point (the library must load, and
-    // export its symbols, on hosts without a driver; nothing here links -lcuda).
+// Host-side TMA descriptor of a bf16 (n, kpad) row-major matrix: box = 64 (K) x box_n rows, SWIZZLE_128B.
+// libcuda is resolved at run time through the runtime's driver entry point (the library must load, and export its
+// symbols, on hosts without a driver; nothing here links -lcuda).
+int ccn_encode_bf16_map(void* tmap_out_host, const void* base, int64_t n, int64_t kpad, int32_t box_n) {
     typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -247,11 +242,19 @@ extern "C" int ccn_weight_tensor_map(void* tmap_out_host, const void* w_bf16, in
         if (q != cudaDriverEntryPointSuccess || !fn) return CCN_EUNSUPPORTED;
         encode = (EncodeTiled)fn;
     }
-    CUresult r = encode((CUtensorMap*)tmap_out_host, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                        const_cast<void*>(w_bf16), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+    cuuint64_t dims[2] = {(cuuint64_t)kpad, (cuuint64_t)n};
+    cuuint64_t strides[1] = {(cuuint64_t)kpad * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_n};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = encode((CUtensorMap*)tmap_out_host, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                        strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? CCN_OK : 1000 + (int)r;
+}
+
+extern "C" int ccn_weight_tensor_map(void* tmap_out_host, const void* w_bf16, int32_t n, int32_t kpad, int32_t box_n) {
+    CCN_REQUIRE(tmap_out_host && w_bf16 && n > 0 && kpad > 0 && (kpad % 8) == 0 && box_n >= 16 && box_n <= 256);
+    return ccn_encode_bf16_map(tmap_out_host, w_bf16, n, kpad, box_n);
 }
 
 extern "C" int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_host, const void* w_lo_tmap_host,

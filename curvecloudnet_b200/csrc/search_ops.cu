@@ -170,6 +170,97 @@ __global__ void __launch_bounds__(256) knn_exact_kernel(
     }
 }
 
+
+// Exact kNN for small K (the K=3 of feature propagation, point_ops.py:331): 8 lanes per query, 32 queries per CTA,
+// the source cloud streamed through shared memory in SoA tiles shared by all queries of the CTA, the K best
+// (d2, index) keys of every lane in registers, merged across the 8 lanes by a shuffle butterfly at the end.
+// Same total order as knn_exact_kernel, so the two agree bit for bit.
+constexpr int kSmallTile = 2048;
+
+template <int K>
+__device__ __forceinline__ void topk_insert(unsigned long long (&k)[K], unsigned long long c) {
+    if (c < k[K - 1]) {
+        k[K - 1] = c;
+#pragma unroll
+        for (int i = K - 1; i > 0; --i) {
+            const unsigned long long a = k[i - 1], b = k[i];
+            const bool sw = b < a;
+            k[i - 1] = sw ? b : a;
+            k[i] = sw ? a : b;
+        }
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(256) knn_small_kernel(
+    const float* __restrict__ p1, const int64_t* __restrict__ batch1, int64_t n1, const float* __restrict__ p2,
+    const int32_t* __restrict__ sptr2, int Kout, int zero_fill, int32_t* __restrict__ idx_out,
+    float* __restrict__ d2_out, int32_t* __restrict__ cnt_out) {
+    __shared__ float sx[kSmallTile], sy[kSmallTile], sz[kSmallTile];
+    __shared__ int s_lo, s_hi;
+    const int sub = threadIdx.x & 7;
+    const int64_t q = (int64_t)blockIdx.x * 32 + (threadIdx.x >> 3);
+    const bool live = q < n1;
+    float qx = 0.f, qy = 0.f, qz = 0.f;
+    int lo2 = 0, hi2 = 0;
+    if (live) {
+        qx = p1[3 * q]; qy = p1[3 * q + 1]; qz = p1[3 * q + 2];
+        const int b = (int)batch1[q];
+        lo2 = sptr2[b]; hi2 = sptr2[b + 1];
+    }
+    if (threadIdx.x == 0) {                 // queries are batch-sorted: the CTA's source range is one interval
+        const int64_t qa = (int64_t)blockIdx.x * 32, qb = min(qa + 31, n1 - 1);
+        s_lo = sptr2[(int)batch1[qa]];
+        s_hi = sptr2[(int)batch1[qb] + 1];
+    }
+    __syncthreads();
+    const int blo = s_lo, bhi = s_hi;
+    unsigned long long best[K];
+#pragma unroll
+    for (int i = 0; i < K; ++i) best[i] = kKeyMax;
+    float worst = INFINITY;
+    for (int t0 = blo; t0 < bhi; t0 += kSmallTile) {
+        const int tn = min(kSmallTile, bhi - t0);
+        __syncthreads();
+        for (int j = threadIdx.x; j < tn; j += blockDim.x) {
+            sx[j] = p2[3 * (int64_t)(t0 + j)]; sy[j] = p2[3 * (int64_t)(t0 + j) + 1]; sz[j] = p2[3 * (int64_t)(t0 + j) + 2];
+        }
+        __syncthreads();
+        const int ja = max(lo2 - t0, 0), jb = min(hi2 - t0, tn);
+        for (int j = ja + sub; j < jb; j += 8) {
+            const float d2 = ccn_sqdist3(qx, qy, qz, sx[j], sy[j], sz[j]);
+            if (d2 <= worst) {
+                topk_insert<K>(best, ccn_pack_key(d2, t0 + j));
+                worst = __uint_as_float((unsigned)(best[K - 1] >> 32));     // +inf bits while the list is not full
+                if (best[K - 1] == kKeyMax) worst = INFINITY;
+            }
+        }
+    }
+    // merge the 8 lanes of a query (all lanes end with the full result)
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        unsigned long long other[K];
+#pragma unroll
+        for (int i = 0; i < K; ++i) other[i] = __shfl_xor_sync(0xffffffffu, best[i], o);
+#pragma unroll
+        for (int i = 0; i < K; ++i) topk_insert<K>(best, other[i]);
+    }
+    if (!live || sub != 0) return;
+    int cnt = 0;
+#pragma unroll
+    for (int i = 0; i < K; ++i) {
+        if (i >= Kout) break;
+        const bool have = best[i] != kKeyMax;
+        const int32_t id = have ? (int32_t)(best[i] & 0xffffffffu) : (zero_fill && hi2 > lo2 ? lo2 : -1);
+        idx_out[q * Kout + i] = id;
+        if (d2_out)
+            d2_out[q * Kout + i] = have ? __uint_as_float((unsigned)(best[i] >> 32))
+                                        : (id >= 0 ? ccn_sqdist3(qx, qy, qz, p2[3 * id], p2[3 * id + 1], p2[3 * id + 2]) : 0.f);
+        cnt += (have || (zero_fill && hi2 > lo2)) ? 1 : 0;
+    }
+    if (cnt_out) cnt_out[q] = cnt;
+}
+
 // ball_query: first K points of the query's cloud in INDEX order with d2 < r2 (strict).
 __global__ void __launch_bounds__(256) ball_query_kernel(
     const float* __restrict__ p1, const int64_t* __restrict__ batch1, int64_t n1, const float* __restrict__ p2,
@@ -250,6 +341,20 @@ extern "C" int ccn_knn_exact(const float* pos1, const int64_t* batch1, int64_t n
                              float* d2_out, int32_t* cnt_out, ccn_stream_t stream) {
     CCN_REQUIRE(n1 >= 0 && K >= 1 && K <= 32 && idx_out && sample_ptr2);
     if (n1 == 0) return CCN_OK;
+    if (K <= 4) {
+        const unsigned blocks = ccn_blocks_exact(n1, 32);
+        if (K <= 2)
+            knn_small_kernel<2><<<blocks, 256, 0, (cudaStream_t)stream>>>(pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
+                                                                          idx_out, d2_out, cnt_out);
+        else if (K == 3)
+            knn_small_kernel<3><<<blocks, 256, 0, (cudaStream_t)stream>>>(pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
+                                                                          idx_out, d2_out, cnt_out);
+        else
+            knn_small_kernel<4><<<blocks, 256, 0, (cudaStream_t)stream>>>(pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
+                                                                          idx_out, d2_out, cnt_out);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     knn_exact_kernel<<<ccn_blocks_exact(n1 * 32, 256), 256, 0, (cudaStream_t)stream>>>(
         pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill, idx_out, d2_out, cnt_out);
     CCN_CHECK_LAUNCH();

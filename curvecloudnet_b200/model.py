@@ -12,7 +12,7 @@ import torch
 
 from . import modules as M
 from . import native, ops
-from .nn import MLP, Draws, ForwardCache, cat_features, get_precision, set_precision
+from .nn import MLP, Draws, ForwardCache, cat_features, get_precision, set_precision, set_weights_epoch
 
 _DOWN_STEPS = ("sa", "sa-geo", "sa-global", "pt-transition-down")
 
@@ -149,11 +149,21 @@ class ModelBase(torch.nn.Module):
         prev = get_precision()
         set_precision(self.precision)
         native.pin_stream(True)
+        set_weights_epoch(self._weights_epoch())
         try:
             return self._forward(data, draws, **kwargs)
         finally:
+            set_weights_epoch(None)
             native.pin_stream(False)
             set_precision(prev)
+
+    def _weights_epoch(self):
+        """Fingerprint of every parameter/buffer (in-place version counters + storage identity + train flag)."""
+        ts = list(self.parameters()) + list(self.buffers())
+        v = 0
+        for t in ts:
+            v += t._version
+        return (id(self), self.training, v, ts[0].data_ptr() if ts else 0, len(ts))
 
     def _forward(self, data, draws: Draws = None, **kwargs):
         """base.py:133-175.  hist[k][i] is the INPUT of step i (the lists start with the raw input)."""

@@ -75,7 +75,7 @@ _prof_shapes = []          # (M, N, K) of every timed Linear call (tools/profile
 _prof_events = []          # (name, start event, end event, algorithmic work of the call)
 
 # algorithmic work of one call: FLOPs for the Linear kernels (2 M N K)
-_MNK = {"ccn_linear_f32": (7, 8, 9), "ccn_linear_tc": (7, 8, 9), "ccn_linear_planes": (10, 11, 12)}
+_MNK = {"ccn_linear_f32": (7, 8, 9), "ccn_linear_tc": (7, 8, 9), "ccn_linear_planes": (11, 12, 13)}
 _WORK = {name: (lambda a, ix=ix: 2.0 * a[ix[0]] * a[ix[1]] * a[ix[2]]) for name, ix in _MNK.items()}
 
 
@@ -111,33 +111,52 @@ def pin_stream(on: bool):
     _stream_handle = torch.cuda.current_stream().cuda_stream if on else None
 
 
+_fns = {}                   # name -> (foreign function, indices of the pointer arguments)
+
+
+def _bind(name):
+    lib = _lib if _lib is not None else load()
+    sig = SIGNATURES[name]
+    ent = (getattr(lib, name), tuple(i for i, ch in enumerate(sig[:-1]) if ch == "p"))
+    _fns[name] = ent
+    return ent
+
+
 def call(name, *args):
     """Call a C-ABI entry point; torch tensors become device pointers, the current stream is appended."""
-    lib = _lib if _lib is not None else load()
-    conv = []
-    for a in args:
-        if torch.is_tensor(a):
+    ent = _fns.get(name) or _bind(name)
+    conv = list(args)
+    for i in ent[1]:
+        a = conv[i]
+        if a.__class__ is not int:
             if not a.is_cuda:
                 raise CcnError("%s: tensor argument is not on a CUDA device (no CPU path exists)" % name)
-            conv.append(a.data_ptr())
-        else:
-            conv.append(a)
+            conv[i] = a.data_ptr()
     conv.append(_stream_handle if _stream_handle is not None else torch.cuda.current_stream().cuda_stream)
-    timed = _prof_names is not None and name in _prof_names
-    if timed:
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-    rc = getattr(lib, name)(*conv)
-    if timed:
-        e1.record()
-        _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
-        if name in _WORK:
-            ix = _MNK[name]
-            _prof_shapes.append((args[ix[0]], args[ix[1]], args[ix[2]]))
+    if _prof_names is not None and name in _prof_names:
+        return _timed_call(name, ent[0], conv, args)
+    rc = ent[0](*conv)
     if rc != 0:
-        if rc < 0:
-            raise CcnError("%s: invalid argument (code %d)" % (name, rc))
-        raise CcnError("%s: CUDA error %d" % (name, rc))
+        _raise(name, rc)
+
+
+def _raise(name, rc):
+    if rc < 0:
+        raise CcnError("%s: invalid argument (code %d)" % (name, rc))
+    raise CcnError("%s: CUDA error %d" % (name, rc))
+
+
+def _timed_call(name, fn, conv, args):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rc = fn(*conv)
+    e1.record()
+    _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
+    if name in _WORK:
+        ix = _MNK[name]
+        _prof_shapes.append((args[ix[0]], args[ix[1]], args[ix[2]]))
+    if rc != 0:
+        _raise(name, rc)
 
 
 def kernel_launches() -> int:

@@ -101,6 +101,15 @@ def fold_batchnorm(weight: torch.Tensor, bias: Optional[torch.Tensor], bn: Optio
     return w.contiguous(), b.contiguous()
 
 
+# Set by ModelBase.forward for the duration of a forward: one model-wide fingerprint of every parameter / buffer
+# version, so that the per-MLP "did my weights change" check is a single comparison on the per-scan path.
+_EPOCH = [None]
+
+
+def set_weights_epoch(epoch):
+    _EPOCH[0] = epoch
+
+
 _PRECISION = {"mode": "fp32"}
 PRECISIONS = ("fp32", "bf16x3", "bf16")
 
@@ -201,6 +210,7 @@ class MLP(torch.nn.Module):
         self.norms = torch.nn.ModuleList(BatchNorm(h) if norm is not None else torch.nn.Identity() for h in hidden)
         self._folded = None
         self._folded_key = None
+        self._folded_epoch = None
 
     @property
     def in_channels(self):
@@ -237,7 +247,11 @@ class MLP(torch.nn.Module):
         if self.training:
             raise NotImplementedError(
                 "curvecloudnet_b200 round 1 implements the inference (eval) path; call model.eval()")
+        epoch = _EPOCH[0]
+        if epoch is not None and self._folded is not None and self._folded_epoch == epoch:
+            return self._folded
         key = self._key()
+        self._folded_epoch = epoch
         if self._folded is None or key != self._folded_key:
             out = []
             act, slope = _ACTS[self.act_name]

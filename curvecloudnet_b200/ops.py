@@ -546,7 +546,6 @@ class Planes:
     def __init__(self, buf: torch.Tensor, m: int, k: int):
         self.buf, self.m, self.k = buf, m, k
         self.n_planes, self.kpad = buf.shape[0], buf.shape[2]
-        self._maps = None
 
     @property
     def shape(self):
@@ -555,13 +554,6 @@ class Planes:
     @property
     def plane_stride(self):
         return self.buf.stride(0)
-
-    def maps(self):
-        if self._maps is None:
-            hi = _tensor_map(self.buf[0].data_ptr(), max(self.m, 1), self.kpad, 128)
-            lo = _tensor_map(self.buf[1].data_ptr(), max(self.m, 1), self.kpad, 128) if self.n_planes == 2 else hi
-            self._maps = (hi[0], lo[0], (hi, lo))
-        return self._maps
 
     def to_f32(self) -> torch.Tensor:
         """Debug/test helper (torch arithmetic, not on the product path)."""
@@ -602,8 +594,7 @@ def linear_planes(A: Planes, tw: "TcWeight", bias: Optional[torch.Tensor], act: 
     Yp = alloc_planes(M, tw.n, A.n_planes, A.buf) if out in ("planes", "both") else None
     box = tw.pick_box_planes(M, A.n_planes)
     w_hi, w_lo, _ = tw.maps(box)
-    a_hi, a_lo, _ = A.maps()
-    call("ccn_linear_planes", a_hi, a_lo, w_hi, w_lo, bias if bias is not None else 0, Y if Y is not None else 0, tw.n,
+    call("ccn_linear_planes", A.buf, A.kpad, A.plane_stride, w_hi, w_lo, bias if bias is not None else 0, Y if Y is not None else 0, tw.n,
          Yp.buf if Yp is not None else 0, Yp.kpad if Yp is not None else 0, Yp.plane_stride if Yp is not None else 0,
          M, tw.n, K, box, mode, act, float(slope))
     return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)

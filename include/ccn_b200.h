@@ -193,13 +193,14 @@ int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_host, const
  *   ccn_pack_planes    up to four fp32 column blocks (block k optionally row-gathered through idx_k) -> planes:
  *                      replaces torch.cat / x[idx] in front of an MLP (pointnet2.py:132-139,160-163; skip_connect.py:13;
  *                      mlp.py:18-20; dgcnn.py:163-164);
- *   ccn_linear_planes  Y = act(A W^T + bias): A planes and W (ccn_split_bf16 layout) through host-encoded tensor maps
- *                      (ccn_weight_tensor_map with box_n = 128 for A, box_n for W); writes fp32 Y and/or output planes. */
+ *   ccn_linear_planes  Y = act(A W^T + bias): A = device planes (row stride a_ld, second plane a_plane_stride elements
+ *                      further), W (ccn_split_bf16 layout) through host-encoded tensor maps (ccn_weight_tensor_map);
+ *                      writes fp32 Y and/or output planes. */
 int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const int64_t* i0, const float* s1, int64_t ld1,
                     int32_t c1, const int64_t* i1, const float* s2, int64_t ld2, int32_t c2, const int64_t* i2,
                     const float* s3, int64_t ld3, int32_t c3, const int64_t* i3, int64_t n, void* planes, int64_t kpad,
                     int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
-int ccn_linear_planes(const void* a_hi_tmap_host, const void* a_lo_tmap_host, const void* w_hi_tmap_host,
+int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_plane_stride, const void* w_hi_tmap_host,
                       const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
                       int64_t yp_plane_stride, int64_t M, int32_t N, int32_t K, int32_t box_n, int32_t mode, int32_t act,
                       float slope, ccn_stream_t stream);

@@ -192,3 +192,42 @@ def test_linear_tensor_core(mode, tol):
         a2 = torch.randn(m, k + 5, generator=gen)          # unaligned, strided A; no bias
         y2 = ops.linear_tc(a2.cuda()[:, 2:2 + k], tw, None, 0, 0.01, mode).cpu()
         assert rel_err(y2, (a2[:, 2:2 + k].double() @ w.double().t()).float()) <= tol, (m, n, k, "strided")
+
+
+@pytest.mark.parametrize("K", [1, 2, 3, 4])
+def test_small_k_exact_knn_equals_warp_kernel_and_oracle(K):
+    """ccn_knn_exact has two kernels (K <= 4: 8 lanes per query over smem tiles; K > 4: warp per query); both must
+    give the oracle's (d2, index) total order, including duplicate points, ragged clouds and clouds shorter than K."""
+    from curvecloudnet_b200 import ops
+    from oracle import tp_ops as tp
+    g = torch.Generator().manual_seed(40 + K)
+    lens2 = [700, 2, 2500, 0, 40]
+    lens1 = [300, 5, 1000, 3, 77]
+    p2 = torch.rand(sum(lens2), 3, generator=g)
+    p2[10:20] = p2[0:10]                                     # exact duplicates -> index tie-break
+    p1 = torch.rand(sum(lens1), 3, generator=g)
+    p1[0:5] = p2[0:5]
+    b1 = torch.cat([torch.full((n,), i, dtype=torch.int64) for i, n in enumerate(lens1)])
+    b2 = torch.cat([torch.full((n,), i, dtype=torch.int64) for i, n in enumerate(lens2)])
+    host = [0]
+    for n in lens2:
+        host.append(host[-1] + n)
+    sp = ops.SamplePtr(torch.tensor(host, dtype=torch.int32).cuda(), host)
+    idx, d2, cnt = ops.knn_exact(p1.cuda(), b1.cuda(), p2.cuda(), sp, K, zero_fill=False, want_d2=True, want_cnt=True)
+    idx5, d25 = ops.knn_exact(p1.cuda(), b1.cuda(), p2.cuda(), sp, 5, zero_fill=False, want_d2=True)
+    assert torch.equal(idx.cpu(), idx5.cpu()[:, :K])
+    valid = idx.cpu() >= 0
+    assert torch.equal(d2.cpu()[valid], d25.cpu()[:, :K][valid])
+    # oracle (pytorch3d.knn_points restatement) on padded clouds
+    off1, off2 = 0, 0
+    for n1_, n2_ in zip(lens1, lens2):
+        if n1_ and n2_:
+            od, oi = tp.knn_points(p1[off1:off1 + n1_][None], p2[off2:off2 + n2_][None], torch.tensor([n1_]), torch.tensor([n2_]), K)
+            kk = min(K, n2_)
+            got = idx.cpu()[off1:off1 + n1_, :kk].long() - off2
+            assert torch.equal(got, oi[0, :, :kk])
+            assert torch.equal(cnt.cpu()[off1:off1 + n1_].long(), torch.full((n1_,), kk))
+        elif n1_:
+            assert bool((idx.cpu()[off1:off1 + n1_] == -1).all())
+        off1 += n1_
+        off2 += n2_

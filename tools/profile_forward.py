@@ -16,6 +16,17 @@ with torch.no_grad():
     for _ in range(3):
         torch.manual_seed(0); model(data)
 torch.cuda.synchronize()
+import time
+ws = []
+for _ in range(5):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        torch.manual_seed(0); model(data)
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    ws.append(((t1 - t0) * 1e3, (time.perf_counter() - t0) * 1e3))
+print("untimed forwards: host return / device done (ms):", ", ".join("%.2f/%.2f" % w for w in ws))
 native.profile_begin(list(native.SIGNATURES))
 native._prof_detail = True
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
