@@ -157,9 +157,20 @@ class ModelBase(torch.nn.Module):
             native.pin_stream(False)
             set_precision(prev)
 
+    def _apply(self, fn, *a, **k):
+        self.__dict__.pop("_epoch_tensors", None)       # .to()/.cuda() replace buffer tensors
+        return super()._apply(fn, *a, **k)
+
+    def load_state_dict(self, *a, **k):
+        self.__dict__.pop("_epoch_tensors", None)
+        return super().load_state_dict(*a, **k)
+
     def _weights_epoch(self):
         """Fingerprint of every parameter/buffer (in-place version counters + storage identity + train flag)."""
-        ts = list(self.parameters()) + list(self.buffers())
+        ts = self.__dict__.get("_epoch_tensors")
+        if ts is None:
+            ts = list(self.parameters()) + list(self.buffers())
+            self.__dict__["_epoch_tensors"] = ts
         v = 0
         for t in ts:
             v += t._version

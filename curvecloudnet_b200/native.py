@@ -79,8 +79,9 @@ _MNK = {"ccn_linear_f32": (7, 8, 9), "ccn_linear_tc": (7, 8, 9), "ccn_linear_pla
 _WORK = {name: (lambda a, ix=ix: 2.0 * a[ix[0]] * a[ix[1]] * a[ix[2]]) for name, ix in _MNK.items()}
 
 
-def profile_begin(names):
-    global _prof_names, _prof_events
+def profile_begin(names, pad_cycles=0):
+    global _prof_names, _prof_events, _prof_pad_cycles
+    _prof_pad_cycles = int(pad_cycles)
     _prof_names = set(names) if names else None
     _prof_events = []
     del _prof_shapes[:]
@@ -146,8 +147,15 @@ def _raise(name, rc):
     raise CcnError("%s: CUDA error %d" % (name, rc))
 
 
+_prof_pad_cycles = 0        # > 0: a spin of that many GPU cycles is queued before every timed launch, so that the
+                            # launch is already in the queue when the GPU reaches the start event (the event pair then
+                            # brackets the kernel, not the host's launch latency)
+
+
 def _timed_call(name, fn, conv, args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if _prof_pad_cycles:
+        torch.cuda._sleep(_prof_pad_cycles)
     e0.record()
     rc = fn(*conv)
     e1.record()

@@ -45,10 +45,41 @@ with torch.no_grad():
         torch.cuda.synchronize()
         print("forward host %.2f ms, of which %.2f ms inside %d tolist/item calls" % ((t1 - t0) * 1e3, sync_t[0] * 1e3, sync_t[1]))
 torch.Tensor.tolist, torch.Tensor.item = _tolist, _item
+
+# time inside the foreign calls (kernel launches) and inside torch.empty
+from curvecloudnet_b200 import native
+ff = {}
+for name, (fn, ptrs) in list(native._fns.items()):
+    def mk(fn, name):
+        def w(*a):
+            t = time.perf_counter(); r = fn(*a); d = time.perf_counter() - t
+            e = ff.setdefault(name, [0.0, 0]); e[0] += d; e[1] += 1
+            return r
+        return w
+    native._fns[name] = (mk(fn, name), ptrs)
+_empty = torch.empty
+et = [0.0, 0]
+def empty(*a, **k):
+    t = time.perf_counter(); r = _empty(*a, **k); et[0] += time.perf_counter() - t; et[1] += 1; return r
+torch.empty = empty
+with torch.no_grad():
+    for rep in range(2):
+        ff.clear(); et[:] = [0.0, 0]
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        torch.manual_seed(0); model(data)
+        t1 = time.perf_counter(); torch.cuda.synchronize()
+    tot = sum(v[0] for v in ff.values())
+    print("forward host %.2f ms (with wrappers); inside foreign calls %.2f ms over %d calls; torch.empty %.2f ms over %d" % ((t1 - t0) * 1e3, tot * 1e3, sum(v[1] for v in ff.values()), et[0] * 1e3, et[1]))
+    for k, v in sorted(ff.items(), key=lambda kv: -kv[1][0])[:12]:
+        print("   %-28s %3d calls %7.1f us each" % (k, v[1], v[0] / v[1] * 1e6))
+torch.empty = _empty
+for name in list(native._fns):
+    native._fns.pop(name)
 pr = cProfile.Profile()
 with torch.no_grad():
     torch.manual_seed(0)
     pr.enable(); model(data); pr.disable()
 torch.cuda.synchronize()
 st = pstats.Stats(pr)
-st.sort_stats("tottime").print_stats(28)
+st.sort_stats("tottime").print_stats(45)
+st.sort_stats("cumulative").print_stats(45)
