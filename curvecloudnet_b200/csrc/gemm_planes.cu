@@ -40,18 +40,29 @@ struct PlanesParams {
     __nv_bfloat16* Yp;      // planes output or null
     int64_t yp_ld;          // row stride (elements) of an output plane
     int64_t yp_plane;       // plane stride (elements)
-    int yp_cols;            // columns to write per output plane row (N rounded up to 8)
+    int yp_cols;            // columns to write per output plane row (N rounded up to 16)
     int M, N, K;
     int BN, tiles_m, tiles_n;
     int stages, resident;
     int act;
     float slope;
+    int nseg;               // A = [A_0 | A_1 | ...] along K: every segment is its own planes tensor
+    int sc1, sc2, sc3, nk;  // first 64-wide K chunk of segments 1..3 (= nk for absent segments), total chunks
 };
+
+__device__ __forceinline__ void st_global_256(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e,
+                                              uint32_t f, uint32_t g, uint32_t h) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d),
+                 "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
+
+constexpr int kMaxSeg = 4;
+struct AMaps { CUtensorMap hi[kMaxSeg], lo[kMaxSeg]; };
 
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
-    const __grid_constant__ CUtensorMap a_hi, const __grid_constant__ CUtensorMap a_lo,
-    const __grid_constant__ CUtensorMap w_hi, const __grid_constant__ CUtensorMap w_lo, const PlanesParams p) {
+    const __grid_constant__ AMaps am, const __grid_constant__ CUtensorMap w_hi,
+    const __grid_constant__ CUtensorMap w_lo, const PlanesParams p) {
     constexpr int P = MODE == 3 ? 2 : 1;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 5];   // full[S], empty[S], wfull, tfull[2], tempty[2]
@@ -60,7 +71,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int BN = p.BN, stages = p.stages;
-    const int nk = (p.K + kBK - 1) / kBK;
+    const int nk = p.nk;
     const int wtile = BN * kBK * 2;                      // bytes of one W tile (one plane, one K chunk)
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t w_res = smem0;                        // resident weights: [nk][P][BN x 64]
@@ -107,12 +118,18 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 const int m0 = (t / p.tiles_n) * kBM, n0 = (t % p.tiles_n) * BN;
                 for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                    const CUtensorMap *mh, *ml;
+                    int ka;                                             // column inside the segment's planes
+                    if (kc < p.sc1) { mh = &am.hi[0]; ml = &am.lo[0]; ka = kc * kBK; }
+                    else if (kc < p.sc2) { mh = &am.hi[1]; ml = &am.lo[1]; ka = (kc - p.sc1) * kBK; }
+                    else if (kc < p.sc3) { mh = &am.hi[2]; ml = &am.lo[2]; ka = (kc - p.sc2) * kBK; }
+                    else { mh = &am.hi[3]; ml = &am.lo[3]; ka = (kc - p.sc3) * kBK; }
                     const int s = cnt % stages;
                     mbar_wait(empty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
                     const uint32_t dst = ring0 + s * stage_bytes;
                     mbar_arrive_expect_tx(full0 + 8 * s, (uint32_t)stage_bytes);
-                    tma_load_2d(dst, &a_hi, kc * kBK, m0, full0 + 8 * s);
-                    if (P == 2) tma_load_2d(dst + kATile, &a_lo, kc * kBK, m0, full0 + 8 * s);
+                    tma_load_2d(dst, mh, ka, m0, full0 + 8 * s);
+                    if (P == 2) tma_load_2d(dst + kATile, ml, ka, m0, full0 + 8 * s);
                     if (!p.resident) {
                         tma_load_2d(dst + P * kATile, &w_hi, kc * kBK, n0, full0 + 8 * s);
                         if (P == 2) tma_load_2d(dst + P * kATile + wtile, &w_lo, kc * kBK, n0, full0 + 8 * s);
@@ -164,7 +181,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
     } else {
         // ------------------------------------------------------------------ epilogue (warps 2..5)
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
-        const bool vecy = p.Y && ((p.ldy & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.Y) & 15) == 0);
+        const bool vecy = p.Y && ((p.ldy & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.Y) & 31) == 0);
         int it = 0, bias_n0 = -1;
         const float* bs = bias_s;
         const int et = threadIdx.x - 64;                // 0..127 over the four epilogue warps
@@ -197,13 +214,15 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     if (p.Y) {
                         float* yrow = p.Y + (int64_t)row * p.ldy + n0 + c0;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
+                        for (int j = 0; j < 32; j += 8) {
                             const int n = n0 + c0 + j;
-                            if (vecy && n + 3 < p.N) {
-                                *reinterpret_cast<float4*>(yrow + j) = make_float4(y[j], y[j + 1], y[j + 2], y[j + 3]);
+                            if (vecy && n + 7 < p.N) {          // one full 32-byte sector per store
+                                st_global_256(yrow + j, __float_as_uint(y[j]), __float_as_uint(y[j + 1]),
+                                              __float_as_uint(y[j + 2]), __float_as_uint(y[j + 3]), __float_as_uint(y[j + 4]),
+                                              __float_as_uint(y[j + 5]), __float_as_uint(y[j + 6]), __float_as_uint(y[j + 7]));
                             } else {
 #pragma unroll
-                                for (int e = 0; e < 4; ++e)
+                                for (int e = 0; e < 8; ++e)
                                     if (n + e < p.N) yrow[j + e] = y[j + e];
                             }
                         }
@@ -211,19 +230,21 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     if (p.Yp) {
                         __nv_bfloat16* hrow = p.Yp + (int64_t)row * p.yp_ld + n0 + c0;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            if (n0 + c0 + j >= p.yp_cols) break;       // yp_cols % 8 == 0: whole groups only
-                            __nv_bfloat162 h[4], l[4];
+                        for (int j = 0; j < 32; j += 16) {
+                            if (n0 + c0 + j >= p.yp_cols) continue;    // yp_cols % 16 == 0: whole groups only
+                            uint32_t h[8], l[8];
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                h[e] = __floats2bfloat162_rn(y[j + 2 * e], y[j + 2 * e + 1]);
+                            for (int e = 0; e < 8; ++e) {
+                                const __nv_bfloat162 hv = __floats2bfloat162_rn(y[j + 2 * e], y[j + 2 * e + 1]);
+                                h[e] = *reinterpret_cast<const uint32_t*>(&hv);
                                 if (P == 2) {
-                                    const float2 f = __bfloat1622float2(h[e]);
-                                    l[e] = __floats2bfloat162_rn(y[j + 2 * e] - f.x, y[j + 2 * e + 1] - f.y);
+                                    const float2 f = __bfloat1622float2(hv);
+                                    const __nv_bfloat162 lv = __floats2bfloat162_rn(y[j + 2 * e] - f.x, y[j + 2 * e + 1] - f.y);
+                                    l[e] = *reinterpret_cast<const uint32_t*>(&lv);
                                 }
                             }
-                            *reinterpret_cast<uint4*>(hrow + j) = *reinterpret_cast<uint4*>(h);
-                            if (P == 2) *reinterpret_cast<uint4*>(hrow + p.yp_plane + j) = *reinterpret_cast<uint4*>(l);
+                            st_global_256(hrow + j, h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
+                            if (P == 2) st_global_256(hrow + p.yp_plane + j, l[0], l[1], l[2], l[3], l[4], l[5], l[6], l[7]);
                         }
                     }
                 }
@@ -307,27 +328,47 @@ extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const i
     return CCN_OK;
 }
 
-extern "C" int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_plane_stride, const void* w_hi_tmap_host,
+extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, const void* a1, int64_t ld1,
+                                 int64_t ps1, int32_t k1, const void* a2, int64_t ld2, int64_t ps2, int32_t k2,
+                                 const void* a3, int64_t ld3, int64_t ps3, int32_t k3, const void* w_hi_tmap_host,
                                  const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes,
-                                 int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N, int32_t K, int32_t box_n,
+                                 int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n,
                                  int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
-    CCN_REQUIRE(a_planes && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0 && K > 0);
-    CCN_REQUIRE((mode == 1 || (mode == 3 && w_lo_tmap_host && (a_plane_stride & 7) == 0)) && act >= 0 && act <= 2);
-    CCN_REQUIRE(a_ld >= K && (a_ld & 7) == 0 && (reinterpret_cast<uintptr_t>(a_planes) & 15) == 0);
+    const void* ap[kMaxSeg] = {a0, a1, a2, a3};
+    const int64_t ald[kMaxSeg] = {ld0, ld1, ld2, ld3}, aps[kMaxSeg] = {ps0, ps1, ps2, ps3};
+    const int32_t ak[kMaxSeg] = {k0, k1, k2, k3};
+    CCN_REQUIRE(a0 && k0 > 0 && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0);
+    CCN_REQUIRE((mode == 1 || (mode == 3 && w_lo_tmap_host)) && act >= 0 && act <= 2);
     CCN_REQUIRE(box_n == 32 || box_n == 64 || box_n == 128 || box_n == 256);
     CCN_REQUIRE(!Y || ldy >= N);
-    const int yp_cols = (N + 7) & ~7;
-    CCN_REQUIRE(!y_planes || (yp_ld >= yp_cols && (yp_ld & 7) == 0 && (reinterpret_cast<uintptr_t>(y_planes) & 15) == 0 &&
-                              (mode == 1 || (yp_plane_stride & 7) == 0)));
+    const int yp_cols = (N + 15) & ~15;
+    CCN_REQUIRE(!y_planes || (yp_ld >= yp_cols && (yp_ld & 15) == 0 && (reinterpret_cast<uintptr_t>(y_planes) & 31) == 0 &&
+                              (mode == 1 || (yp_plane_stride & 15) == 0)));
+    PlanesParams p;
+    p.nseg = 0;
+    int chunk0[kMaxSeg + 1] = {0, 0, 0, 0, 0};
+    int K = 0;
+    for (int i = 0; i < kMaxSeg; ++i) {
+        if (ak[i] <= 0) break;
+        CCN_REQUIRE(ap[i] && ald[i] >= ak[i] && (ald[i] & 7) == 0 && (reinterpret_cast<uintptr_t>(ap[i]) & 15) == 0 &&
+                    (mode == 1 || (aps[i] & 7) == 0));
+        chunk0[i + 1] = chunk0[i] + (ak[i] + kBK - 1) / kBK;
+        K += ak[i];
+        p.nseg = i + 1;
+    }
+    for (int i = p.nseg; i < kMaxSeg; ++i) {
+        CCN_REQUIRE(ak[i] <= 0);
+        chunk0[i + 1] = chunk0[p.nseg];
+    }
+    p.sc1 = chunk0[1]; p.sc2 = chunk0[2]; p.sc3 = chunk0[3]; p.nk = chunk0[p.nseg];
     if (M == 0) return CCN_OK;
     const int P = mode == 3 ? 2 : 1;
-    PlanesParams p;
     p.bias = bias; p.Y = Y; p.ldy = ldy; p.Yp = (__nv_bfloat16*)y_planes; p.yp_ld = yp_ld; p.yp_plane = yp_plane_stride;
     p.yp_cols = yp_cols; p.M = (int)M; p.N = N; p.K = K; p.BN = box_n;
     p.tiles_m = (int)((M + kBM - 1) / kBM);
     p.tiles_n = (N + box_n - 1) / box_n;
     p.act = act; p.slope = slope;
-    const int nk = (K + kBK - 1) / kBK;
+    const int nk = p.nk;
     const int wtile = box_n * kBK * 2;
     const int64_t total = (int64_t)p.tiles_m * p.tiles_n;
     const int budget = kSmemLimit - 2560;        // dynamic limit (kSmemLimit - 1536; 1.2 KB is static) minus the 1024-byte alignment slack
@@ -345,13 +386,15 @@ extern "C" int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_p
     if (stages < 2) return CCN_EUNSUPPORTED;
     p.stages = stages;
     const int smem = (int)((p.resident ? wres : 0) + (int64_t)stages * stage_bytes + 1024);
-    alignas(64) CUtensorMap amaps[2];
-    int rc = ccn_encode_bf16_map(&amaps[0], a_planes, M, a_ld, kBM);
-    if (rc == CCN_OK && mode == 3)
-        rc = ccn_encode_bf16_map(&amaps[1], (const __nv_bfloat16*)a_planes + a_plane_stride, M, a_ld, kBM);
-    if (rc != CCN_OK) return rc;
-    const CUtensorMap* ahi = &amaps[0];
-    const CUtensorMap* alo = mode == 3 ? &amaps[1] : ahi;
+    alignas(64) AMaps am;
+    for (int i = 0; i < kMaxSeg; ++i) {
+        const int j = i < p.nseg ? i : 0;         // unused slots repeat segment 0 (a valid descriptor)
+        int rc = ccn_encode_bf16_map(&am.hi[i], ap[j], M, ald[j], kBM);
+        if (rc == CCN_OK)
+            rc = ccn_encode_bf16_map(&am.lo[i], mode == 3 ? (const void*)((const __nv_bfloat16*)ap[j] + aps[j]) : ap[j], M,
+                                     ald[j], kBM);
+        if (rc != CCN_OK) return rc;
+    }
     const CUtensorMap* whi = (const CUtensorMap*)w_hi_tmap_host;
     const CUtensorMap* wlo = mode == 3 ? (const CUtensorMap*)w_lo_tmap_host : whi;
     cudaStream_t s = (cudaStream_t)stream;
@@ -363,7 +406,7 @@ extern "C" int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_p
             if (e != cudaSuccess) return (int)e;
             attr3 = true;
         }
-        linear_planes_kernel<3><<<grid, kThreads, smem, s>>>(*ahi, *alo, *whi, *wlo, p);
+        linear_planes_kernel<3><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p);
     } else {
         static bool attr1 = false;
         if (!attr1) {
@@ -371,7 +414,7 @@ extern "C" int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_p
             if (e != cudaSuccess) return (int)e;
             attr1 = true;
         }
-        linear_planes_kernel<1><<<grid, kThreads, smem, s>>>(*ahi, *alo, *whi, *wlo, p);
+        linear_planes_kernel<1><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p);
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;

@@ -12,7 +12,8 @@ import torch
 
 from . import modules as M
 from . import native, ops
-from .nn import MLP, Draws, ForwardCache, cat_features, get_precision, set_precision, set_weights_epoch
+from .nn import (MLP, Draws, ForwardCache, cat_features, gemm_input, get_precision, set_precision,
+                 set_weights_epoch)
 
 _DOWN_STEPS = ("sa", "sa-geo", "sa-global", "pt-transition-down")
 
@@ -227,4 +228,4 @@ class ModelBase(torch.nn.Module):
             feat = cat_features([feat, cat_feat], [None, batch0])
         if isinstance(self.mlp, torch.nn.Identity):
             return feat
-        return self.mlp(feat)
+        return self.mlp(gemm_input(feat, kwargs["cache"]))

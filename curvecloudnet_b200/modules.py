@@ -13,14 +13,15 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .nn import DEFAULT_DRAWS, MLP, Draws, PreparedLinear, cat_features, fold_batchnorm, get_cache, n_planes
+from .nn import (DEFAULT_DRAWS, MLP, Draws, PreparedLinear, cat_features, fold_batchnorm, gemm_input, get_cache,
+                 mlp_to_features, n_planes)
 
 
-def _cat_xyz(x, pos, with_xyz):
+def _cat_xyz(x, pos, with_xyz, cache=None):
     """cat[x, pos] as the input of a Linear (activation planes on the tensor-core modes)."""
     if not with_xyz:
-        return x
-    return pos if x is None else cat_features([x, pos])
+        return gemm_input(x, cache)
+    return gemm_input(pos, cache) if x is None else cat_features([x, pos], cache=cache)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -150,7 +151,8 @@ class PointNetConv2(nn.Module):
         self.aggr_type, self.normalize_radius = aggr_type, normalize_radius
         self._dec, self._dec_src = None, None
 
-    def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR):
+    def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR, cache=None):
+        x_src = gemm_input(x_src, cache)
         layers = self.local_nn.layers()
         l0 = layers[0]
         cx = 0 if x_src is None else x_src.shape[1]
@@ -223,7 +225,7 @@ class SAModule(nn.Module):
         else:
             nbr, cnt = ops.ball_query(posq, batchq, pos, sptr, self.r, 128)
         edges = ops.dense_to_csr(nbr, cnt)
-        out = self.conv.forward_edges(x, pos, posq, edges)
+        out = self.conv.forward_edges(x, pos, posq, edges, cache)
         return out, posq, batchq, curveq
 
 
@@ -253,21 +255,21 @@ class GlobalSAModule(nn.Module):
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
         sptr = get_cache(kwargs).sample_ptr(batch)
-        h = self.nn(cat_features([x, pos]))
+        h = self.nn(cat_features([x, pos], cache=get_cache(kwargs)))
         out = ops.seg_aggregate(h, None, sptr.dev, sptr.n_samples, self.pooling)
         first = torch.tensor(sptr.host[:-1], dtype=torch.int64).to(pos.device)
         _, posf, batchf, curvef = _subset(None, pos, batch, point2curveidx, first)
         return out, posf, batchf, curvef
 
 
-def _fp_concat(x, x_skip, pos_skip, with_xyz):
+def _fp_concat(x, x_skip, pos_skip, with_xyz, cache=None):
     """pointnet2.py:132-139 / :194-201."""
     parts = [x]
     if x_skip is not None:
         parts.append(x_skip)
     if with_xyz:
         parts.append(pos_skip[:, :3])
-    return cat_features(parts) if len(parts) > 1 else x
+    return cat_features(parts, cache=cache) if len(parts) > 1 else gemm_input(x, cache)
 
 
 class FPModule(nn.Module):
@@ -279,10 +281,11 @@ class FPModule(nn.Module):
 
     def forward(self, x, pos, batch, x_skip, pos_skip, batch_skip, point2curveidx=None,
                 point2curveidx_skip=None, **kwargs):
-        sptr = get_cache(kwargs).sample_ptr(batch)
+        cache = get_cache(kwargs)
+        sptr = cache.sample_ptr(batch)
         nbr, d2 = ops.knn_exact(pos_skip, batch_skip, pos, sptr, self.k, zero_fill=True, want_d2=True)
         y = ops.interp_blend(x, nbr, d2, from_d2=True)
-        y = self.nn(_fp_concat(y, x_skip, pos_skip, self.with_xyz))
+        y = mlp_to_features(self.nn, _fp_concat(y, x_skip, pos_skip, self.with_xyz, cache), cache)
         return y, pos_skip, batch_skip, point2curveidx_skip
 
 
@@ -302,7 +305,7 @@ class CurveSAModule(nn.Module):
     def forward(self, x, pos, batch, point2curveidx, draws: Draws = DEFAULT_DRAWS, **kwargs):
         cache = get_cache(kwargs)
         topo = cache.topology(batch, point2curveidx)
-        x = _cat_xyz(x, pos, self.with_xyz)
+        x = _cat_xyz(x, pos, self.with_xyz, cache)
         if self.use_curve_fps:
             idx, sptr_q = ops.curve_fps(pos, topo, self.curve_fps_arclen, draws.curve_phase())
         else:
@@ -310,7 +313,7 @@ class CurveSAModule(nn.Module):
         edges = ops.radius_1d_group(pos, topo, idx, self.r)
         _, posq, batchq, curveq = _subset(None, pos, batch, point2curveidx, idx)
         cache.put_sample_ptr(batchq, sptr_q)
-        out = self.conv.forward_edges(x, pos, posq, edges)
+        out = self.conv.forward_edges(x, pos, posq, edges, cache)
         return out, posq, batchq, curveq, None, idx
 
 
@@ -318,10 +321,11 @@ class CurveFPModule(FPModule):
     """pointnet2.py:184-205: interpolation along the curve onto the fine points."""
 
     def forward(self, x, idx, x_skip, pos_skip, batch_skip, point2curveidx_skip=None, **kwargs):
-        topo = get_cache(kwargs).topology(batch_skip, point2curveidx_skip)
+        cache = get_cache(kwargs)
+        topo = cache.topology(batch_skip, point2curveidx_skip)
         nbr, wgt = ops.knn_1d_superset(pos_skip, topo.curve_ord, idx, self.k)
         y = ops.interp_blend(x, nbr, wgt, from_d2=False)
-        y = self.nn(_fp_concat(y, x_skip, pos_skip, self.with_xyz))
+        y = mlp_to_features(self.nn, _fp_concat(y, x_skip, pos_skip, self.with_xyz, cache), cache)
         return y, pos_skip, batch_skip, point2curveidx_skip
 
 
@@ -364,7 +368,7 @@ class SGCNNLayer(nn.Module):
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
         cache = get_cache(kwargs)
         sptr = cache.sample_ptr(batch)
-        x = _cat_xyz(x, pos, self.with_xyz)
+        x = _cat_xyz(x, pos, self.with_xyz, cache)
         lin_pq, act0, slope0 = self._decomposed()
         PQ = lin_pq(x)
         if not self.use_sparse_feat_agg:
@@ -407,7 +411,8 @@ class SharedMLP(nn.Module):
         self.with_xyz = with_xyz
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
-        return self.mlp(_cat_xyz(x, pos, self.with_xyz)), pos, batch, point2curveidx
+        cache = kwargs.get("cache")
+        return mlp_to_features(self.mlp, _cat_xyz(x, pos, self.with_xyz, cache), cache), pos, batch, point2curveidx
 
 
 class SkipConnect(nn.Module):
@@ -418,4 +423,5 @@ class SkipConnect(nn.Module):
         self.num_skips, self.nn = num_skips, nn
 
     def forward(self, xs, pos, batch, point2curveidx=None, **kwargs):
-        return self.nn(cat_features(list(xs))), pos, batch, point2curveidx
+        cache = kwargs.get("cache")
+        return mlp_to_features(self.nn, cat_features(list(xs), cache=cache), cache), pos, batch, point2curveidx

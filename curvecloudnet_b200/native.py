@@ -75,8 +75,9 @@ _prof_shapes = []          # (M, N, K) of every timed Linear call (tools/profile
 _prof_events = []          # (name, start event, end event, algorithmic work of the call)
 
 # algorithmic work of one call: FLOPs for the Linear kernels (2 M N K)
-_MNK = {"ccn_linear_f32": (7, 8, 9), "ccn_linear_tc": (7, 8, 9), "ccn_linear_planes": (11, 12, 13)}
-_WORK = {name: (lambda a, ix=ix: 2.0 * a[ix[0]] * a[ix[1]] * a[ix[2]]) for name, ix in _MNK.items()}
+_MNK = {"ccn_linear_f32": lambda a: (a[7], a[8], a[9]), "ccn_linear_tc": lambda a: (a[7], a[8], a[9]),
+        "ccn_linear_planes": lambda a: (a[24], a[25], a[3] + a[7] + a[11] + a[15])}
+_WORK = {name: (lambda a, f=f: 2.0 * f(a)[0] * f(a)[1] * f(a)[2]) for name, f in _MNK.items()}
 
 
 def profile_begin(names, pad_cycles=0):
@@ -161,8 +162,7 @@ def _timed_call(name, fn, conv, args):
     e1.record()
     _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
     if name in _WORK:
-        ix = _MNK[name]
-        _prof_shapes.append((args[ix[0]], args[ix[1]], args[ix[2]]))
+        _prof_shapes.append(_MNK[name](args))
     if rc != 0:
         _raise(name, rc)
 

@@ -47,6 +47,20 @@ class ForwardCache:
         self._topo = {}
         self.grids = {}     # (pos2 ptr, n2, radius) -> hashed grid          (ops.frnn_knn)
         self.knn = {}       # (pos1 ptr, pos2 ptr, n1, n2, K, radius) -> idx  (ops.frnn_knn)
+        self.planes = {}    # (ptr, rows, cols, ld) -> activation planes of an fp32 matrix
+
+    def planes_for(self, t: torch.Tensor, npl: int) -> "ops.Planes":
+        """Activation planes of an fp32 feature/position matrix: registered by the kernel that produced it
+        (put_planes) or packed here, once per forward."""
+        key = (t.data_ptr(), t.shape[0], t.shape[1], t.stride(0))
+        hit = self.planes.get(key)
+        if hit is None:
+            hit = (ops.pack_planes([t], npl), t)             # keep the tensor alive: data_ptr stays unique
+            self.planes[key] = hit
+        return hit[0]
+
+    def put_planes(self, t: torch.Tensor, pl: "ops.Planes"):
+        self.planes[(t.data_ptr(), t.shape[0], t.shape[1], t.stride(0))] = (pl, t)
 
     def sample_ptr(self, batch: torch.Tensor) -> ops.SamplePtr:
         key = (batch.data_ptr(), batch.shape[0])
@@ -133,15 +147,37 @@ def n_planes() -> int:
     return {"fp32": 0, "bf16x3": 2, "bf16": 1}[_PRECISION["mode"]]
 
 
-def cat_features(parts, idxs=None):
-    """torch.cat(parts, dim=1) (block k row-gathered by idxs[k]) as the input of an MLP: activation planes on the
-    tensor-core modes (one pack kernel, no fp32 concat buffer), an fp32 matrix in fp32 mode."""
+def cat_features(parts, idxs=None, cache=None):
+    """torch.cat(parts, dim=1) (block k row-gathered by idxs[k]) as the input of an MLP.
+    Tensor-core modes: with a ForwardCache every block becomes its own K-segment of the Linear kernel (the planes of
+    a tensor are made once per forward - by its producer when that is one of our kernels - and the concatenation
+    is never materialised); without a cache one pack kernel writes the concatenated planes.  fp32 mode: an fp32 matrix."""
     npl = n_planes()
     if npl:
+        if cache is not None and idxs is None and len(parts) <= 4:
+            return ops.PlanesCat([cache.planes_for(p, npl) for p in parts])
         return ops.pack_planes(parts, npl, idxs)
     if idxs is not None:
         parts = [p if ix is None else ops.gather_rows(p, ix) for p, ix in zip(parts, idxs)]
     return ops.concat_cols(list(parts)) if len(parts) > 1 else parts[0]
+
+
+def gemm_input(x, cache=None):
+    """An fp32 feature matrix as the A operand of a Linear: its (cached) activation planes on the tensor-core modes."""
+    npl = n_planes()
+    if npl and cache is not None and torch.is_tensor(x):
+        return cache.planes_for(x, npl)
+    return x
+
+
+def mlp_to_features(mlp, inp, cache=None):
+    """Run an MLP whose result is a step output (consumed by later concatenations / Linears): on the tensor-core
+    modes the last layer writes the fp32 matrix AND its activation planes, which are registered in the cache."""
+    if n_planes() and cache is not None:
+        y, yp = mlp(inp, out="both")
+        cache.put_planes(y, yp)
+        return y
+    return mlp(inp)
 
 
 class PreparedLinear:
@@ -161,10 +197,14 @@ class PreparedLinear:
     def in_features(self):
         return self.w.shape[1]
 
-    def tc(self):
+    def tc(self, widths=None):
+        """bf16 weight copies + TMA descriptors, per K-segmentation of the input (None = one block)."""
         if self._tc is None:
-            self._tc = ops.prepare_tc_weight(self.w)
-        return self._tc
+            self._tc = {}
+        tw = self._tc.get(widths)
+        if tw is None:
+            tw = self._tc[widths] = ops.prepare_tc_weight(self.w, widths)
+        return tw
 
     def __call__(self, x, out: str = "f32"):
         """x: fp32 (M, K) tensor or ops.Planes.  out: "f32" | "planes" | "both" (planes only on the tensor-core modes)."""
@@ -172,7 +212,11 @@ class PreparedLinear:
         if mode == "fp32":
             assert out == "f32" and torch.is_tensor(x)
             return ops.linear(x, self.w, self.b, self.act, self.slope)
-        if torch.is_tensor(x):
+        if x.__class__ is ops.PlanesCat:
+            if len(x.segs) > 1:
+                return ops.linear_planes(x, self.tc(x.widths), self.b, self.act, self.slope, out)
+            x = x.segs[0]
+        elif torch.is_tensor(x):
             x = ops.pack_planes([x], n_planes())
         return ops.linear_planes(x, self.tc(), self.b, self.act, self.slope, out)
 

@@ -386,7 +386,7 @@ def edge_layer1(H: Optional[torch.Tensor], wp: torch.Tensor, bias: Optional[torc
         H, ldh = _rows(H)
     else:
         ldh = 0
-    if n_planes and c % 8 == 0 and (H is None or ldh % 4 == 0):
+    if n_planes and c % 16 == 0 and (H is None or ldh % 4 == 0):
         out = alloc_planes(edges.n_edges, c, n_planes, wp)
         call("ccn_edge_layer1_planes", H if H is not None else 0, ldh, wp, bias if bias is not None else 0, _f32(pos_src),
              _f32(pos_dst), edges.erow, edges.ecol, edges.n_edges, c, float(normalize_radius or 0.0), act, float(slope),
@@ -402,7 +402,7 @@ def edge_layer1(H: Optional[torch.Tensor], wp: torch.Tensor, bias: Optional[torc
 def edge_pair_layer1(PQ: torch.Tensor, edges: EdgeCSR, act: int, slope: float = 0.01, n_planes: int = 0):
     PQ, ld = _rows(PQ)
     c = PQ.shape[1] // 2
-    if n_planes and c % 8 == 0 and ld % 4 == 0:
+    if n_planes and c % 16 == 0 and ld % 4 == 0:
         out = alloc_planes(edges.n_edges, c, n_planes, PQ)
         call("ccn_edge_pair_layer1_planes", PQ, ld, edges.erow, edges.ecol, edges.n_edges, c, act, float(slope), out.buf,
              out.kpad, out.plane_stride, n_planes)
@@ -428,7 +428,7 @@ def sgcnn_layer1(PQ: torch.Tensor, idx: torch.Tensor, act: int, slope: float = 0
     PQ, ld = _rows(PQ)
     n, K = idx.shape
     c = PQ.shape[1] // 2
-    if n_planes and c % 8 == 0 and ld % 4 == 0:
+    if n_planes and c % 16 == 0 and ld % 4 == 0:
         out = alloc_planes(n * (K + 1), c, n_planes, PQ)
         call("ccn_sgcnn_layer1_planes", PQ, ld, idx, n, K, c, act, float(slope), out.buf, out.kpad, out.plane_stride,
              n_planes)
@@ -471,7 +471,23 @@ class TcWeight:
     """bf16 hi/lo copies of a folded fp32 weight (N, K), K padded to 64, and their host-side TMA descriptors
     (one pair per N-tile width)."""
 
-    def __init__(self, w: torch.Tensor):
+    def __init__(self, w: torch.Tensor, seg_widths=None):
+        """seg_widths: the K axis is a concatenation of blocks of these widths; every block's columns are placed at
+        a multiple of 64 (zero columns in between) so that each block can be its own TMA source (ccn_linear_planes)."""
+        if seg_widths is not None and len(seg_widths) > 1:
+            assert sum(seg_widths) == w.shape[1]
+            offs, tot = [], 0
+            for kw in seg_widths:
+                offs.append(tot)
+                tot += (kw + 63) // 64 * 64
+            wide = torch.zeros((w.shape[0], tot), dtype=torch.float32, device=w.device)   # weight preparation
+            c0 = 0
+            for kw, off in zip(seg_widths, offs):
+                wide[:, off:off + kw] = w[:, c0:c0 + kw]
+                c0 += kw
+            self.k_true, w = w.shape[1], wide
+        else:
+            self.k_true = w.shape[1]
         w, ldw = _rows(w)
         n, k = w.shape
         self.n, self.k = n, k
@@ -562,7 +578,7 @@ class Planes:
 
 
 def alloc_planes(m: int, k: int, n_planes: int, like: torch.Tensor) -> Planes:
-    kpad = (k + 7) // 8 * 8
+    kpad = (k + 15) // 16 * 16        # 32-byte rows: the Linear epilogue writes whole sectors
     return Planes(torch.empty((n_planes, max(m, 1), kpad), dtype=torch.bfloat16, device=like.device), m, k)
 
 
@@ -585,23 +601,51 @@ def pack_planes(parts, n_planes: int, idxs=None) -> Planes:
     return out
 
 
-def linear_planes(A: Planes, tw: "TcWeight", bias: Optional[torch.Tensor], act: int, slope: float, out: str = "f32"):
-    """Y = act(A W^T + bias) with both operands by TMA.  out: "f32" -> tensor, "planes" -> Planes, "both" -> (tensor, Planes)."""
+class PlanesCat:
+    """[A_0 | A_1 | ...]: a column concatenation of activation planes that is never materialised - every block is
+    its own K-segment (TMA source) of ccn_linear_planes."""
+
+    def __init__(self, segs):
+        assert 1 <= len(segs) <= 4 and all(s.m == segs[0].m and s.n_planes == segs[0].n_planes for s in segs)
+        self.segs = list(segs)
+        self.m, self.k, self.n_planes = segs[0].m, sum(s.k for s in segs), segs[0].n_planes
+
+    @property
+    def shape(self):
+        return (self.m, self.k)
+
+    @property
+    def widths(self):
+        return tuple(s.k for s in self.segs)
+
+    def to_f32(self):
+        return torch.cat([s.to_f32() for s in self.segs], dim=1)
+
+
+def linear_planes(A, tw: "TcWeight", bias: Optional[torch.Tensor], act: int, slope: float, out: str = "f32"):
+    """Y = act(A W^T + bias) with both operands by TMA; A: Planes or PlanesCat (tw prepared for the same widths).
+    out: "f32" -> tensor, "planes" -> Planes, "both" -> (tensor, Planes)."""
+    segs = A.segs if isinstance(A, PlanesCat) else (A,)
     M, K = A.shape
-    assert K == tw.k, (A.shape, tw.k)
-    mode = 3 if A.n_planes == 2 else 1
-    Y = _empty((M, tw.n), torch.float32, A.buf) if out in ("f32", "both") else None
-    Yp = alloc_planes(M, tw.n, A.n_planes, A.buf) if out in ("planes", "both") else None
-    box = tw.pick_box_planes(M, A.n_planes)
+    assert K == tw.k_true, (A.shape, tw.k_true)
+    npl = A.n_planes
+    dev = segs[0].buf
+    Y = _empty((M, tw.n), torch.float32, dev) if out != "planes" else None
+    Yp = alloc_planes(M, tw.n, npl, dev) if out != "f32" else None
+    box = tw.pick_box_planes(M, npl)
     w_hi, w_lo, _ = tw.maps(box)
-    call("ccn_linear_planes", A.buf, A.kpad, A.plane_stride, w_hi, w_lo, bias if bias is not None else 0, Y if Y is not None else 0, tw.n,
-         Yp.buf if Yp is not None else 0, Yp.kpad if Yp is not None else 0, Yp.plane_stride if Yp is not None else 0,
-         M, tw.n, K, box, mode, act, float(slope))
+    a = []
+    for sg in segs:
+        a += [sg.buf, sg.kpad, sg.buf.stride(0), sg.k]
+    a += [0, 0, 0, 0] * (4 - len(segs))
+    call("ccn_linear_planes", *a, w_hi, w_lo, bias if bias is not None else 0, Y if Y is not None else 0, tw.n,
+         Yp.buf if Yp is not None else 0, Yp.kpad if Yp is not None else 0, Yp.buf.stride(0) if Yp is not None else 0,
+         M, tw.n, box, 3 if npl == 2 else 1, act, float(slope))
     return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)
 
 
-def prepare_tc_weight(w: torch.Tensor) -> TcWeight:
-    return TcWeight(w)
+def prepare_tc_weight(w: torch.Tensor, seg_widths=None) -> TcWeight:
+    return TcWeight(w, seg_widths)
 
 
 def linear_tc(A: torch.Tensor, tw: TcWeight, bias: Optional[torch.Tensor], act: int, slope: float, mode: int):

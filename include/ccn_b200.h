@@ -189,21 +189,25 @@ int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_host, const
                   int32_t act, float slope, ccn_stream_t stream);
 
 /* Tensor-core path with BOTH operands by TMA.  Activations travel between layers as "split-bf16 planes":
- * (planes, M, kpad) bf16, plane 0 = bf16(x), plane 1 = bf16(x - plane 0) (mode 3 only), kpad % 8 == 0, pad columns 0.
+ * (planes, M, kpad) bf16, plane 0 = bf16(x), plane 1 = bf16(x - plane 0) (mode 3 only), kpad % 8 == 0 (% 16 for
+ * planes written by ccn_linear_planes), pad columns 0.
  *   ccn_pack_planes    up to four fp32 column blocks (block k optionally row-gathered through idx_k) -> planes:
  *                      replaces torch.cat / x[idx] in front of an MLP (pointnet2.py:132-139,160-163; skip_connect.py:13;
  *                      mlp.py:18-20; dgcnn.py:163-164);
- *   ccn_linear_planes  Y = act(A W^T + bias): A = device planes (row stride a_ld, second plane a_plane_stride elements
- *                      further), W (ccn_split_bf16 layout) through host-encoded tensor maps (ccn_weight_tensor_map);
- *                      writes fp32 Y and/or output planes. */
+ *   ccn_linear_planes  Y = act([A_0 | A_1 | A_2 | A_3] W^T + bias): up to four K-segments, each its own planes tensor
+ *                      (a_i, row stride ld_i, second plane ps_i elements further, k_i columns; k_i = 0 ends the list), so
+ *                      a concatenation in front of a Linear (skip_connect.py:13, pointnet2.py:132-139) costs nothing;
+ *                      W in the ccn_split_bf16 layout with every segment's columns starting at a multiple of 64,
+ *                      through host-encoded tensor maps (ccn_weight_tensor_map); writes fp32 Y and/or output planes. */
 int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const int64_t* i0, const float* s1, int64_t ld1,
                     int32_t c1, const int64_t* i1, const float* s2, int64_t ld2, int32_t c2, const int64_t* i2,
                     const float* s3, int64_t ld3, int32_t c3, const int64_t* i3, int64_t n, void* planes, int64_t kpad,
                     int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
-int ccn_linear_planes(const void* a_planes, int64_t a_ld, int64_t a_plane_stride, const void* w_hi_tmap_host,
-                      const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
-                      int64_t yp_plane_stride, int64_t M, int32_t N, int32_t K, int32_t box_n, int32_t mode, int32_t act,
-                      float slope, ccn_stream_t stream);
+int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, const void* a1, int64_t ld1, int64_t ps1,
+                      int32_t k1, const void* a2, int64_t ld2, int64_t ps2, int32_t k2, const void* a3, int64_t ld3,
+                      int64_t ps3, int32_t k3, const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias,
+                      float* Y, int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
+                      int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream);
 
 /* Planes-output variants of the per-edge first layers (the consumer is the next Linear of the edge MLP); c % 8 == 0,
  * kpad == c, fp32 inputs 16-byte aligned with leading dimensions % 4 == 0. */

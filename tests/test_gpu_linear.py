@@ -36,7 +36,7 @@ def test_linear_planes_matches_float64(shape, mode):
         tol = 3e-5 if mode == "bf16x3" else 2e-2
         lin = cnn.PreparedLinear(w, b, act=2, slope=0.01)
         xp = ops.pack_planes([x], npl)
-        assert xp.buf.shape == (npl, M, (K + 7) // 8 * 8)
+        assert xp.buf.shape == (npl, M, (K + 15) // 16 * 16)
         assert float(xp.buf[:, :, K:].float().abs().max() if xp.kpad > K else 0.0) == 0.0
         back = xp.to_f32()
         assert float((back - x).abs().max() / x.abs().max()) <= (2e-5 if npl == 2 else 8e-3)
@@ -72,3 +72,33 @@ def test_pack_concat_and_gather():
     sel = torch.randint(0, 1000, (321,), generator=g).cuda()
     pl = ops.pack_planes([a, b], 1, [sel, sel])
     assert float((pl.to_f32() - torch.cat([a, b], 1)[sel]).abs().max()) <= 8e-3 * float(a.abs().max())
+
+
+@pytest.mark.parametrize("mode", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("widths", [(64, 3), (256, 256, 3), (1024, 1024, 1024), (32, 3), (64, 32, 3), (100, 7, 129, 3)])
+def test_linear_over_concatenated_segments(widths, mode):
+    """[A_0 | A_1 | ...] W^T with every block its own TMA source == Linear over the materialised concatenation."""
+    from curvecloudnet_b200 import nn as cnn, ops
+    M, N = 3000, 192
+    g = torch.Generator().manual_seed(sum(widths))
+    parts = [torch.randn(M, k, generator=g).cuda() for k in widths]
+    K = sum(widths)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).cuda()
+    b = torch.randn(N, generator=g).cuda()
+    prev = cnn.get_precision()
+    cnn.set_precision(mode)
+    try:
+        cache = cnn.ForwardCache()
+        lin = cnn.PreparedLinear(w, b, act=1)
+        a = cnn.cat_features(parts, cache=cache)
+        assert isinstance(a, ops.PlanesCat) and a.shape == (M, K)
+        y = lin(a)
+        want = _ref(torch.cat(parts, 1), w, b, 1)
+        tol = 3e-5 if mode == "bf16x3" else 2e-2
+        assert float((y.double() - want).abs().max() / want.abs().max()) <= tol
+        y2 = lin(torch.cat(parts, 1))                 # packed single-block path
+        assert float((y2 - y).abs().max() / want.abs().max()) <= (1e-6 if mode == "bf16x3" else 1e-6)
+        # planes are made once per tensor and forward
+        assert cnn.cat_features(parts, cache=cache).segs[0] is a.segs[0]
+    finally:
+        cnn.set_precision(prev)
