@@ -94,9 +94,9 @@ __global__ void seg_aggregate_kernel(const float* __restrict__ msg, int64_t ldm,
                 r = msg[(int64_t)b * ldm + k];
                 for (int j = b + 1; j < e; ++j) r = fmaxf(r, msg[(int64_t)j * ldm + k]);
             }
-        } else if (mode == CCN_AGG_MEAN) {
+        } else if (mode == CCN_AGG_MEAN || mode == CCN_AGG_SUM) {
             for (int j = b; j < e; ++j) r += msg[(int64_t)j * ldm + k];
-            r = r / fmaxf((float)(e - b), 1.f);
+            if (mode == CCN_AGG_MEAN) r = r / fmaxf((float)(e - b), 1.f);
         } else if (mode == CCN_AGG_WSUM) {
             for (int j = b; j < e; ++j) {
                 const float a = att[(int64_t)j * lda + k];
@@ -349,8 +349,8 @@ extern "C" int ccn_edge_pair_layer1(const float* PQ, int64_t ldpq, const int32_t
 
 extern "C" int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
                                  int64_t nq, int32_t c, int32_t mode, float* out, int64_t ldo, ccn_stream_t stream) {
-    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 3);
-    CCN_REQUIRE(mode < 2 || att);
+    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 4);
+    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || att);
     if (nq == 0) return CCN_OK;
     seg_aggregate_kernel<<<CCN_ELT_GRID(nq * c), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq, c,
                                                                                  mode, out, ldo);

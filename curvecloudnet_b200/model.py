@@ -225,7 +225,13 @@ class ModelBase(torch.nn.Module):
             onehot = torch.zeros((cats.shape[0], 16), dtype=torch.float32, device=feat.device)
             onehot[torch.arange(cats.shape[0], device=feat.device), cats] = 1.0   # input encoding (B x 16)
             cat_feat = self.lin_categorical(onehot)
-            feat = cat_features([feat, cat_feat], [None, batch0])
+            if self.training:
+                from . import autograd as A
+                feat = A.concat([feat, A.gather_rows(cat_feat, batch0)])
+            else:
+                feat = cat_features([feat, cat_feat], [None, batch0])
         if isinstance(self.mlp, torch.nn.Identity):
             return feat
+        if self.training:
+            return self.mlp(feat)
         return self.mlp(gemm_input(feat, kwargs["cache"]))

@@ -3,7 +3,9 @@ parameter names (reference src/models/modules/{fast_conv1d,pointnet2,point_conv,
 so `ModelBase` configs and checkpoints drop in.  Bodies call the sm_100a kernels through `ops`;
 there is no torch arithmetic on the per-scan path.
 
-Inference (eval) path only in this round: BatchNorm uses running statistics folded into the weights.
+`module.eval()`: the inference path - BatchNorm running statistics folded into the weights, activations as bf16 planes.
+`module.train()`: every forward dispatches to train_steps.py (batch-statistics BatchNorm, differentiable ops with
+hand-written backward kernels, autograd.py).
 """
 from __future__ import annotations
 
@@ -13,6 +15,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from . import train_steps as T
 from .nn import (DEFAULT_DRAWS, MLP, Draws, PreparedLinear, cat_features, fold_batchnorm, gemm_input, get_cache,
                  mlp_to_features, n_planes)
 
@@ -92,6 +95,8 @@ class SymmetricCurve1DConvV2(_CurveConvBase):
         super().__init__(feat_dims, kernel_size, bias, with_xyz, with_diff, diff_every_layer=False)
 
     def forward(self, x, pos, batch, point2curveidx, **kwargs):
+        if self.training:
+            return T.curve_conv_v2(self, x, pos, batch, point2curveidx, **kwargs)
         topo = get_cache(kwargs).topology(batch, point2curveidx)
         n = pos.shape[0]
         feats = ops.curve_feat_prep(x, pos, self.with_xyz, self.with_diff, topo.curve_ord)
@@ -116,6 +121,8 @@ class SymmetricCurve1DConvFastV1(_CurveConvBase):
         super().__init__(feat_dims, kernel_size, bias, with_xyz, with_diff, diff_every_layer=True)
 
     def forward(self, x, pos, batch, point2curveidx, **kwargs):
+        if self.training:
+            return T.curve_conv_v1(self, x, pos, batch, point2curveidx, **kwargs)
         topo = get_cache(kwargs).topology(batch, point2curveidx)
         n = pos.shape[0]
         k = self.kernel_size
@@ -152,6 +159,8 @@ class PointNetConv2(nn.Module):
         self._dec, self._dec_src = None, None
 
     def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR, cache=None):
+        if self.training:
+            return T.pointnet_conv(self, x_src, pos_src, pos_dst, edges)
         x_src = gemm_input(x_src, cache)
         layers = self.local_nn.layers()
         l0 = layers[0]
@@ -203,6 +212,8 @@ class SAModule(nn.Module):
                                   normalize_radius=self.normalize_radius)
 
     def forward(self, x, pos, batch, point2curveidx=None, draws: Draws = DEFAULT_DRAWS, **kwargs):
+        if self.training:
+            return T.sa_module(self, x, pos, batch, point2curveidx, draws=draws, **kwargs)
         cache = get_cache(kwargs)
         sptr = cache.sample_ptr(batch)
         n = pos.shape[0]
@@ -254,6 +265,8 @@ class GlobalSAModule(nn.Module):
             raise NotImplementedError(self.pooling)
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        if self.training:
+            return T.global_sa_module(self, x, pos, batch, point2curveidx, **kwargs)
         sptr = get_cache(kwargs).sample_ptr(batch)
         h = self.nn(cat_features([x, pos], cache=get_cache(kwargs)))
         out = ops.seg_aggregate(h, None, sptr.dev, sptr.n_samples, self.pooling)
@@ -281,6 +294,9 @@ class FPModule(nn.Module):
 
     def forward(self, x, pos, batch, x_skip, pos_skip, batch_skip, point2curveidx=None,
                 point2curveidx_skip=None, **kwargs):
+        if self.training:
+            return T.fp_module(self, x, pos, batch, x_skip, pos_skip, batch_skip, point2curveidx,
+                               point2curveidx_skip, **kwargs)
         cache = get_cache(kwargs)
         sptr = cache.sample_ptr(batch)
         nbr, d2 = ops.knn_exact(pos_skip, batch_skip, pos, sptr, self.k, zero_fill=True, want_d2=True)
@@ -303,6 +319,8 @@ class CurveSAModule(nn.Module):
                                   attend_nn=attend_nn, normalize_radius=self.normalize_radius)
 
     def forward(self, x, pos, batch, point2curveidx, draws: Draws = DEFAULT_DRAWS, **kwargs):
+        if self.training:
+            return T.curve_sa_module(self, x, pos, batch, point2curveidx, draws=draws, **kwargs)
         cache = get_cache(kwargs)
         topo = cache.topology(batch, point2curveidx)
         x = _cat_xyz(x, pos, self.with_xyz, cache)
@@ -321,6 +339,8 @@ class CurveFPModule(FPModule):
     """pointnet2.py:184-205: interpolation along the curve onto the fine points."""
 
     def forward(self, x, idx, x_skip, pos_skip, batch_skip, point2curveidx_skip=None, **kwargs):
+        if self.training:
+            return T.curve_fp_module(self, x, idx, x_skip, pos_skip, batch_skip, point2curveidx_skip, **kwargs)
         cache = get_cache(kwargs)
         topo = cache.topology(batch_skip, point2curveidx_skip)
         nbr, wgt = ops.knn_1d_superset(pos_skip, topo.curve_ord, idx, self.k)
@@ -366,6 +386,8 @@ class SGCNNLayer(nn.Module):
         return self._dec
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        if self.training:
+            return T.sgcnn_layer(self, x, pos, batch, point2curveidx, **kwargs)
         cache = get_cache(kwargs)
         sptr = cache.sample_ptr(batch)
         x = _cat_xyz(x, pos, self.with_xyz, cache)
@@ -411,6 +433,8 @@ class SharedMLP(nn.Module):
         self.with_xyz = with_xyz
 
     def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        if self.training:
+            return T.shared_mlp(self, x, pos, batch, point2curveidx, **kwargs)
         cache = kwargs.get("cache")
         return mlp_to_features(self.mlp, _cat_xyz(x, pos, self.with_xyz, cache), cache), pos, batch, point2curveidx
 
@@ -423,5 +447,7 @@ class SkipConnect(nn.Module):
         self.num_skips, self.nn = num_skips, nn
 
     def forward(self, xs, pos, batch, point2curveidx=None, **kwargs):
+        if self.training:
+            return T.skip_connect(self, xs, pos, batch, point2curveidx, **kwargs)
         cache = kwargs.get("cache")
         return mlp_to_features(self.nn, cat_features(list(xs), cache=cache), cache), pos, batch, point2curveidx

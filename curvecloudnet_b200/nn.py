@@ -289,8 +289,7 @@ class MLP(torch.nn.Module):
     def layers(self):
         """[PreparedLinear] with BatchNorm(eval) folded; cached until a parameter changes."""
         if self.training:
-            raise NotImplementedError(
-                "curvecloudnet_b200 round 1 implements the inference (eval) path; call model.eval()")
+            raise RuntimeError("MLP.layers() is the folded inference form; training goes through autograd.mlp_train")
         epoch = _EPOCH[0]
         if epoch is not None and self._folded is not None and self._folded_epoch == epoch:
             return self._folded
@@ -310,6 +309,9 @@ class MLP(torch.nn.Module):
         return self._folded
 
     def forward(self, x, *args, out: str = "f32", **kwargs):
+        if self.training:
+            from . import autograd as A
+            return A.mlp_train(self, x)
         return self.forward_from(x, 0, out)
 
     def forward_from(self, x, first: int, out: str = "f32"):

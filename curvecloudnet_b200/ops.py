@@ -16,7 +16,7 @@ from . import native
 from .native import call
 
 ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
-AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3}
+AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3, "sum": 4}
 MAX_SAMPLES = 4096
 TOPO_ERRORS = {1: "batch vector is not sorted", 2: "curve ids are not sorted within a sample",
                4: "more than %d samples in a batch" % MAX_SAMPLES, 8: "batch ids are not 0..B-1"}

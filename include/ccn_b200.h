@@ -44,6 +44,7 @@ typedef struct CUstream_st* ccn_stream_t;
 #define CCN_AGG_MEAN 1
 #define CCN_AGG_WSUM 2   /* sum sigmoid(att) * msg */
 #define CCN_AGG_ATTEND 3 /* sum softmax_target(att) * msg */
+#define CCN_AGG_SUM 4
 
 #define CCN_TOPO_ERR_BATCH_UNSORTED 1
 #define CCN_TOPO_ERR_CURVE_UNSORTED 2
@@ -221,6 +222,62 @@ int ccn_edge_layer1_planes(const float* H, int64_t ldh, const float* wp, const f
                            const float* pos_dst, const int32_t* erow, const int32_t* ecol, int64_t E, int32_t c,
                            float normalize_radius, int32_t act, float slope, void* planes, int64_t kpad,
                            int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Training step: backward of the ops above + train-mode BatchNorm + the loss (csrc/train_ops.cu).  Replaces what
+ * the reference obtains from torch autograd over cuBLAS/cuDNN/torch_scatter/pytorch3d (`loss.backward()` in
+ * src/run/shapenet_seg.py:186-188, nuscenes_seg.py:229-252).  Gradient buffers that are accumulated into
+ * (scatter targets, dW, db) are zero-filled by the CALLER.  fp64 scratch `sums`/`acc` is zero-filled by the callee.
+ * --------------------------------------------------------------------------------------------------------------- */
+/* dst[r] = idx[r] >= 0 ? src[idx[r]] : 0          (pad-row insertion of fast_conv1d.py:48-61; backward of a scatter) */
+int ccn_gather_rows_i32(const float* src, int64_t lds, const int32_t* idx, int64_t n, int32_t c, float* dst,
+                        int64_t ldd, ccn_stream_t stream);
+/* dst[idx[r]] += src[r], idx < 0 skipped           (backward of x[idx] / x[col] gathers) */
+int ccn_scatter_add_rows_i32(const float* src, int64_t lds, const int32_t* idx, int64_t n, int32_t c, float* dst,
+                             int64_t ldd, ccn_stream_t stream);
+int ccn_scatter_add_rows_i64(const float* src, int64_t lds, const int64_t* idx, int64_t n, int32_t c, float* dst,
+                             int64_t ldd, ccn_stream_t stream);
+/* dst[i] (+)= sum_g src[i*G + g]                   (backward of the per-point term of the dense SGCNN first layer) */
+int ccn_group_sum_rows(const float* src, int64_t lds, int64_t n, int32_t G, int32_t c, float* dst, int64_t ldd,
+                       int32_t accumulate, ccn_stream_t stream);
+/* dW (N,K) += dY^T X, db (N) += column sums of dY (db may be NULL)      (backward of torch.nn.Linear) */
+int ccn_linear_wgrad(const float* dY, int64_t lddy, const float* X, int64_t ldx, int64_t M, int32_t N, int32_t K,
+                     float* dW, int64_t lddw, float* db, ccn_stream_t stream);
+/* BatchNorm1d batch statistics: mean, invstd = 1/sqrt(var_biased + eps); running stats updated in place when given */
+int ccn_bn_stats(const float* z, int64_t ldz, int64_t M, int32_t C, float eps, float momentum, double* sums,
+                 float* mean, float* invstd, float* running_mean, float* running_var, ccn_stream_t stream);
+/* y = act(((z - mean) invstd) gamma + beta); gamma == NULL: y = act(z) */
+int ccn_bn_apply(const float* z, int64_t ldz, int64_t M, int32_t C, const float* mean, const float* invstd,
+                 const float* gamma, const float* beta, int32_t act, float slope, float* y, int64_t ldy,
+                 ccn_stream_t stream);
+/* backward of ccn_bn_apply (+ the statistics when batch_stats != 0): dz, dgamma, dbeta */
+int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, int64_t ldz, int64_t M, int32_t C,
+                    const float* mean, const float* invstd, const float* gamma, const float* beta, int32_t act,
+                    float slope, int32_t batch_stats, double* sums, float* dz, int64_t lddz, float* dgamma,
+                    float* dbeta, ccn_stream_t stream);
+int ccn_seg_aggregate_bwd(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
+                          int64_t nq, int32_t c, int32_t mode, const float* dout, int64_t ldo, float* dmsg,
+                          int64_t lddm, float* datt, int64_t ldda, ccn_stream_t stream);
+int ccn_group_max_dense_bwd(const float* feat, int64_t ldf, const int32_t* idx, int64_t n, int32_t K, int32_t c,
+                            const float* dout, int64_t ldo, float* dfeat, int64_t lddf, ccn_stream_t stream);
+int ccn_interp_blend_bwd(const int32_t* nbr, const float* wgt, int32_t from_d2, int64_t n, int32_t knn, int32_t c,
+                         const float* dout, int64_t ldo, float* dx, int64_t lddx, ccn_stream_t stream);
+int ccn_curve_feat_prep_bwd(const float* x, int64_t ldx, int32_t cx, int32_t with_xyz, int32_t with_diff,
+                            const int32_t* curve_ord, int64_t n, const float* dout, int64_t ldo, float* dx,
+                            int64_t lddx, ccn_stream_t stream);
+/* rel (E,3) = (pos_src[ecol] - pos_dst[erow]) / radius (radius == 0: no division)      (point_conv.py:60-69) */
+int ccn_edge_rel_pos(const float* pos_src, const float* pos_dst, const int32_t* erow, const int32_t* ecol, int64_t E,
+                     float normalize_radius, float* rel, ccn_stream_t stream);
+/* loss = sum_i w[y_i] (lse_i - logit[i][y_i]) / sum_i w[y_i] over y_i != ignore; lse (n) and acc (fp64 [2]) are kept
+ * for the backward: dlogits = gscale[0] * w[y] / sum_w * (softmax - onehot) */
+int ccn_nll_loss_fwd(const float* logits, int64_t ld, const int64_t* target, const float* class_weight, int64_t n,
+                     int32_t C, int64_t ignore_index, float* lse, double* acc, float* loss, ccn_stream_t stream);
+int ccn_nll_loss_bwd(const float* logits, int64_t ld, const int64_t* target, const float* class_weight, int64_t n,
+                     int32_t C, int64_t ignore_index, const float* lse, const double* acc, const float* gscale,
+                     float* dlogits, int64_t ldd, ccn_stream_t stream);
+/* y = u >= p ? x / (1 - p) : 0 with caller-supplied uniform draws u (n*c); applied to the gradient it is the backward */
+int ccn_dropout(const float* x, int64_t ldx, const float* u, int64_t n, int32_t c, float p, float* y, int64_t ldy,
+                ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,399 @@
+"""GPU parity of the training step: every differentiable op against plain PyTorch autograd of the same op, and the
+whole model (train mode: BatchNorm batch statistics, loss, every parameter gradient, running statistics) against
+the CPU oracle's autograd on the same inputs, weights and random draws."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from golden_utils import rel_err
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _A():
+    from curvecloudnet_b200 import autograd as A
+    from curvecloudnet_b200 import nn, ops
+    return A, nn, ops
+
+
+def _close(a, b, tol, what):
+    err = rel_err(a.detach().cpu(), b.detach().cpu())
+    assert err <= tol, "%s off by %.3e relative" % (what, err)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-5), ("bf16x3", 1e-4)])
+@pytest.mark.parametrize("M,K,N,bias", [(1000, 35, 64, True), (4097, 128, 192, False), (300, 259, 17, True)])
+def test_linear_grads(precision, tol, M, K, N, bias):
+    A, nn, ops = _A()
+    torch.manual_seed(0)
+    x = torch.randn(M, K, device=DEV, requires_grad=True)
+    w = (torch.randn(N, K, device=DEV) / K ** 0.5).requires_grad_()
+    b = torch.randn(N, device=DEV, requires_grad=True) if bias else None
+    g = torch.randn(M, N, device=DEV)
+    nn.set_precision(precision)
+    try:
+        y = A.linear(x, w, b)
+        y.backward(g)
+    finally:
+        nn.set_precision("fp32")
+    got = (y, x.grad, w.grad, b.grad if bias else None)
+    x2, w2 = x.detach().double().requires_grad_(), w.detach().double().requires_grad_()
+    b2 = b.detach().double().requires_grad_() if bias else None
+    y2 = F.linear(x2, w2, b2)
+    y2.backward(g.double())
+    want = (y2, x2.grad, w2.grad, b2.grad if bias else None)
+    for a, r, name in zip(got, want, ("y", "dx", "dW", "db")):
+        if a is not None:
+            _close(a, r, tol, name)
+
+
+@pytest.mark.parametrize("act", ["relu", "leaky_relu", "none"])
+@pytest.mark.parametrize("M,C", [(777, 64), (5000, 192), (300, 515), (64, 35)])
+def test_bn_act_train_and_eval(act, M, C):
+    A, nn, ops = _A()
+    torch.manual_seed(1)
+    code, slope = {"relu": (ops.ACT_RELU, 0.0), "leaky_relu": (ops.ACT_LEAKY, 0.01), "none": (ops.ACT_NONE, 0.0)}[act]
+    ref_act = {"relu": F.relu, "leaky_relu": lambda t: F.leaky_relu(t, 0.01), "none": lambda t: t}[act]
+    for training in (True, False):
+        z = (torch.randn(M, C, device=DEV) * 2 + 3).requires_grad_()
+        g = torch.randn(M, C, device=DEV)
+        bn = torch.nn.BatchNorm1d(C).to(DEV)
+        ref = torch.nn.BatchNorm1d(C).to(DEV).double()
+        with torch.no_grad():
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-1, 1)
+            bn.running_mean.uniform_(2, 4); bn.running_var.uniform_(3, 5)
+            ref.load_state_dict(bn.state_dict())
+        bn.train(training); ref.train(training)
+        y = A.bn_act(z, bn, code, slope)
+        y.backward(g)
+        z2 = z.detach().double().requires_grad_()
+        y2 = ref_act(ref(z2))
+        y2.backward(g.double())
+        _close(y, y2, 2e-5, "y")
+        _close(z.grad, z2.grad, 5e-5, "dz")
+        _close(bn.weight.grad, ref.weight.grad, 5e-5, "dgamma")
+        _close(bn.bias.grad, ref.bias.grad, 5e-5, "dbeta")
+        _close(bn.running_mean, ref.running_mean, 1e-5, "running_mean")
+        _close(bn.running_var, ref.running_var, 1e-5, "running_var")
+        assert int(bn.num_batches_tracked) == int(ref.num_batches_tracked)
+
+
+def _random_csr(nq, n_src, max_deg, seed):
+    from curvecloudnet_b200 import ops
+    gen = torch.Generator().manual_seed(seed)
+    deg = torch.randint(0, max_deg + 1, (nq,), generator=gen)
+    row_ptr = torch.cat([torch.zeros(1, dtype=torch.int64), deg.cumsum(0)])
+    E = int(row_ptr[-1])
+    erow = torch.repeat_interleave(torch.arange(nq), deg)
+    ecol = torch.randint(0, n_src, (E,), generator=gen)
+    return ops.EdgeCSR(row_ptr.to(torch.int32).to(DEV), erow.to(torch.int32).to(DEV), ecol.to(torch.int32).to(DEV), E, nq)
+
+
+def _ref_seg(msg, att, erow, nq, mode):
+    C = msg.shape[1]
+    idx = erow.long()[:, None].expand(-1, C)
+    if mode == "max":
+        out = torch.zeros(nq, C, dtype=msg.dtype, device=msg.device)
+        return out.scatter_reduce(0, idx, msg, "amax", include_self=False)
+    if mode == "mean":
+        out = torch.zeros(nq, C, dtype=msg.dtype, device=msg.device).scatter_add(0, idx, msg)
+        cnt = torch.bincount(erow.long(), minlength=nq).clamp(min=1)
+        return out / cnt[:, None]
+    if mode == "weighted-sum":
+        return torch.zeros(nq, C, dtype=msg.dtype, device=msg.device).scatter_add(0, idx, msg * torch.sigmoid(att))
+    mx = torch.full((nq, C), -1e30, dtype=msg.dtype, device=msg.device).scatter_reduce(0, idx, att, "amax")
+    ex = torch.exp(att - mx[erow.long()])
+    den = torch.zeros(nq, C, dtype=msg.dtype, device=msg.device).scatter_add(0, idx, ex) + 1e-16
+    return torch.zeros(nq, C, dtype=msg.dtype, device=msg.device).scatter_add(0, idx, msg * ex / den[erow.long()])
+
+
+@pytest.mark.parametrize("mode", ["max", "mean", "weighted-sum", "attend"])
+def test_seg_aggregate_grads(mode):
+    A, nn, ops = _A()
+    torch.manual_seed(2)
+    nq, C = 500, 48
+    edges = _random_csr(nq, 100, 9, 5)
+    msg = torch.randn(edges.n_edges, C, device=DEV, requires_grad=True)
+    att = torch.randn(edges.n_edges, C, device=DEV, requires_grad=True) if mode in ("weighted-sum", "attend") else None
+    g = torch.randn(nq, C, device=DEV)
+    out = A.seg_aggregate(msg, att, edges.row_ptr, nq, mode)
+    out.backward(g)
+    m2 = msg.detach().double().requires_grad_()
+    a2 = att.detach().double().requires_grad_() if att is not None else None
+    out2 = _ref_seg(m2, a2, edges.erow, nq, mode)
+    out2.backward(g.double())
+    _close(out, out2, 1e-5, "out")
+    _close(msg.grad, m2.grad, 1e-5, "dmsg")
+    if att is not None:
+        _close(att.grad, a2.grad, 1e-5, "datt")
+
+
+def test_edge_layers_grads():
+    A, nn, ops = _A()
+    torch.manual_seed(3)
+    n_src, nq, C, cx = 300, 120, 64, 32
+    edges = _random_csr(nq, n_src, 12, 7)
+    pos_src, pos_dst = torch.randn(n_src, 3, device=DEV), torch.randn(nq, 3, device=DEV)
+    x = torch.randn(n_src, cx, device=DEV, requires_grad=True)
+    W = (torch.randn(C, cx + 3, device=DEV) / 6).requires_grad_()
+    b = torch.randn(C, device=DEV, requires_grad=True)
+    g = torch.randn(edges.n_edges, C, device=DEV)
+    H = A.linear(x, W[:, :cx], None)
+    z = A.edge_layer1(H, W[:, cx:].t(), b, pos_src, pos_dst, edges, 0.25)
+    z.backward(g)
+    x2, W2, b2 = (t.detach().double().requires_grad_() for t in (x, W, b))
+    j, i = edges.ecol.long(), edges.erow.long()
+    rel = (pos_src.double()[j] - pos_dst.double()[i]) / 0.25
+    z2 = F.linear(torch.cat([x2[j], rel], 1), W2, b2)
+    z2.backward(g.double())
+    for a, r, name in ((z, z2, "z"), (x.grad, x2.grad, "dx"), (W.grad, W2.grad, "dW"), (b.grad, b2.grad, "db")):
+        _close(a, r, 3e-5, name)
+
+    # sparse SGCNN first layer: P[col] + Q[row]
+    PQ = torch.randn(n_src, 2 * C, device=DEV, requires_grad=True)
+    e2 = _random_csr(n_src, n_src, 10, 9)
+    g = torch.randn(e2.n_edges, C, device=DEV)
+    A.edge_pair(PQ, e2).backward(g)
+    P2 = PQ.detach().double().requires_grad_()
+    (P2[e2.ecol.long(), :C] + P2[e2.erow.long(), C:]).backward(g.double())
+    _close(PQ.grad, P2.grad, 1e-5, "dPQ (edge_pair)")
+
+    # dense SGCNN first layer + (K+1)-slot max
+    n, K = 257, 9
+    nbr = torch.randint(-1, n, (n, K), device=DEV, dtype=torch.int32)
+    nbr = torch.where(torch.rand(n, K, device=DEV) < 0.2, torch.full_like(nbr, -1), nbr)
+    PQ = torch.randn(n, 2 * C, device=DEV, requires_grad=True)
+    h = A.sgcnn_layer1(PQ, nbr)
+    out = A.group_max_dense(h, nbr)
+    g = torch.randn(n, C, device=DEV)
+    out.backward(g)
+    P2 = PQ.detach().double().requires_grad_()
+    slots = torch.cat([torch.arange(n, device=DEV)[:, None], nbr.long()], 1)            # (n, K+1)
+    valid = slots >= 0
+    hj = torch.where(valid[..., None], P2[slots.clamp(min=0), :C], torch.zeros((), dtype=torch.float64, device=DEV))
+    h2 = hj + P2[:, None, C:]
+    out2 = torch.where(valid[..., None], h2, torch.full((), -100.0, dtype=torch.float64, device=DEV)).max(1)[0]
+    out2.backward(g.double())
+    _close(h, h2.reshape(-1, C), 1e-5, "sgcnn rows")
+    _close(out, out2, 1e-5, "group max")
+    _close(PQ.grad, P2.grad, 1e-5, "dPQ (dense)")
+
+
+def test_interp_blend_and_gather_grads():
+    A, nn, ops = _A()
+    torch.manual_seed(4)
+    n_c, n_f, C, k = 90, 400, 40, 3
+    x = torch.randn(n_c, C, device=DEV, requires_grad=True)
+    nbr = torch.randint(0, n_c, (n_f, k), device=DEV, dtype=torch.int32)
+    d2 = torch.rand(n_f, k, device=DEV) + 1e-3
+    g = torch.randn(n_f, C, device=DEV)
+    A.interp_blend(x, nbr, d2, True).backward(g)
+    x2 = x.detach().double().requires_grad_()
+    w = 1.0 / d2.double()
+    y2 = (x2[nbr.long()] * w[..., None]).sum(1) / w.sum(1, keepdim=True)
+    y2.backward(g.double())
+    _close(x.grad, x2.grad, 1e-5, "dx (interp)")
+
+    idx = torch.randint(0, n_c, (n_f,), device=DEV)
+    x.grad = None
+    y = A.concat([A.gather_rows(x, idx), torch.randn(n_f, 3, device=DEV)])
+    gg = torch.randn(n_f, C + 3, device=DEV)
+    y.backward(gg)
+    x2 = x.detach().double().requires_grad_()
+    x2[idx].backward(gg[:, :C].double())
+    _close(x.grad, x2.grad, 1e-5, "dx (gather+concat)")
+
+
+def _curves(n, seed):
+    gen = torch.Generator().manual_seed(seed)
+    lens = []
+    while sum(lens) < n:
+        lens.append(int(torch.randint(1, 40, (1,), generator=gen)))
+    lens[-1] -= sum(lens) - n
+    if lens[-1] == 0:
+        lens.pop()
+    return torch.repeat_interleave(torch.arange(len(lens)), torch.tensor(lens))
+
+
+@pytest.mark.parametrize("k", [1, 5, 7])
+def test_curve_conv_stack_grads(k):
+    """pad -> conv -> BatchNorm(train) -> LeakyReLU -> unpad, and the feature differences, against torch."""
+    A, nn, ops = _A()
+    from oracle.ccn_modules import feature_diffs
+    torch.manual_seed(5)
+    n, cin, cout = 600, 24, 40
+    curve = _curves(n, 11)
+    batch = torch.zeros(n, dtype=torch.int64)
+    topo = ops.curve_csr(batch.to(DEV), curve.to(DEV))
+    x = torch.randn(n, cin, device=DEV, requires_grad=True)
+    pos = torch.randn(n, 3, device=DEV)
+    w = (torch.randn(cout, 2 * (cin + 3), k, device=DEV) / 8).requires_grad_()
+    b = torch.randn(cout, device=DEV, requires_grad=True)
+    bn = torch.nn.BatchNorm1d(cout).to(DEV)
+    pad = k // 2
+    row2pt = ops.curve_row_map(topo, pad)
+    feats = A.curve_feat_prep(x, pos, True, True, topo.curve_ord)
+    sig = A.pad_rows(feats, row2pt)
+    z = A.curve_conv(sig, w.permute(2, 1, 0), b, k)
+    y = A.unpad_rows(A.bn_act(z, bn, ops.ACT_LEAKY, 0.01), row2pt, n)
+    g = torch.randn(n, cout, device=DEV)
+    y.backward(g)
+
+    x2 = x.detach().cpu().double().requires_grad_()
+    w2, b2 = w.detach().cpu().double().requires_grad_(), b.detach().cpu().double().requires_grad_()
+    f2 = torch.cat([x2, pos.cpu().double()], 1)
+    f2 = torch.cat([f2, feature_diffs(f2, curve, batch)], 1)
+    r2p = row2pt.cpu().long()
+    valid = r2p >= 0
+    sig2 = torch.zeros(r2p.shape[0], f2.shape[1], dtype=torch.float64)
+    sig2 = sig2.index_put((valid.nonzero()[:, 0],), f2[r2p[valid]])
+    z2 = F.conv1d(sig2.t()[None], w2, b2, padding="same")[0].t()
+    ref_bn = torch.nn.BatchNorm1d(cout).double()
+    y2 = F.leaky_relu(ref_bn(z2))[valid]
+    y2.backward(g.cpu().double())
+    _close(y, y2, 3e-5, "y")
+    _close(x.grad, x2.grad, 1e-4, "dx")
+    _close(w.grad, w2.grad, 1e-4, "dw")
+    # the bias sits in front of a batch-statistics BatchNorm: its true gradient is zero, compare on dw's scale
+    assert float((b.grad.cpu().double() - b2.grad).abs().max()) <= 1e-4 * float(w2.grad.abs().max())
+
+
+def test_nll_loss():
+    A, nn, ops = _A()
+    torch.manual_seed(6)
+    n, C = 3000, 17
+    logits = (torch.randn(n, C, device=DEV) * 3).requires_grad_()
+    y = torch.randint(0, C, (n,), device=DEV)
+    y[::7] = 0
+    wts = torch.rand(C, device=DEV) + 0.5
+    for weight, ignore in ((None, -100), (wts, 0)):
+        logits.grad = None
+        loss = A.nll_loss(logits, y, weight, ignore)
+        (loss * 2.0).backward()
+        l2 = logits.detach().double().requires_grad_()
+        ref = F.nll_loss(F.log_softmax(l2, 1), y, weight=None if weight is None else weight.double(), ignore_index=ignore)
+        (ref * 2.0).backward()
+        _close(loss, ref, 1e-6, "loss")
+        _close(logits.grad, l2.grad, 1e-5, "dlogits")
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# whole model, one training step against the CPU oracle
+# ----------------------------------------------------------------------------------------------------------------
+def _scan(name):
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch
+    if name in ("nuscenes", "kitti", "a2d2"):
+        return driving_scan_batch([3], subsample=1500)
+    return object_scan_batch([1, 2])
+
+
+def _freeze_bn(m, freeze):
+    if freeze:
+        for mod in m.modules():
+            if isinstance(mod, torch.nn.BatchNorm1d):
+                mod.eval()
+    return m
+
+
+def _oracle_step(name, data, freeze, perturb=0.0):
+    """One training step of the CPU oracle -> (model, logits, target, loss, {param: grad})."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    ref = build_model(OracleModel, name)
+    randomize_model_(ref, 1234)
+    if perturb:
+        torch.manual_seed(99)
+        with torch.no_grad():
+            for p in ref.parameters():
+                p.mul_(1 + perturb * (torch.rand_like(p) - 0.5))
+    state = {k: v.clone() for k, v in ref.state_dict().items()}
+    _freeze_bn(ref.train(), freeze)
+    torch.manual_seed(11)
+    out = ref(data)
+    gen = torch.Generator().manual_seed(5)
+    target = torch.randint(0, out.shape[1], (out.shape[0],), generator=gen)
+    loss = F.nll_loss(F.log_softmax(out, 1), target)
+    loss.backward()
+    grads = {k: p.grad.detach().clone() for k, p in ref.named_parameters() if p.grad is not None}
+    return ref, state, out.detach(), target, float(loss), grads
+
+
+def _l2_rel(ga, gb):
+    num = sum(float((ga[k].double().cpu() - gb[k].double()).pow(2).sum()) for k in gb)
+    den = sum(float(gb[k].double().pow(2).sum()) for k in gb)
+    return (num / den) ** 0.5
+
+
+def _ours_step(name, precision, state, data, target, freeze):
+    from curvecloudnet_b200 import autograd as A
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    model = build_model(ModelBase, name, precision=precision)
+    model.load_state_dict(state, strict=True)
+    model = _freeze_bn(model.cuda().train(), freeze)
+    torch.manual_seed(11)
+    got = model(data.to("cuda"))
+    loss = A.nll_loss(got, target.cuda())
+    loss.backward()
+    grads = {k: p.grad.detach() for k, p in model.named_parameters() if p.grad is not None}
+    return model, got.detach().cpu(), float(loss), grads
+
+
+LOGIT_TOL = {"fp32": 1e-4, "bf16x3": 1e-4, "bf16": 2e-2}
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3", "bf16"])
+@pytest.mark.parametrize("name", ["shapenet-seg", "nuscenes", "a2d2", "shapenet-class"])
+def test_training_step_frozen_bn_matches_oracle(name, precision):
+    """BatchNorm on running statistics (the well-conditioned form): logits inside the north-star tolerance, every
+    parameter gradient against the oracle's autograd.  What is left are isolated ReLU / arg-max decisions that flip
+    on a 1e-7 difference in the forward, hence a whole-gradient L2 bound next to the per-tensor bound."""
+    data = _scan(name)
+    ref, state, want, target, loss_ref, g_ref = _oracle_step(name, data, True)
+    model, got, loss, g = _ours_step(name, precision, state, data, target, True)
+    e_logits, e_loss = rel_err(got, want), abs(loss - loss_ref) / abs(loss_ref)
+    l2 = _l2_rel(g, g_ref)
+    gmax = max(float(v.abs().max()) for v in g_ref.values())
+    worst = ("", 0.0)
+    for k, rg in g_ref.items():
+        assert k in g, "no gradient for %s" % k
+        err = float((g[k].cpu().double() - rg.double()).abs().max()) / max(float(rg.abs().max()), 1e-3 * gmax)
+        if err > worst[1]:
+            worst = (k, err)
+    print("%s %s frozen-BN: logits %.3e loss %.3e grad L2 %.3e worst tensor %s %.3e"
+          % (name, precision, e_logits, e_loss, l2, worst[0], worst[1]))
+    assert e_logits <= LOGIT_TOL[precision] and e_loss <= LOGIT_TOL[precision]
+    # fp32 measured: L2 3e-7 .. 5e-4, worst tensor <= 8e-3; bf16x3: L2 <= 1.6e-3, worst <= 2.2e-2; bf16 (2e-2 budget on
+    # the forward): L2 <= 6.4e-2, isolated small tensors up to 0.5 of their own scale
+    assert l2 <= {"fp32": 2e-3, "bf16x3": 5e-3, "bf16": 1.5e-1}[precision], "whole-gradient L2 error %.3e" % l2
+    assert worst[1] <= {"fp32": 2e-2, "bf16x3": 6e-2, "bf16": 1.0}[precision], "gradient of %s off by %.3e" % worst
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+@pytest.mark.parametrize("name", ["shapenet-seg", "nuscenes", "a2d2", "shapenet-class"])
+def test_training_step_batch_stats_matches_oracle(name, precision):
+    """Full training mode (BatchNorm batch statistics, running statistics updated).  On these small batches the
+    step is chaotic in fp32: the oracle run with its weights moved by ONE ULP (2e-7 relative) already changes its own
+    logits by ~5e-5 and its gradients by a few percent.  Parity bar: our distance to the oracle is within 3x of that
+    noise floor (measured in the same test), the loss agrees, the running statistics agree."""
+    data = _scan(name)
+    ref, state, want, target, loss_ref, g_ref = _oracle_step(name, data, False)
+    _, _, want_p, _, loss_p, g_pert = _oracle_step(name, data, False, perturb=2e-7)
+    noise_logits, noise_l2 = rel_err(want_p, want), _l2_rel(g_pert, g_ref)
+    noise_loss = abs(loss_p - loss_ref) / abs(loss_ref)
+    model, got, loss, g = _ours_step(name, precision, state, data, target, False)
+    e_logits, e_loss, l2 = rel_err(got, want), abs(loss - loss_ref) / abs(loss_ref), _l2_rel(g, g_ref)
+    print("%s %s batch-stat BN: logits %.3e (1-ulp noise %.3e) loss %.3e grad L2 %.3e (1-ulp noise %.3e)"
+          % (name, precision, e_logits, noise_logits, e_loss, l2, noise_l2))
+    slack = 3.0 if precision == "fp32" else 30.0          # split-bf16 products carry ~2^-16, not 2^-24, relative error
+    assert e_logits <= max(slack * noise_logits, 1e-4)
+    assert e_loss <= max(slack * noise_loss, 1e-4 if precision == "fp32" else 1e-3)
+    assert l2 <= max(slack * noise_l2, 1e-3)
+    ref_bufs = dict(ref.named_buffers())
+    for bname, b in model.named_buffers():
+        if b.dtype.is_floating_point:
+            assert rel_err(b.cpu(), ref_bufs[bname]) <= (1e-4 if precision == "fp32" else 1e-3), bname
+        else:
+            assert int(b) == int(ref_bufs[bname]), bname
