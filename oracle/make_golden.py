@@ -185,6 +185,61 @@ def make_models(rbase):
     return out
 
 
+def grad_projection(name: str, numel: int) -> torch.Tensor:
+    """Fixed +-1 vector per parameter name (seeded by a hash of the name): gradients are frozen as their projection
+    on it, their L2 norm and - for vectors - in full, which keeps train.pt small."""
+    import zlib
+    gen = torch.Generator().manual_seed(zlib.crc32(name.encode()))
+    return torch.randint(0, 2, (numel,), generator=gen).double() * 2 - 1
+
+
+def make_train(rbase):
+    """One training step of the REAL reference sources (train mode, NLL loss of random targets, loss.backward()):
+    with BatchNorm on running statistics (well conditioned: tight comparison) and on batch statistics."""
+    import torch.nn.functional as F
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch, randomize_model_
+    out = {}
+    specs = {
+        "nuscenes": lambda: driving_scan_batch([51, 52], subsample=1500),
+        "shapenet-seg": lambda: object_scan_batch([55, 56], n_points=768),
+    }
+    for name, mk in specs.items():
+        data = mk()
+        for freeze in (True, False):
+            model = build_model(rbase.ModelBase, name)
+            randomize_model_(model, 1234)
+            model.train()
+            if freeze:
+                for m in model.modules():
+                    if isinstance(m, torch.nn.BatchNorm1d):
+                        m.eval()
+            torch.manual_seed(78)
+            logits = model(data, labels=data.y)
+            gen = torch.Generator().manual_seed(6)
+            target = torch.randint(0, logits.shape[1], (logits.shape[0],), generator=gen)
+            loss = F.nll_loss(F.log_softmax(logits, 1), target)
+            loss.backward()
+            grads = {}
+            for k, p in model.named_parameters():
+                if p.grad is None:
+                    continue
+                gd = p.grad.double().flatten()
+                ent = {"norm": float(gd.norm()), "proj": float((gd * grad_projection(k, gd.numel())).sum()),
+                       "absmax": float(gd.abs().max())}
+                if p.dim() == 1:
+                    ent["full"] = p.grad.clone()
+                grads[k] = ent
+            rec = {"logits": logits.detach(), "loss": float(loss), "grads": grads}
+            if not freeze:
+                rec["buffers"] = {k: v.clone() for k, v in model.named_buffers() if v.dtype.is_floating_point and v.numel() <= 64}
+            out.setdefault(name, {"pos": data.pos, "x": data.x, "batch": data.batch, "curve": data.curve_idxs,
+                                  "labels": getattr(data, "labels", None), "weight_seed": 1234, "rng_seed": 78,
+                                  "target": target})["frozen_bn" if freeze else "batch_stats"] = rec
+            print(name, "frozen" if freeze else "batch-stats", float(loss), len(grads))
+    return out
+
+
 def _compact(obj):
     """int64 -> int32 (all values are small indices) to keep the committed fixtures small;
     tests/golden_utils.load() widens them again."""
@@ -198,6 +253,10 @@ def _compact(obj):
 def main():
     os.makedirs(OUT, exist_ok=True)
     rpo, rbase, rconv, rfps = _import_reference()
+    if len(sys.argv) > 1 and sys.argv[1] == "train":      # only the training-step fixture
+        torch.save(_compact(make_train(rbase)), os.path.join(OUT, "train.pt"))
+        print("train.pt", os.path.getsize(os.path.join(OUT, "train.pt")) // 1024, "KiB")
+        return
     torch.save(_compact(make_ops(rpo, rconv, rfps)), os.path.join(OUT, "ops.pt"))
     torch.save(_compact(make_models(rbase)), os.path.join(OUT, "models.pt"))
     for f in ("ops.pt", "models.pt"):

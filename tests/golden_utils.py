@@ -38,3 +38,34 @@ class FixedDraws:
 def rel_err(a, b):
     """max |a-b| / max |b|  (the 'relative' of BASELINE.json's 1e-4 / 2e-2 tolerances)."""
     return float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp(min=1e-30))
+
+
+def grad_projection(name, numel):
+    """Same +-1 vector per parameter name as oracle/make_golden.py grad_projection."""
+    import zlib
+    gen = torch.Generator().manual_seed(zlib.crc32(name.encode()))
+    return torch.randint(0, 2, (numel,), generator=gen).double() * 2 - 1
+
+
+def check_train_golden(model, logits, loss, rec, logit_tol, grad_tol, label=""):
+    """Compare one training step with a record of tests/golden/train.pt (made from the REAL reference sources):
+    logits, loss, and for every parameter the gradient's L2 norm, its projection on a fixed +-1 vector and (for
+    vectors) every entry.  Errors are relative to the tensor's norm, floored by 1e-3 of the largest norm."""
+    e_logits = rel_err(logits.detach().cpu(), rec["logits"])
+    e_loss = abs(float(loss) - rec["loss"]) / abs(rec["loss"])
+    params = dict(model.named_parameters())
+    nmax = max(g["norm"] for g in rec["grads"].values())
+    worst = ("", 0.0)
+    for k, g in rec["grads"].items():
+        assert params[k].grad is not None, "no gradient for %s" % k
+        gd = params[k].grad.detach().cpu().double().flatten()
+        scale = max(g["norm"], 1e-3 * nmax)
+        errs = [abs(float(gd.norm()) - g["norm"]) / scale,
+                abs(float((gd * grad_projection(k, gd.numel())).sum()) - g["proj"]) / (scale * gd.numel() ** 0.5) * 3]
+        if "full" in g:
+            errs.append(float((gd - g["full"].double().flatten()).norm()) / scale)
+        if max(errs) > worst[1]:
+            worst = (k, max(errs))
+    print("%s train golden: logits %.3e loss %.3e worst gradient %s %.3e" % (label, e_logits, e_loss, worst[0], worst[1]))
+    assert e_logits <= logit_tol and e_loss <= logit_tol, (e_logits, e_loss)
+    assert worst[1] <= grad_tol, "gradient of %s off by %.3e" % worst

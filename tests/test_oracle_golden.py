@@ -95,3 +95,39 @@ def test_model_logits(name):
         logits = model(data)
     assert logits.shape == g["logits"].shape
     assert rel_err(logits, g["logits"]) < 2e-6
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# training step: the oracle's autograd against the step frozen from the REAL reference sources (train.pt)
+# ---------------------------------------------------------------------------------------------------------------
+import pytest  # noqa: E402
+
+from golden_utils import check_train_golden  # noqa: E402
+
+
+@pytest.mark.parametrize("mode", ["frozen_bn", "batch_stats"])
+@pytest.mark.parametrize("name", ["shapenet-seg", "nuscenes"])
+def test_oracle_training_step_matches_reference(name, mode):
+    import torch
+    import torch.nn.functional as F
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import randomize_model_
+    from oracle.ccn_model import ModelBase
+    from oracle.tp_nn import Batch
+    g = load("train.pt")[name]
+    model = build_model(ModelBase, name)
+    randomize_model_(model, g["weight_seed"])
+    model.train()
+    if mode == "frozen_bn":
+        for m in model.modules():
+            if isinstance(m, torch.nn.BatchNorm1d):
+                m.eval()
+    kw = dict(x=g["x"], pos=g["pos"], batch=g["batch"], curve_idxs=g["curve"])
+    if g["labels"] is not None:
+        kw["labels"] = g["labels"]
+    torch.manual_seed(g["rng_seed"])
+    logits = model(Batch(**kw))
+    loss = F.nll_loss(F.log_softmax(logits, 1), g["target"])
+    loss.backward()
+    # the restatement runs the same CPU torch kernels as the reference did: agreement to rounding
+    check_train_golden(model, logits, loss, g[mode], 1e-5, 1e-4 if mode == "frozen_bn" else 1e-3, "%s %s oracle" % (name, mode))
