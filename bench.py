@@ -122,6 +122,177 @@ def run_reference(args):
         "gpu_launches": 0}))
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# --mode train: BASELINE.json configs[1], ShapeNet-seg (grid sampling) fwd+bwd, batch 16 x 2048 points per GPU
+# ------------------------------------------------------------------------------------------------------------------
+TRAIN_METRIC = "points/sec fwd+bwd training step (ShapeNet-seg-shape CurveCloudNet)"
+TRAIN_WORKLOAD = "ShapeNet-seg-shape CurveCloudNet training step (fwd + NLL loss + bwd + Adam), B=%d x 2048 synthetic scan-line points"
+
+
+def cpu_train_points_per_s(batch, iters, warmup, threads):
+    """The CPU oracle's training step (autograd over the restatement) on a bounded batch."""
+    import torch.nn.functional as F
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    torch.set_num_threads(threads)
+    data = object_scan_batch(list(range(batch)))
+    model = build_model(OracleModel, "shapenet-seg")
+    randomize_model_(model, 1234)
+    model.train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    gen = torch.Generator().manual_seed(0)
+    target = torch.randint(0, 50, (data.pos.shape[0],), generator=gen)
+    times = []
+    for i in range(warmup + iters):
+        torch.manual_seed(i)
+        t0 = time.perf_counter()
+        opt.zero_grad()
+        loss = F.nll_loss(F.log_softmax(model(data), 1), target)
+        loss.backward()
+        opt.step()
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return data.pos.shape[0] * len(times) / sum(times), data.pos.shape[0], sum(times) / len(times)
+
+
+def run_train_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = os.cpu_count() or 1
+    steps, warmup = max(min(args.steps, 5), 1), 1
+    pps, n, sec = cpu_train_points_per_s(2, steps, warmup, threads)
+    sample = "oracle port, B=2 x 2048 points per step, %d threads" % threads
+    print(json.dumps({
+        "impl": "reference", "metric": TRAIN_METRIC, "value": pps, "unit": "points/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": TRAIN_WORKLOAD % args.train_batch, "sample": sample},
+        "cpu_baseline": {"value": pps, "unit": "points/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": pps, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+
+
+def run_train(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from curvecloudnet_b200 import autograd as A
+    from curvecloudnet_b200 import native
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.sharding import GradReducer
+    from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
+    native.load()
+    W, K, B = max(args.warmup, 3), max(args.steps, 1), args.train_batch
+    model = build_model(ModelBase, "shapenet-seg", precision=args.precision)
+    randomize_model_(model, 1234)
+    model = model.cuda().train()
+    reducer = GradReducer(model.parameters(), dist)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+    gen = torch.Generator().manual_seed(rank)
+    host, targets = [], []
+    for s in range(args.scans):
+        d = object_scan_batch([10000 * rank + B * s + b for b in range(B)])
+        host.append(d.pin_memory())
+        targets.append(torch.randint(0, 50, (d.pos.shape[0],), generator=gen).pin_memory())
+    dev = [(d.to("cuda"), t.to("cuda")) for d, t in zip(host, targets)]
+    pts = [d.num_points for d in host]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_pass(steps, from_host, profile):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        npts = 0
+        native.profile_begin(("ccn_linear_wgrad",) if profile else None, pad_cycles=0)
+        barrier()
+        l0 = native.kernel_launches()
+        for i in range(steps):
+            flush.zero_()
+            j = i % args.scans
+            torch.manual_seed(i)
+            ev[i][0].record()
+            if from_host:
+                data, tgt = host[j].to("cuda", non_blocking=True), targets[j].to("cuda", non_blocking=True)
+            else:
+                data, tgt = dev[j]
+            reducer.prepare()
+            loss = A.nll_loss(model(data), tgt)
+            loss.backward()
+            reducer.finish()
+            opt.step()
+            if from_host:
+                loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+            ev[i][1].record()
+            npts += pts[j]
+        barrier()
+        launches = native.kernel_launches() - l0
+        prof = native.profile_end()
+        return sum(a.elapsed_time(b) for a, b in ev), npts, launches, prof
+
+    timed_pass(W, False, False)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, npts, launches, _ = timed_pass(K, False, False)
+    ms_e2e, npts_e2e, _, _ = timed_pass(K, True, False)
+    ms_prof, _, _, prof = timed_pass(K, False, True)
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([npts, npts_e2e], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms_max, ms_e2e_max = [float(v) for v in t.tolist()]
+    tot_pts, tot_pts_e2e = [float(v) for v in tot.tolist()]
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    peaks, peak_src = _peaks()
+    wg = prof.get("ccn_linear_wgrad", {"ms": 0.0, "calls": 0, "work": 0.0})
+    peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
+    ach = (wg["work"] / (wg["ms"] * 1e-3) / 1e12) if wg["ms"] > 0 else 0.0
+    line = {
+        "metric": TRAIN_METRIC, "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K,
+        "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "%s Linear fwd/dgrad, f32 weight gradients and everything else" % args.precision, "data": "synthetic",
+        "config": {"workload": TRAIN_WORKLOAD % B, "points_per_step": tot_pts / (K * world), "scans_per_step": B,
+                   "distinct_batches_per_rank": args.scans, "optimizer": "torch.optim.Adam(fused)",
+                   "parallelism": "data parallel dp%d, bucketed gradient all-reduce overlapped with backward" % world,
+                   "l2": "256 MiB buffer written between timed steps (L2 flush)"},
+        "e2e": {"value": tot_pts_e2e / (ms_e2e_max * 1e-3), "unit": "points/s",
+                "h2d_bytes_per_step": int(sum(d.input_bytes() for d in host) / len(host) + targets[0].numel() * 8),
+                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e_max / K},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "tensor", "kernel": "linear_wgrad_kernel (ccn_linear_wgrad, fp32 SIMT split-M)", "achieved": ach,
+                     "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None, "traffic": None,
+                     "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": wg["calls"],
+                     "avg_launch_us": (wg["ms"] * 1e3 / wg["calls"]) if wg["calls"] else None,
+                     "share_of_step": wg["ms"] / ms_prof if ms_prof else None, "flops_per_step": wg["work"] / K},
+        "clocks": clocks,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        pps, n, sec = cpu_train_points_per_s(2, 2, 1, threads)
+        line["cpu_baseline"] = {"value": pps, "unit": "points/s", "cores": threads, "kind": "port",
+                                "sample": "oracle port, B=2 x 2048 points, 2 timed steps, %.2f s each" % sec}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -133,7 +304,12 @@ def main():
     ap.add_argument("--batch", type=int, default=1, help="scans per step (one ModelBase.forward call)")
     ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"],
                     help="shared-MLP Linear arithmetic: fp32 pipe | tcgen05 split-bf16 x3 (1e-4 budget) | tcgen05 bf16 (2e-2 budget)")
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"],
+                    help="infer: nuScenes-shape forward (the headline metric); train: ShapeNet-seg fwd+bwd step (configs[1])")
+    ap.add_argument("--train-batch", type=int, default=16, help="scans per training step per GPU (--mode train)")
     args = ap.parse_args()
+    if args.mode == "train":
+        return run_train_reference(args) if args.impl == "reference" else run_train(args)
     if args.impl == "reference":
         return run_reference(args)
 

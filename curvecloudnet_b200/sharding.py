@@ -45,3 +45,78 @@ def gather_predictions(local: dict, num_scans: int, dist=None) -> list:
     if missing:
         raise RuntimeError("scans %s were processed by no rank" % missing)
     return [merged[i] for i in range(num_scans)]
+
+
+class GradReducer:
+    """Training-step gradient all-reduce ("one gradient all-reduce per step, bucketed in reverse-layer
+    order and overlapped with backward"; the reference itself trains on one GPU, src/main.py:56-60).
+
+    Every parameter's `.grad` is a view into one flat fp32 buffer, cut into buckets in REVERSE parameter order (the
+    order backward finishes them).  A post-accumulate hook counts a bucket's parameters; when the last one has its
+    gradient, the bucket's all-reduce is issued asynchronously (NCCL runs it on its own stream over NVLink/NVSwitch
+    while backward keeps going).  finish() waits for the buckets and leaves the MEAN over ranks in `.grad`.
+    Parameters that got no gradient this step hold zeros (prepare() clears the buffer), so every rank issues the
+    same collectives."""
+
+    def __init__(self, params, dist=None, bucket_bytes: int = 16 << 20):
+        self.params = [p for p in params if p.requires_grad]
+        self.dist = dist if dist is not None and dist.is_initialized() and dist.get_world_size() > 1 else None
+        self.world = self.dist.get_world_size() if self.dist is not None else 1
+        total = sum(p.numel() for p in self.params)
+        dev = self.params[0].device if self.params else "cpu"
+        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.buckets = []                 # [(start, end, n_params)]
+        self._bucket_of = {}
+        off, b_start, b_count = 0, 0, 0
+        for p in reversed(self.params):
+            n = p.numel()
+            p.grad = self.flat[off:off + n].view_as(p)
+            self._bucket_of[id(p)] = len(self.buckets)
+            off += n
+            b_count += 1
+            if (off - b_start) * 4 >= bucket_bytes:
+                self.buckets.append((b_start, off, b_count))
+                b_start, b_count = off, 0
+        if b_count:
+            self.buckets.append((b_start, off, b_count))
+        self._pending = [0] * len(self.buckets)
+        self._work = []
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+
+    def prepare(self):
+        """Call before every backward: zero the flat gradient, re-arm the buckets."""
+        self.flat.zero_()
+        for p in self.params:             # an optimizer's zero_grad(set_to_none=True) would detach the views
+            if p.grad is None or p.grad.data_ptr() < self.flat.data_ptr():
+                raise RuntimeError("GradReducer: .grad was replaced; use optimizer.zero_grad(set_to_none=False) "
+                                   "or just GradReducer.prepare()")
+        self._pending = [b[2] for b in self.buckets]
+        self._work = []
+
+    def _on_grad(self, p):
+        b = self._bucket_of[id(p)]
+        self._pending[b] -= 1
+        if self._pending[b] == 0:
+            self._launch(b)
+
+    def _launch(self, b):
+        if self.dist is None:
+            return
+        s, e, _ = self.buckets[b]
+        self._work.append(self.dist.all_reduce(self.flat[s:e], op=self.dist.ReduceOp.SUM, async_op=True))
+        self._pending[b] = -1
+
+    def finish(self):
+        """Call after backward: flush buckets whose parameters got no gradient, wait, average."""
+        for b, left in enumerate(self._pending):
+            if left >= 0 and self.dist is not None and left != -1:
+                self._launch(b)
+        for w in self._work:
+            w.wait()
+        if self.world > 1:
+            self.flat.div_(self.world)
+        self._work = []
+
+    def remove(self):
+        for h in self._hooks:
+            h.remove()

@@ -53,3 +53,54 @@ def test_world2_gloo_measurement_and_gather():
     for p in procs:
         p.join(60)
     assert res == [(0, True), (1, True)]
+
+
+def _grad_reducer_worker(rank, world, port, q):
+    import os
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from curvecloudnet_b200.sharding import GradReducer
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4), torch.nn.Linear(4, 2))
+    unused = torch.nn.Linear(3, 3)                       # gets no gradient: its bucket must still be reduced
+    params = list(net.parameters()) + list(unused.parameters())
+    red = GradReducer(params, dist, bucket_bytes=64)     # several small buckets
+    assert len(red.buckets) > 2
+    outs = []
+    for step in range(2):
+        torch.manual_seed(100 * step + rank)
+        x = torch.randn(5, 8)
+        red.prepare()
+        net(x).pow(2).sum().backward()
+        red.finish()
+        outs.append([p.grad.clone() for p in params])
+    # reference: the same two steps for every rank, averaged
+    want = []
+    for step in range(2):
+        acc = None
+        for r in range(world):
+            torch.manual_seed(100 * step + r)
+            x = torch.randn(5, 8)
+            g = torch.autograd.grad(net(x).pow(2).sum(), list(net.parameters()))
+            acc = [a + b for a, b in zip(acc, g)] if acc is not None else list(g)
+        want.append([a / world for a in acc])
+    ok = all(torch.allclose(o, w, atol=1e-6) for step in range(2) for o, w in zip(outs[step], want[step]))
+    ok = ok and all(float(o.abs().max()) == 0.0 for o in outs[1][len(want[1]):])
+    q.put((rank, bool(ok)))
+    dist.destroy_process_group()
+
+
+def test_grad_reducer_world2_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29641
+    procs = [ctx.Process(target=_grad_reducer_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == [(0, True), (1, True)]
