@@ -37,15 +37,6 @@ def _empty(shape, like, dtype=torch.float32):
 # ----------------------------------------------------------------------------------------------
 # Linear
 # ----------------------------------------------------------------------------------------------
-def _gemm_nt(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
-    """a (M,K) @ w (N,K)^T + bias with the Linear kernel of the current precision mode."""
-    mode = _precision()
-    if mode == "fp32" or a.shape[0] == 0:
-        return ops.linear(a, w, bias, ops.ACT_NONE)
-    npl = 2 if mode == "bf16x3" else 1
-    return ops.linear_planes(ops.pack_planes([a], npl), ops.TcWeight(w), bias, ops.ACT_NONE, 0.0, "f32")
-
-
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, want_bias: bool):
     dy, lddy = ops._rows(dy)
     x, ldx = ops._rows(x)
@@ -57,21 +48,71 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, want_bias: bool):
     return dW, db
 
 
+def _tc_wgrad_ok(N: int, K: int) -> bool:
+    return N >= 16 and K >= 16
+
+
+def wgrad_planes(dyp: "ops.Planes", xp: "ops.Planes", row_off: int = 0) -> torch.Tensor:
+    """dW (N,K) = dY^T X[. + row_off] on tcgen05 from activation planes (ccn_linear_wgrad_tc)."""
+    M, N = dyp.shape
+    K = xp.shape[1]
+    dW = _zeros((N, K), dyp.buf)
+    call("ccn_linear_wgrad_tc", dyp.buf, dyp.kpad, dyp.plane_stride, xp.buf, xp.kpad, xp.plane_stride, M, N, K,
+         int(row_off), xp.m, 3 if dyp.n_planes == 2 else 1, dW, K)
+    return dW
+
+
+def col_sum(dy: torch.Tensor) -> torch.Tensor:
+    dy, ld = ops._rows(dy)
+    out = _zeros((dy.shape[1],), dy)
+    call("ccn_col_sum", dy, ld, dy.shape[0], dy.shape[1], out)
+    return out
+
+
 class _Linear(Function):
+    """y = x W^T + b.  fp32 mode: FP32-pipe kernels.  Tensor-core modes: x is packed into split-bf16 planes once; the
+    planes serve the forward GEMM and - kept for backward instead of x - the weight gradient; dY is packed once in
+    backward and serves both dX = dY W and dW = dY^T X (all three GEMMs on tcgen05)."""
+
     @staticmethod
     def forward(ctx, x, w, b):
-        ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
-        return _gemm_nt(x, w.detach().contiguous(), None if b is None else b.detach())
+        ctx.mode = mode = _precision()    # backward runs after ModelBase.forward has restored the global mode
+        wd = w.detach().contiguous()
+        bd = None if b is None else b.detach()
+        ctx.xp = None
+        if mode == "fp32" or x.shape[0] == 0:
+            ctx.save_for_backward(x, w)
+            return ops.linear(x, wd, bd, ops.ACT_NONE)
+        xp = ops.pack_planes([x], 2 if mode == "bf16x3" else 1)
+        if _tc_wgrad_ok(wd.shape[0], wd.shape[1]):
+            ctx.xp = xp
+            ctx.save_for_backward(None, w)
+        else:
+            ctx.save_for_backward(x, w)
+        return ops.linear_planes(xp, ops.TcWeight(wd), bd, ops.ACT_NONE, 0.0, "f32")
 
     @staticmethod
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
         dx = dW = db = None
+        need_w = ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2])
+        if ctx.mode == "fp32" or dy.shape[0] == 0:
+            if ctx.needs_input_grad[0]:
+                dx = ops.linear(dy, w.detach().t().contiguous(), None, ops.ACT_NONE)        # dX = dY W
+            if need_w:
+                dW, db = linear_wgrad(dy, x, ctx.has_bias)
+            return dx, dW, db
+        dyp = ops.pack_planes([dy], 2 if ctx.mode == "bf16x3" else 1)
         if ctx.needs_input_grad[0]:
-            dx = _gemm_nt(dy, w.detach().t().contiguous(), None)      # dX = dY W
-        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            dW, db = linear_wgrad(dy, x, ctx.has_bias)
+            dx = ops.linear_planes(dyp, ops.TcWeight(w.detach().t().contiguous()), None, ops.ACT_NONE, 0.0, "f32")
+        if need_w:
+            if ctx.xp is not None:
+                dW = wgrad_planes(dyp, ctx.xp)
+                db = col_sum(dy) if ctx.has_bias else None
+            else:
+                dW, db = linear_wgrad(dy, x, ctx.has_bias)
+        ctx.xp = None
         return dx, dW, db
 
 
@@ -266,6 +307,27 @@ def unpad_rows(sig, row2pt, n):
     return _UnpadRows.apply(sig, row2pt, n)
 
 
+class _AppendZeroRows(Function):
+    """[x ; 0] with n_pad zero rows (to_batch_padded's padding points, point_ops.py:263-284, as extra rows)."""
+
+    @staticmethod
+    def forward(ctx, x, n_pad):
+        x, ld = ops._rows(x)
+        n, c = x.shape
+        ctx.n = n
+        out = _zeros((n + n_pad, c), x)
+        call("ccn_gather_rows_f32", x, ld, 0, n, c, out, c)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        return dy[:ctx.n], None
+
+
+def append_zero_rows(x, n_pad: int):
+    return x if n_pad <= 0 else _AppendZeroRows.apply(x, n_pad)
+
+
 class _Concat(Function):
     @staticmethod
     def forward(ctx, *parts):
@@ -432,7 +494,7 @@ class _GroupMaxDense(Function):
         dout, ldo = ops._rows(dout)
         n, K = nbr.shape
         c = h.shape[1]
-        dh = _empty(h.shape, h)
+        dh = _empty(h.shape, h) if h.shape[0] == n * (K + 1) else _zeros(h.shape, h)   # rows of padded points: no gradient
         call("ccn_group_max_dense_bwd", h, ldf, nbr, n, K, c, dout, ldo, dh, c)
         return dh, None
 
@@ -500,6 +562,7 @@ class _CurveConv(Function):
         sig, _ = ops._rows(sig)
         ctx.save_for_backward(sig, w)
         ctx.ksize = ksize
+        ctx.mode = _precision()
         rows = sig.shape[0]
         dummy = _iota32(1, sig)
         return ops.curve_conv_layer(sig, w.detach().contiguous(), b.detach(), dummy, rows, rows, ksize, False, False,
@@ -517,7 +580,14 @@ class _CurveConv(Function):
             wt = torch.flip(w.detach(), dims=[0]).transpose(1, 2).contiguous()       # (k, cout, cin): weight prep
             zero_b = _zeros((cin,), dz)
             dsig = ops.curve_conv_layer(dz, wt, zero_b, _iota32(1, dz), rows, rows, k, False, False, slope=1.0)
-        if ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
+        if (ctx.needs_input_grad[1] or ctx.needs_input_grad[2]) and ctx.mode != "fp32" and _tc_wgrad_ok(cout, cin):
+            # one tcgen05 weight-gradient GEMM per tap: the tap's row shift is a TMA coordinate offset
+            npl = 2 if ctx.mode == "bf16x3" else 1
+            dzp, sigp = ops.pack_planes([dz], npl), ops.pack_planes([sig], npl)
+            half = k // 2
+            dw = torch.stack([wgrad_planes(dzp, sigp, tap - half).t() for tap in range(k)], dim=0)   # (k, cin, cout)
+            db = col_sum(dz)
+        elif ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
             dw = _zeros((k, cin, cout), dz)
             db = _zeros((cout,), dz)
             half = k // 2

@@ -159,6 +159,12 @@ def curve_sa_module(mod, x, pos, batch, curve, draws: Draws = DEFAULT_DRAWS, **k
 
 
 # ---------------------------------------------------------------------------------------------- dgcnn.py
+def _pad_nbr(nbr, n_pad):
+    if n_pad <= 0:
+        return nbr
+    return torch.cat([nbr, torch.full((n_pad, nbr.shape[1]), -1, dtype=nbr.dtype, device=nbr.device)], dim=0)
+
+
 def sgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
     cache = get_cache(kwargs)
     sptr = cache.sample_ptr(batch)
@@ -171,12 +177,20 @@ def sgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
     # decomposition of the first Linear (see modules.SGCNNLayer): torch arithmetic on the WEIGHTS only
     wpq = torch.cat([wb, wa - wb], dim=0) if mod.use_sparse_feat_agg else torch.cat([wa - wb, wb], dim=0)
     bpq = torch.cat([torch.zeros_like(lin0.bias), lin0.bias]) if lin0.bias is not None else None
+    n_pad = 0
+    if not mod.use_sparse_feat_agg:
+        # forward_fast runs its MLP - hence its BatchNorm batch statistics - over the B x N_max padded layout of
+        # to_batch_padded (dgcnn.py:170-177): every padding point contributes K+1 all-zero input rows.  They are
+        # appended here as zero-feature points without neighbours (BatchNorm statistics do not depend on row order).
+        lens = sptr.lengths
+        n_pad = len(lens) * max(lens) - sum(lens)
+        x = A.append_zero_rows(x, n_pad)
     PQ = A.linear(x, wpq, bpq)
     if not mod.use_sparse_feat_agg:
         if mod.aggr_type != "max":
             raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
         nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, mod.k, mod.r, cache=cache)
-        h = A.mlp_train(mlp, _first_hidden(mlp, A.sgcnn_layer1(PQ, nbr)), first=1)
+        h = A.mlp_train(mlp, _first_hidden(mlp, A.sgcnn_layer1(PQ, _pad_nbr(nbr, n_pad))), first=1)
         return A.group_max_dense(h, nbr), pos, batch, curve
     if mod.use_fast_knn:
         nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, mod.k, mod.r, want_cnt=True, cache=cache)

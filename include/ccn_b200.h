@@ -278,6 +278,14 @@ int ccn_nll_loss_bwd(const float* logits, int64_t ld, const int64_t* target, con
 /* y = u >= p ? x / (1 - p) : 0 with caller-supplied uniform draws u (n*c); applied to the gradient it is the backward */
 int ccn_dropout(const float* x, int64_t ldx, const float* u, int64_t n, int32_t c, float p, float* y, int64_t ldy,
                 ccn_stream_t stream);
+/* out (C) += column sums of src (M,C)                                               (bias gradient) */
+int ccn_col_sum(const float* src, int64_t ld, int64_t M, int32_t C, float* out, ccn_stream_t stream);
+/* dW (N,K) += dY^T X[. + x_row_off] on tcgen05, both operands as split-bf16 activation planes read by TMA as
+ * MN-major UMMA blocks (no transposed copies); x_row_off != 0 serves the taps of the curve convolution; mode 1 = bf16,
+ * 3 = split-bf16 x3.  dW is accumulated into with vector reductions (zero-filled by the caller). */
+int ccn_linear_wgrad_tc(const void* dy_planes, int64_t dy_ld, int64_t dy_plane_stride, const void* x_planes,
+                        int64_t x_ld, int64_t x_plane_stride, int64_t M, int32_t N, int32_t K, int32_t x_row_off,
+                        int64_t x_rows, int32_t mode, float* dW, int64_t lddw, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }
