@@ -192,6 +192,7 @@ def run_train(args):
     from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
     native.load()
     W, K, B = max(args.warmup, 3), max(args.steps, 1), args.train_batch
+    WG = "ccn_linear_wgrad" if args.precision == "fp32" else "ccn_linear_wgrad_tc"
     model = build_model(ModelBase, "shapenet-seg", precision=args.precision)
     randomize_model_(model, 1234)
     model = model.cuda().train()
@@ -217,7 +218,7 @@ def run_train(args):
     def timed_pass(steps, from_host, profile):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         npts = 0
-        native.profile_begin(("ccn_linear_wgrad",) if profile else None, pad_cycles=0)
+        native.profile_begin((WG,) if profile else None, pad_cycles=40000 if profile else 0)
         barrier()
         l0 = native.kernel_launches()
         for i in range(steps):
@@ -261,13 +262,13 @@ def run_train(args):
             dist.destroy_process_group()
         return
     peaks, peak_src = _peaks()
-    wg = prof.get("ccn_linear_wgrad", {"ms": 0.0, "calls": 0, "work": 0.0})
+    wg = prof.get(WG, {"ms": 0.0, "calls": 0, "work": 0.0})
     peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
     ach = (wg["work"] / (wg["ms"] * 1e-3) / 1e12) if wg["ms"] > 0 else 0.0
     line = {
         "metric": TRAIN_METRIC, "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "%s Linear fwd/dgrad, f32 weight gradients and everything else" % args.precision, "data": "synthetic",
+        "dtype": "%s Linear / curve-conv GEMMs (forward, data and weight gradients), f32 everything else" % args.precision, "data": "synthetic",
         "config": {"workload": TRAIN_WORKLOAD % B, "points_per_step": tot_pts / (K * world), "scans_per_step": B,
                    "distinct_batches_per_rank": args.scans, "optimizer": "torch.optim.Adam(fused)",
                    "parallelism": "data parallel dp%d, bucketed gradient all-reduce overlapped with backward" % world,
@@ -276,7 +277,7 @@ def run_train(args):
                 "h2d_bytes_per_step": int(sum(d.input_bytes() for d in host) / len(host) + targets[0].numel() * 8),
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e_max / K},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "linear_wgrad_kernel (ccn_linear_wgrad, fp32 SIMT split-M)", "achieved": ach,
+        "roofline": {"bound": "tensor", "kernel": "linear_wgrad_kernel (fp32 SIMT)" if args.precision == "fp32" else "wgrad_tc_kernel (ccn_linear_wgrad_tc: TMA + tcgen05 MN-major + TMEM, split-M)", "achieved": ach,
                      "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None, "traffic": None,
                      "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": wg["calls"],
                      "avg_launch_us": (wg["ms"] * 1e3 / wg["calls"]) if wg["calls"] else None,

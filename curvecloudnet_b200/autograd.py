@@ -555,18 +555,25 @@ def curve_feat_prep(x, pos, with_xyz, with_diff, curve_ord):
 
 
 class _CurveConv(Function):
-    """z = conv1d('same', zero padded) of the padded signal (rows, cin) with w (k, cin, cout) + b; no norm, no act."""
+    """z = conv1d('same', zero padded) of the padded signal (rows, cin) with w (k, cin, cout) + b; no norm, no act.
+    fp32 mode: the FP32-pipe tap kernel (ccn_curve_conv_layer).  Tensor-core modes: forward, data gradient and weight
+    gradient are tcgen05 GEMMs over the signal's activation planes - a tap's row shift is a TMA coordinate."""
 
     @staticmethod
     def forward(ctx, sig, w, b, ksize):
         sig, _ = ops._rows(sig)
-        ctx.save_for_backward(sig, w)
         ctx.ksize = ksize
-        ctx.mode = _precision()
+        ctx.mode = mode = _precision()
         rows = sig.shape[0]
-        dummy = _iota32(1, sig)
-        return ops.curve_conv_layer(sig, w.detach().contiguous(), b.detach(), dummy, rows, rows, ksize, False, False,
-                                    slope=1.0)
+        wd = w.detach().contiguous()
+        ctx.tc = mode != "fp32" and rows > 0 and wd.shape[1] >= 16 and wd.shape[2] >= 16
+        if ctx.tc:
+            sigp = ops.pack_planes([sig], 2 if mode == "bf16x3" else 1)
+            ctx.sigp = sigp
+            ctx.save_for_backward(None, w)
+            return ops.conv_planes(sigp, wd, b.detach())
+        ctx.save_for_backward(sig, w)
+        return ops.curve_conv_layer(sig, wd, b.detach(), _iota32(1, sig), rows, rows, ksize, False, False, slope=1.0)
 
     @staticmethod
     def backward(ctx, dz):
@@ -574,23 +581,26 @@ class _CurveConv(Function):
         k = ctx.ksize
         dz = dz.contiguous()
         rows, cout = dz.shape
-        cin = sig.shape[1]
+        cin = w.shape[1]
         dsig = dw = db = None
+        half = k // 2
+        need_w = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        wt = torch.flip(w.detach(), dims=[0]).transpose(1, 2).contiguous()           # (k, cout, cin): weight prep
+        if ctx.tc:
+            dzp = ops.pack_planes([dz], 2 if ctx.mode == "bf16x3" else 1)
+            if ctx.needs_input_grad[0]:
+                dsig = ops.conv_planes(dzp, wt, None)
+            if need_w:
+                # one tcgen05 weight-gradient GEMM per tap: the tap's row shift is a TMA coordinate offset
+                dw = torch.stack([wgrad_planes(dzp, ctx.sigp, tap - half).t() for tap in range(k)], dim=0)   # (k, cin, cout)
+                db = col_sum(dz)
+            ctx.sigp = None
+            return dsig, dw, db, None
         if ctx.needs_input_grad[0]:
-            wt = torch.flip(w.detach(), dims=[0]).transpose(1, 2).contiguous()       # (k, cout, cin): weight prep
-            zero_b = _zeros((cin,), dz)
-            dsig = ops.curve_conv_layer(dz, wt, zero_b, _iota32(1, dz), rows, rows, k, False, False, slope=1.0)
-        if (ctx.needs_input_grad[1] or ctx.needs_input_grad[2]) and ctx.mode != "fp32" and _tc_wgrad_ok(cout, cin):
-            # one tcgen05 weight-gradient GEMM per tap: the tap's row shift is a TMA coordinate offset
-            npl = 2 if ctx.mode == "bf16x3" else 1
-            dzp, sigp = ops.pack_planes([dz], npl), ops.pack_planes([sig], npl)
-            half = k // 2
-            dw = torch.stack([wgrad_planes(dzp, sigp, tap - half).t() for tap in range(k)], dim=0)   # (k, cin, cout)
-            db = col_sum(dz)
-        elif ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
+            dsig = ops.curve_conv_layer(dz, wt, _zeros((cin,), dz), _iota32(1, dz), rows, rows, k, False, False, slope=1.0)
+        if need_w:
             dw = _zeros((k, cin, cout), dz)
             db = _zeros((cout,), dz)
-            half = k // 2
             for tap in range(k):
                 off = tap - half                  # z[r] reads sig[r + off]
                 lo, hi = max(0, -off), min(rows, rows - off)

@@ -48,6 +48,7 @@ struct PlanesParams {
     float slope;
     int nseg;               // A = [A_0 | A_1 | ...] along K: every segment is its own planes tensor
     int sc1, sc2, sc3, nk;  // first 64-wide K chunk of segments 1..3 (= nk for absent segments), total chunks
+    int taps, cpt;          // taps > 0: curve convolution - K = taps x (cpt chunks of segment 0), tap t reads rows m + t - taps/2
 };
 
 __device__ __forceinline__ void st_global_256(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e,
@@ -120,7 +121,12 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                 for (int kc = 0; kc < nk; ++kc, ++cnt) {
                     const CUtensorMap *mh, *ml;
                     int ka;                                             // column inside the segment's planes
-                    if (kc < p.sc1) { mh = &am.hi[0]; ml = &am.lo[0]; ka = kc * kBK; }
+                    int roff = 0;                                       // row shift of a convolution tap
+                    if (p.taps) {
+                        const int tap = kc / p.cpt;
+                        mh = &am.hi[0]; ml = &am.lo[0]; ka = (kc - tap * p.cpt) * kBK; roff = tap - (p.taps >> 1);
+                    }
+                    else if (kc < p.sc1) { mh = &am.hi[0]; ml = &am.lo[0]; ka = kc * kBK; }
                     else if (kc < p.sc2) { mh = &am.hi[1]; ml = &am.lo[1]; ka = (kc - p.sc1) * kBK; }
                     else if (kc < p.sc3) { mh = &am.hi[2]; ml = &am.lo[2]; ka = (kc - p.sc2) * kBK; }
                     else { mh = &am.hi[3]; ml = &am.lo[3]; ka = (kc - p.sc3) * kBK; }
@@ -128,8 +134,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     mbar_wait(empty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
                     const uint32_t dst = ring0 + s * stage_bytes;
                     mbar_arrive_expect_tx(full0 + 8 * s, (uint32_t)stage_bytes);
-                    tma_load_2d(dst, mh, ka, m0, full0 + 8 * s);
-                    if (P == 2) tma_load_2d(dst + kATile, ml, ka, m0, full0 + 8 * s);
+                    tma_load_2d(dst, mh, ka, m0 + roff, full0 + 8 * s);      // rows outside [0, M) arrive as zeros
+                    if (P == 2) tma_load_2d(dst + kATile, ml, ka, m0 + roff, full0 + 8 * s);
                     if (!p.resident) {
                         tma_load_2d(dst + P * kATile, &w_hi, kc * kBK, n0, full0 + 8 * s);
                         if (P == 2) tma_load_2d(dst + P * kATile + wtile, &w_lo, kc * kBK, n0, full0 + 8 * s);
@@ -328,15 +334,12 @@ extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const i
     return CCN_OK;
 }
 
-extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, const void* a1, int64_t ld1,
-                                 int64_t ps1, int32_t k1, const void* a2, int64_t ld2, int64_t ps2, int32_t k2,
-                                 const void* a3, int64_t ld3, int64_t ps3, int32_t k3, const void* w_hi_tmap_host,
-                                 const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes,
-                                 int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n,
-                                 int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
-    const void* ap[kMaxSeg] = {a0, a1, a2, a3};
-    const int64_t ald[kMaxSeg] = {ld0, ld1, ld2, ld3}, aps[kMaxSeg] = {ps0, ps1, ps2, ps3};
-    const int32_t ak[kMaxSeg] = {k0, k1, k2, k3};
+static int launch_planes(const void* const* ap, const int64_t* ald, const int64_t* aps, const int32_t* ak, int32_t taps,
+                         const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias, float* Y,
+                         int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
+                         int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
+    const void* a0 = ap[0];
+    const int32_t k0 = ak[0];
     CCN_REQUIRE(a0 && k0 > 0 && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0);
     CCN_REQUIRE((mode == 1 || (mode == 3 && w_lo_tmap_host)) && act >= 0 && act <= 2);
     CCN_REQUIRE(box_n == 32 || box_n == 64 || box_n == 128 || box_n == 256);
@@ -361,6 +364,11 @@ extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32
         chunk0[i + 1] = chunk0[p.nseg];
     }
     p.sc1 = chunk0[1]; p.sc2 = chunk0[2]; p.sc3 = chunk0[3]; p.nk = chunk0[p.nseg];
+    p.taps = 0; p.cpt = 0;
+    if (taps > 0) {
+        CCN_REQUIRE(p.nseg == 1 && (taps & 1) && taps <= 15);
+        p.taps = taps; p.cpt = chunk0[1]; p.nk = taps * p.cpt;
+    }
     if (M == 0) return CCN_OK;
     const int P = mode == 3 ? 2 : 1;
     p.bias = bias; p.Y = Y; p.ldy = ldy; p.Yp = (__nv_bfloat16*)y_planes; p.yp_ld = yp_ld; p.yp_plane = yp_plane_stride;
@@ -418,4 +426,32 @@ extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;
+}
+
+extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, const void* a1, int64_t ld1,
+                                 int64_t ps1, int32_t k1, const void* a2, int64_t ld2, int64_t ps2, int32_t k2,
+                                 const void* a3, int64_t ld3, int64_t ps3, int32_t k3, const void* w_hi_tmap_host,
+                                 const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes,
+                                 int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n,
+                                 int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
+    const void* ap[kMaxSeg] = {a0, a1, a2, a3};
+    const int64_t ald[kMaxSeg] = {ld0, ld1, ld2, ld3}, aps[kMaxSeg] = {ps0, ps1, ps2, ps3};
+    const int32_t ak[kMaxSeg] = {k0, k1, k2, k3};
+    return launch_planes(ap, ald, aps, ak, 0, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
+                         yp_plane_stride, M, N, box_n, mode, act, slope, stream);
+}
+
+// 'same' zero-padded 1-D convolution along the row axis as ONE GEMM: K = taps x cin, tap t of output row m reads
+// input row m + t - taps/2 (a TMA row coordinate; rows outside the signal arrive as zeros).  W: (N, taps x cin) in the
+// ccn_split_bf16 layout with every tap's cin columns starting at a multiple of 64.
+extern "C" int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t taps,
+                               const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias, float* Y,
+                               int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
+                               int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
+    const void* ap[kMaxSeg] = {a, nullptr, nullptr, nullptr};
+    const int64_t ald[kMaxSeg] = {ld, 0, 0, 0}, aps[kMaxSeg] = {ps, 0, 0, 0};
+    const int32_t ak[kMaxSeg] = {cin, 0, 0, 0};
+    CCN_REQUIRE(taps >= 1);
+    return launch_planes(ap, ald, aps, ak, taps, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
+                         yp_plane_stride, M, N, box_n, mode, act, slope, stream);
 }

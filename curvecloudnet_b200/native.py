@@ -77,7 +77,7 @@ _prof_events = []          # (name, start event, end event, algorithmic work of 
 # algorithmic work of one call: FLOPs for the Linear kernels (2 M N K)
 _MNK = {"ccn_linear_f32": lambda a: (a[7], a[8], a[9]), "ccn_linear_tc": lambda a: (a[7], a[8], a[9]),
         "ccn_linear_planes": lambda a: (a[24], a[25], a[3] + a[7] + a[11] + a[15]),
-        "ccn_linear_wgrad": lambda a: (a[4], a[5], a[6])}
+        "ccn_linear_wgrad": lambda a: (a[4], a[5], a[6]), "ccn_linear_wgrad_tc": lambda a: (a[6], a[7], a[8])}
 _WORK = {name: (lambda a, f=f: 2.0 * f(a)[0] * f(a)[1] * f(a)[2]) for name, f in _MNK.items()}
 
 

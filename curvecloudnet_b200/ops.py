@@ -644,6 +644,23 @@ def linear_planes(A, tw: "TcWeight", bias: Optional[torch.Tensor], act: int, slo
     return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)
 
 
+def conv_planes(sig: "Planes", w_kio: torch.Tensor, bias: Optional[torch.Tensor], act: int = ACT_NONE, slope: float = 0.01,
+                tw: "TcWeight" = None) -> torch.Tensor:
+    """'same' zero-padded 1-D convolution along the rows of `sig` (planes of a (rows, cin) signal) as ONE tcgen05 GEMM:
+    w_kio (taps, cin, cout); tap t of output row m reads row m + t - taps/2 (ccn_conv_planes).  fp32 (rows, cout)."""
+    taps, cin, cout = w_kio.shape
+    assert sig.k == cin
+    if tw is None:
+        tw = TcWeight(w_kio.permute(2, 0, 1).reshape(cout, taps * cin).contiguous(), [cin] * taps if taps > 1 else None)
+    M = sig.m
+    Y = _empty((M, cout), torch.float32, sig.buf)
+    box = tw.pick_box_planes(M, sig.n_planes)
+    w_hi, w_lo, _ = tw.maps(box)
+    call("ccn_conv_planes", sig.buf, sig.kpad, sig.buf.stride(0), cin, taps, w_hi, w_lo, bias if bias is not None else 0,
+         Y, cout, 0, 0, 0, M, cout, box, 3 if sig.n_planes == 2 else 1, act, float(slope))
+    return Y
+
+
 def prepare_tc_weight(w: torch.Tensor, seg_widths=None) -> TcWeight:
     return TcWeight(w, seg_widths)
 

@@ -286,6 +286,14 @@ int ccn_col_sum(const float* src, int64_t ld, int64_t M, int32_t C, float* out, 
 int ccn_linear_wgrad_tc(const void* dy_planes, int64_t dy_ld, int64_t dy_plane_stride, const void* x_planes,
                         int64_t x_ld, int64_t x_plane_stride, int64_t M, int32_t N, int32_t K, int32_t x_row_off,
                         int64_t x_rows, int32_t mode, float* dW, int64_t lddw, ccn_stream_t stream);
+/* 'same' zero-padded 1-D convolution along the ROW axis of an activation-planes signal as one tcgen05 GEMM
+ * (fast_conv1d.py:148-187 F.conv1d): K = taps x cin, tap t of output row m reads input row m + t - taps/2 through a
+ * TMA row coordinate (rows outside [0, M) are zeros).  W: (N, taps x cin) in the ccn_split_bf16 layout, every tap's
+ * cin columns starting at a multiple of 64.  Other arguments as ccn_linear_planes. */
+int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t taps, const void* w_hi_tmap_host,
+                    const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
+                    int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n, int32_t mode, int32_t act, float slope,
+                    ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -234,8 +234,9 @@ def _curves(n, seed):
     return torch.repeat_interleave(torch.arange(len(lens)), torch.tensor(lens))
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
 @pytest.mark.parametrize("k", [1, 5, 7])
-def test_curve_conv_stack_grads(k):
+def test_curve_conv_stack_grads(k, precision):
     """pad -> conv -> BatchNorm(train) -> LeakyReLU -> unpad, and the feature differences, against torch."""
     A, nn, ops = _A()
     from oracle.ccn_modules import feature_diffs
@@ -251,12 +252,16 @@ def test_curve_conv_stack_grads(k):
     bn = torch.nn.BatchNorm1d(cout).to(DEV)
     pad = k // 2
     row2pt = ops.curve_row_map(topo, pad)
-    feats = A.curve_feat_prep(x, pos, True, True, topo.curve_ord)
-    sig = A.pad_rows(feats, row2pt)
-    z = A.curve_conv(sig, w.permute(2, 1, 0), b, k)
-    y = A.unpad_rows(A.bn_act(z, bn, ops.ACT_LEAKY, 0.01), row2pt, n)
     g = torch.randn(n, cout, device=DEV)
-    y.backward(g)
+    nn.set_precision(precision)          # bf16x3: conv forward / data gradient / weight gradient on tcgen05
+    try:
+        feats = A.curve_feat_prep(x, pos, True, True, topo.curve_ord)
+        sig = A.pad_rows(feats, row2pt)
+        z = A.curve_conv(sig, w.permute(2, 1, 0), b, k)
+        y = A.unpad_rows(A.bn_act(z, bn, ops.ACT_LEAKY, 0.01), row2pt, n)
+        y.backward(g)
+    finally:
+        nn.set_precision("fp32")
 
     x2 = x.detach().cpu().double().requires_grad_()
     w2, b2 = w.detach().cpu().double().requires_grad_(), b.detach().cpu().double().requires_grad_()
@@ -270,11 +275,12 @@ def test_curve_conv_stack_grads(k):
     ref_bn = torch.nn.BatchNorm1d(cout).double()
     y2 = F.leaky_relu(ref_bn(z2))[valid]
     y2.backward(g.cpu().double())
-    _close(y, y2, 3e-5, "y")
-    _close(x.grad, x2.grad, 1e-4, "dx")
-    _close(w.grad, w2.grad, 1e-4, "dw")
+    t = 1.0 if precision == "fp32" else 3.0
+    _close(y, y2, 3e-5 * t, "y")
+    _close(x.grad, x2.grad, 1e-4 * t, "dx")
+    _close(w.grad, w2.grad, 1e-4 * t, "dw")
     # the bias sits in front of a batch-statistics BatchNorm: its true gradient is zero, compare on dw's scale
-    assert float((b.grad.cpu().double() - b2.grad).abs().max()) <= 1e-4 * float(w2.grad.abs().max())
+    assert float((b.grad.cpu().double() - b2.grad).abs().max()) <= 1e-4 * t * float(w2.grad.abs().max())
 
 
 def test_nll_loss():
