@@ -84,13 +84,13 @@ class _Linear(Function):
         if mode == "fp32" or x.shape[0] == 0:
             ctx.save_for_backward(x, w)
             return ops.linear(x, wd, bd, ops.ACT_NONE)
-        xp = ops.pack_planes([x], 2 if mode == "bf16x3" else 1)
+        xp = _planes_of(x, _npl(mode)) or ops.pack_planes([x], _npl(mode))
         if _tc_wgrad_ok(wd.shape[0], wd.shape[1]):
             ctx.xp = xp
             ctx.save_for_backward(None, w)
         else:
             ctx.save_for_backward(x, w)
-        return ops.linear_planes(xp, ops.TcWeight(wd), bd, ops.ACT_NONE, 0.0, "f32")
+        return ops.linear_planes(xp, ops.tc_weight_scratch(wd), bd, ops.ACT_NONE, 0.0, "f32")
 
     @staticmethod
     def backward(ctx, dy):
@@ -103,13 +103,15 @@ class _Linear(Function):
             if need_w:
                 dW, db = linear_wgrad(dy, x, ctx.has_bias)
             return dx, dW, db
-        dyp = ops.pack_planes([dy], 2 if ctx.mode == "bf16x3" else 1)
+        dyp = _planes_of(dy, _npl(ctx.mode)) or ops.pack_planes([dy], _npl(ctx.mode))
         if ctx.needs_input_grad[0]:
-            dx = ops.linear_planes(dyp, ops.TcWeight(w.detach().t().contiguous()), None, ops.ACT_NONE, 0.0, "f32")
+            dx = ops.linear_planes(dyp, ops.tc_weight_scratch(w.detach().t().contiguous()), None, ops.ACT_NONE, 0.0, "f32")
         if need_w:
             if ctx.xp is not None:
                 dW = wgrad_planes(dyp, ctx.xp)
-                db = col_sum(dy) if ctx.has_bias else None
+                db = (getattr(dy, "_ccn_colsum", None) if ctx.has_bias else None)
+                if ctx.has_bias and db is None:
+                    db = col_sum(dy)
             else:
                 dW, db = linear_wgrad(dy, x, ctx.has_bias)
         ctx.xp = None
@@ -123,14 +125,34 @@ def linear(x, w, b=None):
 # ----------------------------------------------------------------------------------------------
 # BatchNorm (+ activation), dropout
 # ----------------------------------------------------------------------------------------------
+def _npl(mode: str) -> int:
+    return {"fp32": 0, "bf16x3": 2, "bf16": 1}[mode]
+
+
+def _planes_of(t: torch.Tensor, npl: int):
+    """Activation planes a producer kernel attached to `t` (same values, same shape), else None."""
+    pl = getattr(t, "_ccn_planes", None)
+    if pl is not None and pl.n_planes == npl and pl.shape == tuple(t.shape):
+        return pl
+    return None
+
+
 class _BNAct(Function):
+    """act(BatchNorm(z)).  On the tensor-core modes the forward kernel ALSO writes y as activation planes and the
+    backward kernel writes dz as planes plus the column sums of dz; they ride on the returned tensors
+    (`_ccn_planes`, `_ccn_colsum`) so that the Linear behind / in front needs no pack and no bias-gradient pass."""
+
     @staticmethod
-    def forward(ctx, z, gamma, beta, bn, act, slope, batch_stats):
+    def forward(ctx, z, gamma, beta, bn, act, slope, batch_stats, dz_planes=True):
         z, ldz = ops._rows(z)
         M, C = z.shape
         y = _empty((M, C), z)
+        npl = _npl(_precision()) if M > 0 else 0
+        ctx.npl = npl if dz_planes else 0
+        yp = ops.alloc_planes(M, C, npl, z) if npl else None
+        pargs = (yp.buf, yp.kpad, yp.plane_stride, npl) if npl else (0, 0, 0, 0)
         if gamma is None:
-            call("ccn_bn_apply", z, ldz, M, C, 0, 0, 0, 0, act, float(slope), y, C)
+            call("ccn_bn_apply", z, ldz, M, C, 0, 0, 0, 0, act, float(slope), y, C, *pargs)
             mean = invstd = None
         else:
             if batch_stats:
@@ -145,9 +167,12 @@ class _BNAct(Function):
             else:
                 mean = bn.running_mean
                 invstd = torch.rsqrt(bn.running_var + bn.eps)           # C values: weight preparation
-            call("ccn_bn_apply", z, ldz, M, C, mean, invstd, gamma.detach(), beta.detach(), act, float(slope), y, C)
+            call("ccn_bn_apply", z, ldz, M, C, mean, invstd, gamma.detach(), beta.detach(), act, float(slope), y, C,
+                 *pargs)
         ctx.save_for_backward(z, gamma, beta, mean, invstd)
         ctx.cfg = (act, float(slope), bool(batch_stats))
+        if yp is not None:
+            y._ccn_planes = yp
         return y
 
     @staticmethod
@@ -158,23 +183,32 @@ class _BNAct(Function):
         z, ldz = ops._rows(z)
         M, C = z.shape
         dz = _empty((M, C), z)
+        npl = ctx.npl
+        dzp = ops.alloc_planes(M, C, npl, z) if npl else None
+        pargs = (dzp.buf, dzp.kpad, dzp.plane_stride, npl) if npl else (0, 0, 0, 0)
         if gamma is None:
-            call("ccn_bn_backward", dy, lddy, z, ldz, M, C, 0, 0, 0, 0, act, slope, 0, 0, dz, C, 0, 0)
-            return dz, None, None, None, None, None, None
-        dgamma, dbeta = _empty((C,), z), _empty((C,), z)
-        sums = _empty((2 * C,), z, torch.float64)
-        call("ccn_bn_backward", dy, lddy, z, ldz, M, C, mean, invstd, gamma.detach(), beta.detach(), act, slope,
-             int(batch_stats), sums, dz, C, dgamma, dbeta)
-        return dz, dgamma, dbeta, None, None, None, None
+            call("ccn_bn_backward", dy, lddy, z, ldz, M, C, 0, 0, 0, 0, act, slope, 0, 0, dz, C, 0, 0, 0, *pargs)
+        else:
+            dgamma, dbeta, dzsum = _empty((C,), z), _empty((C,), z), _empty((C,), z)
+            sums = _empty((2 * C,), z, torch.float64)
+            call("ccn_bn_backward", dy, lddy, z, ldz, M, C, mean, invstd, gamma.detach(), beta.detach(), act, slope,
+                 int(batch_stats), sums, dz, C, dgamma, dbeta, dzsum, *pargs)
+            dz._ccn_colsum = dzsum
+        if dzp is not None:
+            dz._ccn_planes = dzp
+        if gamma is None:
+            return dz, None, None, None, None, None, None, None
+        return dz, dgamma, dbeta, None, None, None, None, None
 
 
-def bn_act(z, bn: Optional[torch.nn.BatchNorm1d], act: int, slope: float):
-    """act(BatchNorm1d(z)) (bn None: act(z)); batch statistics iff bn.training."""
+def bn_act(z, bn: Optional[torch.nn.BatchNorm1d], act: int, slope: float, dz_planes: bool = True):
+    """act(BatchNorm1d(z)) (bn None: act(z)); batch statistics iff bn.training.  dz_planes=False: the producer of z is
+    not a GEMM (per-edge gather layers), so backward need not emit dz as planes."""
     if bn is None:
         if act == ops.ACT_NONE:
             return z
-        return _BNAct.apply(z, None, None, None, act, slope, False)
-    return _BNAct.apply(z, bn.weight, bn.bias, bn, act, slope, bn.training)
+        return _BNAct.apply(z, None, None, None, act, slope, False, dz_planes)
+    return _BNAct.apply(z, bn.weight, bn.bias, bn, act, slope, bn.training, dz_planes)
 
 
 class _Dropout(Function):
@@ -220,12 +254,12 @@ def mlp_train(mlp, x, first: int = 0):
     return x
 
 
-def hidden_tail(mlp, i: int, z):
+def hidden_tail(mlp, i: int, z, dz_planes: bool = True):
     """BatchNorm -> act -> dropout of hidden layer i applied to its pre-activation z."""
     act, slope = _ACTS[mlp.act_name]
     norm = mlp.norms[i] if i < len(mlp.norms) else None
     bn = norm.module if norm is not None and hasattr(norm, "module") else None
-    z = bn_act(z, bn, act, slope)
+    z = bn_act(z, bn, act, slope, dz_planes)
     return dropout(z, mlp.dropout[i], mlp.training)
 
 
@@ -568,7 +602,7 @@ class _CurveConv(Function):
         wd = w.detach().contiguous()
         ctx.tc = mode != "fp32" and rows > 0 and wd.shape[1] >= 16 and wd.shape[2] >= 16
         if ctx.tc:
-            sigp = ops.pack_planes([sig], 2 if mode == "bf16x3" else 1)
+            sigp = _planes_of(sig, _npl(mode)) or ops.pack_planes([sig], _npl(mode))
             ctx.sigp = sigp
             ctx.save_for_backward(None, w)
             return ops.conv_planes(sigp, wd, b.detach())
@@ -579,7 +613,7 @@ class _CurveConv(Function):
     def backward(ctx, dz):
         sig, w = ctx.saved_tensors
         k = ctx.ksize
-        dz = dz.contiguous()
+        dz_in, dz = dz, dz.contiguous()
         rows, cout = dz.shape
         cin = w.shape[1]
         dsig = dw = db = None
@@ -587,7 +621,7 @@ class _CurveConv(Function):
         need_w = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
         wt = torch.flip(w.detach(), dims=[0]).transpose(1, 2).contiguous()           # (k, cout, cin): weight prep
         if ctx.tc:
-            dzp = ops.pack_planes([dz], 2 if ctx.mode == "bf16x3" else 1)
+            dzp = _planes_of(dz_in, _npl(ctx.mode)) or ops.pack_planes([dz], _npl(ctx.mode))
             if ctx.needs_input_grad[0]:
                 dsig = ops.conv_planes(dzp, wt, None)
             if need_w:

@@ -20,8 +20,9 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, int64_t lds, c
                                    int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
     const int64_t total = n * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t i = t / c;
-        const int k = (int)(t - i * c);
+        int64_t i;
+        int k;
+        ccn_divmod(t, c, i, k);
         const int64_t s = idx ? idx[i] : i;
         dst[i * ldd + k] = src[s * lds + k];
     }
@@ -38,8 +39,9 @@ __global__ void dense_to_csr_kernel(const int32_t* __restrict__ idx, const int32
                                     int K, int32_t* __restrict__ erow, int32_t* __restrict__ ecol) {
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t >= nq * K) return;
-    const int64_t q = t / K;
-    const int k = (int)(t - q * K);
+    int64_t q;
+    int k;
+    ccn_divmod(t, K, q, k);
     const int b = row_ptr[q], cnt = row_ptr[q + 1] - b;
     if (k < cnt) {
         erow[b + k] = (int32_t)q;
@@ -62,8 +64,9 @@ __global__ void edge_layer1_kernel(const float* __restrict__ H, int64_t ldh, con
                                    float radius, int act, float slope, float* __restrict__ out, int64_t ldo) {
     const int64_t total = E * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t e = t / c;
-        const int k = (int)(t - e * c);
+        int64_t e;
+        int k;
+        ccn_divmod(t, c, e, k);
         const int j = ecol[e], i = erow[e];
         float rx = __fsub_rn(pos_src[3 * j], pos_dst[3 * i]);
         float ry = __fsub_rn(pos_src[3 * j + 1], pos_dst[3 * i + 1]);
@@ -85,8 +88,9 @@ __global__ void seg_aggregate_kernel(const float* __restrict__ msg, int64_t ldm,
                                      float* __restrict__ out, int64_t ldo) {
     const int64_t total = nq * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t q = t / c;
-        const int k = (int)(t - q * c);
+        int64_t q;
+        int k;
+        ccn_divmod(t, c, q, k);
         const int b = row_ptr[q], e = row_ptr[q + 1];
         float r = 0.f;
         if (mode == CCN_AGG_MAX) {
@@ -123,8 +127,9 @@ __global__ void sgcnn_layer1_kernel(const float* __restrict__ PQ, int64_t ldpq, 
     const int G = K + 1;
     const int64_t total = n * (int64_t)G * c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t row = t / c;
-        const int k = (int)(t - row * c);
+        int64_t row;
+        int k;
+        ccn_divmod(t, c, row, k);
         const int64_t i = row / G;
         const int g = (int)(row - i * G);
         const int j = g == 0 ? (int)i : idx[i * K + g - 1];
@@ -139,8 +144,9 @@ __global__ void edge_pair_layer1_kernel(const float* __restrict__ PQ, int64_t ld
                                         float* __restrict__ out, int64_t ldo) {
     const int64_t total = E * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t e = t / c;
-        const int k = (int)(t - e * c);
+        int64_t e;
+        int k;
+        ccn_divmod(t, c, e, k);
         const float y = PQ[(int64_t)ecol[e] * ldpq + k] + PQ[(int64_t)erow[e] * ldpq + c + k];
         out[e * ldo + k] = apply_act(y, act, slope);
     }
@@ -152,8 +158,9 @@ __global__ void group_max_dense_kernel(const float* __restrict__ feat, int64_t l
     const int G = K + 1;
     const int64_t total = n * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t i = t / c;
-        const int k = (int)(t - i * c);
+        int64_t i;
+        int k;
+        ccn_divmod(t, c, i, k);
         float r = feat[(i * G) * ldf + k];
         for (int g = 1; g < G; ++g) {
             const float v = idx[i * K + g - 1] >= 0 ? feat[(i * G + g) * ldf + k] : -100.f;
@@ -169,8 +176,9 @@ __global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, co
                                     float* __restrict__ out, int64_t ldo) {
     const int64_t total = n * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t i = t / c;
-        const int k = (int)(t - i * c);
+        int64_t i;
+        int k;
+        ccn_divmod(t, c, i, k);
         float num = 0.f, den = 0.f;
         for (int s = 0; s < knn; ++s) {
             const int j = nbr[i * knn + s];
@@ -213,8 +221,10 @@ __global__ void sgcnn_layer1_planes_kernel(const float* __restrict__ PQ, int64_t
     const int G = K + 1, cg = c >> 3;
     const int64_t total = n * (int64_t)G * cg;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t row = t / cg;
-        const int k = (int)(t - row * cg) << 3;
+        int64_t row;
+        int k;
+        ccn_divmod(t, cg, row, k);
+        k <<= 3;
         const int64_t i = row / G;
         const int g = (int)(row - i * G);
         const int j = g == 0 ? (int)i : idx[i * K + g - 1];
@@ -237,8 +247,10 @@ __global__ void edge_pair_layer1_planes_kernel(const float* __restrict__ PQ, int
     const int cg = c >> 3;
     const int64_t total = E * (int64_t)cg;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t e = t / cg;
-        const int k = (int)(t - e * cg) << 3;
+        int64_t e;
+        int k;
+        ccn_divmod(t, cg, e, k);
+        k <<= 3;
         F8 y = ld8(PQ + (int64_t)ecol[e] * ldpq + k);
         const F8 q = ld8(PQ + (int64_t)erow[e] * ldpq + c + k);
 #pragma unroll
@@ -256,8 +268,10 @@ __global__ void edge_layer1_planes_kernel(const float* __restrict__ H, int64_t l
     const int cg = c >> 3;
     const int64_t total = E * (int64_t)cg;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t e = t / cg;
-        const int k = (int)(t - e * cg) << 3;
+        int64_t e;
+        int k;
+        ccn_divmod(t, cg, e, k);
+        k <<= 3;
         const int j = ecol[e], i = erow[e];
         float rx = __fsub_rn(pos_src[3 * j], pos_dst[3 * i]);
         float ry = __fsub_rn(pos_src[3 * j + 1], pos_dst[3 * i + 1]);

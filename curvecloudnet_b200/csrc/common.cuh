@@ -53,6 +53,19 @@ __device__ __forceinline__ unsigned long long ccn_pack_key(float d2, int idx) {
     return ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)idx;
 }
 
+// q = t / c, rem = t % c for a flat element index: 32-bit division whenever the index fits (a 64-bit integer division
+// costs several times the rest of an element-wise kernel's body)
+__device__ __forceinline__ void ccn_divmod(int64_t t, int c, int64_t& q, int& rem) {
+    if ((unsigned long long)t < 0x80000000ull) {
+        const unsigned tt = (unsigned)t, qq = tt / (unsigned)c;
+        q = qq;
+        rem = (int)(tt - qq * (unsigned)c);
+    } else {
+        q = t / c;
+        rem = (int)(t - q * c);
+    }
+}
+
 __device__ __forceinline__ int ccn_lane() { return threadIdx.x & 31; }
 __device__ __forceinline__ int ccn_warp() { return threadIdx.x >> 5; }
 

@@ -18,8 +18,9 @@ __global__ void curve_feat_prep_kernel(const float* __restrict__ x, int64_t ldx,
     const int c_in = cx + (with_xyz ? 3 : 0);
     const int64_t total = n * (int64_t)c_in;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t i = t / c_in;
-        const int c = (int)(t - i * c_in);
+        int64_t i;
+        int c;
+        ccn_divmod(t, c_in, i, c);
         auto feat = [&](int64_t r) -> float { return c < cx ? x[r * ldx + c] : pos[r * 3 + (c - cx)]; };
         const float v = feat(i);
         out[i * ldo + c] = v;

@@ -283,8 +283,9 @@ __global__ void pack_planes_kernel(const PackSrc s, int64_t n, int ctot, __nv_bf
     const int64_t total = n * groups;
     const int e0 = s.c[0], e1 = e0 + s.c[1], e2 = e1 + s.c[2];
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t i = t / groups;
-        const int g = (int)(t - i * groups);
+        int64_t i;
+        int g;
+        ccn_divmod(t, groups, i, g);
         float v[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {

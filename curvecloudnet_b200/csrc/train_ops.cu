@@ -8,9 +8,23 @@
 //   * segmented max / mean / sigmoid-weighted / softmax-attention aggregation backward
 //   * dense (K+1)-slot max backward, inverse-distance interpolation backward, curve feature-difference backward
 //   * log-softmax + NLL loss forward/backward.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace {
+
+// optional second output of the BatchNorm kernels: the value as split-bf16 activation planes (gemm_planes.cu)
+struct PlanesOut {
+    __nv_bfloat16* p;      // null: no planes
+    int64_t kpad, stride;  // row stride / plane stride in elements
+    int n;                 // 1 = bf16, 2 = hi + lo
+};
+__device__ __forceinline__ void st_plane(const PlanesOut& po, int64_t r, int c, float v) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    po.p[r * po.kpad + c] = h;
+    if (po.n == 2) po.p[po.stride + r * po.kpad + c] = __float2bfloat16_rn(v - __bfloat162float(h));
+}
 
 #define ELT_GRID(total) ccn_grid((total), 256, 148LL * 16)
 #define GRID_STRIDE(t, total) \
@@ -33,8 +47,9 @@ __global__ void gather_rows_i32_kernel(const float* __restrict__ src, int64_t ld
                                        int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
-        const int64_t r = t / c;
-        const int k = (int)(t - r * c);
+        int64_t r;
+        int k;
+        ccn_divmod(t, c, r, k);
         const int s = idx[r];
         dst[r * ldd + k] = s >= 0 ? src[(int64_t)s * lds + k] : 0.f;
     }
@@ -46,8 +61,9 @@ __global__ void scatter_add_rows_kernel(const float* __restrict__ src, int64_t l
                                         int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
-        const int64_t r = t / c;
-        const int k = (int)(t - r * c);
+        int64_t r;
+        int k;
+        ccn_divmod(t, c, r, k);
         const int64_t d = (int64_t)idx[r];
         if (d >= 0) atomicAdd(dst + d * ldd + k, src[r * lds + k]);
     }
@@ -58,8 +74,9 @@ __global__ void group_sum_rows_kernel(const float* __restrict__ src, int64_t lds
                                       float* __restrict__ dst, int64_t ldd, int accumulate) {
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
-        const int64_t i = t / c;
-        const int k = (int)(t - i * c);
+        int64_t i;
+        int k;
+        ccn_divmod(t, c, i, k);
         float s = 0.f;
         for (int g = 0; g < G; ++g) s += src[(i * G + g) * lds + k];
         float* o = dst + i * ldd + k;
@@ -173,14 +190,21 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, int64_t M, i
 __global__ void bn_apply_kernel(const float* __restrict__ z, int64_t ldz, int64_t M, int C,
                                 const float* __restrict__ mean, const float* __restrict__ invstd,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, int act, float slope,
-                                float* __restrict__ y, int64_t ldy) {
-    const int64_t total = M * (int64_t)C;
+                                float* __restrict__ y, int64_t ldy, const PlanesOut po) {
+    const int W = po.p ? (int)po.kpad : C;               // with planes: the pad columns are written too (zeros)
+    const int64_t total = M * (int64_t)W;
     GRID_STRIDE(t, total) {
-        const int64_t r = t / C;
-        const int c = (int)(t - r * C);
-        float v = z[r * ldz + c];
-        if (gamma) v = fmaf((v - mean[c]) * invstd[c], gamma[c], beta[c]);
-        y[r * ldy + c] = act_fwd(v, act, slope);
+        int64_t r;
+        int c;
+        ccn_divmod(t, W, r, c);
+        float o = 0.f;
+        if (c < C) {
+            float v = z[r * ldz + c];
+            if (gamma) v = fmaf((v - mean[c]) * invstd[c], gamma[c], beta[c]);
+            o = act_fwd(v, act, slope);
+            y[r * ldy + c] = o;
+        }
+        if (po.p) st_plane(po, r, c, o);
     }
 }
 
@@ -217,31 +241,149 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ dy, int64_t lddy, 
                                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                                     const float* __restrict__ beta, int act, float slope, int batch_stats,
                                     const double* __restrict__ sums, float* __restrict__ dz, int64_t lddz,
-                                    float* __restrict__ dgamma, float* __restrict__ dbeta) {
-    const int64_t total = M * (int64_t)C;
+                                    float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dzsum,
+                                    const PlanesOut po) {
     if (gamma && blockIdx.x == 0) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             if (dbeta) dbeta[c] = (float)sums[c];
             if (dgamma) dgamma[c] = (float)sums[C + c];
+            // column sums of dz (the bias gradient of the Linear in front): identically zero under batch statistics
+            // (sum xhat = 0), gamma * invstd * sum g on running statistics
+            if (dzsum) dzsum[c] = batch_stats ? 0.f : gamma[c] * invstd[c] * (float)sums[c];
         }
     }
     const float inv_m = 1.f / (float)M;
+    const int W = po.p ? (int)po.kpad : C;
+    const int64_t total = M * (int64_t)W;
     GRID_STRIDE(t, total) {
-        const int64_t r = t / C;
-        const int c = (int)(t - r * C);
-        const float zv = z[r * ldz + c];
-        float out;
-        if (!gamma) {
-            out = dy[r * lddy + c] * act_grad(zv, act, slope);
-        } else {
-            const float is = invstd[c], ga = gamma[c];
-            const float xh = (zv - mean[c]) * is;
-            const float g = dy[r * lddy + c] * act_grad(fmaf(xh, ga, beta[c]), act, slope);
-            out = batch_stats ? ga * is * (g - (float)sums[c] * inv_m - xh * ((float)sums[C + c] * inv_m)) : ga * is * g;
+        int64_t r;
+        int c;
+        ccn_divmod(t, W, r, c);
+        float out = 0.f;
+        if (c < C) {
+            const float zv = z[r * ldz + c];
+            if (!gamma) {
+                out = dy[r * lddy + c] * act_grad(zv, act, slope);
+            } else {
+                const float is = invstd[c], ga = gamma[c];
+                const float xh = (zv - mean[c]) * is;
+                const float g = dy[r * lddy + c] * act_grad(fmaf(xh, ga, beta[c]), act, slope);
+                out = batch_stats ? ga * is * (g - (float)sums[c] * inv_m - xh * ((float)sums[C + c] * inv_m)) : ga * is * g;
+            }
+            dz[r * lddz + c] = out;
         }
-        dz[r * lddz + c] = out;
+        if (po.p) st_plane(po, r, c, out);
     }
 }
+
+
+// ---- float4 variants of the two BatchNorm element-wise kernels (C % 4 == 0, 16-byte aligned rows): no index
+// division, 16-byte loads / stores, 8-byte plane stores.  Thread = (row lane, group of 4 columns).
+__device__ __forceinline__ void st_plane4(const PlanesOut& po, int64_t r, int c, const float (&v)[4]) {
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 u;
+    u.x = *reinterpret_cast<uint32_t*>(&h0);
+    u.y = *reinterpret_cast<uint32_t*>(&h1);
+    *reinterpret_cast<uint2*>(po.p + r * po.kpad + c) = u;
+    if (po.n == 2) {
+        const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+        __nv_bfloat162 l0 = __floats2bfloat162_rn(v[0] - f0.x, v[1] - f0.y), l1 = __floats2bfloat162_rn(v[2] - f1.x, v[3] - f1.y);
+        u.x = *reinterpret_cast<uint32_t*>(&l0);
+        u.y = *reinterpret_cast<uint32_t*>(&l1);
+        *reinterpret_cast<uint2*>(po.p + po.stride + r * po.kpad + c) = u;
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_apply_v4_kernel(const float* __restrict__ z, int64_t ldz, int64_t M, int C,
+                                                          const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                          int act, float slope, float* __restrict__ y, int64_t ldy,
+                                                          const PlanesOut po) {
+    const int G = (po.p ? (int)po.kpad : C) >> 2;
+    const int tg = G < 256 ? G : 256, rows_pb = 256 / tg;
+    const int rl = threadIdx.x / tg, cg0 = threadIdx.x - rl * tg;
+    if (rl >= rows_pb) return;
+    for (int64_t r = (int64_t)blockIdx.x * rows_pb + rl; r < M; r += (int64_t)gridDim.x * rows_pb) {
+        for (int cg = cg0; cg < G; cg += tg) {
+            const int c = cg << 2;
+            float o[4] = {0.f, 0.f, 0.f, 0.f};
+            if (c < C) {
+                const float4 zv = *reinterpret_cast<const float4*>(z + r * ldz + c);
+                float v[4] = {zv.x, zv.y, zv.z, zv.w};
+                if (gamma) {
+                    const float4 mu = *reinterpret_cast<const float4*>(mean + c), is = *reinterpret_cast<const float4*>(invstd + c);
+                    const float4 ga = *reinterpret_cast<const float4*>(gamma + c), be = *reinterpret_cast<const float4*>(beta + c);
+                    v[0] = fmaf((v[0] - mu.x) * is.x, ga.x, be.x); v[1] = fmaf((v[1] - mu.y) * is.y, ga.y, be.y);
+                    v[2] = fmaf((v[2] - mu.z) * is.z, ga.z, be.z); v[3] = fmaf((v[3] - mu.w) * is.w, ga.w, be.w);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) o[j] = act_fwd(v[j], act, slope);
+                *reinterpret_cast<float4*>(y + r * ldy + c) = make_float4(o[0], o[1], o[2], o[3]);
+            }
+            if (po.p) st_plane4(po, r, c, o);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply_v4_kernel(
+    const float* __restrict__ dy, int64_t lddy, const float* __restrict__ z, int64_t ldz, int64_t M, int C,
+    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+    const float* __restrict__ beta, int act, float slope, int batch_stats, const double* __restrict__ sums,
+    float* __restrict__ dz, int64_t lddz, float* __restrict__ dgamma, float* __restrict__ dbeta,
+    float* __restrict__ dzsum, const PlanesOut po) {
+    if (gamma && blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < C; c += blockDim.x) {
+            if (dbeta) dbeta[c] = (float)sums[c];
+            if (dgamma) dgamma[c] = (float)sums[C + c];
+            if (dzsum) dzsum[c] = batch_stats ? 0.f : gamma[c] * invstd[c] * (float)sums[c];
+        }
+    }
+    const float inv_m = 1.f / (float)M;
+    const int G = (po.p ? (int)po.kpad : C) >> 2;
+    const int tg = G < 256 ? G : 256, rows_pb = 256 / tg;
+    const int rl = threadIdx.x / tg, cg0 = threadIdx.x - rl * tg;
+    if (rl >= rows_pb) return;
+    for (int cg = cg0; cg < G; cg += tg) {
+        const int c = cg << 2;
+        float mu[4] = {0, 0, 0, 0}, is[4] = {1, 1, 1, 1}, ga[4] = {1, 1, 1, 1}, be[4] = {0, 0, 0, 0}, s0[4] = {0, 0, 0, 0},
+              s1[4] = {0, 0, 0, 0};
+        if (gamma && c < C) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                mu[j] = mean[c + j]; is[j] = invstd[c + j]; ga[j] = gamma[c + j]; be[j] = beta[c + j];
+                s0[j] = (float)sums[c + j] * inv_m; s1[j] = (float)sums[C + c + j] * inv_m;
+            }
+        }
+        for (int64_t r = (int64_t)blockIdx.x * rows_pb + rl; r < M; r += (int64_t)gridDim.x * rows_pb) {
+            float o[4] = {0.f, 0.f, 0.f, 0.f};
+            if (c < C) {
+                const float4 zv4 = *reinterpret_cast<const float4*>(z + r * ldz + c);
+                const float4 dy4 = *reinterpret_cast<const float4*>(dy + r * lddy + c);
+                const float zv[4] = {zv4.x, zv4.y, zv4.z, zv4.w}, dv[4] = {dy4.x, dy4.y, dy4.z, dy4.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (!gamma) {
+                        o[j] = dv[j] * act_grad(zv[j], act, slope);
+                    } else {
+                        const float xh = (zv[j] - mu[j]) * is[j];
+                        const float g = dv[j] * act_grad(fmaf(xh, ga[j], be[j]), act, slope);
+                        o[j] = batch_stats ? ga[j] * is[j] * (g - s0[j] - xh * s1[j]) : ga[j] * is[j] * g;
+                    }
+                }
+                *reinterpret_cast<float4*>(dz + r * lddz + c) = make_float4(o[0], o[1], o[2], o[3]);
+            }
+            if (po.p) st_plane4(po, r, c, o);
+        }
+    }
+}
+
+static inline unsigned bn_v4_grid(int64_t M, int W) {
+    const int G = W >> 2, tg = G < 256 ? G : 256, rows_pb = 256 / tg;
+    int64_t b = (M + rows_pb - 1) / rows_pb;
+    const int64_t cap = 148LL * 16;
+    return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // ------------------------------------------------------------------------------------------------------------
 // Backward of ccn_seg_aggregate (agg_ops.cu seg_aggregate_kernel; point_conv.py:71-93, dgcnn.py:240-244).
@@ -257,8 +399,9 @@ __global__ void seg_aggregate_bwd_kernel(const float* __restrict__ msg, int64_t 
                                          int64_t lddm, float* __restrict__ datt, int64_t ldda) {
     const int64_t total = nq * (int64_t)c;
     GRID_STRIDE(t, total) {
-        const int64_t q = t / c;
-        const int k = (int)(t - q * c);
+        int64_t q;
+        int k;
+        ccn_divmod(t, c, q, k);
         const int b = row_ptr[q], e = row_ptr[q + 1];
         if (e <= b) continue;
         const float g = dout[q * ldo + k];
@@ -303,8 +446,9 @@ __global__ void group_max_dense_bwd_kernel(const float* __restrict__ feat, int64
     const int G = K + 1;
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
-        const int64_t i = t / c;
-        const int k = (int)(t - i * c);
+        int64_t i;
+        int k;
+        ccn_divmod(t, c, i, k);
         float r = feat[(i * G) * ldf + k];
         int arg = 0;
         for (int g = 1; g < G; ++g) {
@@ -323,8 +467,9 @@ __global__ void interp_blend_bwd_kernel(const int32_t* __restrict__ nbr, const f
                                         float* __restrict__ dx, int64_t lddx) {
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
-        const int64_t i = t / c;
-        const int k = (int)(t - i * c);
+        int64_t i;
+        int k;
+        ccn_divmod(t, c, i, k);
         float den = 0.f;
         for (int s = 0; s < knn; ++s) {
             if (nbr[i * knn + s] < 0) continue;
@@ -350,8 +495,9 @@ __global__ void curve_feat_prep_bwd_kernel(const float* __restrict__ x, int64_t 
                                            int64_t ldo, float* __restrict__ dx, int64_t lddx) {
     const int64_t total = n * (int64_t)cx;
     GRID_STRIDE(t, total) {
-        const int64_t i = t / cx;
-        const int c = (int)(t - i * cx);
+        int64_t i;
+        int c;
+        ccn_divmod(t, cx, i, c);
         float g = dout[i * ldo + c];
         if (with_diff) {
             auto same = [&](int64_t a, int64_t b) { return a >= 0 && b < n && ord[a] == ord[b]; };
@@ -381,8 +527,9 @@ __global__ void edge_rel_pos_kernel(const float* __restrict__ pos_src, const flo
                                     float radius, float* __restrict__ rel) {
     const int64_t total = E * 3;
     GRID_STRIDE(t, total) {
-        const int64_t e = t / 3;
-        const int a = (int)(t - e * 3);
+        int64_t e;
+        int a;
+        ccn_divmod(t, 3, e, a);
         float r = __fsub_rn(pos_src[3 * (int64_t)ecol[e] + a], pos_dst[3 * (int64_t)erow[e] + a]);
         if (radius != 0.f) r = __fdiv_rn(r, radius);
         rel[t] = r;
@@ -434,8 +581,9 @@ __global__ void nll_bwd_kernel(const float* __restrict__ logits, int64_t ld, con
     const int64_t total = n * (int64_t)C;
     const float gs = gscale[0] / (float)acc[1];
     GRID_STRIDE(t, total) {
-        const int64_t i = t / C;
-        const int c = (int)(t - i * C);
+        int64_t i;
+        int c;
+        ccn_divmod(t, C, i, c);
         const int64_t y = target[i];
         float g = 0.f;
         if (y != ignore && y >= 0 && y < C) {
@@ -452,8 +600,9 @@ __global__ void dropout_kernel(const float* __restrict__ x, int64_t ldx, const f
     const int64_t total = n * (int64_t)c;
     const float sc = 1.f / (1.f - p);
     GRID_STRIDE(t, total) {
-        const int64_t r = t / c;
-        const int k = (int)(t - r * c);
+        int64_t r;
+        int k;
+        ccn_divmod(t, c, r, k);
         y[r * ldy + k] = u[t] >= p ? x[r * ldx + k] * sc : 0.f;
     }
 }
@@ -548,12 +697,27 @@ extern "C" int ccn_bn_stats(const float* z, int64_t ldz, int64_t M, int32_t C, f
     return CCN_OK;
 }
 
+static inline bool planes_ok(const void* planes, int64_t kpad, int64_t pstride, int32_t npl, int32_t C) {
+    return !planes || (kpad >= C && (npl == 1 || (npl == 2 && pstride > 0)));
+}
+
 extern "C" int ccn_bn_apply(const float* z, int64_t ldz, int64_t M, int32_t C, const float* mean, const float* invstd,
                             const float* gamma, const float* beta, int32_t act, float slope, float* y, int64_t ldy,
+                            void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int32_t n_planes,
                             ccn_stream_t stream) {
     CCN_REQUIRE(M >= 0 && C > 0 && z && y && ldz >= C && ldy >= C && (!gamma || (mean && invstd && beta)));
+    CCN_REQUIRE(planes_ok(y_planes, yp_ld, yp_plane_stride, n_planes, C));
     if (M == 0) return CCN_OK;
-    bn_apply_kernel<<<ELT_GRID(M * C), 256, 0, S_>>>(z, ldz, M, C, mean, invstd, gamma, beta, act, slope, y, ldy);
+    const PlanesOut po = {(__nv_bfloat16*)y_planes, yp_ld, yp_plane_stride, n_planes};
+    if ((C & 3) == 0 && (ldz & 3) == 0 && (ldy & 3) == 0 && al16(z) && al16(y) && (!gamma || (al16(mean) && al16(invstd) && al16(gamma) && al16(beta))) &&
+        (!y_planes || ((yp_ld & 3) == 0 && (yp_plane_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(y_planes) & 7) == 0))) {
+        bn_apply_v4_kernel<<<bn_v4_grid(M, (int)(y_planes ? yp_ld : C)), 256, 0, S_>>>(z, ldz, M, C, mean, invstd, gamma, beta,
+                                                                                     act, slope, y, ldy, po);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
+    bn_apply_kernel<<<ELT_GRID(M * (y_planes ? yp_ld : C)), 256, 0, S_>>>(z, ldz, M, C, mean, invstd, gamma, beta, act,
+                                                                          slope, y, ldy, po);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -561,9 +725,11 @@ extern "C" int ccn_bn_apply(const float* z, int64_t ldz, int64_t M, int32_t C, c
 extern "C" int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, int64_t ldz, int64_t M, int32_t C,
                                const float* mean, const float* invstd, const float* gamma, const float* beta,
                                int32_t act, float slope, int32_t batch_stats, double* sums, float* dz, int64_t lddz,
-                               float* dgamma, float* dbeta, ccn_stream_t stream) {
+                               float* dgamma, float* dbeta, float* dzsum, void* dz_planes, int64_t dzp_ld,
+                               int64_t dzp_plane_stride, int32_t n_planes, ccn_stream_t stream) {
     CCN_REQUIRE(M >= 0 && C > 0 && dy && z && dz && lddy >= C && ldz >= C && lddz >= C);
     CCN_REQUIRE(!gamma || (mean && invstd && beta && sums));
+    CCN_REQUIRE(planes_ok(dz_planes, dzp_ld, dzp_plane_stride, n_planes, C) && (!dzsum || gamma));
     if (M == 0) return CCN_OK;
     if (gamma) {
         cudaError_t e = cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(double), S_);
@@ -575,8 +741,16 @@ extern "C" int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, in
                                                    sums);
         CCN_CHECK_LAUNCH();
     }
-    bn_bwd_apply_kernel<<<ELT_GRID(M * C), 256, 0, S_>>>(dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope,
-                                                         batch_stats, sums, dz, lddz, dgamma, dbeta);
+    const PlanesOut po = {(__nv_bfloat16*)dz_planes, dzp_ld, dzp_plane_stride, n_planes};
+    if ((C & 3) == 0 && (ldz & 3) == 0 && (lddy & 3) == 0 && (lddz & 3) == 0 && al16(z) && al16(dy) && al16(dz) &&
+        (!dz_planes || ((dzp_ld & 3) == 0 && (dzp_plane_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(dz_planes) & 7) == 0))) {
+        bn_bwd_apply_v4_kernel<<<bn_v4_grid(M, (int)(dz_planes ? dzp_ld : C)), 256, 0, S_>>>(
+            dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, batch_stats, sums, dz, lddz, dgamma, dbeta, dzsum, po);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
+    bn_bwd_apply_kernel<<<ELT_GRID(M * (dz_planes ? dzp_ld : C)), 256, 0, S_>>>(
+        dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, batch_stats, sums, dz, lddz, dgamma, dbeta, dzsum, po);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

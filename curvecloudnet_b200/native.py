@@ -111,7 +111,16 @@ def pin_stream(on: bool):
     """Cache torch's current CUDA stream handle for subsequent calls (the caller must not switch streams
     while pinned); pin_stream(False) returns to per-call lookup."""
     global _stream_handle
-    _stream_handle = torch.cuda.current_stream().cuda_stream if on else None
+    _stream_handle = _current_raw_stream() if on else None
+
+
+def _current_raw_stream() -> int:
+    """torch's current CUDA stream handle of the current device (the C accessors: ~0.3 us instead of the ~15 us of
+    torch.cuda.current_stream(), which matters in backward where no forward has pinned the stream)."""
+    try:
+        return torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice())
+    except AttributeError:          # private accessors moved: fall back to the public API
+        return torch.cuda.current_stream().cuda_stream
 
 
 _fns = {}                   # name -> (foreign function, indices of the pointer arguments)
@@ -135,7 +144,7 @@ def call(name, *args):
             if not a.is_cuda:
                 raise CcnError("%s: tensor argument is not on a CUDA device (no CPU path exists)" % name)
             conv[i] = a.data_ptr()
-    conv.append(_stream_handle if _stream_handle is not None else torch.cuda.current_stream().cuda_stream)
+    conv.append(_stream_handle if _stream_handle is not None else _current_raw_stream())
     if _prof_names is not None and name in _prof_names:
         return _timed_call(name, ent[0], conv, args)
     rc = ent[0](*conv)

@@ -661,6 +661,23 @@ def conv_planes(sig: "Planes", w_kio: torch.Tensor, bias: Optional[torch.Tensor]
     return Y
 
 
+_TC_SCRATCH = {}
+
+
+def tc_weight_scratch(w: torch.Tensor) -> TcWeight:
+    """TcWeight of a weight that changes every step (training): ONE set of bf16 buffers + TMA descriptors per weight
+    shape, refilled by ccn_split_bf16.  Safe because every user launches on the same stream right after the refill
+    (stream order: split -> GEMM -> next split)."""
+    w, ldw = _rows(w)
+    key = (w.shape[0], w.shape[1], w.device)
+    tw = _TC_SCRATCH.get(key)
+    if tw is None:
+        tw = _TC_SCRATCH[key] = TcWeight(w)
+    else:
+        call("ccn_split_bf16", w, ldw, tw.n, tw.k, tw.kpad, tw.hi, tw.lo)
+    return tw
+
+
 def prepare_tc_weight(w: torch.Tensor, seg_widths=None) -> TcWeight:
     return TcWeight(w, seg_widths)
 

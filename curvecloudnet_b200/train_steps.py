@@ -60,7 +60,7 @@ def curve_conv_v1(mod, x, pos, batch, curve, **kwargs):
 # ---------------------------------------------------------------------------------------------- point_conv.py
 def _first_hidden(mlp, z):
     if len(mlp.lins) > 1 or not mlp.plain_last:
-        return A.hidden_tail(mlp, 0, z)
+        return A.hidden_tail(mlp, 0, z, dz_planes=False)       # z comes from a per-edge gather layer, not a GEMM
     return A.dropout(z, mlp.dropout[0], mlp.training)
 
 

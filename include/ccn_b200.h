@@ -246,15 +246,19 @@ int ccn_linear_wgrad(const float* dY, int64_t lddy, const float* X, int64_t ldx,
 /* BatchNorm1d batch statistics: mean, invstd = 1/sqrt(var_biased + eps); running stats updated in place when given */
 int ccn_bn_stats(const float* z, int64_t ldz, int64_t M, int32_t C, float eps, float momentum, double* sums,
                  float* mean, float* invstd, float* running_mean, float* running_var, ccn_stream_t stream);
-/* y = act(((z - mean) invstd) gamma + beta); gamma == NULL: y = act(z) */
+/* y = act(((z - mean) invstd) gamma + beta); gamma == NULL: y = act(z).  y_planes != NULL: y is ALSO written as split-bf16
+ * activation planes (row stride yp_ld >= C, pad columns zeroed) - the input format of the next Linear. */
 int ccn_bn_apply(const float* z, int64_t ldz, int64_t M, int32_t C, const float* mean, const float* invstd,
-                 const float* gamma, const float* beta, int32_t act, float slope, float* y, int64_t ldy,
-                 ccn_stream_t stream);
-/* backward of ccn_bn_apply (+ the statistics when batch_stats != 0): dz, dgamma, dbeta */
+                 const float* gamma, const float* beta, int32_t act, float slope, float* y, int64_t ldy, void* y_planes,
+                 int64_t yp_ld, int64_t yp_plane_stride, int32_t n_planes, ccn_stream_t stream);
+/* backward of ccn_bn_apply (+ the statistics when batch_stats != 0): dz, dgamma, dbeta; optionally the column sums of dz
+ * (bias gradient of the Linear in front: exactly 0 under batch statistics) and dz as activation planes (the operand
+ * of that Linear's data / weight gradient GEMMs). */
 int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, int64_t ldz, int64_t M, int32_t C,
                     const float* mean, const float* invstd, const float* gamma, const float* beta, int32_t act,
                     float slope, int32_t batch_stats, double* sums, float* dz, int64_t lddz, float* dgamma,
-                    float* dbeta, ccn_stream_t stream);
+                    float* dbeta, float* dzsum, void* dz_planes, int64_t dzp_ld, int64_t dzp_plane_stride,
+                    int32_t n_planes, ccn_stream_t stream);
 int ccn_seg_aggregate_bwd(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
                           int64_t nq, int32_t c, int32_t mode, const float* dout, int64_t ldo, float* dmsg,
                           int64_t lddm, float* datt, int64_t ldda, ccn_stream_t stream);
