@@ -118,6 +118,30 @@ def sample_ptr(batch: torch.Tensor) -> SamplePtr:
     return SamplePtr(tail[:B + 1], host[:B + 1])
 
 
+def get_curves(points: torch.Tensor, beam_ids: torch.Tensor, curve_thresh: float = 0.08, n_beams: Optional[int] = None):
+    """_get_curves (nuscenes_dataset.py:91-118): -> (reorder i64, inv_reorder i64, curve_idxs i64, sorted xyz f32 (n,3)).
+    n_beams: beam ids lie in [0, n_beams) (None: read max(beam)+1 back, one extra host sync)."""
+    if points.dtype != torch.float32 or points.dim() != 2 or points.shape[1] < 3:
+        raise TypeError("points must be float32 (n, >=3)")
+    points, ldp = _rows(points)
+    beam_ids = _i64(beam_ids)
+    n = points.shape[0]
+    if n_beams is None:
+        n_beams = int(beam_ids.max().item()) + 1 if n else 1         # host sync
+    scratch = _empty((n_beams + max(n, 1),), torch.int32, points)
+    reorder = _empty((n,), torch.int64, points)
+    inv = _empty((n,), torch.int64, points)
+    sorted_pts = _empty((n, 3), torch.float32, points)
+    cid = _empty((n,), torch.int64, points)
+    counts = _empty((2,), torch.int32, points)
+    if n == 0:
+        counts.zero_()
+        return reorder, inv, cid, sorted_pts, counts
+    call("ccn_get_curves", points, ldp, beam_ids, n, int(n_beams), float(curve_thresh), scratch, reorder, inv, sorted_pts,
+         cid, counts)
+    return reorder, inv, cid, sorted_pts, counts
+
+
 def _finish_subset(parent_batch, idx_buf, count_dev, n_samples) -> Tuple[torch.Tensor, SamplePtr]:
     """Read back {sample_ptr of the selected level, count} with ONE host sync; trims idx."""
     out = _empty((n_samples + 1,), torch.int32, idx_buf)

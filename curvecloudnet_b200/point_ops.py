@@ -179,3 +179,17 @@ def compute_feature_diffs(x, point2curveidx, batch):
     topo = ops.curve_csr(batch, point2curveidx)
     c = x.shape[1]
     return ops.curve_feat_prep(x, x, False, True, topo.curve_ord)[:, c:]
+
+
+def get_curves(points, beam_ids, labels=None, reflectance=None, curve_thresh: float = 0.08, n_beams=None):
+    """SemNuScenes._get_curves / SemKITTI._get_curves (src/data/nuscenes_dataset.py:91-118, kitti_dataset.py:73-92) on the
+    device: -> (points sorted by beam, curve_idxs, labels sorted, reflectance sorted, inv_reorder) like the reference
+    method; points may carry extra columns after xyz (they are reordered with them)."""
+    reorder, inv, cid, sorted_xyz, counts = ops.get_curves(points, beam_ids, curve_thresh, n_beams)
+    if int(counts[1].item()):                                    # host sync (error flag)
+        raise ValueError("get_curves: beam id outside [0, n_beams)")
+    pts = sorted_xyz if points.shape[1] == 3 else ops.gather_rows(points, reorder)
+    lab = None if labels is None else (ops.gather_i64(labels.reshape(-1), reorder).reshape(-1, *labels.shape[1:])
+                                       if labels.dtype == torch.int64 else labels[reorder])
+    ref = None if reflectance is None else ops.gather_rows(reflectance.reshape(reflectance.shape[0], -1).float(), reorder)
+    return pts, cid, lab, ref, inv

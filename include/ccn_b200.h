@@ -298,6 +298,14 @@ int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t 
                     const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
                     int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n, int32_t mode, int32_t act, float slope,
                     ccn_stream_t stream);
+/* Curve grouping of a raw sweep - SemNuScenes._get_curves / SemKITTI._get_curves (src/data/nuscenes_dataset.py:91-118,
+ * src/data/kitti_dataset.py:73-92): reorder = stable argsort of beam ids, inv_reorder its inverse, sorted_points (n,3) =
+ * points[reorder], curve_idxs = running count of splits (beam change, or f64 edge length > curve_thresh * sqrt(|p.xy|)).
+ * points rows have stride ldp >= 3 floats (xyz first).  scratch: int32 [n_beams + n].  counts_out: int32 [2] =
+ * {number of curves, error flags (1 = beam id outside [0, n_beams))}. */
+int ccn_get_curves(const float* points, int64_t ldp, const int64_t* beam, int64_t n, int32_t n_beams, float curve_thresh,
+                   int32_t* scratch, int64_t* reorder, int64_t* inv_reorder, float* sorted_points, int64_t* curve_idxs,
+                   int32_t* counts_out, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

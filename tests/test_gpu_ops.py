@@ -231,3 +231,57 @@ def test_small_k_exact_knn_equals_warp_kernel_and_oracle(K):
             assert bool((idx.cpu()[off1:off1 + n1_] == -1).all())
         off1 += n1_
         off2 += n2_
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# a3: curve grouping of a raw sweep (_get_curves) - bit-exact against the golden vector of the REAL reference method
+# and against the oracle on full synthetic sweeps (32 and 64 beams), empty / single-point / single-beam inputs
+# ---------------------------------------------------------------------------------------------------------------
+def test_get_curves_matches_reference_golden():
+    from curvecloudnet_b200 import ops
+    g = OPS["get_curves"]
+    reorder, inv, cid, pts, counts = ops.get_curves(g["points"].cuda(), g["beam"].cuda(), 0.08, 32)
+    assert counts.tolist()[1] == 0
+    assert torch.equal(inv.cpu(), g["inv_reorder"])
+    assert torch.equal(cid.cpu(), g["curve_idxs"])
+    assert torch.equal(pts.cpu(), g["sorted_points"])
+    assert counts.tolist()[0] == int(g["curve_idxs"].max()) + 1
+
+
+@pytest.mark.parametrize("seed,beams,az", [(5, 32, 1085), (6, 64, 1875)])
+def test_get_curves_full_sweep_matches_oracle(seed, beams, az):
+    from curvecloudnet_b200 import point_ops
+    from curvecloudnet_b200.synthetic import raycast_driving_scan
+    from oracle import ccn_point_ops as po
+    raw = raycast_driving_scan(seed, beams=beams, azimuth_steps=az)
+    pts = torch.from_numpy(raw.points)
+    beam = torch.from_numpy(raw.beam_ids).to(torch.int64)
+    refl = torch.from_numpy(raw.reflectance)[:, None].float()
+    labels = torch.arange(pts.shape[0], dtype=torch.int64)
+    reorder, inv, cid = po.get_curves(pts, beam, 0.08)
+    p2, cid2, lab2, ref2, inv2 = point_ops.get_curves(pts.cuda(), beam.cuda(), labels.cuda(), refl.cuda())
+    assert torch.equal(inv2.cpu(), inv) and torch.equal(cid2.cpu(), cid)
+    assert torch.equal(p2.cpu(), pts[reorder]) and torch.equal(lab2.cpu(), labels[reorder])
+    assert torch.equal(ref2.cpu(), refl[reorder])
+    # size-independent properties: reorder is a permutation sorted by beam, stable inside a beam, ids are non-decreasing
+    b_sorted = beam[lab2.cpu()]
+    assert bool(torch.all(b_sorted[1:] >= b_sorted[:-1]))
+    same = b_sorted[1:] == b_sorted[:-1]
+    assert bool(torch.all(lab2.cpu()[1:][same] > lab2.cpu()[:-1][same]))
+    assert bool(torch.all(cid2.cpu()[1:] - cid2.cpu()[:-1] >= 0)) and int(cid2[0]) == 0
+
+
+def test_get_curves_edge_cases():
+    from curvecloudnet_b200 import ops
+    from oracle import ccn_point_ops as po
+    for n, nb in ((0, 4), (1, 4), (300, 1)):
+        gen = torch.Generator().manual_seed(n)
+        pts = torch.rand(n, 3, generator=gen) * 20
+        beam = torch.randint(0, nb, (n,), generator=gen)
+        reorder, inv, cid, sp, counts = ops.get_curves(pts.cuda(), beam.cuda(), 0.08, nb)
+        if n:
+            r2, i2, c2 = po.get_curves(pts, beam, 0.08)
+            assert torch.equal(inv.cpu(), i2) and torch.equal(cid.cpu(), c2) and torch.equal(reorder.cpu(), r2)
+        assert counts.tolist()[1] == 0
+    bad = ops.get_curves(torch.rand(10, 3).cuda(), torch.full((10,), 9).cuda(), 0.08, 4)[4]
+    assert bad.tolist()[1] == 1
