@@ -656,7 +656,7 @@ def curve_conv(sig, w, b, ksize):
 # ----------------------------------------------------------------------------------------------
 class _NllLoss(Function):
     @staticmethod
-    def forward(ctx, logits, target, weight, ignore_index):
+    def forward(ctx, logits, target, weight, ignore_index, perpoint=None):
         logits, ld = ops._rows(logits)
         n, C = logits.shape
         target = ops._i64(target)
@@ -664,7 +664,7 @@ class _NllLoss(Function):
         acc = _empty((2,), logits, torch.float64)
         loss = _empty((1,), logits)
         call("ccn_nll_loss_fwd", logits, ld, target, weight if weight is not None else 0, n, C, int(ignore_index), lse,
-             acc, loss)
+             acc, loss, perpoint if perpoint is not None else 0)
         ctx.save_for_backward(logits, target, weight, lse, acc)
         ctx.ignore = int(ignore_index)
         return loss.view(())
@@ -677,9 +677,10 @@ class _NllLoss(Function):
         d = _empty((n, C), logits)
         call("ccn_nll_loss_bwd", logits, ld, target, weight if weight is not None else 0, n, C, ctx.ignore, lse, acc,
              g.reshape(1).contiguous().float(), d, C)
-        return d, None, None, None
+        return d, None, None, None, None
 
 
-def nll_loss(logits, target, weight=None, ignore_index=-100):
-    """F.nll_loss(F.log_softmax(logits, dim=1), target, weight=weight, ignore_index=ignore_index) (mean)."""
-    return _NllLoss.apply(logits, target, weight, ignore_index)
+def nll_loss(logits, target, weight=None, ignore_index=-100, perpoint_out=None):
+    """F.nll_loss(F.log_softmax(logits, dim=1), target, weight=weight, ignore_index=ignore_index) (mean).
+    perpoint_out: optional f32 (n) buffer that receives the unweighted per-point NLL (reduction="none")."""
+    return _NllLoss.apply(logits, target, weight, ignore_index, perpoint_out)

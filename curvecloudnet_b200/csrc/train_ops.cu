@@ -542,7 +542,7 @@ __global__ void edge_rel_pos_kernel(const float* __restrict__ pos_src, const flo
 // ------------------------------------------------------------------------------------------------------------
 __global__ void nll_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target,
                                const float* __restrict__ cw, int64_t n, int C, int64_t ignore, float* __restrict__ lse,
-                               double* __restrict__ acc) {
+                               double* __restrict__ acc, float* __restrict__ perpoint) {
     double ls = 0.0, ws = 0.0;
     GRID_STRIDE(i, n) {
         const float* row = logits + i * ld;
@@ -553,6 +553,7 @@ __global__ void nll_fwd_kernel(const float* __restrict__ logits, int64_t ld, con
         const float l = m + logf(s);
         lse[i] = l;
         const int64_t y = target[i];
+        if (perpoint) perpoint[i] = (y >= 0 && y < C) ? l - row[y] : 0.f;      // F.nll_loss(reduction="none"), unweighted
         if (y != ignore && y >= 0 && y < C) {
             const float w = cw ? cw[y] : 1.f;
             ls += (double)(w * (l - row[y]));
@@ -812,12 +813,12 @@ extern "C" int ccn_edge_rel_pos(const float* pos_src, const float* pos_dst, cons
 
 extern "C" int ccn_nll_loss_fwd(const float* logits, int64_t ld, const int64_t* target, const float* class_weight,
                                 int64_t n, int32_t C, int64_t ignore_index, float* lse, double* acc, float* loss,
-                                ccn_stream_t stream) {
+                                float* perpoint, ccn_stream_t stream) {
     CCN_REQUIRE(n > 0 && C > 0 && logits && target && lse && acc && loss && ld >= C);
     cudaError_t e = cudaMemsetAsync(acc, 0, 2 * sizeof(double), S_);
     if (e != cudaSuccess) return (int)e;
     nll_fwd_kernel<<<ccn_grid(n, 128, 148 * 8), 128, 0, S_>>>(logits, ld, target, class_weight, n, C, ignore_index, lse,
-                                                              acc);
+                                                              acc, perpoint);
     CCN_CHECK_LAUNCH();
     nll_finish_kernel<<<1, 1, 0, S_>>>(acc, loss);
     CCN_CHECK_LAUNCH();

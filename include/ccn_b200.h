@@ -275,7 +275,8 @@ int ccn_edge_rel_pos(const float* pos_src, const float* pos_dst, const int32_t* 
 /* loss = sum_i w[y_i] (lse_i - logit[i][y_i]) / sum_i w[y_i] over y_i != ignore; lse (n) and acc (fp64 [2]) are kept
  * for the backward: dlogits = gscale[0] * w[y] / sum_w * (softmax - onehot) */
 int ccn_nll_loss_fwd(const float* logits, int64_t ld, const int64_t* target, const float* class_weight, int64_t n,
-                     int32_t C, int64_t ignore_index, float* lse, double* acc, float* loss, ccn_stream_t stream);
+                     int32_t C, int64_t ignore_index, float* lse, double* acc, float* loss, float* perpoint,
+                     ccn_stream_t stream);   /* perpoint (n) or NULL: the unweighted per-point NLL (reduction="none") */
 int ccn_nll_loss_bwd(const float* logits, int64_t ld, const int64_t* target, const float* class_weight, int64_t n,
                      int32_t C, int64_t ignore_index, const float* lse, const double* acc, const float* gscale,
                      float* dlogits, int64_t ldd, ccn_stream_t stream);
@@ -306,6 +307,33 @@ int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t 
 int ccn_get_curves(const float* points, int64_t ldp, const int64_t* beam, int64_t n, int32_t n_beams, float curve_thresh,
                    int32_t* scratch, int64_t* reorder, int64_t* inv_reorder, float* sorted_points, int64_t* curve_idxs,
                    int32_t* counts_out, ccn_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Loss / metrics epilogue of the segmentation runs (csrc/loss_metrics.cu).
+ * Lovasz-softmax (src/models/utils/lovasz_losses.py:21-33,175-204 via seg_loss, src/run/nuscenes_seg.py:229-243):
+ *   loss = mean over PRESENT classes of dot(sorted errors, lovasz_grad(sorted fg)) on the points with
+ *   target != ignore_index.  Buffers: keys uint64 [C * ccn_lovasz_pad(n)], fg_count int32 [C], lse f32 [n],
+ *   grad f32 [C * n] (the Jaccard gradient of every (class, point), kept for the backward), acc f64 [2].
+ * --------------------------------------------------------------------------------------------------------------- */
+int64_t ccn_lovasz_pad(int64_t n);
+int ccn_lovasz_softmax_fwd(const float* logits, int64_t ld, const int64_t* target, int64_t n, int32_t C,
+                           int64_t ignore_index, void* keys, int32_t* fg_count, float* lse, float* grad, double* acc,
+                           float* loss, ccn_stream_t stream);
+int ccn_lovasz_softmax_bwd(const float* logits, int64_t ld, const int64_t* target, int64_t n, int32_t C,
+                           int64_t ignore_index, const float* lse, const float* grad, const int32_t* fg_count,
+                           const double* acc, const float* gscale, float* dlogits, int64_t ldd, int32_t accumulate,
+                           ccn_stream_t stream);
+/* fast_hist (src/utils/utils.py:4-8) with the arg-max over score columns [col_offset, C) fused: hist (ncls x ncls int64,
+ * accumulated into) [target][pred]; pred_out optional; scores == NULL: predictions are given in pred_in. */
+int ccn_confusion_hist(const float* scores, int64_t ld, int32_t C, const int64_t* pred_in, const int64_t* target, int64_t n,
+                       int32_t ncls, int32_t col_offset, int64_t* pred_out, int64_t* hist, ccn_stream_t stream);
+/* test-time augmentation of val() (src/run/nuscenes_seg.py:86-116): out = [sx x, sy y, z]; acc (+)= src;
+ * out = log_softmax(acc * scale), pred = arg-max. */
+int ccn_scale_xy(const float* pos, int64_t n, float sx, float sy, float* out, ccn_stream_t stream);
+int ccn_accumulate(const float* src, int64_t lds, int64_t n, int32_t C, float* acc, int64_t lda, int32_t first,
+                   ccn_stream_t stream);
+int ccn_mean_logsoftmax(const float* acc, int64_t lda, int64_t n, int32_t C, float scale, float* out, int64_t ldo,
+                        int64_t* pred, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

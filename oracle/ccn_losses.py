@@ -1,0 +1,96 @@
+"""CPU restatement of the loss / metrics epilogue around the path.
+TEST INFRASTRUCTURE - see oracle/__init__.py.
+
+  lovasz_grad, lovasz_softmax_flat   src/models/utils/lovasz_losses.py:21-33, 175-204
+  seg_loss                           src/run/nuscenes_seg.py:229-243
+  fast_hist, per_class_iu            src/utils/utils.py:4-12;  fast_hist_crop nuscenes_seg.py:245-249
+  tta_forward                        the augmentation loop of val(), nuscenes_seg.py:86-116
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+
+def lovasz_grad(gt_sorted):
+    """lovasz_losses.py:21-33."""
+    p = len(gt_sorted)
+    gts = gt_sorted.sum()
+    intersection = gts - gt_sorted.float().cumsum(0)
+    union = gts + (1 - gt_sorted).float().cumsum(0)
+    jaccard = 1.0 - intersection / union
+    if p > 1:
+        jaccard[1:p] = jaccard[1:p] - jaccard[0:-1]
+    return jaccard
+
+
+def lovasz_softmax_flat(probas, labels):
+    """lovasz_losses.py:175-204 with classes='present' (the only mode seg_loss uses)."""
+    if probas.numel() == 0:
+        return probas * 0.0
+    losses = []
+    for c in range(probas.size(1)):
+        fg = (labels == c).float()
+        if fg.sum() == 0:
+            continue
+        errors = (fg - probas[:, c]).abs()
+        errors_sorted, perm = torch.sort(errors, 0, descending=True)
+        losses.append(torch.dot(errors_sorted, lovasz_grad(fg[perm]).detach()))
+    return sum(losses) / len(losses) if losses else probas.sum() * 0.0
+
+
+def seg_loss(pred, gt, ignore=0, use_lovasz=False, ce_weights=None):
+    """nuscenes_seg.py:229-243."""
+    pred_log_soft = F.log_softmax(pred, dim=-1)
+    loss = F.nll_loss(pred_log_soft, gt, reduction="mean", ignore_index=ignore, weight=ce_weights)
+    perpnt_loss = F.nll_loss(pred_log_soft, gt, reduction="none")
+    if use_lovasz:
+        pred_soft = F.softmax(pred, dim=-1)
+        keep = gt != ignore
+        loss = loss + torch.mean(lovasz_softmax_flat(pred_soft[keep], gt[keep]))
+    return loss, perpnt_loss
+
+
+def fast_hist(pred, label, n):
+    """utils.py:4-8."""
+    k = (label >= 0) & (label < n)
+    return torch.bincount(n * label[k] + pred[k], minlength=n ** 2)[:n ** 2].reshape(n, n)
+
+
+def fast_hist_crop(output, target, unique_label):
+    """nuscenes_seg.py:245-249."""
+    ul = torch.as_tensor(unique_label, dtype=torch.int64)
+    hist = fast_hist(output.flatten(), target.flatten(), int(ul.max()) + 2)
+    return hist[ul + 1, :][:, ul + 1]
+
+
+def per_class_iu(hist):
+    """utils.py:11-12."""
+    h = hist.double()
+    d = torch.diagonal(h)
+    return d / (h.sum(1) + h.sum(0) - d)
+
+
+@torch.no_grad()
+def tta_forward(model, data):
+    """nuscenes_seg.py:86-116: 4 xy-flips x 3 xy-scales, out = log_softmax(sum(outs) / 12), predict = argmax."""
+    orig = data.pos.clone()
+    outs = []
+    for axis_flips in range(4):
+        for scales in range(3):
+            pos = orig.clone()
+            if axis_flips == 1:
+                pos[:, 0] *= -1
+            elif axis_flips == 2:
+                pos[:, 1] *= -1
+            elif axis_flips == 3:
+                pos[:, :2] *= -1
+            if scales == 1:
+                pos[:, :2] *= 0.95
+            elif scales == 2:
+                pos[:, :2] *= 1.05
+            data.pos = pos
+            outs.append(model(data, labels=getattr(data, "y", None)))
+    data.pos = orig
+    out = F.log_softmax(sum(outs) / 12, dim=-1)
+    return out, torch.argmax(out, dim=-1)

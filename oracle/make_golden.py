@@ -240,6 +240,51 @@ def make_train(rbase):
     return out
 
 
+def make_losses():
+    """seg_loss (NLL + Lovasz-softmax) of the REAL reference sources on random logits: loss, per-point loss and the
+    gradient w.r.t. the logits.  lovasz_losses.py is pure torch and is imported as is; seg_loss / fast_hist are
+    taken from the reference files by source extraction (their modules import packages that are absent here)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_lovasz", os.path.join(REF, "src/models/utils/lovasz_losses.py"))
+    lov = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(lov)
+    import numpy as np
+    import torch.nn.functional as F
+    src = open(os.path.join(REF, "src/run/nuscenes_seg.py")).read()
+    tree = ast.parse(src)
+    ns = {"F": F, "torch": torch, "np": np, "lovasz_softmax_flat": lov.lovasz_softmax_flat}
+    usrc = open(os.path.join(REF, "src/utils/utils.py")).read()
+    exec(compile(ast.parse(usrc), "utils.py", "exec"), ns)
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in ("seg_loss", "fast_hist_crop"):
+            exec(compile(ast.Module([node], []), "nuscenes_seg.py", "exec"), ns)
+    out = {}
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from golden_utils import grad_projection, loss_case
+    for name, n, C, seed in (("small", 700, 17, 1), ("nuscenes", 34000, 17, 2), ("kitti", 9000, 20, 3)):
+        logits, gt, w = loss_case(name, n, C, seed)                    # inputs are regenerated from the seed by the tests
+        logits.requires_grad_()
+        rec = {"n": n, "C": C, "seed": seed}
+        for lov_on in (False, True):
+            logits.grad = None
+            loss, per = ns["seg_loss"](logits, gt, ignore=0, use_lovasz=lov_on, ce_weights=w)
+            loss.backward()
+            gd = logits.grad.double().flatten()
+            ent = {"loss": float(loss), "perpnt_head": per.detach()[:256].clone(), "perpnt_sum": float(per.double().sum()),
+                   "dnorm": float(gd.norm()), "dproj": float((gd * grad_projection(name, gd.numel())).sum()),
+                   "dhead": logits.grad[:256].clone()}
+            if name == "small":
+                ent["dlogits"] = logits.grad.clone()
+            rec["lovasz" if lov_on else "nll"] = ent
+        pred = torch.argmax(logits.detach(), dim=-1)
+        ul = np.arange(C - 1)
+        rec["hist_crop"] = torch.from_numpy(ns["fast_hist_crop"](pred.numpy(), gt.numpy(), ul))
+        rec["iou"] = torch.from_numpy(ns["per_class_iu"](rec["hist_crop"].numpy()))
+        out[name] = rec
+        print(name, rec["nll"]["loss"], rec["lovasz"]["loss"])
+    return out
+
+
 def _compact(obj):
     """int64 -> int32 (all values are small indices) to keep the committed fixtures small;
     tests/golden_utils.load() widens them again."""
@@ -252,6 +297,10 @@ def _compact(obj):
 
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "losses":     # only the loss / metrics fixture (needs no shims)
+        torch.save(make_losses(), os.path.join(OUT, "losses.pt"))
+        print("losses.pt", os.path.getsize(os.path.join(OUT, "losses.pt")) // 1024, "KiB")
+        return
     rpo, rbase, rconv, rfps = _import_reference()
     if len(sys.argv) > 1 and sys.argv[1] == "train":      # only the training-step fixture
         torch.save(_compact(make_train(rbase)), os.path.join(OUT, "train.pt"))

@@ -69,3 +69,15 @@ def check_train_golden(model, logits, loss, rec, logit_tol, grad_tol, label=""):
     print("%s train golden: logits %.3e loss %.3e worst gradient %s %.3e" % (label, e_logits, e_loss, worst[0], worst[1]))
     assert e_logits <= logit_tol and e_loss <= logit_tol, (e_logits, e_loss)
     assert worst[1] <= grad_tol, "gradient of %s off by %.3e" % worst
+
+
+def loss_case(name, n, C, seed):
+    """Inputs of a tests/golden/losses.pt record (logits, labels with ~30 % ignored zeros, class weights)."""
+    gen = torch.Generator().manual_seed(seed)
+    logits = torch.randn(n, C, generator=gen) * 2.5
+    gt = torch.randint(0, C, (n,), generator=gen)
+    gt[torch.rand(n, generator=gen) < 0.3] = 0
+    if name == "small":
+        gt[gt == 5] = 6                                                # an absent class
+    w = torch.rand(C, generator=gen) + 0.5
+    return logits, gt, w

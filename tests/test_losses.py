@@ -1,0 +1,107 @@
+"""Loss / metrics epilogue (seg_loss = weighted NLL + Lovasz-softmax, fast_hist, per_class_iu, the TTA loop):
+the oracle and the CUDA kernels against tests/golden/losses.pt, which oracle/make_golden.py froze from the REAL
+reference sources (lovasz_losses.py imported as is; seg_loss / fast_hist_crop / per_class_iu executed from their files)."""
+import pytest
+import torch
+
+from golden_utils import grad_projection, load, loss_case, rel_err
+
+GOLD = load("losses.pt")
+
+
+def _check(name, use_lovasz, loss, per, dlogits, tol):
+    rec = GOLD[name]["lovasz" if use_lovasz else "nll"]
+    assert abs(float(loss) - rec["loss"]) <= tol * abs(rec["loss"]), (float(loss), rec["loss"])
+    assert rel_err(per[:256].cpu(), rec["perpnt_head"]) <= tol
+    assert abs(float(per.double().sum()) - rec["perpnt_sum"]) <= tol * abs(rec["perpnt_sum"])
+    gd = dlogits.detach().cpu().double().flatten()
+    assert abs(float(gd.norm()) - rec["dnorm"]) <= 10 * tol * rec["dnorm"]
+    assert abs(float((gd * grad_projection(name, gd.numel())).sum()) - rec["dproj"]) <= 10 * tol * rec["dnorm"]
+    assert rel_err(dlogits[:256].cpu(), rec["dhead"]) <= 10 * tol
+    if "dlogits" in rec:
+        assert rel_err(dlogits.cpu(), rec["dlogits"]) <= 10 * tol
+
+
+@pytest.mark.parametrize("use_lovasz", [False, True])
+@pytest.mark.parametrize("name", list(GOLD))
+def test_oracle_seg_loss_matches_reference(name, use_lovasz):
+    from oracle import ccn_losses as L
+    r = GOLD[name]
+    logits, gt, w = loss_case(name, r["n"], r["C"], r["seed"])
+    logits.requires_grad_()
+    loss, per = L.seg_loss(logits, gt, ignore=0, use_lovasz=use_lovasz, ce_weights=w)
+    loss.backward()
+    _check(name, use_lovasz, loss, per.detach(), logits.grad, 1e-6)
+    pred = torch.argmax(logits.detach(), dim=-1)
+    hist = L.fast_hist_crop(pred, gt, list(range(r["C"] - 1)))
+    assert torch.equal(hist, r["hist_crop"].to(hist.dtype))
+    assert torch.allclose(L.per_class_iu(hist), r["iou"].double(), equal_nan=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("use_lovasz", [False, True])
+@pytest.mark.parametrize("name", list(GOLD))
+def test_cuda_seg_loss_matches_reference(name, use_lovasz):
+    from curvecloudnet_b200 import losses as L
+    r = GOLD[name]
+    logits, gt, w = loss_case(name, r["n"], r["C"], r["seed"])
+    logits = logits.cuda().requires_grad_()
+    loss, per = L.seg_loss(logits, gt.cuda(), ignore=0, use_lovasz=use_lovasz, ce_weights=w.cuda())
+    (loss * 1.0).backward()
+    _check(name, use_lovasz, loss, per, logits.grad, 2e-5)
+    hist = L.fast_hist_crop(torch.argmax(logits.detach(), dim=-1), gt.cuda(), list(range(r["C"] - 1)))
+    assert torch.equal(hist.cpu(), r["hist_crop"].to(torch.int64))              # integer work: bit-exact
+    assert torch.allclose(L.per_class_iu(hist).cpu(), r["iou"].double(), equal_nan=True)
+
+
+@pytest.mark.gpu
+def test_cuda_lovasz_edge_cases():
+    from curvecloudnet_b200 import losses as L
+    from oracle import ccn_losses as O
+    for n, C, seed in ((1, 3, 0), (2, 2, 1), (4097, 5, 2), (300, 40, 3)):
+        gen = torch.Generator().manual_seed(seed)
+        logits = torch.randn(n, C, generator=gen)
+        gt = torch.randint(0, C, (n,), generator=gen)
+        for ignore in (0, -1):
+            a = logits.clone().requires_grad_()
+            keep = gt != ignore
+            ref = O.lovasz_softmax_flat(torch.softmax(a, -1)[keep], gt[keep])
+            ref = ref.sum() if ref.dim() else ref
+            if a.requires_grad and ref.requires_grad:
+                ref.backward()
+            b = logits.clone().cuda().requires_grad_()
+            got = L.lovasz_softmax_flat(b, gt.cuda(), ignore)
+            got.backward()
+            assert abs(float(got) - float(ref)) <= 2e-5 * max(abs(float(ref)), 1e-3), (n, C, ignore)
+            want = a.grad if a.grad is not None else torch.zeros_like(a)
+            assert float((b.grad.cpu() - want).abs().max()) <= 2e-5 * max(float(want.abs().max()), 1e-3)
+    # everything ignored: zero loss, zero gradient
+    b = torch.randn(50, 4).cuda().requires_grad_()
+    got = L.lovasz_softmax_flat(b, torch.zeros(50, dtype=torch.int64).cuda(), 0)
+    got.backward()
+    assert float(got) == 0.0 and float(b.grad.abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+def test_cuda_tta_forward_matches_oracle():
+    """val()'s augmentation loop: 12 forwards (own random draws each), averaged, log_softmax, argmax."""
+    from curvecloudnet_b200 import losses as L
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle import ccn_losses as O
+    from oracle.ccn_model import ModelBase as OracleModel
+    data = driving_scan_batch([7], subsample=1200)
+    ref = build_model(OracleModel, "nuscenes")
+    randomize_model_(ref, 1234)
+    ref.eval()
+    torch.manual_seed(3)
+    want, want_pred = O.tta_forward(ref, data)
+    model = build_model(ModelBase, "nuscenes", precision="fp32")
+    model.load_state_dict(ref.state_dict(), strict=True)
+    model = model.cuda().eval()
+    torch.manual_seed(3)
+    got, pred = L.tta_forward(model, data.to("cuda"))
+    assert rel_err(got.cpu(), want) <= 1e-4
+    agree = float((pred.cpu() == want_pred).float().mean())
+    assert agree >= 0.999, agree
