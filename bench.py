@@ -42,6 +42,14 @@ def _peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def _ncu_traffic(key):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture (profiles/ncu_traffic.json)."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[key]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 class ClockSampler:
     def __init__(self, device_index):
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -278,7 +286,8 @@ def run_train(args):
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e_max / K},
         "gpu_launches": int(launches),
         "roofline": {"bound": "tensor", "kernel": "linear_wgrad_kernel (fp32 SIMT)" if args.precision == "fp32" else "wgrad_tc_kernel (ccn_linear_wgrad_tc: TMA + tcgen05 MN-major + TMEM, split-M)", "achieved": ach,
-                     "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None, "traffic": None,
+                     "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None,
+                     "traffic": _ncu_traffic("ccn_linear_wgrad_tc:%s" % args.precision),
                      "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": wg["calls"],
                      "avg_launch_us": (wg["ms"] * 1e3 / wg["calls"]) if wg["calls"] else None,
                      "share_of_step": wg["ms"] / ms_prof if ms_prof else None, "flops_per_step": wg["work"] / K},
@@ -404,7 +413,8 @@ def main():
     ach_tf = (lin["work"] / (lin["ms"] * 1e-3) / 1e12) if lin["ms"] > 0 else 0.0
     roofline = {"bound": "tensor", "kernel": "linear_f32_kernel (ccn_linear_f32)" if args.precision == "fp32" else
                 "linear_planes_kernel<%d> (ccn_linear_planes: TMA + tcgen05 + TMEM)" % (3 if args.precision == "bf16x3" else 1), "achieved": ach_tf, "peak": peak_tf,
-                "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None, "traffic": None,
+                "unit": "TFLOP/s", "frac": ach_tf / peak_tf if peak_tf else None,
+                "traffic": _ncu_traffic("ccn_linear_planes:%s" % args.precision),
                 "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": lin["calls"],
                 "avg_launch_us": (lin["ms"] * 1e3 / lin["calls"]) if lin["calls"] else None,
                 "share_of_step": lin["ms"] / ms_prof if ms_prof else None, "step_ms_instrumented": ms_prof / K,
