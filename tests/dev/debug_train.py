@@ -1,5 +1,5 @@
 """Per-parameter gradient comparison of one training step: ours (GPU) vs the fp32 CPU oracle vs the oracle in fp64
-(the last tells how much of a difference is conditioning).  usage: python tools/debug_train.py <config> <precision>"""
+(the last tells how much of a difference is conditioning).  usage: python tests/dev/debug_train.py <config> <precision>"""
 import copy
 import os
 import sys
@@ -7,7 +7,7 @@ import sys
 import torch
 import torch.nn.functional as F
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from curvecloudnet_b200 import autograd as A                     # noqa: E402
 from curvecloudnet_b200.configs import build_model               # noqa: E402
 from curvecloudnet_b200.model import ModelBase                   # noqa: E402
