@@ -158,6 +158,7 @@ def _raise(name, rc):
     raise CcnError("%s: CUDA error %d" % (name, rc))
 
 
+_prof_footprint = None      # list: argument footprint (bytes) of every timed call, parallel to _prof_events
 _prof_pad_cycles = 0        # > 0: a spin of that many GPU cycles is queued before every timed launch, so that the
                             # launch is already in the queue when the GPU reaches the start event (the event pair then
                             # brackets the kernel, not the host's launch latency)
@@ -171,6 +172,10 @@ def _timed_call(name, fn, conv, args):
     rc = fn(*conv)
     e1.record()
     _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
+    if _prof_footprint is not None:
+        # bytes of every tensor argument (inputs read + outputs written): the compulsory-traffic proxy of
+        # tools/profile_forward.py's per-kernel GB/s table
+        _prof_footprint.append(sum(a.numel() * a.element_size() for a in args if a.__class__ is not int and a.__class__ is not float))
     if name in _WORK:
         _prof_shapes.append(_MNK[name](args))
     if rc != 0:
