@@ -285,6 +285,31 @@ def make_losses():
     return out
 
 
+def make_models_extra(rbase):
+    """Eval-mode logits of the REAL reference ModelBase for the remaining shipped step lists: A2D2 (sparse SGCNN with
+    softmax attention), Kortx (k=7 convs, knn 30, seg categories) and KITTI (nuScenes step list, voxel 0.025, 20 classes)."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch, randomize_model_
+    out = {}
+    specs = {
+        "a2d2": lambda: driving_scan_batch([61, 62], subsample=1500, n_classes=38),
+        "kortx": lambda: object_scan_batch([63, 64], n_points=768),
+        "kitti": lambda: driving_scan_batch([65], kind="kitti", n_classes=20, subsample=2500),
+    }
+    for name, mk in specs.items():
+        data = mk()
+        model = build_model(rbase.ModelBase, name)
+        randomize_model_(model, 1234)
+        model.eval()
+        torch.manual_seed(79)
+        with torch.no_grad():
+            logits = model(data, labels=data.y)
+        out[name] = {"pos": data.pos, "x": data.x, "batch": data.batch, "curve": data.curve_idxs,
+                     "labels": getattr(data, "labels", None), "weight_seed": 1234, "rng_seed": 79, "logits": logits}
+        print(name, tuple(logits.shape), float(logits.abs().max()))
+    return out
+
+
 def _compact(obj):
     """int64 -> int32 (all values are small indices) to keep the committed fixtures small;
     tests/golden_utils.load() widens them again."""
@@ -302,6 +327,10 @@ def main():
         print("losses.pt", os.path.getsize(os.path.join(OUT, "losses.pt")) // 1024, "KiB")
         return
     rpo, rbase, rconv, rfps = _import_reference()
+    if len(sys.argv) > 1 and sys.argv[1] == "models_extra":
+        torch.save(_compact(make_models_extra(rbase)), os.path.join(OUT, "models_extra.pt"))
+        print("models_extra.pt", os.path.getsize(os.path.join(OUT, "models_extra.pt")) // 1024, "KiB")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "train":      # only the training-step fixture
         torch.save(_compact(make_train(rbase)), os.path.join(OUT, "train.pt"))
         print("train.pt", os.path.getsize(os.path.join(OUT, "train.pt")) // 1024, "KiB")

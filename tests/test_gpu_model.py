@@ -7,6 +7,7 @@ from golden_utils import load, rel_err
 
 pytestmark = pytest.mark.gpu
 MODELS = load("models.pt")
+MODELS.update(load("models_extra.pt"))        # a2d2, kortx, kitti - same generator, the REAL reference sources
 
 
 PRECISION_TOL = {"fp32": 1e-4, "bf16x3": 1e-4, "bf16": 2e-2}     # BASELINE.json north_star tolerances

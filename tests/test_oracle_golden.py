@@ -78,14 +78,14 @@ def test_get_curves():
     assert torch.equal(g["points"][reorder], g["sorted_points"])
 
 
-@pytest.mark.parametrize("name", ["nuscenes", "shapenet-class", "shapenet-seg"])
+@pytest.mark.parametrize("name", ["nuscenes", "shapenet-class", "shapenet-seg", "a2d2", "kortx", "kitti"])
 def test_model_logits(name):
     """End to end: oracle ModelBase == the reference's ModelBase (run over the shims) on the same
     seeded weights, inputs and RNG draws."""
     from curvecloudnet_b200.configs import build_model
     from curvecloudnet_b200.synthetic import ScanBatch, randomize_model_
     from oracle.ccn_model import ModelBase
-    g = load("models.pt")[name]
+    g = load("models.pt" if name in ("nuscenes", "shapenet-class", "shapenet-seg") else "models_extra.pt")[name]
     data = ScanBatch(g["x"], g["pos"], g["batch"], g["curve"], None, g["labels"])
     model = build_model(ModelBase, name)
     randomize_model_(model, g["weight_seed"])
