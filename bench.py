@@ -50,6 +50,23 @@ def _ncu_traffic(key):
         return None
 
 
+def _pin_rank_cores(local, world):
+    """The per-scan path is launch-bound on the host: give every rank its own slice of the allowed cores so that the ranks'
+    Python / driver threads do not migrate onto each other (BENCH_NO_PIN=1 disables)."""
+    if world <= 1 or os.environ.get("BENCH_NO_PIN"):
+        return None
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = len(cores) // world
+        if per < 2:
+            return None
+        mine = cores[local * per:(local + 1) * per]
+        os.sched_setaffinity(0, mine)
+        return len(mine)
+    except Exception:
+        return None
+
+
 class ClockSampler:
     def __init__(self, device_index):
         q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -329,6 +346,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    _pin_rank_cores(local, world)
     dist = None
     if world > 1:
         import torch.distributed as dist
