@@ -46,6 +46,14 @@ __global__ void __launch_bounds__(1024) beam_rank_kernel(const int64_t* __restri
     }
 }
 
+// single-beam sweeps (KITTI): the stable sort is the identity
+__global__ void iota_i64_kernel(int64_t n, int64_t* __restrict__ a, int64_t* __restrict__ b) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        a[i] = i;
+        b[i] = i;
+    }
+}
+
 // sorted_points[j] = points[reorder[j]]; split[j] = beam changes or |p_j - p_{j-1}| (f64) > thresh * sqrt(|p_j.xy|) (f32)
 __global__ void curve_split_kernel(const float* __restrict__ points, int64_t ldp, const int64_t* __restrict__ beam,
                                    const int64_t* __restrict__ reorder, int64_t n, float thresh,
@@ -105,7 +113,8 @@ extern "C" int ccn_get_curves(const float* points, int64_t ldp, const int64_t* b
     int32_t* split = scratch + n_beams;
     beam_hist_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(beam, n, n_beams, count, counts_out + 1);
     CCN_CHECK_LAUNCH();
-    beam_rank_kernel<<<n_beams, 1024, 0, s>>>(beam, n, count, reorder, inv_reorder);
+    if (n_beams == 1) iota_i64_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(n, reorder, inv_reorder);
+    else beam_rank_kernel<<<n_beams, 1024, 0, s>>>(beam, n, count, reorder, inv_reorder);
     CCN_CHECK_LAUNCH();
     curve_split_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(points, ldp, beam, reorder, n, curve_thresh,
                                                                   sorted_points, split);

@@ -15,7 +15,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libccn_b200.so")
 
-_c = {"p": ctypes.c_void_p, "q": ctypes.c_int64, "i": ctypes.c_int32, "f": ctypes.c_float}
+_c = {"p": ctypes.c_void_p, "q": ctypes.c_int64, "i": ctypes.c_int32, "f": ctypes.c_float, "d": ctypes.c_double}
 
 def _parse_header():
     """Derive every entry point's ctypes signature from include/ccn_b200.h (single source of truth)."""
@@ -33,6 +33,8 @@ def _parse_header():
                 codes += "q"
             elif "int32_t" in a:
                 codes += "i"
+            elif "double" in a:
+                codes += "d"
             elif "float" in a:
                 codes += "f"
             else:
@@ -81,6 +83,31 @@ _MNK = {"ccn_linear_f32": lambda a: (a[7], a[8], a[9]), "ccn_linear_tc": lambda 
 _WORK = {name: (lambda a, f=f: 2.0 * f(a)[0] * f(a)[1] * f(a)[2]) for name, f in _MNK.items()}
 
 
+def _is_buf(a):
+    return a.__class__ is not int and a is not None
+
+
+def _planes_bytes(a):
+    """Algorithmic bytes of one ccn_linear_planes launch: every activation plane read once, the weights read once,
+    every output (fp32 rows and / or bf16 planes) written once."""
+    P = 2 if a[27] == 3 else 1
+    M, N = a[24], a[25]
+    kin = sum((a[i] + 7) // 8 * 8 for i in (3, 7, 11, 15))
+    b = M * kin * 2 * P + N * (a[3] + a[7] + a[11] + a[15]) * 2 * P
+    if _is_buf(a[18]):
+        b += N * 4
+    if _is_buf(a[19]):
+        b += M * N * 4
+    if _is_buf(a[21]):
+        b += M * ((N + 15) // 16 * 16) * 2 * P
+    return float(b)
+
+
+# algorithmic bytes of one call (HBM roofline of the Linear kernels)
+_BYTES = {"ccn_linear_planes": _planes_bytes,
+          "ccn_linear_f32": lambda a: 4.0 * (a[7] * a[9] + a[8] * a[9] + a[7] * a[8] + (a[8] if _is_buf(a[4]) else 0))}
+
+
 def profile_begin(names, pad_cycles=0):
     global _prof_names, _prof_events, _prof_pad_cycles
     _prof_pad_cycles = int(pad_cycles)
@@ -95,11 +122,12 @@ def profile_end():
     out = {}
     if _prof_events:
         torch.cuda.synchronize()
-    for name, a, b, work in _prof_events:
-        d = out.setdefault(name, {"ms": 0.0, "calls": 0, "work": 0.0})
+    for name, a, b, work, nbytes in _prof_events:
+        d = out.setdefault(name, {"ms": 0.0, "calls": 0, "work": 0.0, "bytes": 0.0})
         d["ms"] += a.elapsed_time(b)
         d["calls"] += 1
         d["work"] += work
+        d["bytes"] += nbytes
     _prof_names = None
     return out
 
@@ -171,7 +199,8 @@ def _timed_call(name, fn, conv, args):
     e0.record()
     rc = fn(*conv)
     e1.record()
-    _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0))
+    _prof_events.append((name, e0, e1, _WORK[name](args) if name in _WORK else 0.0,
+                         _BYTES[name](args) if name in _BYTES else 0.0))
     if _prof_footprint is not None:
         # bytes of every tensor argument (inputs read + outputs written): the compulsory-traffic proxy of
         # tools/profile_forward.py's per-kernel GB/s table

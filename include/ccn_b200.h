@@ -308,6 +308,23 @@ int ccn_get_curves(const float* points, int64_t ldp, const int64_t* beam, int64_
                    int32_t* scratch, int64_t* reorder, int64_t* inv_reorder, float* sorted_points, int64_t* curve_idxs,
                    int32_t* counts_out, ccn_stream_t stream);
 
+/* Scan ingest - SemNuScenes.get / _load_frame / _get_curves / _training_augmentation
+ * (src/data/nuscenes_dataset.py:42-149) and SemKITTI.get / ... (src/data/kitti_dataset.py:40-152) as ONE call per sweep:
+ * raw (n, rec) f32 records, rec = 5 (x y z intensity ring) or 4 (x y z remission, single sequential beam: n_beams = 1);
+ * labels: label_bytes = 1 (u8 lidarseg), 4 (i32, masked with label_mask = 0xFFFF) or 0 (test split: ones when
+ * lut_size == -1, else zeros), mapped through the learning map lut[lut_size] (int32, < 0 = key absent) and truncated to
+ * u8 like the reference.  Outputs, in beam-sorted order: pos (n,3) = augment(xyz) / pos_div, x (n) reflectance, y (n) i64,
+ * curve_idxs (n) i64, reorder / inv_reorder (n) i64.  augment != 0 applies the training augmentation with the DRAWN values
+ * (rotation cos / sin in f64, flip_type 0..3, f32 xy scale, f64 translation) in the reference's arithmetic.
+ * scratch: int32 [n_beams + n]; beam_tmp: int64 [n]; sorted_tmp: f32 [n,3]; counts_out: int32 [2] = {number of curves,
+ * error flags (1 = ring id outside [0, n_beams), 2 = label without an entry in the learning map)}. */
+int ccn_ingest_scan(const float* raw, int64_t n, int32_t rec, const void* labels, int32_t label_bytes, int32_t label_mask,
+                    const int32_t* lut, int32_t lut_size, int32_t n_beams, float curve_thresh, int32_t augment,
+                    double rot_c, double rot_s, int32_t flip_type, float scale, double tx, double ty, double tz,
+                    float pos_div, int32_t* scratch, int64_t* beam_tmp, float* sorted_tmp, int64_t* reorder,
+                    int64_t* inv_reorder, float* pos, float* x, int64_t* y, int64_t* curve_idxs, int32_t* counts_out,
+                    ccn_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Loss / metrics epilogue of the segmentation runs (csrc/loss_metrics.cu).
  * Lovasz-softmax (src/models/utils/lovasz_losses.py:21-33,175-204 via seg_loss, src/run/nuscenes_seg.py:229-243):

@@ -310,6 +310,116 @@ def make_models_extra(rbase):
     return out
 
 
+def _reference_class(relpath: str, class_name: str, names):
+    """A stand-in class whose methods are compiled from the reference's own source text (the module itself cannot be
+    imported here: nuscenes-devkit / cv2 / mitsuba / torch_geometric.data are absent)."""
+    import numpy as np
+    src = open(os.path.join(REF, relpath)).read()
+    tree = ast.parse(src)
+    ns = {"torch": torch, "np": np, "os": os, "Data": lambda **kw: kw}
+    body = {}
+    for node in ast.walk(tree):
+        if isinstance(node, ast.ClassDef) and node.name == class_name:
+            for item in node.body:
+                if isinstance(item, ast.FunctionDef) and item.name in names:
+                    code = textwrap.dedent(ast.get_source_segment(src, item))
+                    exec(compile(code, "%s:%s" % (relpath, item.name), "exec"), ns)
+                    body[item.name] = ns[item.name]
+                elif isinstance(item, ast.Assign) and isinstance(item.targets[0], ast.Name):
+                    body[item.targets[0].id] = eval(compile(ast.Expression(item.value), relpath, "eval"), ns)
+    missing = set(names) - set(body)
+    if missing:
+        raise RuntimeError("not found in %s: %s" % (relpath, sorted(missing)))
+    return type(class_name + "FromSource", (), body)
+
+
+def make_ingest():
+    """Scan ingest: SemNuScenes.get / SemKITTI.get with their own _load_frame, _get_curves and
+    _training_augmentation, compiled from source and run on synthetic raw files written to a temp directory."""
+    import tempfile
+    import numpy as np
+    from curvecloudnet_b200.synthetic import raycast_driving_scan
+    out = {}
+    tmp = tempfile.mkdtemp(prefix="ccn_ingest_")
+
+    # ---- nuScenes: (n,5) f32 records + u8 lidarseg labels, learning map 0..31 -> 0..16
+    raw = raycast_driving_scan(41)
+    n = 5000
+    rec = np.concatenate([raw.points[:n], raw.reflectance[:n, None], raw.beam_ids[:n, None]], axis=1).astype(np.float32)
+    g = np.random.RandomState(5)
+    lmap = {k: int(g.randint(0, 17)) for k in range(32)}
+    lab = g.randint(0, 32, size=n).astype(np.uint8)
+    os.makedirs(os.path.join(tmp, "samples", "LIDAR_TOP"), exist_ok=True)
+    os.makedirs(os.path.join(tmp, "lidarseg"), exist_ok=True)
+    rec.tofile(os.path.join(tmp, "samples", "LIDAR_TOP", "a.pcd.bin"))
+    lab.tofile(os.path.join(tmp, "lidarseg", "a_lidarseg.bin"))
+
+    class _Nusc:
+        dataroot = tmp
+
+        def get(self, table, token):
+            return {"data": {"LIDAR_TOP": "tok"}} if table == "sample" else {"filename": "lidarseg/a_lidarseg.bin"}
+
+    cls = _reference_class("src/data/nuscenes_dataset.py", "SemNuScenes",
+                           ["get", "_load_frame", "_get_curves", "_training_augmentation"])
+    cls.len = lambda self: 1
+    g_nusc = {"raw": torch.from_numpy(rec), "labels": torch.from_numpy(lab),
+              "learning_map": torch.tensor([lmap[k] for k in range(32)], dtype=torch.int32)}
+    for split, seed in (("val", None), ("train", 7), ("test", None)):
+        ds = cls()
+        ds.split, ds.polarmix_aug, ds.learning_map, ds.nusc, ds.data_path = split, False, lmap, _Nusc(), tmp
+        ds.nusc_infos = [{"lidar_path": "x/samples/LIDAR_TOP/a.pcd.bin", "token": "t"}]
+        if seed is not None:
+            np.random.seed(seed)
+        d = ds.get(0)
+        full = {"pos": d["pos"], "x": d["x"], "y": d["y"].to(torch.uint8), "curve_idxs": d["curve_idxs"], "reorder": d["reorder"]}
+        if split != "val":          # only what differs from the validation split is stored
+            for k in ("x", "curve_idxs", "reorder"):
+                assert torch.equal(full[k], g_nusc["val"][k])
+            full = {"pos": full["pos"]} if split == "train" else {"y": full["y"]}
+        g_nusc[split] = full
+        g_nusc[split + "_seed"] = -1 if seed is None else seed
+    out["nuscenes"] = g_nusc
+
+    # ---- KITTI: (n,4) f32 records + i32 labels (instance id in the high 16 bits), sparse learning map
+    raw = raycast_driving_scan(42, beams=64, azimuth_steps=300, elev_deg=(-24.8, 2.0))
+    n = min(6000, raw.points.shape[0])
+    rec = np.concatenate([raw.points[:n], raw.reflectance[:n, None]], axis=1).astype(np.float32)
+    keys = [0, 1, 10, 11, 13, 15, 16, 18, 20, 30, 31, 32, 40, 44, 48, 49, 50, 51, 52, 60, 70, 71, 72, 80, 81, 99, 252,
+            253, 254, 255, 256, 257, 258, 259]
+    kmap = {k: int(g.randint(0, 20)) for k in keys}
+    sem = np.asarray(keys, dtype=np.int32)[g.randint(0, len(keys), size=n)]
+    klab = (sem | (g.randint(0, 500, size=n).astype(np.int32) << 16)).astype(np.int32)
+    os.makedirs(os.path.join(tmp, "seq", "velodyne"), exist_ok=True)
+    os.makedirs(os.path.join(tmp, "seq", "labels"), exist_ok=True)
+    fbin = os.path.join(tmp, "seq", "velodyne", "000000.bin")
+    rec.tofile(fbin)
+    klab.tofile(os.path.join(tmp, "seq", "labels", "000000.label"))
+    kcls = _reference_class("src/data/kitti_dataset.py", "SemKITTI",
+                            ["get", "_load_frame", "_get_curves", "_training_augmentation"])
+    lut = np.full(260, -1, dtype=np.int32)
+    for k, v in kmap.items():
+        lut[k] = v
+    g_kitti = {"raw": torch.from_numpy(rec), "labels": torch.from_numpy(klab), "learning_map": torch.from_numpy(lut)}
+    for split, seed in (("val", None), ("train", 9), ("test", None)):
+        ds = kcls()
+        ds.split, ds.polarmix_aug, ds.learning_map, ds.fpaths = split, False, kmap, [fbin]
+        if seed is not None:
+            np.random.seed(seed)
+        d = ds.get(0)
+        full = {"pos": d["pos"], "x": d["x"], "y": d["y"].to(torch.uint8), "curve_idxs": d["curve_idxs"]}
+        if split != "val":
+            for k in ("x", "curve_idxs"):
+                assert torch.equal(full[k], g_kitti["val"][k])
+            full = {"pos": full["pos"]} if split == "train" else {"y": full["y"]}
+        g_kitti[split] = full
+        g_kitti[split + "_seed"] = -1 if seed is None else seed
+    out["kitti"] = g_kitti
+    import shutil
+    shutil.rmtree(tmp, ignore_errors=True)
+    return out
+
+
 def _compact(obj):
     """int64 -> int32 (all values are small indices) to keep the committed fixtures small;
     tests/golden_utils.load() widens them again."""
@@ -325,6 +435,11 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "losses":     # only the loss / metrics fixture (needs no shims)
         torch.save(make_losses(), os.path.join(OUT, "losses.pt"))
         print("losses.pt", os.path.getsize(os.path.join(OUT, "losses.pt")) // 1024, "KiB")
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "ingest":     # only the scan-ingest fixture (source-compiled dataset methods)
+        sys.path.insert(0, ROOT)
+        torch.save(_compact(make_ingest()), os.path.join(OUT, "ingest.pt"))
+        print("ingest.pt", os.path.getsize(os.path.join(OUT, "ingest.pt")) // 1024, "KiB")
         return
     rpo, rbase, rconv, rfps = _import_reference()
     if len(sys.argv) > 1 and sys.argv[1] == "models_extra":

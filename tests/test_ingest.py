@@ -1,0 +1,170 @@
+"""Scan ingest: raw sweep records -> Data fields.
+
+tests/golden/ingest.pt holds the outputs of the reference's OWN `get()` / `_load_frame` / `_get_curves` /
+`_training_augmentation` (SemNuScenes, SemKITTI; compiled from their source text by oracle/make_golden.py `ingest`) on
+synthetic raw files.  CPU tests pin the oracle restatement (oracle/ccn_ingest.py) against it; GPU tests compare
+`ccn_ingest_scan` (through curvecloudnet_b200.ingest) with the fixture and, on full-size sweeps, with the oracle.
+Tolerances: everything integer / index / label / reflectance is bit-exact; positions are bit-exact without augmentation
+and within 1 ulp (f32) with it (the reference's rotation is a BLAS f64 product whose summation order is not specified).
+"""
+import numpy as np
+import pytest
+import torch
+
+from golden_utils import load
+
+G = load("ingest.pt")
+
+
+def _lmap_dict(lut):
+    return {k: int(v) for k, v in enumerate(lut.tolist()) if v >= 0}
+
+
+def _labels_np(ds):
+    lab = G[ds]["labels"]
+    return lab.numpy().astype(np.uint8) if ds == "nuscenes" else lab.numpy().astype(np.int32)
+
+
+def _ulp_close(a, b, ulps=1):
+    a, b = a.double(), b.double()
+    tol = ulps * torch.maximum(b.abs(), torch.full_like(b, 1e-30)).float().double() * 2.0 ** -23
+    return bool(torch.all((a - b).abs() <= tol))
+
+
+# ------------------------------------------------------------------------------------------------ CPU: the oracle
+@pytest.mark.parametrize("ds", ["nuscenes", "kitti"])
+def test_oracle_ingest_matches_reference(ds):
+    from oracle import ccn_ingest as oi
+    g = G[ds]
+    raw = g["raw"].numpy()
+    lm = _lmap_dict(g["learning_map"])
+    val = oi.ingest_scan(raw, _labels_np(ds), lm, ds, None)
+    for k in ("pos", "x", "curve_idxs"):
+        assert torch.equal(val[k], g["val"][k]), k
+    assert torch.equal(val["y"], g["val"]["y"].long())
+    if ds == "nuscenes":
+        assert torch.equal(val["inv_reorder"], g["val"]["reorder"])
+    np.random.seed(int(g["train_seed"]))
+    aug = oi.draw_augmentation(ds)
+    tr = oi.ingest_scan(raw, _labels_np(ds), lm, ds, aug)
+    assert _ulp_close(tr["pos"], g["train"]["pos"])
+    assert (tr["pos"] != g["train"]["pos"]).float().mean() < 1e-3      # the 1-ulp allowance is for rare ties only
+    te = oi.ingest_scan(raw, None, lm, ds, None)
+    assert torch.equal(te["y"], g["test"]["y"].long())
+
+
+@pytest.mark.parametrize("ds", ["nuscenes", "kitti"])
+def test_augmentation_draws_replay_the_reference_order(ds):
+    from curvecloudnet_b200.ingest import ScanAugmentation
+    from oracle import ccn_ingest as oi
+    np.random.seed(123)
+    a = oi.draw_augmentation(ds)
+    np.random.seed(123)
+    b = ScanAugmentation.draw(ds)
+    assert (a["rot_c"], a["rot_s"], a["flip"], a["scale"]) == (b.rot_c, b.rot_s, b.flip, b.scale)
+    assert tuple(a["translate"]) == tuple(b.translate)
+    if ds == "kitti":
+        assert b.rot_c >= 0.0                                          # +-90 degrees
+
+
+# ------------------------------------------------------------------------------------------------ GPU: the CUDA path
+@pytest.mark.gpu
+@pytest.mark.parametrize("ds", ["nuscenes", "kitti"])
+def test_ingest_matches_reference_golden(ds):
+    from curvecloudnet_b200.ingest import LearningMap, ScanAugmentation, ingest_scan
+    g = G[ds]
+    lm = LearningMap(_lmap_dict(g["learning_map"]))
+    raw_bytes = g["raw"].numpy().tobytes()                              # the .bin file content
+    lab_bytes = _labels_np(ds).tobytes()
+    d = ingest_scan(raw_bytes, lab_bytes, lm, ds)
+    for k in ("pos", "x", "curve_idxs"):
+        assert torch.equal(getattr(d, k).cpu(), g["val"][k]), k
+    assert torch.equal(d.y.cpu(), g["val"]["y"].long())
+    if ds == "nuscenes":
+        assert torch.equal(d.reorder.cpu(), g["val"]["reorder"])
+    assert int(d.counts[0]) == int(g["val"]["curve_idxs"].max()) + 1
+    np.random.seed(int(g["train_seed"]))
+    t = ingest_scan(g["raw"], _labels_np(ds), lm, ds, ScanAugmentation.draw(ds))
+    assert _ulp_close(t.pos.cpu(), g["train"]["pos"])
+    assert (t.pos.cpu() != g["train"]["pos"]).float().mean() < 1e-3
+    assert torch.equal(t.y.cpu(), g["val"]["y"].long()) and torch.equal(t.curve_idxs.cpu(), g["val"]["curve_idxs"])
+    te = ingest_scan(g["raw"], None, None, ds)
+    assert torch.equal(te.y.cpu(), g["test"]["y"].long())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ds,seed,beams,az,elev", [("nuscenes", 51, 32, 1085, (-30.67, 10.67)),
+                                                   ("kitti", 52, 64, 1875, (-24.8, 2.0))])
+def test_ingest_full_sweep_matches_oracle(ds, seed, beams, az, elev):
+    from curvecloudnet_b200.ingest import LearningMap, ScanAugmentation, ingest_scan
+    from curvecloudnet_b200.synthetic import raycast_driving_scan
+    from oracle import ccn_ingest as oi
+    raw = raycast_driving_scan(seed, beams=beams, azimuth_steps=az, elev_deg=elev)
+    cols = [raw.points, raw.reflectance[:, None]] + ([raw.beam_ids[:, None]] if ds == "nuscenes" else [])
+    rec = np.concatenate(cols, axis=1).astype(np.float32)
+    n = rec.shape[0]
+    gen = np.random.RandomState(seed)
+    mapping = {k: int(gen.randint(0, 17)) for k in range(0, 64, 2)}
+    keys = np.asarray(sorted(mapping))
+    lab = keys[gen.randint(0, len(keys), size=n)]
+    lab = lab.astype(np.uint8) if ds == "nuscenes" else (lab | (gen.randint(0, 99, size=n) << 16)).astype(np.int32)
+    np.random.seed(seed)
+    aug_o = oi.draw_augmentation(ds)
+    np.random.seed(seed)
+    aug = ScanAugmentation.draw(ds)
+    for a_o, a in ((None, None), (aug_o, aug)):
+        want = oi.ingest_scan(rec, lab, mapping, ds, a_o)
+        got = ingest_scan(rec, lab, LearningMap(mapping), ds, a)
+        assert torch.equal(got.x.cpu(), want["x"]) and torch.equal(got.y.cpu(), want["y"])
+        assert torch.equal(got.curve_idxs.cpu(), want["curve_idxs"]) and torch.equal(got.reorder.cpu(), want["inv_reorder"])
+        if a is None:
+            assert torch.equal(got.pos.cpu(), want["pos"])
+        else:
+            assert _ulp_close(got.pos.cpu(), want["pos"])
+    # size-independent properties: x / y are a permutation of the inputs, curve ids are non-decreasing and dense
+    assert torch.equal(torch.sort(got.x.cpu().flatten())[0], torch.sort(torch.from_numpy(rec[:, 3].copy()))[0])
+    cid = got.curve_idxs.cpu()
+    assert int(cid[0]) == 0 and bool(torch.all((cid[1:] - cid[:-1]) >= 0)) and bool(torch.all((cid[1:] - cid[:-1]) <= 1))
+
+
+@pytest.mark.gpu
+def test_ingest_edge_cases_and_errors():
+    from curvecloudnet_b200.ingest import LearningMap, ingest_scan
+    lm = LearningMap({0: 0, 1: 3})
+    d = ingest_scan(np.zeros((0, 5), np.float32), np.zeros((0,), np.uint8), lm, "nuscenes")
+    assert d.pos.shape == (0, 3) and d.y.shape == (0,) and d.counts.tolist() == [0, 0]
+    one = np.array([[1.0, 2.0, 3.0, 7.0, 5.0]], np.float32)
+    d = ingest_scan(one, np.array([1], np.uint8), lm, "nuscenes")
+    assert d.y.tolist() == [3] and d.curve_idxs.tolist() == [0] and d.x.tolist() == [[7.0]]
+    assert torch.equal(d.pos.cpu(), torch.tensor([[1.0, 2.0, 3.0]]) / 20)
+    with pytest.raises(KeyError):                                       # learning_map.__getitem__ KeyError upstream
+        ingest_scan(one, np.array([2], np.uint8), lm, "nuscenes")
+    with pytest.raises(ValueError):                                     # ring id outside [0, n_beams)
+        ingest_scan(np.array([[1.0, 2.0, 3.0, 7.0, 40.0]], np.float32), np.array([1], np.uint8), lm, "nuscenes")
+    with pytest.raises(ValueError):                                     # truncated file
+        ingest_scan(np.zeros(7, np.float32), None, None, "nuscenes")
+    with pytest.raises(ValueError):
+        ingest_scan(one, np.array([1, 1], np.uint8), lm, "nuscenes")
+
+
+@pytest.mark.gpu
+def test_ingest_batch_feeds_the_model():
+    """raw records -> ingest_batch -> forward: the ingested Batch is what ModelBase.forward consumes."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.ingest import LearningMap, ingest_batch
+    from curvecloudnet_b200.synthetic import randomize_model_, raycast_driving_scan
+    sweeps = []
+    for seed in (61, 62):
+        raw = raycast_driving_scan(seed, azimuth_steps=200)
+        rec = np.concatenate([raw.points, raw.reflectance[:, None], raw.beam_ids[:, None]], axis=1).astype(np.float32)
+        sweeps.append({"raw": rec, "labels": np.zeros(rec.shape[0], np.uint8)})
+    batch = ingest_batch(sweeps, LearningMap({0: 0}), "nuscenes", augment=True, rng=np.random.RandomState(3))
+    n = sum(s["raw"].shape[0] for s in sweeps)
+    assert batch.pos.shape == (n, 3) and batch.batch.shape == (n,) and int(batch.batch[-1]) == 1
+    from curvecloudnet_b200.model import ModelBase
+    model = build_model(ModelBase, "nuscenes")
+    randomize_model_(model, 1234)
+    model = model.cuda().eval()
+    with torch.no_grad():
+        out = model(batch)
+    assert out.shape[0] == n and bool(torch.isfinite(out).all())

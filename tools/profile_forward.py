@@ -47,14 +47,15 @@ tot = sum(d["ms"] for d in prof.values())
 print("sum of per-call device times: %.3f ms over %d calls" % (tot, sum(d["calls"] for d in prof.values())))
 for k, d in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]):
     print("  %-28s calls %4d  %8.3f ms  %5.1f%%" % (k, d["calls"], d["ms"], 100 * d["ms"] / tot))
-print("linear calls (M, N, K) us TFLOP/s:")
+print("linear calls (M, N, K) us TFLOP/s, algorithmic MB and GB/s:")
 rows = []
-for name, a, b, work in ev:
+for name, a, b, work, nbytes in ev:
     if name.startswith("ccn_linear"):
-        rows.append((a.elapsed_time(b) * 1e3, work))
+        rows.append((a.elapsed_time(b) * 1e3, work, nbytes))
 shapes = native._prof_shapes
-for (us, work), shp in zip(rows, shapes):
-    print("   M=%7d N=%5d K=%5d  %8.1f us  %7.1f TF/s" % (shp[0], shp[1], shp[2], us, work / us / 1e6))
+for (us, work, nbytes), shp in zip(rows, shapes):
+    print("   M=%7d N=%5d K=%5d  %8.1f us  %7.1f TF/s  %8.2f MB  %7.0f GB/s"
+          % (shp[0], shp[1], shp[2], us, work / us / 1e6, nbytes / 1e6, nbytes / us / 1e3))
 
 # per-kernel achieved bandwidth: argument footprint (bytes of every tensor argument: inputs read + outputs written;
 # gathers count their whole source) / device time, against the measured HBM copy peak
@@ -64,7 +65,7 @@ try:
 except Exception:
     peak = 6650.0
 agg = collections.OrderedDict()
-for (name, a, b, work), fb in zip(ev, foot):
+for (name, a, b, work, _nb), fb in zip(ev, foot):
     d = agg.setdefault(name, [0.0, 0.0, 0])
     d[0] += fb; d[1] += a.elapsed_time(b) * 1e-3; d[2] += 1
 print("per-entry-point footprint bandwidth (peak %.0f GB/s measured copy bandwidth):" % peak)

@@ -54,7 +54,7 @@ print("%s %s B=%d (%d points): sum of per-call device times %.3f ms over %d call
       % (name, prec, B, data.pos.shape[0], tot, sum(d["calls"] for d in prof.values())))
 for k, d in sorted(prof.items(), key=lambda kv: -kv[1]["ms"]):
     print("  %-28s calls %4d  %8.3f ms  %5.1f%%" % (k, d["calls"], d["ms"], 100 * d["ms"] / tot))
-rows = [(n, a.elapsed_time(b) * 1e3, w) for n, a, b, w in ev if n in native._WORK]
+rows = [(n, a.elapsed_time(b) * 1e3, w) for n, a, b, w, _nb in ev if n in native._WORK]
 print("GEMM-shaped calls (M, N, K) us TFLOP/s:")
 for (n, us, w), shp in zip(rows, shapes):
     print("   %-18s M=%7d N=%5d K=%5d  %8.1f us  %7.1f TF/s" % (n, shp[0], shp[1], shp[2], us, w / us / 1e6))
