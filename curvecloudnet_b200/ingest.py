@@ -6,9 +6,11 @@ augmentation and the position normalisation run in ONE C-ABI call (`ccn_ingest_s
 file bytes; the host only draws the augmentation's random numbers (same numpy calls, same order as the reference, so a
 seeded run reproduces the reference's augmented sweep) and moves the bytes.
 
-PolarMix (`_apply_polarmix`, data_utils.py:5-85) is unreachable in the reference as shipped (it calls methods that do not
-exist: `_load_nusc_data`, `_polarmix`), and A2D2's five-sensor curve builder (audi_dataset.py:140-210) is a different
-algorithm; neither is part of this entry point.
+PolarMix (`polarmix` / `swap` / `rotate_copy`, data_utils.py:5-85, driven like `_apply_polarmix` drives them) runs on the
+device as well (`ccn_polarmix`, csrc/polarmix.cu) between the grouping and the augmentation: `ingest_scan_polarmix`.  (The
+dataset methods that call it are broken as shipped - `_load_nusc_data` / `_polarmix` do not exist - so the partner sweep is
+handed in by the caller.)  A2D2's five-sensor kNN curve builder (audi_dataset.py:140-210) is a different algorithm and not
+part of this module.
 """
 from __future__ import annotations
 
@@ -23,6 +25,9 @@ from .model import Batch
 
 POS_NORMALIZE = 20.0          # nuscenes_dataset.py:18, kitti_dataset.py:17
 CURVE_THRESH = 0.08           # nuscenes_dataset.py:17, kitti_dataset.py:16
+
+# polarmix instance classes (nuscenes_dataset.py:12-13, kitti_dataset.py:10-12)
+INSTANCE_CLASSES = {"nuscenes": (2, 3, 4, 5, 6, 7, 9, 10), "kitti": (1, 2, 3, 4, 5, 6, 7, 8)}
 
 ERR_RING = 1
 ERR_LABEL = 2
@@ -110,7 +115,7 @@ def _as_device(buf, dtype, device):
 
 def ingest_scan(raw, labels=None, learning_map: Optional[LearningMap] = None, dataset: str = "nuscenes",
                 augmentation: Optional[ScanAugmentation] = None, n_beams: int = 32, device="cuda",
-                check: bool = True) -> Batch:
+                check: bool = True, pos_div: float = POS_NORMALIZE) -> Batch:
     """One sweep -> `Data` fields (a one-sample attribute bag; `ingest_batch` concatenates).
 
     raw     the `.bin` file content: (n,5) f32 x y z intensity ring for nuScenes, (n,4) f32 x y z remission for KITTI
@@ -155,7 +160,7 @@ def ingest_scan(raw, labels=None, learning_map: Optional[LearningMap] = None, da
         native.call("ccn_ingest_scan", rawd, n, rec, labd, label_bytes, 0xFFFF if label_bytes == 4 else 0xFF, lut, lut_size,
                     nb, CURVE_THRESH, 1 if a is not None else 0, float(a.rot_c) if a else 1.0, float(a.rot_s) if a else 0.0,
                     int(a.flip) if a else 0, float(a.scale) if a else 1.0, float(t[0]), float(t[1]), float(t[2]),
-                    POS_NORMALIZE, scratch, beam_tmp, sorted_tmp, reorder, inv, pos, x, y, cid, counts)
+                    float(pos_div), scratch, beam_tmp, sorted_tmp, reorder, inv, pos, x, y, cid, counts)
         if check:
             flags = int(counts[1].item())                    # host sync
             if flags & ERR_RING:
@@ -163,6 +168,81 @@ def ingest_scan(raw, labels=None, learning_map: Optional[LearningMap] = None, da
             if flags & ERR_LABEL:
                 raise KeyError("ingest_scan: label without an entry in the learning map")
     return Batch(x=x, pos=pos, y=y, curve_idxs=cid, reorder=inv, counts=counts)
+
+
+@dataclass
+class PolarMixDraw:
+    """The drawn values of `_apply_polarmix` + `polarmix` (nuscenes_dataset.py:151-166, data_utils.py:69-85)."""
+    idx2: int
+    alpha: float
+    beta: float
+    omega0: float
+    omega1: float
+    do_swap: bool
+    do_paste: bool
+
+    @classmethod
+    def draw(cls, n_sweeps: int, rng=np.random) -> "PolarMixDraw":
+        """Same numpy calls in the same order as the reference (partner sweep, sector, rotation angles, two gates)."""
+        idx2 = int(rng.randint(n_sweeps))
+        alpha = (rng.random() - 1) * np.pi
+        beta = alpha + np.pi
+        omega0 = rng.random() * np.pi * 2 / 3
+        omega1 = (rng.random() + 1) * np.pi * 2 / 3
+        do_swap = bool(rng.random() < 0.5)
+        do_paste = bool(rng.random() < 0.5)
+        return cls(idx2, float(alpha), float(beta), float(omega0), float(omega1), do_swap, do_paste)
+
+
+def polarmix(d1: Batch, d2: Batch, mix: PolarMixDraw, instance_classes: Sequence[int]) -> Batch:
+    """`polarmix` (data_utils.py:69-85) + the curve-id bookkeeping of `_apply_polarmix` on two ingested sweeps whose
+    positions are still in sensor units (`ingest_scan(..., pos_div=1.0)`, no augmentation).  One host sync (the size of
+    the result)."""
+    import ctypes
+    n1, n2 = d1.pos.shape[0], d2.pos.shape[0]
+    if n1 == 0 or n2 == 0:
+        raise ValueError("polarmix needs two non-empty sweeps")       # np.max of an empty array raises upstream too
+    dev = d1.pos.device
+    n_max = n1 + 4 * n2
+    pos = torch.empty((n_max, 3), dtype=torch.float32, device=dev)
+    x = torch.empty((n_max, 1), dtype=torch.float32, device=dev)
+    y = torch.empty((n_max,), dtype=torch.int64, device=dev)
+    cid = torch.empty((n_max,), dtype=torch.int64, device=dev)
+    counts = torch.zeros((2,), dtype=torch.int32, device=dev)
+    scratch = torch.empty((2 * n1 + 7 * n2 + 8,), dtype=torch.int32, device=dev)
+    cls = (ctypes.c_int32 * max(len(instance_classes), 1))(*[int(c) for c in instance_classes])
+    native.call("ccn_polarmix", d1.pos, d1.x, d1.y, d1.curve_idxs, n1, d2.pos, d2.x, d2.y, d2.curve_idxs, n2, d2.counts,
+                int(mix.do_swap), float(np.float32(mix.alpha)), float(np.float32(mix.beta)), int(mix.do_paste),
+                ctypes.addressof(cls), len(instance_classes), float(mix.omega0), float(mix.omega1), scratch, pos, x, y, cid,
+                counts)
+    n_out, n_curves = counts.tolist()                                   # host sync
+    return Batch(x=x[:n_out], pos=pos[:n_out], y=y[:n_out], curve_idxs=cid[:n_out], counts=counts)
+
+
+def augment_points(pos: torch.Tensor, augmentation: Optional[ScanAugmentation], pos_div: float = POS_NORMALIZE):
+    """`_training_augmentation` + `points /= POS_NORMALIZE` on grouped points (the tail of `get()` after PolarMix)."""
+    out = torch.empty_like(pos)
+    a = augmentation
+    t = a.translate if a is not None else (0.0, 0.0, 0.0)
+    native.call("ccn_augment_points", pos, pos.shape[0], 1 if a is not None else 0, float(a.rot_c) if a else 1.0,
+                float(a.rot_s) if a else 0.0, int(a.flip) if a else 0, float(a.scale) if a else 1.0, float(t[0]), float(t[1]),
+                float(t[2]), float(pos_div), out)
+    return out
+
+
+def ingest_scan_polarmix(sweep1: dict, sweep2: dict, mix: PolarMixDraw, learning_map: LearningMap,
+                         dataset: str = "nuscenes", augmentation: Optional[ScanAugmentation] = None, n_beams: int = 32,
+                         device="cuda") -> Batch:
+    """`get()` of the training split with `polarmix_aug` (nuscenes_dataset.py:42-65): ingest both sweeps, mix them, then
+    augment and normalise.  sweep = {"raw": ..., "labels": ...}; `mix.idx2` selected sweep2 (the caller owns the files)."""
+    d1 = ingest_scan(sweep1["raw"], sweep1.get("labels"), learning_map, dataset, None, n_beams, device, False, 1.0)
+    d2 = ingest_scan(sweep2["raw"], sweep2.get("labels"), learning_map, dataset, None, n_beams, device, False, 1.0)
+    out = polarmix(d1, d2, mix, INSTANCE_CLASSES[dataset])
+    flags = int(torch.maximum(d1.counts[1], d2.counts[1]).item())
+    if flags:
+        raise ValueError("ingest_scan_polarmix: ring id out of range or unmapped label (flags %d)" % flags)
+    out.pos = augment_points(out.pos, augmentation)
+    return out
 
 
 def ingest_batch(sweeps: List[dict], learning_map: Optional[LearningMap] = None, dataset: str = "nuscenes",

@@ -325,6 +325,26 @@ int ccn_ingest_scan(const float* raw, int64_t n, int32_t rec, const void* labels
                     int64_t* inv_reorder, float* pos, float* x, int64_t* y, int64_t* curve_idxs, int32_t* counts_out,
                     ccn_stream_t stream);
 
+/* PolarMix of two ingested sweeps - swap / rotate_copy / polarmix (src/data/data_utils.py:5-85) as driven by
+ * _apply_polarmix (src/data/nuscenes_dataset.py:151-178, src/data/kitti_dataset.py:94-121), including the final
+ * torch.unique(curve_idxs, return_inverse=True).  Inputs per sweep: xyz (n,3) in sensor units, reflectance (n), labels (n)
+ * i64 in [0,256), curve ids (n) i64 dense, non-decreasing, starting at 0 (what ccn_ingest_scan emits with pos_div = 1 and
+ * no augmentation); n_curves2: DEVICE int32 (counts_out[0] of sweep 2's ingest).  The DRAWN values come from the host:
+ * do_swap / do_paste (the two np.random.random() < 0.5 gates), alpha / beta (yaw sector, compared in f32 like numpy
+ * does), omega0 / omega1; instance_classes: HOST int32 [n_classes].  Outputs hold up to n1 + 4 n2 points:
+ * [sweep 1 outside the sector][sweep 2 inside][instance points of sweep 2][rotated by omega0][rotated by omega1];
+ * cid_out = dense ids; counts_out: DEVICE int32 [2] = {points, curves}.  scratch: int32 [2 n1 + 7 n2 + 8]. */
+int ccn_polarmix(const float* pos1, const float* x1, const int64_t* y1, const int64_t* cid1, int64_t n1,
+                 const float* pos2, const float* x2, const int64_t* y2, const int64_t* cid2, int64_t n2,
+                 const int32_t* n_curves2, int32_t do_swap, float alpha, float beta, int32_t do_paste,
+                 const int32_t* instance_classes, int32_t n_classes, double omega0, double omega1, int32_t* scratch,
+                 float* pos_out, float* x_out, int64_t* y_out, int64_t* cid_out, int32_t* counts_out,
+                 ccn_stream_t stream);
+/* _training_augmentation + position normalisation on already grouped points (the tail of ccn_ingest_scan as its own
+ * entry, for the PolarMix path where the mix sits between the grouping and the augmentation). */
+int ccn_augment_points(const float* pos_in, int64_t n, int32_t augment, double rot_c, double rot_s, int32_t flip_type,
+                       float scale, double tx, double ty, double tz, float pos_div, float* pos_out, ccn_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------------------------
  * Loss / metrics epilogue of the segmentation runs (csrc/loss_metrics.cu).
  * Lovasz-softmax (src/models/utils/lovasz_losses.py:21-33,175-204 via seg_loss, src/run/nuscenes_seg.py:229-243):

@@ -6,8 +6,10 @@ Follows SemNuScenes.get / _load_frame / _get_curves / _training_augmentation
 (src/data/kitti_dataset.py:40-152).  Pinned by tests/golden/ingest.pt, generated from those methods' own source
 text by oracle/make_golden.py (mode `ingest`).
 
-PolarMix (`_apply_polarmix`, data_utils.py:5-85) is unreachable in the reference as shipped: the nuScenes method
-calls `self._load_nusc_data` and SemKITTI.get calls `self._polarmix`, neither of which exists - it is not restated.
+PolarMix: `polarmix` / `swap` / `rotate_copy` (data_utils.py:5-85) are restated below and pinned by golden vectors of
+the real functions; the dataset methods that drive them are broken as shipped (the nuScenes `_apply_polarmix` calls
+`self._load_nusc_data`, `SemKITTI.get` calls `self._polarmix`; neither exists), so the restatement follows the body of
+`_apply_polarmix` with the partner sweep handed in.
 """
 from __future__ import annotations
 
@@ -52,7 +54,7 @@ def training_augmentation(xyz: np.ndarray, aug) -> np.ndarray:
     return xyz
 
 
-def ingest_scan(raw: np.ndarray, labels, learning_map, dataset: str = "nuscenes", aug=None):
+def ingest_scan(raw: np.ndarray, labels, learning_map, dataset: str = "nuscenes", aug=None, pos_div=POS_NORMALIZE):
     """raw: (n,5) f32 nuScenes records or (n,4) f32 KITTI records; labels: u8 (nuScenes) / i32 (KITTI) / None (test
     split); learning_map: dict raw label -> class.  -> dict(pos, x, y, curve_idxs, reorder, inv_reorder)."""
     n = raw.shape[0]
@@ -72,6 +74,63 @@ def ingest_scan(raw: np.ndarray, labels, learning_map, dataset: str = "nuscenes"
     xyz = pts[reorder].numpy()
     if aug is not None:
         xyz = training_augmentation(xyz, aug)
-    pos = torch.from_numpy(xyz) / POS_NORMALIZE
+    pos = torch.from_numpy(xyz) / pos_div
     return {"pos": pos, "x": torch.from_numpy(raw[:, 3].copy())[reorder][:, None],
             "y": torch.from_numpy(lab)[reorder].long(), "curve_idxs": cid.long(), "reorder": reorder, "inv_reorder": inv}
+
+
+# ------------------------------------------------------------------------------------------------------ PolarMix
+def draw_polarmix(n_sweeps: int, rng=np.random):
+    """Draw order of `_apply_polarmix` + `polarmix` (nuscenes_dataset.py:151-166, data_utils.py:69-85)."""
+    idx2 = int(rng.randint(n_sweeps))
+    alpha = (rng.random() - 1) * np.pi
+    omega = [rng.random() * np.pi * 2 / 3, (rng.random() + 1) * np.pi * 2 / 3]
+    return {"idx2": idx2, "alpha": alpha, "beta": alpha + np.pi, "omega": omega,
+            "do_swap": bool(rng.random() < 0.5), "do_paste": bool(rng.random() < 0.5)}
+
+
+def _sector(rows: np.ndarray, lo, hi) -> np.ndarray:
+    yaw = -np.arctan2(rows[:, 1], rows[:, 0])                      # f32 in, f32 out (data_utils.py:7-9)
+    return (yaw > np.float32(lo)) & (yaw < np.float32(hi))
+
+
+def polarmix(d1, d2, mix, instance_classes):
+    """data_utils.py:5-85 with the draws given, on two ingested sweeps (pos in sensor units, dense curve ids), plus
+    the id bookkeeping of `_apply_polarmix` (nuscenes_dataset.py:151-178): sweep-2 ids += max(sweep-1 ids) before, dense
+    ranks (`torch.unique(..., return_inverse=True)`) after.  Rows are [x y z reflectance curve_id] in f32."""
+    def rows_of(d, off):
+        cid = (d["curve_idxs"].numpy() + off).astype(np.float32)
+        return np.concatenate([d["pos"].numpy(), d["x"].numpy().reshape(-1, 1), cid[:, None]], axis=1).astype(np.float32)
+
+    r1 = rows_of(d1, 0)
+    r2 = rows_of(d2, int(d1["curve_idxs"].max()))
+    l1, l2 = d1["y"].numpy().astype(np.uint8), d2["y"].numpy().astype(np.uint8)
+    rows, labs = r1, l1
+    if mix["do_swap"]:                                              # swap(): sweep 1 outside the sector + sweep 2 inside
+        m1, m2 = _sector(r1, mix["alpha"], mix["beta"]), _sector(r2, mix["alpha"], mix["beta"])
+        rows = np.concatenate([r1[~m1], r2[m2]])
+        labs = np.concatenate([l1[~m1], l2[m2]])
+    if mix["do_paste"]:                                             # rotate_copy() of sweep 2's instance points
+        sel = np.concatenate([np.nonzero(l2 == c)[0] for c in instance_classes])
+        sel = sel[np.argsort(r2[sel, 4], kind="stable")]
+        inst, ilab = r2[sel], l2[sel]
+        copies, prev = [inst], inst
+        for om in mix["omega"]:
+            c, s = np.cos(om), np.sin(om)
+            new = np.zeros_like(inst)
+            x, y = inst[:, 0].astype(np.float64), inst[:, 1].astype(np.float64)
+            new[:, 0] = x * c + y * (-s)
+            new[:, 1] = x * s + y * c
+            new[:, 2] = inst[:, 2]
+            new[:, 3] = inst[:, 3]
+            if len(inst):
+                new[:, 4] = inst[:, 4] + np.max(prev[:, 4])
+            copies.append(new)
+            prev = new
+        pasted = np.concatenate(copies)
+        pasted[:, 4] += np.max(rows[:, 4])
+        rows = np.concatenate([rows, pasted])
+        labs = np.concatenate([labs, ilab, ilab, ilab])
+    dense = torch.unique(torch.from_numpy(rows[:, 4].copy()), return_inverse=True)[1]
+    return {"pos": torch.from_numpy(rows[:, :3].copy()), "x": torch.from_numpy(rows[:, 3:4].copy()),
+            "y": torch.from_numpy(labs).long(), "curve_idxs": dense.long()}

@@ -420,6 +420,63 @@ def make_ingest():
     return out
 
 
+def polarmix_inputs(n=1500):
+    """Two synthetic nuScenes sweeps (records + class labels) for the PolarMix fixture; tests rebuild them from here."""
+    import numpy as np
+    from curvecloudnet_b200.synthetic import raycast_driving_scan
+    out = []
+    for seed in (71, 72):
+        raw = raycast_driving_scan(seed)
+        sl = slice(seed * 10, seed * 10 + n)
+        rec = np.concatenate([raw.points[sl], raw.reflectance[sl, None], raw.beam_ids[sl, None]], axis=1).astype(np.float32)
+        lab = np.random.RandomState(seed).randint(0, 17, size=n).astype(np.uint8)
+        out.append((rec, lab))
+    return out
+
+
+def make_polarmix():
+    """PolarMix: the REAL `polarmix` of src/data/data_utils.py (imported from its file), driven
+    like `_apply_polarmix` (nuscenes_dataset.py:151-178) drives it: sweep-2 ids += max(sweep-1 ids), rows
+    [xyz, reflectance, curve id] concatenated in f32, polarmix(...), torch.unique(..., return_inverse=True)."""
+    import importlib.util
+    import numpy as np
+    from oracle import ccn_ingest as oi
+    spec = importlib.util.spec_from_file_location("ref_data_utils", os.path.join(REF, "src/data/data_utils.py"))
+    du = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(du)
+    ident = {k: k for k in range(32)}
+    (rec1, lab1), (rec2, lab2) = polarmix_inputs()
+    d1 = oi.ingest_scan(rec1, lab1, ident, "nuscenes", None, pos_div=1.0)
+    d2 = oi.ingest_scan(rec2, lab2, ident, "nuscenes", None, pos_div=1.0)
+    classes = [2, 3, 4, 5, 6, 7, 9, 10]                                  # nuscenes_dataset.py:12-13
+    out = {"labels1": torch.from_numpy(lab1), "labels2": torch.from_numpy(lab2), "instance_classes": classes, "cases": []}
+    want = {(True, True), (True, False), (False, True), (False, False)}
+    seed = 0
+    while want:
+        seed += 1
+        g = np.random.RandomState(seed)
+        gates = (bool(g.random_sample() < 0.5), bool(g.random_sample() < 0.5))
+        if gates not in want:
+            continue
+        want.discard(gates)
+        alpha = (np.random.RandomState(100 + seed).random_sample() - 1) * np.pi
+        beta = alpha + np.pi
+        omega = [0.37 * np.pi * 2 / 3, 1.61 * np.pi * 2 / 3]
+        cid2 = d2["curve_idxs"] + torch.max(d1["curve_idxs"])
+        in1 = torch.cat([d1["pos"], d1["x"], d1["curve_idxs"].reshape(-1, 1)], dim=-1)
+        in2 = torch.cat([d2["pos"], d2["x"], cid2.reshape(-1, 1)], dim=-1)
+        np.random.seed(seed)                                             # the two gates are drawn inside polarmix
+        aug, laug = du.polarmix(in1.numpy(), d1["y"].numpy().flatten().astype(np.uint8), in2.numpy(),
+                                d2["y"].numpy().flatten().astype(np.uint8), alpha=alpha, beta=beta,
+                                instance_classes=classes, Omega=omega)
+        dense = torch.unique(torch.from_numpy(aug[:, 4].copy()), return_inverse=True)[1]
+        out["cases"].append({"seed": seed, "do_swap": gates[0], "do_paste": gates[1], "alpha": float(alpha),
+                             "beta": float(beta), "omega": [float(o) for o in omega],
+                             "pos": torch.from_numpy(aug[:, :3].copy()), "x": torch.from_numpy(aug[:, 3:4].copy()),
+                             "y": torch.from_numpy(laug.astype(np.uint8)), "curve_idxs": dense})
+    return out
+
+
 def _compact(obj):
     """int64 -> int32 (all values are small indices) to keep the committed fixtures small;
     tests/golden_utils.load() widens them again."""
@@ -440,6 +497,11 @@ def main():
         sys.path.insert(0, ROOT)
         torch.save(_compact(make_ingest()), os.path.join(OUT, "ingest.pt"))
         print("ingest.pt", os.path.getsize(os.path.join(OUT, "ingest.pt")) // 1024, "KiB")
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "polarmix":   # only the PolarMix fixture (the real data_utils.polarmix)
+        sys.path.insert(0, ROOT)
+        torch.save(_compact(make_polarmix()), os.path.join(OUT, "polarmix.pt"))
+        print("polarmix.pt", os.path.getsize(os.path.join(OUT, "polarmix.pt")) // 1024, "KiB")
         return
     rpo, rbase, rconv, rfps = _import_reference()
     if len(sys.argv) > 1 and sys.argv[1] == "models_extra":

@@ -25,9 +25,10 @@ def _labels_np(ds):
     return lab.numpy().astype(np.uint8) if ds == "nuscenes" else lab.numpy().astype(np.int32)
 
 
-def _ulp_close(a, b, ulps=1):
+def _ulp_close(a, b, ulps=1, floor=1e-30):
+    """|a - b| <= ulps * 2^-23 * max(|b|, floor); `floor` > 0 where a translation may cancel the magnitude."""
     a, b = a.double(), b.double()
-    tol = ulps * torch.maximum(b.abs(), torch.full_like(b, 1e-30)).float().double() * 2.0 ** -23
+    tol = ulps * torch.maximum(b.abs(), torch.full_like(b, floor)).float().double() * 2.0 ** -23
     return bool(torch.all((a - b).abs() <= tol))
 
 
@@ -168,3 +169,102 @@ def test_ingest_batch_feeds_the_model():
     with torch.no_grad():
         out = model(batch)
     assert out.shape[0] == n and bool(torch.isfinite(out).all())
+
+
+# ================================================================================================ PolarMix
+# tests/golden/polarmix.pt: outputs of the REAL `polarmix` (src/data/data_utils.py:69-85, with swap / rotate_copy) driven
+# like `_apply_polarmix` drives it, for the four gate combinations.  Selection, order, labels, reflectance and dense
+# curve ids are bit-exact; the rotated copies are within 1 ulp (f64 BLAS product upstream).
+PM = load("polarmix.pt")
+
+
+def _pm_sweeps():
+    from oracle.make_golden import polarmix_inputs
+    return polarmix_inputs()
+
+
+def _pm_check(got, case):
+    n = case["pos"].shape[0]
+    assert got["pos"].shape[0] == n
+    assert torch.equal(got["y"].cpu(), case["y"].long())
+    assert torch.equal(got["x"].cpu().reshape(-1), case["x"].reshape(-1))
+    assert torch.equal(got["curve_idxs"].cpu(), case["curve_idxs"])
+    assert _ulp_close(got["pos"].cpu(), case["pos"])
+    assert (got["pos"].cpu() != case["pos"]).float().mean() < 1e-3
+
+
+@pytest.mark.parametrize("ci", range(4))
+def test_oracle_polarmix_matches_reference(ci):
+    from oracle import ccn_ingest as oi
+    case = PM["cases"][ci]
+    ident = {k: k for k in range(32)}
+    (rec1, lab1), (rec2, lab2) = _pm_sweeps()
+    assert torch.equal(torch.from_numpy(lab1), PM["labels1"].to(torch.uint8))
+    d1 = oi.ingest_scan(rec1, lab1, ident, "nuscenes", None, pos_div=1.0)
+    d2 = oi.ingest_scan(rec2, lab2, ident, "nuscenes", None, pos_div=1.0)
+    mix = {"alpha": case["alpha"], "beta": case["beta"], "omega": case["omega"], "do_swap": case["do_swap"],
+           "do_paste": case["do_paste"]}
+    _pm_check(oi.polarmix(d1, d2, mix, PM["instance_classes"]), case)
+
+
+def test_polarmix_draws_replay_the_reference_order():
+    from curvecloudnet_b200.ingest import PolarMixDraw
+    from oracle import ccn_ingest as oi
+    np.random.seed(77)
+    a = oi.draw_polarmix(1000)
+    np.random.seed(77)
+    b = PolarMixDraw.draw(1000)
+    assert (a["idx2"], a["alpha"], a["beta"], a["omega"][0], a["omega"][1], a["do_swap"], a["do_paste"]) == \
+        (b.idx2, b.alpha, b.beta, b.omega0, b.omega1, b.do_swap, b.do_paste)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", range(4))
+def test_polarmix_matches_reference_golden(ci):
+    from curvecloudnet_b200.ingest import LearningMap, PolarMixDraw, ingest_scan, polarmix
+    case = PM["cases"][ci]
+    lm = LearningMap({k: k for k in range(32)})
+    (rec1, lab1), (rec2, lab2) = _pm_sweeps()
+    d1 = ingest_scan(rec1, lab1, lm, "nuscenes", pos_div=1.0)
+    d2 = ingest_scan(rec2, lab2, lm, "nuscenes", pos_div=1.0)
+    mix = PolarMixDraw(0, case["alpha"], case["beta"], case["omega"][0], case["omega"][1], case["do_swap"], case["do_paste"])
+    out = polarmix(d1, d2, mix, PM["instance_classes"])
+    _pm_check({"pos": out.pos, "x": out.x, "y": out.y, "curve_idxs": out.curve_idxs}, case)
+    assert out.counts.tolist() == [case["pos"].shape[0], int(case["curve_idxs"].max()) + 1]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ds,beams,az,elev", [("nuscenes", 32, 1085, (-30.67, 10.67)), ("kitti", 64, 1875, (-24.8, 2.0))])
+def test_polarmix_full_sweeps_match_oracle(ds, beams, az, elev):
+    """Full-size sweeps through ingest -> PolarMix -> augmentation, every gate combination, against the oracle."""
+    from curvecloudnet_b200.ingest import (INSTANCE_CLASSES, LearningMap, PolarMixDraw, ScanAugmentation,
+                                           ingest_scan_polarmix)
+    from curvecloudnet_b200.synthetic import raycast_driving_scan
+    from oracle import ccn_ingest as oi
+    sweeps = []
+    for seed in (81, 82):
+        raw = raycast_driving_scan(seed, beams=beams, azimuth_steps=az, elev_deg=elev)
+        cols = [raw.points, raw.reflectance[:, None]] + ([raw.beam_ids[:, None]] if ds == "nuscenes" else [])
+        rec = np.concatenate(cols, axis=1).astype(np.float32)
+        lab = np.random.RandomState(seed).randint(0, 17, size=rec.shape[0])
+        sweeps.append({"raw": rec, "labels": lab.astype(np.uint8 if ds == "nuscenes" else np.int32)})
+    ident = {k: k for k in range(32)}
+    lm = LearningMap(ident)
+    np.random.seed(5)
+    aug = ScanAugmentation.draw(ds)
+    np.random.seed(5)
+    aug_o = oi.draw_augmentation(ds)
+    d1 = oi.ingest_scan(sweeps[0]["raw"], sweeps[0]["labels"], ident, ds, None, pos_div=1.0)
+    d2 = oi.ingest_scan(sweeps[1]["raw"], sweeps[1]["labels"], ident, ds, None, pos_div=1.0)
+    for do_swap, do_paste in ((True, True), (False, True), (True, False), (False, False)):
+        mix = PolarMixDraw(1, -2.3, -2.3 + np.pi, 0.9, 3.1, do_swap, do_paste)
+        got = ingest_scan_polarmix(sweeps[0], sweeps[1], mix, lm, ds, aug)
+        want = oi.polarmix(d1, d2, {"alpha": mix.alpha, "beta": mix.beta, "omega": [mix.omega0, mix.omega1],
+                                    "do_swap": do_swap, "do_paste": do_paste}, INSTANCE_CLASSES[ds])
+        wpos = torch.from_numpy(oi.training_augmentation(want["pos"].numpy(), aug_o)) / oi.POS_NORMALIZE
+        assert got.pos.shape[0] == wpos.shape[0]
+        assert torch.equal(got.y.cpu(), want["y"]) and torch.equal(got.x.cpu(), want["x"])
+        assert torch.equal(got.curve_idxs.cpu(), want["curve_idxs"])
+        assert _ulp_close(got.pos.cpu(), wpos, ulps=2, floor=0.05)      # two roundings (copy rotation, augmentation)
+        cid = got.curve_idxs.cpu()
+        assert int(cid[0]) == 0 and bool(torch.all((cid[1:] - cid[:-1]) >= 0)) and bool(torch.all((cid[1:] - cid[:-1]) <= 1))
