@@ -93,18 +93,49 @@ TTA_FLIPS = ((1.0, 1.0), (-1.0, 1.0), (1.0, -1.0), (-1.0, -1.0))       # nuscene
 TTA_SCALES = (1.0, 0.95, 1.05)                                         # :100-103
 
 
-@torch.no_grad()
-def tta_forward(model, data, flips=TTA_FLIPS, scales=TTA_SCALES):
-    """The augmentation loop of val() (nuscenes_seg.py:86-116): 12 forwards over xy-flipped / xy-scaled positions,
-    out = log_softmax(sum(outs) / 12), predict = argmax.  -> (out (N, C) log-probabilities, predict_labels (N) int64).
-    Every forward draws its own sampling randomness, exactly like the reference loop."""
+def tta_stack(data, factors):
+    """The augmented copies of `data` as ONE batch: copy g (xy factors `factors[g]`) becomes samples g*B .. g*B + B - 1.
+    Per-point and per-sample tensors are repeated; positions are scaled by ccn_scale_xy."""
+    from .model import Batch
     pos0 = ops._f32(data.pos)
     n = pos0.shape[0]
+    G = len(factors)
+    nb = int(data.batch[-1].item()) + 1 if n else 0                     # host sync (once per stack)
+    pos = torch.empty((G * n, 3), dtype=torch.float32, device=pos0.device)
+    for g, (sx, sy) in enumerate(factors):
+        call("ccn_scale_xy", pos0, n, float(sx), float(sy), pos[g * n:(g + 1) * n])
+    out = Batch()
+    for k, v in data.__dict__.items():
+        if k == "pos":
+            out.pos = pos
+        elif k == "batch":
+            out.batch = (v.unsqueeze(0) + torch.arange(G, device=v.device, dtype=v.dtype).unsqueeze(1) * nb).reshape(-1)
+        elif torch.is_tensor(v) and v.dim() >= 1 and v.shape[0] in (n, nb):
+            out.__dict__[k] = v.repeat(G, *([1] * (v.dim() - 1)))
+        else:
+            out.__dict__[k] = v
+    return out
+
+
+@torch.no_grad()
+def tta_forward(model, data, flips=TTA_FLIPS, scales=TTA_SCALES, group: int = 1):
+    """The augmentation loop of val() (nuscenes_seg.py:86-116): 12 forwards over xy-flipped / xy-scaled positions,
+    out = log_softmax(sum(outs) / 12), predict = argmax.  -> (out (N, C) log-probabilities, predict_labels (N) int64).
+
+    group = 1: one forward per augmented copy, every forward draws its own sampling randomness exactly like the
+    reference loop (draw-for-draw reproducible against it under a seed).
+    group = G > 1: G augmented copies are stacked into one batch of G*B samples per forward (12 / G forwards).  Every op
+    of the path is per sample and eval-mode BatchNorm is frozen, so each copy is processed exactly as if alone; only the
+    ORDER in which the random sampling draws are consumed differs from the loop (the reference's draws are unseeded).
+    The stacked forward runs the device at its batched rate instead of the launch-bound B=1 rate."""
+    pos0 = ops._f32(data.pos)
+    n = pos0.shape[0]
+    factors = [(fx * sc, fy * sc) for fx, fy in flips for sc in scales]
     acc, first = None, True
-    for fx, fy in flips:
-        for sc in scales:
+    if group <= 1:
+        for sx, sy in factors:
             pos = torch.empty_like(pos0)
-            call("ccn_scale_xy", pos0, n, float(fx * sc), float(fy * sc), pos)
+            call("ccn_scale_xy", pos0, n, float(sx), float(sy), pos)
             data.pos = pos
             out = model(data, labels=getattr(data, "y", None))
             out, ld = ops._rows(out)
@@ -112,9 +143,19 @@ def tta_forward(model, data, flips=TTA_FLIPS, scales=TTA_SCALES):
                 acc = torch.empty((n, out.shape[1]), dtype=torch.float32, device=out.device)
             call("ccn_accumulate", out, ld, n, out.shape[1], acc, acc.shape[1], int(first))
             first = False
-    data.pos = pos0
+        data.pos = pos0
+    else:
+        for g0 in range(0, len(factors), group):
+            stacked = tta_stack(data, factors[g0:g0 + group])
+            out = model(stacked, labels=getattr(stacked, "y", None))
+            out, ld = ops._rows(out)
+            if acc is None:
+                acc = torch.empty((n, out.shape[1]), dtype=torch.float32, device=out.device)
+            for g in range(len(factors[g0:g0 + group])):
+                call("ccn_accumulate", out[g * n:(g + 1) * n], ld, n, out.shape[1], acc, acc.shape[1], int(first))
+                first = False
     C = acc.shape[1]
     logp = torch.empty_like(acc)
     pred = torch.empty((n,), dtype=torch.int64, device=acc.device)
-    call("ccn_mean_logsoftmax", acc, C, n, C, 1.0 / (len(flips) * len(scales)), logp, C, pred)
+    call("ccn_mean_logsoftmax", acc, C, n, C, 1.0 / len(factors), logp, C, pred)
     return logp, pred

@@ -94,3 +94,35 @@ def tta_forward(model, data):
     data.pos = orig
     out = F.log_softmax(sum(outs) / 12, dim=-1)
     return out, torch.argmax(out, dim=-1)
+
+
+def tta_forward_stacked(model, data, group):
+    """The same 12 augmented copies, `group` of them stacked into one batch per forward (copy g -> samples g*B ..):
+    the CPU statement of curvecloudnet_b200.losses.tta_forward(group > 1).  Every op of the path is per sample, so this
+    differs from the loop above only in the order the sampling draws are consumed."""
+    import copy
+    factors = [(fx * sc, fy * sc) for fx, fy in ((1.0, 1.0), (-1.0, 1.0), (1.0, -1.0), (-1.0, -1.0))
+               for sc in (1.0, 0.95, 1.05)]
+    n = data.pos.shape[0]
+    nb = int(data.batch[-1]) + 1
+    total = None
+    for g0 in range(0, len(factors), group):
+        fs = factors[g0:g0 + group]
+        G = len(fs)
+        st = copy.copy(data)
+        parts = []
+        for sx, sy in fs:
+            p = data.pos.clone()
+            p[:, 0] *= sx
+            p[:, 1] *= sy
+            parts.append(p)
+        st.pos = torch.cat(parts)
+        st.batch = torch.cat([data.batch + g * nb for g in range(G)])
+        for k, v in data.__dict__.items():
+            if k not in ("pos", "batch") and torch.is_tensor(v) and v.dim() >= 1 and v.shape[0] in (n, nb):
+                setattr(st, k, v.repeat(G, *([1] * (v.dim() - 1))))
+        out = model(st, labels=getattr(st, "y", None))
+        for g in range(G):
+            total = out[g * n:(g + 1) * n] if total is None else total + out[g * n:(g + 1) * n]
+    out = F.log_softmax(total / len(factors), dim=-1)
+    return out, torch.argmax(out, dim=-1)

@@ -105,3 +105,37 @@ def test_cuda_tta_forward_matches_oracle():
     assert rel_err(got.cpu(), want) <= 1e-4
     agree = float((pred.cpu() == want_pred).float().mean())
     assert agree >= 0.999, agree
+
+
+@pytest.mark.gpu
+def test_cuda_tta_forward_stacked_matches_oracle():
+    """tta_forward(group=4): four augmented copies per forward as one batch; same seed -> same draws as the oracle's
+    stacked statement; and the stacked result agrees with the loop up to the sampling randomness."""
+    from curvecloudnet_b200 import losses as L
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle import ccn_losses as O
+    from oracle.ccn_model import ModelBase as OracleModel
+    data = driving_scan_batch([8], subsample=900)
+    ref = build_model(OracleModel, "nuscenes")
+    randomize_model_(ref, 1234)
+    ref.eval()
+    torch.manual_seed(4)
+    want, want_pred = O.tta_forward_stacked(ref, data, 4)
+    model = build_model(ModelBase, "nuscenes", precision="fp32")
+    model.load_state_dict(ref.state_dict(), strict=True)
+    model = model.cuda().eval()
+    dev = data.to("cuda")
+    torch.manual_seed(4)
+    got, pred = L.tta_forward(model, dev, group=4)
+    assert rel_err(got.cpu(), want) <= 1e-4
+    assert float((pred.cpu() == want_pred).float().mean()) >= 0.999
+    assert torch.equal(dev.pos.cpu(), data.pos)                        # the input batch is left untouched
+    # two-sample batch: copy g of sample b lands in sample g*B + b
+    data2 = driving_scan_batch([8, 9], subsample=700)
+    st = L.tta_stack(data2.to("cuda"), [(1.0, 1.0), (-1.05, 1.05)])
+    n = data2.pos.shape[0]
+    assert st.batch.cpu().tolist() == data2.batch.tolist() + (data2.batch + 2).tolist()
+    assert torch.equal(st.pos[:n].cpu(), data2.pos)
+    assert torch.equal(st.pos[n:, 2].cpu(), data2.pos[:, 2]) and torch.equal(st.curve_idxs[n:].cpu(), data2.curve_idxs)
