@@ -220,6 +220,7 @@ def run_train(args):
     native.load()
     W, K, B = max(args.warmup, 3), max(args.steps, 1), args.train_batch
     WG = "ccn_linear_wgrad" if args.precision == "fp32" else "ccn_linear_wgrad_tc"
+    LIN = "ccn_linear_f32" if args.precision == "fp32" else "ccn_linear_planes"
     model = build_model(ModelBase, "shapenet-seg", precision=args.precision)
     randomize_model_(model, 1234)
     model = model.cuda().train()
@@ -245,7 +246,7 @@ def run_train(args):
     def timed_pass(steps, from_host, profile):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         npts = 0
-        native.profile_begin((WG,) if profile else None, pad_cycles=40000 if profile else 0)
+        native.profile_begin((WG, LIN) if profile else None, pad_cycles=40000 if profile else 0)
         barrier()
         l0 = native.kernel_launches()
         for i in range(steps):
@@ -289,9 +290,32 @@ def run_train(args):
             dist.destroy_process_group()
         return
     peaks, peak_src = _peaks()
-    wg = prof.get(WG, {"ms": 0.0, "calls": 0, "work": 0.0})
-    peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops")))
-    ach = (wg["work"] / (wg["ms"] * 1e-3) / 1e12) if wg["ms"] > 0 else 0.0
+    peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1371.7)))
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+
+    def kernel_roofline(name, kernel, traffic_key):
+        # both GEMM kernels of the step sit below the tensor / HBM ridge (210 FLOP/B) at this network's widths
+        # (DESIGN.md section 4): algorithmic bytes against the measured copy bandwidth, tensor-pipe view beside it
+        d = prof.get(name, {"ms": 0.0, "calls": 0, "work": 0.0, "bytes": 0.0})
+        sec = d["ms"] * 1e-3
+        gbs = d["bytes"] / sec / 1e9 if sec > 0 else 0.0
+        tf = d["work"] / sec / 1e12 if sec > 0 else 0.0
+        return {"bound": "hbm", "kernel": kernel, "achieved": gbs, "peak": peak_gbs, "unit": "GB/s",
+                "frac": gbs / peak_gbs if peak_gbs else None, "traffic": _ncu_traffic(traffic_key),
+                "peak_source": peak_src + " (hbm_gbs)", "launches": d["calls"],
+                "algorithmic_bytes_per_launch": d["bytes"] / d["calls"] if d["calls"] else None,
+                "avg_launch_us": (d["ms"] * 1e3 / d["calls"]) if d["calls"] else None,
+                "share_of_step": d["ms"] / ms_prof if ms_prof else None, "flops_per_step": d["work"] / K,
+                "tensor_achieved_tflops": tf, "tensor_peak_tflops": peak_tf, "tensor_frac": tf / peak_tf if peak_tf else None}
+
+    if args.precision == "fp32":
+        roofline = kernel_roofline("ccn_linear_f32", "linear_f32_kernel (ccn_linear_f32)", "ccn_linear_f32:fp32")
+    else:
+        # the dominant kernel family of the step: forward Linear layers and data gradients (dX = dY W) run on the same kernel
+        roofline = kernel_roofline(LIN, "linear_planes_kernel<%d> (ccn_linear_planes: forward + data gradients)"
+                                   % (3 if args.precision == "bf16x3" else 1), "ccn_linear_planes:train:%s" % args.precision)
+        roofline["wgrad"] = kernel_roofline(WG, "wgrad_tc_kernel (ccn_linear_wgrad_tc: TMA + tcgen05 MN-major + TMEM, split-M)",
+                                            "ccn_linear_wgrad_tc:%s" % args.precision)
     line = {
         "metric": TRAIN_METRIC, "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -304,12 +328,7 @@ def run_train(args):
                 "h2d_bytes_per_step": int(sum(d.input_bytes() for d in host) / len(host) + targets[0].numel() * 8),
                 "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e_max / K},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "linear_wgrad_kernel (fp32 SIMT)" if args.precision == "fp32" else "wgrad_tc_kernel (ccn_linear_wgrad_tc: TMA + tcgen05 MN-major + TMEM, split-M)", "achieved": ach,
-                     "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf if peak_tf else None,
-                     "traffic": _ncu_traffic("ccn_linear_wgrad_tc:%s" % args.precision),
-                     "peak_source": peak_src + " (bf16_tflops_sustained)", "launches": wg["calls"],
-                     "avg_launch_us": (wg["ms"] * 1e3 / wg["calls"]) if wg["calls"] else None,
-                     "share_of_step": wg["ms"] / ms_prof if ms_prof else None, "flops_per_step": wg["work"] / K},
+        "roofline": roofline,
         "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:

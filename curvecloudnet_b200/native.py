@@ -104,7 +104,15 @@ def _planes_bytes(a):
 
 
 # algorithmic bytes of one call (HBM roofline of the Linear kernels)
-_BYTES = {"ccn_linear_planes": _planes_bytes,
+def _wgrad_bytes(a):
+    """ccn_linear_wgrad_tc: dY planes and X planes read once, dW (fp32) accumulated once per row split (counted once)."""
+    P = 2 if a[11] == 3 else 1
+    M, N, K = a[6], a[7], a[8]
+    return float(M * ((N + 7) // 8 * 8 + (K + 7) // 8 * 8) * 2 * P + N * K * 4)
+
+
+_BYTES = {"ccn_linear_planes": _planes_bytes, "ccn_linear_wgrad_tc": _wgrad_bytes,
+          "ccn_linear_wgrad": lambda a: 4.0 * (a[4] * (a[5] + a[6]) + a[5] * a[6]),
           "ccn_linear_f32": lambda a: 4.0 * (a[7] * a[9] + a[8] * a[9] + a[7] * a[8] + (a[8] if _is_buf(a[4]) else 0))}
 
 
