@@ -90,7 +90,7 @@ class _Linear(Function):
             ctx.save_for_backward(None, w)
         else:
             ctx.save_for_backward(x, w)
-        return ops.linear_planes(xp, ops.tc_weight_scratch(wd), bd, ops.ACT_NONE, 0.0, "f32")
+        return ops.linear_planes(xp, ops.tc_weight_param(w), bd, ops.ACT_NONE, 0.0, "f32")
 
     @staticmethod
     def backward(ctx, dy):
@@ -105,7 +105,8 @@ class _Linear(Function):
             return dx, dW, db
         dyp = _planes_of(dy, _npl(ctx.mode)) or ops.pack_planes([dy], _npl(ctx.mode))
         if ctx.needs_input_grad[0]:
-            dx = ops.linear_planes(dyp, ops.tc_weight_scratch(w.detach().t().contiguous()), None, ops.ACT_NONE, 0.0, "f32")
+            # dX = dY W straight from the forward weight's planes (MN-major B tiles): no transpose, no second split
+            dx = ops.linear_planes_bt(dyp, ops.tc_weight_param(w))
         if need_w:
             if ctx.xp is not None:
                 dW = wgrad_planes(dyp, ctx.xp)

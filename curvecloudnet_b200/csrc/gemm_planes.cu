@@ -49,7 +49,33 @@ struct PlanesParams {
     int nseg;               // A = [A_0 | A_1 | ...] along K: every segment is its own planes tensor
     int sc1, sc2, sc3, nk;  // first 64-wide K chunk of segments 1..3 (= nk for absent segments), total chunks
     int taps, cpt;          // taps > 0: curve convolution - K = taps x (cpt chunks of segment 0), tap t reads rows m + t - taps/2
+    int b_mn;               // 1: the weight is given as (K, N) row-major (Y = A W, the data gradient with the FORWARD weight):
+                            //    B tiles are MN-major UMMA operands, one 64 x 64 TMA box per 64 output columns
 };
+
+constexpr int kBoxBytes = 64 * 64 * 2;    // one 64 (N) x 64 (K) bf16 box = one MN-major SWIZZLE_128B block
+
+// MN-major, SWIZZLE_128B shared-memory matrix descriptor (see gemm_wgrad.cu): LBO = distance between 64-column blocks,
+// SBO = 1024 = 8 K-rows of 128 bytes
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(lbo_bytes >> 4) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// one W tile (BN output columns x 64 reduction elements) of plane `m`: K-major = one box, MN-major = BN / 64 boxes
+__device__ __forceinline__ void load_w_tile(uint32_t dst, const CUtensorMap* m, int kc, int n0, int BN, int b_mn,
+                                            uint32_t bar) {
+    if (!b_mn) {
+        tma_load_2d(dst, m, kc * kBK, n0, bar);
+    } else {
+        for (int j = 0; j < BN / 64; ++j) tma_load_2d(dst + j * kBoxBytes, m, n0 + 64 * j, kc * kBK, bar);
+    }
+}
 
 __device__ __forceinline__ void st_global_256(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e,
                                               uint32_t f, uint32_t g, uint32_t h) {
@@ -111,8 +137,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                 const int n0 = (blockIdx.x % p.tiles_n) * BN;
                 mbar_arrive_expect_tx(wfull, (uint32_t)(nk * P * wtile));
                 for (int kc = 0; kc < nk; ++kc) {
-                    tma_load_2d(w_res + (kc * P) * wtile, &w_hi, kc * kBK, n0, wfull);
-                    if (P == 2) tma_load_2d(w_res + (kc * P + 1) * wtile, &w_lo, kc * kBK, n0, wfull);
+                    load_w_tile(w_res + (kc * P) * wtile, &w_hi, kc, n0, BN, p.b_mn, wfull);
+                    if (P == 2) load_w_tile(w_res + (kc * P + 1) * wtile, &w_lo, kc, n0, BN, p.b_mn, wfull);
                 }
             }
             uint32_t cnt = 0;
@@ -137,8 +163,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     tma_load_2d(dst, mh, ka, m0 + roff, full0 + 8 * s);      // rows outside [0, M) arrive as zeros
                     if (P == 2) tma_load_2d(dst + kATile, ml, ka, m0 + roff, full0 + 8 * s);
                     if (!p.resident) {
-                        tma_load_2d(dst + P * kATile, &w_hi, kc * kBK, n0, full0 + 8 * s);
-                        if (P == 2) tma_load_2d(dst + P * kATile + wtile, &w_lo, kc * kBK, n0, full0 + 8 * s);
+                        load_w_tile(dst + P * kATile, &w_hi, kc, n0, BN, p.b_mn, full0 + 8 * s);
+                        if (P == 2) load_w_tile(dst + P * kATile + wtile, &w_lo, kc, n0, BN, p.b_mn, full0 + 8 * s);
                     }
                 }
             }
@@ -157,7 +183,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                 const int mma_n = min(BN, ((p.N - n0) + 15) & ~15);
                 // instruction descriptor: D=f32, A=B=bf16, K-major both, N>>3 at bit 17, M>>4 at bit 24
                 const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(mma_n >> 3) << 17) |
-                                       ((uint32_t)(kBM >> 4) << 24);
+                                       ((uint32_t)(kBM >> 4) << 24) | (p.b_mn ? (1u << 16) : 0u);   // bit 16: B is MN-major
                 const int buf = it & 1;
                 mbar_wait(tempty0 + 8 * buf, ((it >> 1) & 1) ^ 1);     // epilogue has drained this accumulator
                 tc_fence_after();
@@ -173,10 +199,13 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
 #pragma unroll
                     for (int k = 0; k < kBK / 16; ++k) {
                         const uint32_t ko = k * 32;     // 16 bf16 = 32 bytes inside the 128-byte swizzle row
-                        umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), umma_desc_sw128(w_hi_s + ko), idesc, (kc | k) ? 1u : 0u);
+                        // MN-major B: 16 reduction rows of 128 bytes further down the box
+                        const uint64_t dwh = p.b_mn ? umma_desc_mn_sw128(w_hi_s + k * 2048, kBoxBytes) : umma_desc_sw128(w_hi_s + ko);
+                        umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), dwh, idesc, (kc | k) ? 1u : 0u);
                         if (P == 2) {
-                            umma_bf16(acc, umma_desc_sw128(a_lo_s + ko), umma_desc_sw128(w_hi_s + ko), idesc, 1u);
-                            umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), umma_desc_sw128(w_lo_s + ko), idesc, 1u);
+                            const uint64_t dwl = p.b_mn ? umma_desc_mn_sw128(w_lo_s + k * 2048, kBoxBytes) : umma_desc_sw128(w_lo_s + ko);
+                            umma_bf16(acc, umma_desc_sw128(a_lo_s + ko), dwh, idesc, 1u);
+                            umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), dwl, idesc, 1u);
                         }
                     }
                     umma_commit(empty0 + 8 * s);        // stage reusable once these MMAs have read it
@@ -336,7 +365,7 @@ extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const i
 }
 
 static int launch_planes(const void* const* ap, const int64_t* ald, const int64_t* aps, const int32_t* ak, int32_t taps,
-                         const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias, float* Y,
+                         int32_t b_mn, const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias, float* Y,
                          int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
                          int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
     const void* a0 = ap[0];
@@ -344,6 +373,7 @@ static int launch_planes(const void* const* ap, const int64_t* ald, const int64_
     CCN_REQUIRE(a0 && k0 > 0 && w_hi_tmap_host && (Y || y_planes) && M >= 0 && M < 0x7fffffff && N > 0);
     CCN_REQUIRE((mode == 1 || (mode == 3 && w_lo_tmap_host)) && act >= 0 && act <= 2);
     CCN_REQUIRE(box_n == 32 || box_n == 64 || box_n == 128 || box_n == 256);
+    CCN_REQUIRE(!b_mn || (box_n >= 64 && taps == 0));
     CCN_REQUIRE(!Y || ldy >= N);
     const int yp_cols = (N + 15) & ~15;
     CCN_REQUIRE(!y_planes || (yp_ld >= yp_cols && (yp_ld & 15) == 0 && (reinterpret_cast<uintptr_t>(y_planes) & 31) == 0 &&
@@ -365,7 +395,7 @@ static int launch_planes(const void* const* ap, const int64_t* ald, const int64_
         chunk0[i + 1] = chunk0[p.nseg];
     }
     p.sc1 = chunk0[1]; p.sc2 = chunk0[2]; p.sc3 = chunk0[3]; p.nk = chunk0[p.nseg];
-    p.taps = 0; p.cpt = 0;
+    p.taps = 0; p.cpt = 0; p.b_mn = b_mn;
     if (taps > 0) {
         CCN_REQUIRE(p.nseg == 1 && (taps & 1) && taps <= 15);
         p.taps = taps; p.cpt = chunk0[1]; p.nk = taps * p.cpt;
@@ -438,8 +468,22 @@ extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32
     const void* ap[kMaxSeg] = {a0, a1, a2, a3};
     const int64_t ald[kMaxSeg] = {ld0, ld1, ld2, ld3}, aps[kMaxSeg] = {ps0, ps1, ps2, ps3};
     const int32_t ak[kMaxSeg] = {k0, k1, k2, k3};
-    return launch_planes(ap, ald, aps, ak, 0, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
+    return launch_planes(ap, ald, aps, ak, 0, 0, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
                          yp_plane_stride, M, N, box_n, mode, act, slope, stream);
+}
+
+// Y[M, N] = A[M, K] W[K, N] with W given as a (K, N) row-major split-bf16 weight - the data gradient dX = dY W computed
+// from the FORWARD weight's planes (no transposed copy, no second split): the tensor maps must have a 64 x 64 box
+// (ccn_weight_tensor_map(..., box_n = 64) on the (K rows, N-padded cols) planes); box_n here is the OUTPUT tile width.
+extern "C" int ccn_linear_planes_bt(const void* a, int64_t ld, int64_t ps, int32_t k, const void* w_hi_tmap_host,
+                                    const void* w_lo_tmap_host, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
+                                    int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n, int32_t mode,
+                                    ccn_stream_t stream) {
+    const void* ap[kMaxSeg] = {a, nullptr, nullptr, nullptr};
+    const int64_t ald[kMaxSeg] = {ld, 0, 0, 0}, aps[kMaxSeg] = {ps, 0, 0, 0};
+    const int32_t ak[kMaxSeg] = {k, 0, 0, 0};
+    return launch_planes(ap, ald, aps, ak, 0, 1, w_hi_tmap_host, w_lo_tmap_host, nullptr, Y, ldy, y_planes, yp_ld,
+                         yp_plane_stride, M, N, box_n, mode, CCN_ACT_NONE, 0.f, stream);
 }
 
 // 'same' zero-padded 1-D convolution along the row axis as ONE GEMM: K = taps x cin, tap t of output row m reads
@@ -453,6 +497,6 @@ extern "C" int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t ci
     const int64_t ald[kMaxSeg] = {ld, 0, 0, 0}, aps[kMaxSeg] = {ps, 0, 0, 0};
     const int32_t ak[kMaxSeg] = {cin, 0, 0, 0};
     CCN_REQUIRE(taps >= 1);
-    return launch_planes(ap, ald, aps, ak, taps, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
+    return launch_planes(ap, ald, aps, ak, taps, 0, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
                          yp_plane_stride, M, N, box_n, mode, act, slope, stream);
 }

@@ -668,6 +668,33 @@ def linear_planes(A, tw: "TcWeight", bias: Optional[torch.Tensor], act: int, slo
     return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)
 
 
+def linear_planes_bt(A: "Planes", tw: "TcWeight") -> torch.Tensor:
+    """Y (M, K_w) = A (M, N_w) @ W with W = the (N_w, K_w) weight behind `tw`, read as MN-major tiles from its FORWARD
+    planes (ccn_linear_planes_bt): the data gradient dX = dY W without a transposed copy of W."""
+    M, K = A.shape
+    assert K == tw.n and tw.k == tw.k_true, (A.shape, tw.n, tw.k)
+    npl = A.n_planes
+    n_out = tw.k
+    Y = _empty((M, n_out), torch.float32, A.buf)
+    # output tile width: the widest of 256 / 128 / 64 whose weight slice stays resident (big M) or that fills the SMs
+    tiles_m = (M + 127) // 128
+    nk = (tw.n + 63) // 64
+    cand = [b for b in (256, 128, 64) if b == 64 or b // 2 < n_out]
+    box = cand[-1]
+    for b in cand:
+        if tiles_m >= 148:
+            if nk * npl * b * 128 + 3 * npl * 16384 <= SMEM_BUDGET:
+                box = b
+                break
+        elif tiles_m * ((n_out + b - 1) // b) >= 148:
+            box = b
+            break
+    w_hi, w_lo, _ = tw.maps(64)
+    call("ccn_linear_planes_bt", A.buf, A.kpad, A.buf.stride(0), A.k, w_hi, w_lo, Y, n_out, 0, 0, 0, M, n_out, box,
+         3 if npl == 2 else 1)
+    return Y
+
+
 def conv_planes(sig: "Planes", w_kio: torch.Tensor, bias: Optional[torch.Tensor], act: int = ACT_NONE, slope: float = 0.01,
                 tw: "TcWeight" = None) -> torch.Tensor:
     """'same' zero-padded 1-D convolution along the rows of `sig` (planes of a (rows, cin) signal) as ONE tcgen05 GEMM:
@@ -699,6 +726,25 @@ def tc_weight_scratch(w: torch.Tensor) -> TcWeight:
         tw = _TC_SCRATCH[key] = TcWeight(w)
     else:
         call("ccn_split_bf16", w, ldw, tw.n, tw.k, tw.kpad, tw.hi, tw.lo)
+    return tw
+
+
+def tc_weight_param(w: torch.Tensor) -> TcWeight:
+    """TcWeight of a PARAMETER in training: bf16 planes + TMA descriptors kept on the parameter object and refilled only
+    when its in-place version changed (once per optimiser step) - the forward GEMM and the data gradient of the same step
+    share one split.  Anything that is not a leaf parameter (slices, concatenations) goes through tc_weight_scratch."""
+    if not (w.is_leaf and isinstance(w, torch.nn.Parameter) and w.is_contiguous()):
+        return tc_weight_scratch(w.detach())
+    hit = w.__dict__.get("_ccn_tw")
+    if hit is not None and hit[0] == w._version and hit[2] == w.data_ptr():
+        return hit[1]
+    wd = w.detach()
+    if hit is not None and hit[1].n == wd.shape[0] and hit[1].k == wd.shape[1] and hit[1].hi.device == wd.device:
+        tw = hit[1]
+        call("ccn_split_bf16", wd, wd.stride(0), tw.n, tw.k, tw.kpad, tw.hi, tw.lo)
+    else:
+        tw = TcWeight(wd)
+    w.__dict__["_ccn_tw"] = (w._version, tw, w.data_ptr())
     return tw
 
 

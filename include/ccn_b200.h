@@ -209,6 +209,14 @@ int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, cons
                       int64_t ps3, int32_t k3, const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias,
                       float* Y, int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
                       int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream);
+/* Y[M, N] = A[M, K] W[K, N] with W given as a (K, N) row-major split-bf16 weight: the data gradient dX = dY W of a Linear
+ * layer computed from the FORWARD weight's bf16 planes (cuBLAS SGEMM `NN` in Linear.backward upstream) - no transposed
+ * copy, no second split.  The B tiles are MN-major UMMA operands; the tensor maps must have a 64 x 64 box
+ * (ccn_weight_tensor_map(..., box_n = 64) on the (K rows, N cols padded to 64) planes); box_n = output tile width
+ * (64 | 128 | 256). */
+int ccn_linear_planes_bt(const void* a, int64_t ld, int64_t ps, int32_t k, const void* w_hi_tmap_host,
+                         const void* w_lo_tmap_host, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
+                         int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n, int32_t mode, ccn_stream_t stream);
 
 /* Planes-output variants of the per-edge first layers (the consumer is the next Linear of the edge MLP); c % 8 == 0,
  * kpad == c, fp32 inputs 16-byte aligned with leading dimensions % 4 == 0. */

@@ -66,6 +66,33 @@ def test_wgrad_tensor_core(npl, tol, M, N, K, off):
     _close(A.col_sum(dy), dy.double().sum(0), 1e-5, "db")
 
 
+@pytest.mark.parametrize("npl,tol", [(2, 5e-5), (1, 1e-2)])
+@pytest.mark.parametrize("M,N,K", [(5000, 192, 128), (777, 17, 259), (100000, 256, 256), (300, 1024, 515), (64, 64, 64),
+                                   (40000, 64, 35), (20000, 515, 512), (1, 3, 70)])
+def test_dgrad_from_forward_weight_planes(npl, tol, M, N, K):
+    """dX = dY W on tcgen05 with W read as MN-major tiles from the FORWARD weight's planes (ccn_linear_planes_bt)
+    against fp64; the parameter cache splits a weight once per in-place version."""
+    A, nn, ops = _A()
+    torch.manual_seed(11)
+    dy = torch.randn(M, N, device=DEV)
+    w = torch.nn.Parameter(torch.randn(N, K, device=DEV) / N ** 0.5)
+    tw = ops.tc_weight_param(w)
+    assert ops.tc_weight_param(w) is tw                                  # same version: no second split
+    dx = ops.linear_planes_bt(ops.pack_planes([dy], npl), tw)
+    _close(dx, dy.double() @ w.detach().double(), tol, "dX")
+    with torch.no_grad():
+        w.mul_(2.0)                                                      # in-place update (an optimiser step)
+    tw2 = ops.tc_weight_param(w)
+    assert tw2 is tw                                                     # same buffers, refilled
+    dx2 = ops.linear_planes_bt(ops.pack_planes([dy], npl), tw2)
+    _close(dx2, dy.double() @ w.detach().double(), tol, "dX after update")
+    # a slice of a parameter (pointnet_conv's W[:, :cx]) goes through the scratch buffers
+    if K > 8:
+        ws = w[:, :K - 3]
+        dxs = ops.linear_planes_bt(ops.pack_planes([dy], npl), ops.tc_weight_param(ws))
+        _close(dxs, dy.double() @ ws.detach().double(), tol, "dX slice")
+
+
 @pytest.mark.parametrize("act", ["relu", "leaky_relu", "none"])
 @pytest.mark.parametrize("M,C", [(777, 64), (5000, 192), (300, 515), (64, 35)])
 def test_bn_act_train_and_eval(act, M, C):
