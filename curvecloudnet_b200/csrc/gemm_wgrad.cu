@@ -189,9 +189,13 @@ __global__ void __launch_bounds__(256) col_sum_kernel(const float* __restrict__ 
 
 }  // namespace
 
+int ccn_col_sum_v4(const float* src, int64_t ld, int64_t M, int32_t C, float* out, cudaStream_t s);   // train_ops.cu
+
 extern "C" int ccn_col_sum(const float* src, int64_t ld, int64_t M, int32_t C, float* out, ccn_stream_t stream) {
     CCN_REQUIRE(M >= 0 && C > 0 && src && out && ld >= C);
     if (M == 0) return CCN_OK;
+    if ((C & 3) == 0 && (ld & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0)
+        return ccn_col_sum_v4(src, ld, M, C, out, (cudaStream_t)stream);
     const int gy = (C + 255) / 256;
     int64_t gx = (148 * 8) / gy;
     const int64_t max_gx = (M + 255) / 256;

@@ -168,6 +168,122 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__
     atomicAdd(sums + C + col, q);
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Vectorised column reductions (C % 4 == 0, 16-byte aligned rows): a thread owns 4 adjacent columns (float4 loads)
+// and a row lane; two / four rows in flight per thread; the row lanes of a CTA are combined in shared memory so
+// that a CTA issues ONE atomic per column and statistic.  MODE 0: float column sums (bias gradient),
+// MODE 1: fp64 (sum z, sum z^2) of BatchNorm's batch statistics, MODE 2: fp64 (sum g, sum g * xhat) of its backward.
+// ------------------------------------------------------------------------------------------------------------
+struct ColRed {
+    const float* a; int64_t lda;          // MODE 0: src, 1: z, 2: dy
+    const float* z; int64_t ldz;          // MODE 2: z
+    const float *mean, *invstd, *gamma, *beta;
+    int act; float slope;
+    int64_t M; int C; int64_t rows_per_cta;
+    double* sums; float* out;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256) col_reduce_v4_kernel(const ColRed p) {
+    constexpr int NS = MODE == 0 ? 4 : 8;              // statistics per thread
+    constexpr int UNR = MODE == 2 ? 2 : 4;             // rows in flight per thread
+    __shared__ double red[256 * NS];
+    const int c4n = p.C >> 2;
+    const int cw = c4n >= 256 ? 256 : c4n;
+    const int lanes = 256 / cw;
+    const int g = blockIdx.y * 256 + (threadIdx.x % cw);
+    const int lane = threadIdx.x / cw;
+    const bool live = g < c4n && lane < lanes;
+    const int64_t r0 = (int64_t)blockIdx.x * p.rows_per_cta, r1 = min(p.M, r0 + p.rows_per_cta);
+    double acc[NS];
+#pragma unroll
+    for (int k = 0; k < NS; ++k) acc[k] = 0.0;
+    if (live) {
+        const int c = g << 2;
+        float4 mu = make_float4(0, 0, 0, 0), is = mu, ga = mu, be = mu;
+        if (MODE == 2) {
+            mu = *reinterpret_cast<const float4*>(p.mean + c); is = *reinterpret_cast<const float4*>(p.invstd + c);
+            ga = *reinterpret_cast<const float4*>(p.gamma + c); be = *reinterpret_cast<const float4*>(p.beta + c);
+        }
+        float fs[4] = {0.f, 0.f, 0.f, 0.f};            // MODE 0 accumulates in float like the scalar kernel
+        for (int64_t r = r0 + lane; r < r1; r += (int64_t)lanes * UNR) {
+            float4 va[UNR], vz[UNR];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const int64_t rr = r + (int64_t)u * lanes;
+                const bool ok = rr < r1;
+                va[u] = ok ? *reinterpret_cast<const float4*>(p.a + rr * p.lda + c) : make_float4(0, 0, 0, 0);
+                if (MODE == 2) vz[u] = ok ? *reinterpret_cast<const float4*>(p.z + rr * p.ldz + c) : mu;
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                const float a4[4] = {va[u].x, va[u].y, va[u].z, va[u].w};
+                if (MODE == 0) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) fs[e] += a4[e];
+                } else if (MODE == 1) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const double v = (double)a4[e];
+                        acc[e] += v;
+                        acc[4 + e] = fma(v, v, acc[4 + e]);
+                    }
+                } else {
+                    const float z4[4] = {vz[u].x, vz[u].y, vz[u].z, vz[u].w};
+                    const float m4[4] = {mu.x, mu.y, mu.z, mu.w}, i4[4] = {is.x, is.y, is.z, is.w};
+                    const float g4[4] = {ga.x, ga.y, ga.z, ga.w}, b4[4] = {be.x, be.y, be.z, be.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float xh = (z4[e] - m4[e]) * i4[e];
+                        const float gg = a4[e] * act_grad(fmaf(xh, g4[e], b4[e]), p.act, p.slope);
+                        acc[e] += (double)gg;
+                        acc[4 + e] += (double)gg * (double)xh;
+                    }
+                }
+            }
+        }
+        if (MODE == 0) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[e] = (double)fs[e];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < NS; ++k) red[k * 256 + threadIdx.x] = acc[k];
+    __syncthreads();
+    if (live && lane == 0) {
+        const int c = g << 2;
+#pragma unroll
+        for (int k = 0; k < NS; ++k) {
+            double t = acc[k];
+            for (int l = 1; l < lanes; ++l) t += red[k * 256 + l * cw + (threadIdx.x % cw)];
+            if (MODE == 0) atomicAdd(p.out + c + k, (float)t);
+            else atomicAdd(p.sums + (k < 4 ? c + k : p.C + c + (k - 4)), t);
+        }
+    }
+}
+
+static inline bool col_reduce_v4_ok(const float* a, int64_t lda, int32_t C) {
+    return (C & 3) == 0 && (lda & 3) == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0;
+}
+
+template <int MODE>
+static int launch_col_reduce_v4(ColRed p, cudaStream_t s) {
+    const int c4n = p.C >> 2;
+    const int gy = (c4n + 255) / 256;
+    const int cw = c4n >= 256 ? 256 : c4n;
+    const int lanes = 256 / cw;
+    int64_t gx = (148 * 4) / gy;                                      // ~4 CTAs of 8 warps per SM
+    const int64_t max_gx = (p.M + (int64_t)lanes * 8 - 1) / ((int64_t)lanes * 8);
+    if (gx > max_gx) gx = max_gx;
+    if (gx < 1) gx = 1;
+    p.rows_per_cta = (p.M + gx - 1) / gx;
+    gx = (p.M + p.rows_per_cta - 1) / p.rows_per_cta;
+    col_reduce_v4_kernel<MODE><<<dim3((unsigned)gx, (unsigned)gy), 256, 0, s>>>(p);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+
 // mean / invstd from the sums; running statistics updated like torch (momentum, unbiased variance).
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, int64_t M, int C, float eps, float momentum,
                                    float* __restrict__ mean, float* __restrict__ invstd,
@@ -610,6 +726,13 @@ __global__ void dropout_kernel(const float* __restrict__ x, int64_t ldx, const f
 
 }  // namespace
 
+// bias gradient: out[c] += sum_r src[r][c] (called by ccn_col_sum, gemm_wgrad.cu)
+int ccn_col_sum_v4(const float* src, int64_t ld, int64_t M, int32_t C, float* out, cudaStream_t s) {
+    ColRed p = {};
+    p.a = src; p.lda = ld; p.M = M; p.C = C; p.out = out;
+    return launch_col_reduce_v4<0>(p, s);
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // C-ABI (include/ccn_b200.h, "Training step")
 // ------------------------------------------------------------------------------------------------------------
@@ -687,11 +810,21 @@ extern "C" int ccn_bn_stats(const float* z, int64_t ldz, int64_t M, int32_t C, f
     CCN_REQUIRE(M > 0 && C > 0 && z && sums && mean && invstd && ldz >= C);
     cudaError_t e = cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(double), S_);
     if (e != cudaSuccess) return (int)e;
-    dim3 grid;
-    int64_t rpc;
-    bn_grid(M, C, &grid, &rpc);
-    bn_stats_kernel<<<grid, 256, 0, S_>>>(z, ldz, M, C, rpc, sums);
-    CCN_CHECK_LAUNCH();
+    // measured inside the training step (tools/profile_train.py): for the fp64 statistics the float4 kernel wins on
+    // narrow layers (many row lanes per CTA), the one-column-per-thread kernel on wide ones; the bias-gradient and the
+    // BatchNorm-backward reductions are faster vectorised at every width
+    if (C <= 128 && col_reduce_v4_ok(z, ldz, C)) {
+        ColRed p = {};
+        p.a = z; p.lda = ldz; p.M = M; p.C = C; p.sums = sums;
+        const int rc = launch_col_reduce_v4<1>(p, S_);
+        if (rc != CCN_OK) return rc;
+    } else {
+        dim3 grid;
+        int64_t rpc;
+        bn_grid(M, C, &grid, &rpc);
+        bn_stats_kernel<<<grid, 256, 0, S_>>>(z, ldz, M, C, rpc, sums);
+        CCN_CHECK_LAUNCH();
+    }
     bn_finalize_kernel<<<(C + 255) / 256, 256, 0, S_>>>(sums, M, C, eps, momentum, mean, invstd, running_mean,
                                                         running_var);
     CCN_CHECK_LAUNCH();
@@ -735,12 +868,21 @@ extern "C" int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, in
     if (gamma) {
         cudaError_t e = cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(double), S_);
         if (e != cudaSuccess) return (int)e;
-        dim3 grid;
-        int64_t rpc;
-        bn_grid(M, C, &grid, &rpc);
-        bn_bwd_reduce_kernel<<<grid, 256, 0, S_>>>(dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, rpc,
-                                                   sums);
-        CCN_CHECK_LAUNCH();
+        if (col_reduce_v4_ok(dy, lddy, C) && col_reduce_v4_ok(z, ldz, C) && al16(mean) && al16(invstd) && al16(gamma) &&
+            al16(beta)) {
+            ColRed p = {};
+            p.a = dy; p.lda = lddy; p.z = z; p.ldz = ldz; p.mean = mean; p.invstd = invstd; p.gamma = gamma; p.beta = beta;
+            p.act = act; p.slope = slope; p.M = M; p.C = C; p.sums = sums;
+            const int rc = launch_col_reduce_v4<2>(p, S_);
+            if (rc != CCN_OK) return rc;
+        } else {
+            dim3 grid;
+            int64_t rpc;
+            bn_grid(M, C, &grid, &rpc);
+            bn_bwd_reduce_kernel<<<grid, 256, 0, S_>>>(dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, rpc,
+                                                       sums);
+            CCN_CHECK_LAUNCH();
+        }
     }
     const PlanesOut po = {(__nv_bfloat16*)dz_planes, dzp_ld, dzp_plane_stride, n_planes};
     if ((C & 3) == 0 && (ldz & 3) == 0 && (lddy & 3) == 0 && (lddz & 3) == 0 && al16(z) && al16(dy) && al16(dz) &&
