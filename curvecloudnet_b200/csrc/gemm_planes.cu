@@ -316,17 +316,36 @@ __global__ void pack_planes_kernel(const PackSrc s, int64_t n, int ctot, __nv_bf
         int g;
         ccn_divmod(t, groups, i, g);
         float v[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const int c = g * 8 + e;
-            float x = 0.f;
-            if (c < ctot) {
-                const int k = c < e0 ? 0 : c < e1 ? 1 : c < e2 ? 2 : 3;
-                const int cc = c - (k == 0 ? 0 : k == 1 ? e0 : k == 2 ? e1 : e2);
+        bool vec = false;
+        const int c0 = g * 8;
+        if (c0 + 8 <= ctot) {
+            // all 8 columns inside one source block and 16-byte aligned: two float4 loads
+            const int k = c0 < e0 ? 0 : c0 < e1 ? 1 : c0 < e2 ? 2 : 3;
+            const int kend = k == 0 ? e0 : k == 1 ? e1 : k == 2 ? e2 : ctot;
+            if (c0 + 8 <= kend) {
+                const int cc = c0 - (k == 0 ? 0 : k == 1 ? e0 : k == 2 ? e1 : e2);
                 const int64_t r = s.idx[k] ? s.idx[k][i] : i;
-                x = s.p[k][r * s.ld[k] + cc];
+                const float* src = s.p[k] + r * s.ld[k] + cc;
+                if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+                    const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+                    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+                    vec = true;
+                }
             }
-            v[e] = x;
+        }
+        if (!vec) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int c = c0 + e;
+                float x = 0.f;
+                if (c < ctot) {
+                    const int k = c < e0 ? 0 : c < e1 ? 1 : c < e2 ? 2 : 3;
+                    const int cc = c - (k == 0 ? 0 : k == 1 ? e0 : k == 2 ? e1 : e2);
+                    const int64_t r = s.idx[k] ? s.idx[k][i] : i;
+                    x = s.p[k][r * s.ld[k] + cc];
+                }
+                v[e] = x;
+            }
         }
         __nv_bfloat162 h[4], l[4];
 #pragma unroll
