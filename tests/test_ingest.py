@@ -268,3 +268,26 @@ def test_polarmix_full_sweeps_match_oracle(ds, beams, az, elev):
         assert _ulp_close(got.pos.cpu(), wpos, ulps=2, floor=0.05)      # two roundings (copy rotation, augmentation)
         cid = got.curve_idxs.cpu()
         assert int(cid[0]) == 0 and bool(torch.all((cid[1:] - cid[:-1]) >= 0)) and bool(torch.all((cid[1:] - cid[:-1]) <= 1))
+
+
+@pytest.mark.gpu
+def test_polarmix_degenerate_cases():
+    """No instance points in the partner sweep, an empty yaw sector, and a sector holding everything."""
+    from curvecloudnet_b200.ingest import LearningMap, PolarMixDraw, ingest_scan, polarmix
+    from oracle import ccn_ingest as oi
+    ident = {k: k for k in range(32)}
+    lm = LearningMap(ident)
+    (rec1, lab1), (rec2, lab2) = _pm_sweeps()
+    none2 = np.zeros_like(lab2)                                         # class 0 is not an instance class
+    for labels2, alpha, beta in ((none2, -2.0, 1.0), (lab2, 0.5, 0.5), (lab2, -4.0, 4.0)):
+        d1 = ingest_scan(rec1, lab1, lm, "nuscenes", pos_div=1.0)
+        d2 = ingest_scan(rec2, labels2, lm, "nuscenes", pos_div=1.0)
+        o1 = oi.ingest_scan(rec1, lab1, ident, "nuscenes", None, pos_div=1.0)
+        o2 = oi.ingest_scan(rec2, labels2, ident, "nuscenes", None, pos_div=1.0)
+        mix = PolarMixDraw(0, alpha, beta, 0.4, 2.9, True, True)
+        got = polarmix(d1, d2, mix, PM["instance_classes"])
+        want = oi.polarmix(o1, o2, {"alpha": alpha, "beta": beta, "omega": [0.4, 2.9], "do_swap": True, "do_paste": True},
+                           PM["instance_classes"])
+        assert got.pos.shape[0] == want["pos"].shape[0]
+        assert torch.equal(got.y.cpu(), want["y"]) and torch.equal(got.curve_idxs.cpu(), want["curve_idxs"])
+        assert torch.equal(got.x.cpu(), want["x"]) and _ulp_close(got.pos.cpu(), want["pos"])
