@@ -446,12 +446,19 @@ static int launch_planes(const void* const* ap, const int64_t* ald, const int64_
     const int smem = (int)((p.resident ? wres : 0) + (int64_t)stages * stage_bytes + 1024);
     alignas(64) AMaps am;
     for (int i = 0; i < kMaxSeg; ++i) {
-        const int j = i < p.nseg ? i : 0;         // unused slots repeat segment 0 (a valid descriptor)
-        int rc = ccn_encode_bf16_map(&am.hi[i], ap[j], M, ald[j], kBM);
-        if (rc == CCN_OK)
-            rc = ccn_encode_bf16_map(&am.lo[i], mode == 3 ? (const void*)((const __nv_bfloat16*)ap[j] + aps[j]) : ap[j], M,
-                                     ald[j], kBM);
+        if (i >= p.nseg) {                        // unused slots repeat segment 0 (a valid descriptor): no driver call
+            am.hi[i] = am.hi[0];
+            am.lo[i] = am.lo[0];
+            continue;
+        }
+        int rc = ccn_encode_bf16_map(&am.hi[i], ap[i], M, ald[i], kBM);
         if (rc != CCN_OK) return rc;
+        if (mode == 3) {
+            rc = ccn_encode_bf16_map(&am.lo[i], (const void*)((const __nv_bfloat16*)ap[i] + aps[i]), M, ald[i], kBM);
+            if (rc != CCN_OK) return rc;
+        } else {
+            am.lo[i] = am.hi[i];
+        }
     }
     const CUtensorMap* whi = (const CUtensorMap*)w_hi_tmap_host;
     const CUtensorMap* wlo = mode == 3 ? (const CUtensorMap*)w_lo_tmap_host : whi;
