@@ -108,8 +108,27 @@ class SymmetricCurve1DConvV2(_CurveConvBase):
         sig = feats
         for li, (w, b) in enumerate(layers):
             first, last = li == 0, li == len(layers) - 1
+            if first and not last and self._wide_first(w, rows):
+                # wide first layer (fp-side conv: C_in = 262): the k x C_in x C_out contraction as ONE tcgen05 GEMM over the
+                # padded signal (a tap's row shift is a TMA row coordinate) instead of the FP32-pipe tap kernel
+                padded = ops.gather_rows_i32(feats, row2pt)              # zero rows at the curve boundaries
+                sig = ops.conv_planes(ops.pack_planes([padded], n_planes()), w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_first(w))
+                continue
             sig = ops.curve_conv_layer(sig, w, b, row2pt, rows, n if last else rows, k, first, last)
         return sig, pos, batch, point2curveidx
+
+    def _wide_first(self, w, rows):
+        return n_planes() > 0 and rows > 0 and w.shape[1] >= 128 and w.shape[2] >= 16
+
+    def _tc_first(self, w):
+        """bf16 planes + TMA descriptors of the first layer's folded weight, rebuilt when the folded weights change."""
+        hit = self.__dict__.get("_tc_first_cache")
+        if hit is None or hit[0] is not w:
+            taps, cin, cout = w.shape
+            tw = ops.TcWeight(w.permute(2, 0, 1).reshape(cout, taps * cin).contiguous(), [cin] * taps if taps > 1 else None)
+            hit = (w, tw)
+            self.__dict__["_tc_first_cache"] = hit
+        return hit[1]
 
 
 class SymmetricCurve1DConvFastV1(_CurveConvBase):

@@ -176,6 +176,15 @@ def curve_row_map(topo: CurveTopology, pad: int) -> torch.Tensor:
     return row2pt[:rows]
 
 
+def gather_rows_i32(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """out[r] = src[idx[r]] if idx[r] >= 0 else 0   (pad-row insertion of fast_conv1d.py:48-61); idx int32."""
+    src, lds = _rows(src)
+    out = _empty((idx.shape[0], src.shape[1]), torch.float32, src)
+    if idx.shape[0]:
+        call("ccn_gather_rows_i32", src, lds, idx, idx.shape[0], src.shape[1], out, src.shape[1])
+    return out
+
+
 def curve_conv_layer(inp: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, row2pt: torch.Tensor, rows: int,
                      out_rows: int, ksize: int, in_mapped: bool, out_mapped: bool, slope: float = 0.01) -> torch.Tensor:
     """w: (ksize, cin, cout) folded, bias: (cout) folded."""

@@ -1,4 +1,5 @@
-"""Dev tool: per-entry-point device time of one nuScenes-shape forward (CUDA events around every C-ABI call)."""
+"""Dev tool: per-entry-point device time of one nuScenes-shape forward (CUDA events around every C-ABI call).
+usage: python tools/profile_forward.py [precision] [scans per forward]"""
 import sys, os, collections
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -11,7 +12,8 @@ prec = sys.argv[1] if len(sys.argv) > 1 else "bf16"
 model = build_model(ModelBase, "nuscenes", precision=prec)
 randomize_model_(model, 1234)
 model = model.cuda().eval()
-data = driving_scan_batch([0]).to("cuda")
+nb = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+data = driving_scan_batch(list(range(nb))).to("cuda")
 with torch.no_grad():
     for _ in range(3):
         torch.manual_seed(0); model(data)
