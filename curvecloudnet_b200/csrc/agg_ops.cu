@@ -321,6 +321,32 @@ extern "C" int ccn_gather_i64(const int64_t* src, const int64_t* idx, int64_t n,
     return CCN_OK;
 }
 
+namespace {
+// pos / batch / curve of the selected points in one pass (pos[idx], batch[idx], curve_idxs[idx] of pointnet2.py:69-72)
+__global__ void subset_gather_kernel(const float* __restrict__ pos, int64_t ldp, const int64_t* __restrict__ batch,
+                                     const int64_t* __restrict__ curve, const int64_t* __restrict__ idx, int64_t n,
+                                     float* __restrict__ posq, int64_t* __restrict__ batchq, int64_t* __restrict__ curveq) {
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int64_t i = idx[t];
+    posq[3 * t] = pos[i * ldp]; posq[3 * t + 1] = pos[i * ldp + 1]; posq[3 * t + 2] = pos[i * ldp + 2];
+    batchq[t] = batch[i];
+    if (curve) curveq[t] = curve[i];
+}
+}  // namespace
+
+extern "C" int ccn_subset_gather(const float* pos, int64_t ldp, const int64_t* batch, const int64_t* curve,
+                                 const int64_t* idx, int64_t n, float* posq, int64_t* batchq, int64_t* curveq,
+                                 ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && ldp >= 3);
+    if (n == 0) return CCN_OK;
+    CCN_REQUIRE(pos && batch && idx && posq && batchq && (!curve || curveq));
+    subset_gather_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(pos, ldp, batch, curve, idx, n, posq,
+                                                                                      batchq, curveq);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
 extern "C" int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int64_t nq, int32_t K, int32_t* erow,
                                 int32_t* ecol, ccn_stream_t stream) {
     CCN_REQUIRE(nq >= 0 && K >= 1 && idx && row_ptr && erow && ecol);

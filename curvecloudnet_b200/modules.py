@@ -211,8 +211,8 @@ class PointNetConv2(nn.Module):
 # pointnet2.py
 # ----------------------------------------------------------------------------------------------
 def _subset(x, pos, batch, curve, idx):
-    return (None if x is None else ops.gather_rows(x, idx), ops.gather_rows(pos, idx), ops.gather_i64(batch, idx),
-            None if curve is None else ops.gather_i64(curve, idx))
+    posq, batchq, curveq = ops.subset_gather(pos, batch, curve, idx)
+    return (None if x is None else ops.gather_rows(x, idx)), posq, batchq, curveq
 
 
 class SAModule(nn.Module):

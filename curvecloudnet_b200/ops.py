@@ -385,6 +385,20 @@ def gather_i64(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def subset_gather(pos: torch.Tensor, batch: torch.Tensor, curve: Optional[torch.Tensor], idx: torch.Tensor):
+    """(pos[idx], batch[idx], curve[idx]) in one launch; curve may be None."""
+    pos, ldp = _rows(_f32(pos))
+    batch, idx = _i64(batch), _i64(idx)
+    n = idx.shape[0]
+    posq = _empty((n, 3), torch.float32, pos)
+    batchq = _empty((n,), torch.int64, pos)
+    curveq = _empty((n,), torch.int64, pos) if curve is not None else None
+    if n:
+        call("ccn_subset_gather", pos, ldp, batch, _i64(curve) if curve is not None else 0, idx, n, posq, batchq,
+             curveq if curveq is not None else 0)
+    return posq, batchq, curveq
+
+
 def concat_cols(parts: List[torch.Tensor]) -> torch.Tensor:
     """torch.cat(parts, dim=1) with our copy kernel (column-offset strided writes)."""
     n = parts[0].shape[0]

@@ -152,6 +152,10 @@ int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t n1, const f
 int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t* idx, int64_t n, int32_t c, float* dst,
                         int64_t ldd, ccn_stream_t stream);
 int ccn_gather_i64(const int64_t* src, const int64_t* idx, int64_t n, int64_t* dst, ccn_stream_t stream);
+/* pos[idx], batch[idx], curve_idxs[idx] of a down-sampled level in one launch (src/models/modules/pointnet2.py:69-72,
+ * 176-179); curve / curveq may be null. */
+int ccn_subset_gather(const float* pos, int64_t ldp, const int64_t* batch, const int64_t* curve, const int64_t* idx,
+                      int64_t n, float* posq, int64_t* batchq, int64_t* curveq, ccn_stream_t stream);
 int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int64_t nq, int32_t K, int32_t* erow, int32_t* ecol,
                      ccn_stream_t stream);
 int ccn_csr_rows(const int32_t* row_ptr, int64_t nq, int32_t* erow, ccn_stream_t stream);
