@@ -565,7 +565,7 @@ class TcWeight:
 
     def pick_box_planes(self, m: int, n_planes: int) -> int:
         """N-tile width for ccn_linear_planes.  Big M (>= one m-tile per SM): the widest tile whose weight slice stays
-        resident in shared memory next to a 3-stage A ring; otherwise the widest tile that still gives >= 148 tiles."""
+        resident in shared memory next to a 3-stage A ring; otherwise the widest tile that still gives >= _BOX_MIN_TILES tiles."""
         cand = [b for b in (256, 128, 64, 32) if b == 32 or b // 2 < self.n]
         tiles_m = (m + 127) // 128
         nk = self.kpad // 64
@@ -575,7 +575,7 @@ class TcWeight:
                     return b
             return cand[-1]
         for b in cand:
-            if tiles_m * ((self.n + b - 1) // b) >= 148:
+            if tiles_m * ((self.n + b - 1) // b) >= _BOX_MIN_TILES:
                 return b
         return 32
 
@@ -589,6 +589,9 @@ class TcWeight:
 
 
 SMEM_BUDGET = 227 * 1024 - 2560
+# small-M layers: the widest N tile that still gives half a wave of CTAs (measured with tools/bench_linear.py: one wide tile
+# per CTA beats two narrow ones that re-read the activation tile, down to ~74 tiles)
+_BOX_MIN_TILES = 74
 
 
 def _tensor_map(base_ptr: int, rows: int, kpad: int, box_rows: int):

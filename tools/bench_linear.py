@@ -13,7 +13,10 @@ which = sys.argv[2] if len(sys.argv) > 2 else "both"
 SHAPES = [(373989, 64, 64), (92272, 256, 256), (92272, 128, 64), (119595, 128, 128), (40593, 256, 256), (32710, 256, 256),
           (15584, 512, 512), (12180, 512, 512), (3654, 1024, 1024), (17809, 256, 259), (32568, 64, 35), (5695, 256, 256),
           (1933, 512, 512), (580, 1024, 1024), (580, 1024, 2051), (174, 2048, 3072), (174, 2048, 1027), (32568, 17, 64)]
-if len(sys.argv) > 3:
+if len(sys.argv) > 3 and sys.argv[3] == "small":
+    SHAPES = [(17809, 128, 128), (17809, 256, 259), (17809, 128, 256), (17809, 64, 128), (5695, 256, 256), (5695, 128, 256),
+              (32710, 256, 256), (32710, 128, 256), (32568, 128, 128), (32568, 64, 64), (66388, 128, 128), (1933, 512, 259)]
+elif len(sys.argv) > 3:
     SHAPES = SHAPES[:int(sys.argv[3])]
 cnn.set_precision(mode)
 npl = cnn.n_planes()
