@@ -170,6 +170,97 @@ __global__ void group_max_dense_kernel(const float* __restrict__ feat, int64_t l
     }
 }
 
+// ---- float4 forms of the two reductions above (c % 4 == 0, 16-byte aligned rows): a thread owns 4 adjacent channels
+// of one target; every channel sees exactly the scalar kernel's operation order, so results are bit-identical.
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 max4(float4 a, float4 b) {
+    return make_float4(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w));
+}
+
+__global__ void group_max_dense_v4_kernel(const float* __restrict__ feat, int64_t ldf, const int32_t* __restrict__ idx,
+                                          int64_t n, int K, int c4, float* __restrict__ out, int64_t ldo) {
+    const int G = K + 1;
+    const int64_t total = n * (int64_t)c4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t i;
+        int k4;
+        ccn_divmod(t, c4, i, k4);
+        const float* base = feat + (i * G) * ldf + 4 * k4;
+        float4 r = ld4(base);
+        const float4 skip = make_float4(-100.f, -100.f, -100.f, -100.f);
+#pragma unroll 4
+        for (int g = 1; g < G; ++g) {
+            const float4 v = idx[i * K + g - 1] >= 0 ? ld4(base + (int64_t)g * ldf) : skip;
+            r = max4(r, v);
+        }
+        *reinterpret_cast<float4*>(out + i * ldo + 4 * k4) = r;
+    }
+}
+
+__global__ void seg_aggregate_v4_kernel(const float* __restrict__ msg, int64_t ldm, const float* __restrict__ att,
+                                        int64_t lda, const int32_t* __restrict__ row_ptr, int64_t nq, int c4, int mode,
+                                        float* __restrict__ out, int64_t ldo) {
+    const int64_t total = nq * (int64_t)c4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t q;
+        int k4;
+        ccn_divmod(t, c4, q, k4);
+        const int b = row_ptr[q], e = row_ptr[q + 1];
+        const float* m0 = msg + 4 * k4;
+        const float* a0 = att ? att + 4 * k4 : nullptr;
+        float r[4] = {0.f, 0.f, 0.f, 0.f};
+        if (mode == CCN_AGG_MAX) {
+            if (e > b) {
+                float4 v = ld4(m0 + (int64_t)b * ldm);
+#pragma unroll 4
+                for (int j = b + 1; j < e; ++j) v = max4(v, ld4(m0 + (int64_t)j * ldm));
+                r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
+            }
+        } else if (mode == CCN_AGG_MEAN || mode == CCN_AGG_SUM) {
+#pragma unroll 4
+            for (int j = b; j < e; ++j) {
+                const float4 v = ld4(m0 + (int64_t)j * ldm);
+                r[0] += v.x; r[1] += v.y; r[2] += v.z; r[3] += v.w;
+            }
+            if (mode == CCN_AGG_MEAN) {
+                const float d = fmaxf((float)(e - b), 1.f);
+#pragma unroll
+                for (int l = 0; l < 4; ++l) r[l] = r[l] / d;
+            }
+        } else if (mode == CCN_AGG_WSUM) {
+#pragma unroll 2
+            for (int j = b; j < e; ++j) {
+                const float4 a = ld4(a0 + (int64_t)j * lda), v = ld4(m0 + (int64_t)j * ldm);
+                const float av[4] = {a.x, a.y, a.z, a.w}, mv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int l = 0; l < 4; ++l) r[l] += mv[l] * (1.f / (1.f + expf(-av[l])));
+            }
+        } else {
+            float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, sum[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+            for (int j = b; j < e; ++j) {
+                const float4 a = ld4(a0 + (int64_t)j * lda);
+                mx[0] = fmaxf(mx[0], a.x); mx[1] = fmaxf(mx[1], a.y); mx[2] = fmaxf(mx[2], a.z); mx[3] = fmaxf(mx[3], a.w);
+            }
+#pragma unroll 2
+            for (int j = b; j < e; ++j) {
+                const float4 a = ld4(a0 + (int64_t)j * lda);
+                sum[0] += expf(a.x - mx[0]); sum[1] += expf(a.y - mx[1]); sum[2] += expf(a.z - mx[2]); sum[3] += expf(a.w - mx[3]);
+            }
+            float inv[4];
+#pragma unroll
+            for (int l = 0; l < 4; ++l) inv[l] = 1.f / (sum[l] + 1e-16f);
+#pragma unroll 2
+            for (int j = b; j < e; ++j) {
+                const float4 a = ld4(a0 + (int64_t)j * lda), v = ld4(m0 + (int64_t)j * ldm);
+                r[0] += v.x * (expf(a.x - mx[0]) * inv[0]); r[1] += v.y * (expf(a.y - mx[1]) * inv[1]);
+                r[2] += v.z * (expf(a.z - mx[2]) * inv[2]); r[3] += v.w * (expf(a.w - mx[3]) * inv[3]);
+            }
+        }
+        *reinterpret_cast<float4*>(out + q * ldo + 4 * k4) = make_float4(r[0], r[1], r[2], r[3]);
+    }
+}
+
 // y[i] = sum_k w x[nbr] / sum_k w   (point_ops.py:336-341, 350-355); w = 1/clamp(d2, 1e-16) when from_d2.
 __global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, const int32_t* __restrict__ nbr,
                                     const float* __restrict__ wgt, int from_d2, int64_t n, int knn, int c,
@@ -303,6 +394,7 @@ __global__ void edge_layer1_planes_kernel(const float* __restrict__ H, int64_t l
 }  // namespace
 
 #define CCN_ELT_GRID(total) ccn_grid((total), 256, 148LL * 32)
+static inline bool ccn_al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 extern "C" int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t* idx, int64_t n, int32_t c,
                                    float* dst, int64_t ldd, ccn_stream_t stream) {
@@ -392,6 +484,13 @@ extern "C" int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att
     CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 4);
     CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || att);
     if (nq == 0) return CCN_OK;
+    if ((c & 3) == 0 && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) && ccn_al16(out) &&
+        (!att || ((lda & 3) == 0 && ccn_al16(att)))) {
+        seg_aggregate_v4_kernel<<<CCN_ELT_GRID(nq * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq,
+                                                                                                c >> 2, mode, out, ldo);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     seg_aggregate_kernel<<<CCN_ELT_GRID(nq * c), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq, c,
                                                                                  mode, out, ldo);
     CCN_CHECK_LAUNCH();
@@ -412,6 +511,12 @@ extern "C" int ccn_group_max_dense(const float* feat, int64_t ldf, const int32_t
                                    int32_t c, float* out, int64_t ldo, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && feat && out);
     if (n == 0) return CCN_OK;
+    if ((c & 3) == 0 && (ldf & 3) == 0 && (ldo & 3) == 0 && ccn_al16(feat) && ccn_al16(out)) {
+        group_max_dense_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(feat, ldf, idx, n, K, c >> 2,
+                                                                                                 out, ldo);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     group_max_dense_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(feat, ldf, idx, n, K, c, out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -427,7 +532,6 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
     return CCN_OK;
 }
 
-static inline bool ccn_al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 #define CCN_PLANES_OK(planes, kpad, pstride, npl, c) \
     ((planes) && ccn_al16(planes) && ((kpad) & 7) == 0 && (kpad) >= (c) && ((c) & 7) == 0 && ((npl) == 1 || ((npl) == 2 && ((pstride) & 7) == 0)))
 
