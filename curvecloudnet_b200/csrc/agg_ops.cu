@@ -284,6 +284,30 @@ __global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, co
 }
 
 
+__global__ void interp_blend_v4_kernel(const float* __restrict__ x, int64_t ldx, const int32_t* __restrict__ nbr,
+                                       const float* __restrict__ wgt, int from_d2, int64_t n, int knn, int c4,
+                                       float* __restrict__ out, int64_t ldo) {
+    const int64_t total = n * (int64_t)c4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t i;
+        int k4;
+        ccn_divmod(t, c4, i, k4);
+        float num[4] = {0.f, 0.f, 0.f, 0.f}, den = 0.f;
+        for (int s = 0; s < knn; ++s) {
+            const int j = nbr[i * knn + s];
+            if (j < 0) continue;
+            float w = wgt[i * knn + s];
+            if (from_d2) w = __fdiv_rn(1.f, fmaxf(w, 1e-16f));
+            const float4 v = ld4(x + (int64_t)j * ldx + 4 * k4);
+            num[0] = __fadd_rn(num[0], __fmul_rn(v.x, w)); num[1] = __fadd_rn(num[1], __fmul_rn(v.y, w));
+            num[2] = __fadd_rn(num[2], __fmul_rn(v.z, w)); num[3] = __fadd_rn(num[3], __fmul_rn(v.w, w));
+            den = __fadd_rn(den, w);
+        }
+        *reinterpret_cast<float4*>(out + i * ldo + 4 * k4) =
+            make_float4(__fdiv_rn(num[0], den), __fdiv_rn(num[1], den), __fdiv_rn(num[2], den), __fdiv_rn(num[3], den));
+    }
+}
+
 // ---- planes-output variants of the per-edge first layers (the consumer is always the next Linear of the MLP):
 // one thread per (row, 8 channels); requires c % 8 == 0 and 16-byte aligned fp32 rows.
 struct F8 { float v[8]; };
@@ -526,6 +550,12 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
                                 int64_t n, int32_t knn, int32_t c, float* out, int64_t ldo, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && knn >= 1 && c > 0 && x && nbr && wgt && out);
     if (n == 0) return CCN_OK;
+    if ((c & 3) == 0 && (ldx & 3) == 0 && (ldo & 3) == 0 && ccn_al16(x) && ccn_al16(out)) {
+        interp_blend_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn,
+                                                                                              c >> 2, out, ldo);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     interp_blend_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn, c,
                                                                                out, ldo);
     CCN_CHECK_LAUNCH();
