@@ -28,6 +28,18 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, int64_t lds, c
     }
 }
 
+__global__ void gather_rows_v4_kernel(const float* __restrict__ src, int64_t lds, const int64_t* __restrict__ idx,
+                                      int64_t n, int c4, float* __restrict__ dst, int64_t ldd) {
+    const int64_t total = n * (int64_t)c4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t i;
+        int k;
+        ccn_divmod(t, c4, i, k);
+        const int64_t s = idx ? idx[i] : i;
+        *reinterpret_cast<float4*>(dst + i * ldd + 4 * k) = *reinterpret_cast<const float4*>(src + s * lds + 4 * k);
+    }
+}
+
 __global__ void gather_i64_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ idx, int64_t n,
                                   int64_t* __restrict__ dst) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -308,6 +320,55 @@ __global__ void interp_blend_v4_kernel(const float* __restrict__ x, int64_t ldx,
     }
 }
 
+// float4 forms of the fp32-output per-edge first layers (training keeps fp32 activations in front of BatchNorm)
+__global__ void edge_layer1_v4_kernel(const float* __restrict__ H, int64_t ldh, const float* __restrict__ wp,
+                                      const float* __restrict__ bias, const float* __restrict__ pos_src,
+                                      const float* __restrict__ pos_dst, const int32_t* __restrict__ erow,
+                                      const int32_t* __restrict__ ecol, int64_t E, int c, float inv_norm_is_div,
+                                      float radius, int act, float slope, float* __restrict__ out, int64_t ldo) {
+    const int c4 = c >> 2;
+    const int64_t total = E * (int64_t)c4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t e;
+        int k;
+        ccn_divmod(t, c4, e, k);
+        k <<= 2;
+        const int j = ecol[e], i = erow[e];
+        float rx = __fsub_rn(pos_src[3 * j], pos_dst[3 * i]);
+        float ry = __fsub_rn(pos_src[3 * j + 1], pos_dst[3 * i + 1]);
+        float rz = __fsub_rn(pos_src[3 * j + 2], pos_dst[3 * i + 2]);
+        if (inv_norm_is_div != 0.f) { rx = __fdiv_rn(rx, radius); ry = __fdiv_rn(ry, radius); rz = __fdiv_rn(rz, radius); }
+        float4 y = bias ? ld4(bias + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (H) {
+            const float4 h = ld4(H + (int64_t)j * ldh + k);
+            y.x += h.x; y.y += h.y; y.z += h.z; y.w += h.w;
+        }
+        const float4 wx = ld4(wp + k), wy = ld4(wp + c + k), wz = ld4(wp + 2 * c + k);
+        y.x = apply_act(fmaf(wz.x, rz, fmaf(wy.x, ry, fmaf(wx.x, rx, y.x))), act, slope);
+        y.y = apply_act(fmaf(wz.y, rz, fmaf(wy.y, ry, fmaf(wx.y, rx, y.y))), act, slope);
+        y.z = apply_act(fmaf(wz.z, rz, fmaf(wy.z, ry, fmaf(wx.z, rx, y.z))), act, slope);
+        y.w = apply_act(fmaf(wz.w, rz, fmaf(wy.w, ry, fmaf(wx.w, rx, y.w))), act, slope);
+        *reinterpret_cast<float4*>(out + e * ldo + k) = y;
+    }
+}
+
+__global__ void edge_pair_layer1_v4_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ erow,
+                                           const int32_t* __restrict__ ecol, int64_t E, int c, int act, float slope,
+                                           float* __restrict__ out, int64_t ldo) {
+    const int c4 = c >> 2;
+    const int64_t total = E * (int64_t)c4;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t e;
+        int k;
+        ccn_divmod(t, c4, e, k);
+        k <<= 2;
+        const float4 a = ld4(PQ + (int64_t)ecol[e] * ldpq + k), b = ld4(PQ + (int64_t)erow[e] * ldpq + c + k);
+        *reinterpret_cast<float4*>(out + e * ldo + k) =
+            make_float4(apply_act(a.x + b.x, act, slope), apply_act(a.y + b.y, act, slope), apply_act(a.z + b.z, act, slope),
+                        apply_act(a.w + b.w, act, slope));
+    }
+}
+
 // ---- planes-output variants of the per-edge first layers (the consumer is always the next Linear of the MLP):
 // one thread per (row, 8 channels); requires c % 8 == 0 and 16-byte aligned fp32 rows.
 struct F8 { float v[8]; };
@@ -424,6 +485,11 @@ extern "C" int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t*
                                    float* dst, int64_t ldd, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && c > 0 && src && dst && lds >= c && ldd >= c);
     if (n == 0) return CCN_OK;
+    if ((c & 3) == 0 && (lds & 3) == 0 && (ldd & 3) == 0 && ccn_al16(src) && ccn_al16(dst)) {
+        gather_rows_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, n, c >> 2, dst, ldd);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     gather_rows_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, n, c, dst, ldd);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -486,6 +552,14 @@ extern "C" int ccn_edge_layer1(const float* H, int64_t ldh, const float* wp, con
                                ccn_stream_t stream) {
     CCN_REQUIRE(E >= 0 && c > 0 && wp && pos_src && pos_dst && erow && ecol && out && ldo >= c);
     if (E == 0) return CCN_OK;
+    if ((c & 3) == 0 && (ldo & 3) == 0 && ccn_al16(out) && ccn_al16(wp) && (!bias || ccn_al16(bias)) &&
+        (!H || ((ldh & 3) == 0 && ccn_al16(H)))) {
+        edge_layer1_v4_kernel<<<CCN_ELT_GRID(E * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+            H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
+            slope, out, ldo);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     edge_layer1_kernel<<<CCN_ELT_GRID(E * c), 256, 0, (cudaStream_t)stream>>>(
         H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
         slope, out, ldo);
@@ -497,6 +571,12 @@ extern "C" int ccn_edge_pair_layer1(const float* PQ, int64_t ldpq, const int32_t
                                     int32_t c, int32_t act, float slope, float* out, int64_t ldo, ccn_stream_t stream) {
     CCN_REQUIRE(E >= 0 && c > 0 && PQ && erow && ecol && out && ldpq >= 2 * c && ldo >= c);
     if (E == 0) return CCN_OK;
+    if ((c & 3) == 0 && (ldpq & 3) == 0 && (ldo & 3) == 0 && ccn_al16(PQ) && ccn_al16(out)) {
+        edge_pair_layer1_v4_kernel<<<CCN_ELT_GRID(E * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, erow, ecol, E, c, act,
+                                                                                                  slope, out, ldo);
+        CCN_CHECK_LAUNCH();
+        return CCN_OK;
+    }
     edge_pair_layer1_kernel<<<CCN_ELT_GRID(E * c), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, erow, ecol, E, c, act,
                                                                                    slope, out, ldo);
     CCN_CHECK_LAUNCH();
