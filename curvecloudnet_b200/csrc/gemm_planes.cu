@@ -86,10 +86,14 @@ __device__ __forceinline__ void st_global_256(void* p, uint32_t a, uint32_t b, u
 constexpr int kMaxSeg = 4;
 struct AMaps { CUtensorMap hi[kMaxSeg], lo[kMaxSeg]; };
 
-template <int MODE>
+template <int MODE, bool MAPPED>
 __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
     const __grid_constant__ AMaps am, const __grid_constant__ CUtensorMap w_hi,
-    const __grid_constant__ CUtensorMap w_lo, const PlanesParams p) {
+    const __grid_constant__ CUtensorMap w_lo, const PlanesParams p, const int32_t* __restrict__ out_map) {
+    // out_map (MAPPED only): output row m lands in row out_map[m] of Y / Yp, dropped when negative (valid-row selection of
+    // the last curve-conv layer).  It is a kernel parameter of its own and MAPPED a template parameter on purpose: growing
+    // PlanesParams by 8 bytes, or testing the pointer at run time, changed ptxas' allocation of the epilogue (103 -> 88
+    // registers) and cost the big-M layers 45 % of their throughput (measured A/B on one box, profiles/r01h_ab.log).
     constexpr int P = MODE == 3 ? 2 : 1;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 5];   // full[S], empty[S], wfull, tfull[2], tempty[2]
@@ -233,6 +237,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
             mbar_wait(tfull0 + 8 * buf, (it >> 1) & 1);
             tc_fence_after();
             const int row = m0 + q * 32 + lane;
+            const int orow = MAPPED ? (row < p.M ? __ldg(out_map + row) : -1) : row;
             const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
             for (int c0 = 0; c0 < mma_n; c0 += 32) {
                 uint32_t v[32];
@@ -245,9 +250,9 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     else if (p.act == CCN_ACT_LEAKY) o = o > 0.f ? o : o * p.slope;
                     y[j] = o;
                 }
-                if (row < p.M) {
+                if (MAPPED ? orow >= 0 : row < p.M) {
                     if (p.Y) {
-                        float* yrow = p.Y + (int64_t)row * p.ldy + n0 + c0;
+                        float* yrow = p.Y + (int64_t)orow * p.ldy + n0 + c0;
 #pragma unroll
                         for (int j = 0; j < 32; j += 8) {
                             const int n = n0 + c0 + j;
@@ -263,7 +268,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                         }
                     }
                     if (p.Yp) {
-                        __nv_bfloat16* hrow = p.Yp + (int64_t)row * p.yp_ld + n0 + c0;
+                        __nv_bfloat16* hrow = p.Yp + (int64_t)orow * p.yp_ld + n0 + c0;
 #pragma unroll
                         for (int j = 0; j < 32; j += 16) {
                             if (n0 + c0 + j >= p.yp_cols) continue;    // yp_cols % 16 == 0: whole groups only
@@ -384,7 +389,8 @@ extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const i
 }
 
 static int launch_planes(const void* const* ap, const int64_t* ald, const int64_t* aps, const int32_t* ak, int32_t taps,
-                         int32_t b_mn, const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias, float* Y,
+                         int32_t b_mn, const int32_t* out_map, const void* w_hi_tmap_host, const void* w_lo_tmap_host,
+                         const float* bias, float* Y,
                          int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
                          int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
     const void* a0 = ap[0];
@@ -464,22 +470,23 @@ static int launch_planes(const void* const* ap, const int64_t* ald, const int64_
     const CUtensorMap* wlo = mode == 3 ? (const CUtensorMap*)w_lo_tmap_host : whi;
     cudaStream_t s = (cudaStream_t)stream;
     cudaError_t e;
-    if (mode == 3) {
-        static bool attr3 = false;
-        if (!attr3) {
-            e = cudaFuncSetAttribute(linear_planes_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536);
-            if (e != cudaSuccess) return (int)e;
-            attr3 = true;
+    static bool attr[4] = {false, false, false, false};
+    const int which = (mode == 3 ? 2 : 0) + (out_map ? 1 : 0);
+    if (!attr[which]) {
+        switch (which) {
+            case 0: e = cudaFuncSetAttribute(linear_planes_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536); break;
+            case 1: e = cudaFuncSetAttribute(linear_planes_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536); break;
+            case 2: e = cudaFuncSetAttribute(linear_planes_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536); break;
+            default: e = cudaFuncSetAttribute(linear_planes_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536); break;
         }
-        linear_planes_kernel<3><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p);
-    } else {
-        static bool attr1 = false;
-        if (!attr1) {
-            e = cudaFuncSetAttribute(linear_planes_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 1536);
-            if (e != cudaSuccess) return (int)e;
-            attr1 = true;
-        }
-        linear_planes_kernel<1><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p);
+        if (e != cudaSuccess) return (int)e;
+        attr[which] = true;
+    }
+    switch (which) {
+        case 0: linear_planes_kernel<1, false><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
+        case 1: linear_planes_kernel<1, true><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
+        case 2: linear_planes_kernel<3, false><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
+        default: linear_planes_kernel<3, true><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -494,7 +501,7 @@ extern "C" int ccn_linear_planes(const void* a0, int64_t ld0, int64_t ps0, int32
     const void* ap[kMaxSeg] = {a0, a1, a2, a3};
     const int64_t ald[kMaxSeg] = {ld0, ld1, ld2, ld3}, aps[kMaxSeg] = {ps0, ps1, ps2, ps3};
     const int32_t ak[kMaxSeg] = {k0, k1, k2, k3};
-    return launch_planes(ap, ald, aps, ak, 0, 0, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
+    return launch_planes(ap, ald, aps, ak, 0, 0, nullptr, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
                          yp_plane_stride, M, N, box_n, mode, act, slope, stream);
 }
 
@@ -508,21 +515,24 @@ extern "C" int ccn_linear_planes_bt(const void* a, int64_t ld, int64_t ps, int32
     const void* ap[kMaxSeg] = {a, nullptr, nullptr, nullptr};
     const int64_t ald[kMaxSeg] = {ld, 0, 0, 0}, aps[kMaxSeg] = {ps, 0, 0, 0};
     const int32_t ak[kMaxSeg] = {k, 0, 0, 0};
-    return launch_planes(ap, ald, aps, ak, 0, 1, w_hi_tmap_host, w_lo_tmap_host, nullptr, Y, ldy, y_planes, yp_ld,
+    return launch_planes(ap, ald, aps, ak, 0, 1, nullptr, w_hi_tmap_host, w_lo_tmap_host, nullptr, Y, ldy, y_planes, yp_ld,
                          yp_plane_stride, M, N, box_n, mode, CCN_ACT_NONE, 0.f, stream);
 }
 
 // 'same' zero-padded 1-D convolution along the row axis as ONE GEMM: K = taps x cin, tap t of output row m reads
-// input row m + t - taps/2 (a TMA row coordinate; rows outside the signal arrive as zeros).  W: (N, taps x cin) in the
+// input row m + t - taps/2 (a TMA row coordinate; rows outside the signal arrive as zeros).  out_row_map (optional,
+// int32 [M]): output row m is stored at row out_row_map[m], dropped when negative (the stack's last layer keeps the
+// curve points and drops the pad rows).  W: (N, taps x cin) in the
 // ccn_split_bf16 layout with every tap's cin columns starting at a multiple of 64.
 extern "C" int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t taps,
                                const void* w_hi_tmap_host, const void* w_lo_tmap_host, const float* bias, float* Y,
                                int64_t ldy, void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, int64_t M, int32_t N,
-                               int32_t box_n, int32_t mode, int32_t act, float slope, ccn_stream_t stream) {
+                               int32_t box_n, int32_t mode, int32_t act, float slope, const int32_t* out_row_map,
+                               ccn_stream_t stream) {
     const void* ap[kMaxSeg] = {a, nullptr, nullptr, nullptr};
     const int64_t ald[kMaxSeg] = {ld, 0, 0, 0}, aps[kMaxSeg] = {ps, 0, 0, 0};
     const int32_t ak[kMaxSeg] = {cin, 0, 0, 0};
     CCN_REQUIRE(taps >= 1);
-    return launch_planes(ap, ald, aps, ak, taps, 0, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
+    return launch_planes(ap, ald, aps, ak, taps, 0, out_row_map, w_hi_tmap_host, w_lo_tmap_host, bias, Y, ldy, y_planes, yp_ld,
                          yp_plane_stride, M, N, box_n, mode, act, slope, stream);
 }

@@ -105,29 +105,44 @@ class SymmetricCurve1DConvV2(_CurveConvBase):
         pad = (k // 2) * len(layers) if k > 1 else 0
         row2pt = ops.curve_row_map(topo, pad)
         rows = row2pt.shape[0]
-        sig = feats
+        # tensor-core layers: from the first layer on whose successors are all GEMM-sized, the k x C_in x C_out contraction
+        # of a layer is ONE tcgen05 GEMM over the padded signal (a tap's row shift is a TMA row coordinate), activations
+        # stay in bf16 planes between the layers and the last layer stores the curve points only (row map in the
+        # epilogue).  Narrow first layers (C_in = 8 at the input of the network) stay on the FP32-pipe tap kernel, which
+        # reads the points through the pad-row map.
+        tc_from = len(layers)
+        if n_planes() > 0 and rows > 0:
+            while tc_from > 0 and self._tc_layer(layers[tc_from - 1][0], tc_from - 1 == 0):
+                tc_from -= 1
+        sig, sigp = feats, None
         for li, (w, b) in enumerate(layers):
             first, last = li == 0, li == len(layers) - 1
-            if first and not last and self._wide_first(w, rows):
-                # wide first layer (fp-side conv: C_in = 262): the k x C_in x C_out contraction as ONE tcgen05 GEMM over the
-                # padded signal (a tap's row shift is a TMA row coordinate) instead of the FP32-pipe tap kernel
-                padded = ops.gather_rows_i32(feats, row2pt)              # zero rows at the curve boundaries
-                sig = ops.conv_planes(ops.pack_planes([padded], n_planes()), w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_first(w))
+            if li >= tc_from:
+                if first:
+                    sigp = ops.pack_planes([ops.gather_rows_i32(feats, row2pt)], n_planes())   # zero rows at the curve boundaries
+                elif sigp is None:
+                    sigp = ops.pack_planes([sig], n_planes())
+                if last:
+                    sig = ops.conv_planes(sigp, w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_weight(li, w), out_map=row2pt, out_rows=n)
+                else:
+                    sigp = ops.conv_planes(sigp, w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_weight(li, w), out="planes")
                 continue
             sig = ops.curve_conv_layer(sig, w, b, row2pt, rows, n if last else rows, k, first, last)
         return sig, pos, batch, point2curveidx
 
-    def _wide_first(self, w, rows):
-        return n_planes() > 0 and rows > 0 and w.shape[1] >= 128 and w.shape[2] >= 16
+    @staticmethod
+    def _tc_layer(w, first):
+        return w.shape[2] >= 16 and w.shape[1] >= (128 if first else 16)
 
-    def _tc_first(self, w):
-        """bf16 planes + TMA descriptors of the first layer's folded weight, rebuilt when the folded weights change."""
-        hit = self.__dict__.get("_tc_first_cache")
+    def _tc_weight(self, li, w):
+        """bf16 planes + TMA descriptors of a layer's folded weight, rebuilt when the folded weights change."""
+        cache = self.__dict__.setdefault("_tc_cache", {})
+        hit = cache.get(li)
         if hit is None or hit[0] is not w:
             taps, cin, cout = w.shape
             tw = ops.TcWeight(w.permute(2, 0, 1).reshape(cout, taps * cin).contiguous(), [cin] * taps if taps > 1 else None)
             hit = (w, tw)
-            self.__dict__["_tc_first_cache"] = hit
+            cache[li] = hit
         return hit[1]
 
 

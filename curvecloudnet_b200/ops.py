@@ -722,20 +722,26 @@ def linear_planes_bt(A: "Planes", tw: "TcWeight") -> torch.Tensor:
 
 
 def conv_planes(sig: "Planes", w_kio: torch.Tensor, bias: Optional[torch.Tensor], act: int = ACT_NONE, slope: float = 0.01,
-                tw: "TcWeight" = None) -> torch.Tensor:
+                tw: "TcWeight" = None, out: str = "f32", out_map: Optional[torch.Tensor] = None, out_rows: int = 0):
     """'same' zero-padded 1-D convolution along the rows of `sig` (planes of a (rows, cin) signal) as ONE tcgen05 GEMM:
-    w_kio (taps, cin, cout); tap t of output row m reads row m + t - taps/2 (ccn_conv_planes).  fp32 (rows, cout)."""
+    w_kio (taps, cin, cout); tap t of output row m reads row m + t - taps/2 (ccn_conv_planes).  out = "f32": fp32
+    (rows, cout); "planes": activation planes for the next layer of the stack.  out_map (int32 (rows), with out_rows):
+    output row m is stored at row out_map[m] and dropped when negative (the last layer keeps the curve points only)."""
     taps, cin, cout = w_kio.shape
     assert sig.k == cin
     if tw is None:
         tw = TcWeight(w_kio.permute(2, 0, 1).reshape(cout, taps * cin).contiguous(), [cin] * taps if taps > 1 else None)
     M = sig.m
-    Y = _empty((M, cout), torch.float32, sig.buf)
+    rows_out = out_rows if out_map is not None else M
+    Y = _empty((rows_out, cout), torch.float32, sig.buf) if out == "f32" else None
+    Yp = alloc_planes(rows_out, cout, sig.n_planes, sig.buf) if out == "planes" else None
     box = tw.pick_box_planes(M, sig.n_planes)
     w_hi, w_lo, _ = tw.maps(box)
     call("ccn_conv_planes", sig.buf, sig.kpad, sig.buf.stride(0), cin, taps, w_hi, w_lo, bias if bias is not None else 0,
-         Y, cout, 0, 0, 0, M, cout, box, 3 if sig.n_planes == 2 else 1, act, float(slope))
-    return Y
+         Y if Y is not None else 0, cout, Yp.buf if Yp is not None else 0, Yp.kpad if Yp is not None else 0,
+         Yp.buf.stride(0) if Yp is not None else 0, M, cout, box, 3 if sig.n_planes == 2 else 1, act, float(slope),
+         out_map if out_map is not None else 0)
+    return Y if out == "f32" else Yp
 
 
 _TC_SCRATCH = {}

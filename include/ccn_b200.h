@@ -306,11 +306,13 @@ int ccn_linear_wgrad_tc(const void* dy_planes, int64_t dy_ld, int64_t dy_plane_s
 /* 'same' zero-padded 1-D convolution along the ROW axis of an activation-planes signal as one tcgen05 GEMM
  * (fast_conv1d.py:148-187 F.conv1d): K = taps x cin, tap t of output row m reads input row m + t - taps/2 through a
  * TMA row coordinate (rows outside [0, M) are zeros).  W: (N, taps x cin) in the ccn_split_bf16 layout, every tap's
- * cin columns starting at a multiple of 64.  Other arguments as ccn_linear_planes. */
+ * cin columns starting at a multiple of 64.  out_row_map (optional int32 [M]): output row m is stored at row
+ * out_row_map[m] of Y / y_planes and dropped when negative - the last layer of a conv stack keeps the curve points and
+ * drops the pad rows (fast_conv1d.py:70-73).  Other arguments as ccn_linear_planes. */
 int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t taps, const void* w_hi_tmap_host,
                     const void* w_lo_tmap_host, const float* bias, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
                     int64_t yp_plane_stride, int64_t M, int32_t N, int32_t box_n, int32_t mode, int32_t act, float slope,
-                    ccn_stream_t stream);
+                    const int32_t* out_row_map, ccn_stream_t stream);
 /* Curve grouping of a raw sweep - SemNuScenes._get_curves / SemKITTI._get_curves (src/data/nuscenes_dataset.py:91-118,
  * src/data/kitti_dataset.py:73-92): reorder = stable argsort of beam ids, inv_reorder its inverse, sorted_points (n,3) =
  * points[reorder], curve_idxs = running count of splits (beam change, or f64 edge length > curve_thresh * sqrt(|p.xy|)).
