@@ -19,6 +19,8 @@
 //   warps 2-5 epilogue: tcgen05.ld (32 lanes x 32 columns), bias + activation, then fp32 rows and/or bf16 planes.
 // Tile order: tile t -> (m = t / tiles_n, n = t % tiles_n); the grid is a multiple of tiles_n in resident mode, so
 // a CTA keeps one N-slice and the CTAs sharing an A tile run concurrently (second read served by L2).
+#include <type_traits>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -239,15 +241,18 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
             const int row = m0 + q * 32 + lane;
             const int orow = MAPPED ? (row < p.M ? __ldg(out_map + row) : -1) : row;
             const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
-            for (int c0 = 0; c0 < mma_n; c0 += 32) {
-                uint32_t v[32];
-                tmem_ld32(tbase + (uint32_t)c0, v);
+            // The activation is a compile-time constant of the chunk loop (switch below): ptxas only unswitched the
+            // run-time test on its own while the parameter struct stayed small, and the branchy form (two uniform branches
+            // per element, 150 BRA in the kernel) ran the HBM-bound layers 1.6-1.8x slower (profiles/r01h_ab.log).
+            auto chunks = [&](auto act_tag) {
+            constexpr int ACT = decltype(act_tag)::value;
+            auto emit = [&](const uint32_t (&v)[32], const int c0) {
                 float y[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     float o = __uint_as_float(v[j]) + bs[c0 + j];
-                    if (p.act == CCN_ACT_RELU) o = fmaxf(o, 0.f);
-                    else if (p.act == CCN_ACT_LEAKY) o = o > 0.f ? o : o * p.slope;
+                    if (ACT == CCN_ACT_RELU) o = fmaxf(o, 0.f);
+                    else if (ACT == CCN_ACT_LEAKY) o = o > 0.f ? o : o * p.slope;
                     y[j] = o;
                 }
                 if (MAPPED ? orow >= 0 : row < p.M) {
@@ -288,7 +293,16 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                         }
                     }
                 }
+            };
+            for (int c0 = 0; c0 < mma_n; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tbase + (uint32_t)c0, v);
+                emit(v, c0);
             }
+            };
+            if (p.act == CCN_ACT_RELU) chunks(std::integral_constant<int, CCN_ACT_RELU>{});
+            else if (p.act == CCN_ACT_LEAKY) chunks(std::integral_constant<int, CCN_ACT_LEAKY>{});
+            else chunks(std::integral_constant<int, CCN_ACT_NONE>{});
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
