@@ -189,8 +189,27 @@ __device__ __forceinline__ float4 max4(float4 a, float4 b) {
     return make_float4(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w));
 }
 
+// fp32 result AND its activation planes from the producing kernel (the consumer is a Linear: saves the pack launch):
+// 4 channels -> 4 bf16 hi (+ 4 bf16 lo), one 8-byte store per plane
+__device__ __forceinline__ void st_planes4(const float4 y, __nv_bfloat16* o, int64_t plane_stride, int n_planes) {
+    const __nv_bfloat162 h0 = __floats2bfloat162_rn(y.x, y.y), h1 = __floats2bfloat162_rn(y.z, y.w);
+    uint2 hv;
+    hv.x = *reinterpret_cast<const uint32_t*>(&h0);
+    hv.y = *reinterpret_cast<const uint32_t*>(&h1);
+    *reinterpret_cast<uint2*>(o) = hv;
+    if (n_planes == 2) {
+        const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+        const __nv_bfloat162 l0 = __floats2bfloat162_rn(y.x - f0.x, y.y - f0.y), l1 = __floats2bfloat162_rn(y.z - f1.x, y.w - f1.y);
+        uint2 lv;
+        lv.x = *reinterpret_cast<const uint32_t*>(&l0);
+        lv.y = *reinterpret_cast<const uint32_t*>(&l1);
+        *reinterpret_cast<uint2*>(o + plane_stride) = lv;
+    }
+}
+
 __global__ void group_max_dense_v4_kernel(const float* __restrict__ feat, int64_t ldf, const int32_t* __restrict__ idx,
-                                          int64_t n, int K, int c4, float* __restrict__ out, int64_t ldo) {
+                                          int64_t n, int K, int c4, float* __restrict__ out, int64_t ldo,
+                                          __nv_bfloat16* __restrict__ planes, int64_t kpad, int64_t pstride, int npl) {
     const int G = K + 1;
     const int64_t total = n * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -206,12 +225,14 @@ __global__ void group_max_dense_v4_kernel(const float* __restrict__ feat, int64_
             r = max4(r, v);
         }
         *reinterpret_cast<float4*>(out + i * ldo + 4 * k4) = r;
+        if (planes) st_planes4(r, planes + i * kpad + 4 * k4, pstride, npl);
     }
 }
 
 __global__ void seg_aggregate_v4_kernel(const float* __restrict__ msg, int64_t ldm, const float* __restrict__ att,
                                         int64_t lda, const int32_t* __restrict__ row_ptr, int64_t nq, int c4, int mode,
-                                        float* __restrict__ out, int64_t ldo) {
+                                        float* __restrict__ out, int64_t ldo, __nv_bfloat16* __restrict__ planes,
+                                        int64_t kpad, int64_t pstride, int npl) {
     const int64_t total = nq * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t q;
@@ -269,7 +290,9 @@ __global__ void seg_aggregate_v4_kernel(const float* __restrict__ msg, int64_t l
                 r[2] += v.z * (expf(a.z - mx[2]) * inv[2]); r[3] += v.w * (expf(a.w - mx[3]) * inv[3]);
             }
         }
-        *reinterpret_cast<float4*>(out + q * ldo + 4 * k4) = make_float4(r[0], r[1], r[2], r[3]);
+        const float4 rv = make_float4(r[0], r[1], r[2], r[3]);
+        *reinterpret_cast<float4*>(out + q * ldo + 4 * k4) = rv;
+        if (planes) st_planes4(rv, planes + q * kpad + 4 * k4, pstride, npl);
     }
 }
 
@@ -298,7 +321,8 @@ __global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, co
 
 __global__ void interp_blend_v4_kernel(const float* __restrict__ x, int64_t ldx, const int32_t* __restrict__ nbr,
                                        const float* __restrict__ wgt, int from_d2, int64_t n, int knn, int c4,
-                                       float* __restrict__ out, int64_t ldo) {
+                                       float* __restrict__ out, int64_t ldo, __nv_bfloat16* __restrict__ planes,
+                                       int64_t kpad, int64_t pstride, int npl) {
     const int64_t total = n * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t i;
@@ -315,8 +339,9 @@ __global__ void interp_blend_v4_kernel(const float* __restrict__ x, int64_t ldx,
             num[2] = __fadd_rn(num[2], __fmul_rn(v.z, w)); num[3] = __fadd_rn(num[3], __fmul_rn(v.w, w));
             den = __fadd_rn(den, w);
         }
-        *reinterpret_cast<float4*>(out + i * ldo + 4 * k4) =
-            make_float4(__fdiv_rn(num[0], den), __fdiv_rn(num[1], den), __fdiv_rn(num[2], den), __fdiv_rn(num[3], den));
+        const float4 rv = make_float4(__fdiv_rn(num[0], den), __fdiv_rn(num[1], den), __fdiv_rn(num[2], den), __fdiv_rn(num[3], den));
+        *reinterpret_cast<float4*>(out + i * ldo + 4 * k4) = rv;
+        if (planes) st_planes4(rv, planes + i * kpad + 4 * k4, pstride, npl);
     }
 }
 
@@ -591,7 +616,7 @@ extern "C" int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att
     if ((c & 3) == 0 && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) && ccn_al16(out) &&
         (!att || ((lda & 3) == 0 && ccn_al16(att)))) {
         seg_aggregate_v4_kernel<<<CCN_ELT_GRID(nq * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq,
-                                                                                                c >> 2, mode, out, ldo);
+                                                                                                c >> 2, mode, out, ldo, nullptr, 0, 0, 0);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
@@ -617,7 +642,7 @@ extern "C" int ccn_group_max_dense(const float* feat, int64_t ldf, const int32_t
     if (n == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldf & 3) == 0 && (ldo & 3) == 0 && ccn_al16(feat) && ccn_al16(out)) {
         group_max_dense_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(feat, ldf, idx, n, K, c >> 2,
-                                                                                                 out, ldo);
+                                                                                                 out, ldo, nullptr, 0, 0, 0);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
@@ -632,7 +657,7 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
     if (n == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldx & 3) == 0 && (ldo & 3) == 0 && ccn_al16(x) && ccn_al16(out)) {
         interp_blend_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn,
-                                                                                              c >> 2, out, ldo);
+                                                                                              c >> 2, out, ldo, nullptr, 0, 0, 0);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
@@ -644,6 +669,50 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
 
 #define CCN_PLANES_OK(planes, kpad, pstride, npl, c) \
     ((planes) && ccn_al16(planes) && ((kpad) & 7) == 0 && (kpad) >= (c) && ((c) & 7) == 0 && ((npl) == 1 || ((npl) == 2 && ((pstride) & 7) == 0)))
+
+// fp32 result + activation planes in one launch (float4 kernels; c % 16 == 0 so that the planes carry no pad columns)
+#define CCN_BOTH_OK(planes, kpad, pstride, npl, c) \
+    (CCN_PLANES_OK(planes, kpad, pstride, npl, c) && ((c) & 15) == 0 && (kpad) == (c))
+
+extern "C" int ccn_seg_aggregate_both(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
+                                      int64_t nq, int32_t c, int32_t mode, float* out, int64_t ldo, void* planes,
+                                      int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 4);
+    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || att);
+    CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) &&
+                ccn_al16(out) && (!att || ((lda & 3) == 0 && ccn_al16(att))));
+    if (nq == 0) return CCN_OK;
+    seg_aggregate_v4_kernel<<<CCN_ELT_GRID(nq * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+        msg, ldm, att, lda, row_ptr, nq, c >> 2, mode, out, ldo, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_group_max_dense_both(const float* feat, int64_t ldf, const int32_t* idx, int64_t n, int32_t K, int32_t c,
+                                        float* out, int64_t ldo, void* planes, int64_t kpad, int64_t plane_stride,
+                                        int32_t n_planes, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && feat && out && (K == 0 || idx));
+    CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldf & 3) == 0 && (ldo & 3) == 0 && ccn_al16(feat) &&
+                ccn_al16(out));
+    if (n == 0) return CCN_OK;
+    group_max_dense_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+        feat, ldf, idx, n, K, c >> 2, out, ldo, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_interp_blend_both(const float* x, int64_t ldx, const int32_t* nbr, const float* wgt, int32_t from_d2,
+                                     int64_t n, int32_t knn, int32_t c, float* out, int64_t ldo, void* planes, int64_t kpad,
+                                     int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && knn >= 1 && c > 0 && x && nbr && wgt && out);
+    CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldx & 3) == 0 && (ldo & 3) == 0 && ccn_al16(x) &&
+                ccn_al16(out));
+    if (n == 0) return CCN_OK;
+    interp_blend_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+        x, ldx, nbr, wgt, from_d2, n, knn, c >> 2, out, ldo, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
 
 extern "C" int ccn_sgcnn_layer1_planes(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c,
                                        int32_t act, float slope, void* planes, int64_t kpad, int64_t plane_stride,

@@ -123,7 +123,10 @@ class SymmetricCurve1DConvV2(_CurveConvBase):
                 elif sigp is None:
                     sigp = ops.pack_planes([sig], n_planes())
                 if last:
-                    sig = ops.conv_planes(sigp, w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_weight(li, w), out_map=row2pt, out_rows=n)
+                    # the step output feeds Linear layers: fp32 rows and their planes from the same epilogue
+                    sig, outp = ops.conv_planes(sigp, w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_weight(li, w), out="both",
+                                                out_map=row2pt, out_rows=n)
+                    get_cache(kwargs).put_planes(sig, outp)
                 else:
                     sigp = ops.conv_planes(sigp, w, b, ops.ACT_LEAKY, 0.01, tw=self._tc_weight(li, w), out="planes")
                 continue
@@ -209,14 +212,14 @@ class PointNetConv2(nn.Module):
         msg = ops.edge_layer1(H, wp, l0.b, pos_src, pos_dst, edges, self.normalize_radius, l0.act, l0.slope, npl)
         if self.aggr_type in ("max", "mean"):
             msg = self.local_nn.forward_from(msg, 1)
-            out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, self.aggr_type)
+            out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, self.aggr_type, n_planes(), cache)
         else:
             # the message is needed twice: fp32 for the aggregation, planes as the input of attend_nn
             both = npl > 0
             msg = self.local_nn.forward_from(msg, 1, "both" if both else "f32")
             msg, msg_in = msg if both else (msg, msg)
             att = self.attend_nn(msg_in)
-            out = ops.seg_aggregate(msg, att, edges.row_ptr, edges.nq, self.aggr_type)
+            out = ops.seg_aggregate(msg, att, edges.row_ptr, edges.nq, self.aggr_type, n_planes(), cache)
         if self.global_nn is not None:
             out = self.global_nn(out)
         return out
@@ -334,7 +337,7 @@ class FPModule(nn.Module):
         cache = get_cache(kwargs)
         sptr = cache.sample_ptr(batch)
         nbr, d2 = ops.knn_exact(pos_skip, batch_skip, pos, sptr, self.k, zero_fill=True, want_d2=True)
-        y = ops.interp_blend(x, nbr, d2, from_d2=True)
+        y = ops.interp_blend(x, nbr, d2, from_d2=True, npl=n_planes(), cache=cache)
         y = mlp_to_features(self.nn, _fp_concat(y, x_skip, pos_skip, self.with_xyz, cache), cache)
         return y, pos_skip, batch_skip, point2curveidx_skip
 
@@ -378,7 +381,7 @@ class CurveFPModule(FPModule):
         cache = get_cache(kwargs)
         topo = cache.topology(batch_skip, point2curveidx_skip)
         nbr, wgt = ops.knn_1d_superset(pos_skip, topo.curve_ord, idx, self.k)
-        y = ops.interp_blend(x, nbr, wgt, from_d2=False)
+        y = ops.interp_blend(x, nbr, wgt, from_d2=False, npl=n_planes(), cache=cache)
         y = mlp_to_features(self.nn, _fp_concat(y, x_skip, pos_skip, self.with_xyz, cache), cache)
         return y, pos_skip, batch_skip, point2curveidx_skip
 
@@ -433,7 +436,7 @@ class SGCNNLayer(nn.Module):
             nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, cache=cache)
             h = ops.sgcnn_layer1(PQ, nbr, act0, slope0, n_planes() if self.nn.num_layers > 1 else 0)
             h = self.nn.forward_from(h, 1)
-            return ops.group_max_dense(h, nbr), pos, batch, point2curveidx
+            return ops.group_max_dense(h, nbr, n_planes(), cache), pos, batch, point2curveidx
         if self.use_fast_knn:
             nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, want_cnt=True, cache=cache)
         else:
@@ -443,12 +446,12 @@ class SGCNNLayer(nn.Module):
         msg = ops.edge_pair_layer1(PQ, edges, act0, slope0, npl)
         if self.aggr_type == "max":
             msg = self.nn.forward_from(msg, 1)
-            out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "max")
+            out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "max", n_planes(), cache)
         elif self.aggr_type == "attend":
             both = npl > 0
             msg = self.nn.forward_from(msg, 1, "both" if both else "f32")
             msg, msg_in = msg if both else (msg, msg)
-            out = ops.seg_aggregate(msg, self.attend_nn(msg_in), edges.row_ptr, edges.nq, "attend")
+            out = ops.seg_aggregate(msg, self.attend_nn(msg_in), edges.row_ptr, edges.nq, "attend", n_planes(), cache)
         else:
             raise NotImplementedError("sparse SGCNN path: aggregation %r" % self.aggr_type)
         return out, pos, batch, point2curveidx

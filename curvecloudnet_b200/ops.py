@@ -459,7 +459,21 @@ def edge_pair_layer1(PQ: torch.Tensor, edges: EdgeCSR, act: int, slope: float = 
     return out
 
 
-def seg_aggregate(msg: torch.Tensor, att: Optional[torch.Tensor], row_ptr: torch.Tensor, nq: int, mode: str):
+def _both_ok(npl: int, cache, c: int, *mats) -> bool:
+    """A producer may write its fp32 result AND the activation planes in one launch (ccn_*_both): tensor-core mode, a
+    forward cache to register the planes in, c % 16 == 0 and 16-byte aligned fp32 rows."""
+    if not npl or cache is None or c % 16:
+        return False
+    for t, ld in mats:
+        if t is not None and (ld % 4 or t.data_ptr() % 16):
+            return False
+    return True
+
+
+def seg_aggregate(msg: torch.Tensor, att: Optional[torch.Tensor], row_ptr: torch.Tensor, nq: int, mode: str,
+                  npl: int = 0, cache=None):
+    """npl / cache: on the tensor-core modes the result's activation planes are written by the same launch and
+    registered in the forward cache (the consumers of a step output are Linear layers)."""
     msg, ldm = _rows(msg)
     c = msg.shape[1]
     if att is not None:
@@ -467,6 +481,12 @@ def seg_aggregate(msg: torch.Tensor, att: Optional[torch.Tensor], row_ptr: torch
     else:
         lda = 0
     out = _empty((nq, c), torch.float32, msg)
+    if nq and _both_ok(npl, cache, c, (msg, ldm), (att, lda)):
+        pl = alloc_planes(nq, c, npl, msg)
+        call("ccn_seg_aggregate_both", msg, ldm, att if att is not None else 0, lda, row_ptr, nq, c, AGG[mode], out, c,
+             pl.buf, pl.kpad, pl.plane_stride, npl)
+        cache.put_planes(out, pl)
+        return out
     call("ccn_seg_aggregate", msg, ldm, att if att is not None else 0, lda, row_ptr, nq, c, AGG[mode], out, c)
     return out
 
@@ -485,20 +505,31 @@ def sgcnn_layer1(PQ: torch.Tensor, idx: torch.Tensor, act: int, slope: float = 0
     return out
 
 
-def group_max_dense(feat: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+def group_max_dense(feat: torch.Tensor, idx: torch.Tensor, npl: int = 0, cache=None) -> torch.Tensor:
     feat, ld = _rows(feat)
     n, K = idx.shape
     c = feat.shape[1]
     out = _empty((n, c), torch.float32, feat)
+    if n and _both_ok(npl, cache, c, (feat, ld)):
+        pl = alloc_planes(n, c, npl, feat)
+        call("ccn_group_max_dense_both", feat, ld, idx, n, K, c, out, c, pl.buf, pl.kpad, pl.plane_stride, npl)
+        cache.put_planes(out, pl)
+        return out
     call("ccn_group_max_dense", feat, ld, idx, n, K, c, out, c)
     return out
 
 
-def interp_blend(x: torch.Tensor, nbr: torch.Tensor, wgt: torch.Tensor, from_d2: bool) -> torch.Tensor:
+def interp_blend(x: torch.Tensor, nbr: torch.Tensor, wgt: torch.Tensor, from_d2: bool, npl: int = 0, cache=None) -> torch.Tensor:
     x, ldx = _rows(x)
     n, knn = nbr.shape
     c = x.shape[1]
     out = _empty((n, c), torch.float32, x)
+    if n and _both_ok(npl, cache, c, (x, ldx)):
+        pl = alloc_planes(n, c, npl, x)
+        call("ccn_interp_blend_both", x, ldx, nbr, wgt, int(from_d2), n, knn, c, out, c, pl.buf, pl.kpad, pl.plane_stride,
+             npl)
+        cache.put_planes(out, pl)
+        return out
     call("ccn_interp_blend", x, ldx, nbr, wgt, int(from_d2), n, knn, c, out, c)
     return out
 
@@ -725,7 +756,7 @@ def conv_planes(sig: "Planes", w_kio: torch.Tensor, bias: Optional[torch.Tensor]
                 tw: "TcWeight" = None, out: str = "f32", out_map: Optional[torch.Tensor] = None, out_rows: int = 0):
     """'same' zero-padded 1-D convolution along the rows of `sig` (planes of a (rows, cin) signal) as ONE tcgen05 GEMM:
     w_kio (taps, cin, cout); tap t of output row m reads row m + t - taps/2 (ccn_conv_planes).  out = "f32": fp32
-    (rows, cout); "planes": activation planes for the next layer of the stack.  out_map (int32 (rows), with out_rows):
+    (rows, cout); "planes": activation planes for the next layer of the stack; "both": (fp32, planes).  out_map (int32 (rows), with out_rows):
     output row m is stored at row out_map[m] and dropped when negative (the last layer keeps the curve points only)."""
     taps, cin, cout = w_kio.shape
     assert sig.k == cin
@@ -733,15 +764,15 @@ def conv_planes(sig: "Planes", w_kio: torch.Tensor, bias: Optional[torch.Tensor]
         tw = TcWeight(w_kio.permute(2, 0, 1).reshape(cout, taps * cin).contiguous(), [cin] * taps if taps > 1 else None)
     M = sig.m
     rows_out = out_rows if out_map is not None else M
-    Y = _empty((rows_out, cout), torch.float32, sig.buf) if out == "f32" else None
-    Yp = alloc_planes(rows_out, cout, sig.n_planes, sig.buf) if out == "planes" else None
+    Y = _empty((rows_out, cout), torch.float32, sig.buf) if out != "planes" else None
+    Yp = alloc_planes(rows_out, cout, sig.n_planes, sig.buf) if out != "f32" else None
     box = tw.pick_box_planes(M, sig.n_planes)
     w_hi, w_lo, _ = tw.maps(box)
     call("ccn_conv_planes", sig.buf, sig.kpad, sig.buf.stride(0), cin, taps, w_hi, w_lo, bias if bias is not None else 0,
          Y if Y is not None else 0, cout, Yp.buf if Yp is not None else 0, Yp.kpad if Yp is not None else 0,
          Yp.buf.stride(0) if Yp is not None else 0, M, cout, box, 3 if sig.n_planes == 2 else 1, act, float(slope),
          out_map if out_map is not None else 0)
-    return Y if out == "f32" else Yp
+    return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)
 
 
 _TC_SCRATCH = {}

@@ -174,6 +174,18 @@ int ccn_group_max_dense(const float* feat, int64_t ldf, const int32_t* idx, int6
                         int64_t ldo, ccn_stream_t stream);
 int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr, const float* wgt, int32_t from_d2, int64_t n,
                      int32_t knn, int32_t c, float* out, int64_t ldo, ccn_stream_t stream);
+/* The three producers above with the result written twice in ONE launch: fp32 rows (as above) and split-bf16 activation
+ * planes (layout of ccn_pack_planes; kpad == c, c % 16 == 0, 16-byte aligned fp32 rows) - the consumers of these step outputs
+ * are Linear layers (skip-connect / feature-propagation MLPs, base.py:179-209), so the separate pack launch disappears. */
+int ccn_seg_aggregate_both(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr, int64_t nq,
+                           int32_t c, int32_t mode, float* out, int64_t ldo, void* planes, int64_t kpad,
+                           int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
+int ccn_group_max_dense_both(const float* feat, int64_t ldf, const int32_t* idx, int64_t n, int32_t K, int32_t c, float* out,
+                             int64_t ldo, void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes,
+                             ccn_stream_t stream);
+int ccn_interp_blend_both(const float* x, int64_t ldx, const int32_t* nbr, const float* wgt, int32_t from_d2, int64_t n,
+                          int32_t knn, int32_t c, float* out, int64_t ldo, void* planes, int64_t kpad, int64_t plane_stride,
+                          int32_t n_planes, ccn_stream_t stream);
 
 /* ---- shared MLP layer (torch_geometric.nn.MLP -> nn.Linear/BatchNorm1d/act; base.py:32, mlp.py:16-22) ----
  * Y = act(A W^T + bias), W is (N, K) row-major with BatchNorm(eval) folded by the caller. */
