@@ -532,24 +532,41 @@ namespace {
 // pos / batch / curve of the selected points in one pass (pos[idx], batch[idx], curve_idxs[idx] of pointnet2.py:69-72)
 __global__ void subset_gather_kernel(const float* __restrict__ pos, int64_t ldp, const int64_t* __restrict__ batch,
                                      const int64_t* __restrict__ curve, const int64_t* __restrict__ idx, int64_t n,
-                                     float* __restrict__ posq, int64_t* __restrict__ batchq, int64_t* __restrict__ curveq) {
+                                     float* __restrict__ posq, int64_t* __restrict__ batchq, int64_t* __restrict__ curveq,
+                                     __nv_bfloat16* __restrict__ planes, int64_t pstride, int npl) {
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t >= n) return;
     const int64_t i = idx[t];
-    posq[3 * t] = pos[i * ldp]; posq[3 * t + 1] = pos[i * ldp + 1]; posq[3 * t + 2] = pos[i * ldp + 2];
+    const float x = pos[i * ldp], y = pos[i * ldp + 1], z = pos[i * ldp + 2];
+    posq[3 * t] = x; posq[3 * t + 1] = y; posq[3 * t + 2] = z;
     batchq[t] = batch[i];
     if (curve) curveq[t] = curve[i];
+    if (planes) {
+        // activation planes of the (n, 3) position matrix (kpad = 16: xyz + 13 zero columns), ccn_pack_planes layout
+        const __nv_bfloat162 h0 = __floats2bfloat162_rn(x, y), h1 = __floats2bfloat162_rn(z, 0.f);
+        __nv_bfloat16* o = planes + t * 16;
+        *reinterpret_cast<uint4*>(o) = make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1), 0u, 0u);
+        *reinterpret_cast<uint4*>(o + 8) = make_uint4(0u, 0u, 0u, 0u);
+        if (npl == 2) {
+            const float2 f0 = __bfloat1622float2(h0), f1 = __bfloat1622float2(h1);
+            const __nv_bfloat162 l0 = __floats2bfloat162_rn(x - f0.x, y - f0.y), l1 = __floats2bfloat162_rn(z - f1.x, 0.f);
+            o += pstride;
+            *reinterpret_cast<uint4*>(o) = make_uint4(*reinterpret_cast<const uint32_t*>(&l0), *reinterpret_cast<const uint32_t*>(&l1), 0u, 0u);
+            *reinterpret_cast<uint4*>(o + 8) = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
 }
 }  // namespace
 
 extern "C" int ccn_subset_gather(const float* pos, int64_t ldp, const int64_t* batch, const int64_t* curve,
                                  const int64_t* idx, int64_t n, float* posq, int64_t* batchq, int64_t* curveq,
-                                 ccn_stream_t stream) {
+                                 void* pos_planes, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && ldp >= 3);
     if (n == 0) return CCN_OK;
     CCN_REQUIRE(pos && batch && idx && posq && batchq && (!curve || curveq));
-    subset_gather_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(pos, ldp, batch, curve, idx, n, posq,
-                                                                                      batchq, curveq);
+    CCN_REQUIRE(!pos_planes || (ccn_al16(pos_planes) && (n_planes == 1 || (n_planes == 2 && (plane_stride & 7) == 0))));
+    subset_gather_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(
+        pos, ldp, batch, curve, idx, n, posq, batchq, curveq, (__nv_bfloat16*)pos_planes, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

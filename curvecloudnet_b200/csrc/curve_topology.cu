@@ -7,88 +7,125 @@ namespace {
 
 constexpr int kItems = 4;
 
-// One CTA walks the sorted (batch, curve) id vectors once with a running carry:
-// hi 32 bits of the scanned value count sample starts, lo 32 bits curve starts.
-__global__ void __launch_bounds__(1024) curve_csr_kernel(
-    const int64_t* __restrict__ batch, const int64_t* __restrict__ curve, int64_t n,
-    int32_t* __restrict__ ord, int32_t* __restrict__ cptr, int32_t* __restrict__ sptr,
-    int64_t* __restrict__ soff, int64_t* __restrict__ glob, int32_t* __restrict__ counts, int max_samples) {
-    __shared__ unsigned long long sm[33];
-    __shared__ int s_err;
-    if (threadIdx.x == 0) s_err = 0;
-    __syncthreads();
-    unsigned long long carry = 0;
-    int err = 0;
-    for (int64_t base = 0; base < n; base += 1024 * kItems) {
-        const int64_t i0 = base + (int64_t)threadIdx.x * kItems;
-        unsigned long long f[kItems];
-        unsigned long long local = 0;
-#pragma unroll
-        for (int e = 0; e < kItems; ++e) {
-            const int64_t i = i0 + e;
-            f[e] = 0;
-            if (i < n) {
-                const int64_t b = batch[i], c = curve[i];
-                bool ss = true, cs = true;
-                if (i > 0) {
-                    const int64_t pb = batch[i - 1], pc = curve[i - 1];
-                    ss = b != pb;
-                    cs = ss || c != pc;
-                    if (b < pb) err |= CCN_TOPO_ERR_BATCH_UNSORTED;
-                    if (!ss && c < pc) err |= CCN_TOPO_ERR_CURVE_UNSORTED;
-                }
-                f[e] = ((unsigned long long)ss << 32) | (unsigned long long)cs;
-            }
-            local += f[e];
-        }
-        unsigned long long total;
-        unsigned long long run = carry + ccn_block_excl_scan<unsigned long long>(local, sm, &total);
-#pragma unroll
-        for (int e = 0; e < kItems; ++e) {
-            const int64_t i = i0 + e;
-            if (i < n) {
-                run += f[e];
-                const int c_ord = (int)(run & 0xffffffffu) - 1;
-                const int s_ord = (int)(run >> 32) - 1;
-                ord[i] = c_ord;
-                if (f[e] & 1ull) cptr[c_ord] = (int32_t)i;
-                if (f[e] >> 32) {
-                    if (s_ord < max_samples) sptr[s_ord] = (int32_t)i;
-                    else err |= CCN_TOPO_ERR_TOO_MANY_SAMPLES;
-                    if (batch[i] != (int64_t)s_ord) err |= CCN_TOPO_ERR_BATCH_NOT_DENSE;
-                }
-            }
-        }
-        carry += total;
+// Multi-CTA scan over the sorted (batch, curve) id vectors in four small launches (a single CTA serialised over the
+// whole batch: 0.27 ms at 6 x 32 k points).  Start flags are packed in one 64-bit word: hi 32 bits count sample starts,
+// lo 32 bits curve starts.
+//   1. tile_flags_kernel   per 4096-point tile: sum of the packed flags -> tile_sum[t]; sortedness errors -> counts[2]
+//   2. tile_scan_kernel    carry = sum of tile_sum[0..t), then the tile's own scan: ord / cptr / sptr; the last tile writes
+//                          the end pointers and {n_samples, n_curves}
+//   3. sample_offsets_kernel (one CTA)  soff[b] = sum over b' < b of (last curve id of b' + 1)  (point_ops.py:32-35)
+//   4. glob_ids_kernel     glob[i] = curve[i] + soff[batch[i]]
+// tile_sum lives in the head of the glob output buffer (8 bytes per tile <= 8 bytes per point), which step 4 overwrites.
+constexpr int kTile = 1024 * kItems;
+
+__device__ __forceinline__ unsigned long long point_flags(const int64_t* __restrict__ batch, const int64_t* __restrict__ curve,
+                                                          int64_t i, int& err) {
+    const int64_t b = batch[i], c = curve[i];
+    bool ss = true, cs = true;
+    if (i > 0) {
+        const int64_t pb = batch[i - 1], pc = curve[i - 1];
+        ss = b != pb;
+        cs = ss || c != pc;
+        if (b < pb) err |= CCN_TOPO_ERR_BATCH_UNSORTED;
+        if (!ss && c < pc) err |= CCN_TOPO_ERR_CURVE_UNSORTED;
     }
-    if (err) atomicOr(&s_err, err);
-    const int n_samples = (int)(carry >> 32), n_curves = (int)(carry & 0xffffffffu);
-    if (threadIdx.x == 0) {
+    return ((unsigned long long)ss << 32) | (unsigned long long)cs;
+}
+
+__global__ void __launch_bounds__(1024) tile_flags_kernel(const int64_t* __restrict__ batch, const int64_t* __restrict__ curve,
+                                                          int64_t n, unsigned long long* __restrict__ tile_sum,
+                                                          int32_t* __restrict__ counts) {
+    __shared__ unsigned long long sm[33];
+    const int64_t i0 = (int64_t)blockIdx.x * kTile + (int64_t)threadIdx.x * kItems;
+    unsigned long long local = 0;
+    int err = 0;
+#pragma unroll
+    for (int e = 0; e < kItems; ++e)
+        if (i0 + e < n) local += point_flags(batch, curve, i0 + e, err);
+    unsigned long long total;
+    ccn_block_excl_scan<unsigned long long>(local, sm, &total);
+    if (threadIdx.x == 0) tile_sum[blockIdx.x] = total;
+    if (err) atomicOr(&counts[2], err);
+}
+
+__global__ void __launch_bounds__(1024) tile_scan_kernel(
+    const int64_t* __restrict__ batch, const int64_t* __restrict__ curve, int64_t n,
+    const unsigned long long* __restrict__ tile_sum, int32_t* __restrict__ ord, int32_t* __restrict__ cptr,
+    int32_t* __restrict__ sptr, int32_t* __restrict__ counts, int max_samples) {
+    __shared__ unsigned long long sm[33];
+    // carry of this tile = sum of the earlier tiles' totals
+    unsigned long long part = 0;
+    for (int t = threadIdx.x; t < (int)blockIdx.x; t += blockDim.x) part += tile_sum[t];
+    unsigned long long carry;
+    ccn_block_excl_scan<unsigned long long>(part, sm, &carry);
+    const int64_t i0 = (int64_t)blockIdx.x * kTile + (int64_t)threadIdx.x * kItems;
+    unsigned long long f[kItems], local = 0;
+    int err = 0, dummy = 0;
+#pragma unroll
+    for (int e = 0; e < kItems; ++e) {
+        f[e] = (i0 + e < n) ? point_flags(batch, curve, i0 + e, dummy) : 0ull;
+        local += f[e];
+    }
+    unsigned long long total;
+    unsigned long long run = carry + ccn_block_excl_scan<unsigned long long>(local, sm, &total);
+#pragma unroll
+    for (int e = 0; e < kItems; ++e) {
+        const int64_t i = i0 + e;
+        if (i < n) {
+            run += f[e];
+            const int c_ord = (int)(run & 0xffffffffu) - 1;
+            const int s_ord = (int)(run >> 32) - 1;
+            ord[i] = c_ord;
+            if (f[e] & 1ull) cptr[c_ord] = (int32_t)i;
+            if (f[e] >> 32) {
+                if (s_ord < max_samples) sptr[s_ord] = (int32_t)i;
+                else err |= CCN_TOPO_ERR_TOO_MANY_SAMPLES;
+                if (batch[i] != (int64_t)s_ord) err |= CCN_TOPO_ERR_BATCH_NOT_DENSE;
+            }
+        }
+    }
+    if (err) atomicOr(&counts[2], err);
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+        const unsigned long long all = carry + total;
+        const int n_samples = (int)(all >> 32), n_curves = (int)(all & 0xffffffffu);
         cptr[n_curves] = (int32_t)n;
         if (n_samples <= max_samples) sptr[n_samples] = (int32_t)n;
-    }
-    __syncthreads();
-    const int errs = s_err;
-    if (threadIdx.x == 0) {
-        // reference point_ops.py:32-35: offset of sample b = sum over b' < b of (last curve id of b' + 1)
-        int64_t off = 0;
-        if (!errs) {
-            for (int b = 0; b < n_samples; ++b) {
-                soff[b] = off;
-                off += curve[sptr[b + 1] - 1] + 1;
-            }
-            if (n_samples == 1) off = curve[n - 1] + 1;
-        }
         counts[0] = n_samples;
         counts[1] = n_curves;
-        counts[2] = errs;
+    }
+}
+
+__global__ void __launch_bounds__(1024) sample_offsets_kernel(const int64_t* __restrict__ curve, int64_t n,
+                                                              const int32_t* __restrict__ sptr, int64_t* __restrict__ soff,
+                                                              int32_t* __restrict__ counts) {
+    __shared__ long long sm[33];
+    if (counts[2]) {                       // invalid topology: sptr is not trustworthy
+        if (threadIdx.x == 0) counts[3] = 0;
+        return;
+    }
+    const int n_samples = counts[0];
+    long long carry = 0;
+    for (int base = 0; base < n_samples; base += blockDim.x) {
+        const int b = base + threadIdx.x;
+        const long long v = b < n_samples ? (long long)curve[sptr[b + 1] - 1] + 1 : 0;
+        long long total;
+        const long long ex = carry + ccn_block_excl_scan<long long>(v, sm, &total);
+        if (b < n_samples) soff[b] = ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        const long long off = n_samples == 1 ? (long long)curve[n - 1] + 1 : carry;
         counts[3] = (int32_t)(off > 0x7fffffff ? 0x7fffffff : off);   // max global id + 1
     }
-    __syncthreads();
-    if (errs) return;
-    // point_ops.py:27-28: a single sample keeps its ids unchanged
-    for (int64_t i = threadIdx.x; i < n; i += blockDim.x)
-        glob[i] = curve[i] + (n_samples == 1 ? 0 : soff[batch[i]]);
+}
+
+__global__ void glob_ids_kernel(const int64_t* __restrict__ batch, const int64_t* __restrict__ curve, int64_t n,
+                                const int64_t* __restrict__ soff, const int32_t* __restrict__ counts,
+                                int64_t* __restrict__ glob) {
+    if (counts[2]) return;
+    const bool single = counts[0] == 1;     // point_ops.py:27-28: a single sample keeps its ids unchanged
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        glob[i] = curve[i] + (single ? 0 : soff[batch[i]]);
 }
 
 // CSR pointer of a sorted int64 id vector (batch2ptr with ends) for the levels that carry no curves.
@@ -134,8 +171,23 @@ extern "C" int ccn_curve_csr(const int64_t* batch, const int64_t* curve, int64_t
                              int64_t* curve_glob, int32_t* counts, int32_t max_samples, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && n < 0x7fffffff && max_samples > 0);
     CCN_REQUIRE(batch && curve && curve_ord && curve_ptr && sample_ptr && sample_curve_off && curve_glob && counts);
-    curve_csr_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(batch, curve, n, curve_ord, curve_ptr, sample_ptr,
-                                                           sample_curve_off, curve_glob, counts, max_samples);
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(counts, 0, 4 * sizeof(int32_t), s);
+    if (e != cudaSuccess) return (int)e;
+    if (n == 0) {                            // empty batch: end pointers only (counts stay zero)
+        e = cudaMemsetAsync(curve_ptr, 0, sizeof(int32_t), s);
+        if (e == cudaSuccess) e = cudaMemsetAsync(sample_ptr, 0, sizeof(int32_t), s);
+        return e == cudaSuccess ? CCN_OK : (int)e;
+    }
+    const int tiles = (int)((n + kTile - 1) / kTile);
+    unsigned long long* tile_sum = reinterpret_cast<unsigned long long*>(curve_glob);
+    tile_flags_kernel<<<tiles, 1024, 0, s>>>(batch, curve, n, tile_sum, counts);
+    CCN_CHECK_LAUNCH();
+    tile_scan_kernel<<<tiles, 1024, 0, s>>>(batch, curve, n, tile_sum, curve_ord, curve_ptr, sample_ptr, counts, max_samples);
+    CCN_CHECK_LAUNCH();
+    sample_offsets_kernel<<<1, 1024, 0, s>>>(curve, n, sample_ptr, sample_curve_off, counts);
+    CCN_CHECK_LAUNCH();
+    glob_ids_kernel<<<ccn_grid(n, 256, 148LL * 8), 256, 0, s>>>(batch, curve, n, sample_curve_off, counts, curve_glob);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

@@ -228,8 +228,8 @@ class PointNetConv2(nn.Module):
 # ----------------------------------------------------------------------------------------------
 # pointnet2.py
 # ----------------------------------------------------------------------------------------------
-def _subset(x, pos, batch, curve, idx):
-    posq, batchq, curveq = ops.subset_gather(pos, batch, curve, idx)
+def _subset(x, pos, batch, curve, idx, cache=None):
+    posq, batchq, curveq = ops.subset_gather(pos, batch, curve, idx, n_planes(), cache)
     return (None if x is None else ops.gather_rows(x, idx)), posq, batchq, curveq
 
 
@@ -265,7 +265,7 @@ class SAModule(nn.Module):
             idx, sptr_q = ops.voxel_fps(pos, batch, self.voxel_size, draws.voxel_noise(n), sptr.n_samples)
         else:
             idx, sptr_q = fps_sorted(pos, sptr, self.ratio, draws)
-        xq, posq, batchq, curveq = _subset(x, pos, batch, point2curveidx, idx)
+        xq, posq, batchq, curveq = _subset(x, pos, batch, point2curveidx, idx, cache)
         if sptr_q is not None:
             cache.put_sample_ptr(batchq, sptr_q)
         if self.use_fast_knn:
@@ -366,7 +366,7 @@ class CurveSAModule(nn.Module):
         else:
             idx, sptr_q = fps_sorted(pos, topo.sptr, self.ratio, draws)
         edges = ops.radius_1d_group(pos, topo, idx, self.r)
-        _, posq, batchq, curveq = _subset(None, pos, batch, point2curveidx, idx)
+        _, posq, batchq, curveq = _subset(None, pos, batch, point2curveidx, idx, cache)
         cache.put_sample_ptr(batchq, sptr_q)
         out = self.conv.forward_edges(x, pos, posq, edges, cache)
         return out, posq, batchq, curveq, None, idx

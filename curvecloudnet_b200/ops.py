@@ -385,8 +385,10 @@ def gather_i64(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def subset_gather(pos: torch.Tensor, batch: torch.Tensor, curve: Optional[torch.Tensor], idx: torch.Tensor):
-    """(pos[idx], batch[idx], curve[idx]) in one launch; curve may be None."""
+def subset_gather(pos: torch.Tensor, batch: torch.Tensor, curve: Optional[torch.Tensor], idx: torch.Tensor, npl: int = 0,
+                  cache=None):
+    """(pos[idx], batch[idx], curve[idx]) in one launch; curve may be None.  npl / cache: the activation planes of the new
+    position matrix are written by the same launch and registered in the forward cache."""
     pos, ldp = _rows(_f32(pos))
     batch, idx = _i64(batch), _i64(idx)
     n = idx.shape[0]
@@ -394,8 +396,12 @@ def subset_gather(pos: torch.Tensor, batch: torch.Tensor, curve: Optional[torch.
     batchq = _empty((n,), torch.int64, pos)
     curveq = _empty((n,), torch.int64, pos) if curve is not None else None
     if n:
+        pl = alloc_planes(n, 3, npl, pos) if npl and cache is not None else None
         call("ccn_subset_gather", pos, ldp, batch, _i64(curve) if curve is not None else 0, idx, n, posq, batchq,
-             curveq if curveq is not None else 0)
+             curveq if curveq is not None else 0, pl.buf if pl is not None else 0, pl.plane_stride if pl is not None else 0,
+             npl)
+        if pl is not None:
+            cache.put_planes(posq, pl)
     return posq, batchq, curveq
 
 

@@ -153,9 +153,11 @@ int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t* idx, int64
                         int64_t ldd, ccn_stream_t stream);
 int ccn_gather_i64(const int64_t* src, const int64_t* idx, int64_t n, int64_t* dst, ccn_stream_t stream);
 /* pos[idx], batch[idx], curve_idxs[idx] of a down-sampled level in one launch (src/models/modules/pointnet2.py:69-72,
- * 176-179); curve / curveq may be null. */
+ * 176-179); curve / curveq may be null.  pos_planes (optional): the activation planes of posq (n_planes x n x 16 bf16, xyz +
+ * zero columns; ccn_pack_planes layout) written by the same launch - positions are concatenated into the next MLP's input. */
 int ccn_subset_gather(const float* pos, int64_t ldp, const int64_t* batch, const int64_t* curve, const int64_t* idx,
-                      int64_t n, float* posq, int64_t* batchq, int64_t* curveq, ccn_stream_t stream);
+                      int64_t n, float* posq, int64_t* batchq, int64_t* curveq, void* pos_planes, int64_t plane_stride,
+                      int32_t n_planes, ccn_stream_t stream);
 int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int64_t nq, int32_t K, int32_t* erow, int32_t* ecol,
                      ccn_stream_t stream);
 int ccn_csr_rows(const int32_t* row_ptr, int64_t nq, int32_t* erow, ccn_stream_t stream);

@@ -102,3 +102,47 @@ def test_linear_over_concatenated_segments(widths, mode):
         assert cnn.cat_features(parts, cache=cache).segs[0] is a.segs[0]
     finally:
         cnn.set_precision(prev)
+
+
+def test_producers_write_planes_identical_to_pack():
+    """ccn_*_both / ccn_subset_gather(pos_planes): the planes a producer writes beside its fp32 result are bit-identical to
+    ccn_pack_planes of that result, and the fp32 result equals the plain entry point's."""
+    from curvecloudnet_b200 import ops
+    from curvecloudnet_b200.nn import ForwardCache
+    g = torch.Generator().manual_seed(21)
+    n, K, c = 3001, 9, 64
+    feat = torch.randn(n * (K + 1), c, generator=g).cuda()
+    idx = torch.randint(-1, n, (n, K), generator=g, dtype=torch.int32).cuda()
+    for npl in (1, 2):
+        cache = ForwardCache()
+        a, b = ops.group_max_dense(feat, idx), ops.group_max_dense(feat, idx, npl, cache)
+        assert torch.equal(a, b) and len(cache.planes) == 1
+        assert torch.equal(cache.planes_for(b, npl).buf, ops.pack_planes([a], npl).buf)
+        # segmented aggregation (max and attention) over a ragged CSR
+        cnt = torch.randint(0, 12, (n,), generator=g)
+        row_ptr = torch.cat([torch.zeros(1, dtype=torch.int64), torch.cumsum(cnt, 0)]).to(torch.int32).cuda()
+        E = int(cnt.sum())
+        msg, att = torch.randn(E, c, generator=g).cuda(), torch.randn(E, c, generator=g).cuda()
+        for mode, at in (("max", None), ("attend", att), ("mean", None)):
+            cache = ForwardCache()
+            a, b = ops.seg_aggregate(msg, at, row_ptr, n, mode), ops.seg_aggregate(msg, at, row_ptr, n, mode, npl, cache)
+            assert torch.equal(a, b) and len(cache.planes) == 1
+            assert torch.equal(cache.planes_for(b, npl).buf, ops.pack_planes([a], npl).buf)
+        # interpolation
+        x = torch.randn(700, c, generator=g).cuda()
+        nbr = torch.randint(0, 700, (n, 3), generator=g, dtype=torch.int32).cuda()
+        d2 = torch.rand(n, 3, generator=g).cuda()
+        cache = ForwardCache()
+        a, b = ops.interp_blend(x, nbr, d2, True), ops.interp_blend(x, nbr, d2, True, npl, cache)
+        assert torch.equal(a, b) and torch.equal(cache.planes_for(b, npl).buf, ops.pack_planes([a], npl).buf)
+        # positions of a down-sampled level
+        pos = torch.randn(n, 3, generator=g).cuda()
+        batch = torch.zeros(n, dtype=torch.int64).cuda()
+        sel = torch.arange(0, n, 3).cuda()
+        cache = ForwardCache()
+        pq, _, _ = ops.subset_gather(pos, batch, None, sel, npl, cache)
+        assert torch.equal(pq, pos[sel]) and torch.equal(cache.planes_for(pq, npl).buf, ops.pack_planes([pq], npl).buf)
+    # widths the float4 / 16-column planes path does not cover fall back to the plain kernel and register nothing
+    cache = ForwardCache()
+    odd = torch.randn(n * (K + 1), 24, generator=g).cuda()
+    assert torch.equal(ops.group_max_dense(odd, idx, 2, cache), ops.group_max_dense(odd, idx)) and not cache.planes
