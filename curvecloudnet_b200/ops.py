@@ -203,7 +203,7 @@ def curve_fps(pos: torch.Tensor, topo: CurveTopology, arclen: float, u: torch.Te
     """CurveFPS.forward -> (idx int64 ascending, sample ptr of the kept points)."""
     pos = _f32(pos)
     n = pos.shape[0]
-    run = _empty((max(n, 1),), torch.float32, pos)
+    run = _empty((max(n, 1) + (n + 4095) // 4096,), torch.float32, pos)   # running arclength + per-tile counts
     idx = _empty((max(n, 1),), torch.int64, pos)
     cnt = _empty((1,), torch.int32, pos)
     u = u.to(device=pos.device, dtype=torch.float32).reshape(1)

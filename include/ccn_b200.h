@@ -93,7 +93,7 @@ int ccn_curve_conv_layer(const float* in, int64_t ld_in, const float* w, const f
 
 /* ---- sampling / grouping along curves --------------------------------------------------------------
  * curve_fps: CurveFPS.forward (src/models/modules/fps_ops.py:16-39); u = the torch.rand(1) draw (:30);
- *            idx_out ascending (capacity n), *count_out = number kept; run_scratch n floats.
+ *            idx_out ascending (capacity n), *count_out = number kept; run_scratch n + ceil(n / 4096) floats.
  * radius_1d_group_{count,fill}: radius_1d_group_subset (point_ops.py:143-193) as CSR over queries:
  *            count writes row_ptr[0..nq] and *total_out = E; fill writes col[E] (point indices, in the
  *            reference's candidate order 0,-1,+1,...).  kc_scratch n_curves floats, stats_scratch 2 ints.
