@@ -523,4 +523,13 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    # stdout carries the JSON line and nothing else: NCCL writes its version banner to fd 1 from C, so fd 1 is pointed at stderr
+    # for the run and the real stdout is kept aside for the line(s) main() prints.
+    sys.stdout.flush()
+    _real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = _real
+    try:
+        main()
+    finally:
+        _real.flush()
