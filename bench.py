@@ -34,7 +34,6 @@ import torch  # noqa: E402
 
 METRIC = "points/sec fwd seg (nuScenes-shape CurveCloudNet)"
 WORKLOAD = "nuScenes-shape CurveCloudNet segmentation forward, 32-beam synthetic scan, B=1 scan/step"
-CPU_SAMPLE_POINTS = 8000
 
 
 def _peaks():
@@ -113,42 +112,103 @@ class ClockSampler:
                 "reasons": sorted(reasons)}
 
 
-def cpu_reference_points_per_s(sample_points, iters, warmup, threads):
-    """Times the CPU oracle (port of the reference) on a bounded azimuth sector of the same scan."""
+def _cpu_model():
     from curvecloudnet_b200.configs import build_model
-    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from curvecloudnet_b200.synthetic import randomize_model_
     from oracle.ccn_model import ModelBase as OracleModel
-    torch.set_num_threads(threads)
-    data = driving_scan_batch([0], subsample=sample_points)
     model = build_model(OracleModel, "nuscenes")
     randomize_model_(model, 1234)
-    model.eval()
-    n = data.pos.shape[0]
-    times = []
+    return model.eval()
+
+
+def cpu_reference_run(scans, steps, warmup, threads, budget_s=None):
+    """Times the CPU oracle (port of the reference; its neighbour searches are the grid-pruned C statement
+    oracle/nbr_search.c, multi-threaded) on the SAME scans, cycled in the same order with the same per-step seeds as
+    the GPU arm.  A 256 MiB host buffer is written between the timed steps (the CPU-side counterpart of the L2 flush).
+    -> (points/s, mean points per step, seconds per step, timed steps)."""
+    torch.set_num_threads(threads)
+    model = _cpu_model()
+    flush = torch.empty(256 << 20, dtype=torch.uint8)
+    times, npts = [], 0
+    t_begin = time.perf_counter()
     with torch.no_grad():
-        for i in range(warmup + iters):
-            torch.manual_seed(i)
+        for i in range(-warmup, steps):
+            flush.zero_()
+            data = scans[(i if i >= 0 else i + warmup) % len(scans)]
+            torch.manual_seed(max(i, 0))
             t0 = time.perf_counter()
             model(data)
             dt = time.perf_counter() - t0
-            if i >= warmup:
+            if i >= 0:
                 times.append(dt)
+                npts += data.pos.shape[0]
+                if budget_s is not None and time.perf_counter() - t_begin > budget_s and len(times) >= 3:
+                    break
     total = sum(times)
-    return n * len(times) / total, n, total / len(times)
+    return npts / total, npts / len(times), total / len(times), len(times)
+
+
+def cpu_frnn_bruteforce_points_per_s(scan, K=20, radius=0.04, max_queries=4096):
+    """the reference's own FRNNBruteForceCPU (third_party/FRNN/frnn/csrc/bruteforce/
+    bruteforce_cpu.cpp:5-58, compiled from the reference tree into oracle/_ref/) on the scan's level-0 self-query -
+    the one piece of the reference's neighbour search that exists as CPU code.  Single-threaded O(P1*P2) upstream;
+    timed on a bounded number of queries against the full cloud.  None if the library was not built."""
+    import ctypes
+    so = os.path.join(ROOT, "oracle", "_ref", "libref_frnn_bf.so")
+    if not os.path.exists(so):
+        return None
+    try:
+        lib = ctypes.CDLL(so)
+        vp = ctypes.c_void_p
+        lib.ref_frnn_bruteforce_cpu.argtypes = [vp, vp, vp, vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int,
+                                                ctypes.c_float, vp, vp]
+        pos = scan.pos.contiguous()
+        nq = min(max_queries, pos.shape[0])
+        p1 = pos[:nq].contiguous()
+        l1, l2 = torch.tensor([nq]), torch.tensor([pos.shape[0]])
+        idx = torch.empty((1, nq, K), dtype=torch.int64)
+        d = torch.empty((1, nq, K), dtype=torch.float32)
+        t0 = time.perf_counter()
+        rc = lib.ref_frnn_bruteforce_cpu(p1.data_ptr(), pos.data_ptr(), l1.data_ptr(), l2.data_ptr(), 1, nq, pos.shape[0], K,
+                                         float(radius), idx.data_ptr(), d.data_ptr())
+        dt = time.perf_counter() - t0
+        if rc != 0:
+            return None
+    except Exception:
+        return None
+    return {"queries_per_s": nq / dt, "queries": nq, "sources": int(pos.shape[0]), "K": K, "radius": radius,
+            "seconds": dt, "kind": "reference (FRNNBruteForceCPU compiled from the reference tree), 1 thread"}
+
+
+def _rank0_scans(rank, n_scans, batch=1):
+    from curvecloudnet_b200.synthetic import driving_scan_batch
+    return [driving_scan_batch([1000 * rank + batch * s + b for b in range(batch)]) for s in range(n_scans)]
+
+
+def _config(mean_pts, batch, n_scans, world):
+    """The `config` object of BOTH arms (the reference arm runs the same scans in the same order)."""
+    return {"workload": WORKLOAD.replace("B=1", "B=%d" % batch), "points_per_step": mean_pts, "scans_per_step": batch,
+            "distinct_batches_per_rank": n_scans, "parallelism": "scan-sharded dp%d, no collective" % world,
+            "l2": "256 MiB buffer written between timed steps (cache flush)"}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     threads = os.cpu_count() or 1
-    steps, warmup = max(args.steps, 1), max(min(args.warmup, 2), 1)
-    pps, n, sec = cpu_reference_points_per_s(CPU_SAMPLE_POINTS, steps, warmup, threads)
-    sample = "oracle port on a %d-point azimuth sector of scan seed 0 per step, %d threads" % (n, threads)
+    steps, warmup = max(args.steps, 1), max(args.warmup, 3)
+    scans = _rank0_scans(0, args.scans, args.batch)
+    # the whole run must end within a few minutes: past 8 minutes of CPU work the timed steps stop early (>= 3 kept)
+    # and the line reports the number of steps actually timed
+    pps, mean_pts, sec, done = cpu_reference_run(scans, steps, warmup, threads, budget_s=480.0)
+    sample = ("oracle port (plain-torch restatement of the reference; grid-pruned C neighbour search), the same %d full scans "
+              "cycled as the GPU arm, %d threads" % (len(scans), threads))
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": pps, "unit": "points/s", "n_gpus": args.gpus, "steps": steps,
+        "impl": "reference", "metric": METRIC, "value": pps, "unit": "points/s", "n_gpus": args.gpus, "steps": done,
         "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
+        "dtype": "f32", "data": "synthetic", "config": _config(mean_pts, args.batch, args.scans, world),
         "cpu_baseline": {"value": pps, "unit": "points/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": pps, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -391,8 +451,7 @@ def main():
     randomize_model_(model, 1234)
     model = model.cuda().eval()
     lin_name = "ccn_linear_f32" if args.precision == "fp32" else "ccn_linear_planes"
-    host_scans = [driving_scan_batch([1000 * rank + args.batch * s + b for b in range(args.batch)]).pin_memory()
-                  for s in range(args.scans)]
+    host_scans = [s.pin_memory() for s in _rank0_scans(rank, args.scans, args.batch)]
     dev_scans = [s.to("cuda") for s in host_scans]
     pts = [s.num_points for s in host_scans]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
@@ -482,10 +541,7 @@ def main():
         "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (split-bf16 tensor-core MLPs, fp32-class accuracy; all else f32)",
                   "bf16": "bf16 (tensor-core MLPs, fp32 accumulate; all else f32)"}[args.precision],
         "data": "synthetic", "scans_per_s": (K * world * args.batch) / (ms_max * 1e-3),
-        "config": {"workload": WORKLOAD.replace("B=1", "B=%d" % args.batch), "points_per_step": mean_pts,
-                   "scans_per_step": args.batch, "distinct_batches_per_rank": args.scans,
-                   "parallelism": "scan-sharded dp%d, no collective" % world,
-                   "l2": "256 MiB buffer written between timed steps (L2 flush)"},
+        "config": _config(mean_pts, args.batch, args.scans, world),
         "e2e": {"value": tot_pts_e2e / (ms_e2e_max * 1e-3), "unit": "points/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e_max / K},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks,
@@ -513,10 +569,16 @@ def main():
                                    "ms_per_scan": tot_ms / (8 * B6), "steps": 8, "warmup": 3}
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        pps, n, sec = cpu_reference_points_per_s(CPU_SAMPLE_POINTS, 3, 1, threads)
+        # bounded sample of the SAME workload: the full seed-0 scan (the first scan of the timed cycle), 1 warm-up + 3 timed
+        # forwards of the oracle port on all host threads
+        scan0 = _rank0_scans(0, 1)
+        pps, n, sec, done = cpu_reference_run(scan0, 3, 1, threads)
         line["cpu_baseline"] = {"value": pps, "unit": "points/s", "cores": threads, "kind": "port",
-                                "sample": "oracle port, %d-point azimuth sector of scan seed 0, 3 timed forwards, %.2f s each"
-                                          % (n, sec)}
+                                "sample": "oracle port (grid-pruned C neighbour search), the full %d-point seed-0 scan, %d timed "
+                                          "forwards, %.2f s each" % (int(n), done, sec)}
+        bf = cpu_frnn_bruteforce_points_per_s(scan0[0])
+        if bf is not None:
+            line["cpu_baseline"]["frnn_bruteforce_cpu"] = bf
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

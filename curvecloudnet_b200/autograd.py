@@ -159,12 +159,20 @@ class _BNAct(Function):
             if batch_stats:
                 mean, invstd = _empty((C,), z), _empty((C,), z)
                 sums = _empty((2 * C,), z, torch.float64)
-                mom = bn.momentum if bn.momentum is not None else 0.1
                 track = bn.track_running_stats and bn.running_mean is not None
+                if bn.momentum is None and track:
+                    # torch's cumulative moving average (momentum=None -> 1 / num_batches_tracked) is not built
+                    raise NotImplementedError("BatchNorm1d(momentum=None) (cumulative moving average) is not supported")
+                mom = bn.momentum if bn.momentum is not None else 0.0
                 call("ccn_bn_stats", z, ldz, M, C, float(bn.eps), float(mom), sums, mean, invstd,
                      bn.running_mean if track else 0, bn.running_var if track else 0)
-                if track and bn.num_batches_tracked is not None:
-                    bn.num_batches_tracked.add_(1)
+                if track:
+                    # the kernel updated the running statistics through raw pointers: bump their version counters so that
+                    # the folded-weight caches (nn.MLP._key, modules._CurveConvBase._layers) see the change
+                    torch.autograd.graph.increment_version(bn.running_mean)
+                    torch.autograd.graph.increment_version(bn.running_var)
+                    if bn.num_batches_tracked is not None:
+                        bn.num_batches_tracked.add_(1)
             else:
                 mean = bn.running_mean
                 invstd = torch.rsqrt(bn.running_var + bn.eps)           # C values: weight preparation

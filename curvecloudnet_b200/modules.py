@@ -67,13 +67,14 @@ class _CurveConvBase(nn.Module):
     def _layers(self):
         """[(w (k, C_in, C_out), b (C_out))]: mirrored kernel with BatchNorm(eval) folded."""
         if self.training:
-            raise NotImplementedError("curvecloudnet_b200 round 1 implements the inference (eval) path")
+            raise RuntimeError("_layers() is the folded inference form; training goes through train_steps.curve_conv_*")
         from . import nn as _nn
         epoch = _nn._EPOCH[0]
         if epoch is not None and self._folded is not None and self._folded_epoch == epoch:
             return self._folded
         self._folded_epoch = epoch
-        key = tuple(c.weight._version + n.weight._version + n.running_mean._version + n.running_var._version
+        key = tuple(c.weight._version + n.weight._version + n.bias._version + n.running_mean._version + n.running_var._version +
+                    (c.bias._version if c.bias is not None else 0)
                     for c, n in zip(self.conv_modules, self.norm_modules)) + (self.conv_modules[0].weight.data_ptr(),)
         if self._folded is None or key != self._folded_key:
             out = []

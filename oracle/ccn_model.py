@@ -119,6 +119,7 @@ class ModelBase(torch.nn.Module):
             data = Batch.from_data_list(data)
         if draws is not None:
             kwargs["draws"] = draws
+        trace = kwargs.pop("trace", None)     # test hook: list receiving every step's (name, x, pos, batch, curve, down_idx)
         cur = (data.x, data.pos, data.batch, data.curve_idxs)
         hist = {"x": [data.x], "pos": [data.pos], "batch": [data.batch], "curve": [data.curve_idxs.clone()]}
         down_idx, prop_stack, down_stack = [], [], []
@@ -150,6 +151,8 @@ class ModelBase(torch.nn.Module):
             hist["x"].append(out[0]); hist["pos"].append(out[1])
             hist["batch"].append(out[2]); hist["curve"].append(out[3])
             down_idx.append(out[5] if len(out) > 5 else None)
+            if trace is not None:
+                trace.append((name, out[0], out[1], out[2], out[3], down_idx[-1]))
             if name in self.skip_connect_state_store:
                 prop_stack.append(i)
             if name in _DOWN_STEPS:

@@ -16,6 +16,57 @@ import torch
 
 _I64_MAX = torch.iinfo(torch.int64).max
 
+# ----------------------------------------------------------------------------------
+# C restatement of the neighbour queries (oracle/nbr_search.c, built by oracle/Makefile into
+# oracle/_build/liboracle_nbr.so): same result contract as the torch statements below, a cell grid
+# prunes the candidates so that full-size scans finish in seconds.  SEARCH_IMPL = "torch" forces the
+# O(P1*P2) torch statements (tests/test_oracle_numerics.py compares the two).
+# ----------------------------------------------------------------------------------
+SEARCH_IMPL = "auto"        # "auto" (C when built) | "c" | "torch"
+_nbr_lib = None
+
+
+def _nbr():
+    global _nbr_lib
+    if SEARCH_IMPL == "torch":
+        return None
+    if _nbr_lib is None:
+        import ctypes
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_build", "liboracle_nbr.so")
+        if not os.path.exists(path):
+            if SEARCH_IMPL == "c":
+                raise RuntimeError("%s not built (make -C oracle)" % path)
+            _nbr_lib = False
+        else:
+            lib = ctypes.CDLL(path)
+            P, Q, I, F = ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_float
+            lib.oracle_frnn.argtypes = [P, Q, P, Q, I, F, P, P, I]
+            lib.oracle_ball.argtypes = [P, Q, P, Q, I, F, P, I]
+            lib.oracle_knn.argtypes = [P, Q, P, Q, I, P, P, I]
+            _nbr_lib = lib
+    return _nbr_lib or None
+
+
+def _c_search(kind, q, pts, K, r=0.0):
+    """One cloud through nbr_search.c -> (idx int64 (n1,K) -1 padded, d2 f32 (n1,K) -1 padded | None)."""
+    lib = _nbr()
+    q = q.contiguous().float()
+    pts = pts.contiguous().float()
+    n1, n2 = q.shape[0], pts.shape[0]
+    idx = torch.empty((n1, K), dtype=torch.int64)
+    d2 = torch.empty((n1, K), dtype=torch.float32) if kind != "ball" else None
+    th = max(1, torch.get_num_threads())
+    if kind == "frnn":
+        rc = lib.oracle_frnn(q.data_ptr(), n1, pts.data_ptr(), n2, K, float(r), idx.data_ptr(), d2.data_ptr(), th)
+    elif kind == "ball":
+        rc = lib.oracle_ball(q.data_ptr(), n1, pts.data_ptr(), n2, K, float(r), idx.data_ptr(), th)
+    else:
+        rc = lib.oracle_knn(q.data_ptr(), n1, pts.data_ptr(), n2, K, idx.data_ptr(), d2.data_ptr(), th)
+    if rc:
+        raise RuntimeError("oracle nbr_search: error %d" % rc)
+    return idx, d2
+
 
 # ----------------------------------------------------------------------------------
 # helpers
@@ -111,6 +162,9 @@ def ball_query(p1, p2, lengths1, lengths2, K, radius):
         l1, l2 = int(lengths1[n]), int(lengths2[n])
         if l1 == 0 or l2 == 0:
             continue
+        if p1.shape[-1] == 3 and _nbr() is not None:
+            out[n, :l1] = _c_search("ball", p1[n, :l1], p2[n, :l2], K, float(torch.tensor(radius, dtype=torch.float32)))[0]
+            continue
         for s in range(0, l1, 2048):
             q = p1[n, s:min(s + 2048, l1)]
             inside = sqdist3(q[:, None, :], p2[n, None, :l2, :]) < r2
@@ -134,6 +188,11 @@ def knn_points(p1, p2, lengths1, lengths2, K):
     for n in range(N):
         l1, l2 = int(lengths1[n]), int(lengths2[n])
         if l1 == 0 or l2 == 0:
+            continue
+        if p1.shape[-1] == 3 and _nbr() is not None:
+            cols, dd = _c_search("knn", p1[n, :l1], p2[n, :l2], K)
+            idx[n, :l1] = torch.where(cols >= 0, cols, torch.zeros_like(cols))
+            dists[n, :l1] = torch.where(cols >= 0, dd, torch.zeros_like(dd))
             continue
         for s in range(0, l1, 2048):
             e = min(s + 2048, l1)
@@ -168,6 +227,9 @@ def frnn_grid_points(points1, points2, lengths1, lengths2, K, r):
         if l1 == 0 or l2 == 0:
             continue
         r2 = r[n] * r[n]
+        if points1.shape[-1] == 3 and _nbr() is not None:
+            idx[n, :l1], dists[n, :l1] = _c_search("frnn", points1[n, :l1], points2[n, :l2], K, float(r[n]))
+            continue
         for s in range(0, l1, 2048):
             e = min(s + 2048, l1)
             d2 = _sqdist(points1[n, s:e, None, :], points2[n, None, :l2, :])

@@ -1,0 +1,149 @@
+"""Full-size parity AGAINST THE CPU ORACLE (VERDICT r01 "next round" item 1): the configurations BASELINE.json quotes
+are run once through oracle/ (whose neighbour searches go through the grid-pruned C statement oracle/nbr_search.c, so
+that a 32.5 k-point scan takes seconds) and compared with the CUDA path STEP BY STEP:
+
+  * every index decision bit-exact: the level's positions / batch / curve ids after every down-sampling step (equal
+    positions <=> equal CurveFPS / VoxelFPS / FPS index sets, the clouds have no duplicate points), the sa-geo
+    down-sampling indices themselves, and - op by op on the oracle's own levels - the FRNN tables, the exact 3-NN
+    tables, the 1-D curve groupings (reference quirks at full size: point_ops.py:185 local-vs-global curve id,
+    :63 f32 ceil(len*ratio), find_nbrs.cu:490 `<=`, knn_points zero fill point_ops.py:101);
+  * features after every step and the logits within the north_star tolerance of the precision mode
+    (1e-4 fp32 / bf16x3, 2e-2 bf16; relative to the largest magnitude of the oracle's tensor).
+
+Cases: the seed-0 nuScenes-shape scan bench.py times (configs[3]), a KITTI-shape 64-beam scan (configs[4] forward),
+ShapeNet-seg B=16 x 2048 (configs[1]) and Kortx B=64 x 2048 (configs[2])."""
+import pytest
+import torch
+
+from golden_utils import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 1e-4, "bf16x3": 1e-4, "bf16": 2e-2}
+
+
+def _data(case):
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch
+    if case == "nuscenes":
+        return "nuscenes", driving_scan_batch([0])                 # the scan bench.py's rank 0 times first
+    if case == "kitti":
+        return "kitti", driving_scan_batch([2], kind="kitti")
+    if case == "shapenet-seg":
+        d = object_scan_batch(list(range(16)))
+        d.labels = torch.arange(16) % 16
+        return "shapenet-seg", d
+    if case == "kortx":
+        return "kortx", object_scan_batch(list(range(64)))
+    raise KeyError(case)
+
+
+_oracle_cache = {}
+
+
+def _oracle(case):
+    """(config name, data, oracle trace, oracle logits, oracle model state_dict) - computed once per case."""
+    if case not in _oracle_cache:
+        from curvecloudnet_b200.configs import build_model
+        from curvecloudnet_b200.synthetic import randomize_model_
+        from oracle.ccn_model import ModelBase as OracleModel
+        cfg, data = _data(case)
+        model = randomize_model_(build_model(OracleModel, cfg), 1234).eval()
+        trace = []
+        torch.manual_seed(11)
+        with torch.no_grad():
+            logits = model(data, trace=trace)
+        _oracle_cache[case] = (cfg, data, trace, logits, model.state_dict())
+    return _oracle_cache[case]
+
+
+CASES = ["nuscenes", "shapenet-seg", "kortx", "kitti"]
+
+
+@pytest.mark.parametrize("precision", list(TOL))
+@pytest.mark.parametrize("case", CASES)
+def test_forward_matches_oracle_step_by_step(case, precision):
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    cfg, data, want, want_logits, state = _oracle(case)
+    model = build_model(ModelBase, cfg, precision=precision)
+    model.load_state_dict(state, strict=True)
+    model = model.cuda().eval()
+    got = []
+    torch.manual_seed(11)
+    with torch.no_grad():
+        logits = model(data.to("cuda"), trace=got)
+    assert len(got) == len(want)
+    tol = TOL[precision]
+    worst = 0.0
+    for i, (g, w) in enumerate(zip(got, want)):
+        name = w[0]
+        assert g[0] == name
+        # index decisions: the level itself
+        assert torch.equal(g[2].cpu(), w[2]), "step %d (%s): positions differ - a sampler picked other points" % (i, name)
+        assert torch.equal(g[3].cpu(), w[3]), "step %d (%s): batch vector differs" % (i, name)
+        if w[4] is not None:
+            assert torch.equal(g[4].cpu(), w[4]), "step %d (%s): curve ids differ" % (i, name)
+        if w[5] is not None:
+            assert torch.equal(g[5].cpu(), w[5]), "step %d (%s): down-sampling indices differ" % (i, name)
+        if w[1] is not None:
+            assert g[1].shape == w[1].shape, (i, name, g[1].shape, w[1].shape)
+            e = rel_err(g[1].cpu(), w[1])
+            worst = max(worst, e)
+            assert e <= tol, "step %d (%s): features off by %.3e relative (%s)" % (i, name, e, precision)
+    e = rel_err(logits.cpu(), want_logits)
+    print("%s %s: logits rel err %.3e, worst step %.3e, %d points" % (case, precision, e, worst, data.pos.shape[0]))
+    assert logits.shape == want_logits.shape and e <= tol
+
+
+def _levels(trace, data):
+    """Distinct (pos, batch, curve) levels of a forward, finest first."""
+    out = [(data.pos, data.batch, data.curve_idxs)]
+    for t in trace:
+        if t[2].shape[0] != out[-1][0].shape[0] and all(t[2].shape[0] != o[0].shape[0] for o in out):
+            out.append((t[2], t[3], t[4]))
+    return out
+
+
+@pytest.mark.parametrize("case", ["nuscenes", "kitti"])
+def test_neighbour_tables_match_oracle_at_full_size(case):
+    """Every neighbour query of the step list, on the oracle's own levels, bit-exact: FRNN self-queries (sgcnn, K=20) and
+    cross-level queries (sa, K=32) with the config's radii, exact 3-NN (fp), the 1-D curve groupings (sa-geo / fp-geo)."""
+    from curvecloudnet_b200 import point_ops as po
+    from curvecloudnet_b200.configs import MODEL_CONFIGS
+    from oracle import ccn_point_ops as opo
+    cfg, data, trace, _, _ = _oracle(case)
+    lv = _levels(trace, data)
+    assert len(lv) == 6
+    conf = MODEL_CONFIGS[cfg][0]()
+    radii, steps = conf["radii"], [s if isinstance(s, str) else s["step_name"] for s in conf["steps"]]
+    dev = lambda t: t.cuda()
+    # sgcnn self-queries: (level, radius) pairs of the encoder (steps 3, 6, 9, 12, 15)
+    sg = [i for i, s in enumerate(steps) if s == "sgcnn"][:5]
+    for l, i in enumerate(sg, start=1):
+        pos, batch = lv[l][0], lv[l][1]
+        want, _, _ = opo.knn_ball_group(pos, pos, batch, batch, "knn", radius=radii[i], knn=20, return_dense=True)
+        got, _, _ = po.knn_ball_group_pytorch3d(dev(pos), dev(pos), dev(batch), dev(batch), "knn", radius=radii[i], knn=20,
+                                                return_dense=True)
+        assert torch.equal(got.cpu(), want), "FRNN self-query of level %d (r=%g)" % (l, radii[i])
+    # sa cross-level queries (steps 5, 8, 11, 14): queries = level l+1, sources = level l
+    sa = [i for i, s in enumerate(steps) if s == "sa"]
+    for l, i in enumerate(sa, start=1):
+        (p2, b2, _), (p1, b1, _) = lv[l], lv[l + 1]
+        want = opo.knn_ball_group(p1, p2, b1, b2, "knn", radius=radii[i], knn=32)
+        got = po.knn_ball_group_pytorch3d(dev(p1), dev(p2), dev(b1), dev(b2), "knn", radius=radii[i], knn=32)
+        assert torch.equal(got[0].cpu(), want[0]) and torch.equal(got[1].cpu(), want[1]), "FRNN sa query %d" % l
+    # fp: exact 3-NN of every fine point among the coarse level (no radius, zero fill)
+    for l in range(1, 5):
+        (pf, bf, _), (pc, bc, _) = lv[l], lv[l + 1]
+        want = opo.knn_ball_group(pf, pc, bf, bc, "knn", knn=3, accel_knn=False)
+        got = po.knn_ball_group_pytorch3d(dev(pf), dev(pc), dev(bf), dev(bc), "knn", knn=3, accel_knn=False)
+        assert torch.equal(got[0].cpu(), want[0]) and torch.equal(got[1].cpu(), want[1]), "exact 3-NN %d -> %d" % (l + 1, l)
+    # 1-D groupings along the curves: sa-geo's edge list and fp-geo's candidate set, with the sa-geo indices of the trace
+    idx = next(t[5] for t in trace if t[0] == "sa-geo")
+    pos, batch, curve = lv[0]
+    want = opo.radius_1d_group_subset(pos, idx, curve, batch, radii[1])
+    got = po.radius_1d_group_subset(dev(pos), dev(idx), dev(curve), dev(batch), radii[1])
+    assert torch.equal(got[0].cpu(), want[0]) and torch.equal(got[1].cpu(), want[1])
+    want = opo.knn_1d_group_superset(pos, idx, curve, batch, 3)
+    got = po.knn_1d_group_superset(dev(pos), dev(idx), dev(curve), dev(batch), 3)
+    assert torch.equal(got[0].cpu(), want[0]) and torch.equal(got[1].cpu(), want[1])

@@ -483,3 +483,32 @@ def test_training_step_matches_reference_golden(name, mode, precision):
         # path counts the padding rows of to_batch_padded (logits are off by 0.57 without them).
         check_train_golden(model, logits, loss, g[mode], 2e-2 if precision == "fp32" else 1e-1, 1.5,
                            "%s %s %s" % (name, mode, precision))
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+def test_eval_after_train_forward_refolds_batchnorm(precision):
+    """a train-mode forward updates the BatchNorm running statistics through raw device pointers; the
+    next eval forward must re-fold them even when NO weight changed in between (frozen layers, BN recalibration under
+    no_grad): eval -> train forward without an optimiser step -> eval equals a fresh model loaded from the state_dict."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
+    data = object_scan_batch([0, 1]).to(DEV)
+    model = randomize_model_(build_model(ModelBase, "shapenet-class", precision=precision), 1234).cuda().eval()
+    with torch.no_grad():
+        torch.manual_seed(3)
+        before = model(data)
+        model.train()
+        torch.manual_seed(4)
+        model(data)                                   # updates running_mean / running_var, no optimiser step
+        model.eval()
+        torch.manual_seed(3)
+        after = model(data)
+    fresh = build_model(ModelBase, "shapenet-class", precision=precision)
+    fresh.load_state_dict(model.state_dict(), strict=True)
+    fresh = fresh.cuda().eval()
+    with torch.no_grad():
+        torch.manual_seed(3)
+        want = fresh(data)
+    assert not torch.equal(before, after), "the train-mode forward did not change the running statistics"
+    assert torch.equal(after, want), "stale folded BatchNorm: eval after a train forward differs from a fresh fold"
