@@ -95,3 +95,47 @@ def test_scatter_semantics():
     assert tp.scatter_mean(src, index, 0, None, 3).flatten().tolist() == [-0.5, 0.0, 5.0]
     sm = tp.segment_softmax(torch.tensor([[0.0], [1.0], [1.0], [0.0]]), index)
     assert torch.allclose(sm.flatten(), torch.tensor([0.5, 0.5, 0.5, 0.5]))
+
+
+def test_c_neighbour_search_equals_the_torch_statements():
+    """oracle/nbr_search.c (grid-pruned, multi-threaded) against the O(P1*P2) torch statements of tp_ops it accelerates:
+    FRNN (d2 <= r2, (d2, idx) order), ball_query (first K by index, strict), knn_points (exact, zero fill) - bit-exact,
+    incl. duplicate points, quantised coordinates (distance ties), queries outside the cloud and K > cloud size."""
+    import os
+    from oracle import tp_ops
+    so = os.path.join(os.path.dirname(os.path.abspath(tp_ops.__file__)), "_build", "liboracle_nbr.so")
+    if not os.path.exists(so):
+        pytest.skip("oracle/_build/liboracle_nbr.so not built (make -C oracle)")
+    gen = torch.Generator().manual_seed(0)
+
+    def both(fn, *a):
+        prev = tp_ops.SEARCH_IMPL
+        try:
+            tp_ops.SEARCH_IMPL = "torch"
+            x = fn(*a)
+            tp_ops.SEARCH_IMPL = "c"
+            y = fn(*a)
+        finally:
+            tp_ops.SEARCH_IMPL = prev
+        return x, y
+
+    for trial in range(4):
+        n1, n2 = 700, 1500
+        p2 = torch.rand(1, n2, 3, generator=gen) * torch.tensor([4.0, 4.0, 0.5])
+        p2[0, 100:200] = p2[0, 0:100]
+        if trial % 2:
+            p2 = (p2 * 32).round() / 32
+        p1 = p2[:, :n1].clone() if trial < 2 else torch.rand(1, n1, 3, generator=gen) * 5 - 0.5
+        l1, l2 = torch.tensor([n1]), torch.tensor([n2])
+        for K, r in ((20, 0.1), (32, 0.3), (5, 0.01)):
+            a, b = both(tp_ops.frnn_grid_points, p1, p2, l1, l2, K, r)
+            assert torch.equal(a[1], b[1]) and torch.equal(a[0], b[0]), (trial, K, r)
+        for K in (3, 20):
+            a, b = both(tp_ops.knn_points, p1, p2, l1, l2, K)
+            assert torch.equal(a[1], b[1]) and torch.equal(a[0], b[0]), (trial, K)
+        for K, r in ((128, 0.3), (16, 0.2)):
+            a, b = both(tp_ops.ball_query, p1, p2, l1, l2, K, r)
+            assert torch.equal(a, b), (trial, K, r)
+    p2, p1 = torch.rand(1, 2, 3, generator=gen), torch.rand(1, 5, 3, generator=gen)
+    a, b = both(tp_ops.knn_points, p1, p2, torch.tensor([5]), torch.tensor([2]), 3)
+    assert torch.equal(a[1], b[1]) and torch.equal(a[0], b[0])
