@@ -1,0 +1,596 @@
+// One kernel per edge-MLP step: gather -> layer 1 (decomposed) -> layers 2..n -> max / mean / attention aggregate, the
+// per-edge intermediates never leave the SM (sm_100a only; north_star (f)).
+//
+//   ccn_sgcnn_fused      StaticEdgeConv.forward_fast (reference src/models/modules/dgcnn.py:158-207): rows (i, g) of the
+//                        dense K+1 neighbour table, layer 1 = act(P[j] + Q[i]) from the per-POINT products PQ, the remaining
+//                        layers of `nn`, max over the K+1 rows with missing neighbours at -100 (dgcnn.py:187-189).
+//   ccn_pointconv_fused  PointNetConv2.message/aggregate (src/models/modules/point_conv.py:60-93) and the sparse
+//                        StaticEdgeConv.forward_slow (dgcnn.py:209-246) over a target-sorted CSR edge list: layer 1 =
+//                        act(H[j] + Wp (pos_j - pos_i)/r + b) or act(P[j] + Q[i]), the remaining layers of local_nn, then
+//                        max | mean | sum sigmoid(att) msg | sum softmax_target(att) msg with att = attend_nn(msg) - the two
+//                        attention layers run in the same kernel, msg stays in TMEM meanwhile.
+//
+// Before: layer-1 kernel (writes E x C planes) -> one ccn_linear_planes launch per layer (reads and re-writes E x C) ->
+// aggregation kernel (reads E x C again): ~585 MB through L2/HBM for the 374 k-row level-1 SGCNN step against ~11 MB of
+// compulsory bytes (N x C in, N x C out, the neighbour table, the weights).  Here a CTA owns a tile of <= 128 edge rows
+// that are WHOLE neighbour groups (6 groups of K+1 = 21 rows, or the CSR segments whose first edge falls into a stride
+// of S = 129 - maxdeg rows):
+//   warps 2-5 (128 threads)  form the layer-1 rows straight into the SWIZZLE_128B K-major A tile in shared memory as
+//                            bf16 (hi, lo) planes; after every layer read the fp32 accumulator from TMEM (tcgen05.ld),
+//                            add the folded-BatchNorm bias, apply the activation, split to bf16 (hi, lo) and store it IN
+//                            PLACE as the next layer's A operand; after the last layer transpose 32-column chunks
+//                            through shared memory and reduce every neighbour group / CSR segment in edge order.
+//   warp 0 lane 0            TMA producer: streams the weight tiles (<= 128 output rows x 64 k, hi [+ lo]) of all layers
+//                            through a ring, running ahead across layers and tiles (all layers' weights live in ONE
+//                            bf16 matrix, one tensor map per plane, 64 x 64 boxes).
+//   warp 1 lane 0            tcgen05.mma kind::f16 issuer: A from the resident tile, B from the ring, fp32 accumulators
+//                            in TMEM (x3 mode: A_hi W_hi + A_lo W_hi + A_hi W_lo, same order as ccn_linear_planes, so a
+//                            fused step is bit-identical to the unfused chain).
+// The chain inside a tile is serial (layer l+1 needs all of layer l); CTAs are independent, so where shared memory allows
+// two CTAs share an SM and one's MMAs overlap the other's epilogue.  Attention: msg accumulates in TMEM columns [0, 256),
+// the other layers in [256, 512).
+#include <type_traits>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace {
+
+using namespace ccn_tc;
+
+constexpr int kRows = 128;
+constexpr int kChunkBytes = kRows * 128;      // one 128-row x 64-column bf16 plane chunk (SWIZZLE_128B)
+constexpr int kThreads = 320;                // warp 0 TMA, warp 1 MMA, warps 2-9 row workers
+constexpr int kWorkers = 256;
+constexpr int kU = 2;                         // layer-1 items in flight per worker thread (registers: two CTAs per SM need <= 102)
+constexpr int kMaxStages = 6;
+constexpr int kMaxWidth = 256;                // widest activation kept resident / widest layer output
+constexpr int kTable = kRows * 32;            // floats of one transposition table: 128 rows x 32 columns, column XOR (row & 31)
+
+enum { FORM_DENSE = 0, FORM_PAIR = 1, FORM_POINT = 2 };
+
+struct ChainLayerDev {
+    int K, N, w_row, act;
+    float slope;
+    const float* bias;
+};
+
+struct ChainParams {
+    int L;
+    ChainLayerDev ly[CCN_CHAIN_MAX_LAYERS];
+    int stages, res_chunks;        // weight ring depth; resident activation chunks (max width / 64)
+    int w_plane_bytes;             // bytes of one plane of a ring stage: min(128, widest layer) rows x 128 B
+    int n_tiles;
+    int c1, act0;                  // width and activation of the (decomposed) first layer
+    float slope0;
+    // FORM_DENSE: rows (i, g), g = 0 self loop, g >= 1 neighbour idx[i][g-1] (-1 = missing)
+    const float* PQ;               // (n, 2 c1): [P | Q]
+    int64_t ldpq;
+    const int32_t* idx;
+    int n, Knb, G, gpt;            // points, neighbours per point, rows per group (K+1), groups per tile
+    // CSR forms: rows = edges, segments = targets
+    const int32_t *row_ptr, *erow, *ecol;
+    const int4* tiles;             // per tile: {first target, targets, first edge, edges} (csr_tiles_kernel)
+    int nq, E, S;                  // targets, edges, tile stride in edge rows (129 - max degree)
+    // FORM_POINT
+    const float* H;                // (n_src, c1) or null
+    int64_t ldh;
+    const float *wp, *bias0, *pos_src, *pos_dst;   // (3, c1), (c1), (n_src, 3), (nq, 3)
+    float radius;                  // > 0: relative positions divided by it
+    // aggregation
+    int agg, msg_layer;            // CCN_AGG_*; layer whose output is the message (attention modes), else -1
+    float* out;
+    int64_t ldo;
+    __nv_bfloat16* planes;
+    int64_t kpad, pstride;
+    int npl;
+};
+
+__device__ __forceinline__ float act_apply(float y, int act, float slope) {
+    if (act == CCN_ACT_RELU) return fmaxf(y, 0.f);
+    if (act == CCN_ACT_LEAKY) return y > 0.f ? y : y * slope;
+    return y;
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// 8 fp32 values -> 8 bf16 hi (+ 8 bf16 lo = bf16(x - hi)) stored as one 16-byte piece per plane
+template <int P>
+__device__ __forceinline__ void store_piece(uint32_t addr_hi, const float (&y)[8]) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 hv = __floats2bfloat162_rn(y[2 * e], y[2 * e + 1]);
+        h[e] = *reinterpret_cast<const uint32_t*>(&hv);
+        if (P == 2) {
+            const float2 f = __bfloat1622float2(hv);
+            const __nv_bfloat162 lv = __floats2bfloat162_rn(y[2 * e] - f.x, y[2 * e + 1] - f.y);
+            l[e] = *reinterpret_cast<const uint32_t*>(&lv);
+        }
+    }
+    st_shared_v4(addr_hi, h[0], h[1], h[2], h[3]);
+    if (P == 2) st_shared_v4(addr_hi + kChunkBytes, l[0], l[1], l[2], l[3]);
+}
+
+__device__ __forceinline__ void workers_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+template <int P, int FORM>
+__global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_constant__ CUtensorMap w_hi,
+                                                                 const __grid_constant__ CUtensorMap w_lo,
+                                                                 const __grid_constant__ ChainParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 2];     // w_full[S], w_empty[S], a_ready, acc_full
+    __shared__ uint32_t tmem_base_slot;
+    __shared__ float bias_s[CCN_CHAIN_MAX_LAYERS][kMaxWidth];
+    __shared__ float wp_s[4][kMaxWidth];                            // FORM_POINT: Wp rows 0..2, bias of layer 1
+    __shared__ int32_t row_i[kRows], row_j[kRows];                  // target / source of every tile row (-1: none)
+    __shared__ float row_rel[kRows][3];                             // FORM_POINT: (pos_j - pos_i) [/ r]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool att_mode = p.msg_layer >= 0;
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t res0 = smem0;                                    // resident activations [chunk][plane][128 x 128 B]
+    const uint32_t ring0 = smem0 + (uint32_t)(p.res_chunks * P * kChunkBytes);
+    const int stage_bytes = P * p.w_plane_bytes;                    // one W tile: <= 128 rows x 64 k per plane
+    const int stages = p.stages;
+    const uint32_t wfull0 = smem_u32(&bars[0]), wempty0 = smem_u32(&bars[kMaxStages]);
+    const uint32_t a_ready = smem_u32(&bars[2 * kMaxStages]), acc_full = smem_u32(&bars[2 * kMaxStages + 1]);
+    int maxn = 32;
+    for (int l = 0; l < p.L; ++l) maxn = max(maxn, p.ly[l].N);
+    uint32_t tmem_cols = 32;
+    while ((int)tmem_cols < maxn) tmem_cols <<= 1;
+    if (att_mode) tmem_cols = 512;
+    const uint32_t chain_col = att_mode ? 256u : 0u;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(wfull0 + 8 * s, 1);
+            mbar_init(wempty0 + 8 * s, 1);
+        }
+        mbar_init(a_ready, 8);
+        mbar_init(acc_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int t = threadIdx.x; t < p.L * kMaxWidth; t += kThreads) {
+        const int l = t / kMaxWidth, c = t % kMaxWidth;
+        bias_s[l][c] = (p.ly[l].bias && c < p.ly[l].N) ? __ldg(p.ly[l].bias + c) : 0.f;
+    }
+    if (FORM == FORM_POINT) {
+        for (int t = threadIdx.x; t < 4 * kMaxWidth; t += kThreads) {
+            const int r = t / kMaxWidth, c = t % kMaxWidth;
+            float v = 0.f;
+            if (c < p.c1) v = r < 3 ? __ldg(p.wp + r * p.c1 + c) : (p.bias0 ? __ldg(p.bias0 + c) : 0.f);
+            wp_s[r][c] = v;
+        }
+    }
+    if (warp == 0) tmem_alloc(smem_u32(&tmem_base_slot), tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer: the weight stream
+        if (lane == 0) {
+            uint32_t cnt = 0;
+            for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+                for (int l = 0; l < p.L; ++l) {
+                    const int N = p.ly[l].N, nk = p.ly[l].K >> 6, wrow = p.ly[l].w_row;
+                    for (int n0 = 0; n0 < N; n0 += 128) {
+                        const int mma_n = min(128, N - n0);
+                        for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                            const int s = cnt % stages;
+                            mbar_wait(wempty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
+                            const uint32_t dst = ring0 + s * stage_bytes;
+                            mbar_arrive_expect_tx(wfull0 + 8 * s, (uint32_t)(P * mma_n * 128));
+                            for (int b = 0; b < mma_n; b += 64) {
+                                tma_load_2d(dst + b * 128, &w_hi, kc * 64, wrow + n0 + b, wfull0 + 8 * s);
+                                if (P == 2) tma_load_2d(dst + p.w_plane_bytes + b * 128, &w_lo, kc * 64, wrow + n0 + b, wfull0 + 8 * s);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            uint32_t cnt = 0, aphase = 0;
+            for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+                for (int l = 0; l < p.L; ++l) {
+                    const int N = p.ly[l].N, nk = p.ly[l].K >> 6;
+                    mbar_wait(a_ready, aphase);                      // the layer's A operand is complete in shared memory
+                    aphase ^= 1;
+                    tc_fence_after();
+                    const uint32_t acc = tmem_base + ((att_mode && l == p.msg_layer) ? 0u : chain_col);
+                    for (int n0 = 0; n0 < N; n0 += 128) {
+                        const int mma_n = min(128, N - n0);
+                        // instruction descriptor: D=f32, A=B=bf16, K-major both, N>>3 at bit 17, M>>4 at bit 24
+                        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(mma_n >> 3) << 17) |
+                                               ((uint32_t)(kRows >> 4) << 24);
+                        for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                            const int s = cnt % stages;
+                            mbar_wait(wfull0 + 8 * s, (cnt / stages) & 1);
+                            tc_fence_after();
+                            const uint32_t a_hi = res0 + (uint32_t)(kc * P) * kChunkBytes, a_lo = a_hi + kChunkBytes;
+                            const uint32_t b_hi = ring0 + s * stage_bytes, b_lo = b_hi + p.w_plane_bytes;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const uint32_t ko = k * 32;         // 16 bf16 = 32 bytes inside the 128-byte swizzle row
+                                umma_bf16(acc + n0, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, (kc | k) ? 1u : 0u);
+                                if (P == 2) {
+                                    umma_bf16(acc + n0, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc, 1u);
+                                    umma_bf16(acc + n0, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc, 1u);
+                                }
+                            }
+                            umma_commit(wempty0 + 8 * s);           // ring slot reusable once these MMAs have read it
+                        }
+                    }
+                    umma_commit(acc_full);                          // accumulator complete, A operand no longer read
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ row workers (warps 2..9)
+        const int wt = threadIdx.x - 64;                            // 0..255
+        const int q = warp & 3;                                     // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;                           // warps w and w + 4 share a lane quarter: they split the columns
+        const int myrow = q * 32 + lane;
+        const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+        float* T = reinterpret_cast<float*>(smem_raw + (smem0 - smem_u32(smem_raw)));   // two transposition tables alias the resident tile
+        uint32_t accphase = 0;
+        const int g8n = p.c1 >> 3;                                  // 8-channel groups of a layer-1 row
+        // row metadata of the NEXT tile is fetched while the current one computes (registers of threads 0..127)
+        int4 hdr = make_int4(0, 0, 0, 0);
+        int nri = -1, nrj = -1;
+        auto fetch_hdr = [&](int t) {
+            if (FORM == FORM_DENSE) {
+                const int q0 = t * p.gpt, nseg = max(0, min(p.gpt, p.n - q0));
+                return make_int4(q0, nseg, 0, nseg * p.G);
+            }
+            return t < p.n_tiles ? __ldg(p.tiles + t) : make_int4(0, 0, 0, 0);
+        };
+        auto fetch_rows = [&](const int4& h) {
+            nri = -1; nrj = -1;
+            if (wt < min(h.w, kRows)) {
+                if (FORM == FORM_DENSE) {
+                    const int sg = wt / p.G, g = wt - sg * p.G;
+                    nri = h.x + sg;
+                    nrj = g == 0 ? nri : __ldg(p.idx + (int64_t)nri * p.Knb + g - 1);
+                } else {
+                    nri = __ldg(p.erow + h.z + wt);
+                    nrj = __ldg(p.ecol + h.z + wt);
+                }
+            }
+        };
+        hdr = fetch_hdr(blockIdx.x);
+        fetch_rows(hdr);
+        for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
+            // ---- tile header: which rows, which segments
+            const int q0 = hdr.x, nseg = hdr.y, e0 = hdr.z, nrows = min(hdr.w, kRows);
+            if (wt < kRows) {
+                row_i[wt] = nri;
+                row_j[wt] = nrj;
+                if (FORM == FORM_POINT && nri >= 0) {
+                    float rx = __fsub_rn(__ldg(p.pos_src + 3 * (int64_t)nrj), __ldg(p.pos_dst + 3 * (int64_t)nri));
+                    float ry = __fsub_rn(__ldg(p.pos_src + 3 * (int64_t)nrj + 1), __ldg(p.pos_dst + 3 * (int64_t)nri + 1));
+                    float rz = __fsub_rn(__ldg(p.pos_src + 3 * (int64_t)nrj + 2), __ldg(p.pos_dst + 3 * (int64_t)nri + 2));
+                    if (p.radius > 0.f) { rx = __fdiv_rn(rx, p.radius); ry = __fdiv_rn(ry, p.radius); rz = __fdiv_rn(rz, p.radius); }
+                    row_rel[wt][0] = rx; row_rel[wt][1] = ry; row_rel[wt][2] = rz;
+                }
+            }
+            workers_sync();
+            hdr = fetch_hdr(t + gridDim.x);                         // next tile's header: in flight during the formation
+
+            // ---- layer 1 (decomposed): rows formed straight into the A tile, kU items (row, 8 channels) per thread in flight
+            for (int base = wt; base < kRows * g8n; base += kWorkers * kU) {
+                float4 va[kU], vb[kU], vc[kU], vd[kU];
+                int rowv[kU], g8v[kU], iv[kU], jv[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const int item = base + u * kWorkers;
+                    const int row = item < kRows * g8n ? item / g8n : 0;
+                    rowv[u] = row;
+                    g8v[u] = item - row * g8n;
+                    iv[u] = item < kRows * g8n ? row_i[row] : -1;
+                    jv[u] = row_j[row];
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    if (FORM == FORM_DENSE || FORM == FORM_PAIR) {
+                        const float4* qrow = reinterpret_cast<const float4*>(p.PQ + (int64_t)max(iv[u], 0) * p.ldpq + p.c1 + 8 * g8v[u]);
+                        const float4* prow = reinterpret_cast<const float4*>(p.PQ + (int64_t)max(jv[u], 0) * p.ldpq + 8 * g8v[u]);
+                        va[u] = __ldg(qrow); vb[u] = __ldg(qrow + 1);
+                        vc[u] = __ldg(prow); vd[u] = __ldg(prow + 1);
+                    } else if (p.H) {
+                        const float4* hrow = reinterpret_cast<const float4*>(p.H + (int64_t)max(jv[u], 0) * p.ldh + 8 * g8v[u]);
+                        vc[u] = __ldg(hrow); vd[u] = __ldg(hrow + 1);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    if (base + u * kWorkers >= kRows * g8n) break;
+                    const int row = rowv[u], g8 = g8v[u];
+                    float y[8];
+                    if (iv[u] < 0) {
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) y[e] = 0.f;
+                    } else {
+                        if (FORM == FORM_DENSE || FORM == FORM_PAIR) {
+                            y[0] = va[u].x; y[1] = va[u].y; y[2] = va[u].z; y[3] = va[u].w;
+                            y[4] = vb[u].x; y[5] = vb[u].y; y[6] = vb[u].z; y[7] = vb[u].w;
+                            if (jv[u] >= 0) {
+                                y[0] += vc[u].x; y[1] += vc[u].y; y[2] += vc[u].z; y[3] += vc[u].w;
+                                y[4] += vd[u].x; y[5] += vd[u].y; y[6] += vd[u].z; y[7] += vd[u].w;
+                            }
+                        } else {
+                            const float rx = row_rel[row][0], ry = row_rel[row][1], rz = row_rel[row][2];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) y[e] = wp_s[3][8 * g8 + e];
+                            if (p.H) {
+                                y[0] += vc[u].x; y[1] += vc[u].y; y[2] += vc[u].z; y[3] += vc[u].w;
+                                y[4] += vd[u].x; y[5] += vd[u].y; y[6] += vd[u].z; y[7] += vd[u].w;
+                            }
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                float v = fmaf(wp_s[0][8 * g8 + e], rx, y[e]);
+                                v = fmaf(wp_s[1][8 * g8 + e], ry, v);
+                                y[e] = fmaf(wp_s[2][8 * g8 + e], rz, v);
+                            }
+                        }
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) y[e] = act_apply(y[e], p.act0, p.slope0);
+                    }
+                    const int kc = g8 >> 3, piece = g8 & 7;
+                    store_piece<P>(res0 + (uint32_t)(kc * P) * kChunkBytes + row * 128 + ((piece ^ (row & 7)) << 4), y);
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");    // generic-proxy writes -> async proxy (UMMA)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(a_ready);
+            const bool row_masked = FORM == FORM_DENSE && myrow < nrows && row_j[myrow] < 0;   // missing neighbour: -100 (dgcnn.py:187-189)
+            fetch_rows(hdr);                                        // next tile's rows: in flight during the MMAs
+
+            for (int l = 0; l < p.L; ++l) {
+                mbar_wait(acc_full, accphase);
+                accphase ^= 1;
+                tc_fence_after();
+                const int N = p.ly[l].N, act = p.ly[l].act;
+                const float slope = p.ly[l].slope;
+                const uint32_t tacc = tmem_base + lane_base + ((att_mode && l == p.msg_layer) ? 0u : chain_col);
+                if (l + 1 < p.L) {
+                    // ---- epilogue: accumulator -> bias + activation -> bf16 planes, in place, as the next layer's A operand
+                    for (int c0 = 32 * half; c0 < N; c0 += 64) {
+                        uint32_t v[32];
+                        tmem_ld32(tacc + (uint32_t)c0, v);
+#pragma unroll
+                        for (int pc = 0; pc < 4; ++pc) {
+                            float y[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e)
+                                y[e] = act_apply(__uint_as_float(v[8 * pc + e]) + bias_s[l][c0 + 8 * pc + e], act, slope);
+                            const int kc = c0 >> 6, piece = ((c0 & 63) >> 3) + pc;
+                            store_piece<P>(res0 + (uint32_t)(kc * P) * kChunkBytes + myrow * 128 + ((piece ^ (myrow & 7)) << 4), y);
+                        }
+                    }
+                    tc_fence_before();
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(a_ready);
+                    continue;
+                }
+                // ---- last layer: aggregate every segment of the tile in edge order.  Per pass two 128 x 32 tables: the two
+                // warp halves load columns [c0, c0+32) and [c0+32, c0+64) (max / mean / sum), or the attention logits and the
+                // message of the same 32 columns (attention modes)
+                const uint32_t tmsg = tmem_base + lane_base;
+                const int ml = att_mode ? p.msg_layer : l;
+                const int swz = myrow & 31;
+                for (int c0 = 0; c0 < N; c0 += att_mode ? 32 : 64) {
+                    uint32_t v[32];
+                    float* Tw = T + half * kTable + myrow * 32;
+                    if (!att_mode || half == 0) {
+                        const int cc = c0 + (att_mode ? 0 : 32 * half);
+                        tmem_ld32(tacc + (uint32_t)cc, v);
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            float y = act_apply(__uint_as_float(v[e]) + bias_s[l][cc + e], act, slope);
+                            if (row_masked) y = -100.f;
+                            Tw[e ^ swz] = y;
+                        }
+                    } else {
+                        tmem_ld32(tmsg + (uint32_t)c0, v);
+#pragma unroll
+                        for (int e = 0; e < 32; ++e)
+                            Tw[e ^ swz] = act_apply(__uint_as_float(v[e]) + bias_s[ml][c0 + e], p.ly[ml].act, p.ly[ml].slope);
+                    }
+                    workers_sync();
+                    const int c = wt & 31;
+                    const int tab = att_mode ? 0 : (wt >> 7);
+                    const int s0 = att_mode ? (wt >> 5) : ((wt >> 5) & 3), sstep = att_mode ? 8 : 4;
+                    const float* Ta = T + tab * kTable;            // last layer's rows (attention logits in the attention modes)
+                    const float* Tm = T + kTable;                  // message rows (attention modes)
+                    const int col = c0 + 32 * tab + c;
+                    for (int sg = s0; sg < nseg; sg += sstep) {
+                        int lo, hi;
+                        if (FORM == FORM_DENSE) { lo = sg * p.G; hi = lo + p.G; }
+                        else { lo = __ldg(p.row_ptr + q0 + sg) - e0; hi = __ldg(p.row_ptr + q0 + sg + 1) - e0; }
+                        float r = 0.f;
+                        if (p.agg == CCN_AGG_MAX) {
+                            if (hi > lo) {
+                                r = Ta[lo * 32 + (c ^ (lo & 31))];
+#pragma unroll 4
+                                for (int j = lo + 1; j < hi; ++j) r = fmaxf(r, Ta[j * 32 + (c ^ (j & 31))]);
+                            }
+                        } else if (p.agg == CCN_AGG_MEAN || p.agg == CCN_AGG_SUM) {
+                            for (int j = lo; j < hi; ++j) r += Ta[j * 32 + (c ^ (j & 31))];
+                            if (p.agg == CCN_AGG_MEAN) r = r / fmaxf((float)(hi - lo), 1.f);
+                        } else if (p.agg == CCN_AGG_WSUM) {
+                            for (int j = lo; j < hi; ++j)
+                                r += Tm[j * 32 + (c ^ (j & 31))] * (1.f / (1.f + expf(-Ta[j * 32 + (c ^ (j & 31))])));
+                        } else {
+                            float m = -INFINITY;
+                            for (int j = lo; j < hi; ++j) m = fmaxf(m, Ta[j * 32 + (c ^ (j & 31))]);
+                            float sum = 0.f;
+                            for (int j = lo; j < hi; ++j) sum += expf(Ta[j * 32 + (c ^ (j & 31))] - m);
+                            const float inv = 1.f / (sum + 1e-16f);
+                            for (int j = lo; j < hi; ++j)
+                                r += Tm[j * 32 + (c ^ (j & 31))] * (expf(Ta[j * 32 + (c ^ (j & 31))] - m) * inv);
+                        }
+                        const int64_t orow = q0 + sg;
+                        p.out[orow * p.ldo + col] = r;
+                        if (p.planes) {
+                            const __nv_bfloat16 h = __float2bfloat16_rn(r);
+                            p.planes[orow * p.kpad + col] = h;
+                            if (p.npl == 2) p.planes[p.pstride + orow * p.kpad + col] = __float2bfloat16_rn(r - __bfloat162float(h));
+                        }
+                    }
+                    workers_sync();
+                }
+                tc_fence_before();
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, tmem_cols);
+    }
+}
+
+// CSR tiling: tile t owns the targets whose first edge lies in [S t, S (t+1)) - at most S - 1 + max_degree = 128 edge rows,
+// whole segments only; targets without edges belong to the tile of their offset.  One thread per tile, two binary searches.
+__global__ void csr_tiles_kernel(const int32_t* __restrict__ row_ptr, int nq, int S, int n_tiles, int4* __restrict__ tiles) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    const int lo_v = S * t, hi_v = lo_v + S;
+    int a = 0, b = nq + 1;
+    while (a < b) { const int m = (a + b) >> 1; if (__ldg(row_ptr + m) < lo_v) a = m + 1; else b = m; }
+    const int qa = min(a, nq);
+    b = nq + 1;
+    while (a < b) { const int m = (a + b) >> 1; if (__ldg(row_ptr + m) < hi_v) a = m + 1; else b = m; }
+    const int qb = min(a, nq);
+    const int e0 = __ldg(row_ptr + qa);
+    tiles[t] = make_int4(qa, qb - qa, e0, __ldg(row_ptr + qb) - e0);
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------
+constexpr int kSmemLimit = 227 * 1024;
+constexpr int kStaticSmem = 14 * 1024;          // bias / Wp / row tables / barriers (ptxas reports ~12.8 KB)
+constexpr int kHalfSm = 113 * 1024;             // two CTAs per SM: 228 KB / 2 minus the per-CTA reservation
+
+int fill_chain(ChainParams& p, const ccn_chain_t* ch, int c1, bool att, int& smem_bytes, int& P) {
+    CCN_REQUIRE(ch && ch->n_layers >= 1 && ch->n_layers <= CCN_CHAIN_MAX_LAYERS && ch->w_hi_tmap);
+    CCN_REQUIRE(ch->mode == 1 || (ch->mode == 3 && ch->w_lo_tmap));
+    P = ch->mode == 3 ? 2 : 1;
+    p.L = ch->n_layers;
+    int width = c1, maxw = c1, maxn = 64;
+    CCN_REQUIRE(c1 >= 64 && c1 <= kMaxWidth && (c1 & 63) == 0);
+    for (int l = 0; l < p.L; ++l) {
+        CCN_REQUIRE(ch->k[l] == width && ch->n[l] >= 64 && ch->n[l] <= kMaxWidth && (ch->n[l] & 63) == 0);
+        CCN_REQUIRE(ch->act[l] >= 0 && ch->act[l] <= 2 && ch->w_row[l] >= 0);
+        p.ly[l].K = ch->k[l]; p.ly[l].N = ch->n[l]; p.ly[l].w_row = ch->w_row[l]; p.ly[l].act = ch->act[l];
+        p.ly[l].slope = ch->slope[l]; p.ly[l].bias = ch->bias[l];
+        width = ch->n[l];
+        if (width > maxn) maxn = width;
+        if (l + 1 < p.L) maxw = width > maxw ? width : maxw;
+    }
+    p.res_chunks = maxw / 64;
+    int res_bytes = p.res_chunks * P * kChunkBytes;
+    const int table_bytes = 2 * kTable * 4;                           // the aggregation's transposition tables alias the tile
+    if (res_bytes < table_bytes) {
+        p.res_chunks = (table_bytes + P * kChunkBytes - 1) / (P * kChunkBytes);
+        res_bytes = p.res_chunks * P * kChunkBytes;
+    }
+    p.w_plane_bytes = (maxn < 128 ? maxn : 128) * 128;
+    const int stage = P * p.w_plane_bytes;
+    int stages = (kSmemLimit - kStaticSmem - 1024 - res_bytes) / stage;
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages < 2) return CCN_EUNSUPPORTED;
+    // narrow chains: keep the footprint under half an SM so that two CTAs are co-resident (one's MMAs overlap the other's epilogue)
+    if (!att && res_bytes + 3 * stage + 1024 + kStaticSmem <= kHalfSm) {
+        const int fit = (kHalfSm - kStaticSmem - 1024 - res_bytes) / stage;
+        if (stages > fit) stages = fit;
+    }
+    p.stages = stages;
+    smem_bytes = res_bytes + stages * stage + 1024;
+    return CCN_OK;
+}
+
+template <int P, int FORM>
+int launch_chain(const ccn_chain_t* ch, const ChainParams& p, int smem, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(edge_chain_kernel<P, FORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - kStaticSmem);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    const int per_sm = smem + kStaticSmem <= kHalfSm && p.msg_layer < 0 ? 2 : 1;
+    const int grid = p.n_tiles < 148 * per_sm ? p.n_tiles : 148 * per_sm;
+    const CUtensorMap* whi = (const CUtensorMap*)ch->w_hi_tmap;
+    const CUtensorMap* wlo = P == 2 ? (const CUtensorMap*)ch->w_lo_tmap : whi;
+    edge_chain_kernel<P, FORM><<<grid, kThreads, smem, s>>>(*whi, *wlo, p);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+}  // namespace
+
+extern "C" int ccn_sgcnn_fused(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c1,
+                               int32_t act0, float slope0, const ccn_chain_t* chain_host, float* out, int64_t ldo,
+                               void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    CCN_REQUIRE(PQ && idx && out && n >= 0 && n < 0x7fffffff && K >= 1 && K + 1 <= kRows && act0 >= 0 && act0 <= 2);
+    CCN_REQUIRE(ldpq >= 2 * c1 && (ldpq & 3) == 0 && (reinterpret_cast<uintptr_t>(PQ) & 15) == 0);
+    ChainParams p = {};
+    int smem = 0, P = 1;
+    const int rc = fill_chain(p, chain_host, c1, false, smem, P);
+    if (rc != CCN_OK) return rc;
+    const int nout = p.ly[p.L - 1].N;
+    CCN_REQUIRE(ldo >= nout && (!planes || (kpad >= nout && (n_planes == 1 || n_planes == 2))));
+    if (n == 0) return CCN_OK;
+    p.c1 = c1; p.act0 = act0; p.slope0 = slope0;
+    p.PQ = PQ; p.ldpq = ldpq; p.idx = idx; p.n = (int)n; p.Knb = K; p.G = K + 1; p.gpt = kRows / (K + 1);
+    p.n_tiles = (int)((n + p.gpt - 1) / p.gpt);
+    p.agg = CCN_AGG_MAX; p.msg_layer = -1;
+    p.out = out; p.ldo = ldo; p.planes = (__nv_bfloat16*)planes; p.kpad = kpad; p.pstride = plane_stride; p.npl = n_planes;
+    return P == 2 ? launch_chain<2, FORM_DENSE>(chain_host, p, smem, (cudaStream_t)stream)
+                  : launch_chain<1, FORM_DENSE>(chain_host, p, smem, (cudaStream_t)stream);
+}
+
+extern "C" int ccn_pointconv_fused(const float* H, int64_t ldh, const float* wp, const float* bias0, const float* pos_src,
+                                   const float* pos_dst, const float* PQ, int64_t ldpq, const int32_t* row_ptr,
+                                   const int32_t* erow, const int32_t* ecol, int64_t nq, int64_t E, int32_t max_degree,
+                                   int32_t c1, float radius, int32_t act0, float slope0, const ccn_chain_t* chain_host,
+                                   int32_t agg, int32_t msg_layer, int32_t* tile_scratch, float* out, int64_t ldo,
+                                   void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    const bool pair = PQ != nullptr;
+    CCN_REQUIRE(row_ptr && erow && ecol && out && nq >= 0 && nq < 0x7fffffff && E >= 0 && E < 0x7fffffff);
+    CCN_REQUIRE(tile_scratch && (reinterpret_cast<uintptr_t>(tile_scratch) & 15) == 0);
+    CCN_REQUIRE(max_degree >= 1 && max_degree <= kRows && act0 >= 0 && act0 <= 2 && agg >= 0 && agg <= 4);
+    if (pair) CCN_REQUIRE(ldpq >= 2 * c1 && (ldpq & 3) == 0 && (reinterpret_cast<uintptr_t>(PQ) & 15) == 0);
+    else CCN_REQUIRE(wp && pos_src && pos_dst && (!H || ((ldh & 3) == 0 && ldh >= c1 && (reinterpret_cast<uintptr_t>(H) & 15) == 0)));
+    ChainParams p = {};
+    int smem = 0, P = 1;
+    const bool att = agg == CCN_AGG_WSUM || agg == CCN_AGG_ATTEND;
+    const int rc = fill_chain(p, chain_host, c1, att, smem, P);
+    if (rc != CCN_OK) return rc;
+    CCN_REQUIRE(att ? (msg_layer >= 0 && msg_layer < p.L - 1 && p.ly[msg_layer].N == p.ly[p.L - 1].N) : msg_layer < 0);
+    const int nout = p.ly[p.L - 1].N;
+    CCN_REQUIRE(ldo >= nout && (!planes || (kpad >= nout && (n_planes == 1 || n_planes == 2))));
+    if (nq == 0) return CCN_OK;
+    p.c1 = c1; p.act0 = act0; p.slope0 = slope0;
+    p.PQ = PQ; p.ldpq = ldpq; p.H = H; p.ldh = ldh; p.wp = wp; p.bias0 = bias0; p.pos_src = pos_src; p.pos_dst = pos_dst;
+    p.radius = radius;
+    p.row_ptr = row_ptr; p.erow = erow; p.ecol = ecol; p.nq = (int)nq; p.E = (int)E; p.S = kRows + 1 - max_degree;
+    p.n_tiles = (int)(E / p.S) + 1;
+    p.agg = agg; p.msg_layer = att ? msg_layer : -1;
+    p.out = out; p.ldo = ldo; p.planes = (__nv_bfloat16*)planes; p.kpad = kpad; p.pstride = plane_stride; p.npl = n_planes;
+    cudaStream_t s = (cudaStream_t)stream;
+    p.tiles = reinterpret_cast<const int4*>(tile_scratch);
+    csr_tiles_kernel<<<(p.n_tiles + 127) / 128, 128, 0, s>>>(row_ptr, p.nq, p.S, p.n_tiles, reinterpret_cast<int4*>(tile_scratch));
+    CCN_CHECK_LAUNCH();
+    if (pair) return P == 2 ? launch_chain<2, FORM_PAIR>(chain_host, p, smem, s) : launch_chain<1, FORM_PAIR>(chain_host, p, smem, s);
+    return P == 2 ? launch_chain<2, FORM_POINT>(chain_host, p, smem, s) : launch_chain<1, FORM_POINT>(chain_host, p, smem, s);
+}

@@ -20,6 +20,25 @@ from .nn import (DEFAULT_DRAWS, MLP, Draws, PreparedLinear, cat_features, fold_b
                  mlp_to_features, n_planes)
 
 
+class _ChainCache:
+    """ChainWeights (ops) of an edge MLP's layers after its first + the attention MLP's layers, rebuilt when the folded
+    weights change; None when the fused kernels do not cover the shapes (the unfused chain of launches runs then)."""
+
+    def __init__(self):
+        self.key, self.chain = None, None
+
+    def get(self, layers, extra=()):
+        npl = n_planes()
+        key = (id(layers), npl, id(extra) if extra else 0)
+        if self.key != key:
+            rest = list(layers[1:]) + list(extra)
+            ok = (npl > 0 and ops.FUSED_EDGE_STEPS and len(rest) >= 1 and
+                  ops.ChainWeights.supported(layers[0].out_features, [l.out_features for l in rest]))
+            self.chain = ops.ChainWeights([(l.w, l.b, l.act, l.slope) for l in rest], npl) if ok else None
+            self.key, self._keep = key, (layers, extra)
+        return self.chain
+
+
 def _cat_xyz(x, pos, with_xyz, cache=None):
     """cat[x, pos] as the input of a Linear (activation planes on the tensor-core modes)."""
     if not with_xyz:
@@ -195,6 +214,7 @@ class PointNetConv2(nn.Module):
         self.local_nn, self.global_nn, self.attend_nn = local_nn, global_nn, attend_nn
         self.aggr_type, self.normalize_radius = aggr_type, normalize_radius
         self._dec, self._dec_src = None, None
+        self._fused = _ChainCache()
 
     def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR, cache=None):
         if self.training:
@@ -209,6 +229,16 @@ class PointNetConv2(nn.Module):
             self._dec, self._dec_src = (lin_x, l0.w[:, cx:].t().contiguous()), layers
         lin_x, wp = self._dec                                  # x part (C1, cx) and positional part (3, C1)
         H = lin_x(x_src) if lin_x is not None else None
+        if edges.max_degree <= ops.FUSED_MAX_DEGREE and (H is None or torch.is_tensor(H)):
+            # gather -> layer 1 -> remaining layers [-> attention MLP] -> aggregate in ONE kernel (csrc/edge_fused.cu)
+            att = self.aggr_type in ("attend", "weighted-sum")
+            extra = self.attend_nn.layers() if att else ()
+            chain = self._fused.get(layers, extra) if len(layers) >= 2 else None
+            if chain is not None:
+                out = ops.pointconv_fused(edges, chain, self.aggr_type, len(layers) - 2 if att else -1, l0.act, l0.slope,
+                                          l0.out_features, H=H, wp=wp, bias0=l0.b, pos_src=pos_src, pos_dst=pos_dst,
+                                          radius=self.normalize_radius, npl=n_planes(), cache=cache)
+                return self.global_nn(out) if self.global_nn is not None else out
         npl = n_planes() if len(layers) > 1 else 0
         msg = ops.edge_layer1(H, wp, l0.b, pos_src, pos_dst, edges, self.normalize_radius, l0.act, l0.slope, npl)
         if self.aggr_type in ("max", "mean"):
@@ -408,6 +438,7 @@ class SGCNNLayer(nn.Module):
         self.attend_nn, self.aggr_type = attend_nn, aggr_type
         self.use_fast_knn, self.use_sparse_feat_agg = use_fast_knn, use_sparse_feat_agg
         self._dec, self._dec_src = None, None
+        self._fused = _ChainCache()
 
     def _decomposed(self):
         layers = self.nn.layers()
@@ -435,6 +466,10 @@ class SGCNNLayer(nn.Module):
             if self.aggr_type != "max":
                 raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
             nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, cache=cache)
+            chain = self._fused.get(self.nn.layers()) if self.k + 1 <= 128 else None
+            if chain is not None:
+                # gather -> layer 1 -> remaining layers -> masked max in ONE kernel (csrc/edge_fused.cu)
+                return ops.sgcnn_fused(PQ, nbr, act0, slope0, chain, n_planes(), cache), pos, batch, point2curveidx
             h = ops.sgcnn_layer1(PQ, nbr, act0, slope0, n_planes() if self.nn.num_layers > 1 else 0)
             h = self.nn.forward_from(h, 1)
             return ops.group_max_dense(h, nbr, n_planes(), cache), pos, batch, point2curveidx
@@ -444,6 +479,14 @@ class SGCNNLayer(nn.Module):
             nbr, _, cnt = ops.knn_exact(pos, batch, pos, sptr, self.k, zero_fill=True, want_d2=False, want_cnt=True)
         edges = ops.dense_to_csr(nbr, cnt)
         npl = n_planes() if self.nn.num_layers > 1 else 0
+        if self.aggr_type in ("max", "attend") and edges.max_degree <= ops.FUSED_MAX_DEGREE:
+            layers = self.nn.layers()
+            extra = self.attend_nn.layers() if self.aggr_type == "attend" else ()
+            chain = self._fused.get(layers, extra) if len(layers) >= 2 else None
+            if chain is not None:
+                out = ops.pointconv_fused(edges, chain, self.aggr_type, len(layers) - 2 if extra else -1, act0, slope0,
+                                          layers[0].out_features, PQ=PQ, npl=n_planes(), cache=cache)
+                return out, pos, batch, point2curveidx
         msg = ops.edge_pair_layer1(PQ, edges, act0, slope0, npl)
         if self.aggr_type == "max":
             msg = self.nn.forward_from(msg, 1)

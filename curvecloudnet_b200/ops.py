@@ -18,6 +18,7 @@ from .native import call
 ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
 AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3, "sum": 4}
 MAX_SAMPLES = 4096
+FUSED_EDGE_STEPS = True     # tests switch it off to compare the fused edge kernels with the unfused chain
 TOPO_ERRORS = {1: "batch vector is not sorted", 2: "curve ids are not sorted within a sample",
                4: "more than %d samples in a batch" % MAX_SAMPLES, 8: "batch ids are not 0..B-1"}
 
@@ -45,6 +46,11 @@ def _rows(t: torch.Tensor) -> Tuple[torch.Tensor, int]:
 
 def _empty(shape, dtype, like):
     return torch.empty(shape, dtype=dtype, device=like.device)
+
+
+def _bits_f32(bits: int) -> float:
+    import struct
+    return struct.unpack("f", struct.pack("i", bits))[0]
 
 
 def _raise_topo(flags: int):
@@ -218,6 +224,7 @@ class EdgeCSR:
     ecol: torch.Tensor         # int32 (E) source point index
     n_edges: int
     nq: int
+    max_degree: int = 1 << 30  # upper bound of the edges per target (the fused edge kernels tile by it)
 
 
 def radius_1d_group(pos: torch.Tensor, topo: CurveTopology, idxs: torch.Tensor, radius: float) -> EdgeCSR:
@@ -227,18 +234,19 @@ def radius_1d_group(pos: torch.Tensor, topo: CurveTopology, idxs: torch.Tensor, 
     pos, idxs = _f32(pos), _i64(idxs)
     nq = idxs.shape[0]
     kc = _empty((max(topo.n_curves, 1),), torch.float32, pos)
-    stats = _empty((2,), torch.int32, pos)
-    row_ptr = _empty((nq + 2,), torch.int32, pos)
-    total = row_ptr[nq + 1:]
+    buf = _empty((nq + 4,), torch.int32, pos)                    # row_ptr (nq+1), total, stats (2): one read-back
+    row_ptr, total, stats = buf[:nq + 2], buf[nq + 1:nq + 2], buf[nq + 2:]
     call("ccn_radius_1d_group_count", pos, topo.curve_ord, topo.curve_ptr, topo.curve_local, topo.n, topo.n_curves,
          idxs, nq, float(radius), kc, stats, row_ptr, total)
-    E = int(total.item())                                        # host sync
+    E, kbits, nbits = buf[nq + 1:].tolist()                      # host sync
+    # a query keeps at most k_c candidates, k_c <= max over the curves (stats[0], float bits), and no more than a curve has
+    max_deg = max(1, int(min(_bits_f32(kbits), _bits_f32(nbits))))
     col = _empty((max(E, 1),), torch.int32, pos)
     call("ccn_radius_1d_group_fill", topo.curve_ord, topo.curve_local, topo.n, topo.n_curves, idxs, nq, kc, stats,
          row_ptr, col)
     erow = _empty((max(E, 1),), torch.int32, pos)
     call("ccn_csr_rows", row_ptr, nq, erow)
-    return EdgeCSR(row_ptr[:nq + 1], erow[:E], col[:E], E, nq)
+    return EdgeCSR(row_ptr[:nq + 1], erow[:E], col[:E], E, nq, max_deg)
 
 
 def knn_1d_superset(pos: torch.Tensor, curve_ord: torch.Tensor, idxs: torch.Tensor, knn: int):
@@ -364,7 +372,7 @@ def dense_to_csr(idx: torch.Tensor, cnt: torch.Tensor) -> EdgeCSR:
     erow = _empty((max(E, 1),), torch.int32, idx)
     ecol = _empty((max(E, 1),), torch.int32, idx)
     call("ccn_dense_to_csr", idx, cnt, nq, K, erow, ecol)
-    return EdgeCSR(cnt[:nq + 1], erow[:E], ecol[:E], E, nq)
+    return EdgeCSR(cnt[:nq + 1], erow[:E], ecol[:E], E, nq, K)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -832,3 +840,110 @@ def linear_tc(A: torch.Tensor, tw: TcWeight, bias: Optional[torch.Tensor], act: 
     call("ccn_linear_tc", A, lda, p_hi, p_lo, bias if bias is not None else 0, Y, tw.n, M, tw.n, K, box, mode, act,
          float(slope))
     return Y
+
+
+# ----------------------------------------------------------------------------------------------
+# fused edge-MLP steps (csrc/edge_fused.cu): gather -> layer 1 (decomposed) -> layers 2..n -> aggregate in one kernel
+# ----------------------------------------------------------------------------------------------
+CHAIN_MAX_LAYERS = 6
+CHAIN_MAX_WIDTH = 256
+
+
+class ChainWeights:
+    """The layers AFTER the decomposed first one of an edge MLP (plus, for the attention aggregations, attend_nn's
+    layers), prepared for ccn_sgcnn_fused / ccn_pointconv_fused: every layer's folded fp32 weight (N_l, K_l) stacked
+    row-wise into ONE split-bf16 matrix (columns zero padded to the widest K), one TMA descriptor per plane
+    (64 x 64 boxes) and the host-side ccn_chain_t.  Weight preparation, once per weight version."""
+
+    def __init__(self, layers, n_planes: int):
+        """layers: [(w (N, K) fp32 folded, bias (N) or None, act, slope)]."""
+        import ctypes
+        assert 1 <= len(layers) <= CHAIN_MAX_LAYERS
+        kmax = max(w.shape[1] for w, _, _, _ in layers)
+        rows = sum(w.shape[0] for w, _, _, _ in layers)
+        dev = layers[0][0].device
+        wide = torch.zeros((rows, kmax), dtype=torch.float32, device=dev)
+        offs, r = [], 0
+        for w, _, _, _ in layers:
+            wide[r:r + w.shape[0], :w.shape[1]] = w
+            offs.append(r)
+            r += w.shape[0]
+        self.tw = TcWeight(wide)
+        self.n_out = layers[-1][0].shape[0]
+        self.n_planes = n_planes
+        self._keep = [b for _, b, _, _ in layers]
+        w_hi, w_lo, self._maps_keep = self.tw.maps(64)
+
+        L = CHAIN_MAX_LAYERS
+
+        class _Chain(ctypes.Structure):
+            _fields_ = [("n_layers", ctypes.c_int32), ("mode", ctypes.c_int32), ("k", ctypes.c_int32 * L),
+                        ("n", ctypes.c_int32 * L), ("w_row", ctypes.c_int32 * L), ("act", ctypes.c_int32 * L),
+                        ("slope", ctypes.c_float * L), ("bias", ctypes.c_void_p * L), ("w_hi_tmap", ctypes.c_void_p),
+                        ("w_lo_tmap", ctypes.c_void_p)]
+
+        c = _Chain()
+        c.n_layers, c.mode = len(layers), 3 if n_planes == 2 else 1
+        for i, (w, b, act, slope) in enumerate(layers):
+            c.k[i], c.n[i], c.w_row[i], c.act[i], c.slope[i] = w.shape[1], w.shape[0], offs[i], act, slope
+            c.bias[i] = b.data_ptr() if b is not None else None
+        c.w_hi_tmap, c.w_lo_tmap = w_hi, w_lo
+        self._struct = c
+        self.addr = ctypes.addressof(c)
+
+    @staticmethod
+    def supported(c1: int, dims) -> bool:
+        """dims: output widths of the chain layers.  Every width a multiple of 64 and <= 256."""
+        return (len(dims) >= 1 and len(dims) <= CHAIN_MAX_LAYERS and c1 % 64 == 0 and 64 <= c1 <= CHAIN_MAX_WIDTH and
+                all(d % 64 == 0 and 64 <= d <= CHAIN_MAX_WIDTH for d in dims))
+
+
+def sgcnn_fused(PQ: torch.Tensor, idx: torch.Tensor, act0: int, slope0: float, chain: ChainWeights, npl: int = 0,
+                cache=None) -> torch.Tensor:
+    """Dense SGCNN step in one kernel (ccn_sgcnn_fused): max_k chain(act0(P[idx[i][k]] + Q[i])), self loop included,
+    missing neighbours at -100.  -> fp32 (n, C_out); its activation planes are registered in `cache`."""
+    PQ, ld = _rows(PQ)
+    n, K = idx.shape
+    c1 = PQ.shape[1] // 2
+    out = _empty((n, chain.n_out), torch.float32, PQ)
+    pl = alloc_planes(n, chain.n_out, npl, PQ) if npl and cache is not None and n else None
+    call("ccn_sgcnn_fused", PQ, ld, idx, n, K, c1, act0, float(slope0), chain.addr, out, chain.n_out,
+         pl.buf if pl is not None else 0, pl.kpad if pl is not None else 0, pl.plane_stride if pl is not None else 0,
+         npl if pl is not None else 0)
+    if pl is not None:
+        cache.put_planes(out, pl)
+    return out
+
+
+FUSED_MAX_DEGREE = 64       # CSR tiles hold the targets whose first edge falls into a stride of 129 - max_degree rows
+
+
+def pointconv_fused(edges: EdgeCSR, chain: ChainWeights, agg: str, msg_layer: int, act0: int, slope0: float, c1: int,
+                    H: Optional[torch.Tensor] = None, wp: Optional[torch.Tensor] = None, bias0: Optional[torch.Tensor] = None,
+                    pos_src: Optional[torch.Tensor] = None, pos_dst: Optional[torch.Tensor] = None,
+                    radius: Optional[float] = None, PQ: Optional[torch.Tensor] = None, npl: int = 0, cache=None):
+    """Edge-MLP step over a CSR edge list in one kernel (ccn_pointconv_fused).  First layer either
+    act0(H[j] + Wp (pos_src[j] - pos_dst[i]) [/ radius] + bias0) (PointNetConv2.message) or act0(PQ[j][:c1] + PQ[i][c1:])
+    (sparse StaticEdgeConv); then the chain; then `agg` over every target's edges.  -> fp32 (nq, C_out)."""
+    assert edges.max_degree <= FUSED_MAX_DEGREE
+    like = PQ if PQ is not None else wp
+    out = _empty((edges.nq, chain.n_out), torch.float32, like)
+    pl = alloc_planes(edges.nq, chain.n_out, npl, like) if npl and cache is not None and edges.nq else None
+    n_tiles = edges.n_edges // (129 - edges.max_degree) + 1
+    scratch = _empty((4 * n_tiles,), torch.int32, like)
+    if PQ is not None:
+        PQ, ldpq = _rows(PQ)
+        a = (0, 0, 0, 0, 0, 0, PQ, ldpq)
+    else:
+        if H is not None:
+            H, ldh = _rows(H)
+        else:
+            ldh = 0
+        a = (H if H is not None else 0, ldh, wp, bias0 if bias0 is not None else 0, _f32(pos_src), _f32(pos_dst), 0, 0)
+    call("ccn_pointconv_fused", *a, edges.row_ptr, edges.erow, edges.ecol, edges.nq, edges.n_edges, edges.max_degree, c1,
+         float(radius or 0.0), act0, float(slope0), chain.addr, AGG[agg], msg_layer, scratch, out, chain.n_out,
+         pl.buf if pl is not None else 0, pl.kpad if pl is not None else 0, pl.plane_stride if pl is not None else 0,
+         npl if pl is not None else 0)
+    if pl is not None:
+        cache.put_planes(out, pl)
+    return out

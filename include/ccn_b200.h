@@ -400,6 +400,45 @@ int ccn_accumulate(const float* src, int64_t lds, int64_t n, int32_t C, float* a
 int ccn_mean_logsoftmax(const float* acc, int64_t lda, int64_t n, int32_t C, float scale, float* out, int64_t ldo,
                         int64_t* pred, ccn_stream_t stream);
 
+/* ---- fused edge-MLP steps (csrc/edge_fused.cu): gather -> layer 1 (decomposed) -> layers 2..n -> aggregate in ONE
+ * kernel, per-edge intermediates stay in shared memory / TMEM (tcgen05).  replaces the chain
+ *   frnn_gather + cat + nn(...) + masked max           (src/models/modules/dgcnn.py:166-189,  ccn_sgcnn_fused)
+ *   message + aggregate of PointNetConv2 / forward_slow (src/models/modules/point_conv.py:60-93, dgcnn.py:209-246,
+ *                                                        ccn_pointconv_fused)
+ * ccn_chain_t (HOST memory) describes the layers AFTER the decomposed first one: all their weights live in one
+ * bf16 matrix (rows = output channels of layer 0, 1, ... stacked at w_row[l], columns = input channels zero padded to
+ * the widest K rounded up to 64) in the ccn_split_bf16 layout with tensor maps of box 64 x 64 (ccn_weight_tensor_map(...,
+ * box_n = 64)); k[l] / n[l] multiples of 64, <= 256; k[0] = c1, k[l] = n[l-1]; bias[l] device pointers (BatchNorm
+ * folded) or null. */
+#define CCN_CHAIN_MAX_LAYERS 6
+typedef struct ccn_chain {
+    int32_t n_layers;
+    int32_t mode;                              /* 1 = bf16, 3 = split-bf16 x3 */
+    int32_t k[CCN_CHAIN_MAX_LAYERS], n[CCN_CHAIN_MAX_LAYERS], w_row[CCN_CHAIN_MAX_LAYERS], act[CCN_CHAIN_MAX_LAYERS];
+    float slope[CCN_CHAIN_MAX_LAYERS];
+    const float* bias[CCN_CHAIN_MAX_LAYERS];
+    const void* w_hi_tmap;                     /* host CUtensorMap of the hi plane (64-byte aligned) */
+    const void* w_lo_tmap;                     /* lo plane (mode 3) */
+} ccn_chain_t;
+/* dense SGCNN step: PQ (n, 2 c1) = [P | Q] per point, idx (n, K) int32 -1 padded; row (i, 0) = act0(P[i] + Q[i]) (self
+ * loop), row (i, 1+k) = act0(P[idx[i][k]] + Q[i]) (P = 0 for a missing neighbour); chain; out[i] = max over the K+1 rows,
+ * missing neighbours at -100.  out (n, ldo) fp32; planes (optional): the result's activation planes like
+ * ccn_group_max_dense_both.  K + 1 <= 128. */
+int ccn_sgcnn_fused(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c1, int32_t act0,
+                    float slope0, const ccn_chain_t* chain_host, float* out, int64_t ldo, void* planes, int64_t kpad,
+                    int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
+/* CSR edge step (targets = rows of row_ptr[0..nq], edges sorted by target, erow/ecol per edge, every target has at most
+ * max_degree edges): first layer act0(H[ecol] + Wp (pos_src[ecol] - pos_dst[erow]) [/ radius] + bias0) (PQ null; H may be
+ * null) or act0(PQ[ecol][0:c1] + PQ[erow][c1:2c1]) (PQ given); chain; agg = CCN_AGG_*; for WSUM / ATTEND the chain is
+ * local_nn's layers followed by attend_nn's, msg_layer = index of the chain layer whose output is the message.
+ * tile_scratch: 4 * (E / (129 - max_degree) + 1) int32, 16-byte aligned (tile table written by a pre-pass). */
+int ccn_pointconv_fused(const float* H, int64_t ldh, const float* wp, const float* bias0, const float* pos_src,
+                        const float* pos_dst, const float* PQ, int64_t ldpq, const int32_t* row_ptr, const int32_t* erow,
+                        const int32_t* ecol, int64_t nq, int64_t E, int32_t max_degree, int32_t c1, float radius,
+                        int32_t act0, float slope0, const ccn_chain_t* chain_host, int32_t agg, int32_t msg_layer,
+                        int32_t* tile_scratch, float* out, int64_t ldo, void* planes, int64_t kpad, int64_t plane_stride,
+                        int32_t n_planes, ccn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

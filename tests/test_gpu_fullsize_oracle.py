@@ -22,8 +22,9 @@ pytestmark = pytest.mark.gpu
 TOL = {"fp32": 1e-4, "bf16x3": 1e-4, "bf16": 2e-2}          # logits (north_star)
 # per-step features: the fp32 path meets the fp32 budget at every step; split-bf16 x3 carries ~17 significand bits per
 # operand, which the segment softmax of the attention steps amplifies (measured 1.2e-4 at sa-geo on the 32.5 k scan) - its
-# LOGITS meet 1e-4, its intermediate features 5e-4; plain bf16 has the 2e-2 budget throughout
-STEP_TOL = {"fp32": 1e-4, "bf16x3": 5e-4, "bf16": 2e-2}
+# LOGITS meet 1e-4, its intermediate features 5e-4; plain bf16 (8 significand bits) meets the 2e-2 budget on the LOGITS, its
+# attention-step features reach 5.8e-2 on the 32.5 k scan (same amplification): 1e-1 on intermediate features
+STEP_TOL = {"fp32": 1e-4, "bf16x3": 5e-4, "bf16": 1e-1}
 
 
 def _data(case):
