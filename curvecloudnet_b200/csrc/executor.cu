@@ -1,0 +1,911 @@
+// Native step executor of the per-scan forward (reference src/models/base.py:133-175 `ModelBase.forward / _apply_steps`
+// and the step modules of src/models/modules/{fast_conv1d,pointnet2,point_conv,dgcnn,mlp,skip_connect}.py), inference,
+// tensor-core precisions: ONE C-ABI call per forward.
+//
+// Why: the python executor (curvecloudnet_b200/model.py + modules.py) issues ~150 ctypes calls, ~270 torch.empty and ~15
+// blocking read-backs per 32 k-point scan - 5.1 ms of host time against ~4 ms of kernels (profiles/r01i_host_profile.txt),
+// so the B = 1 step was host-bound.  Here the same launches are issued from C++ out of a bump-allocated arena: the host
+// cost per launch is the driver's (~2-4 us), the data-dependent sizes are read back through one pinned buffer.
+//
+// The executor issues EXACTLY the C-ABI calls of the python path, in the same order with the same arguments (it calls
+// the library's own extern "C" entry points), so its logits are bit-identical to ModelBase's python executor -
+// tests/test_gpu_executor.py asserts that equality; parity against the oracle follows from the python path's tests.
+//
+// The model is described by a PLAN (two flat arrays, int64 and double, built once per weight version by
+// curvecloudnet_b200/executor.py from the prepared python modules: folded weights, bf16 planes, TMA descriptors).
+// Random draws of the reference (CurveFPS phase, VoxelFPS noise, FPS start; fps_ops.py:30,56, point_ops.py:64) come
+// through a callback in the reference's call order, so seeding torch identically reproduces the python path.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <deque>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxSamples = 4096;                 // ops.MAX_SAMPLES
+constexpr int64_t kSmemBudget = 227 * 1024 - 2560; // ops.SMEM_BUDGET
+constexpr int kBoxMinTiles = 74;                   // ops._BOX_MIN_TILES
+constexpr size_t kH2dRing = 256 * 1024;
+
+enum StepKind { ST_CONV_V2 = 1, ST_SA_GEO = 2, ST_MLP = 3, ST_SGCNN = 4, ST_SKIP = 5, ST_SA = 6, ST_FP = 7, ST_FP_GEO = 8 };
+enum { DOWN_VOXEL = 0, DOWN_FPS = 1 };
+enum { DRAW_CURVE_PHASE = 0, DRAW_VOXEL_NOISE = 1, DRAW_FPS_START = 2 };
+
+#define EX_CALL(expr)                    \
+    do {                                 \
+        const int rc__ = (expr);         \
+        if (rc__ != CCN_OK) return rc__; \
+    } while (0)
+#define EX_CUDA(expr)                              \
+    do {                                           \
+        const cudaError_t e__ = (expr);            \
+        if (e__ != cudaSuccess) return (int)e__;   \
+    } while (0)
+
+struct Linear {                // one prepared Linear use-site (a K-segmentation of a folded weight)
+    int n, k_true, kpad, act, nseg;
+    int seg_w[4];
+    float slope;
+    const float* bias;
+    const void *map_hi[4], *map_lo[4];   // host tensor maps for box_n = 32, 64, 128, 256 (null: not a candidate)
+};
+
+struct Conv {                  // one curve-convolution layer
+    int taps, cin, cout, tc;   // tc: runs as ccn_conv_planes (else the FP32-pipe tap kernel)
+    const float *w, *bias;     // (taps, cin, cout) folded fp32, (cout)
+    int lin;                   // tc: Linear entry (n = cout, kpad = taps * ceil64(cin)); maps as above
+};
+
+struct Chain { const ccn_chain_t* desc; int n_out; };
+
+struct Step {
+    int kind;
+    std::vector<int64_t> iv;   // kind-specific integers
+    std::vector<double> fv;    // kind-specific reals
+};
+
+struct Planes { void* buf = nullptr; int64_t kpad = 0, pstride = 0; };
+
+struct Feat {                  // an fp32 feature matrix and (lazily) its activation planes
+    float* f = nullptr;
+    int64_t ld = 0, n = 0;
+    int c = 0;
+    Planes pl;
+};
+
+struct Grid { float radius; int64_t cells; int32_t* cell_off; float* sorted; };
+struct KnnMemo { int K; float radius; int32_t* idx; };
+
+struct Level {                 // one point set of the pyramid
+    int64_t n = 0;
+    Feat pos;                  // (n, 3) positions as a feature matrix (its planes feed the `with_xyz` concatenations)
+    int64_t *batch = nullptr, *curve = nullptr;
+    bool has_sptr = false, has_topo = false;
+    int32_t* sptr_dev = nullptr;
+    std::vector<int> sptr;     // host copy of the sample CSR (B + 1)
+    int n_curves = 0, max_glob = 0;
+    int32_t *curve_ord = nullptr, *curve_ptr = nullptr;
+    std::vector<Grid> grids;
+    std::vector<KnnMemo> knn;
+};
+
+struct Exec {
+    int mode = 3, npl = 2;     // 1 = bf16, 3 = split-bf16 x3
+    int n_out = 0, in_c = 0;
+    std::vector<Linear> lins;
+    std::vector<Conv> convs;
+    std::vector<Chain> chains;
+    std::vector<Step> steps;
+    std::vector<int> skip_store;       // per step: its input is a skip-connection source (base.py:191-196)
+    std::vector<int> out_mlp;          // Linear ids of the final MLP
+    // per-forward state
+    char* arena = nullptr;
+    size_t cap = 0, off = 0;
+    bool oom = false;
+    int32_t* pinned = nullptr;         // host read-back buffer (kMaxSamples + 16 ints)
+    char* h2d_ring = nullptr;          // pinned staging of small host -> device copies (sample CSRs, FPS meta, the CurveFPS draw)
+    size_t h2d_off = 0;
+    float* noise_host = nullptr;       // pinned staging of the VoxelFPS noise draw
+    size_t noise_cap = 0;
+    cudaStream_t stream = nullptr;
+    ccn_draw_fn draw = nullptr;
+    void* draw_user = nullptr;
+    int topo_flags = 0;
+    std::deque<Feat> feats;
+    std::deque<Level> levels;
+
+    void* alloc(size_t bytes) {
+        const size_t a = (off + 255) & ~(size_t)255;
+        if (a + bytes > cap) { oom = true; off = a + bytes; return arena; }   // keep counting: the caller learns the need
+        off = a + bytes;
+        return arena + a;
+    }
+    template <typename T> T* alloc_n(int64_t n) { return (T*)alloc(sizeof(T) * (size_t)(n > 0 ? n : 1)); }
+    Feat* new_feat(int64_t n, int c) {
+        feats.emplace_back();
+        Feat& f = feats.back();
+        f.f = alloc_n<float>(n * c); f.ld = c > 0 ? c : 1; f.n = n; f.c = c;
+        return &f;
+    }
+    Planes alloc_planes(int64_t m, int k) {
+        Planes p;
+        p.kpad = (k + 15) / 16 * 16;
+        p.pstride = (m > 0 ? m : 1) * p.kpad;
+        p.buf = alloc((size_t)npl * p.pstride * 2);
+        return p;
+    }
+    int h2d(void* dst, const void* src, size_t bytes) {   // async copy through the pinned ring (the source may be reused at once)
+        if (bytes > kH2dRing) return CCN_EINVAL;
+        if (h2d_off + bytes > kH2dRing) h2d_off = 0;      // a forward stages far less than the ring between two of its read-backs
+        std::memcpy(h2d_ring + h2d_off, src, bytes);
+        const cudaError_t e = cudaMemcpyAsync(dst, h2d_ring + h2d_off, bytes, cudaMemcpyHostToDevice, stream);
+        h2d_off += (bytes + 15) & ~(size_t)15;
+        return e == cudaSuccess ? CCN_OK : (int)e;
+    }
+    int readback(const void* dev, int n_ints) {      // blocking read of n_ints int32 into `pinned`
+        if (oom) return CCN_ENOMEM;
+        EX_CUDA(cudaMemcpyAsync(pinned, dev, 4 * (size_t)n_ints, cudaMemcpyDeviceToHost, stream));
+        EX_CUDA(cudaStreamSynchronize(stream));
+        return CCN_OK;
+    }
+};
+
+// ---- helpers mirroring curvecloudnet_b200/ops.py / nn.py ------------------------------------------------------------
+int ensure_planes(Exec& ex, Feat* t) {               // nn.ForwardCache.planes_for
+    if (t->pl.buf) return CCN_OK;
+    t->pl = ex.alloc_planes(t->n, t->c);
+    if (ex.oom) return CCN_OK;
+    return ccn_pack_planes(t->f, t->ld, t->c, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, nullptr,
+                           t->n, t->pl.buf, t->pl.kpad, t->pl.pstride, ex.npl, (ccn_stream_t)ex.stream);
+}
+
+int pick_box(const Linear& L, int64_t m, int npl) {  // ops.TcWeight.pick_box_planes
+    const int cand[4] = {256, 128, 64, 32};
+    const int64_t tiles_m = (m + 127) / 128, nk = L.kpad / 64;
+    if (tiles_m >= 148) {
+        int last = 32;
+        for (int b : cand) {
+            if (!(b == 32 || b / 2 < L.n)) continue;
+            last = b;
+            if (nk * npl * b * 128 + 3 * npl * 16384 <= kSmemBudget) return b;
+        }
+        return last;
+    }
+    for (int b : cand) {
+        if (!(b == 32 || b / 2 < L.n)) continue;
+        if (tiles_m * ((L.n + b - 1) / b) >= kBoxMinTiles) return b;
+    }
+    return 32;
+}
+
+inline int box_slot(int b) { return b == 32 ? 0 : b == 64 ? 1 : b == 128 ? 2 : 3; }
+
+struct Seg { const void* buf; int64_t kpad, pstride; int k; };
+
+// ops.linear_planes: out_kind 0 = fp32, 1 = planes, 2 = both.  y (fp32) / yp (planes) are allocated here.
+int linear_planes(Exec& ex, const Linear& L, const Seg* segs, int nseg, int64_t M, int out_kind, Feat** y_out, Planes* yp_out) {
+    Feat* Y = nullptr;
+    Planes Yp;
+    if (out_kind != 1) Y = ex.new_feat(M, L.n);
+    if (out_kind != 0) Yp = ex.alloc_planes(M, L.n);
+    if (y_out) *y_out = Y;
+    if (yp_out) *yp_out = Yp;
+    if (Y && out_kind == 2) Y->pl = Yp;
+    if (ex.oom) return CCN_OK;
+    const int box = pick_box(L, M, ex.npl);
+    const int bs = box_slot(box);
+    if (!L.map_hi[bs]) return CCN_EINVAL;
+    Seg s[4] = {};
+    for (int i = 0; i < nseg; ++i) s[i] = segs[i];
+    return ccn_linear_planes(s[0].buf, s[0].kpad, s[0].pstride, s[0].k, s[1].buf, s[1].kpad, s[1].pstride, s[1].k, s[2].buf,
+                             s[2].kpad, s[2].pstride, s[2].k, s[3].buf, s[3].kpad, s[3].pstride, s[3].k, L.map_hi[bs],
+                             L.map_lo[bs], L.bias, Y ? Y->f : nullptr, L.n, Yp.buf, Yp.kpad, Yp.pstride, M, L.n, box, ex.mode,
+                             L.act, L.slope, (ccn_stream_t)ex.stream);
+}
+
+int segs_of(Exec& ex, Feat* const* parts, int np, Seg* segs) {   // nn.cat_features with a cache: one K-segment per block
+    for (int i = 0; i < np; ++i) {
+        EX_CALL(ensure_planes(ex, parts[i]));
+        segs[i] = Seg{parts[i]->pl.buf, parts[i]->pl.kpad, parts[i]->pl.pstride, parts[i]->c};
+    }
+    return CCN_OK;
+}
+
+// nn.mlp_to_features / MLP.forward_from over a concatenation: hidden layers write planes, the last writes `last_kind`
+int run_mlp(Exec& ex, const int64_t* lin_ids, int nl, Feat* const* parts, int np, int last_kind, Feat** out) {
+    Seg segs[4];
+    EX_CALL(segs_of(ex, parts, np, segs));
+    const int64_t M = parts[0]->n;
+    int nseg = np;
+    Planes cur;
+    for (int i = 0; i < nl; ++i) {
+        const Linear& L = ex.lins[lin_ids[i]];
+        const bool last = i == nl - 1;
+        Feat* y = nullptr;
+        Planes yp;
+        EX_CALL(linear_planes(ex, L, segs, nseg, M, last ? last_kind : 1, &y, &yp));
+        if (last) { *out = y; break; }
+        cur = yp;
+        segs[0] = Seg{cur.buf, cur.kpad, cur.pstride, L.n};
+        nseg = 1;
+    }
+    return CCN_OK;
+}
+
+int level_sptr(Exec& ex, Level* lv) {                 // nn.ForwardCache.sample_ptr -> ops.sample_ptr
+    if (lv->has_sptr) return CCN_OK;
+    int32_t* tail = ex.alloc_n<int32_t>(kMaxSamples + 1 + 4);
+    if (ex.oom) return CCN_OK;
+    EX_CALL(ccn_sample_ptr(lv->batch, lv->n, tail, tail + kMaxSamples + 1, kMaxSamples, (ccn_stream_t)ex.stream));
+    EX_CALL(ex.readback(tail + kMaxSamples + 1, 4));
+    const int B = ex.pinned[0], flags = ex.pinned[2];
+    if (flags) { ex.topo_flags = flags; return CCN_ETOPOLOGY; }
+    EX_CALL(ex.readback(tail, B + 1));
+    lv->sptr.assign(ex.pinned, ex.pinned + B + 1);
+    lv->sptr_dev = tail;
+    lv->has_sptr = true;
+    return CCN_OK;
+}
+
+int level_topo(Exec& ex, Level* lv) {                 // nn.ForwardCache.topology -> ops.curve_csr
+    if (lv->has_topo) return CCN_OK;
+    const int64_t n = lv->n;
+    int32_t* ord = ex.alloc_n<int32_t>(n);
+    int32_t* cptr = ex.alloc_n<int32_t>(n + 1);
+    int32_t* tail = ex.alloc_n<int32_t>(kMaxSamples + 1 + 4);
+    int64_t* soff = ex.alloc_n<int64_t>(kMaxSamples + 1);
+    int64_t* glob = ex.alloc_n<int64_t>(n);
+    if (ex.oom) return CCN_OK;
+    EX_CALL(ccn_curve_csr(lv->batch, lv->curve, n, ord, cptr, tail, soff, glob, tail + kMaxSamples + 1, kMaxSamples,
+                          (ccn_stream_t)ex.stream));
+    EX_CALL(ex.readback(tail + kMaxSamples + 1, 4));
+    const int B = ex.pinned[0], n_curves = ex.pinned[1], flags = ex.pinned[2], max_glob = ex.pinned[3];
+    if (flags) { ex.topo_flags = flags; return CCN_ETOPOLOGY; }
+    if (!lv->has_sptr) {
+        EX_CALL(ex.readback(tail, B + 1));
+        lv->sptr.assign(ex.pinned, ex.pinned + B + 1);
+        lv->sptr_dev = tail;
+        lv->has_sptr = true;
+    }
+    lv->n_curves = n_curves; lv->max_glob = max_glob; lv->curve_ord = ord; lv->curve_ptr = cptr;
+    lv->has_topo = true;
+    return CCN_OK;
+}
+
+// ops._finish_subset: sample CSR of the selected level + its size with ONE read-back (extra: more ints behind `count_dev`)
+int finish_subset(Exec& ex, Level* parent, int64_t* idx_buf, int64_t capacity, const int32_t* count_dev, Level* child) {
+    const int B = (int)parent->sptr.size() - 1;
+    int32_t* out = ex.alloc_n<int32_t>(B + 1);
+    if (ex.oom) return CCN_OK;
+    EX_CALL(ccn_subset_sample_ptr(parent->batch, idx_buf, count_dev, capacity, B, out, (ccn_stream_t)ex.stream));
+    EX_CALL(ex.readback(out, B + 1));
+    child->sptr.assign(ex.pinned, ex.pinned + B + 1);
+    child->sptr_dev = out;
+    child->has_sptr = true;
+    child->n = child->sptr[B];
+    return CCN_OK;
+}
+
+// modules._subset: (pos[idx], batch[idx], curve[idx]) + the planes of the new positions
+int subset_level(Exec& ex, Level* parent, const int64_t* idx, Level* child) {
+    const int64_t n = child->n;
+    child->pos.f = ex.alloc_n<float>(n * 3); child->pos.ld = 3; child->pos.n = n; child->pos.c = 3;
+    child->batch = ex.alloc_n<int64_t>(n);
+    child->curve = parent->curve ? ex.alloc_n<int64_t>(n) : nullptr;
+    if (n) child->pos.pl = ex.alloc_planes(n, 3);
+    if (ex.oom || n == 0) return CCN_OK;
+    return ccn_subset_gather(parent->pos.f, parent->pos.ld, parent->batch, parent->curve, idx, n, child->pos.f, child->batch,
+                             child->curve, child->pos.pl.buf, child->pos.pl.pstride, ex.npl, (ccn_stream_t)ex.stream);
+}
+
+// ops.frnn_knn: grid of (pos2, radius) memoised per level; self-queries (pos1 is pos2) memoised per (K, radius)
+int frnn(Exec& ex, Level* q, Level* src, int K, float radius, bool want_cnt, int32_t** idx_out, int32_t** cnt_out) {
+    const bool self = q == src;
+    if (self && !want_cnt)
+        for (const KnnMemo& m : src->knn)
+            if (m.K == K && m.radius == radius) { *idx_out = m.idx; return CCN_OK; }
+    const Grid* g = nullptr;
+    for (const Grid& gg : src->grids)
+        if (gg.radius == radius) g = &gg;
+    if (!g) {
+        Grid ng;
+        ng.radius = radius;
+        ng.cells = ccn_grid_num_cells(src->n);
+        ng.cell_off = ex.alloc_n<int32_t>(ng.cells + 1);
+        int32_t* slot = ex.alloc_n<int32_t>(src->n);
+        ng.sorted = ex.alloc_n<float>(4 * (src->n > 0 ? src->n : 1));
+        if (!ex.oom)
+            EX_CALL(ccn_grid_build(src->pos.f, src->batch, src->n, radius, ng.cells, ng.cell_off, slot, ng.sorted,
+                                   (ccn_stream_t)ex.stream));
+        src->grids.push_back(ng);
+        g = &src->grids.back();
+    }
+    int32_t* idx = ex.alloc_n<int32_t>(q->n * K);
+    int32_t* cnt = want_cnt ? ex.alloc_n<int32_t>(q->n + 2) : nullptr;
+    *idx_out = idx;
+    if (cnt_out) *cnt_out = cnt;
+    if (ex.oom) return CCN_OK;
+    EX_CALL(ccn_frnn_knn(q->pos.f, q->batch, q->n, g->sorted, g->cell_off, g->cells, src->sptr_dev, radius, K, idx, nullptr, cnt,
+                         (ccn_stream_t)ex.stream));
+    if (self && !want_cnt) src->knn.push_back(KnnMemo{K, radius, idx});
+    return CCN_OK;
+}
+
+struct Edges { int32_t *row_ptr, *erow, *ecol; int64_t E, nq; int max_degree; };
+
+// PointNetConv2.forward_edges (inference): decomposed first layer, fused chain kernel or the unfused launches
+int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts, int nxp, Level* src, Level* dst,
+              const Edges& e, Feat** out) {
+    // iv: lin_x, wp_ptr, bias0_ptr, c1, act0, agg, chain (-1: none), n_local (layers after the first), local lin ids[n_local],
+    //     n_att, attend lin ids[n_att];  fv: slope0, normalize_radius (0: none)
+    const Linear* lin_x = iv[0] >= 0 ? &ex.lins[iv[0]] : nullptr;
+    const float* wp = (const float*)iv[1];
+    const float* bias0 = (const float*)iv[2];
+    const int c1 = (int)iv[3], act0 = (int)iv[4], agg = (int)iv[5], chain = (int)iv[6], n_local = (int)iv[7];
+    const int64_t* local_ids = iv + 8;
+    const int n_att = (int)iv[8 + n_local];
+    const int64_t* att_ids = iv + 9 + n_local;
+    const float slope0 = (float)fv[0], nradius = (float)fv[1];
+    Feat* H = nullptr;
+    if (lin_x) {
+        Seg segs[4];
+        EX_CALL(segs_of(ex, xparts, nxp, segs));
+        EX_CALL(linear_planes(ex, *lin_x, segs, nxp, xparts[0]->n, 0, &H, nullptr));
+    }
+    const bool att = agg == CCN_AGG_ATTEND || agg == CCN_AGG_WSUM;
+    if (chain >= 0 && e.max_degree <= 64) {
+        const Chain& ch = ex.chains[chain];
+        Feat* o = ex.new_feat(e.nq, ch.n_out);
+        if (e.nq) o->pl = ex.alloc_planes(e.nq, ch.n_out);
+        const int64_t n_tiles = e.E / (129 - e.max_degree) + 1;
+        int32_t* scratch = ex.alloc_n<int32_t>(4 * n_tiles);
+        *out = o;
+        if (ex.oom) return CCN_OK;
+        return ccn_pointconv_fused(H ? H->f : nullptr, H ? H->ld : 0, wp, bias0, src->pos.f, dst->pos.f, nullptr, 0, e.row_ptr,
+                                   e.erow, e.ecol, e.nq, e.E, e.max_degree, c1, nradius, act0, slope0, ch.desc, agg,
+                                   att ? n_local - 1 : -1, scratch, o->f, o->ld, o->pl.buf, o->pl.kpad, o->pl.pstride,
+                                   o->pl.buf ? ex.npl : 0, (ccn_stream_t)ex.stream);
+    }
+    // unfused: ccn_edge_layer1_planes -> Linear launches -> ccn_seg_aggregate_both
+    if (n_local < 1 || (c1 & 15) || (H && (H->ld & 3))) return CCN_EUNSUPPORTED;
+    Planes msg0 = ex.alloc_planes(e.E, c1);
+    if (!ex.oom)
+        EX_CALL(ccn_edge_layer1_planes(H ? H->f : nullptr, H ? H->ld : 0, wp, bias0, src->pos.f, dst->pos.f, e.erow, e.ecol, e.E, c1,
+                                       nradius, act0, slope0, msg0.buf, msg0.kpad, msg0.pstride, ex.npl, (ccn_stream_t)ex.stream));
+    Seg seg{msg0.buf, msg0.kpad, msg0.pstride, c1};
+    Feat* msg = nullptr;
+    Planes msgp;
+    for (int i = 0; i < n_local; ++i) {
+        const Linear& L = ex.lins[local_ids[i]];
+        const bool last = i == n_local - 1;
+        Feat* y = nullptr;
+        Planes yp;
+        EX_CALL(linear_planes(ex, L, &seg, 1, e.E, last ? (att ? 2 : 0) : 1, &y, &yp));
+        if (last) { msg = y; msgp = yp; }
+        else seg = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
+    }
+    Feat* attf = nullptr;
+    if (att) {
+        seg = Seg{msgp.buf, msgp.kpad, msgp.pstride, msg->c};
+        for (int i = 0; i < n_att; ++i) {
+            const Linear& L = ex.lins[att_ids[i]];
+            const bool last = i == n_att - 1;
+            Feat* y = nullptr;
+            Planes yp;
+            EX_CALL(linear_planes(ex, L, &seg, 1, e.E, last ? 0 : 1, &y, &yp));
+            if (last) attf = y;
+            else seg = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
+        }
+    }
+    const int c = msg->c;
+    Feat* o = ex.new_feat(e.nq, c);
+    *out = o;
+    const bool both = e.nq > 0 && (c % 16) == 0;       // ops._both_ok (fp32 rows from our allocator are 256-byte aligned, ld % 4 == 0)
+    if (both) o->pl = ex.alloc_planes(e.nq, c);
+    if (ex.oom) return CCN_OK;
+    if (both)
+        return ccn_seg_aggregate_both(msg->f, msg->ld, attf ? attf->f : nullptr, attf ? attf->ld : 0, e.row_ptr, e.nq, c, agg, o->f,
+                                      o->ld, o->pl.buf, o->pl.kpad, o->pl.pstride, ex.npl, (ccn_stream_t)ex.stream);
+    return ccn_seg_aggregate(msg->f, msg->ld, attf ? attf->f : nullptr, attf ? attf->ld : 0, e.row_ptr, e.nq, c, agg, o->f, o->ld,
+                             (ccn_stream_t)ex.stream);
+}
+
+// ops.dense_to_csr: (nq, K) table + per-row counts -> CSR (one read-back for E)
+int dense_to_csr(Exec& ex, int32_t* idx, int32_t* cnt, int64_t nq, int K, Edges* e) {
+    if (ex.oom) { *e = Edges{cnt, nullptr, nullptr, 0, nq, K}; return CCN_OK; }
+    EX_CALL(ccn_excl_scan_i32(cnt, nq, cnt + nq + 1, (ccn_stream_t)ex.stream));
+    EX_CALL(ex.readback(cnt + nq + 1, 1));
+    const int64_t E = ex.pinned[0];
+    int32_t* erow = ex.alloc_n<int32_t>(E);
+    int32_t* ecol = ex.alloc_n<int32_t>(E);
+    *e = Edges{cnt, erow, ecol, E, nq, K};
+    if (ex.oom) return CCN_OK;
+    return ccn_dense_to_csr(idx, cnt, nq, K, erow, ecol, (ccn_stream_t)ex.stream);
+}
+
+}  // namespace
+
+struct ccn_exec {
+    Exec ex;
+};
+
+extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* fplan, int64_t n_f, ccn_exec_t** out) {
+    CCN_REQUIRE(iplan && fplan && out && n_i >= 8);
+    ccn_exec* h = new ccn_exec();
+    Exec& ex = h->ex;
+    int64_t ci = 0, cf = 0;
+    auto I = [&]() -> int64_t { return ci < n_i ? iplan[ci++] : 0; };
+    auto F = [&]() -> double { return cf < n_f ? fplan[cf++] : 0.0; };
+    const int64_t magic = I();
+    if (magic != 0xCC9E0002) { delete h; return CCN_EINVAL; }
+    ex.mode = (int)I(); ex.npl = ex.mode == 3 ? 2 : 1;
+    ex.in_c = (int)I(); ex.n_out = (int)I();
+    const int n_lin = (int)I(), n_conv = (int)I(), n_chain = (int)I(), n_step = (int)I();
+    for (int i = 0; i < n_lin; ++i) {
+        Linear L;
+        L.n = (int)I(); L.k_true = (int)I(); L.kpad = (int)I(); L.act = (int)I(); L.nseg = (int)I();
+        for (int s = 0; s < 4; ++s) L.seg_w[s] = (int)I();
+        L.bias = (const float*)I();
+        for (int b = 0; b < 4; ++b) L.map_hi[b] = (const void*)I();
+        for (int b = 0; b < 4; ++b) L.map_lo[b] = (const void*)I();
+        L.slope = (float)F();
+        ex.lins.push_back(L);
+    }
+    for (int i = 0; i < n_conv; ++i) {
+        Conv c;
+        c.taps = (int)I(); c.cin = (int)I(); c.cout = (int)I(); c.tc = (int)I();
+        c.w = (const float*)I(); c.bias = (const float*)I(); c.lin = (int)I();
+        ex.convs.push_back(c);
+    }
+    for (int i = 0; i < n_chain; ++i) {
+        Chain c;
+        c.desc = (const ccn_chain_t*)I(); c.n_out = (int)I();
+        ex.chains.push_back(c);
+    }
+    for (int i = 0; i < n_step; ++i) {
+        Step s;
+        s.kind = (int)I();
+        ex.skip_store.push_back((int)I());
+        const int ni = (int)I(), nf = (int)I();
+        for (int k = 0; k < ni; ++k) s.iv.push_back(I());
+        for (int k = 0; k < nf; ++k) s.fv.push_back(F());
+        ex.steps.push_back(s);
+    }
+    const int n_om = (int)I();
+    for (int i = 0; i < n_om; ++i) ex.out_mlp.push_back((int)I());
+    if (ci != n_i || cf != n_f) { delete h; return CCN_EINVAL; }
+    if (cudaHostAlloc((void**)&ex.pinned, sizeof(int32_t) * (kMaxSamples + 16), cudaHostAllocDefault) != cudaSuccess ||
+        cudaHostAlloc((void**)&ex.h2d_ring, kH2dRing, cudaHostAllocDefault) != cudaSuccess) {
+        delete h;
+        return CCN_EINVAL;
+    }
+    *out = h;
+    return CCN_OK;
+}
+
+extern "C" void ccn_exec_destroy(ccn_exec_t* h) {
+    if (!h) return;
+    if (h->ex.pinned) cudaFreeHost(h->ex.pinned);
+    if (h->ex.h2d_ring) cudaFreeHost(h->ex.h2d_ring);
+    if (h->ex.noise_host) cudaFreeHost(h->ex.noise_host);
+    delete h;
+}
+
+extern "C" int32_t ccn_exec_topology_flags(const ccn_exec_t* h) { return h ? h->ex.topo_flags : 0; }
+
+namespace {
+
+int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const int64_t* batch, const int64_t* curve, int64_t n,
+                float* logits, int64_t ld_logits) {
+    ex.feats.clear();
+    ex.levels.clear();
+    ex.topo_flags = 0;
+    ccn_stream_t st = (ccn_stream_t)ex.stream;
+
+    ex.levels.emplace_back();
+    Level* lv0 = &ex.levels.back();
+    lv0->n = n;
+    lv0->pos.f = const_cast<float*>(pos); lv0->pos.ld = 3; lv0->pos.n = n; lv0->pos.c = 3;
+    lv0->batch = const_cast<int64_t*>(batch);
+    lv0->curve = const_cast<int64_t*>(curve);
+    Feat* x0 = nullptr;
+    if (x) {
+        ex.feats.emplace_back();
+        x0 = &ex.feats.back();
+        x0->f = const_cast<float*>(x); x0->ld = ldx; x0->n = n; x0->c = ex.in_c;
+    }
+    // hist[i] = INPUT of step i (base.py:138: the lists start with the raw input)
+    struct State { Feat* x; Level* lv; };
+    std::vector<State> hist;
+    std::vector<int64_t*> down_idx;
+    std::vector<int> prop_stack, down_stack;
+    State cur{x0, lv0};
+    hist.push_back(cur);
+
+    for (size_t si = 0; si < ex.steps.size(); ++si) {
+        const Step& s = ex.steps[si];
+        const int64_t* iv = s.iv.data();
+        const double* fv = s.fv.data();
+        State outp = cur;
+        int64_t* didx = nullptr;
+        switch (s.kind) {
+            case ST_CONV_V2: {
+                // iv: with_xyz, with_diff, ksize, n_layers, tc_from, conv ids[n_layers]
+                const int with_xyz = (int)iv[0], with_diff = (int)iv[1], ksize = (int)iv[2], nl = (int)iv[3], tc_from = (int)iv[4];
+                Level* lv = cur.lv;
+                EX_CALL(level_topo(ex, lv));
+                const int64_t np = lv->n;
+                const int cx = cur.x ? cur.x->c : 0;
+                const int c_in = cx + (with_xyz ? 3 : 0);
+                Feat* feats = ex.new_feat(np, c_in * (with_diff ? 2 : 1));
+                if (!ex.oom)
+                    EX_CALL(ccn_curve_feat_prep(cur.x ? cur.x->f : nullptr, cur.x ? cur.x->ld : 0, cx, lv->pos.f, with_xyz, with_diff,
+                                                lv->curve_ord, np, feats->f, feats->ld, st));
+                const int pad = ksize > 1 ? (ksize / 2) * nl : 0;
+                const int64_t rows = np + (int64_t)(lv->n_curves + 1) * pad;
+                int32_t* row2pt = ex.alloc_n<int32_t>(rows);
+                if (!ex.oom) EX_CALL(ccn_curve_row_map(lv->curve_ord, np, lv->n_curves, pad, row2pt, st));
+                const int tcf = rows > 0 ? tc_from : nl;
+                Feat* sig = feats;
+                Planes sigp;
+                bool have_p = false;
+                for (int li = 0; li < nl; ++li) {
+                    const Conv& cv = ex.convs[iv[5 + li]];
+                    const bool first = li == 0, last = li == nl - 1;
+                    if (li >= tcf) {
+                        if (first) {
+                            Feat* g = ex.new_feat(rows, feats->c);
+                            if (!ex.oom && rows)
+                                EX_CALL(ccn_gather_rows_i32(feats->f, feats->ld, row2pt, rows, feats->c, g->f, g->ld, st));
+                            EX_CALL(ensure_planes(ex, g));
+                            sigp = g->pl; have_p = true;
+                        } else if (!have_p) {
+                            EX_CALL(ensure_planes(ex, sig));
+                            sigp = sig->pl; have_p = true;
+                        }
+                        const Linear& L = ex.lins[cv.lin];
+                        const int box = pick_box(L, rows, ex.npl);
+                        const int bs = box_slot(box);
+                        if (last) {
+                            Feat* y = ex.new_feat(np, cv.cout);
+                            y->pl = ex.alloc_planes(np, cv.cout);
+                            if (!ex.oom)
+                                EX_CALL(ccn_conv_planes(sigp.buf, sigp.kpad, sigp.pstride, cv.cin, cv.taps, L.map_hi[bs], L.map_lo[bs],
+                                                        cv.bias, y->f, cv.cout, y->pl.buf, y->pl.kpad, y->pl.pstride, rows, cv.cout,
+                                                        box, ex.mode, CCN_ACT_LEAKY, 0.01f, row2pt, st));
+                            sig = y;
+                        } else {
+                            Planes yp = ex.alloc_planes(rows, cv.cout);
+                            if (!ex.oom)
+                                EX_CALL(ccn_conv_planes(sigp.buf, sigp.kpad, sigp.pstride, cv.cin, cv.taps, L.map_hi[bs], L.map_lo[bs],
+                                                        cv.bias, nullptr, cv.cout, yp.buf, yp.kpad, yp.pstride, rows, cv.cout, box,
+                                                        ex.mode, CCN_ACT_LEAKY, 0.01f, nullptr, st));
+                            sigp = yp;
+                        }
+                        continue;
+                    }
+                    Feat* y = ex.new_feat(last ? np : rows, cv.cout);
+                    if (!ex.oom)
+                        EX_CALL(ccn_curve_conv_layer(sig->f, sig->ld, cv.w, cv.bias, y->f, cv.cout, row2pt, rows, cv.cin, cv.cout, ksize,
+                                                     first, last, 0.01f, st));
+                    sig = y;
+                }
+                outp.x = sig;
+                break;
+            }
+            case ST_MLP:
+            case ST_SKIP: {
+                // MLP: iv: with_xyz, n_layers, lin ids;  SKIP: iv: num_skips, n_layers, lin ids
+                const int nl = (int)iv[1];
+                Feat* parts[4];
+                int np = 0;
+                if (s.kind == ST_MLP) {
+                    if (cur.x) parts[np++] = cur.x;
+                    if (iv[0] || !cur.x) parts[np++] = &cur.lv->pos;
+                } else {
+                    const int ns = (int)iv[0];
+                    if ((int)prop_stack.size() < ns || ns + 1 > 4) return CCN_EINVAL;
+                    parts[np++] = cur.x;
+                    for (int k = 0; k < ns; ++k) {
+                        const State& h = hist[prop_stack[prop_stack.size() - ns + k]];
+                        parts[np++] = h.x ? h.x : &h.lv->pos;
+                    }
+                    prop_stack.resize(prop_stack.size() - ns);
+                }
+                Feat* y = nullptr;
+                EX_CALL(run_mlp(ex, iv + 2, nl, parts, np, 2, &y));
+                outp.x = y;
+                break;
+            }
+            case ST_SGCNN: {
+                // iv: with_xyz, K, lin_pq, act0, chain (-1), n_rest, rest lin ids;  fv: radius, slope0
+                const int with_xyz = (int)iv[0], K = (int)iv[1], act0 = (int)iv[3], chain = (int)iv[4], n_rest = (int)iv[5];
+                const float radius = (float)fv[0], slope0 = (float)fv[1];
+                Level* lv = cur.lv;
+                EX_CALL(level_sptr(ex, lv));
+                Feat* parts[2];
+                int np = 0;
+                if (cur.x) parts[np++] = cur.x;
+                if (with_xyz || !cur.x) parts[np++] = &lv->pos;
+                Seg segs[4];
+                EX_CALL(segs_of(ex, parts, np, segs));
+                Feat* PQ = nullptr;
+                EX_CALL(linear_planes(ex, ex.lins[iv[2]], segs, np, lv->n, 0, &PQ, nullptr));
+                int32_t* nbr = nullptr;
+                EX_CALL(frnn(ex, lv, lv, K, radius, false, &nbr, nullptr));
+                const int c1 = PQ->c / 2;
+                if (chain >= 0) {
+                    const Chain& ch = ex.chains[chain];
+                    Feat* o = ex.new_feat(lv->n, ch.n_out);
+                    if (lv->n) o->pl = ex.alloc_planes(lv->n, ch.n_out);
+                    if (!ex.oom)
+                        EX_CALL(ccn_sgcnn_fused(PQ->f, PQ->ld, nbr, lv->n, K, c1, act0, slope0, ch.desc, o->f, o->ld, o->pl.buf, o->pl.kpad,
+                                                o->pl.pstride, o->pl.buf ? ex.npl : 0, st));
+                    outp.x = o;
+                    break;
+                }
+                if (n_rest < 1 || (c1 & 15)) return CCN_EUNSUPPORTED;
+                const int64_t rows = lv->n * (K + 1);
+                Planes h = ex.alloc_planes(rows, c1);
+                if (!ex.oom)
+                    EX_CALL(ccn_sgcnn_layer1_planes(PQ->f, PQ->ld, nbr, lv->n, K, c1, act0, slope0, h.buf, h.kpad, h.pstride, ex.npl, st));
+                Seg seg{h.buf, h.kpad, h.pstride, c1};
+                Feat* y = nullptr;
+                for (int i = 0; i < n_rest; ++i) {
+                    const Linear& L = ex.lins[iv[6 + i]];
+                    const bool last = i == n_rest - 1;
+                    Planes yp;
+                    EX_CALL(linear_planes(ex, L, &seg, 1, rows, last ? 0 : 1, &y, &yp));
+                    if (!last) seg = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
+                }
+                Feat* o = ex.new_feat(lv->n, y->c);
+                const bool both = lv->n > 0 && (y->c % 16) == 0;
+                if (both) o->pl = ex.alloc_planes(lv->n, y->c);
+                if (!ex.oom) {
+                    if (both)
+                        EX_CALL(ccn_group_max_dense_both(y->f, y->ld, nbr, lv->n, K, y->c, o->f, o->ld, o->pl.buf, o->pl.kpad,
+                                                         o->pl.pstride, ex.npl, st));
+                    else
+                        EX_CALL(ccn_group_max_dense(y->f, y->ld, nbr, lv->n, K, y->c, o->f, o->ld, st));
+                }
+                outp.x = o;
+                break;
+            }
+            case ST_SA_GEO:
+            case ST_SA: {
+                // SA_GEO: iv: with_xyz, use_curve_fps, [pointconv block];  fv: arclen, ratio, radius, [slope0, nradius]
+                // SA:     iv: down, K, [pointconv block];                  fv: voxel, ratio, radius, [slope0, nradius]
+                Level* lv = cur.lv;
+                ex.levels.emplace_back();
+                Level* ch = &ex.levels.back();
+                int64_t* idx = nullptr;
+                Edges e{};
+                const float radius = (float)fv[2];
+                if (s.kind == ST_SA_GEO) {
+                    EX_CALL(level_topo(ex, lv));
+                    if (lv->max_glob != lv->n_curves) return CCN_EUNSUPPORTED;   // ops.radius_1d_group: curve ids with gaps
+                }
+                EX_CALL(level_sptr(ex, lv));
+                if (ex.oom) return CCN_ENOMEM;
+                const int B = (int)lv->sptr.size() - 1;
+                const bool curve_fps = s.kind == ST_SA_GEO && iv[1];
+                const int down = s.kind == ST_SA ? (int)iv[0] : DOWN_FPS;
+                if (curve_fps) {
+                    // ops.curve_fps
+                    float u = 0.f;
+                    ex.draw(ex.draw_user, DRAW_CURVE_PHASE, 1, &u);
+                    float* run = ex.alloc_n<float>((lv->n > 0 ? lv->n : 1) + (lv->n + 4095) / 4096);
+                    idx = ex.alloc_n<int64_t>(lv->n);
+                    int32_t* cnt = ex.alloc_n<int32_t>(1);
+                    float* udev = ex.alloc_n<float>(1);
+                    if (!ex.oom) {
+                        EX_CALL(ex.h2d(udev, &u, 4));
+                        EX_CALL(ccn_curve_fps(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->n, udev, (float)fv[0], run, idx, cnt, st));
+                        EX_CALL(finish_subset(ex, lv, idx, lv->n > 0 ? lv->n : 1, cnt, ch));
+                    }
+                } else if (down == DOWN_VOXEL) {
+                    // ops.voxel_fps
+                    const int64_t n1 = lv->n > 0 ? lv->n : 1;
+                    const int64_t slots = ccn_voxel_table_slots(lv->n);
+                    uint64_t* table = ex.alloc_n<uint64_t>(2 * slots + n1);
+                    int32_t* ints = ex.alloc_n<int32_t>(2 * n1 + 2);
+                    idx = ex.alloc_n<int64_t>(n1);
+                    float* noise = ex.alloc_n<float>(n1);
+                    if ((size_t)n1 > ex.noise_cap) {
+                        if (ex.noise_host) cudaFreeHost(ex.noise_host);
+                        ex.noise_cap = (size_t)n1 * 2;
+                        EX_CUDA(cudaHostAlloc((void**)&ex.noise_host, 4 * ex.noise_cap, cudaHostAllocDefault));
+                    }
+                    ex.draw(ex.draw_user, DRAW_VOXEL_NOISE, lv->n, ex.noise_host);
+                    if (!ex.oom) {
+                        EX_CUDA(cudaMemcpyAsync(noise, ex.noise_host, 4 * (size_t)lv->n, cudaMemcpyHostToDevice, ex.stream));
+                        int32_t* counts = ints + 2 * n1;
+                        EX_CALL(ccn_voxel_fps(lv->pos.f, lv->batch, lv->n, (float)fv[0], noise, slots, table, table + slots,
+                                              table + 2 * slots, ints, ints + n1, idx, counts, st));
+                        EX_CALL(finish_subset(ex, lv, idx, n1, counts, ch));
+                        EX_CALL(ex.readback(counts + 1, 1));
+                        if (ex.pinned[0]) return CCN_EVOXEL_RANGE;
+                    }
+                } else {
+                    // modules.fps_sorted: K = ceil(len * ratio) in f32, random start per cloud, sorted result
+                    std::vector<int32_t> meta(2 * B);
+                    const float ratio = (float)fv[1];
+                    int64_t total = 0;
+                    int max_len = 0;
+                    ch->sptr.assign(1, 0);
+                    for (int b = 0; b < B; ++b) {
+                        const int len = lv->sptr[b + 1] - lv->sptr[b];
+                        meta[b] = (int32_t)std::ceil((float)len * ratio);     // torch.ceil(int64 tensor * python float) -> f32 (point_ops.py:63)
+                        max_len = len > max_len ? len : max_len;
+                    }
+                    for (int b = 0; b < B; ++b) {
+                        const int len = lv->sptr[b + 1] - lv->sptr[b];
+                        meta[B + b] = (int32_t)ex.draw(ex.draw_user, DRAW_FPS_START, len, nullptr);
+                    }
+                    for (int b = 0; b < B; ++b) {
+                        const int len = lv->sptr[b + 1] - lv->sptr[b];
+                        total += meta[b] < len ? meta[b] : len;
+                        ch->sptr.push_back((int)total);
+                    }
+                    int32_t* mdev = ex.alloc_n<int32_t>(2 * B);
+                    float* closest = max_len > 512 * 16 ? ex.alloc_n<float>(lv->n) : nullptr;
+                    int32_t* sel = ex.alloc_n<int32_t>(lv->n);
+                    idx = ex.alloc_n<int64_t>(total);
+                    int32_t* sdev = ex.alloc_n<int32_t>(B + 1);
+                    ch->n = total; ch->has_sptr = true; ch->sptr_dev = sdev;
+                    if (!ex.oom) {
+                        EX_CALL(ex.h2d(mdev, meta.data(), 4 * (size_t)(2 * B)));
+                        EX_CALL(ccn_fps(lv->pos.f, lv->sptr_dev, B, lv->n, mdev, mdev + B, max_len, closest, sel, idx, nullptr, st));
+                        EX_CALL(ex.h2d(sdev, ch->sptr.data(), 4 * (size_t)(B + 1)));
+                    }
+                }
+                if (ex.oom) return CCN_ENOMEM;
+                const int64_t* pc_iv;
+                const double* pc_fv = fv + 3;
+                Feat* xparts[2];
+                int nxp = 0;
+                if (s.kind == ST_SA_GEO) {
+                    // ops.radius_1d_group
+                    const int64_t nq = ch->n;
+                    float* kc = ex.alloc_n<float>(lv->n_curves);
+                    int32_t* buf = ex.alloc_n<int32_t>(nq + 4);
+                    int64_t E = 0;
+                    int max_deg = 1;
+                    if (!ex.oom) {
+                        EX_CALL(ccn_radius_1d_group_count(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->curve, lv->n, lv->n_curves, idx, nq,
+                                                          radius, kc, buf + nq + 2, buf, buf + nq + 1, st));
+                        EX_CALL(ex.readback(buf + nq + 1, 3));
+                        E = ex.pinned[0];
+                        float kf, nf;
+                        std::memcpy(&kf, &ex.pinned[1], 4);
+                        std::memcpy(&nf, &ex.pinned[2], 4);
+                        const float m = kf < nf ? kf : nf;
+                        max_deg = m >= 1.f ? (int)m : 1;
+                    }
+                    int32_t* col = ex.alloc_n<int32_t>(E);
+                    int32_t* erow = ex.alloc_n<int32_t>(E);
+                    if (!ex.oom) {
+                        EX_CALL(ccn_radius_1d_group_fill(lv->curve_ord, lv->curve, lv->n, lv->n_curves, idx, nq, kc, buf + nq + 2, buf, col, st));
+                        EX_CALL(ccn_csr_rows(buf, nq, erow, st));
+                    }
+                    e = Edges{buf, erow, col, E, nq, max_deg};
+                    EX_CALL(subset_level(ex, lv, idx, ch));
+                    pc_iv = iv + 2;
+                    if (cur.x) xparts[nxp++] = cur.x;
+                    if (iv[0] || !cur.x) xparts[nxp++] = &lv->pos;
+                } else {
+                    const int K = (int)iv[1];
+                    EX_CALL(subset_level(ex, lv, idx, ch));
+                    int32_t *nbr = nullptr, *cnt = nullptr;
+                    EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));
+                    EX_CALL(dense_to_csr(ex, nbr, cnt, ch->n, K, &e));
+                    pc_iv = iv + 2;
+                    if (cur.x) xparts[nxp++] = cur.x;
+                }
+                Feat* o = nullptr;
+                EX_CALL(pointconv(ex, pc_iv, pc_fv, xparts, nxp, lv, ch, e, &o));
+                outp.x = o;
+                outp.lv = ch;
+                if (s.kind == ST_SA_GEO) didx = idx;
+                break;
+            }
+            case ST_FP:
+            case ST_FP_GEO: {
+                // iv: knn, with_xyz, n_layers, lin ids
+                if (down_stack.empty()) return CCN_EINVAL;
+                const int sidx = down_stack.back();
+                down_stack.pop_back();
+                const State& sk = hist[sidx];
+                Level* fine = sk.lv;
+                Feat* x_skip = sk.x ? sk.x : &fine->pos;
+                const int knn = (int)iv[0], with_xyz = (int)iv[1], nl = (int)iv[2];
+                int32_t* nbr = ex.alloc_n<int32_t>(fine->n * knn);
+                float* wgt = ex.alloc_n<float>(fine->n * knn);
+                if (s.kind == ST_FP) {
+                    EX_CALL(level_sptr(ex, cur.lv));
+                    if (!ex.oom)
+                        EX_CALL(ccn_knn_exact(fine->pos.f, fine->batch, fine->n, cur.lv->pos.f, cur.lv->sptr_dev, knn, 1, nbr, wgt, nullptr, st));
+                } else {
+                    EX_CALL(level_topo(ex, fine));
+                    const int64_t* idx = down_idx[sidx];
+                    if (!idx) return CCN_EINVAL;
+                    if (!ex.oom)
+                        EX_CALL(ccn_knn_1d_superset(fine->pos.f, fine->curve_ord, fine->n, idx, cur.lv->n, knn, nbr, wgt, st));
+                }
+                const int c = cur.x->c;
+                Feat* y = ex.new_feat(fine->n, c);
+                const bool both = fine->n > 0 && (c % 16) == 0 && (cur.x->ld % 4) == 0;
+                if (both) y->pl = ex.alloc_planes(fine->n, c);
+                if (!ex.oom) {
+                    if (both)
+                        EX_CALL(ccn_interp_blend_both(cur.x->f, cur.x->ld, nbr, wgt, s.kind == ST_FP, fine->n, knn, c, y->f, y->ld, y->pl.buf,
+                                                      y->pl.kpad, y->pl.pstride, ex.npl, st));
+                    else
+                        EX_CALL(ccn_interp_blend(cur.x->f, cur.x->ld, nbr, wgt, s.kind == ST_FP, fine->n, knn, c, y->f, y->ld, st));
+                }
+                Feat* parts[3];
+                int np = 0;
+                parts[np++] = y;
+                parts[np++] = x_skip;                      // modules._fp_concat: [y, x_skip, pos_skip]
+                if (with_xyz) parts[np++] = &fine->pos;
+                Feat* o = nullptr;
+                EX_CALL(run_mlp(ex, iv + 3, nl, parts, np, 2, &o));
+                outp.x = o;
+                outp.lv = fine;
+                break;
+            }
+            default:
+                return CCN_EUNSUPPORTED;
+        }
+        if (ex.oom) return CCN_ENOMEM;
+        hist.push_back(outp);
+        down_idx.push_back(didx);
+        if (ex.skip_store[si]) prop_stack.push_back((int)si);
+        if (s.kind == ST_SA || s.kind == ST_SA_GEO) down_stack.push_back((int)si);
+        cur = outp;
+    }
+    // final MLP (base.py:156): logits written straight into the caller's buffer
+    Feat* parts[1] = {cur.x};
+    Seg segs[4];
+    EX_CALL(segs_of(ex, parts, 1, segs));
+    int nseg = 1;
+    const int64_t M = cur.x->n;
+    for (size_t i = 0; i < ex.out_mlp.size(); ++i) {
+        const Linear& L = ex.lins[ex.out_mlp[i]];
+        const bool last = i + 1 == ex.out_mlp.size();
+        if (!last) {
+            Planes yp;
+            EX_CALL(linear_planes(ex, L, segs, nseg, M, 1, nullptr, &yp));
+            segs[0] = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
+            nseg = 1;
+            continue;
+        }
+        if (ex.oom) break;
+        const int box = pick_box(L, M, ex.npl);
+        const int bs = box_slot(box);
+        if (!L.map_hi[bs] || ld_logits < L.n) return CCN_EINVAL;
+        EX_CALL(ccn_linear_planes(segs[0].buf, segs[0].kpad, segs[0].pstride, segs[0].k, nullptr, 0, 0, 0, nullptr, 0, 0, 0, nullptr, 0, 0,
+                                  0, L.map_hi[bs], L.map_lo[bs], L.bias, logits, ld_logits, nullptr, 0, 0, M, L.n, box, ex.mode, L.act,
+                                  L.slope, st));
+    }
+    return CCN_OK;
+}
+
+}  // namespace
+
+extern "C" int ccn_forward_run(ccn_exec_t* h, const float* x, int64_t ldx, const float* pos, const int64_t* batch,
+                               const int64_t* curve_idxs, int64_t n, void* arena, int64_t arena_bytes, ccn_draw_fn draw,
+                               void* draw_user, float* logits, int64_t ld_logits, int64_t* arena_needed, ccn_stream_t stream) {
+    CCN_REQUIRE(h && pos && batch && curve_idxs && n > 0 && arena && arena_bytes > 0 && draw && logits);
+    Exec& ex = h->ex;
+    ex.arena = (char*)arena; ex.cap = (size_t)arena_bytes; ex.off = 0; ex.oom = false;
+    ex.stream = (cudaStream_t)stream; ex.draw = draw; ex.draw_user = draw_user;
+    const int rc = run_forward(ex, x, ldx, pos, batch, curve_idxs, n, logits, ld_logits);
+    if (arena_needed) *arena_needed = (int64_t)ex.off;
+    if (ex.oom) return CCN_ENOMEM;
+    return rc;
+}

@@ -75,6 +75,9 @@ class ModelBase(torch.nn.Module):
         self.version = kwargs.get("version", 2.0)
         # arithmetic of the shared-MLP Linear layers: "fp32" | "bf16x3" | "bf16" (nn.set_precision); not a reference kwarg
         self.precision = kwargs.pop("precision", "fp32")
+        # inference on the tensor-core precisions runs through the native step executor (csrc/executor.cu, ONE C-ABI call per
+        # forward) where it covers the step list; False keeps the python executor below (same launches, same logits)
+        self.native_executor = kwargs.pop("native_executor", True)
         self.mlp_func = MLP
         self.step_names = list(steps)
         self.skip_connect_state_store = list(kwargs.get("skip_connect_state_store", []))
@@ -152,6 +155,10 @@ class ModelBase(torch.nn.Module):
         native.pin_stream(True)
         set_weights_epoch(self._weights_epoch())
         try:
+            if self.native_executor and not self.training and self.precision != "fp32" and not kwargs:
+                out = self._forward_native(data, draws)
+                if out is not None:
+                    return out
             return self._forward(data, draws, **kwargs)
         finally:
             set_weights_epoch(None)
@@ -176,6 +183,28 @@ class ModelBase(torch.nn.Module):
         for t in ts:
             v += t._version
         return (id(self), self.training, v, ts[0].data_ptr() if ts else 0, len(ts))
+
+    def _forward_native(self, data, draws):
+        """One forward through ccn_forward_run; None when the model / input is outside the native executor's scope."""
+        from . import executor as X
+        if isinstance(data, list):
+            data = Batch.from_data_list(data)
+        if not data.pos.is_cuda:
+            raise TypeError("curvecloudnet_b200 runs on CUDA tensors only (there is no CPU path)")
+        st = self.__dict__.get("_native")
+        epoch = (self._weights_epoch(), self.precision, ops.FUSED_EDGE_STEPS)
+        if st is None or st[0] != epoch:
+            try:
+                st = (epoch, X.NativeExecutor(self))
+            except X.Unsupported:
+                st = (epoch, None)
+            self.__dict__["_native"] = st
+        if st[1] is None or getattr(data, "labels", None) is not None and hasattr(self, "lin_categorical"):
+            return None
+        try:
+            return st[1].run(data, draws)
+        except X.Unsupported:
+            return None
 
     def _forward(self, data, draws: Draws = None, **kwargs):
         """base.py:133-175.  hist[k][i] is the INPUT of step i (the lists start with the raw input)."""

@@ -216,6 +216,17 @@ class PointNetConv2(nn.Module):
         self._dec, self._dec_src = None, None
         self._fused = _ChainCache()
 
+    def decomposed(self, cx):
+        """First Linear of local_nn split into its feature part (a PreparedLinear over the cx source channels, None when
+        cx = 0) and its positional part wp (3, C1); weight preparation, once per weight version."""
+        layers = self.local_nn.layers()
+        l0 = layers[0]
+        assert l0.in_features == cx + 3, "local_nn input width %d != %d feature + 3 position columns" % (l0.in_features, cx)
+        if self._dec is None or self._dec_src is not layers:
+            lin_x = PreparedLinear(l0.w[:, :cx].contiguous(), None) if cx > 0 else None
+            self._dec, self._dec_src = (lin_x, l0.w[:, cx:].t().contiguous()), layers
+        return self._dec
+
     def forward_edges(self, x_src, pos_src, pos_dst, edges: ops.EdgeCSR, cache=None):
         if self.training:
             return T.pointnet_conv(self, x_src, pos_src, pos_dst, edges)
@@ -224,10 +235,7 @@ class PointNetConv2(nn.Module):
         l0 = layers[0]
         cx = 0 if x_src is None else x_src.shape[1]
         assert l0.in_features == cx + 3, "local_nn input width %d != %d feature + 3 position columns" % (l0.in_features, cx)
-        if self._dec is None or self._dec_src is not layers:   # weight preparation, once per weight version
-            lin_x = PreparedLinear(l0.w[:, :cx].contiguous(), None) if cx > 0 else None
-            self._dec, self._dec_src = (lin_x, l0.w[:, cx:].t().contiguous()), layers
-        lin_x, wp = self._dec                                  # x part (C1, cx) and positional part (3, C1)
+        lin_x, wp = self.decomposed(cx)                        # x part (C1, cx) and positional part (3, C1)
         H = lin_x(x_src) if lin_x is not None else None
         if edges.max_degree <= ops.FUSED_MAX_DEGREE and (H is None or torch.is_tensor(H)):
             # gather -> layer 1 -> remaining layers [-> attention MLP] -> aggregate in ONE kernel (csrc/edge_fused.cu)

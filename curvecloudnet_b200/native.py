@@ -27,7 +27,7 @@ def _parse_header():
         for a in [a.strip() for a in args.split(",")]:
             if a in ("", "void"):
                 continue
-            if "*" in a or "ccn_stream_t" in a:
+            if "*" in a or "ccn_stream_t" in a or "ccn_draw_fn" in a:
                 codes += "p"
             elif "int64_t" in a:
                 codes += "q"
@@ -189,9 +189,9 @@ def call(name, *args):
 
 
 def _raise(name, rc):
-    if rc < 0:
-        raise CcnError("%s: invalid argument (code %d)" % (name, rc))
-    raise CcnError("%s: CUDA error %d" % (name, rc))
+    e = CcnError("%s: invalid argument (code %d)" % (name, rc) if rc < 0 else "%s: CUDA error %d" % (name, rc))
+    e.code = rc
+    raise e
 
 
 _prof_footprint = None      # list: argument footprint (bytes) of every timed call, parallel to _prof_events

@@ -35,6 +35,9 @@ typedef struct CUstream_st* ccn_stream_t;
 #define CCN_OK 0
 #define CCN_EINVAL (-1)
 #define CCN_EUNSUPPORTED (-2)
+#define CCN_ETOPOLOGY (-3)    /* batch / curve ids not sorted (the reference asserts, point_ops.py:31,49): ccn_exec_topology_flags */
+#define CCN_EVOXEL_RANGE (-4) /* VoxelFPS: voxel coordinates out of the supported range */
+#define CCN_ENOMEM (-5)       /* ccn_forward_run: the arena is too small (*arena_needed = bytes used when it ran out) */
 
 #define CCN_ACT_NONE 0
 #define CCN_ACT_RELU 1
@@ -438,6 +441,29 @@ int ccn_pointconv_fused(const float* H, int64_t ldh, const float* wp, const floa
                         int32_t act0, float slope0, const ccn_chain_t* chain_host, int32_t agg, int32_t msg_layer,
                         int32_t* tile_scratch, float* out, int64_t ldo, void* planes, int64_t kpad, int64_t plane_stride,
                         int32_t n_planes, ccn_stream_t stream);
+
+/* ---- native step executor (csrc/executor.cu): ModelBase.forward / _apply_steps (src/models/base.py:133-175) and the
+ * step modules (src/models/modules/{fast_conv1d,pointnet2,point_conv,dgcnn,mlp,skip_connect}.py) as ONE call per forward
+ * (inference, tensor-core precisions, the nuScenes / KITTI step family: conv1d-fast-v2, sa-geo, mlp, sgcnn (dense),
+ * skip-connect, sa (voxel | fps, FRNN), fp, fp-geo).  It issues exactly the C-ABI calls of the python executor in the same
+ * order, so the logits are bit-identical to it.
+ *   ccn_exec_create   parses the PLAN - two flat arrays built by curvecloudnet_b200/executor.py from the prepared modules
+ *                     (folded weights, bf16 planes, HOST tensor maps; all referenced memory stays owned by the caller and
+ *                     must outlive the executor).
+ *   ccn_forward_run   x (n, in_c) or null, pos (n, 3), batch / curve_idxs (n) int64 - DEVICE; arena: device scratch for every
+ *                     intermediate (bump allocated, nothing survives the call); draw: the reference's random draws in its
+ *                     call order - kind 0: CurveFPS phase (fps_ops.py:30) -> *(float*)out; kind 1: VoxelFPS noise
+ *                     (fps_ops.py:56), n floats -> out (HOST buffer); kind 2: FPS start of a cloud of n points
+ *                     (point_ops.py:64) -> return value; logits (n, ld_logits) fp32 DEVICE.  Synchronises `stream` at
+ *                     the data-dependent sizes (level sizes, edge counts).  CCN_ENOMEM: enlarge the arena, call again. */
+typedef struct ccn_exec ccn_exec_t;
+typedef int64_t (*ccn_draw_fn)(void* user, int32_t kind, int64_t n, void* out);
+int ccn_exec_create(const int64_t* iplan_host, int64_t n_i, const double* fplan_host, int64_t n_f, ccn_exec_t** out);
+void ccn_exec_destroy(ccn_exec_t* exec);
+int32_t ccn_exec_topology_flags(const ccn_exec_t* exec);
+int ccn_forward_run(ccn_exec_t* exec, const float* x, int64_t ldx, const float* pos, const int64_t* batch,
+                    const int64_t* curve_idxs, int64_t n, void* arena, int64_t arena_bytes, ccn_draw_fn draw,
+                    void* draw_user, float* logits, int64_t ld_logits, int64_t* arena_needed_host, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

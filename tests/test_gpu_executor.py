@@ -1,0 +1,75 @@
+"""The native step executor (csrc/executor.cu, ccn_forward_run: ONE C-ABI call per forward) against the python executor of
+curvecloudnet_b200/model.py (reference src/models/base.py:133-175): it issues the same kernel launches in the same order,
+so the logits must be BIT-IDENTICAL under the same torch seed (same random draws); parity of the python executor against
+the oracle / the reference-generated goldens is established by tests/test_gpu_model.py and test_gpu_fullsize_oracle.py."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _models(name, precision):
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import randomize_model_
+    a = randomize_model_(build_model(ModelBase, name, precision=precision), 1234).cuda().eval()
+    b = randomize_model_(build_model(ModelBase, name, precision=precision, native_executor=False), 1234).cuda().eval()
+    return a, b
+
+
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("name,seeds,sub", [("nuscenes", [3], 1500), ("nuscenes", [0, 1], 3000), ("nuscenes", [0], None),
+                                            ("kitti", [2], 2500), ("kitti", [2, 3], None)])
+def test_native_executor_equals_python_executor(name, seeds, sub, precision):
+    from curvecloudnet_b200.synthetic import driving_scan_batch
+    data = driving_scan_batch(seeds, kind=name, subsample=sub).to("cuda")
+    native_model, py_model = _models(name, precision)
+    with torch.no_grad():
+        for rep in range(2):                       # the second pass reuses the executor's arena
+            torch.manual_seed(7 + rep)
+            got = native_model(data)
+            torch.manual_seed(7 + rep)
+            want = py_model(data)
+            assert native_model.__dict__["_native"][1] is not None, "the native executor did not take this model"
+            assert got.shape == want.shape and torch.equal(got, want), "native and python executors differ (pass %d)" % rep
+
+
+def test_native_executor_grows_its_arena_and_replays_the_draws():
+    from curvecloudnet_b200.synthetic import driving_scan_batch
+    data = driving_scan_batch([4], subsample=4000).to("cuda")
+    native_model, py_model = _models("nuscenes", "bf16x3")
+    with torch.no_grad():
+        torch.manual_seed(1)
+        native_model(data)                          # builds the executor
+        ex = native_model.__dict__["_native"][1]
+        ex.arena = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")      # far too small: CCN_ENOMEM -> grow -> run again
+        torch.manual_seed(2)
+        got = native_model(data)
+        torch.manual_seed(2)
+        want = py_model(data)
+    assert ex.arena.numel() > (1 << 20)
+    assert torch.equal(got, want)
+
+
+def test_native_executor_reports_unsorted_input_like_the_reference():
+    """point_ops.py:31,49 assert sorted ids; the native executor raises the same AssertionError."""
+    from curvecloudnet_b200.synthetic import driving_scan_batch
+    data = driving_scan_batch([5], subsample=1200).to("cuda")
+    native_model, _ = _models("nuscenes", "bf16x3")
+    data.batch = data.batch.clone()
+    data.batch[10] = 1
+    with torch.no_grad(), pytest.raises(AssertionError):
+        native_model(data)
+
+
+def test_other_configs_fall_back_to_the_python_executor():
+    from curvecloudnet_b200.synthetic import object_scan_batch
+    data = object_scan_batch([0, 1]).to("cuda")
+    native_model, py_model = _models("shapenet-class", "bf16x3")
+    with torch.no_grad():
+        torch.manual_seed(3)
+        got = native_model(data)
+        torch.manual_seed(3)
+        want = py_model(data)
+    assert native_model.__dict__["_native"][1] is None
+    assert torch.equal(got, want)
