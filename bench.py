@@ -464,9 +464,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def native_exec():
+        st = model.__dict__.get("_native")
+        return st[1] if st else None
+
+    fam_tot = {}
+
     def timed_pass(steps, from_host, profile):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         outs, npts = [], 0
+        nx = native_exec()
+        if profile and nx is not None:
+            nx.profile(True, 20000)               # per-family CUDA events inside ccn_forward_run (csrc/executor.cu)
         native.profile_begin((lin_name,) if profile else None, pad_cycles=40000 if profile else 0)
         barrier()
         l0 = native.kernel_launches()
@@ -478,6 +487,11 @@ def main():
                 ev[i][0].record()
                 data = host_scans[j].to("cuda", non_blocking=True) if from_host else dev_scans[j]
                 logits = model(data)
+                if profile and nx is not None:
+                    for f, d in nx.profile_read().items():
+                        t = fam_tot.setdefault(f, {"ms": 0.0, "calls": 0.0, "flops": 0.0, "bytes": 0.0})
+                        for k in t:
+                            t[k] += d[k]
                 if from_host:
                     # D2H of the step's result into pinned host memory, asynchronous (double-buffered): the copy is
                     # inside the step's event pair; the host only waits for it at the next forward's first readback
@@ -487,6 +501,8 @@ def main():
         barrier()
         launches = native.kernel_launches() - l0
         prof = native.profile_end()
+        if profile and nx is not None:
+            nx.profile(False)
         ms = sum(a.elapsed_time(b) for a, b in ev)
         return ms, npts, launches, prof, (logits.shape if steps else None)
 
@@ -513,25 +529,51 @@ def main():
         return
 
     peaks, peak_src = _peaks()
-    lin = prof.get(lin_name, {"ms": 0.0, "calls": 0, "work": 0.0, "bytes": 0.0})
-    # Every Linear of this network is on the HBM side of the ridge: bf16x3 arithmetic intensity is
-    # 6 K N / (4 K + 4 N [+ 4 N]) <= 128 FLOP/B at K = N = 256 against 1371.7 TF/s / 6.54 TB/s = 210 FLOP/B, so the
-    # bound is the activation traffic.  The tensor-pipe figures stay beside it.
     peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
     peak_tf = float(peaks.get("bf16_tflops_sustained", peaks.get("bf16_tflops", 1371.7)))
-    sec = lin["ms"] * 1e-3
-    ach_gbs = (lin["bytes"] / sec / 1e9) if sec > 0 else 0.0
-    ach_tf = (lin["work"] / sec / 1e12) if sec > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "linear_f32_kernel (ccn_linear_f32)" if args.precision == "fp32" else
-                "linear_planes_kernel<%d> (ccn_linear_planes: TMA + tcgen05 + TMEM)" % (3 if args.precision == "bf16x3" else 1),
-                "achieved": ach_gbs, "peak": peak_gbs, "unit": "GB/s", "frac": ach_gbs / peak_gbs if peak_gbs else None,
-                "traffic": _ncu_traffic("ccn_linear_planes:%s" % args.precision),
-                "peak_source": peak_src + " (hbm_gbs)", "launches": lin["calls"],
-                "algorithmic_bytes_per_launch": (lin["bytes"] / lin["calls"]) if lin["calls"] else None,
-                "avg_launch_us": (lin["ms"] * 1e3 / lin["calls"]) if lin["calls"] else None,
-                "share_of_step": lin["ms"] / ms_prof if ms_prof else None, "step_ms_instrumented": ms_prof / K,
-                "flops_per_step": lin["work"] / K, "tensor_achieved_tflops": ach_tf, "tensor_peak_tflops": peak_tf,
-                "tensor_frac": ach_tf / peak_tf if peak_tf else None}
+    KERNELS = {"linear": "linear_planes_kernel (ccn_linear_planes: per-point shared-MLP layers, TMA + tcgen05 + TMEM)",
+               "edge_fused": "edge_chain_kernel (ccn_sgcnn_fused / ccn_pointconv_fused: gather -> MLP chain -> aggregate, tcgen05 + TMEM)",
+               "conv": "linear_planes_kernel (ccn_conv_planes: curve convolution as one GEMM)",
+               "search": "grid_build / frnn_knn / knn_exact kernels", "sample": "curve_fps / voxel_fps / fps kernels"}
+    if not fam_tot:
+        # python executor (fp32 precision or native_executor=False): only the Linear family is instrumented (native.profile_begin)
+        lin = prof.get(lin_name, {"ms": 0.0, "calls": 0, "work": 0.0, "bytes": 0.0})
+        fam_tot["linear"] = {"ms": lin["ms"], "calls": lin["calls"], "flops": lin["work"], "bytes": lin["bytes"]}
+        if args.precision == "fp32":
+            KERNELS["linear"] = "linear_f32_kernel (ccn_linear_f32)"
+
+    def family_view(f):
+        d = fam_tot[f]
+        sec = d["ms"] * 1e-3
+        tf = d["flops"] / sec / 1e12 if sec > 0 else 0.0
+        gbs = d["bytes"] / sec / 1e9 if sec > 0 else 0.0
+        mma = 3 if args.precision == "bf16x3" else 1
+        return {"kernel": KERNELS[f], "launches": int(d["calls"]), "avg_launch_us": d["ms"] * 1e3 / d["calls"] if d["calls"] else None,
+                "share_of_step": d["ms"] / ms_prof if ms_prof else None,
+                "algorithmic_flops_per_step": d["flops"] / K, "algorithmic_bytes_per_step": d["bytes"] / K,
+                "tensor_achieved_tflops": tf, "tensor_frac": tf / peak_tf if peak_tf else None,
+                "tensor_frac_executed": mma * tf / peak_tf if peak_tf else None,
+                "hbm_achieved_gbs": gbs, "hbm_frac": gbs / peak_gbs if peak_gbs else None}
+
+    # The dominant kernel family of the step by device time.  Its bound follows from its ALGORITHMIC intensity (SURVEY 8(d):
+    # FLOPs over valid edges / compulsory bytes without inter-layer intermediates) against the ridge of the measured peaks:
+    # the fused edge steps and the wide per-point layers sit on the tensor side, everything else on the HBM side.
+    dom = max(fam_tot, key=lambda f: fam_tot[f]["ms"])
+    dv = family_view(dom)
+    ridge = peak_tf * 1e12 / (peak_gbs * 1e9)
+    inten = (fam_tot[dom]["flops"] / fam_tot[dom]["bytes"]) if fam_tot[dom]["bytes"] else 0.0
+    tensor_bound = inten >= ridge
+    roofline = {"bound": "tensor" if tensor_bound else "hbm", "kernel": dv["kernel"],
+                "achieved": dv["tensor_achieved_tflops"] if tensor_bound else dv["hbm_achieved_gbs"],
+                "peak": peak_tf if tensor_bound else peak_gbs, "unit": "TFLOP/s" if tensor_bound else "GB/s",
+                "frac": dv["tensor_frac"] if tensor_bound else dv["hbm_frac"],
+                "traffic": _ncu_traffic("%s:%s" % (dom, args.precision)),
+                "peak_source": peak_src + (" (bf16_tflops_sustained)" if tensor_bound else " (hbm_gbs)"),
+                "algorithmic_intensity_flop_per_byte": inten, "ridge_flop_per_byte": ridge,
+                "mma_per_algorithmic_mma": 3 if args.precision == "bf16x3" else 1,
+                "launches": dv["launches"], "avg_launch_us": dv["avg_launch_us"], "share_of_step": dv["share_of_step"],
+                "step_ms_instrumented": ms_prof / K,
+                "families": {f: family_view(f) for f in fam_tot}}
     mean_pts = tot_pts / (K * world)
     h2d = sum(s.input_bytes() for s in host_scans) / len(host_scans)
     d2h = mean_pts * (oshape[1] if oshape else 17) * 4

@@ -42,6 +42,7 @@ constexpr int kRows = 128;
 constexpr int kChunkBytes = kRows * 128;      // one 128-row x 64-column bf16 plane chunk (SWIZZLE_128B)
 constexpr int kThreads = 320;                // warp 0 TMA, warp 1 MMA, warps 2-9 row workers
 constexpr int kWorkers = 256;
+constexpr int kSegTable = 264;                // segment offsets staged per tile (tiles with more, i.e. runs of empty targets, read row_ptr)
 constexpr int kU = 2;                         // layer-1 items in flight per worker thread (registers: two CTAs per SM need <= 102)
 constexpr int kMaxStages = 6;
 constexpr int kMaxWidth = 256;                // widest activation kept resident / widest layer output
@@ -127,6 +128,7 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
     __shared__ float wp_s[4][kMaxWidth];                            // FORM_POINT: Wp rows 0..2, bias of layer 1
     __shared__ int32_t row_i[kRows], row_j[kRows];                  // target / source of every tile row (-1: none)
     __shared__ float row_rel[kRows][3];                             // FORM_POINT: (pos_j - pos_i) [/ r]
+    __shared__ int32_t seg_s[kSegTable];                            // CSR forms: first tile row of every segment (+ end)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool att_mode = p.msg_layer >= 0;
@@ -281,6 +283,8 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                     row_rel[wt][0] = rx; row_rel[wt][1] = ry; row_rel[wt][2] = rz;
                 }
             }
+            if (FORM != FORM_DENSE && nseg < kSegTable)
+                for (int sg = wt; sg <= nseg; sg += kWorkers) seg_s[sg] = __ldg(p.row_ptr + q0 + sg) - e0;
             workers_sync();
             hdr = fetch_hdr(t + gridDim.x);                         // next tile's header: in flight during the formation
 
@@ -409,12 +413,13 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                     const int c = wt & 31;
                     const int tab = att_mode ? 0 : (wt >> 7);
                     const int s0 = att_mode ? (wt >> 5) : ((wt >> 5) & 3), sstep = att_mode ? 8 : 4;
-                    const float* Ta = T + tab * kTable;            // last layer's rows (attention logits in the attention modes)
+                    float* Ta = T + tab * kTable;                  // last layer's rows (attention logits in the attention modes)
                     const float* Tm = T + kTable;                  // message rows (attention modes)
                     const int col = c0 + 32 * tab + c;
                     for (int sg = s0; sg < nseg; sg += sstep) {
                         int lo, hi;
                         if (FORM == FORM_DENSE) { lo = sg * p.G; hi = lo + p.G; }
+                        else if (nseg < kSegTable) { lo = seg_s[sg]; hi = seg_s[sg + 1]; }
                         else { lo = __ldg(p.row_ptr + q0 + sg) - e0; hi = __ldg(p.row_ptr + q0 + sg + 1) - e0; }
                         float r = 0.f;
                         if (p.agg == CCN_AGG_MAX) {
@@ -433,10 +438,13 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                             float m = -INFINITY;
                             for (int j = lo; j < hi; ++j) m = fmaxf(m, Ta[j * 32 + (c ^ (j & 31))]);
                             float sum = 0.f;
-                            for (int j = lo; j < hi; ++j) sum += expf(Ta[j * 32 + (c ^ (j & 31))] - m);
+                            for (int j = lo; j < hi; ++j) {          // exp(a - max) once per element, kept in the table (own column)
+                                const float ev = expf(Ta[j * 32 + (c ^ (j & 31))] - m);
+                                Ta[j * 32 + (c ^ (j & 31))] = ev;
+                                sum += ev;
+                            }
                             const float inv = 1.f / (sum + 1e-16f);
-                            for (int j = lo; j < hi; ++j)
-                                r += Tm[j * 32 + (c ^ (j & 31))] * (expf(Ta[j * 32 + (c ^ (j & 31))] - m) * inv);
+                            for (int j = lo; j < hi; ++j) r += Tm[j * 32 + (c ^ (j & 31))] * (Ta[j * 32 + (c ^ (j & 31))] * inv);
                         }
                         const int64_t orow = q0 + sg;
                         p.out[orow * p.ldo + col] = r;

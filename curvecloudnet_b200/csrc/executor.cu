@@ -112,9 +112,33 @@ struct Exec {
     float* noise_host = nullptr;       // pinned staging of the VoxelFPS noise draw
     size_t noise_cap = 0;
     cudaStream_t stream = nullptr;
+    // farthest-point sampling of the NEXT levels runs ahead on a side stream (one CTA per cloud, K sequential rounds: 0.3 ms on
+    // one SM at B = 1) while the main stream runs the edge steps of the current level; events order the two
+    cudaStream_t side = nullptr;
+    std::vector<int> fps_next;          // per step: the next `sa` step that FPS-samples the level this step creates (-1: none)
+    struct Pre { bool done = false; Level* ch = nullptr; int64_t* idx = nullptr; cudaEvent_t ready = nullptr; };
+    std::vector<Pre> pre;
+    cudaEvent_t lvl_ready = nullptr;
+    bool use_side = true;
     ccn_draw_fn draw = nullptr;
     void* draw_user = nullptr;
     int topo_flags = 0;
+    // optional per-family device timing (bench.py's roofline leg): CUDA events around every launch of a family, a short spin
+    // queued before each so that the pair brackets the kernel and not the host's launch gap
+    bool prof = false;
+    int prof_spin = 0;
+    struct ProfRec { int fam; cudaEvent_t a, b; double flops, bytes; };
+    std::vector<ProfRec> prof_recs;
+    std::vector<cudaEvent_t> prof_pool;
+    size_t prof_used = 0;
+    cudaEvent_t prof_event() {
+        if (prof_used == prof_pool.size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            prof_pool.push_back(e);
+        }
+        return prof_pool[prof_used++];
+    }
     std::deque<Feat> feats;
     std::deque<Level> levels;
 
@@ -154,6 +178,28 @@ struct Exec {
     }
 };
 
+enum { FAM_LINEAR = 0, FAM_EDGE_FUSED = 1, FAM_CONV = 2, FAM_SEARCH = 3, FAM_SAMPLE = 4, FAM_COUNT = 5 };
+
+__global__ void spin_kernel(long long cycles) {
+    const long long t0 = clock64();
+    while (clock64() - t0 < cycles) {}
+}
+
+struct ProfScope {            // brackets the launches issued during its lifetime
+    Exec& ex;
+    bool on;
+    ProfScope(Exec& e, int fam, double flops, double bytes) : ex(e), on(e.prof && !e.oom) {
+        if (!on) return;
+        if (ex.prof_spin > 0) spin_kernel<<<1, 1, 0, ex.stream>>>(ex.prof_spin);
+        Exec::ProfRec r{fam, ex.prof_event(), ex.prof_event(), flops, bytes};
+        cudaEventRecord(r.a, ex.stream);
+        ex.prof_recs.push_back(r);
+    }
+    ~ProfScope() {
+        if (on) cudaEventRecord(ex.prof_recs.back().b, ex.stream);
+    }
+};
+
 // ---- helpers mirroring curvecloudnet_b200/ops.py / nn.py ------------------------------------------------------------
 int ensure_planes(Exec& ex, Feat* t) {               // nn.ForwardCache.planes_for
     if (t->pl.buf) return CCN_OK;
@@ -187,7 +233,10 @@ inline int box_slot(int b) { return b == 32 ? 0 : b == 64 ? 1 : b == 128 ? 2 : 3
 struct Seg { const void* buf; int64_t kpad, pstride; int k; };
 
 // ops.linear_planes: out_kind 0 = fp32, 1 = planes, 2 = both.  y (fp32) / yp (planes) are allocated here.
-int linear_planes(Exec& ex, const Linear& L, const Seg* segs, int nseg, int64_t M, int out_kind, Feat** y_out, Planes* yp_out) {
+// Accounting: FLOPs 2 M N K; bytes = the weights + the input rows if they are a step input (io & 1) + the output
+// rows if they are a step output (io & 2) at fp32 width - the activations BETWEEN the layers of an MLP are not compulsory.
+int linear_planes(Exec& ex, const Linear& L, const Seg* segs, int nseg, int64_t M, int out_kind, Feat** y_out, Planes* yp_out,
+                  int io = 3) {
     Feat* Y = nullptr;
     Planes Yp;
     if (out_kind != 1) Y = ex.new_feat(M, L.n);
@@ -201,6 +250,8 @@ int linear_planes(Exec& ex, const Linear& L, const Seg* segs, int nseg, int64_t 
     if (!L.map_hi[bs]) return CCN_EINVAL;
     Seg s[4] = {};
     for (int i = 0; i < nseg; ++i) s[i] = segs[i];
+    ProfScope ps(ex, FAM_LINEAR, 2.0 * M * L.n * L.k_true,
+                 (double)L.n * L.k_true * 2 * ex.npl + ((io & 1) ? 4.0 * M * L.k_true : 0.0) + ((io & 2) ? 4.0 * M * L.n : 0.0));
     return ccn_linear_planes(s[0].buf, s[0].kpad, s[0].pstride, s[0].k, s[1].buf, s[1].kpad, s[1].pstride, s[1].k, s[2].buf,
                              s[2].kpad, s[2].pstride, s[2].k, s[3].buf, s[3].kpad, s[3].pstride, s[3].k, L.map_hi[bs],
                              L.map_lo[bs], L.bias, Y ? Y->f : nullptr, L.n, Yp.buf, Yp.kpad, Yp.pstride, M, L.n, box, ex.mode,
@@ -227,7 +278,7 @@ int run_mlp(Exec& ex, const int64_t* lin_ids, int nl, Feat* const* parts, int np
         const bool last = i == nl - 1;
         Feat* y = nullptr;
         Planes yp;
-        EX_CALL(linear_planes(ex, L, segs, nseg, M, last ? last_kind : 1, &y, &yp));
+        EX_CALL(linear_planes(ex, L, segs, nseg, M, last ? last_kind : 1, &y, &yp, (i == 0 ? 1 : 0) | (last ? 2 : 0)));
         if (last) { *out = y; break; }
         cur = yp;
         segs[0] = Seg{cur.buf, cur.kpad, cur.pstride, L.n};
@@ -318,6 +369,7 @@ int frnn(Exec& ex, Level* q, Level* src, int K, float radius, bool want_cnt, int
         ng.cell_off = ex.alloc_n<int32_t>(ng.cells + 1);
         int32_t* slot = ex.alloc_n<int32_t>(src->n);
         ng.sorted = ex.alloc_n<float>(4 * (src->n > 0 ? src->n : 1));
+        ProfScope psg(ex, FAM_SEARCH, 0, 28.0 * src->n + 4.0 * ng.cells);
         if (!ex.oom)
             EX_CALL(ccn_grid_build(src->pos.f, src->batch, src->n, radius, ng.cells, ng.cell_off, slot, ng.sorted,
                                    (ccn_stream_t)ex.stream));
@@ -329,6 +381,7 @@ int frnn(Exec& ex, Level* q, Level* src, int K, float radius, bool want_cnt, int
     *idx_out = idx;
     if (cnt_out) *cnt_out = cnt;
     if (ex.oom) return CCN_OK;
+    ProfScope ps(ex, FAM_SEARCH, 0, 12.0 * q->n + 16.0 * src->n + 4.0 * q->n * K);
     EX_CALL(ccn_frnn_knn(q->pos.f, q->batch, q->n, g->sorted, g->cell_off, g->cells, src->sptr_dev, radius, K, idx, nullptr, cnt,
                          (ccn_stream_t)ex.stream));
     if (self && !want_cnt) src->knn.push_back(KnnMemo{K, radius, idx});
@@ -365,6 +418,11 @@ int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts
         int32_t* scratch = ex.alloc_n<int32_t>(4 * n_tiles);
         *out = o;
         if (ex.oom) return CCN_OK;
+        double mac = 0, wbytes = 0;
+        for (int l = 0; l < ch.desc->n_layers; ++l) { mac += (double)ch.desc->k[l] * ch.desc->n[l]; }
+        wbytes = mac * 2 * ex.npl;
+        // gather_mlp_aggregate: N_src C 4 + E 4 + N_q (12 + C_out 4) + weights
+        ProfScope ps(ex, FAM_EDGE_FUSED, 2.0 * e.E * mac, 4.0 * src->n * c1 + 4.0 * e.E + e.nq * (12.0 + 4.0 * ch.n_out) + wbytes);
         return ccn_pointconv_fused(H ? H->f : nullptr, H ? H->ld : 0, wp, bias0, src->pos.f, dst->pos.f, nullptr, 0, e.row_ptr,
                                    e.erow, e.ecol, e.nq, e.E, e.max_degree, c1, nradius, act0, slope0, ch.desc, agg,
                                    att ? n_local - 1 : -1, scratch, o->f, o->ld, o->pl.buf, o->pl.kpad, o->pl.pstride,
@@ -384,7 +442,7 @@ int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts
         const bool last = i == n_local - 1;
         Feat* y = nullptr;
         Planes yp;
-        EX_CALL(linear_planes(ex, L, &seg, 1, e.E, last ? (att ? 2 : 0) : 1, &y, &yp));
+        EX_CALL(linear_planes(ex, L, &seg, 1, e.E, last ? (att ? 2 : 0) : 1, &y, &yp, 0));
         if (last) { msg = y; msgp = yp; }
         else seg = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
     }
@@ -396,7 +454,7 @@ int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts
             const bool last = i == n_att - 1;
             Feat* y = nullptr;
             Planes yp;
-            EX_CALL(linear_planes(ex, L, &seg, 1, e.E, last ? 0 : 1, &y, &yp));
+            EX_CALL(linear_planes(ex, L, &seg, 1, e.E, last ? 0 : 1, &y, &yp, 0));
             if (last) attf = y;
             else seg = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
         }
@@ -425,6 +483,73 @@ int dense_to_csr(Exec& ex, int32_t* idx, int32_t* cnt, int64_t nq, int K, Edges*
     *e = Edges{cnt, erow, ecol, E, nq, K};
     if (ex.oom) return CCN_OK;
     return ccn_dense_to_csr(idx, cnt, nq, K, erow, ecol, (ccn_stream_t)ex.stream);
+}
+
+// modules.fps_sorted + ops.fps: K = ceil(len * ratio) in f32 (point_ops.py:63), random start per cloud, selected indices sorted;
+// the level sizes follow from the parent's sample CSR on the host - no read-back.  Launches go to ex.stream.
+int fps_downsample(Exec& ex, Level* lv, float ratio, Level* ch, int64_t** idx_out) {
+    const int B = (int)lv->sptr.size() - 1;
+    std::vector<int32_t> meta(2 * (B > 0 ? B : 1));
+    int64_t total = 0;
+    int max_len = 0;
+    ch->sptr.assign(1, 0);
+    for (int b = 0; b < B; ++b) {
+        const int len = lv->sptr[b + 1] - lv->sptr[b];
+        meta[b] = (int32_t)std::ceil((float)len * ratio);     // torch.ceil(int64 tensor * python float) -> f32 (point_ops.py:63)
+        max_len = len > max_len ? len : max_len;
+    }
+    for (int b = 0; b < B; ++b) {
+        const int len = lv->sptr[b + 1] - lv->sptr[b];
+        meta[B + b] = (int32_t)ex.draw(ex.draw_user, DRAW_FPS_START, len, nullptr);
+    }
+    for (int b = 0; b < B; ++b) {
+        const int len = lv->sptr[b + 1] - lv->sptr[b];
+        total += meta[b] < len ? meta[b] : len;
+        ch->sptr.push_back((int)total);
+    }
+    int32_t* mdev = ex.alloc_n<int32_t>(2 * B);
+    float* closest = max_len > 512 * 16 ? ex.alloc_n<float>(lv->n) : nullptr;
+    int32_t* sel = ex.alloc_n<int32_t>(lv->n);
+    int64_t* idx = ex.alloc_n<int64_t>(total);
+    int32_t* sdev = ex.alloc_n<int32_t>(B + 1);
+    ch->n = total; ch->has_sptr = true; ch->sptr_dev = sdev;
+    *idx_out = idx;
+    if (ex.oom) return CCN_OK;
+    EX_CALL(ex.h2d(mdev, meta.data(), 4 * (size_t)(2 * B)));
+    {
+        ProfScope ps(ex, FAM_SAMPLE, 0, 12.0 * lv->n + 4.0 * total);
+        EX_CALL(ccn_fps(lv->pos.f, lv->sptr_dev, B, lv->n, mdev, mdev + B, max_len, closest, sel, idx, nullptr, (ccn_stream_t)ex.stream));
+    }
+    EX_CALL(ex.h2d(sdev, ch->sptr.data(), 4 * (size_t)(B + 1)));
+    return CCN_OK;
+}
+
+// Right after step `si` has created level `lv` (its gathers are queued on the main stream): sample - and gather - the levels
+// of the following FPS `sa` steps on the side stream.  Their sizes are host arithmetic, their draws are the next draws of
+// the reference's sequence (no step in between draws), so nothing but the overlap changes.
+int presample_ahead(Exec& ex, int si, Level* lv) {
+    if (!ex.use_side || ex.prof || !ex.side || ex.fps_next[si] < 0 || ex.oom) return CCN_OK;
+    EX_CUDA(cudaEventRecord(ex.lvl_ready, ex.stream));
+    EX_CUDA(cudaStreamWaitEvent(ex.side, ex.lvl_ready, 0));
+    cudaStream_t main_stream = ex.stream;
+    ex.stream = ex.side;
+    int rc = CCN_OK;
+    for (int k = ex.fps_next[si]; k >= 0 && rc == CCN_OK && !ex.oom; k = ex.fps_next[k]) {
+        ex.levels.emplace_back();
+        Level* ch = &ex.levels.back();
+        int64_t* idx = nullptr;
+        rc = fps_downsample(ex, lv, (float)ex.steps[k].fv[1], ch, &idx);
+        if (rc == CCN_OK) rc = subset_level(ex, lv, idx, ch);
+        if (rc == CCN_OK && !ex.oom) {
+            Exec::Pre& pr = ex.pre[k];
+            if (!pr.ready && cudaEventCreateWithFlags(&pr.ready, cudaEventDisableTiming) != cudaSuccess) rc = CCN_EINVAL;
+            if (rc == CCN_OK && cudaEventRecord(pr.ready, ex.side) != cudaSuccess) rc = CCN_EINVAL;
+            pr.done = true; pr.ch = ch; pr.idx = idx;
+        }
+        lv = ch;
+    }
+    ex.stream = main_stream;
+    return rc;
 }
 
 }  // namespace
@@ -475,6 +600,16 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
         for (int k = 0; k < nf; ++k) s.fv.push_back(F());
         ex.steps.push_back(s);
     }
+    ex.fps_next.assign(ex.steps.size(), -1);
+    ex.pre.resize(ex.steps.size());
+    for (size_t i = 0; i < ex.steps.size(); ++i) {
+        if (ex.steps[i].kind != ST_SA && ex.steps[i].kind != ST_SA_GEO) continue;
+        for (size_t j = i + 1; j < ex.steps.size(); ++j) {
+            const int k = ex.steps[j].kind;
+            if (k == ST_SA && ex.steps[j].iv[0] == DOWN_FPS) { ex.fps_next[i] = (int)j; break; }
+            if (k == ST_SA || k == ST_SA_GEO || k == ST_FP || k == ST_FP_GEO) break;      // another level change first
+        }
+    }
     const int n_om = (int)I();
     for (int i = 0; i < n_om; ++i) ex.out_mlp.push_back((int)I());
     if (ci != n_i || cf != n_f) { delete h; return CCN_EINVAL; }
@@ -482,6 +617,10 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
         cudaHostAlloc((void**)&ex.h2d_ring, kH2dRing, cudaHostAllocDefault) != cudaSuccess) {
         delete h;
         return CCN_EINVAL;
+    }
+    if (cudaStreamCreateWithFlags(&ex.side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ex.lvl_ready, cudaEventDisableTiming) != cudaSuccess) {
+        ex.side = nullptr;                       // no side stream: everything stays on the caller's stream
     }
     *out = h;
     return CCN_OK;
@@ -491,11 +630,36 @@ extern "C" void ccn_exec_destroy(ccn_exec_t* h) {
     if (!h) return;
     if (h->ex.pinned) cudaFreeHost(h->ex.pinned);
     if (h->ex.h2d_ring) cudaFreeHost(h->ex.h2d_ring);
+    if (h->ex.side) cudaStreamDestroy(h->ex.side);
+    if (h->ex.lvl_ready) cudaEventDestroy(h->ex.lvl_ready);
+    for (Exec::Pre& pr : h->ex.pre) if (pr.ready) cudaEventDestroy(pr.ready);
+    for (cudaEvent_t e : h->ex.prof_pool) cudaEventDestroy(e);
     if (h->ex.noise_host) cudaFreeHost(h->ex.noise_host);
     delete h;
 }
 
 extern "C" int32_t ccn_exec_topology_flags(const ccn_exec_t* h) { return h ? h->ex.topo_flags : 0; }
+
+extern "C" int ccn_exec_profile(ccn_exec_t* h, int32_t enable, int32_t spin_cycles) {
+    CCN_REQUIRE(h);
+    h->ex.prof = enable != 0;
+    h->ex.prof_spin = spin_cycles;
+    return CCN_OK;
+}
+
+// out[family][4] = {milliseconds, launches, algorithmic FLOPs, algorithmic bytes} of the LAST forward, summed per kernel family
+// (0 Linear, 1 fused edge steps, 2 curve-conv GEMMs, 3 neighbour search, 4 samplers); synchronises the device.
+extern "C" int ccn_exec_profile_read(ccn_exec_t* h, double* out, int32_t n_families) {
+    CCN_REQUIRE(h && out && n_families >= FAM_COUNT);
+    for (int i = 0; i < 4 * n_families; ++i) out[i] = 0.0;
+    for (const Exec::ProfRec& r : h->ex.prof_recs) {
+        if (cudaEventSynchronize(r.b) != cudaSuccess) return CCN_EINVAL;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.a, r.b) != cudaSuccess) return CCN_EINVAL;
+        out[4 * r.fam] += ms; out[4 * r.fam + 1] += 1; out[4 * r.fam + 2] += r.flops; out[4 * r.fam + 3] += r.bytes;
+    }
+    return CCN_OK;
+}
 
 namespace {
 
@@ -504,6 +668,9 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
     ex.feats.clear();
     ex.levels.clear();
     ex.topo_flags = 0;
+    ex.prof_recs.clear();
+    ex.prof_used = 0;
+    for (Exec::Pre& pr : ex.pre) { pr.done = false; pr.ch = nullptr; pr.idx = nullptr; }
     ccn_stream_t st = (ccn_stream_t)ex.stream;
 
     ex.levels.emplace_back();
@@ -573,6 +740,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                         if (last) {
                             Feat* y = ex.new_feat(np, cv.cout);
                             y->pl = ex.alloc_planes(np, cv.cout);
+                            ProfScope ps(ex, FAM_CONV, 2.0 * rows * cv.taps * cv.cin * cv.cout, 4.0 * np * cv.cout + 2.0 * ex.npl * cv.taps * cv.cin * cv.cout);
                             if (!ex.oom)
                                 EX_CALL(ccn_conv_planes(sigp.buf, sigp.kpad, sigp.pstride, cv.cin, cv.taps, L.map_hi[bs], L.map_lo[bs],
                                                         cv.bias, y->f, cv.cout, y->pl.buf, y->pl.kpad, y->pl.pstride, rows, cv.cout,
@@ -580,6 +748,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                             sig = y;
                         } else {
                             Planes yp = ex.alloc_planes(rows, cv.cout);
+                            ProfScope ps(ex, FAM_CONV, 2.0 * rows * cv.taps * cv.cin * cv.cout, 2.0 * ex.npl * cv.taps * cv.cin * cv.cout);
                             if (!ex.oom)
                                 EX_CALL(ccn_conv_planes(sigp.buf, sigp.kpad, sigp.pstride, cv.cin, cv.taps, L.map_hi[bs], L.map_lo[bs],
                                                         cv.bias, nullptr, cv.cout, yp.buf, yp.kpad, yp.pstride, rows, cv.cout, box,
@@ -642,9 +811,16 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     const Chain& ch = ex.chains[chain];
                     Feat* o = ex.new_feat(lv->n, ch.n_out);
                     if (lv->n) o->pl = ex.alloc_planes(lv->n, ch.n_out);
-                    if (!ex.oom)
+                    if (!ex.oom) {
+                        double mac = 0;
+                        for (int l = 0; l < ch.desc->n_layers; ++l) mac += (double)ch.desc->k[l] * ch.desc->n[l];
+                        // valid rows = self loops + found neighbours; the padded n (K+1) rows bound them (the count stays on the device)
+                        const double rows = (double)lv->n * (K + 1);
+                        ProfScope ps(ex, FAM_EDGE_FUSED, 2.0 * rows * mac,
+                                     8.0 * lv->n * c1 + 4.0 * lv->n * K + lv->n * (12.0 + 4.0 * ch.n_out) + mac * 2 * ex.npl);
                         EX_CALL(ccn_sgcnn_fused(PQ->f, PQ->ld, nbr, lv->n, K, c1, act0, slope0, ch.desc, o->f, o->ld, o->pl.buf, o->pl.kpad,
                                                 o->pl.pstride, o->pl.buf ? ex.npl : 0, st));
+                    }
                     outp.x = o;
                     break;
                 }
@@ -659,7 +835,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     const Linear& L = ex.lins[iv[6 + i]];
                     const bool last = i == n_rest - 1;
                     Planes yp;
-                    EX_CALL(linear_planes(ex, L, &seg, 1, rows, last ? 0 : 1, &y, &yp));
+                    EX_CALL(linear_planes(ex, L, &seg, 1, rows, last ? 0 : 1, &y, &yp, 0));
                     if (!last) seg = Seg{yp.buf, yp.kpad, yp.pstride, L.n};
                 }
                 Feat* o = ex.new_feat(lv->n, y->c);
@@ -680,9 +856,10 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 // SA_GEO: iv: with_xyz, use_curve_fps, [pointconv block];  fv: arclen, ratio, radius, [slope0, nradius]
                 // SA:     iv: down, K, [pointconv block];                  fv: voxel, ratio, radius, [slope0, nradius]
                 Level* lv = cur.lv;
-                ex.levels.emplace_back();
-                Level* ch = &ex.levels.back();
-                int64_t* idx = nullptr;
+                const bool presampled = ex.pre[si].done;
+                if (!presampled) ex.levels.emplace_back();
+                Level* ch = presampled ? ex.pre[si].ch : &ex.levels.back();
+                int64_t* idx = presampled ? ex.pre[si].idx : nullptr;
                 Edges e{};
                 const float radius = (float)fv[2];
                 if (s.kind == ST_SA_GEO) {
@@ -694,7 +871,10 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 const int B = (int)lv->sptr.size() - 1;
                 const bool curve_fps = s.kind == ST_SA_GEO && iv[1];
                 const int down = s.kind == ST_SA ? (int)iv[0] : DOWN_FPS;
-                if (curve_fps) {
+                if (presampled) {
+                    // sampled (and gathered) ahead on the side stream: the main stream joins it here
+                    EX_CUDA(cudaStreamWaitEvent(ex.stream, ex.pre[si].ready, 0));
+                } else if (curve_fps) {
                     // ops.curve_fps
                     float u = 0.f;
                     ex.draw(ex.draw_user, DRAW_CURVE_PHASE, 1, &u);
@@ -704,6 +884,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     float* udev = ex.alloc_n<float>(1);
                     if (!ex.oom) {
                         EX_CALL(ex.h2d(udev, &u, 4));
+                        ProfScope ps(ex, FAM_SAMPLE, 0, 20.0 * lv->n);
                         EX_CALL(ccn_curve_fps(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->n, udev, (float)fv[0], run, idx, cnt, st));
                         EX_CALL(finish_subset(ex, lv, idx, lv->n > 0 ? lv->n : 1, cnt, ch));
                     }
@@ -724,6 +905,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     if (!ex.oom) {
                         EX_CUDA(cudaMemcpyAsync(noise, ex.noise_host, 4 * (size_t)lv->n, cudaMemcpyHostToDevice, ex.stream));
                         int32_t* counts = ints + 2 * n1;
+                        ProfScope ps(ex, FAM_SAMPLE, 0, 20.0 * lv->n);
                         EX_CALL(ccn_voxel_fps(lv->pos.f, lv->batch, lv->n, (float)fv[0], noise, slots, table, table + slots,
                                               table + 2 * slots, ints, ints + n1, idx, counts, st));
                         EX_CALL(finish_subset(ex, lv, idx, n1, counts, ch));
@@ -731,37 +913,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                         if (ex.pinned[0]) return CCN_EVOXEL_RANGE;
                     }
                 } else {
-                    // modules.fps_sorted: K = ceil(len * ratio) in f32, random start per cloud, sorted result
-                    std::vector<int32_t> meta(2 * B);
-                    const float ratio = (float)fv[1];
-                    int64_t total = 0;
-                    int max_len = 0;
-                    ch->sptr.assign(1, 0);
-                    for (int b = 0; b < B; ++b) {
-                        const int len = lv->sptr[b + 1] - lv->sptr[b];
-                        meta[b] = (int32_t)std::ceil((float)len * ratio);     // torch.ceil(int64 tensor * python float) -> f32 (point_ops.py:63)
-                        max_len = len > max_len ? len : max_len;
-                    }
-                    for (int b = 0; b < B; ++b) {
-                        const int len = lv->sptr[b + 1] - lv->sptr[b];
-                        meta[B + b] = (int32_t)ex.draw(ex.draw_user, DRAW_FPS_START, len, nullptr);
-                    }
-                    for (int b = 0; b < B; ++b) {
-                        const int len = lv->sptr[b + 1] - lv->sptr[b];
-                        total += meta[b] < len ? meta[b] : len;
-                        ch->sptr.push_back((int)total);
-                    }
-                    int32_t* mdev = ex.alloc_n<int32_t>(2 * B);
-                    float* closest = max_len > 512 * 16 ? ex.alloc_n<float>(lv->n) : nullptr;
-                    int32_t* sel = ex.alloc_n<int32_t>(lv->n);
-                    idx = ex.alloc_n<int64_t>(total);
-                    int32_t* sdev = ex.alloc_n<int32_t>(B + 1);
-                    ch->n = total; ch->has_sptr = true; ch->sptr_dev = sdev;
-                    if (!ex.oom) {
-                        EX_CALL(ex.h2d(mdev, meta.data(), 4 * (size_t)(2 * B)));
-                        EX_CALL(ccn_fps(lv->pos.f, lv->sptr_dev, B, lv->n, mdev, mdev + B, max_len, closest, sel, idx, nullptr, st));
-                        EX_CALL(ex.h2d(sdev, ch->sptr.data(), 4 * (size_t)(B + 1)));
-                    }
+                    EX_CALL(fps_downsample(ex, lv, (float)fv[1], ch, &idx));
                 }
                 if (ex.oom) return CCN_ENOMEM;
                 const int64_t* pc_iv;
@@ -793,13 +945,15 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                         EX_CALL(ccn_csr_rows(buf, nq, erow, st));
                     }
                     e = Edges{buf, erow, col, E, nq, max_deg};
-                    EX_CALL(subset_level(ex, lv, idx, ch));
+                    if (!presampled) EX_CALL(subset_level(ex, lv, idx, ch));
+                    EX_CALL(presample_ahead(ex, (int)si, ch));
                     pc_iv = iv + 2;
                     if (cur.x) xparts[nxp++] = cur.x;
                     if (iv[0] || !cur.x) xparts[nxp++] = &lv->pos;
                 } else {
                     const int K = (int)iv[1];
-                    EX_CALL(subset_level(ex, lv, idx, ch));
+                    if (!presampled) EX_CALL(subset_level(ex, lv, idx, ch));
+                    EX_CALL(presample_ahead(ex, (int)si, ch));
                     int32_t *nbr = nullptr, *cnt = nullptr;
                     EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));
                     EX_CALL(dense_to_csr(ex, nbr, cnt, ch->n, K, &e));
@@ -827,6 +981,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 float* wgt = ex.alloc_n<float>(fine->n * knn);
                 if (s.kind == ST_FP) {
                     EX_CALL(level_sptr(ex, cur.lv));
+                    ProfScope ps(ex, FAM_SEARCH, 0, 12.0 * fine->n + 12.0 * cur.lv->n + 8.0 * fine->n * knn);
                     if (!ex.oom)
                         EX_CALL(ccn_knn_exact(fine->pos.f, fine->batch, fine->n, cur.lv->pos.f, cur.lv->sptr_dev, knn, 1, nbr, wgt, nullptr, st));
                 } else {

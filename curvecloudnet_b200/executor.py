@@ -235,6 +235,25 @@ class NativeExecutor:
         except Exception:
             pass
 
+    FAMILIES = ("linear", "edge_fused", "conv", "search", "sample")
+
+    def profile(self, enable: bool, spin_cycles: int = 20000):
+        """Per-family device timing of the following forwards (CUDA events around every launch of a family; the FPS
+        look-ahead on the side stream is off meanwhile)."""
+        rc = self.lib.ccn_exec_profile(self.handle, int(bool(enable)), int(spin_cycles))
+        if rc:
+            raise native.CcnError("ccn_exec_profile failed (code %d)" % rc)
+
+    def profile_read(self):
+        """{family: {"ms", "calls", "flops", "bytes"}} of the last forward (synchronises)."""
+        n = len(self.FAMILIES)
+        buf = (ctypes.c_double * (4 * n))()
+        rc = self.lib.ccn_exec_profile_read(self.handle, ctypes.cast(buf, ctypes.c_void_p), n)
+        if rc:
+            raise native.CcnError("ccn_exec_profile_read failed (code %d)" % rc)
+        return {f: {"ms": buf[4 * i], "calls": buf[4 * i + 1], "flops": buf[4 * i + 2], "bytes": buf[4 * i + 3]}
+                for i, f in enumerate(self.FAMILIES)}
+
     def _draw_fn(self, draws, errors):
         def cb(user, kind, n, out):
             try:

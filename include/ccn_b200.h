@@ -461,6 +461,12 @@ typedef int64_t (*ccn_draw_fn)(void* user, int32_t kind, int64_t n, void* out);
 int ccn_exec_create(const int64_t* iplan_host, int64_t n_i, const double* fplan_host, int64_t n_f, ccn_exec_t** out);
 void ccn_exec_destroy(ccn_exec_t* exec);
 int32_t ccn_exec_topology_flags(const ccn_exec_t* exec);
+/* optional per-family device timing of ccn_forward_run (CUDA events on `stream` around every launch of a family, a spin of
+ * spin_cycles GPU cycles queued before each so that the pair brackets the kernel, not the launch gap): out[family][4] =
+ * {ms, launches, algorithmic FLOPs, algorithmic bytes} of the last forward; families: 0 Linear, 1 fused edge
+ * steps, 2 curve-conv GEMMs, 3 neighbour search, 4 samplers.  n_families >= 5. */
+int ccn_exec_profile(ccn_exec_t* exec, int32_t enable, int32_t spin_cycles);
+int ccn_exec_profile_read(ccn_exec_t* exec, double* out_host, int32_t n_families);
 int ccn_forward_run(ccn_exec_t* exec, const float* x, int64_t ldx, const float* pos, const int64_t* batch,
                     const int64_t* curve_idxs, int64_t n, void* arena, int64_t arena_bytes, ccn_draw_fn draw,
                     void* draw_user, float* logits, int64_t ld_logits, int64_t* arena_needed_host, ccn_stream_t stream);

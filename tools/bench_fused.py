@@ -68,3 +68,52 @@ for n, K, dims in [(17809, 20, [64, 64, 64]), (5695, 20, [128, 128]), (1933, 20,
     tf, tu = timed(fused), timed(unfused)
     print("sgcnn n=%6d rows=%7d dims=%-16s fused %7.1f us (%6.1f TF/s alg)   unfused %7.1f us   x%.2f"
           % (n, rows, dims, tf, flops / tf / 1e6, tu, tu / tf))
+
+
+def random_csr(nq, n_src, avg_deg, max_deg, seed):
+    gen = torch.Generator().manual_seed(seed)
+    deg = torch.clamp((torch.rand(nq, generator=gen) * 2 * avg_deg).long() + 1, max=max_deg)
+    row_ptr = torch.zeros(nq + 1, dtype=torch.int64)
+    row_ptr[1:] = torch.cumsum(deg, 0)
+    E = int(row_ptr[-1])
+    erow = torch.repeat_interleave(torch.arange(nq), deg)
+    ecol = torch.randint(0, n_src, (E,), generator=gen)
+    return ops.EdgeCSR(row_ptr.to(torch.int32).cuda(), erow.to(torch.int32).cuda(), ecol.to(torch.int32).cuda(), E, nq, max_deg)
+
+
+for name, nq, n_src, avg, mx, dims, att_h, mode in [("sa-geo", 17809, 32568, 5.2, 9, [64, 128, 192, 256], 256, "attend"),
+                                                    ("sa L1->L2", 5695, 17809, 11.6, 32, [128, 128, 128], 64, "attend"),
+                                                    ("sa L2->L3", 1933, 5695, 17, 32, [256, 256, 256], 128, "attend")]:
+    edges = random_csr(nq, n_src, avg, mx, nq)
+    gen = torch.Generator().manual_seed(7)
+    c1, C = dims[0], dims[-1]
+    H = torch.randn(n_src, c1, generator=gen).cuda()
+    wp = torch.randn(3, c1, generator=gen).cuda()
+    b0 = (torch.randn(c1, generator=gen) * 0.1).cuda()
+    ps, pd = torch.rand(n_src, 3, generator=gen).cuda(), torch.rand(nq, 3, generator=gen).cuda()
+    local = layers_of(dims, [2] * (len(dims) - 2) + [0])
+    attend = layers_of([C, att_h, C], [2, 0])
+    chain = ops.ChainWeights(local + attend, npl)
+    ll = [PreparedLinear(w, b, a, s) for w, b, a, s in local]
+    al = [PreparedLinear(w, b, a, s) for w, b, a, s in attend]
+
+    def fused():
+        return ops.pointconv_fused(edges, chain, mode, len(local) - 1, 2, 0.01, c1, H=H, wp=wp, bias0=b0, pos_src=ps, pos_dst=pd,
+                                   radius=0.02, npl=npl, cache=ForwardCache())
+
+    def unfused():
+        h = ops.edge_layer1(H, wp, b0, ps, pd, edges, 0.02, 2, 0.01, npl)
+        for i, lin in enumerate(ll):
+            h = lin(h, "both" if i == len(ll) - 1 else "planes")
+        msg, a_in = h
+        for i, lin in enumerate(al):
+            a_in = lin(a_in, "f32" if i == len(al) - 1 else "planes")
+        return ops.seg_aggregate(msg, a_in, edges.row_ptr, edges.nq, mode, npl, ForwardCache())
+
+    a, b = fused(), unfused()
+    assert torch.equal(a, b)
+    alld = dims + [att_h, C]
+    flops = 2.0 * edges.n_edges * (sum(k * m for k, m in zip(dims[:-1], dims[1:])) + C * att_h + att_h * C)
+    tf, tu = timed(fused), timed(unfused)
+    print("%-10s E=%6d nq=%5d dims=%-22s fused %7.1f us (%6.1f TF/s alg)   unfused %7.1f us   x%.2f"
+          % (name, edges.n_edges, nq, alld, tf, flops / tf / 1e6, tu, tu / tf))
