@@ -115,8 +115,10 @@ struct Exec {
     // farthest-point sampling of the NEXT levels runs ahead on a side stream (one CTA per cloud, K sequential rounds: 0.3 ms on
     // one SM at B = 1) while the main stream runs the edge steps of the current level; events order the two
     cudaStream_t side = nullptr;
-    std::vector<int> fps_next;          // per step: the next `sa` step that FPS-samples the level this step creates (-1: none)
-    struct Pre { bool done = false; Level* ch = nullptr; int64_t* idx = nullptr; cudaEvent_t ready = nullptr; };
+    std::vector<int> fps_next;          // per step: the next `sa` step (FPS or voxel sampling) on the level this step creates (-1: none)
+    struct VoxelJob { int64_t* idx = nullptr; int32_t* out = nullptr; int B = 0; int64_t n1 = 0; };
+    struct Pre { bool done = false; bool voxel = false; Level* ch = nullptr; int64_t* idx = nullptr; cudaEvent_t ready = nullptr; VoxelJob job; };
+    int32_t* pinned_side = nullptr;     // read-back buffer of the side stream
     std::vector<Pre> pre;
     cudaEvent_t lvl_ready = nullptr;
     bool use_side = true;
@@ -485,6 +487,48 @@ int dense_to_csr(Exec& ex, int32_t* idx, int32_t* cnt, int64_t nq, int K, Edges*
     return ccn_dense_to_csr(idx, cnt, nq, K, erow, ecol, (ccn_stream_t)ex.stream);
 }
 
+// ops.voxel_fps + ops._finish_subset, split in two: `launch` queues the sampler, the sample CSR of the kept points and the
+// read-back of {CSR, error flag} into `host` on ex.stream WITHOUT waiting; `collect` (after that stream work is complete)
+// sizes the new level.  One read-back instead of the python path's two.
+int voxel_launch(Exec& ex, Level* lv, float voxel, int32_t* host, Exec::VoxelJob* job) {
+    const int64_t n1 = lv->n > 0 ? lv->n : 1;
+    const int B = (int)lv->sptr.size() - 1;
+    const int64_t slots = ccn_voxel_table_slots(lv->n);
+    uint64_t* table = ex.alloc_n<uint64_t>(2 * slots + n1);
+    int32_t* ints = ex.alloc_n<int32_t>(2 * n1 + 2);
+    int64_t* idx = ex.alloc_n<int64_t>(n1);
+    float* noise = ex.alloc_n<float>(n1);
+    int32_t* out = ex.alloc_n<int32_t>(B + 2);
+    if ((size_t)n1 > ex.noise_cap) {
+        if (ex.noise_host) cudaFreeHost(ex.noise_host);
+        ex.noise_cap = (size_t)n1 * 2;
+        EX_CUDA(cudaHostAlloc((void**)&ex.noise_host, 4 * ex.noise_cap, cudaHostAllocDefault));
+    }
+    ex.draw(ex.draw_user, DRAW_VOXEL_NOISE, lv->n, ex.noise_host);
+    job->idx = idx; job->out = out; job->B = B; job->n1 = n1;
+    if (ex.oom) return CCN_OK;
+    EX_CUDA(cudaMemcpyAsync(noise, ex.noise_host, 4 * (size_t)lv->n, cudaMemcpyHostToDevice, ex.stream));
+    int32_t* counts = ints + 2 * n1;
+    {
+        ProfScope ps(ex, FAM_SAMPLE, 0, 20.0 * lv->n);
+        EX_CALL(ccn_voxel_fps(lv->pos.f, lv->batch, lv->n, voxel, noise, slots, table, table + slots, table + 2 * slots, ints,
+                              ints + n1, idx, counts, (ccn_stream_t)ex.stream));
+    }
+    EX_CALL(ccn_subset_sample_ptr(lv->batch, idx, counts, n1, B, out, (ccn_stream_t)ex.stream));
+    EX_CUDA(cudaMemcpyAsync(host, out, 4 * (size_t)(B + 1), cudaMemcpyDeviceToHost, ex.stream));
+    EX_CUDA(cudaMemcpyAsync(host + B + 1, counts + 1, 4, cudaMemcpyDeviceToHost, ex.stream));
+    return CCN_OK;
+}
+
+int voxel_collect(const int32_t* host, const Exec::VoxelJob& job, Level* ch) {
+    if (host[job.B + 1]) return CCN_EVOXEL_RANGE;
+    ch->sptr.assign(host, host + job.B + 1);
+    ch->sptr_dev = job.out;
+    ch->has_sptr = true;
+    ch->n = ch->sptr[job.B];
+    return CCN_OK;
+}
+
 // modules.fps_sorted + ops.fps: K = ceil(len * ratio) in f32 (point_ops.py:63), random start per cloud, selected indices sorted;
 // the level sizes follow from the parent's sample CSR on the host - no read-back.  Launches go to ex.stream.
 int fps_downsample(Exec& ex, Level* lv, float ratio, Level* ch, int64_t** idx_out) {
@@ -529,6 +573,7 @@ int fps_downsample(Exec& ex, Level* lv, float ratio, Level* ch, int64_t** idx_ou
 // the reference's sequence (no step in between draws), so nothing but the overlap changes.
 int presample_ahead(Exec& ex, int si, Level* lv) {
     if (!ex.use_side || ex.prof || !ex.side || ex.fps_next[si] < 0 || ex.oom) return CCN_OK;
+    if (ex.pre[ex.fps_next[si]].done) return CCN_OK;      // already sampled as part of an earlier step's look-ahead chain
     EX_CUDA(cudaEventRecord(ex.lvl_ready, ex.stream));
     EX_CUDA(cudaStreamWaitEvent(ex.side, ex.lvl_ready, 0));
     cudaStream_t main_stream = ex.stream;
@@ -538,13 +583,24 @@ int presample_ahead(Exec& ex, int si, Level* lv) {
         ex.levels.emplace_back();
         Level* ch = &ex.levels.back();
         int64_t* idx = nullptr;
+        if (ex.steps[k].iv[0] == DOWN_VOXEL) {
+            // voxel sampling: the size of the new level is data dependent - queue the sampler and its read-back, stop the chain
+            Exec::Pre& pr = ex.pre[k];
+            rc = voxel_launch(ex, lv, (float)ex.steps[k].fv[0], ex.pinned_side, &pr.job);
+            if (rc == CCN_OK && !ex.oom) {
+                if (!pr.ready && cudaEventCreateWithFlags(&pr.ready, cudaEventDisableTiming) != cudaSuccess) rc = CCN_EINVAL;
+                if (rc == CCN_OK && cudaEventRecord(pr.ready, ex.side) != cudaSuccess) rc = CCN_EINVAL;
+                pr.done = true; pr.voxel = true; pr.ch = ch;
+            }
+            break;
+        }
         rc = fps_downsample(ex, lv, (float)ex.steps[k].fv[1], ch, &idx);
         if (rc == CCN_OK) rc = subset_level(ex, lv, idx, ch);
         if (rc == CCN_OK && !ex.oom) {
             Exec::Pre& pr = ex.pre[k];
             if (!pr.ready && cudaEventCreateWithFlags(&pr.ready, cudaEventDisableTiming) != cudaSuccess) rc = CCN_EINVAL;
             if (rc == CCN_OK && cudaEventRecord(pr.ready, ex.side) != cudaSuccess) rc = CCN_EINVAL;
-            pr.done = true; pr.ch = ch; pr.idx = idx;
+            pr.done = true; pr.voxel = false; pr.ch = ch; pr.idx = idx;
         }
         lv = ch;
     }
@@ -606,7 +662,7 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
         if (ex.steps[i].kind != ST_SA && ex.steps[i].kind != ST_SA_GEO) continue;
         for (size_t j = i + 1; j < ex.steps.size(); ++j) {
             const int k = ex.steps[j].kind;
-            if (k == ST_SA && ex.steps[j].iv[0] == DOWN_FPS) { ex.fps_next[i] = (int)j; break; }
+            if (k == ST_SA) { ex.fps_next[i] = (int)j; break; }
             if (k == ST_SA || k == ST_SA_GEO || k == ST_FP || k == ST_FP_GEO) break;      // another level change first
         }
     }
@@ -614,7 +670,8 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
     for (int i = 0; i < n_om; ++i) ex.out_mlp.push_back((int)I());
     if (ci != n_i || cf != n_f) { delete h; return CCN_EINVAL; }
     if (cudaHostAlloc((void**)&ex.pinned, sizeof(int32_t) * (kMaxSamples + 16), cudaHostAllocDefault) != cudaSuccess ||
-        cudaHostAlloc((void**)&ex.h2d_ring, kH2dRing, cudaHostAllocDefault) != cudaSuccess) {
+        cudaHostAlloc((void**)&ex.h2d_ring, kH2dRing, cudaHostAllocDefault) != cudaSuccess ||
+        cudaHostAlloc((void**)&ex.pinned_side, sizeof(int32_t) * (kMaxSamples + 16), cudaHostAllocDefault) != cudaSuccess) {
         delete h;
         return CCN_EINVAL;
     }
@@ -630,6 +687,7 @@ extern "C" void ccn_exec_destroy(ccn_exec_t* h) {
     if (!h) return;
     if (h->ex.pinned) cudaFreeHost(h->ex.pinned);
     if (h->ex.h2d_ring) cudaFreeHost(h->ex.h2d_ring);
+    if (h->ex.pinned_side) cudaFreeHost(h->ex.pinned_side);
     if (h->ex.side) cudaStreamDestroy(h->ex.side);
     if (h->ex.lvl_ready) cudaEventDestroy(h->ex.lvl_ready);
     for (Exec::Pre& pr : h->ex.pre) if (pr.ready) cudaEventDestroy(pr.ready);
@@ -871,7 +929,12 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 const int B = (int)lv->sptr.size() - 1;
                 const bool curve_fps = s.kind == ST_SA_GEO && iv[1];
                 const int down = s.kind == ST_SA ? (int)iv[0] : DOWN_FPS;
-                if (presampled) {
+                if (presampled && ex.pre[si].voxel) {
+                    // the voxel sampler ran ahead on the side stream: wait for its read-back, size the level
+                    EX_CUDA(cudaEventSynchronize(ex.pre[si].ready));
+                    EX_CALL(voxel_collect(ex.pinned_side, ex.pre[si].job, ch));
+                    idx = ex.pre[si].job.idx;
+                } else if (presampled) {
                     // sampled (and gathered) ahead on the side stream: the main stream joins it here
                     EX_CUDA(cudaStreamWaitEvent(ex.stream, ex.pre[si].ready, 0));
                 } else if (curve_fps) {
@@ -889,29 +952,12 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                         EX_CALL(finish_subset(ex, lv, idx, lv->n > 0 ? lv->n : 1, cnt, ch));
                     }
                 } else if (down == DOWN_VOXEL) {
-                    // ops.voxel_fps
-                    const int64_t n1 = lv->n > 0 ? lv->n : 1;
-                    const int64_t slots = ccn_voxel_table_slots(lv->n);
-                    uint64_t* table = ex.alloc_n<uint64_t>(2 * slots + n1);
-                    int32_t* ints = ex.alloc_n<int32_t>(2 * n1 + 2);
-                    idx = ex.alloc_n<int64_t>(n1);
-                    float* noise = ex.alloc_n<float>(n1);
-                    if ((size_t)n1 > ex.noise_cap) {
-                        if (ex.noise_host) cudaFreeHost(ex.noise_host);
-                        ex.noise_cap = (size_t)n1 * 2;
-                        EX_CUDA(cudaHostAlloc((void**)&ex.noise_host, 4 * ex.noise_cap, cudaHostAllocDefault));
-                    }
-                    ex.draw(ex.draw_user, DRAW_VOXEL_NOISE, lv->n, ex.noise_host);
-                    if (!ex.oom) {
-                        EX_CUDA(cudaMemcpyAsync(noise, ex.noise_host, 4 * (size_t)lv->n, cudaMemcpyHostToDevice, ex.stream));
-                        int32_t* counts = ints + 2 * n1;
-                        ProfScope ps(ex, FAM_SAMPLE, 0, 20.0 * lv->n);
-                        EX_CALL(ccn_voxel_fps(lv->pos.f, lv->batch, lv->n, (float)fv[0], noise, slots, table, table + slots,
-                                              table + 2 * slots, ints, ints + n1, idx, counts, st));
-                        EX_CALL(finish_subset(ex, lv, idx, n1, counts, ch));
-                        EX_CALL(ex.readback(counts + 1, 1));
-                        if (ex.pinned[0]) return CCN_EVOXEL_RANGE;
-                    }
+                    Exec::VoxelJob job;
+                    EX_CALL(voxel_launch(ex, lv, (float)fv[0], ex.pinned, &job));
+                    if (ex.oom) return CCN_ENOMEM;
+                    EX_CUDA(cudaStreamSynchronize(ex.stream));
+                    EX_CALL(voxel_collect(ex.pinned, job, ch));
+                    idx = job.idx;
                 } else {
                     EX_CALL(fps_downsample(ex, lv, (float)fv[1], ch, &idx));
                 }
@@ -952,7 +998,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     if (iv[0] || !cur.x) xparts[nxp++] = &lv->pos;
                 } else {
                     const int K = (int)iv[1];
-                    if (!presampled) EX_CALL(subset_level(ex, lv, idx, ch));
+                    if (!presampled || ex.pre[si].voxel) EX_CALL(subset_level(ex, lv, idx, ch));
                     EX_CALL(presample_ahead(ex, (int)si, ch));
                     int32_t *nbr = nullptr, *cnt = nullptr;
                     EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));

@@ -29,11 +29,12 @@ class _ChainCache:
 
     def get(self, layers, extra=()):
         npl = n_planes()
-        key = (id(layers), npl, id(extra) if extra else 0)
+        key = (id(layers), npl, id(extra) if extra else 0, ops.FUSED_EDGE_STEPS)
         if self.key != key:
             rest = list(layers[1:]) + list(extra)
-            ok = (npl > 0 and ops.FUSED_EDGE_STEPS and len(rest) >= 1 and
-                  ops.ChainWeights.supported(layers[0].out_features, [l.out_features for l in rest]))
+            ok = (npl > 0 and len(rest) >= 1 and
+                  ops.ChainWeights.supported(layers[0].out_features, [l.out_features for l in rest]) and
+                  ops.fused_profitable(layers[0].out_features, npl, bool(extra)))
             self.chain = ops.ChainWeights([(l.w, l.b, l.act, l.slope) for l in rest], npl) if ok else None
             self.key, self._keep = key, (layers, extra)
         return self.chain

@@ -18,7 +18,9 @@ from .native import call
 ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
 AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3, "sum": 4}
 MAX_SAMPLES = 4096
-FUSED_EDGE_STEPS = True     # tests switch it off to compare the fused edge kernels with the unfused chain
+# Fused edge-step kernels (csrc/edge_fused.cu): "auto" = where they are the faster path today (fused_profitable), True = wherever
+# the kernel covers the shapes, False = never (the unfused chain of launches).  All three give bit-identical results.
+FUSED_EDGE_STEPS = "auto"
 TOPO_ERRORS = {1: "batch vector is not sorted", 2: "curve ids are not sorted within a sample",
                4: "more than %d samples in a batch" % MAX_SAMPLES, 8: "batch ids are not 0..B-1"}
 
@@ -896,6 +898,16 @@ class ChainWeights:
         """dims: output widths of the chain layers.  Every width a multiple of 64 and <= 256."""
         return (len(dims) >= 1 and len(dims) <= CHAIN_MAX_LAYERS and c1 % 64 == 0 and 64 <= c1 <= CHAIN_MAX_WIDTH and
                 all(d % 64 == 0 and 64 <= d <= CHAIN_MAX_WIDTH for d in dims))
+
+
+def fused_profitable(c1: int, n_planes: int, attention: bool) -> bool:
+    """Measured on B200 (tools/bench_fused.py, profiles/r02g_fused.txt): the one-kernel edge step wins for the NARROW chains
+    (resident activation tile <= 32 KB: two CTAs per SM overlap each other's latency chains) - the 374 k-row level-1 SGCNN
+    steps, 96 us against 116 us in bf16x3 - and loses to the unfused launches on the 128 / 256-wide chains (one CTA per SM,
+    the serial form -> MMA -> epilogue chain of a tile is not hidden) and on the attention steps (1.5x slower)."""
+    if FUSED_EDGE_STEPS != "auto":
+        return bool(FUSED_EDGE_STEPS)
+    return (not attention) and c1 * n_planes <= 128
 
 
 def sgcnn_fused(PQ: torch.Tensor, idx: torch.Tensor, act0: int, slope0: float, chain: ChainWeights, npl: int = 0,

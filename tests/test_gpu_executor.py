@@ -73,3 +73,26 @@ def test_other_configs_fall_back_to_the_python_executor():
         want = py_model(data)
     assert native_model.__dict__["_native"][1] is None
     assert torch.equal(got, want)
+
+
+@pytest.mark.parametrize("native", [True, False])
+def test_fused_edge_step_setting_does_not_change_the_logits(native):
+    """ops.FUSED_EDGE_STEPS: "auto" (fused kernels where they are the faster path), True (wherever they cover the shapes),
+    False (unfused launches) - the same arithmetic in the same order, bit-identical logits on both executors."""
+    from curvecloudnet_b200 import ops
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    data = driving_scan_batch([6], subsample=5000).to("cuda")
+    outs = {}
+    prev = ops.FUSED_EDGE_STEPS
+    try:
+        for setting in ("auto", True, False):
+            ops.FUSED_EDGE_STEPS = setting
+            model = randomize_model_(build_model(ModelBase, "nuscenes", precision="bf16x3", native_executor=native), 1234).cuda().eval()
+            with torch.no_grad():
+                torch.manual_seed(9)
+                outs[setting] = model(data)
+    finally:
+        ops.FUSED_EDGE_STEPS = prev
+    assert torch.equal(outs["auto"], outs[True]) and torch.equal(outs["auto"], outs[False])
