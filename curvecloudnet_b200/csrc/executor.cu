@@ -77,8 +77,9 @@ struct Feat {                  // an fp32 feature matrix and (lazily) its activa
     Planes pl;
 };
 
-struct Grid { float radius; int64_t cells; int32_t* cell_off; float* sorted; };
-struct KnnMemo { int K; float radius; int32_t* idx; };
+// `ready`: recorded on the geometry stream when the entry was produced there; the main stream waits for it once (then null)
+struct Grid { float radius; int64_t cells; int32_t* cell_off; float* sorted; cudaEvent_t ready; };
+struct KnnMemo { int K; float radius; int32_t* idx; cudaEvent_t ready; };
 
 struct Level {                 // one point set of the pyramid
     int64_t n = 0;
@@ -122,6 +123,24 @@ struct Exec {
     std::vector<Pre> pre;
     cudaEvent_t lvl_ready = nullptr;
     bool use_side = true;
+    // neighbour searches depend on positions only: as soon as a level exists, the kNN tables of the sgcnn steps that will run
+    // on it and the interpolation table of the fp / fp-geo step that will return to its parent are computed on a second side
+    // stream (`geo`), concurrently with the feature kernels of the main stream
+    cudaStream_t geo = nullptr;
+    std::vector<int> fp_partner;        // per down step: the fp / fp-geo step that pops it (-1: none)
+    struct UpMemo { bool valid = false; int32_t* nbr = nullptr; float* wgt = nullptr; cudaEvent_t ready = nullptr; };
+    std::vector<UpMemo> up;             // per fp step: its interpolation table, if computed ahead
+    std::vector<cudaEvent_t> geo_events;
+    size_t geo_used = 0;
+    cudaEvent_t geo_event() {
+        if (geo_used == geo_events.size()) {
+            cudaEvent_t e = nullptr;
+            cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+            geo_events.push_back(e);
+        }
+        return geo_events[geo_used++];
+    }
+    bool on_main() const { return stream != side && stream != geo; }
     ccn_draw_fn draw = nullptr;
     void* draw_user = nullptr;
     int topo_flags = 0;
@@ -359,14 +378,26 @@ int subset_level(Exec& ex, Level* parent, const int64_t* idx, Level* child) {
 int frnn(Exec& ex, Level* q, Level* src, int K, float radius, bool want_cnt, int32_t** idx_out, int32_t** cnt_out) {
     const bool self = q == src;
     if (self && !want_cnt)
-        for (const KnnMemo& m : src->knn)
-            if (m.K == K && m.radius == radius) { *idx_out = m.idx; return CCN_OK; }
-    const Grid* g = nullptr;
-    for (const Grid& gg : src->grids)
+        for (KnnMemo& m : src->knn)
+            if (m.K == K && m.radius == radius) {
+                if (m.ready && ex.on_main()) {             // produced on the geometry stream: join it once
+                    EX_CUDA(cudaStreamWaitEvent(ex.stream, m.ready, 0));
+                    m.ready = nullptr;
+                }
+                *idx_out = m.idx;
+                return CCN_OK;
+            }
+    Grid* g = nullptr;
+    for (Grid& gg : src->grids)
         if (gg.radius == radius) g = &gg;
+    if (g && g->ready && ex.on_main()) {
+        EX_CUDA(cudaStreamWaitEvent(ex.stream, g->ready, 0));
+        g->ready = nullptr;
+    }
     if (!g) {
         Grid ng;
         ng.radius = radius;
+        ng.ready = nullptr;
         ng.cells = ccn_grid_num_cells(src->n);
         ng.cell_off = ex.alloc_n<int32_t>(ng.cells + 1);
         int32_t* slot = ex.alloc_n<int32_t>(src->n);
@@ -386,7 +417,7 @@ int frnn(Exec& ex, Level* q, Level* src, int K, float radius, bool want_cnt, int
     ProfScope ps(ex, FAM_SEARCH, 0, 12.0 * q->n + 16.0 * src->n + 4.0 * q->n * K);
     EX_CALL(ccn_frnn_knn(q->pos.f, q->batch, q->n, g->sorted, g->cell_off, g->cells, src->sptr_dev, radius, K, idx, nullptr, cnt,
                          (ccn_stream_t)ex.stream));
-    if (self && !want_cnt) src->knn.push_back(KnnMemo{K, radius, idx});
+    if (self && !want_cnt) src->knn.push_back(KnnMemo{K, radius, idx, nullptr});
     return CCN_OK;
 }
 
@@ -608,6 +639,64 @@ int presample_ahead(Exec& ex, int si, Level* lv) {
     return rc;
 }
 
+// Step `si` has created level `ch` from `lv` (sampled indices `idx`): queue, on the geometry stream, (1) the interpolation
+// table of the fp / fp-geo step that will pop this down step and (2) the kNN tables of the sgcnn steps that run on `ch` before
+// the next level change.  The main stream joins through events at first use.
+int geometry_ahead(Exec& ex, int si, Level* lv, Level* ch, const int64_t* idx) {
+    if (!ex.use_side || ex.prof || !ex.geo || ex.oom || ch->n == 0) return CCN_OK;
+    cudaEvent_t start = ex.geo_event();
+    EX_CUDA(cudaEventRecord(start, ex.stream));            // the level's positions / batch are queued on the main (or sampling) stream
+    EX_CUDA(cudaStreamWaitEvent(ex.geo, start, 0));
+    cudaStream_t saved = ex.stream;
+    ex.stream = ex.geo;
+    int rc = CCN_OK;
+    bool any = false;
+    const int j = ex.fp_partner[si];
+    if (j >= 0 && ch->has_sptr) {
+        const Step& fp = ex.steps[j];
+        const int knn = (int)fp.iv[0];
+        int32_t* nbr = ex.alloc_n<int32_t>(lv->n * knn);
+        float* wgt = ex.alloc_n<float>(lv->n * knn);
+        if (!ex.oom) {
+            if (fp.kind == ST_FP)
+                rc = ccn_knn_exact(lv->pos.f, lv->batch, lv->n, ch->pos.f, ch->sptr_dev, knn, 1, nbr, wgt, nullptr, (ccn_stream_t)ex.geo);
+            else if (lv->has_topo && idx)
+                rc = ccn_knn_1d_superset(lv->pos.f, lv->curve_ord, lv->n, idx, ch->n, knn, nbr, wgt, (ccn_stream_t)ex.geo);
+            else
+                nbr = nullptr;
+            if (rc == CCN_OK && nbr) {
+                Exec::UpMemo& u = ex.up[j];
+                u.valid = true; u.nbr = nbr; u.wgt = wgt; u.ready = ex.geo_event();
+                if (cudaEventRecord(u.ready, ex.geo) != cudaSuccess) rc = CCN_EINVAL;
+                any = true;
+            }
+        }
+    }
+    for (size_t k = (size_t)si + 1; k < ex.steps.size() && rc == CCN_OK && !ex.oom; ++k) {
+        const int kind = ex.steps[k].kind;
+        if (kind == ST_SA || kind == ST_SA_GEO || kind == ST_FP || kind == ST_FP_GEO) break;
+        if (kind != ST_SGCNN || !ch->has_sptr) continue;
+        const int K = (int)ex.steps[k].iv[1];
+        const float radius = (float)ex.steps[k].fv[0];
+        bool have = false;
+        for (const KnnMemo& m : ch->knn) have = have || (m.K == K && m.radius == radius);
+        if (have) continue;
+        int32_t* nbr = nullptr;
+        rc = frnn(ex, ch, ch, K, radius, false, &nbr, nullptr);
+        if (rc == CCN_OK && !ex.oom) {
+            cudaEvent_t e = ex.geo_event();
+            if (cudaEventRecord(e, ex.geo) != cudaSuccess) { rc = CCN_EINVAL; break; }
+            ch->knn.back().ready = e;
+            for (Grid& g : ch->grids)
+                if (g.radius == radius && !g.ready) g.ready = e;      // built just now on the geometry stream
+            any = true;
+        }
+    }
+    (void)any;
+    ex.stream = saved;
+    return rc;
+}
+
 }  // namespace
 
 struct ccn_exec {
@@ -666,6 +755,16 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
             if (k == ST_SA || k == ST_SA_GEO || k == ST_FP || k == ST_FP_GEO) break;      // another level change first
         }
     }
+    ex.fp_partner.assign(ex.steps.size(), -1);
+    ex.up.resize(ex.steps.size());
+    {
+        std::vector<int> stack;
+        for (size_t i = 0; i < ex.steps.size(); ++i) {
+            const int k = ex.steps[i].kind;
+            if (k == ST_SA || k == ST_SA_GEO) stack.push_back((int)i);
+            if ((k == ST_FP || k == ST_FP_GEO) && !stack.empty()) { ex.fp_partner[stack.back()] = (int)i; stack.pop_back(); }
+        }
+    }
     const int n_om = (int)I();
     for (int i = 0; i < n_om; ++i) ex.out_mlp.push_back((int)I());
     if (ci != n_i || cf != n_f) { delete h; return CCN_EINVAL; }
@@ -679,6 +778,7 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
         cudaEventCreateWithFlags(&ex.lvl_ready, cudaEventDisableTiming) != cudaSuccess) {
         ex.side = nullptr;                       // no side stream: everything stays on the caller's stream
     }
+    if (cudaStreamCreateWithFlags(&ex.geo, cudaStreamNonBlocking) != cudaSuccess) ex.geo = nullptr;
     *out = h;
     return CCN_OK;
 }
@@ -689,6 +789,8 @@ extern "C" void ccn_exec_destroy(ccn_exec_t* h) {
     if (h->ex.h2d_ring) cudaFreeHost(h->ex.h2d_ring);
     if (h->ex.pinned_side) cudaFreeHost(h->ex.pinned_side);
     if (h->ex.side) cudaStreamDestroy(h->ex.side);
+    if (h->ex.geo) cudaStreamDestroy(h->ex.geo);
+    for (cudaEvent_t e : h->ex.geo_events) if (e) cudaEventDestroy(e);
     if (h->ex.lvl_ready) cudaEventDestroy(h->ex.lvl_ready);
     for (Exec::Pre& pr : h->ex.pre) if (pr.ready) cudaEventDestroy(pr.ready);
     for (cudaEvent_t e : h->ex.prof_pool) cudaEventDestroy(e);
@@ -729,6 +831,8 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
     ex.prof_recs.clear();
     ex.prof_used = 0;
     for (Exec::Pre& pr : ex.pre) { pr.done = false; pr.ch = nullptr; pr.idx = nullptr; }
+    for (Exec::UpMemo& u : ex.up) u.valid = false;
+    ex.geo_used = 0;
     ccn_stream_t st = (ccn_stream_t)ex.stream;
 
     ex.levels.emplace_back();
@@ -993,6 +1097,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     e = Edges{buf, erow, col, E, nq, max_deg};
                     if (!presampled) EX_CALL(subset_level(ex, lv, idx, ch));
                     EX_CALL(presample_ahead(ex, (int)si, ch));
+                    EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx));
                     pc_iv = iv + 2;
                     if (cur.x) xparts[nxp++] = cur.x;
                     if (iv[0] || !cur.x) xparts[nxp++] = &lv->pos;
@@ -1000,6 +1105,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     const int K = (int)iv[1];
                     if (!presampled || ex.pre[si].voxel) EX_CALL(subset_level(ex, lv, idx, ch));
                     EX_CALL(presample_ahead(ex, (int)si, ch));
+                    EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx));
                     int32_t *nbr = nullptr, *cnt = nullptr;
                     EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));
                     EX_CALL(dense_to_csr(ex, nbr, cnt, ch->n, K, &e));
@@ -1023,9 +1129,12 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 Level* fine = sk.lv;
                 Feat* x_skip = sk.x ? sk.x : &fine->pos;
                 const int knn = (int)iv[0], with_xyz = (int)iv[1], nl = (int)iv[2];
-                int32_t* nbr = ex.alloc_n<int32_t>(fine->n * knn);
-                float* wgt = ex.alloc_n<float>(fine->n * knn);
-                if (s.kind == ST_FP) {
+                const bool ahead = ex.up[si].valid;
+                int32_t* nbr = ahead ? ex.up[si].nbr : ex.alloc_n<int32_t>(fine->n * knn);
+                float* wgt = ahead ? ex.up[si].wgt : ex.alloc_n<float>(fine->n * knn);
+                if (ahead) {
+                    EX_CUDA(cudaStreamWaitEvent(ex.stream, ex.up[si].ready, 0));     // computed on the geometry stream at level creation
+                } else if (s.kind == ST_FP) {
                     EX_CALL(level_sptr(ex, cur.lv));
                     ProfScope ps(ex, FAM_SEARCH, 0, 12.0 * fine->n + 12.0 * cur.lv->n + 8.0 * fine->n * knn);
                     if (!ex.oom)
