@@ -407,6 +407,58 @@ def run_train(args):
         dist.destroy_process_group()
 
 
+def train_variant(dist, rank, world, precision, batch=16, steps=4, warmup=2):
+    """Informational line inside the default (inference) bench at EVERY N: the ShapeNet-seg training step (BASELINE.json
+    configs[1], fwd + NLL + bwd + fused Adam, B = 16 x 2048 points per GPU) through sharding.GradReducer - the ONE collective
+    of the design (bucketed NCCL gradient all-reduce overlapped with backward), so that the driver's scaling run sees it.
+    Runs on every rank; -> dict on rank 0 (device-event time, max over ranks; points of all ranks)."""
+    from curvecloudnet_b200 import autograd as A
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.sharding import GradReducer
+    from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
+    model = build_model(ModelBase, "shapenet-seg", precision=precision)
+    randomize_model_(model, 1234)
+    model = model.cuda().train()
+    reducer = GradReducer(model.parameters(), dist)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+    data = object_scan_batch([10000 * rank + b for b in range(batch)]).to("cuda")
+    tgt = torch.randint(0, 50, (data.pos.shape[0],), generator=torch.Generator().manual_seed(rank)).to("cuda")
+    ev = []
+    for i in range(warmup + steps):
+        if i == warmup:
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+            torch.cuda.synchronize()
+        torch.manual_seed(i)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        reducer.prepare()
+        loss = A.nll_loss(model(data), tgt)
+        loss.backward()
+        reducer.finish()
+        opt.step()
+        b.record()
+        if i >= warmup:
+            ev.append((a, b))
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    pts = torch.tensor([float(data.pos.shape[0] * steps)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(pts, op=dist.ReduceOp.SUM)
+    grad_bytes = int(reducer.flat.numel() * 4)
+    reducer.remove()
+    return {"workload": TRAIN_WORKLOAD % batch, "value": float(pts.item()) / (float(t.item()) * 1e-3), "unit": "points/s",
+            "ms_per_step": float(t.item()) / steps, "steps": steps, "warmup": warmup, "n_gpus": world, "scaling": "weak",
+            "collective": "bucketed NCCL all-reduce of %d gradient bytes per step, overlapped with backward (sharding.GradReducer)"
+                          % grad_bytes if world > 1 else "none (one GPU)", "dtype": precision}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -421,6 +473,7 @@ def main():
     ap.add_argument("--mode", default="infer", choices=["infer", "train"],
                     help="infer: nuScenes-shape forward (the headline metric); train: ShapeNet-seg fwd+bwd step (configs[1])")
     ap.add_argument("--no-batched-variant", action="store_true", help="skip the informational B=6 line (batched_variant)")
+    ap.add_argument("--no-train-variant", action="store_true", help="skip the informational training-step line (train_variant)")
     ap.add_argument("--train-batch", type=int, default=16, help="scans per training step per GPU (--mode train)")
     args = ap.parse_args()
     if args.mode == "train":
@@ -447,7 +500,8 @@ def main():
     native.load()
     W, K = max(args.warmup, 3), max(args.steps, 1)
 
-    model = build_model(ModelBase, "nuscenes", precision=args.precision)
+    # BENCH_PYTHON_EXECUTOR=1 (dev A/B): the python step executor of model.py instead of ccn_forward_run
+    model = build_model(ModelBase, "nuscenes", precision=args.precision, native_executor=not os.environ.get("BENCH_PYTHON_EXECUTOR"))
     randomize_model_(model, 1234)
     model = model.cuda().eval()
     lin_name = "ccn_linear_f32" if args.precision == "fp32" else "ccn_linear_planes"
@@ -523,6 +577,12 @@ def main():
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     ms_max, ms_e2e_max = [float(v) for v in t.tolist()]
     tot_pts, tot_pts_e2e = [float(v) for v in tot.tolist()]
+    tv = None
+    if not args.no_train_variant and args.batch == 1:
+        try:
+            tv = train_variant(dist, rank, world, args.precision)
+        except Exception as e:                      # informational: never take the headline line down
+            tv = {"error": "%s: %s" % (type(e).__name__, e)}
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -609,6 +669,8 @@ def main():
                 tot_p += bpts[i % 2]
         line["batched_variant"] = {"scans_per_step": B6, "value": tot_p / (tot_ms * 1e-3), "unit": "points/s",
                                    "ms_per_scan": tot_ms / (8 * B6), "steps": 8, "warmup": 3}
+    if tv is not None:
+        line["train_variant"] = tv
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         # bounded sample of the SAME workload: the full seed-0 scan (the first scan of the timed cycle), 1 warm-up + 3 timed

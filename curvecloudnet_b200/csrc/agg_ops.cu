@@ -118,6 +118,13 @@ __global__ void seg_aggregate_kernel(const float* __restrict__ msg, int64_t ldm,
                 const float a = att[(int64_t)j * lda + k];
                 r += msg[(int64_t)j * ldm + k] * (1.f / (1.f + expf(-a)));
             }
+        } else if (mode == CCN_AGG_WSUM_NORM) {
+            // dense SGCNN 'weighted-sum' (dgcnn.py:190-197): w = sigmoid(att) / clamp(sum w, 1e-3)
+            float tot = 0.f;
+            for (int j = b; j < e; ++j) tot += 1.f / (1.f + expf(-att[(int64_t)j * lda + k]));
+            const float den = fmaxf(tot, 1e-3f);
+            for (int j = b; j < e; ++j)
+                r += msg[(int64_t)j * ldm + k] * ((1.f / (1.f + expf(-att[(int64_t)j * lda + k]))) / den);
         } else {
             float m = -INFINITY;
             for (int j = b; j < e; ++j) m = fmaxf(m, att[(int64_t)j * lda + k]);
@@ -267,6 +274,19 @@ __global__ void seg_aggregate_v4_kernel(const float* __restrict__ msg, int64_t l
                 const float av[4] = {a.x, a.y, a.z, a.w}, mv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                 for (int l = 0; l < 4; ++l) r[l] += mv[l] * (1.f / (1.f + expf(-av[l])));
+            }
+        } else if (mode == CCN_AGG_WSUM_NORM) {
+            float tot[4] = {0.f, 0.f, 0.f, 0.f};
+            for (int j = b; j < e; ++j) {
+                const float4 a = ld4(a0 + (int64_t)j * lda);
+                tot[0] += 1.f / (1.f + expf(-a.x)); tot[1] += 1.f / (1.f + expf(-a.y));
+                tot[2] += 1.f / (1.f + expf(-a.z)); tot[3] += 1.f / (1.f + expf(-a.w));
+            }
+            for (int j = b; j < e; ++j) {
+                const float4 a = ld4(a0 + (int64_t)j * lda), v = ld4(m0 + (int64_t)j * ldm);
+                const float av[4] = {a.x, a.y, a.z, a.w}, mv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int l = 0; l < 4; ++l) r[l] += mv[l] * ((1.f / (1.f + expf(-av[l]))) / fmaxf(tot[l], 1e-3f));
             }
         } else {
             float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, sum[4] = {0.f, 0.f, 0.f, 0.f};
@@ -627,8 +647,8 @@ extern "C" int ccn_edge_pair_layer1(const float* PQ, int64_t ldpq, const int32_t
 
 extern "C" int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
                                  int64_t nq, int32_t c, int32_t mode, float* out, int64_t ldo, ccn_stream_t stream) {
-    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 4);
-    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || att);
+    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 5);
+    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND && mode != CCN_AGG_WSUM_NORM) || att);
     if (nq == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) && ccn_al16(out) &&
         (!att || ((lda & 3) == 0 && ccn_al16(att)))) {
@@ -694,8 +714,8 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
 extern "C" int ccn_seg_aggregate_both(const float* msg, int64_t ldm, const float* att, int64_t lda, const int32_t* row_ptr,
                                       int64_t nq, int32_t c, int32_t mode, float* out, int64_t ldo, void* planes,
                                       int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
-    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 4);
-    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || att);
+    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && out && mode >= 0 && mode <= 5);
+    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND && mode != CCN_AGG_WSUM_NORM) || att);
     CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) &&
                 ccn_al16(out) && (!att || ((lda & 3) == 0 && ccn_al16(att))));
     if (nq == 0) return CCN_OK;

@@ -17,6 +17,7 @@
 // through a callback in the reference's call order, so seeding torch identically reproduces the python path.
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <deque>
@@ -144,6 +145,23 @@ struct Exec {
     ccn_draw_fn draw = nullptr;
     void* draw_user = nullptr;
     int topo_flags = 0;
+    // host-side accounting of the last forward: wall time of ccn_forward_run, time blocked in stream / event synchronisation
+    double host_total_ms = 0, host_blocked_ms = 0;
+    int host_syncs = 0;
+    int sync_stream(cudaStream_t s) {
+        const auto t0 = std::chrono::steady_clock::now();
+        const cudaError_t e = cudaStreamSynchronize(s);
+        host_blocked_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        ++host_syncs;
+        return e == cudaSuccess ? CCN_OK : (int)e;
+    }
+    int sync_event(cudaEvent_t ev) {
+        const auto t0 = std::chrono::steady_clock::now();
+        const cudaError_t e = cudaEventSynchronize(ev);
+        host_blocked_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        ++host_syncs;
+        return e == cudaSuccess ? CCN_OK : (int)e;
+    }
     // optional per-family device timing (bench.py's roofline leg): CUDA events around every launch of a family, a short spin
     // queued before each so that the pair brackets the kernel and not the host's launch gap
     bool prof = false;
@@ -194,8 +212,7 @@ struct Exec {
     int readback(const void* dev, int n_ints) {      // blocking read of n_ints int32 into `pinned`
         if (oom) return CCN_ENOMEM;
         EX_CUDA(cudaMemcpyAsync(pinned, dev, 4 * (size_t)n_ints, cudaMemcpyDeviceToHost, stream));
-        EX_CUDA(cudaStreamSynchronize(stream));
-        return CCN_OK;
+        return sync_stream(stream);
     }
 };
 
@@ -800,6 +817,13 @@ extern "C" void ccn_exec_destroy(ccn_exec_t* h) {
 
 extern "C" int32_t ccn_exec_topology_flags(const ccn_exec_t* h) { return h ? h->ex.topo_flags : 0; }
 
+// out[3] = {wall ms of the last ccn_forward_run, ms of it blocked in stream / event synchronisation, number of those waits}
+extern "C" int ccn_exec_host_stats(const ccn_exec_t* h, double* out) {
+    CCN_REQUIRE(h && out);
+    out[0] = h->ex.host_total_ms; out[1] = h->ex.host_blocked_ms; out[2] = h->ex.host_syncs;
+    return CCN_OK;
+}
+
 extern "C" int ccn_exec_profile(ccn_exec_t* h, int32_t enable, int32_t spin_cycles) {
     CCN_REQUIRE(h);
     h->ex.prof = enable != 0;
@@ -1035,7 +1059,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 const int down = s.kind == ST_SA ? (int)iv[0] : DOWN_FPS;
                 if (presampled && ex.pre[si].voxel) {
                     // the voxel sampler ran ahead on the side stream: wait for its read-back, size the level
-                    EX_CUDA(cudaEventSynchronize(ex.pre[si].ready));
+                    EX_CALL(ex.sync_event(ex.pre[si].ready));
                     EX_CALL(voxel_collect(ex.pinned_side, ex.pre[si].job, ch));
                     idx = ex.pre[si].job.idx;
                 } else if (presampled) {
@@ -1059,7 +1083,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     Exec::VoxelJob job;
                     EX_CALL(voxel_launch(ex, lv, (float)fv[0], ex.pinned, &job));
                     if (ex.oom) return CCN_ENOMEM;
-                    EX_CUDA(cudaStreamSynchronize(ex.stream));
+                    EX_CALL(ex.sync_stream(ex.stream));
                     EX_CALL(voxel_collect(ex.pinned, job, ch));
                     idx = job.idx;
                 } else {
@@ -1214,7 +1238,10 @@ extern "C" int ccn_forward_run(ccn_exec_t* h, const float* x, int64_t ldx, const
     Exec& ex = h->ex;
     ex.arena = (char*)arena; ex.cap = (size_t)arena_bytes; ex.off = 0; ex.oom = false;
     ex.stream = (cudaStream_t)stream; ex.draw = draw; ex.draw_user = draw_user;
+    ex.host_blocked_ms = 0; ex.host_syncs = 0;
+    const auto t0 = std::chrono::steady_clock::now();
     const int rc = run_forward(ex, x, ldx, pos, batch, curve_idxs, n, logits, ld_logits);
+    ex.host_total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (arena_needed) *arena_needed = (int64_t)ex.off;
     if (ex.oom) return CCN_ENOMEM;
     return rc;

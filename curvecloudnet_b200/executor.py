@@ -254,6 +254,13 @@ class NativeExecutor:
         return {f: {"ms": buf[4 * i], "calls": buf[4 * i + 1], "flops": buf[4 * i + 2], "bytes": buf[4 * i + 3]}
                 for i, f in enumerate(self.FAMILIES)}
 
+    def host_stats(self):
+        """{"total_ms", "blocked_ms", "syncs"} of the last forward: wall time inside ccn_forward_run, the part of it spent waiting
+        for the device at the data-dependent sizes, the number of those waits."""
+        buf = (ctypes.c_double * 3)()
+        self.lib.ccn_exec_host_stats(self.handle, ctypes.cast(buf, ctypes.c_void_p))
+        return {"total_ms": buf[0], "blocked_ms": buf[1], "syncs": int(buf[2])}
+
     def _draw_fn(self, draws, errors):
         def cb(user, kind, n, out):
             try:

@@ -133,17 +133,20 @@ def tta_forward(model, data, flips=TTA_FLIPS, scales=TTA_SCALES, group: int = 1)
     factors = [(fx * sc, fy * sc) for fx, fy in flips for sc in scales]
     acc, first = None, True
     if group <= 1:
-        for sx, sy in factors:
-            pos = torch.empty_like(pos0)
-            call("ccn_scale_xy", pos0, n, float(sx), float(sy), pos)
-            data.pos = pos
-            out = model(data, labels=getattr(data, "y", None))
-            out, ld = ops._rows(out)
-            if acc is None:
-                acc = torch.empty((n, out.shape[1]), dtype=torch.float32, device=out.device)
-            call("ccn_accumulate", out, ld, n, out.shape[1], acc, acc.shape[1], int(first))
-            first = False
-        data.pos = pos0
+        orig = data.pos
+        try:
+            for sx, sy in factors:
+                pos = torch.empty_like(pos0)
+                call("ccn_scale_xy", pos0, n, float(sx), float(sy), pos)
+                data.pos = pos
+                out = model(data, labels=getattr(data, "y", None))
+                out, ld = ops._rows(out)
+                if acc is None:
+                    acc = torch.empty((n, out.shape[1]), dtype=torch.float32, device=out.device)
+                call("ccn_accumulate", out, ld, n, out.shape[1], acc, acc.shape[1], int(first))
+                first = False
+        finally:
+            data.pos = orig               # the caller's batch gets its positions back even if a forward raises
     else:
         for g0 in range(0, len(factors), group):
             stacked = tta_stack(data, factors[g0:g0 + group])

@@ -471,9 +471,28 @@ class SGCNNLayer(nn.Module):
         x = _cat_xyz(x, pos, self.with_xyz, cache)
         lin_pq, act0, slope0 = self._decomposed()
         PQ = lin_pq(x)
+        if not self.use_sparse_feat_agg and self.aggr_type in ("mean", "attend", "weighted-sum"):
+            # dgcnn.py:182-203: mean / sigmoid-weighted (renormalised by clamp(sum w, 1e-3)) / softmax over the VALID rows of the
+            # K+1 table (invalid rows are zeroed / weight 0 / pushed to -5e2, i.e. weight exp(-500 - max) = 0): the same
+            # reductions over the edge list [self loop, found neighbours]
+            nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, want_cnt=True, cache=cache)
+            n = pos.shape[0]
+            ext = torch.cat([torch.arange(n, dtype=torch.int32, device=pos.device).view(n, 1), nbr], dim=1).contiguous()
+            cnt = cnt.clone()
+            cnt[:n] += 1
+            edges = ops.dense_to_csr(ext, cnt)
+            npl = n_planes() if self.nn.num_layers > 1 else 0
+            msg = ops.edge_pair_layer1(PQ, edges, act0, slope0, npl)
+            if self.aggr_type == "mean":
+                msg = self.nn.forward_from(msg, 1)
+                return ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "mean", n_planes(), cache), pos, batch, point2curveidx
+            both = npl > 0
+            msg = self.nn.forward_from(msg, 1, "both" if both else "f32")
+            msg, msg_in = msg if both else (msg, msg)
+            mode = "attend" if self.aggr_type == "attend" else "weighted-sum-norm"
+            out = ops.seg_aggregate(msg, self.attend_nn(msg_in), edges.row_ptr, edges.nq, mode, n_planes(), cache)
+            return out, pos, batch, point2curveidx
         if not self.use_sparse_feat_agg:
-            if self.aggr_type != "max":
-                raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
             nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, cache=cache)
             chain = self._fused.get(self.nn.layers()) if self.k + 1 <= 128 else None
             if chain is not None:
@@ -488,25 +507,26 @@ class SGCNNLayer(nn.Module):
             nbr, _, cnt = ops.knn_exact(pos, batch, pos, sptr, self.k, zero_fill=True, want_d2=False, want_cnt=True)
         edges = ops.dense_to_csr(nbr, cnt)
         npl = n_planes() if self.nn.num_layers > 1 else 0
-        if self.aggr_type in ("max", "attend") and edges.max_degree <= ops.FUSED_MAX_DEGREE:
+        sparse_mode = "max" if self.aggr_type == "max" else "attend"     # dgcnn.py:240-244: every other aggr_type takes the softmax branch
+        if edges.max_degree <= ops.FUSED_MAX_DEGREE and (sparse_mode == "max" or self.attend_nn is not None):
             layers = self.nn.layers()
-            extra = self.attend_nn.layers() if self.aggr_type == "attend" else ()
+            extra = self.attend_nn.layers() if sparse_mode == "attend" else ()
             chain = self._fused.get(layers, extra) if len(layers) >= 2 else None
             if chain is not None:
-                out = ops.pointconv_fused(edges, chain, self.aggr_type, len(layers) - 2 if extra else -1, act0, slope0,
+                out = ops.pointconv_fused(edges, chain, sparse_mode, len(layers) - 2 if extra else -1, act0, slope0,
                                           layers[0].out_features, PQ=PQ, npl=n_planes(), cache=cache)
                 return out, pos, batch, point2curveidx
         msg = ops.edge_pair_layer1(PQ, edges, act0, slope0, npl)
         if self.aggr_type == "max":
             msg = self.nn.forward_from(msg, 1)
             out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "max", n_planes(), cache)
-        elif self.aggr_type == "attend":
+        else:
+            if self.attend_nn is None:
+                raise UnboundLocalError("attend_nn")                  # the reference dereferences self.attend_nn (dgcnn.py:242)
             both = npl > 0
             msg = self.nn.forward_from(msg, 1, "both" if both else "f32")
             msg, msg_in = msg if both else (msg, msg)
             out = ops.seg_aggregate(msg, self.attend_nn(msg_in), edges.row_ptr, edges.nq, "attend", n_planes(), cache)
-        else:
-            raise NotImplementedError("sparse SGCNN path: aggregation %r" % self.aggr_type)
         return out, pos, batch, point2curveidx
 
 

@@ -16,7 +16,7 @@ from . import native
 from .native import call
 
 ACT_NONE, ACT_RELU, ACT_LEAKY = 0, 1, 2
-AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3, "sum": 4}
+AGG = {"max": 0, "mean": 1, "weighted-sum": 2, "attend": 3, "sum": 4, "weighted-sum-norm": 5}
 MAX_SAMPLES = 4096
 # Fused edge-step kernels (csrc/edge_fused.cu): "auto" = where they are the faster path today (fused_profitable), True = wherever
 # the kernel covers the shapes, False = never (the unfused chain of launches).  All three give bit-identical results.

@@ -81,36 +81,46 @@ class GradReducer:
             self.buckets.append((b_start, off, b_count))
         self._pending = [0] * len(self.buckets)
         self._work = []
+        self._next = 0
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
 
     def prepare(self):
         """Call before every backward: zero the flat gradient, re-arm the buckets."""
         self.flat.zero_()
+        lo, hi = self.flat.data_ptr(), self.flat.data_ptr() + self.flat.numel() * 4
         for p in self.params:             # an optimizer's zero_grad(set_to_none=True) would detach the views
-            if p.grad is None or p.grad.data_ptr() < self.flat.data_ptr():
+            if p.grad is None or not (lo <= p.grad.data_ptr() < hi):
                 raise RuntimeError("GradReducer: .grad was replaced; use optimizer.zero_grad(set_to_none=False) "
                                    "or just GradReducer.prepare()")
         self._pending = [b[2] for b in self.buckets]
         self._work = []
+        self._next = 0                    # buckets are launched strictly in index order on every rank
 
     def _on_grad(self, p):
         b = self._bucket_of[id(p)]
         self._pending[b] -= 1
-        if self._pending[b] == 0:
-            self._launch(b)
+        self._launch_ready()
+
+    def _launch_ready(self):
+        """Issue the all-reduce of every complete bucket at the head of the queue.  A bucket only starts after all buckets
+        before it have started, so that every rank issues the same collectives in the same ORDER even if a data-dependent
+        branch makes the ranks finish their buckets in different orders (NCCL pairs collectives by issue order)."""
+        while self._next < len(self.buckets) and self._pending[self._next] == 0:
+            self._launch(self._next)
+            self._next += 1
 
     def _launch(self, b):
         if self.dist is None:
             return
         s, e, _ = self.buckets[b]
         self._work.append(self.dist.all_reduce(self.flat[s:e], op=self.dist.ReduceOp.SUM, async_op=True))
-        self._pending[b] = -1
 
     def finish(self):
-        """Call after backward: flush buckets whose parameters got no gradient, wait, average."""
-        for b, left in enumerate(self._pending):
-            if left >= 0 and self.dist is not None and left != -1:
-                self._launch(b)
+        """Call after backward: flush, in order, the buckets that did not complete (parameters without a gradient this
+        step hold zeros), wait, average."""
+        while self._next < len(self.buckets):
+            self._launch(self._next)
+            self._next += 1
         for w in self._work:
             w.wait()
         if self.world > 1:

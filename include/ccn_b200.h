@@ -48,6 +48,7 @@ typedef struct CUstream_st* ccn_stream_t;
 #define CCN_AGG_WSUM 2   /* sum sigmoid(att) * msg */
 #define CCN_AGG_ATTEND 3 /* sum softmax_target(att) * msg */
 #define CCN_AGG_SUM 4
+#define CCN_AGG_WSUM_NORM 5 /* sum msg * sigmoid(att) / clamp(sum sigmoid(att), 1e-3): dense SGCNN 'weighted-sum' (dgcnn.py:190-197) */
 
 #define CCN_TOPO_ERR_BATCH_UNSORTED 1
 #define CCN_TOPO_ERR_CURVE_UNSORTED 2
@@ -466,6 +467,9 @@ int32_t ccn_exec_topology_flags(const ccn_exec_t* exec);
  * {ms, launches, algorithmic FLOPs, algorithmic bytes} of the last forward; families: 0 Linear, 1 fused edge
  * steps, 2 curve-conv GEMMs, 3 neighbour search, 4 samplers.  n_families >= 5. */
 int ccn_exec_profile(ccn_exec_t* exec, int32_t enable, int32_t spin_cycles);
+/* host-side accounting of the last ccn_forward_run: out[3] = {wall ms of the call, ms of it blocked waiting for the device
+ * (data-dependent sizes), number of those waits}; wall - blocked = the host's own work (launches, planning). */
+int ccn_exec_host_stats(const ccn_exec_t* exec, double* out_host);
 int ccn_exec_profile_read(ccn_exec_t* exec, double* out_host, int32_t n_families);
 int ccn_forward_run(ccn_exec_t* exec, const float* x, int64_t ldx, const float* pos, const int64_t* batch,
                     const int64_t* curve_idxs, int64_t n, void* arena, int64_t arena_bytes, ccn_draw_fn draw,

@@ -285,3 +285,38 @@ def test_get_curves_edge_cases():
         assert counts.tolist()[1] == 0
     bad = ops.get_curves(torch.rand(10, 3).cuda(), torch.full((10,), 9).cuda(), 0.08, 4)[4]
     assert bad.tolist()[1] == 1
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16x3"])
+@pytest.mark.parametrize("aggr", ["max", "mean", "attend", "weighted-sum"])
+def test_dense_sgcnn_aggregations_match_oracle(aggr, precision):
+    """StaticEdgeConv.forward_fast with every aggregation of dgcnn.py:180-203 (the shipped configs use 'max' only): our
+    SGCNNLayer against the oracle's restatement, same weights, B = 2 so that padded rows and a sample boundary occur."""
+    from curvecloudnet_b200 import modules as M
+    from curvecloudnet_b200 import nn as N
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle import ccn_modules as OM
+    from oracle.tp_nn import MLP as OMLP
+    data = driving_scan_batch([1, 2], subsample=900)
+    gen = torch.Generator().manual_seed(4)
+    x = torch.randn(data.pos.shape[0], 13, generator=gen)
+    dims = [2 * (13 + 3), 64, 64]
+    att = aggr in ("attend", "weighted-sum")
+    want_mod = OM.SGCNNLayer(OMLP(dims), 9, r=0.12, with_xyz=True, aggr_type=aggr,
+                             attend_nn=OMLP([64, 64, 64], act="leaky_relu") if att else None)
+    randomize_model_(want_mod, 77)
+    want_mod.eval()
+    with torch.no_grad():
+        want = want_mod(x, data.pos, data.batch)[0]
+    mod = M.SGCNNLayer(N.MLP(dims), 9, r=0.12, with_xyz=True, aggr_type=aggr,
+                       attend_nn=N.MLP([64, 64, 64], act="leaky_relu") if att else None)
+    mod.load_state_dict(want_mod.state_dict(), strict=True)
+    mod = mod.cuda().eval()
+    N.set_precision(precision)
+    try:
+        with torch.no_grad():
+            got = mod(x.cuda(), data.pos.cuda(), data.batch.cuda(), cache=N.ForwardCache())[0]
+    finally:
+        N.set_precision("fp32")
+    assert got.shape == want.shape
+    assert rel_err(got.cpu(), want) <= (1e-4 if precision == "fp32" else 3e-4), aggr

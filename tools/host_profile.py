@@ -13,7 +13,26 @@ from curvecloudnet_b200.model import ModelBase
 from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
 
 prec = sys.argv[1] if len(sys.argv) > 1 else "bf16x3"
-model = build_model(ModelBase, "nuscenes", precision=prec)
+# the native step executor (csrc/executor.cu): host wall time of ccn_forward_run, split into waiting and working
+nmodel = randomize_model_(build_model(ModelBase, "nuscenes", precision=prec), 1234).cuda().eval()
+ndata = driving_scan_batch([0]).to("cuda")
+with torch.no_grad():
+    for i in range(6):
+        torch.manual_seed(0)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        nmodel(ndata)
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        st = nmodel.__dict__["_native"][1].host_stats()
+        if i >= 3:
+            print("native executor: forward call %.2f ms (device done %.2f ms); inside ccn_forward_run %.2f ms = %.2f ms host work + "
+                  "%.2f ms blocked in %d waits for data-dependent sizes" % ((t1 - t0) * 1e3, (t2 - t0) * 1e3, st["total_ms"],
+                                                                          st["total_ms"] - st["blocked_ms"], st["blocked_ms"], st["syncs"]))
+del nmodel
+print("python executor (native_executor=False):")
+model = build_model(ModelBase, "nuscenes", precision=prec, native_executor=False)
 randomize_model_(model, 1234)
 model = model.cuda().eval()
 data = driving_scan_batch([0]).to("cuda")
