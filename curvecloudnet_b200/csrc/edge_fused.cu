@@ -115,6 +115,20 @@ __device__ __forceinline__ void store_piece(uint32_t addr_hi, const float (&y)[8
     if (P == 2) st_shared_v4(addr_hi + kChunkBytes, l[0], l[1], l[2], l[3]);
 }
 
+// 1-D bulk async copy global -> shared (TMA engine), completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
 __device__ __forceinline__ void workers_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 template <int P, int FORM>
@@ -484,6 +498,280 @@ __global__ void csr_tiles_kernel(const int32_t* __restrict__ row_ptr, int nq, in
     tiles[t] = make_int4(qa, qb - qa, e0, __ldg(row_ptr + qb) - e0);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Dense SGCNN step whose `nn` has ONE layer after the decomposed first (levels 2..5 of the driving configs: 128 -> 128 ...
+// 1024 -> 1024): a pipelined GEMM whose A operand is FORMED on the fly and whose epilogue is the masked group max.
+//   warps 2-5   form act0(P[j] + Q[i]) for one 64-channel chunk of the tile's 128 rows straight into the ring stage
+//               (SWIZZLE_128B bf16 hi/lo planes), running ahead of the MMAs by the depth of the ring;
+//   warp 0      TMA: the matching W chunk (BN output rows x 64 k) into the same stage;
+//   warp 1      tcgen05.mma into one of TWO TMEM accumulators, so that
+//   warps 6-9   the epilogue of tile t (bias, -100 on missing neighbours, max over every group of K+1 rows through a
+//               128 x 32 transposition table) overlaps the formation and MMAs of tile t+1.
+// A CTA owns one (row tile, BN-column slice) at a time (persistent over the tile list), so wide layers spread over many CTAs.
+// Same arithmetic and order as the unfused chain (ccn_sgcnn_layer1_planes -> ccn_linear_planes -> ccn_group_max_dense).
+constexpr int kStreamThreads = 320;
+constexpr int kMaskSlots = 16;               // tiles a former may run ahead of the epilogue (ring depth / chunks per tile + 2 accumulators)
+
+struct StreamParams {
+    const float* PQ;
+    int64_t ldpq;
+    const int32_t* idx;
+    int n, Knb, G, gpt;
+    int c1, act0;
+    float slope0;
+    int N, act;                    // the layer: c1 -> N
+    float slope;
+    const float* bias;
+    int BN, n_slices, tiles_m, stages;
+    int w_plane_bytes;             // BN * 128
+    float* out;
+    int64_t ldo;
+    __nv_bfloat16* planes;
+    int64_t kpad, pstride;
+    int npl;
+};
+
+template <int P>
+__global__ void __launch_bounds__(kStreamThreads, 1) sgcnn_stream_kernel(const __grid_constant__ CUtensorMap w_hi,
+                                                                         const __grid_constant__ CUtensorMap w_lo,
+                                                                         const __grid_constant__ StreamParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];     // full[S], empty[S], tfull[2], tempty[2]
+    __shared__ uint32_t tmem_base_slot;
+    __shared__ float bias_s[256];
+    __shared__ int32_t row_i[2][kRows], row_j[2][kRows];           // per-tile row metadata of the formers (double buffered)
+    __shared__ uint8_t row_mask[kMaskSlots][kRows];                 // 1: missing neighbour (-100 in the max), per tile in flight
+    __shared__ __align__(8) uint64_t gbars[2];                      // row gathers of the two staging buffers
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int stages = p.stages, nk = p.c1 >> 6, BN = p.BN;
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const int a_bytes = P * kChunkBytes, stage_bytes = a_bytes + P * p.w_plane_bytes;
+    const uint32_t table0 = smem0 + (uint32_t)(stages * stage_bytes);              // epilogue's transposition table
+    const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[kMaxStages]);
+    const uint32_t tfull0 = smem_u32(&bars[2 * kMaxStages]), tempty0 = smem_u32(&bars[2 * kMaxStages + 2]);
+    uint32_t tmem_cols = 32;
+    while ((int)tmem_cols < 2 * BN) tmem_cols <<= 1;
+    const int total = p.tiles_m * p.n_slices;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(full0 + 8 * s, 5);           // 4 former warps + the TMA thread's expect_tx arrive
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull0 + 8 * b, 1);
+            mbar_init(tempty0 + 8 * b, 4);
+            mbar_init(smem_u32(&gbars[b]), 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) tmem_alloc(smem_u32(&tmem_base_slot), tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA: weight chunks
+        if (lane == 0) {
+            uint32_t cnt = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int n0 = (t % p.n_slices) * BN;
+                const int mma_n = min(BN, p.N - n0);
+                for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                    const int s = cnt % stages;
+                    mbar_wait(empty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
+                    const uint32_t dst = smem0 + s * stage_bytes + a_bytes;
+                    mbar_arrive_expect_tx(full0 + 8 * s, (uint32_t)(P * mma_n * 128));
+                    for (int b = 0; b < mma_n; b += 64) {
+                        tma_load_2d(dst + b * 128, &w_hi, kc * 64, n0 + b, full0 + 8 * s);
+                        if (P == 2) tma_load_2d(dst + p.w_plane_bytes + b * 128, &w_lo, kc * 64, n0 + b, full0 + 8 * s);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            uint32_t cnt = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+                const int n0 = (t % p.n_slices) * BN;
+                const int mma_n = min(BN, p.N - n0);
+                const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(mma_n >> 3) << 17) | ((uint32_t)(kRows >> 4) << 24);
+                const int buf = it & 1;
+                mbar_wait(tempty0 + 8 * buf, ((it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t acc = tmem_base + (uint32_t)(buf * BN);
+                for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                    const int s = cnt % stages;
+                    mbar_wait(full0 + 8 * s, (cnt / stages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_hi = smem0 + s * stage_bytes, a_lo = a_hi + kChunkBytes;
+                    const uint32_t b_hi = a_hi + a_bytes, b_lo = b_hi + p.w_plane_bytes;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t ko = k * 32;
+                        umma_bf16(acc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, (kc | k) ? 1u : 0u);
+                        if (P == 2) {
+                            umma_bf16(acc, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc, 1u);
+                            umma_bf16(acc, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc, 1u);
+                        }
+                    }
+                    umma_commit(empty0 + 8 * s);
+                }
+                umma_commit(tfull0 + 8 * buf);
+            }
+        }
+    } else if (warp < 6) {
+        // ------------------------------------------------------------------ formers (warps 2..5)
+        // The P rows (one per tile row: the neighbour's product) and the Q rows (one per group: the point's own product) of a
+        // 64-channel chunk are GATHERED by the TMA engine (one 256-byte cp.async.bulk per row, issued one chunk ahead into a
+        // double-buffered fp32 staging area), so the formation itself only converts shared memory to shared memory.
+        const int ft = threadIdx.x - 64;                            // 0..127
+        const uint32_t stageP0 = table0 + kTable * 4;               // [2][128 rows][64 f32]
+        const uint32_t stageQ0 = stageP0 + 2 * kRows * 256;         // [2][gpt rows][64 f32]
+        const uint32_t gbar0 = smem_u32(&gbars[0]);
+        // sequence of (tile, chunk) steps of this CTA
+        const int my_tiles = blockIdx.x < total ? (total - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+        const int n_steps = my_tiles * nk;
+        int ri_cur = -1, rj_cur = -1, ri_nxt = -1, rj_nxt = -1;
+        auto meta_of = [&](int tile_iter, int& ri, int& rj) {
+            const int t = blockIdx.x + tile_iter * gridDim.x;
+            ri = -1; rj = -1;
+            if (tile_iter >= my_tiles) return;
+            const int q0 = (t / p.n_slices) * p.gpt, nseg = max(0, min(p.gpt, p.n - q0));
+            if (ft < nseg * p.G) {
+                const int sg = ft / p.G, g = ft - sg * p.G;
+                ri = q0 + sg;
+                rj = g == 0 ? ri : __ldg(p.idx + (int64_t)ri * p.Knb + g - 1);
+            }
+        };
+        auto issue = [&](int step, int ri, int rj) {                // gathers of step -> staging buffer step & 1
+            const int kc = step % nk, b = step & 1;
+            const int t = blockIdx.x + (step / nk) * gridDim.x;
+            const int q0 = (t / p.n_slices) * p.gpt, nseg = max(0, min(p.gpt, p.n - q0));
+            uint32_t bytes = 0;
+            if (rj >= 0) bytes += 256;
+            if (ft < nseg) bytes += 256;
+            mbar_arrive_tx(gbar0 + 8 * b, bytes);
+            if (rj >= 0) bulk_g2s(stageP0 + (uint32_t)(b * kRows + ft) * 256, p.PQ + (int64_t)rj * p.ldpq + kc * 64, 256, gbar0 + 8 * b);
+            if (ft < nseg)
+                bulk_g2s(stageQ0 + (uint32_t)(b * p.gpt + ft) * 256, p.PQ + (int64_t)(q0 + ft) * p.ldpq + p.c1 + kc * 64, 256, gbar0 + 8 * b);
+        };
+        meta_of(0, ri_cur, rj_cur);
+        if (n_steps > 0) issue(0, ri_cur, rj_cur);
+        uint32_t cnt = 0;
+        for (int step = 0; step < n_steps; ++step, ++cnt) {
+            const int it = step / nk, kc = step - it * nk, b = step & 1, mb = it & 1;
+            if (kc == 0) {
+                row_i[mb][ft] = ri_cur;
+                row_j[mb][ft] = rj_cur;
+                row_mask[it & (kMaskSlots - 1)][ft] = (ri_cur >= 0 && rj_cur < 0) ? 1 : 0;
+                meta_of(it + 1, ri_nxt, rj_nxt);                    // next tile's neighbour ids: in flight during this tile
+            }
+            asm volatile("bar.sync 2, 128;" ::: "memory");          // metadata visible; everyone has converted step - 1 (buffer b ^ 1 free)
+            if (step + 1 < n_steps) {
+                const bool next_tile = kc + 1 == nk;
+                issue(step + 1, next_tile ? ri_nxt : ri_cur, next_tile ? rj_nxt : rj_cur);
+            }
+            mbar_wait(gbar0 + 8 * b, (step >> 1) & 1);              // this step's rows have landed
+            const int s = cnt % stages;
+            mbar_wait(empty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
+            const uint32_t a0 = smem0 + s * stage_bytes;
+#pragma unroll 2
+            for (int item = ft; item < kRows * 8; item += 128) {
+                const int row = item >> 3, g8 = item & 7;
+                const int i = row_i[mb][row], j = row_j[mb][row];
+                float y[8];
+                if (i < 0) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) y[e] = 0.f;
+                } else {
+                    const int sg = row / p.G;
+                    const uint32_t qa = stageQ0 + (uint32_t)(b * p.gpt + sg) * 256 + g8 * 32;
+                    const float4 a = lds128(qa), c = lds128(qa + 16);
+                    y[0] = a.x; y[1] = a.y; y[2] = a.z; y[3] = a.w; y[4] = c.x; y[5] = c.y; y[6] = c.z; y[7] = c.w;
+                    if (j >= 0) {
+                        const uint32_t pa = stageP0 + (uint32_t)(b * kRows + row) * 256 + g8 * 32;
+                        const float4 d = lds128(pa), f = lds128(pa + 16);
+                        y[0] += d.x; y[1] += d.y; y[2] += d.z; y[3] += d.w; y[4] += f.x; y[5] += f.y; y[6] += f.z; y[7] += f.w;
+                    }
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) y[e] = act_apply(y[e], p.act0, p.slope0);
+                }
+                store_piece<P>(a0 + row * 128 + ((g8 ^ (row & 7)) << 4), y);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(full0 + 8 * s);
+            if (kc + 1 == nk) { ri_cur = ri_nxt; rj_cur = rj_nxt; }
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue (warps 6..9)
+        const int et = threadIdx.x - 192;                           // 0..127
+        const int q = warp & 3;
+        const int myrow = q * 32 + lane;
+        const uint32_t lane_base = (uint32_t)(q * 32) << 16;
+        float* T = reinterpret_cast<float*>(smem_raw + (table0 - smem_u32(smem_raw)));
+        const int swz = myrow & 31;
+        int it = 0, bias_n0 = -1;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+            const int m_tile = t / p.n_slices, n0 = (t % p.n_slices) * BN;
+            const int mma_n = min(BN, p.N - n0);
+            const int q0 = m_tile * p.gpt, nseg = max(0, min(p.gpt, p.n - q0));
+            const int buf = it & 1;
+            if (n0 != bias_n0) {
+                asm volatile("bar.sync 3, 128;" ::: "memory");
+                for (int j = et; j < BN; j += 128) bias_s[j] = (p.bias && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+                asm volatile("bar.sync 3, 128;" ::: "memory");
+                bias_n0 = n0;
+            }
+            mbar_wait(tfull0 + 8 * buf, (it >> 1) & 1);
+            tc_fence_after();
+            const bool masked = row_mask[it & (kMaskSlots - 1)][myrow] != 0;
+            const uint32_t tacc = tmem_base + lane_base + (uint32_t)(buf * BN);
+            for (int c0 = 0; c0 < mma_n; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tacc + (uint32_t)c0, v);
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    float y = act_apply(__uint_as_float(v[e]) + bias_s[c0 + e], p.act, p.slope);
+                    if (masked) y = -100.f;
+                    T[myrow * 32 + (e ^ swz)] = y;
+                }
+                asm volatile("bar.sync 3, 128;" ::: "memory");
+                const int c = et & 31;
+                for (int sg = et >> 5; sg < nseg; sg += 4) {
+                    const int lo = sg * p.G, hi = lo + p.G;
+                    float r = T[lo * 32 + (c ^ (lo & 31))];
+#pragma unroll 4
+                    for (int j = lo + 1; j < hi; ++j) r = fmaxf(r, T[j * 32 + (c ^ (j & 31))]);
+                    const int64_t orow = q0 + sg;
+                    const int col = n0 + c0 + c;
+                    p.out[orow * p.ldo + col] = r;
+                    if (p.planes) {
+                        const __nv_bfloat16 h = __float2bfloat16_rn(r);
+                        p.planes[orow * p.kpad + col] = h;
+                        if (p.npl == 2) p.planes[p.pstride + orow * p.kpad + col] = __float2bfloat16_rn(r - __bfloat162float(h));
+                    }
+                }
+                asm volatile("bar.sync 3, 128;" ::: "memory");
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, tmem_cols);
+    }
+}
+
 // ---- host side -------------------------------------------------------------------------------------------------
 constexpr int kSmemLimit = 227 * 1024;
 constexpr int kStaticSmem = 14 * 1024;          // bias / Wp / row tables / barriers (ptxas reports ~12.8 KB)
@@ -544,6 +832,55 @@ int launch_chain(const ccn_chain_t* ch, const ChainParams& p, int smem, cudaStre
     return CCN_OK;
 }
 
+template <int P>
+int launch_stream_t(const StreamParams& p, const ccn_chain_t* ch, int smem, int grid, cudaStream_t s) {
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(sgcnn_stream_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit - 8 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr = true;
+    }
+    const CUtensorMap* whi = (const CUtensorMap*)ch->w_hi_tmap;
+    const CUtensorMap* wlo = P == 2 ? (const CUtensorMap*)ch->w_lo_tmap : whi;
+    sgcnn_stream_kernel<P><<<grid, kStreamThreads, smem, s>>>(*whi, *wlo, p);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+int launch_stream(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c1, int32_t act0, float slope0,
+                  const ccn_chain_t* ch, float* out, int64_t ldo, void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes,
+                  cudaStream_t s) {
+    CCN_REQUIRE(ch->w_hi_tmap && (ch->mode == 1 || (ch->mode == 3 && ch->w_lo_tmap)));
+    const int P = ch->mode == 3 ? 2 : 1;
+    const int N = ch->n[0];
+    CCN_REQUIRE(ch->k[0] == c1 && c1 >= 64 && c1 <= 1024 && (c1 & 63) == 0 && N >= 64 && N <= 1024 && (N & 63) == 0);
+    CCN_REQUIRE(ch->act[0] >= 0 && ch->act[0] <= 2 && ch->w_row[0] == 0);
+    CCN_REQUIRE(ldo >= N && (!planes || (kpad >= N && (n_planes == 1 || n_planes == 2))));
+    CCN_REQUIRE((ldpq & 3) == 0 && (reinterpret_cast<uintptr_t>(PQ) & 15) == 0);       // 16-byte aligned rows for the bulk gathers
+    if (n == 0) return CCN_OK;
+    StreamParams p = {};
+    p.PQ = PQ; p.ldpq = ldpq; p.idx = idx; p.n = (int)n; p.Knb = K; p.G = K + 1; p.gpt = kRows / (K + 1);
+    p.c1 = c1; p.act0 = act0; p.slope0 = slope0;
+    p.N = N; p.act = ch->act[0]; p.slope = ch->slope[0]; p.bias = ch->bias[0];
+    p.BN = N < 128 ? N : 128;
+    p.n_slices = (N + p.BN - 1) / p.BN;
+    p.tiles_m = (int)((n + p.gpt - 1) / p.gpt);
+    p.w_plane_bytes = p.BN * 128;
+    const int stage = P * kChunkBytes + P * p.w_plane_bytes;
+    const int table = kTable * 4 + 2 * kRows * 256 + 2 * p.gpt * 256;      // transposition table + fp32 row staging (P rows, Q rows)
+    int stages = (kSmemLimit - 8 * 1024 - 1024 - table) / stage;
+    if (stages > kMaxStages) stages = kMaxStages;
+    if (stages < 2) return CCN_EUNSUPPORTED;
+    p.stages = stages;
+    p.out = out; p.ldo = ldo; p.planes = (__nv_bfloat16*)planes; p.kpad = kpad; p.pstride = plane_stride; p.npl = n_planes;
+    const int smem = stages * stage + table + 1024;
+    const int64_t total = (int64_t)p.tiles_m * p.n_slices;
+    // a CTA keeps one column slice (tile t -> slice t % n_slices): the grid is a multiple of n_slices
+    int grid = (int)(total < 148 ? total : (148 / p.n_slices) * p.n_slices);
+    if (grid < 1) grid = 1;
+    return P == 2 ? launch_stream_t<2>(p, ch, smem, grid, s) : launch_stream_t<1>(p, ch, smem, grid, s);
+}
+
 }  // namespace
 
 extern "C" int ccn_sgcnn_fused(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n, int32_t K, int32_t c1,
@@ -551,6 +888,9 @@ extern "C" int ccn_sgcnn_fused(const float* PQ, int64_t ldpq, const int32_t* idx
                                void* planes, int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
     CCN_REQUIRE(PQ && idx && out && n >= 0 && n < 0x7fffffff && K >= 1 && K + 1 <= kRows && act0 >= 0 && act0 <= 2);
     CCN_REQUIRE(ldpq >= 2 * c1 && (ldpq & 3) == 0 && (reinterpret_cast<uintptr_t>(PQ) & 15) == 0);
+    if (chain_host && chain_host->n_layers == 1)
+        return launch_stream(PQ, ldpq, idx, n, K, c1, act0, slope0, chain_host, out, ldo, planes, kpad, plane_stride, n_planes,
+                             (cudaStream_t)stream);
     ChainParams p = {};
     int smem = 0, P = 1;
     const int rc = fill_chain(p, chain_host, c1, false, smem, P);

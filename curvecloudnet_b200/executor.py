@@ -157,7 +157,7 @@ class _PlanBuilder:
                 w = xw + ([3] if step.with_xyz or not cur else [])
                 lin_pq, act0, slope0 = step._decomposed()
                 layers = step.nn.layers()
-                cw = step._fused.get(layers) if step.k + 1 <= 128 else None
+                cw = step._fused.get(layers, dense=True) if step.k + 1 <= 128 else None
                 rest = [self.linear(l) for l in layers[1:]]
                 self.keep += [layers, lin_pq]
                 iv = [int(step.with_xyz), step.k, self.linear(lin_pq, w), act0, self.chain(cw), len(rest)] + rest

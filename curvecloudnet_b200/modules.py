@@ -27,14 +27,14 @@ class _ChainCache:
     def __init__(self):
         self.key, self.chain = None, None
 
-    def get(self, layers, extra=()):
+    def get(self, layers, extra=(), dense=False):
         npl = n_planes()
-        key = (id(layers), npl, id(extra) if extra else 0, ops.FUSED_EDGE_STEPS)
+        key = (id(layers), npl, id(extra) if extra else 0, ops.FUSED_EDGE_STEPS, dense)
         if self.key != key:
             rest = list(layers[1:]) + list(extra)
             ok = (npl > 0 and len(rest) >= 1 and
-                  ops.ChainWeights.supported(layers[0].out_features, [l.out_features for l in rest]) and
-                  ops.fused_profitable(layers[0].out_features, npl, bool(extra)))
+                  ops.ChainWeights.supported(layers[0].out_features, [l.out_features for l in rest], dense) and
+                  ops.fused_profitable(layers[0].out_features, npl, bool(extra), dense and len(rest) == 1))
             self.chain = ops.ChainWeights([(l.w, l.b, l.act, l.slope) for l in rest], npl) if ok else None
             self.key, self._keep = key, (layers, extra)
         return self.chain
@@ -494,7 +494,7 @@ class SGCNNLayer(nn.Module):
             return out, pos, batch, point2curveidx
         if not self.use_sparse_feat_agg:
             nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, self.k, self.r, cache=cache)
-            chain = self._fused.get(self.nn.layers()) if self.k + 1 <= 128 else None
+            chain = self._fused.get(self.nn.layers(), dense=True) if self.k + 1 <= 128 else None
             if chain is not None:
                 # gather -> layer 1 -> remaining layers -> masked max in ONE kernel (csrc/edge_fused.cu)
                 return ops.sgcnn_fused(PQ, nbr, act0, slope0, chain, n_planes(), cache), pos, batch, point2curveidx

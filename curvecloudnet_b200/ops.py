@@ -849,6 +849,7 @@ def linear_tc(A: torch.Tensor, tw: TcWeight, bias: Optional[torch.Tensor], act: 
 # ----------------------------------------------------------------------------------------------
 CHAIN_MAX_LAYERS = 6
 CHAIN_MAX_WIDTH = 256
+STREAM_MAX_WIDTH = 1024
 
 
 class ChainWeights:
@@ -894,19 +895,28 @@ class ChainWeights:
         self.addr = ctypes.addressof(c)
 
     @staticmethod
-    def supported(c1: int, dims) -> bool:
-        """dims: output widths of the chain layers.  Every width a multiple of 64 and <= 256."""
-        return (len(dims) >= 1 and len(dims) <= CHAIN_MAX_LAYERS and c1 % 64 == 0 and 64 <= c1 <= CHAIN_MAX_WIDTH and
-                all(d % 64 == 0 and 64 <= d <= CHAIN_MAX_WIDTH for d in dims))
+    def supported(c1: int, dims, dense: bool = False) -> bool:
+        """dims: output widths of the chain layers.  Every width a multiple of 64 and <= 256 (the activations of a tile stay
+        resident in shared memory); a dense SGCNN step with ONE chain layer streams its operands instead and takes widths up
+        to 1024 (sgcnn_stream_kernel)."""
+        wmax = STREAM_MAX_WIDTH if dense and len(dims) == 1 else CHAIN_MAX_WIDTH
+        return (len(dims) >= 1 and len(dims) <= CHAIN_MAX_LAYERS and c1 % 64 == 0 and 64 <= c1 <= wmax and
+                all(d % 64 == 0 and 64 <= d <= wmax for d in dims))
 
 
-def fused_profitable(c1: int, n_planes: int, attention: bool) -> bool:
+def fused_profitable(c1: int, n_planes: int, attention: bool, dense_single_layer: bool = False) -> bool:
     """Measured on B200 (tools/bench_fused.py, profiles/r02g_fused.txt): the one-kernel edge step wins for the NARROW chains
     (resident activation tile <= 32 KB: two CTAs per SM overlap each other's latency chains) - the 374 k-row level-1 SGCNN
     steps, 96 us against 116 us in bf16x3 - and loses to the unfused launches on the 128 / 256-wide chains (one CTA per SM,
     the serial form -> MMA -> epilogue chain of a tile is not hidden) and on the attention steps (1.5x slower)."""
     if FUSED_EDGE_STEPS != "auto":
         return bool(FUSED_EDGE_STEPS)
+    if dense_single_layer:
+        # sgcnn_stream_kernel (one chain layer, widths up to 1024): 76 / 90 / 101 / 130 us against 58 / 48 / 50 / 46 us of the
+        # unfused launches at the level-2..5 shapes (profiles/r02l_fused_bf16x3.txt) - forming the A operand inside the GEMM
+        # is bound by the gather rate of one SM's few producer warps (per-thread loads: 74 us; TMA row gathers of 256 bytes:
+        # 76 us, the copy engine serialises small copies), where the stand-alone layer-1 kernel gathers at full occupancy
+        return False
     return (not attention) and c1 * n_planes <= 128
 
 

@@ -37,7 +37,9 @@ def _set(precision):
 
 @pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
 @pytest.mark.parametrize("n,K,dims", [(1000, 20, [64, 64, 64]), (37, 20, [128, 128]), (5000, 20, [256, 256]),
-                                       (777, 9, [64, 128, 192, 256]), (4, 31, [128, 64]), (2500, 20, [64, 64])])
+                                       (777, 9, [64, 128, 192, 256]), (4, 31, [128, 64]), (2500, 20, [64, 64]),
+                                       (12180 // 21, 20, [512, 512]), (174, 20, [1024, 1024]), (3000, 20, [128, 192]),
+                                       (900, 5, [256, 64])])
 def test_sgcnn_fused(precision, n, K, dims):
     from curvecloudnet_b200 import nn, ops
     from curvecloudnet_b200.nn import ForwardCache, PreparedLinear

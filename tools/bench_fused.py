@@ -40,7 +40,7 @@ def layers_of(dims, acts):
 
 
 print("precision", precision)
-for n, K, dims in [(17809, 20, [64, 64, 64]), (5695, 20, [128, 128]), (1933, 20, [256, 256])]:
+for n, K, dims in [(17809, 20, [64, 64, 64]), (5695, 20, [128, 128]), (1933, 20, [256, 256]), (580, 20, [512, 512]), (174, 20, [1024, 1024])]:
     gen = torch.Generator().manual_seed(n)
     c1 = dims[0]
     PQ = torch.randn(n, 2 * c1, generator=gen).cuda()
