@@ -219,6 +219,23 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------------------------
 TRAIN_METRIC = "points/sec fwd+bwd training step (ShapeNet-seg-shape CurveCloudNet)"
 TRAIN_WORKLOAD = "ShapeNet-seg-shape CurveCloudNet training step (fwd + NLL loss + bwd + Adam), B=%d x 2048 synthetic scan-line points"
+# --train-config: the other data-parallel training configurations of BASELINE.json (per-GPU batch fixed: weak scaling)
+TRAIN_CONFIGS = {
+    "shapenet-seg": dict(model="shapenet-seg", batch=16, lovasz=False, metric=TRAIN_METRIC, workload=TRAIN_WORKLOAD),
+    "kortx": dict(model="kortx", batch=64, lovasz=False,
+                  metric="points/sec fwd+bwd training step (Kortx-shape CurveCloudNet)",
+                  workload="Kortx-shape CurveCloudNet training step (fwd + NLL loss + bwd + Adam), B=%d x 2048-point crops per GPU (BASELINE configs[2])"),
+    "kitti": dict(model="kitti", batch=2, lovasz=True,
+                  metric="points/sec fwd+bwd training step (KITTI-shape CurveCloudNet)",
+                  workload="KITTI/A2D2-shape CurveCloudNet training step (fwd + NLL + Lovasz loss + bwd + Adam), B=%d x ~114 k-point 64-beam scans per GPU (BASELINE configs[4])"),
+}
+
+
+def _train_batch(cfg, seeds):
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch
+    if cfg["model"] == "kitti":
+        return driving_scan_batch(seeds, kind="kitti", n_classes=20)
+    return object_scan_batch(seeds)
 
 
 def cpu_train_points_per_s(batch, iters, warmup, threads):
@@ -260,7 +277,7 @@ def run_train_reference(args):
         "impl": "reference", "metric": TRAIN_METRIC, "value": pps, "unit": "points/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": TRAIN_WORKLOAD % args.train_batch, "sample": sample},
+        "config": {"workload": TRAIN_WORKLOAD % (args.train_batch or 16), "sample": sample},
         "cpu_baseline": {"value": pps, "unit": "points/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": pps, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
@@ -283,10 +300,13 @@ def run_train(args):
     from curvecloudnet_b200.sharding import GradReducer
     from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
     native.load()
-    W, K, B = max(args.warmup, 3), max(args.steps, 1), args.train_batch
+    tcfg = TRAIN_CONFIGS[args.train_config]
+    W, K = max(args.warmup, 3), max(args.steps, 1)
+    B = args.train_batch if args.train_batch > 0 else tcfg["batch"]
     WG = "ccn_linear_wgrad" if args.precision == "fp32" else "ccn_linear_wgrad_tc"
     LIN = "ccn_linear_f32" if args.precision == "fp32" else "ccn_linear_planes"
-    model = build_model(ModelBase, "shapenet-seg", precision=args.precision)
+    from curvecloudnet_b200 import losses as L
+    model = build_model(ModelBase, tcfg["model"], precision=args.precision)
     randomize_model_(model, 1234)
     model = model.cuda().train()
     reducer = GradReducer(model.parameters(), dist)
@@ -294,9 +314,9 @@ def run_train(args):
     gen = torch.Generator().manual_seed(rank)
     host, targets = [], []
     for s in range(args.scans):
-        d = object_scan_batch([10000 * rank + B * s + b for b in range(B)])
+        d = _train_batch(tcfg, [10000 * rank + B * s + b for b in range(B)])
         host.append(d.pin_memory())
-        targets.append(torch.randint(0, 50, (d.pos.shape[0],), generator=gen).pin_memory())
+        targets.append(torch.randint(0, model.n_out, (d.pos.shape[0],), generator=gen).pin_memory())
     dev = [(d.to("cuda"), t.to("cuda")) for d, t in zip(host, targets)]
     pts = [d.num_points for d in host]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -324,7 +344,10 @@ def run_train(args):
             else:
                 data, tgt = dev[j]
             reducer.prepare()
-            loss = A.nll_loss(model(data), tgt)
+            if tcfg["lovasz"]:
+                loss, _ = L.seg_loss(model(data), tgt, ignore=0, use_lovasz=True)
+            else:
+                loss = A.nll_loss(model(data), tgt)
             loss.backward()
             reducer.finish()
             opt.step()
@@ -383,10 +406,10 @@ def run_train(args):
         roofline["wgrad"] = kernel_roofline(WG, "wgrad_tc_kernel (ccn_linear_wgrad_tc: TMA + tcgen05 MN-major + TMEM, split-M)",
                                             "ccn_linear_wgrad_tc:%s" % args.precision)
     line = {
-        "metric": TRAIN_METRIC, "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K,
+        "metric": tcfg["metric"], "value": tot_pts / (ms_max * 1e-3), "unit": "points/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "%s Linear / curve-conv GEMMs (forward, data and weight gradients), f32 everything else" % args.precision, "data": "synthetic",
-        "config": {"workload": TRAIN_WORKLOAD % B, "points_per_step": tot_pts / (K * world), "scans_per_step": B,
+        "config": {"workload": tcfg["workload"] % B, "points_per_step": tot_pts / (K * world), "scans_per_step": B,
                    "distinct_batches_per_rank": args.scans, "optimizer": "torch.optim.Adam(fused)",
                    "parallelism": "data parallel dp%d, bucketed gradient all-reduce overlapped with backward" % world,
                    "l2": "256 MiB buffer written between timed steps (L2 flush)"},
@@ -397,7 +420,7 @@ def run_train(args):
         "roofline": roofline,
         "clocks": clocks,
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and args.train_config == "shapenet-seg":
         threads = os.cpu_count() or 1
         pps, n, sec = cpu_train_points_per_s(2, 2, 1, threads)
         line["cpu_baseline"] = {"value": pps, "unit": "points/s", "cores": threads, "kind": "port",
@@ -474,7 +497,9 @@ def main():
                     help="infer: nuScenes-shape forward (the headline metric); train: ShapeNet-seg fwd+bwd step (configs[1])")
     ap.add_argument("--no-batched-variant", action="store_true", help="skip the informational B=6 line (batched_variant)")
     ap.add_argument("--no-train-variant", action="store_true", help="skip the informational training-step line (train_variant)")
-    ap.add_argument("--train-batch", type=int, default=16, help="scans per training step per GPU (--mode train)")
+    ap.add_argument("--train-batch", type=int, default=0, help="scans per training step per GPU (--mode train; 0 = the config's)")
+    ap.add_argument("--train-config", default="shapenet-seg", choices=["shapenet-seg", "kortx", "kitti"],
+                    help="--mode train: ShapeNet-seg B=16 (configs[1]) | Kortx B=64 (configs[2]) | KITTI-shape B=2, NLL+Lovasz (configs[4])")
     args = ap.parse_args()
     if args.mode == "train":
         return run_train_reference(args) if args.impl == "reference" else run_train(args)

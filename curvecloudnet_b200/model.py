@@ -155,7 +155,9 @@ class ModelBase(torch.nn.Module):
         native.pin_stream(True)
         set_weights_epoch(self._weights_epoch())
         try:
-            if self.native_executor and not self.training and self.precision != "fp32" and not kwargs:
+            # `labels=` is what the run scripts pass (nuscenes_seg.py:36) and no step reads: it does not keep a forward off the
+            # native executor; any other keyword (trace=, cache= ...) selects the python executor
+            if self.native_executor and not self.training and self.precision != "fp32" and not (set(kwargs) - {"labels"}):
                 out = self._forward_native(data, draws)
                 if out is not None:
                     return out
