@@ -430,7 +430,7 @@ def run_train(args):
         dist.destroy_process_group()
 
 
-def train_variant(dist, rank, world, precision, batch=16, steps=4, warmup=2):
+def train_variant(dist, rank, world, precision, batch=16, steps=6, warmup=4):
     """Informational line inside the default (inference) bench at EVERY N: the ShapeNet-seg training step (BASELINE.json
     configs[1], fwd + NLL + bwd + fused Adam, B = 16 x 2048 points per GPU) through sharding.GradReducer - the ONE collective
     of the design (bucketed NCCL gradient all-reduce overlapped with backward), so that the driver's scaling run sees it.
