@@ -438,6 +438,23 @@ int frnn(Exec& ex, Level* q, Level* src, int K, float radius, bool want_cnt, int
     return CCN_OK;
 }
 
+// ops.knn_exact: brute force, or the hashed grid from ~7e8 query x source pairs on (same result bit for bit; ops.KNN_GRID_MIN_PAIRS)
+int knn_exact(Exec& ex, Level* fine, Level* coarse, int knn, int32_t* nbr, float* wgt) {
+    if (knn <= 4 && (double)fine->n * (double)coarse->n >= 7e8) {
+        const int64_t cells = ccn_grid_num_cells(coarse->n);
+        int32_t* cell_off = ex.alloc_n<int32_t>(cells + 1);
+        int32_t* slot = ex.alloc_n<int32_t>(coarse->n);
+        float* sorted = ex.alloc_n<float>(4 * (coarse->n > 0 ? coarse->n : 1));
+        int32_t* scratch = ex.alloc_n<int32_t>(16 + fine->n);
+        if (ex.oom) return CCN_OK;
+        return ccn_knn_grid(fine->pos.f, fine->batch, fine->n, coarse->pos.f, coarse->batch, coarse->n, coarse->sptr_dev, knn, 1, 0.f,
+                            cells, cell_off, slot, sorted, scratch, nbr, wgt, nullptr, (ccn_stream_t)ex.stream);
+    }
+    if (ex.oom) return CCN_OK;
+    return ccn_knn_exact(fine->pos.f, fine->batch, fine->n, coarse->pos.f, coarse->sptr_dev, knn, 1, nbr, wgt, nullptr,
+                         (ccn_stream_t)ex.stream);
+}
+
 struct Edges { int32_t *row_ptr, *erow, *ecol; int64_t E, nq; int max_degree; };
 
 // PointNetConv2.forward_edges (inference): decomposed first layer, fused chain kernel or the unfused launches
@@ -676,7 +693,7 @@ int geometry_ahead(Exec& ex, int si, Level* lv, Level* ch, const int64_t* idx) {
         float* wgt = ex.alloc_n<float>(lv->n * knn);
         if (!ex.oom) {
             if (fp.kind == ST_FP)
-                rc = ccn_knn_exact(lv->pos.f, lv->batch, lv->n, ch->pos.f, ch->sptr_dev, knn, 1, nbr, wgt, nullptr, (ccn_stream_t)ex.geo);
+                rc = knn_exact(ex, lv, ch, knn, nbr, wgt);
             else if (lv->has_topo && idx)
                 rc = ccn_knn_1d_superset(lv->pos.f, lv->curve_ord, lv->n, idx, ch->n, knn, nbr, wgt, (ccn_stream_t)ex.geo);
             else
@@ -1161,8 +1178,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 } else if (s.kind == ST_FP) {
                     EX_CALL(level_sptr(ex, cur.lv));
                     ProfScope ps(ex, FAM_SEARCH, 0, 12.0 * fine->n + 12.0 * cur.lv->n + 8.0 * fine->n * knn);
-                    if (!ex.oom)
-                        EX_CALL(ccn_knn_exact(fine->pos.f, fine->batch, fine->n, cur.lv->pos.f, cur.lv->sptr_dev, knn, 1, nbr, wgt, nullptr, st));
+                    EX_CALL(knn_exact(ex, fine, cur.lv, knn, nbr, wgt));
                 } else {
                     EX_CALL(level_topo(ex, fine));
                     const int64_t* idx = down_idx[sidx];

@@ -103,14 +103,16 @@ constexpr int kFpsThreads = 512;
 
 struct FpsPartial { unsigned bits; int idx; float x, y, z; };
 
-template <int PPT>
-__global__ void __launch_bounds__(kFpsThreads) fps_kernel(const float* __restrict__ pos,
+// THREADS: the K selection rounds are sequential; a round = every thread's serial argmax over its own points + one block-wide
+// argmax, so the block is as WIDE as the cloud allows (2 points per thread up to 2048 points).
+template <int PPT, int THREADS>
+__global__ void __launch_bounds__(THREADS) fps_kernel(const float* __restrict__ pos,
                                                           const int32_t* __restrict__ sptr,
                                                           const int32_t* __restrict__ ksel,
                                                           const int32_t* __restrict__ start,
                                                           float* __restrict__ closest_scratch,
                                                           int32_t* __restrict__ sel_cnt) {
-    __shared__ FpsPartial part[2][kFpsThreads / 32];
+    __shared__ FpsPartial part[2][THREADS / 32];
     const int b = blockIdx.x;
     const int lo = sptr[b], len = sptr[b + 1] - lo;
     const int k = min(ksel[b], len);
@@ -120,13 +122,13 @@ __global__ void __launch_bounds__(kFpsThreads) fps_kernel(const float* __restric
     if (PPT > 0) {
 #pragma unroll
         for (int j = 0; j < PPT; ++j) {
-            const int i = threadIdx.x + j * kFpsThreads;
+            const int i = threadIdx.x + j * THREADS;
             if (i < len) { px[j] = pos[3 * (lo + i)]; py[j] = pos[3 * (lo + i) + 1]; pz[j] = pos[3 * (lo + i) + 2]; }
             else { px[j] = py[j] = pz[j] = 0.f; }
             cl[j] = __int_as_float(0x7f800000);
         }
     } else {
-        for (int i = threadIdx.x; i < len; i += kFpsThreads) closest_scratch[lo + i] = __int_as_float(0x7f800000);
+        for (int i = threadIdx.x; i < len; i += THREADS) closest_scratch[lo + i] = __int_as_float(0x7f800000);
     }
     int sel = start[b];
     float sx = pos[3 * (lo + sel)], sy = pos[3 * (lo + sel) + 1], sz = pos[3 * (lo + sel) + 2];
@@ -138,7 +140,7 @@ __global__ void __launch_bounds__(kFpsThreads) fps_kernel(const float* __restric
         if (PPT > 0) {
 #pragma unroll
             for (int j = 0; j < PPT; ++j) {
-                const int i = threadIdx.x + j * kFpsThreads;
+                const int i = threadIdx.x + j * THREADS;
                 if (i < len) {
                     const float d = ccn_sqdist3(px[j], py[j], pz[j], sx, sy, sz);
                     const float c = fminf(cl[j], d);
@@ -148,7 +150,7 @@ __global__ void __launch_bounds__(kFpsThreads) fps_kernel(const float* __restric
                 }
             }
         } else {
-            for (int i = threadIdx.x; i < len; i += kFpsThreads) {
+            for (int i = threadIdx.x; i < len; i += THREADS) {
                 const float x = pos[3 * (lo + i)], y = pos[3 * (lo + i) + 1], z = pos[3 * (lo + i) + 2];
                 const float c = fminf(closest_scratch[lo + i], ccn_sqdist3(x, y, z, sx, sy, sz));
                 closest_scratch[lo + i] = c;
@@ -164,8 +166,8 @@ __global__ void __launch_bounds__(kFpsThreads) fps_kernel(const float* __restric
         if (has && bidx == widx) { part[buf][warp] = FpsPartial{wmax, widx, bx, by, bz}; }
         else if (widx == 0x7fffffff && lane == 0) { part[buf][warp] = FpsPartial{0u, 0x7fffffff, 0.f, 0.f, 0.f}; }
         __syncthreads();
-        FpsPartial p = part[buf][lane < kFpsThreads / 32 ? lane : 0];
-        const bool phas = lane < kFpsThreads / 32 && p.idx != 0x7fffffff;
+        FpsPartial p = part[buf][lane < THREADS / 32 ? lane : 0];
+        const bool phas = lane < THREADS / 32 && p.idx != 0x7fffffff;
         const unsigned gmax = __reduce_max_sync(0xffffffffu, phas ? p.bits : 0u);
         const int gidx = __reduce_min_sync(0xffffffffu, (phas && p.bits == gmax) ? p.idx : 0x7fffffff);
         const unsigned owner = __ballot_sync(0xffffffffu, phas && p.bits == gmax && p.idx == gidx);
@@ -241,15 +243,20 @@ extern "C" int ccn_fps(const float* pos, const int32_t* sample_ptr, int32_t n_sa
     cudaError_t e = cudaMemsetAsync(sel_cnt_scratch, 0, (n > 0 ? n : 1) * 4, s);
     if (e != cudaSuccess) return (int)e;
     if (n_samples > 0 && n > 0) {
-        const int ppt = (max_len + kFpsThreads - 1) / kFpsThreads;
-        if (ppt <= 2) fps_kernel<2><<<n_samples, kFpsThreads, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch);
-        else if (ppt <= 4) fps_kernel<4><<<n_samples, kFpsThreads, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch);
-        else if (ppt <= 8) fps_kernel<8><<<n_samples, kFpsThreads, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch);
-        else if (ppt <= 16) fps_kernel<16><<<n_samples, kFpsThreads, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch);
+#define CCN_FPS_LAUNCH(PPT, T) fps_kernel<PPT, T><<<n_samples, T, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch)
+        // measured (tools/bench_fps.py, profiles/r02o_fps_variants.txt): a round costs ~0.5 us whatever the split - 4 warps x 16
+        // points 0.95 us, 32 warps x 2 points 0.60 us, 16 warps x 4 points 0.50 us (kept): the round is the latency chain
+        // distance -> warp argmax -> shared memory -> barrier -> block argmax, not arithmetic, so a CTA cluster per cloud (a
+        // slower barrier per round) cannot shorten it; at B = 1 the executor hides the sampler behind the edge steps instead
+        if (max_len <= 1024) CCN_FPS_LAUNCH(2, 512);
+        else if (max_len <= 2048) CCN_FPS_LAUNCH(4, 512);
+        else if (max_len <= 4096) CCN_FPS_LAUNCH(8, 512);
+        else if (max_len <= 8192) CCN_FPS_LAUNCH(16, 512);
         else {
             CCN_REQUIRE(closest_scratch);
-            fps_kernel<0><<<n_samples, kFpsThreads, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch);
+            CCN_FPS_LAUNCH(0, 1024);
         }
+#undef CCN_FPS_LAUNCH
         CCN_CHECK_LAUNCH();
     }
     expand_counts_kernel<<<1, 1024, 0, s>>>(sel_cnt_scratch, n, idx_out, total_out);

@@ -376,7 +376,7 @@ class FPModule(nn.Module):
                                point2curveidx_skip, **kwargs)
         cache = get_cache(kwargs)
         sptr = cache.sample_ptr(batch)
-        nbr, d2 = ops.knn_exact(pos_skip, batch_skip, pos, sptr, self.k, zero_fill=True, want_d2=True)
+        nbr, d2 = ops.knn_exact(pos_skip, batch_skip, pos, sptr, self.k, zero_fill=True, want_d2=True, batch2=batch)
         y = ops.interp_blend(x, nbr, d2, from_d2=True, npl=n_planes(), cache=cache)
         y = mlp_to_features(self.nn, _fp_concat(y, x_skip, pos_skip, self.with_xyz, cache), cache)
         return y, pos_skip, batch_skip, point2curveidx_skip

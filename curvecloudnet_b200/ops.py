@@ -344,12 +344,31 @@ def frnn_knn(pos1, batch1, pos2, batch2, sptr2: SamplePtr, K: int, radius: float
     return idx, d2, cnt
 
 
-def knn_exact(pos1, batch1, pos2, sptr2: SamplePtr, K: int, zero_fill=True, want_d2=True, want_cnt=False):
+# exact 3-NN through the hashed grid pays from ~7e8 query x source pairs on (tools/bench_knn.py, profiles/r02o_knn.txt:
+# 113 k x 57 k: 4.24 ms brute force -> 0.77 ms; 32 k x 16 k: 0.43 ms brute force, 0.70 ms grid)
+KNN_GRID_MIN_PAIRS = 7e8
+
+
+def knn_exact(pos1, batch1, pos2, sptr2: SamplePtr, K: int, zero_fill=True, want_d2=True, want_cnt=False, batch2=None,
+              use_grid=None):
+    """pytorch3d.ops.knn_points (point_ops.py:91): exact K nearest by (d2, index).  K <= 4 with `batch2` given: through the
+    hashed grid (ccn_knn_grid, same result bit for bit) when the source cloud is large (use_grid None) or forced."""
     pos1, pos2, batch1 = _f32(pos1), _f32(pos2), _i64(batch1)
-    n1 = pos1.shape[0]
+    n1, n2 = pos1.shape[0], pos2.shape[0]
     idx = _empty((n1, K), torch.int32, pos1)
     d2 = _empty((n1, K), torch.float32, pos1) if want_d2 else None
     cnt = _empty((n1 + 2,), torch.int32, pos1) if want_cnt else None
+    if use_grid is None:
+        use_grid = float(n1) * float(n2) >= KNN_GRID_MIN_PAIRS
+    if use_grid and batch2 is not None and K <= 4 and n1 > 0:
+        cells = native.grid_num_cells(n2)
+        cell_off = _empty((cells + 1,), torch.int32, pos1)
+        slot = _empty((max(n2, 1),), torch.int32, pos1)
+        sorted_ = _empty((max(n2, 1), 4), torch.float32, pos1)
+        scratch = _empty((16 + n1,), torch.int32, pos1)
+        call("ccn_knn_grid", pos1, batch1, n1, pos2, _i64(batch2), n2, sptr2.dev, K, int(zero_fill), 0.0, cells, cell_off, slot,
+             sorted_, scratch, idx, d2 if want_d2 else 0, cnt if want_cnt else 0)
+        return (idx, d2, cnt) if want_cnt else (idx, d2)
     call("ccn_knn_exact", pos1, batch1, n1, pos2, sptr2.dev, K, int(zero_fill), idx, d2 if want_d2 else 0,
          cnt if want_cnt else 0)
     if want_cnt:

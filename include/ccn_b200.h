@@ -147,6 +147,15 @@ int ccn_frnn_knn(const float* pos1, const int64_t* batch1, int64_t n1, const flo
                  int32_t* idx_out, float* d2_out, int32_t* cnt_out, ccn_stream_t stream);
 int ccn_knn_exact(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const int32_t* sample_ptr2,
                   int32_t K, int32_t zero_fill, int32_t* idx_out, float* d2_out, int32_t* cnt_out, ccn_stream_t stream);
+/* ccn_knn_exact for K <= 4 through a hashed grid of the sources (csrc/knn_grid.cu): same result bit for bit, O(P1) instead of
+ * O(P1 P2).  cell > 0: cell edge given; <= 0: derived on the device from the sources' bounding box (1.5 sqrt(A / n2)).
+ * scratch: cell_off num_cells+1 ints (num_cells = ccn_grid_num_cells(n2)), slot_scratch n2 ints, sorted_xyzi 4*n2 floats,
+ * open_scratch 16 + n1 ints (queries the grid could not close - sparse regions, clouds smaller than K - are finished by a
+ * brute-force pass; their count never leaves the device). */
+int ccn_knn_grid(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const int64_t* batch2, int64_t n2,
+                 const int32_t* sample_ptr2, int32_t K, int32_t zero_fill, float cell, int64_t num_cells, int32_t* cell_off,
+                 int32_t* slot_scratch, float* sorted_xyzi, int32_t* open_scratch, int32_t* idx_out, float* d2_out,
+                 int32_t* cnt_out, ccn_stream_t stream);
 int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const int32_t* sample_ptr2,
                    float radius, int32_t K, int32_t* idx_out, int32_t* cnt_out, ccn_stream_t stream);
 

@@ -23,6 +23,15 @@ def test_every_declared_symbol_is_exported(lib):
     assert len(native.SIGNATURES) >= 30
     for name in native.SIGNATURES:
         assert hasattr(lib, name), name
+    # entry points whose return type is not int / int64_t (the signature parser of native.py skips them): every `ccn_*(` the
+    # header declares must resolve in the library
+    hdr = open(os.path.join(ROOT, "include", "ccn_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(ccn_\w+)\s*\(", hdr)) - {"ccn_draw_fn"}
+    assert {"ccn_forward_run", "ccn_exec_create", "ccn_exec_destroy", "ccn_exec_topology_flags", "ccn_sgcnn_fused",
+            "ccn_pointconv_fused", "ccn_exec_profile", "ccn_exec_host_stats"} <= declared
+    for name in declared:
+        assert hasattr(lib, name), name
     assert lib.ccn_version() >= 1
     assert native.grid_num_cells(1000) == 2048
     assert native.kernel_launches() == 0 or native.kernel_launches() > 0

@@ -320,3 +320,34 @@ def test_dense_sgcnn_aggregations_match_oracle(aggr, precision):
         N.set_precision("fp32")
     assert got.shape == want.shape
     assert rel_err(got.cpu(), want) <= (1e-4 if precision == "fp32" else 3e-4), aggr
+
+
+@pytest.mark.parametrize("K", [1, 3, 4])
+def test_knn_grid_equals_brute_force(K):
+    """ccn_knn_grid (hashed grid + shells + brute-force pass for the open queries) against ccn_knn_exact and the oracle's
+    knn_points: identical indices and distances - surface-like clouds, duplicates, clouds smaller than K (zero fill),
+    queries far outside the sources, ragged batches."""
+    from curvecloudnet_b200 import ops
+    from oracle import tp_ops as tp
+    gen = torch.Generator().manual_seed(K)
+    for trial in range(4):
+        lens2 = [3000, 2, 1500][:1 + trial % 3] if trial else [5000]
+        lens1 = [int(l * 1.7) + 5 for l in lens2]
+        p2 = torch.cat([torch.rand(l, 3, generator=gen) * torch.tensor([6.0, 6.0, 0.3]) for l in lens2])
+        p1 = torch.cat([torch.rand(l, 3, generator=gen) * torch.tensor([9.0, 6.0, 0.3]) - 1.0 for l in lens1])
+        if trial == 1:
+            p2[100:200] = p2[0:100]                       # duplicates: ties by lowest index
+            p2 = (p2 * 16).round() / 16
+        b2 = torch.repeat_interleave(torch.arange(len(lens2)), torch.tensor(lens2))
+        b1 = torch.repeat_interleave(torch.arange(len(lens1)), torch.tensor(lens1))
+        s2 = ops.sample_ptr(b2.cuda())
+        a = ops.knn_exact(p1.cuda(), b1.cuda(), p2.cuda(), s2, K, use_grid=False, want_cnt=True)
+        g = ops.knn_exact(p1.cuda(), b1.cuda(), p2.cuda(), s2, K, batch2=b2.cuda(), use_grid=True, want_cnt=True)
+        assert torch.equal(a[0], g[0]) and torch.equal(a[1], g[1]) and torch.equal(a[2][:p1.shape[0]], g[2][:p1.shape[0]]), trial
+        # the oracle, cloud by cloud (global indices, zero fill -> first point of the cloud)
+        off1 = off2 = 0
+        for l1, l2 in zip(lens1, lens2):
+            dd, ii = tp.knn_points(p1[off1:off1 + l1][None], p2[off2:off2 + l2][None], torch.tensor([l1]), torch.tensor([l2]), K)
+            assert torch.equal(g[0][off1:off1 + l1].cpu().long(), ii[0] + off2), trial
+            off1 += l1
+            off2 += l2
