@@ -48,7 +48,8 @@ constexpr int kMaxStages = 6;
 constexpr int kMaxWidth = 256;                // widest activation kept resident / widest layer output
 constexpr int kTable = kRows * 32;            // floats of one transposition table: 128 rows x 32 columns, column XOR (row & 31)
 
-enum { FORM_DENSE = 0, FORM_PAIR = 1, FORM_POINT = 2 };
+enum { FORM_DENSE = 0, FORM_PAIR = 1, FORM_POINT = 2, FORM_ROWS = 3 };   // FORM_ROWS: per-point MLP chain, A rows = input planes
+constexpr int kAggNone = 100;                 // FORM_ROWS: no aggregation, the last layer's rows are the result
 
 struct ChainLayerDev {
     int K, N, w_row, act;
@@ -78,6 +79,12 @@ struct ChainParams {
     int64_t ldh;
     const float *wp, *bias0, *pos_src, *pos_dst;   // (3, c1), (c1), (n_src, 3), (nq, 3)
     float radius;                  // > 0: relative positions divided by it
+    // FORM_ROWS: the chain's input activations [A_0 | A_1 | ...] as up to four split-bf16 planes tensors (M rows; segment s
+    // has seg_k[s] columns, row stride seg_ld[s] with zero pad columns, and occupies the 64-column chunks from seg_c0[s] on)
+    const __nv_bfloat16* seg_p[4];
+    int64_t seg_ld[4], seg_ps[4];
+    int seg_k[4], seg_c0[4], nsegs;
+    int M;
     // aggregation
     int agg, msg_layer;            // CCN_AGG_*; layer whose output is the message (attention modes), else -1
     float* out;
@@ -195,7 +202,7 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                 for (int l = 0; l < p.L; ++l) {
                     const int N = p.ly[l].N, nk = p.ly[l].K >> 6, wrow = p.ly[l].w_row;
                     for (int n0 = 0; n0 < N; n0 += 128) {
-                        const int mma_n = min(128, N - n0);
+                        const int mma_n = (min(128, N - n0) + 63) & ~63;     // whole 64-row boxes (rows past the matrix: zeros)
                         for (int kc = 0; kc < nk; ++kc, ++cnt) {
                             const int s = cnt % stages;
                             mbar_wait(wempty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
@@ -222,7 +229,7 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                     tc_fence_after();
                     const uint32_t acc = tmem_base + ((att_mode && l == p.msg_layer) ? 0u : chain_col);
                     for (int n0 = 0; n0 < N; n0 += 128) {
-                        const int mma_n = min(128, N - n0);
+                        const int mma_n = (min(128, N - n0) + 15) & ~15;
                         // instruction descriptor: D=f32, A=B=bf16, K-major both, N>>3 at bit 17, M>>4 at bit 24
                         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(mma_n >> 3) << 17) |
                                                ((uint32_t)(kRows >> 4) << 24);
@@ -266,10 +273,12 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                 const int q0 = t * p.gpt, nseg = max(0, min(p.gpt, p.n - q0));
                 return make_int4(q0, nseg, 0, nseg * p.G);
             }
+            if (FORM == FORM_ROWS) return make_int4(t * kRows, 0, 0, max(0, min(kRows, p.M - t * kRows)));
             return t < p.n_tiles ? __ldg(p.tiles + t) : make_int4(0, 0, 0, 0);
         };
         auto fetch_rows = [&](const int4& h) {
             nri = -1; nrj = -1;
+            if (FORM == FORM_ROWS) return;
             if (wt < min(h.w, kRows)) {
                 if (FORM == FORM_DENSE) {
                     const int sg = wt / p.G, g = wt - sg * p.G;
@@ -302,8 +311,39 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
             workers_sync();
             hdr = fetch_hdr(t + gridDim.x);                         // next tile's header: in flight during the formation
 
+            if (FORM == FORM_ROWS) {
+                // per-point MLP chain: the input planes ARE the A operand - 16-byte pieces copied into the swizzled tile
+                for (int sgm = 0; sgm < p.nsegs; ++sgm) {
+                    const int nchunks = (p.seg_k[sgm] + 63) >> 6, pieces = nchunks * 8, have = (int)(p.seg_ld[sgm] >> 3);
+                    const __nv_bfloat16* sp = p.seg_p[sgm];
+                    for (int base = wt; base < kRows * pieces; base += kWorkers * 4) {
+                        uint4 hv[4], lv[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int item = base + u * kWorkers;
+                            const int row = item / pieces, g8 = item - row * pieces;
+                            hv[u] = make_uint4(0, 0, 0, 0); lv[u] = hv[u];
+                            if (item < kRows * pieces && row < nrows && g8 < have) {      // pad columns of the planes are zero
+                                const __nv_bfloat16* src = sp + (int64_t)(q0 + row) * p.seg_ld[sgm] + 8 * g8;
+                                hv[u] = __ldg(reinterpret_cast<const uint4*>(src));
+                                if (P == 2) lv[u] = __ldg(reinterpret_cast<const uint4*>(src + p.seg_ps[sgm]));
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int item = base + u * kWorkers;
+                            if (item >= kRows * pieces) break;
+                            const int row = item / pieces, g8 = item - row * pieces;
+                            const uint32_t a = res0 + (uint32_t)((p.seg_c0[sgm] + (g8 >> 3)) * P) * kChunkBytes + row * 128 +
+                                               (((g8 & 7) ^ (row & 7)) << 4);
+                            st_shared_v4(a, hv[u].x, hv[u].y, hv[u].z, hv[u].w);
+                            if (P == 2) st_shared_v4(a + kChunkBytes, lv[u].x, lv[u].y, lv[u].z, lv[u].w);
+                        }
+                    }
+                }
+            }
             // ---- layer 1 (decomposed): rows formed straight into the A tile, kU items (row, 8 channels) per thread in flight
-            for (int base = wt; base < kRows * g8n; base += kWorkers * kU) {
+            for (int base = wt; FORM != FORM_ROWS && base < kRows * g8n; base += kWorkers * kU) {
                 float4 va[kU], vb[kU], vc[kU], vd[kU];
                 int rowv[kU], g8v[kU], iv[kU], jv[kU];
 #pragma unroll
@@ -397,6 +437,51 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     __syncwarp();
                     if (lane == 0) mbar_arrive(a_ready);
+                    continue;
+                }
+                if (FORM == FORM_ROWS) {
+                    // ---- per-point chain: the last layer's rows are the result (fp32 rows and / or activation planes)
+                    const int64_t orow = (int64_t)q0 + myrow;
+                    const int ncols = p.planes ? (int)p.kpad : N;                    // plane rows are written to their padded width (zeros)
+                    for (int c0 = 32 * half; c0 < ncols; c0 += 64) {
+                        uint32_t v[32];
+                        tmem_ld32(tacc + (uint32_t)c0, v);
+                        if (myrow >= nrows) continue;
+                        float y[32];
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) y[e] = act_apply(__uint_as_float(v[e]) + bias_s[l][c0 + e], act, slope);
+                        if (p.out) {
+                            float* yrow = p.out + orow * p.ldo + c0;
+                            if (c0 + 32 <= N && (p.ldo & 3) == 0) {
+#pragma unroll
+                                for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(yrow + e) = make_float4(y[e], y[e + 1], y[e + 2], y[e + 3]);
+                            } else {
+#pragma unroll
+                                for (int e = 0; e < 32; ++e)
+                                    if (c0 + e < N) yrow[e] = y[e];
+                            }
+                        }
+                        if (p.planes) {
+                            __nv_bfloat16* hrow = p.planes + orow * p.kpad + c0;
+#pragma unroll
+                            for (int e = 0; e < 32; e += 8) {
+                                if (c0 + e >= (int)p.kpad) break;                    // kpad % 16 == 0: whole 8-column pieces
+                                uint32_t h[4], lo[4];
+#pragma unroll
+                                for (int k2 = 0; k2 < 4; ++k2) {
+                                    const __nv_bfloat162 hv2 = __floats2bfloat162_rn(y[e + 2 * k2], y[e + 2 * k2 + 1]);
+                                    h[k2] = *reinterpret_cast<const uint32_t*>(&hv2);
+                                    const float2 f = __bfloat1622float2(hv2);
+                                    const __nv_bfloat162 lv2 = __floats2bfloat162_rn(y[e + 2 * k2] - f.x, y[e + 2 * k2 + 1] - f.y);
+                                    lo[k2] = *reinterpret_cast<const uint32_t*>(&lv2);
+                                }
+                                *reinterpret_cast<uint4*>(hrow + e) = make_uint4(h[0], h[1], h[2], h[3]);
+                                if (p.npl == 2) *reinterpret_cast<uint4*>(hrow + p.pstride + e) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                            }
+                        }
+                    }
+                    tc_fence_before();
+                    workers_sync();               // the tile (shared row tables, TMEM) is free for the next one
                     continue;
                 }
                 // ---- last layer: aggregate every segment of the tile in edge order.  Per pass two 128 x 32 tables: the two
@@ -777,7 +862,7 @@ constexpr int kSmemLimit = 227 * 1024;
 constexpr int kStaticSmem = 14 * 1024;          // bias / Wp / row tables / barriers (ptxas reports ~12.8 KB)
 constexpr int kHalfSm = 113 * 1024;             // two CTAs per SM: 228 KB / 2 minus the per-CTA reservation
 
-int fill_chain(ChainParams& p, const ccn_chain_t* ch, int c1, bool att, int& smem_bytes, int& P) {
+int fill_chain(ChainParams& p, const ccn_chain_t* ch, int c1, bool att, int& smem_bytes, int& P, bool rows_form = false) {
     CCN_REQUIRE(ch && ch->n_layers >= 1 && ch->n_layers <= CCN_CHAIN_MAX_LAYERS && ch->w_hi_tmap);
     CCN_REQUIRE(ch->mode == 1 || (ch->mode == 3 && ch->w_lo_tmap));
     P = ch->mode == 3 ? 2 : 1;
@@ -785,8 +870,10 @@ int fill_chain(ChainParams& p, const ccn_chain_t* ch, int c1, bool att, int& sme
     int width = c1, maxw = c1, maxn = 64;
     CCN_REQUIRE(c1 >= 64 && c1 <= kMaxWidth && (c1 & 63) == 0);
     for (int l = 0; l < p.L; ++l) {
-        CCN_REQUIRE(ch->k[l] == width && ch->n[l] >= 64 && ch->n[l] <= kMaxWidth && (ch->n[l] & 63) == 0);
-        CCN_REQUIRE(ch->act[l] >= 0 && ch->act[l] <= 2 && ch->w_row[l] >= 0);
+        // the LAST layer may have any width (its rows end the stacked weight matrix: the TMA boxes past them arrive as zeros)
+        const bool last_any = rows_form && l + 1 == p.L;
+        CCN_REQUIRE(ch->k[l] == width && ch->n[l] >= (last_any ? 1 : 64) && ch->n[l] <= kMaxWidth && (last_any || (ch->n[l] & 63) == 0));
+        CCN_REQUIRE(ch->act[l] >= 0 && ch->act[l] <= 2 && ch->w_row[l] >= 0 && (ch->w_row[l] & 63) == 0);
         p.ly[l].K = ch->k[l]; p.ly[l].N = ch->n[l]; p.ly[l].w_row = ch->w_row[l]; p.ly[l].act = ch->act[l];
         p.ly[l].slope = ch->slope[l]; p.ly[l].bias = ch->bias[l];
         width = ch->n[l];
@@ -800,7 +887,7 @@ int fill_chain(ChainParams& p, const ccn_chain_t* ch, int c1, bool att, int& sme
         p.res_chunks = (table_bytes + P * kChunkBytes - 1) / (P * kChunkBytes);
         res_bytes = p.res_chunks * P * kChunkBytes;
     }
-    p.w_plane_bytes = (maxn < 128 ? maxn : 128) * 128;
+    p.w_plane_bytes = (maxn < 128 ? ((maxn + 63) & ~63) : 128) * 128;
     const int stage = P * p.w_plane_bytes;
     int stages = (kSmemLimit - kStaticSmem - 1024 - res_bytes) / stage;
     if (stages > kMaxStages) stages = kMaxStages;
@@ -941,4 +1028,47 @@ extern "C" int ccn_pointconv_fused(const float* H, int64_t ldh, const float* wp,
     CCN_CHECK_LAUNCH();
     if (pair) return P == 2 ? launch_chain<2, FORM_PAIR>(chain_host, p, smem, s) : launch_chain<1, FORM_PAIR>(chain_host, p, smem, s);
     return P == 2 ? launch_chain<2, FORM_POINT>(chain_host, p, smem, s) : launch_chain<1, FORM_POINT>(chain_host, p, smem, s);
+}
+
+// Per-point MLP chain: Y = layer_n(... layer_1(A)) for 2+ consecutive Linear (+ folded BatchNorm + activation) layers of a shared
+// MLP (torch_geometric.nn.MLP, reference src/models/base.py:32, mlp.py:16-22, skip_connect.py:12-15) in ONE launch: the
+// 128-row activation tile stays in shared memory between the layers (edge_chain_kernel, FORM_ROWS).  A: the input activations
+// as split-bf16 planes (k = chain->k[0], a multiple of 64, <= 256); every layer width but the last a multiple of 64, all <= 256.
+// Same MMA / bias / activation order as consecutive ccn_linear_planes launches: bit-identical to them.
+extern "C" int ccn_mlp_chain(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, const void* a1, int64_t ld1, int64_t ps1,
+                             int32_t k1, const void* a2, int64_t ld2, int64_t ps2, int32_t k2, const void* a3, int64_t ld3,
+                             int64_t ps3, int32_t k3, int64_t M, const ccn_chain_t* chain_host, float* Y, int64_t ldy,
+                             void* y_planes, int64_t yp_ld, int64_t yp_plane_stride, ccn_stream_t stream) {
+    const void* ap[4] = {a0, a1, a2, a3};
+    const int64_t ald[4] = {ld0, ld1, ld2, ld3}, aps[4] = {ps0, ps1, ps2, ps3};
+    const int32_t ak[4] = {k0, k1, k2, k3};
+    CCN_REQUIRE(a0 && k0 > 0 && M >= 0 && M < 0x7fffffff && (Y || y_planes));
+    ChainParams p = {};
+    int c1 = 0;
+    for (int i = 0; i < 4; ++i) {
+        if (ak[i] <= 0) break;
+        CCN_REQUIRE(ap[i] && ald[i] >= ((ak[i] + 7) & ~7) && (ald[i] & 7) == 0 && (reinterpret_cast<uintptr_t>(ap[i]) & 15) == 0);
+        p.seg_p[i] = (const __nv_bfloat16*)ap[i]; p.seg_ld[i] = ald[i]; p.seg_ps[i] = aps[i]; p.seg_k[i] = ak[i];
+        p.seg_c0[i] = c1 >> 6;
+        c1 += (ak[i] + 63) & ~63;
+        p.nsegs = i + 1;
+    }
+    int smem = 0, P = 1;
+    const int rc = fill_chain(p, chain_host, c1, false, smem, P, true);
+    if (rc != CCN_OK) return rc;
+    const int nout = p.ly[p.L - 1].N;
+    for (int i = 0; i < p.nsegs; ++i) CCN_REQUIRE(P == 1 || (aps[i] & 7) == 0);
+    CCN_REQUIRE(!Y || ldy >= nout);
+    CCN_REQUIRE(!y_planes || (yp_ld == ((nout + 15) & ~15) && (reinterpret_cast<uintptr_t>(y_planes) & 15) == 0 &&
+                              (P == 1 || (yp_plane_stride & 7) == 0)));
+    if (M == 0) return CCN_OK;
+    p.c1 = c1; p.act0 = CCN_ACT_NONE; p.slope0 = 0.f;
+    p.M = (int)M;
+    p.n_tiles = (int)((M + kRows - 1) / kRows);
+    p.agg = kAggNone; p.msg_layer = -1;
+    p.out = Y; p.ldo = ldy; p.planes = (__nv_bfloat16*)y_planes;
+    p.kpad = y_planes ? yp_ld : 0;                         // row stride = columns written per plane row (pad columns: zeros)
+    p.pstride = yp_plane_stride; p.npl = P;
+    cudaStream_t s = (cudaStream_t)stream;
+    return P == 2 ? launch_chain<2, FORM_ROWS>(chain_host, p, smem, s) : launch_chain<1, FORM_ROWS>(chain_host, p, smem, s);
 }

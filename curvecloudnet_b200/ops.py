@@ -877,10 +877,22 @@ class ChainWeights:
     row-wise into ONE split-bf16 matrix (columns zero padded to the widest K), one TMA descriptor per plane
     (64 x 64 boxes) and the host-side ccn_chain_t.  Weight preparation, once per weight version."""
 
-    def __init__(self, layers, n_planes: int):
-        """layers: [(w (N, K) fp32 folded, bias (N) or None, act, slope)]."""
+    def __init__(self, layers, n_planes: int, first_seg_widths=None):
+        """layers: [(w (N, K) fp32 folded, bias (N) or None, act, slope)].  first_seg_widths (ccn_mlp_chain): the first
+        layer's input is a concatenation of blocks of these widths; every block's weight columns start at a multiple of 64."""
         import ctypes
         assert 1 <= len(layers) <= CHAIN_MAX_LAYERS
+        if first_seg_widths is not None:
+            w0 = layers[0][0]
+            assert sum(first_seg_widths) == w0.shape[1]
+            tot = sum((kw + 63) // 64 * 64 for kw in first_seg_widths)
+            wide0 = torch.zeros((w0.shape[0], tot), dtype=torch.float32, device=w0.device)
+            c0 = off = 0
+            for kw in first_seg_widths:
+                wide0[:, off:off + kw] = w0[:, c0:c0 + kw]
+                c0 += kw
+                off += (kw + 63) // 64 * 64
+            layers = [(wide0,) + tuple(layers[0][1:])] + list(layers[1:])
         kmax = max(w.shape[1] for w, _, _, _ in layers)
         rows = sum(w.shape[0] for w, _, _, _ in layers)
         dev = layers[0][0].device
@@ -988,3 +1000,32 @@ def pointconv_fused(edges: EdgeCSR, chain: ChainWeights, agg: str, msg_layer: in
     if pl is not None:
         cache.put_planes(out, pl)
     return out
+
+
+# Per-point MLP chains (ccn_mlp_chain): 2+ consecutive Linear layers of a shared MLP in one launch.  "auto": where measured
+# faster than the per-layer launches (mlp_chain_profitable); True / False force it (bit-identical results either way).
+CHAIN_MLP_LAYERS = "auto"
+
+
+def mlp_chain_supported(seg_widths, dims) -> bool:
+    """seg_widths: K-blocks of the chain's input; dims: output widths of its layers."""
+    k0 = sum((kw + 63) // 64 * 64 for kw in seg_widths)
+    return (2 <= len(dims) <= CHAIN_MAX_LAYERS and 1 <= len(seg_widths) <= 4 and 64 <= k0 <= CHAIN_MAX_WIDTH and
+            all(d % 64 == 0 and 64 <= d <= CHAIN_MAX_WIDTH for d in dims[:-1]) and 1 <= dims[-1] <= CHAIN_MAX_WIDTH)
+
+
+def mlp_chain(A, chain: ChainWeights, out: str = "f32"):
+    """A: Planes or PlanesCat (<= 4 blocks); -> fp32 (M, N) | Planes | (fp32, Planes) like linear_planes."""
+    segs = A.segs if isinstance(A, PlanesCat) else (A,)
+    M = A.shape[0]
+    npl = segs[0].n_planes
+    dev = segs[0].buf
+    Y = _empty((M, chain.n_out), torch.float32, dev) if out != "planes" else None
+    Yp = alloc_planes(M, chain.n_out, npl, dev) if out != "f32" else None
+    a = []
+    for sg in segs:
+        a += [sg.buf, sg.kpad, sg.buf.stride(0), sg.k]
+    a += [0, 0, 0, 0] * (4 - len(segs))
+    call("ccn_mlp_chain", *a, M, chain.addr, Y if Y is not None else 0, chain.n_out, Yp.buf if Yp is not None else 0,
+         Yp.kpad if Yp is not None else 0, Yp.buf.stride(0) if Yp is not None else 0)
+    return Y if out == "f32" else Yp if out == "planes" else (Y, Yp)

@@ -445,6 +445,17 @@ int ccn_sgcnn_fused(const float* PQ, int64_t ldpq, const int32_t* idx, int64_t n
  * null) or act0(PQ[ecol][0:c1] + PQ[erow][c1:2c1]) (PQ given); chain; agg = CCN_AGG_*; for WSUM / ATTEND the chain is
  * local_nn's layers followed by attend_nn's, msg_layer = index of the chain layer whose output is the message.
  * tile_scratch: 4 * (E / (129 - max_degree) + 1) int32, 16-byte aligned (tile table written by a pre-pass). */
+/* 2+ consecutive layers of a shared per-point MLP (torch_geometric.nn.MLP: Linear + folded BatchNorm + activation; base.py:32,
+ * mlp.py:16-22, skip_connect.py:12-15) in ONE launch, the 128-row activation tile resident in shared memory between the
+ * layers.  Input [A_0 | A_1 | A_2 | A_3] as in ccn_linear_planes (split-bf16 planes per K-segment; k_i = 0 ends the list);
+ * every segment occupies whole 64-column chunks, sum of ceil64(k_i) <= 256; chain: the layers - the first layer's weight
+ * columns laid out per padded segment (chain->k[0] = that sum), every width but the last a multiple of 64, all <= 256;
+ * writes fp32 Y (ldy) and / or output planes (row stride yp_ld = last width rounded up to 16).  Bit-identical to
+ * consecutive ccn_linear_planes launches. */
+int ccn_mlp_chain(const void* a0, int64_t ld0, int64_t ps0, int32_t k0, const void* a1, int64_t ld1, int64_t ps1, int32_t k1,
+                  const void* a2, int64_t ld2, int64_t ps2, int32_t k2, const void* a3, int64_t ld3, int64_t ps3, int32_t k3,
+                  int64_t M, const ccn_chain_t* chain_host, float* Y, int64_t ldy, void* y_planes, int64_t yp_ld,
+                  int64_t yp_plane_stride, ccn_stream_t stream);
 int ccn_pointconv_fused(const float* H, int64_t ldh, const float* wp, const float* bias0, const float* pos_src,
                         const float* pos_dst, const float* PQ, int64_t ldpq, const int32_t* row_ptr, const int32_t* erow,
                         const int32_t* ecol, int64_t nq, int64_t E, int32_t max_degree, int32_t c1, float radius,

@@ -212,3 +212,35 @@ def test_sparse_sgcnn_fused(precision, mode):
         assert torch.equal(got, want), "fused and unfused chains differ by %.3e" % rel_err(got.cpu(), want.cpu())
     finally:
         nn.set_precision("fp32")
+
+
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("M,segs,dims", [(5000, [64], [64, 64, 17]), (700, [256], [128, 128, 64]), (3001, [64, 64], [128, 128]),
+                                          (129, [32, 128], [128, 64]), (40000, [64, 32, 3], [128, 128]), (1, [128, 128], [256, 128])])
+def test_mlp_chain_equals_consecutive_linears(precision, M, segs, dims):
+    """ccn_mlp_chain (2+ layers of a shared per-point MLP in one launch, activation tile resident between the layers) against
+    consecutive ccn_linear_planes launches: bit-identical fp32 rows and planes; segmented inputs, last width 17, M = 1."""
+    from curvecloudnet_b200 import nn, ops
+    from curvecloudnet_b200.nn import PreparedLinear
+    gen = torch.Generator().manual_seed(M)
+    parts = [torch.randn(M, k, generator=gen).to(DEV) for k in segs]
+    layers = _mlp_layers([sum(segs)] + dims, [2] * (len(dims) - 1) + [0], seed=31)
+    try:
+        npl = _set(precision)
+        A = ops.PlanesCat([ops.pack_planes([t], npl) for t in parts]) if len(parts) > 1 else ops.pack_planes(parts, npl)
+        chain = ops.ChainWeights(layers, npl, first_seg_widths=segs)
+        y, yp = ops.mlp_chain(A, chain, "both")
+        lins = [PreparedLinear(w, b, a, s) for w, b, a, s in layers]
+        h = A
+        for i, lin in enumerate(lins):
+            if i == 0 and len(parts) > 1:
+                h = ops.linear_planes(h, lin.tc(tuple(segs)), lin.b, lin.act, lin.slope, "planes")
+            else:
+                h = lin(h, "both" if i == len(lins) - 1 else "planes")
+        want, wantp = h
+        assert torch.equal(y, want), "chain differs from the per-layer launches by %.3e" % rel_err(y.cpu(), want.cpu())
+        assert torch.equal(yp.buf, wantp.buf)
+        only = ops.mlp_chain(A, chain, "f32")
+        assert torch.equal(only, want)
+    finally:
+        nn.set_precision("fp32")

@@ -117,3 +117,29 @@ for name, nq, n_src, avg, mx, dims, att_h, mode in [("sa-geo", 17809, 32568, 5.2
     tf, tu = timed(fused), timed(unfused)
     print("%-10s E=%6d nq=%5d dims=%-22s fused %7.1f us (%6.1f TF/s alg)   unfused %7.1f us   x%.2f"
           % (name, edges.n_edges, nq, alld, tf, flops / tf / 1e6, tu, tu / tf))
+
+
+print("per-point MLP chains (ccn_mlp_chain) against per-layer ccn_linear_planes launches")
+for M, segs, dims in [(32568, [64], [64, 64, 17]), (17809, [256], [128, 128, 64]), (17809, [64, 64], [128, 128]),
+                      (32568, [32, 128], [128, 64]), (32568, [64, 32, 3], [128, 128]), (17809, [64, 64], [64, 64]),
+                      (5695, [128, 128], [256, 128])]:
+    gen = torch.Generator().manual_seed(M)
+    parts = [torch.randn(M, k, generator=gen).cuda() for k in segs]
+    layers = layers_of([sum(segs)] + dims, [2] * (len(dims) - 1) + [0])
+    A = ops.PlanesCat([ops.pack_planes([t], npl) for t in parts]) if len(parts) > 1 else ops.pack_planes(parts, npl)
+    chain = ops.ChainWeights(layers, npl, first_seg_widths=segs)
+    lins = [PreparedLinear(w, b, a, s) for w, b, a, s in layers]
+    tws = [lins[0].tc(tuple(segs) if len(segs) > 1 else None)] + [l.tc() for l in lins[1:]]
+
+    def fused():
+        return ops.mlp_chain(A, chain, "both")
+
+    def unfused():
+        h = A
+        for i, (lin, tw) in enumerate(zip(lins, tws)):
+            h = ops.linear_planes(h, tw, lin.b, lin.act, lin.slope, "both" if i == len(lins) - 1 else "planes")
+        return h
+
+    assert torch.equal(fused()[0], unfused()[0])
+    tf, tu = timed(fused), timed(unfused)
+    print("mlp M=%6d in=%-14s dims=%-16s chain %6.1f us   per-layer %6.1f us   x%.2f" % (M, segs, dims, tf, tu, tu / tf))
