@@ -53,6 +53,7 @@ struct Linear {                // one prepared Linear use-site (a K-segmentation
     float slope;
     const float* bias;
     const void *map_hi[4], *map_lo[4];   // host tensor maps for box_n = 32, 64, 128, 256 (null: not a candidate)
+    int chain;                           // >= 0: this layer and the rest of its MLP run as that ccn_mlp_chain entry
 };
 
 struct Conv {                  // one curve-convolution layer
@@ -304,6 +305,33 @@ int segs_of(Exec& ex, Feat* const* parts, int np, Seg* segs) {   // nn.cat_featu
     return CCN_OK;
 }
 
+// ops.mlp_chain: layers lin_ids[0..nl) of an MLP as ONE launch.  y_ext: write the fp32 result there (the logits) instead of
+// allocating it.  Accounting as linear_planes: the weights of every layer, the input rows, the output rows.
+int mlp_chain(Exec& ex, const Chain& ch, const int64_t* lin_ids, int nl, const Seg* segs, int nseg, int64_t M, int out_kind,
+              Feat** y_out, float* y_ext = nullptr, int64_t ld_ext = 0) {
+    Feat* Y = nullptr;
+    Planes Yp;
+    if (out_kind != 1 && !y_ext) Y = ex.new_feat(M, ch.n_out);
+    if (out_kind != 0) Yp = ex.alloc_planes(M, ch.n_out);
+    if (y_out) *y_out = Y;
+    if (Y && out_kind == 2) Y->pl = Yp;
+    if (ex.oom) return CCN_OK;
+    Seg s[4] = {};
+    for (int i = 0; i < nseg; ++i) s[i] = segs[i];
+    double flops = 0, bytes = 0;
+    for (int i = 0; i < nl; ++i) {
+        const Linear& L = ex.lins[lin_ids[i]];
+        flops += 2.0 * M * L.n * L.k_true;
+        bytes += (double)L.n * L.k_true * 2 * ex.npl;
+        if (i == 0) bytes += 4.0 * M * L.k_true;
+        if (i == nl - 1) bytes += 4.0 * M * L.n;
+    }
+    ProfScope ps(ex, FAM_LINEAR, flops, bytes);
+    return ccn_mlp_chain(s[0].buf, s[0].kpad, s[0].pstride, s[0].k, s[1].buf, s[1].kpad, s[1].pstride, s[1].k, s[2].buf, s[2].kpad,
+                         s[2].pstride, s[2].k, s[3].buf, s[3].kpad, s[3].pstride, s[3].k, M, ch.desc, y_ext ? y_ext : (Y ? Y->f : nullptr),
+                         y_ext ? ld_ext : ch.n_out, Yp.buf, Yp.kpad, Yp.pstride, (ccn_stream_t)ex.stream);
+}
+
 // nn.mlp_to_features / MLP.forward_from over a concatenation: hidden layers write planes, the last writes `last_kind`
 int run_mlp(Exec& ex, const int64_t* lin_ids, int nl, Feat* const* parts, int np, int last_kind, Feat** out) {
     Seg segs[4];
@@ -314,6 +342,7 @@ int run_mlp(Exec& ex, const int64_t* lin_ids, int nl, Feat* const* parts, int np
     for (int i = 0; i < nl; ++i) {
         const Linear& L = ex.lins[lin_ids[i]];
         const bool last = i == nl - 1;
+        if (L.chain >= 0) return mlp_chain(ex, ex.chains[L.chain], lin_ids + i, nl - i, segs, nseg, M, last_kind, out);
         Feat* y = nullptr;
         Planes yp;
         EX_CALL(linear_planes(ex, L, segs, nseg, M, last ? last_kind : 1, &y, &yp, (i == 0 ? 1 : 0) | (last ? 2 : 0)));
@@ -745,7 +774,7 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
     auto I = [&]() -> int64_t { return ci < n_i ? iplan[ci++] : 0; };
     auto F = [&]() -> double { return cf < n_f ? fplan[cf++] : 0.0; };
     const int64_t magic = I();
-    if (magic != 0xCC9E0002) { delete h; return CCN_EINVAL; }
+    if (magic != 0xCC9E0003) { delete h; return CCN_EINVAL; }
     ex.mode = (int)I(); ex.npl = ex.mode == 3 ? 2 : 1;
     ex.in_c = (int)I(); ex.n_out = (int)I();
     const int n_lin = (int)I(), n_conv = (int)I(), n_chain = (int)I(), n_step = (int)I();
@@ -756,6 +785,7 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
         L.bias = (const float*)I();
         for (int b = 0; b < 4; ++b) L.map_hi[b] = (const void*)I();
         for (int b = 0; b < 4; ++b) L.map_lo[b] = (const void*)I();
+        L.chain = (int)I();
         L.slope = (float)F();
         ex.lins.push_back(L);
     }
@@ -1227,6 +1257,12 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
     for (size_t i = 0; i < ex.out_mlp.size(); ++i) {
         const Linear& L = ex.lins[ex.out_mlp[i]];
         const bool last = i + 1 == ex.out_mlp.size();
+        if (L.chain >= 0) {
+            if (ld_logits < ex.chains[L.chain].n_out) return CCN_EINVAL;
+            std::vector<int64_t> ids(ex.out_mlp.begin() + i, ex.out_mlp.end());
+            EX_CALL(mlp_chain(ex, ex.chains[L.chain], ids.data(), (int)ids.size(), segs, nseg, M, 0, nullptr, logits, ld_logits));
+            break;
+        }
         if (!last) {
             Planes yp;
             EX_CALL(linear_planes(ex, L, segs, nseg, M, 1, nullptr, &yp));

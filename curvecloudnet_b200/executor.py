@@ -14,7 +14,7 @@ from . import modules as M
 from . import native, ops
 from .nn import DEFAULT_DRAWS, MLP, n_planes
 
-MAGIC = 0xCC9E0002
+MAGIC = 0xCC9E0003
 ST = {"conv1d-fast-v2": 1, "sa-geo": 2, "mlp": 3, "sgcnn": 4, "skip-connect": 5, "sa": 6, "fp": 7, "fp-geo": 8}
 CCN_EUNSUPPORTED, CCN_ETOPOLOGY, CCN_EVOXEL_RANGE, CCN_ENOMEM = -2, -3, -4, -5
 _DRAW_FN = ctypes.CFUNCTYPE(ctypes.c_int64, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_void_p)
@@ -37,8 +37,9 @@ class _PlanBuilder:
         self.keep = []                          # every python object whose memory the plan points into
 
     # ---- tables
-    def linear(self, lin, widths=None):
-        """Registers one use-site of a PreparedLinear: widths = K-segmentation of its input (None: one block)."""
+    def linear(self, lin, widths=None, chain=-1):
+        """Registers one use-site of a PreparedLinear: widths = K-segmentation of its input (None: one block).
+        chain >= 0: this layer and the ones after it in its MLP run as that ccn_mlp_chain entry."""
         if widths is not None and len(widths) <= 1:
             widths = None
         tw = lin.tc(tuple(widths) if widths is not None else None)
@@ -52,7 +53,7 @@ class _PlanBuilder:
                 hi[slot], lo[slot] = h, l
                 self.keep.append(keep)
         bias = lin.b.data_ptr() if lin.b is not None else 0
-        self.lins += [tw.n, tw.k_true, tw.kpad, lin.act, len(seg)] + (seg + [0] * 4)[:4] + [bias] + hi + lo
+        self.lins += [tw.n, tw.k_true, tw.kpad, lin.act, len(seg)] + (seg + [0] * 4)[:4] + [bias] + hi + lo + [chain]
         self.lin_f.append(float(lin.slope))
         self.keep += [lin, tw]
         self.n_lin += 1
@@ -66,7 +67,7 @@ class _PlanBuilder:
                 h, l, keep = tw.maps(b)
                 hi[slot], lo[slot] = h, l
                 self.keep.append(keep)
-        self.lins += [tw.n, tw.k_true, tw.kpad, act, 1, tw.k_true, 0, 0, 0, bias.data_ptr() if bias is not None else 0] + hi + lo
+        self.lins += [tw.n, tw.k_true, tw.kpad, act, 1, tw.k_true, 0, 0, 0, bias.data_ptr() if bias is not None else 0] + hi + lo + [-1]
         self.lin_f.append(float(slope))
         self.keep += [tw, bias]
         self.n_lin += 1
@@ -83,7 +84,10 @@ class _PlanBuilder:
     def mlp_ids(self, mlp: MLP, widths):
         layers = mlp.layers()
         self.keep.append(layers)
-        return [self.linear(l, widths if i == 0 else None) for i, l in enumerate(layers)]
+        # the same ccn_mlp_chain launches as MLP.forward_from (nn.MLP.chain_for)
+        cw, start = mlp.chain_for(tuple(widths)) if len(layers) >= 2 else (None, 0)
+        return [self.linear(l, widths if i == 0 else None, self.chain(cw) if cw is not None and i == start else -1)
+                for i, l in enumerate(layers)]
 
     # ---- PointNetConv2 block (shared by sa / sa-geo)
     def pointconv(self, conv: M.PointNetConv2, widths):

@@ -194,7 +194,7 @@ class ModelBase(torch.nn.Module):
         if not data.pos.is_cuda:
             raise TypeError("curvecloudnet_b200 runs on CUDA tensors only (there is no CPU path)")
         st = self.__dict__.get("_native")
-        epoch = (self._weights_epoch(), self.precision, ops.FUSED_EDGE_STEPS)
+        epoch = (self._weights_epoch(), self.precision, ops.FUSED_EDGE_STEPS, ops.CHAIN_MLP_LAYERS)
         if st is None or st[0] != epoch:
             try:
                 st = (epoch, X.NativeExecutor(self))

@@ -322,7 +322,40 @@ class MLP(torch.nn.Module):
             if out != "f32" or not torch.is_tensor(x):
                 raise NotImplementedError("one-layer edge MLP on the planes path (no shipped config has one)")
             return x
-        inner = "planes" if _PRECISION["mode"] != "fp32" else "f32"
+        tc = _PRECISION["mode"] != "fp32"
+        inner = "planes" if tc else "f32"
+        if tc and first == 0 and len(layers) >= 2:
+            # per-point MLP: the profitable suffix of its layers as ONE launch (ops.mlp_chain_plan), same bits either way
+            if torch.is_tensor(x):
+                x = ops.pack_planes([x], n_planes())
+            elif x.__class__ is ops.PlanesCat and len(x.segs) == 1:
+                x = x.segs[0]
+            widths = x.widths if x.__class__ is ops.PlanesCat else (x.k,)
+            cw, start = self.chain_for(widths)
+            if cw is not None:
+                for lin in layers[:start]:
+                    x = lin(x, inner)
+                return ops.mlp_chain(x, cw, out)
         for lin in layers[:-1]:
             x = lin(x, inner)
         return layers[-1](x, out)
+
+    def chain_for(self, widths):
+        """(ops.ChainWeights, start layer) of this MLP for an input of K-blocks `widths`, or (None, 0): weight preparation,
+        cached per folded-weight version and precision."""
+        layers = self.layers()
+        npl = n_planes()
+        memo = getattr(self, "_chains", None)
+        if memo is None or memo[0] is not layers:
+            memo = self._chains = (layers, {})
+        key = (tuple(widths), npl, ops.CHAIN_MLP_LAYERS)
+        hit = memo[1].get(key)
+        if hit is None:
+            plan = ops.mlp_chain_plan(layers, widths) if npl else None
+            if plan is None:
+                hit = (None, 0)
+            else:
+                start, segw = plan
+                hit = (ops.ChainWeights([(l.w, l.b, l.act, l.slope) for l in layers[start:]], npl, first_seg_widths=segw), start)
+            memo[1][key] = hit
+        return hit

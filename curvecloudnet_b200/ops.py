@@ -1014,6 +1014,36 @@ def mlp_chain_supported(seg_widths, dims) -> bool:
             all(d % 64 == 0 and 64 <= d <= CHAIN_MAX_WIDTH for d in dims[:-1]) and 1 <= dims[-1] <= CHAIN_MAX_WIDTH)
 
 
+def mlp_chain_profitable(seg_widths, dims) -> bool:
+    """Measured on B200 (tools/bench_fused.py `mlp` lines, profiles/r02p_mlp_chain.txt; bf16x3, launch to launch with a
+    flushed L2): one launch beats the per-layer launches for the 3+-layer chains over a single input block - the out MLP
+    [64] -> [64, 64, 17] at 32.5 k rows 21 us against 32 us, [256] -> [128, 128, 64] at 17.8 k rows 28 against 33 us - and for
+    the narrow two-layer chains ([64, 64] -> [64, 64]: 17 against 19 us).  It loses (0.8x) where a two-layer chain is 128+
+    wide or its input blocks need padding to the 64-column chunks (one CTA per SM, a tile's serial load -> MMA -> epilogue
+    chain is not hidden, and the per-layer kernels already run at the launch floor)."""
+    if CHAIN_MLP_LAYERS != "auto":
+        return bool(CHAIN_MLP_LAYERS)
+    if len(dims) >= 3 and len(seg_widths) == 1:
+        return True
+    k0 = sum(seg_widths)
+    return all(kw % 64 == 0 for kw in seg_widths) and k0 <= 128 and max(dims) <= 64
+
+
+def mlp_chain_plan(layers, seg_widths):
+    """Which suffix of an MLP runs as one ccn_mlp_chain launch: -> (start layer, K-blocks of its input) or None.
+    layers: [PreparedLinear]; seg_widths: K-blocks of the MLP's input.  Either the whole MLP, or everything after its
+    first layer (whose input is too wide / too ragged for a resident tile)."""
+    if CHAIN_MLP_LAYERS is False:
+        return None
+    dims = [l.out_features for l in layers]
+    seg_widths = tuple(int(kw) for kw in seg_widths)
+    if mlp_chain_supported(seg_widths, dims) and mlp_chain_profitable(seg_widths, dims):
+        return 0, seg_widths
+    if len(dims) >= 3 and mlp_chain_supported((dims[0],), dims[1:]) and mlp_chain_profitable((dims[0],), dims[1:]):
+        return 1, (dims[0],)
+    return None
+
+
 def mlp_chain(A, chain: ChainWeights, out: str = "f32"):
     """A: Planes or PlanesCat (<= 4 blocks); -> fp32 (M, N) | Planes | (fp32, Planes) like linear_planes."""
     segs = A.segs if isinstance(A, PlanesCat) else (A,)

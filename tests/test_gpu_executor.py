@@ -96,3 +96,37 @@ def test_fused_edge_step_setting_does_not_change_the_logits(native):
     finally:
         ops.FUSED_EDGE_STEPS = prev
     assert torch.equal(outs["auto"], outs[True]) and torch.equal(outs["auto"], outs[False])
+
+
+@pytest.mark.parametrize("precision", ["bf16x3", "bf16"])
+@pytest.mark.parametrize("native", [True, False])
+def test_mlp_chain_setting_does_not_change_the_logits(native, precision):
+    """ops.CHAIN_MLP_LAYERS: "auto" (ccn_mlp_chain where ops.mlp_chain_profitable says so), True (every per-point MLP the
+    kernel covers), False (one launch per Linear) - bit-identical logits on both executors, and the chain launches happen."""
+    from curvecloudnet_b200 import native as nat, ops
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    data = driving_scan_batch([6], subsample=5000).to("cuda")
+    outs, chained = {}, {}
+    prev, real_call = ops.CHAIN_MLP_LAYERS, ops.call
+    try:
+        for setting in ("auto", True, False):
+            ops.CHAIN_MLP_LAYERS = setting
+            model = randomize_model_(build_model(ModelBase, "nuscenes", precision=precision, native_executor=native), 1234).cuda().eval()
+            count = [0]
+
+            def counting(name, *a):
+                count[0] += name == "ccn_mlp_chain"
+                return real_call(name, *a)
+            ops.call = counting
+            with torch.no_grad():
+                torch.manual_seed(9)
+                outs[setting] = model(data)
+            ops.call = real_call
+            chained[setting] = count[0]
+    finally:
+        ops.CHAIN_MLP_LAYERS, ops.call = prev, real_call
+    assert torch.equal(outs["auto"], outs[True]) and torch.equal(outs["auto"], outs[False])
+    if not native:           # the python executor's launches go through ops.call
+        assert chained[False] == 0 and chained["auto"] >= 2 and chained[True] > chained["auto"]
