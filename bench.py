@@ -672,6 +672,7 @@ def main():
         "e2e": {"value": tot_pts_e2e / (ms_e2e_max * 1e-3), "unit": "points/s", "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e_max / K},
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks,
+        "dependent_launch": bool(native.set_dependent_launch(-1)),      # programmatic dependent launch (CCN_PDL=0: off)
     }
     if world == 1 and args.batch == 1 and not args.no_batched_variant:
         # SURVEY 8(d) config 4 also names "a batched variant B=6 (train batch)": the same scans, six per forward; reported

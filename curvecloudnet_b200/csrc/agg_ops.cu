@@ -18,6 +18,7 @@ __device__ __forceinline__ float apply_act(float y, int act, float slope) {
 
 __global__ void gather_rows_kernel(const float* __restrict__ src, int64_t lds, const int64_t* __restrict__ idx,
                                    int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t i;
@@ -30,6 +31,7 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, int64_t lds, c
 
 __global__ void gather_rows_v4_kernel(const float* __restrict__ src, int64_t lds, const int64_t* __restrict__ idx,
                                       int64_t n, int c4, float* __restrict__ dst, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t i;
@@ -42,6 +44,7 @@ __global__ void gather_rows_v4_kernel(const float* __restrict__ src, int64_t lds
 
 __global__ void gather_i64_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ idx, int64_t n,
                                   int64_t* __restrict__ dst) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i < n) dst[i] = src[idx[i]];
 }
@@ -49,6 +52,7 @@ __global__ void gather_i64_kernel(const int64_t* __restrict__ src, const int64_t
 // CSR from a dense (nq, K) neighbour table whose valid entries lead every row.
 __global__ void dense_to_csr_kernel(const int32_t* __restrict__ idx, const int32_t* __restrict__ row_ptr, int64_t nq,
                                     int K, int32_t* __restrict__ erow, int32_t* __restrict__ ecol) {
+    ccn_pdl_wait();
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t >= nq * K) return;
     int64_t q;
@@ -62,6 +66,7 @@ __global__ void dense_to_csr_kernel(const int32_t* __restrict__ idx, const int32
 }
 
 __global__ void csr_rows_kernel(const int32_t* __restrict__ row_ptr, int64_t nq, int32_t* __restrict__ erow) {
+    ccn_pdl_wait();
     const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (q >= nq) return;
     for (int e = row_ptr[q]; e < row_ptr[q + 1]; ++e) erow[e] = (int32_t)q;
@@ -74,6 +79,7 @@ __global__ void edge_layer1_kernel(const float* __restrict__ H, int64_t ldh, con
                                    const float* __restrict__ pos_dst, const int32_t* __restrict__ erow,
                                    const int32_t* __restrict__ ecol, int64_t E, int c, float inv_norm_is_div,
                                    float radius, int act, float slope, float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int64_t total = E * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t e;
@@ -98,6 +104,7 @@ __global__ void edge_layer1_kernel(const float* __restrict__ H, int64_t ldh, con
 __global__ void seg_aggregate_kernel(const float* __restrict__ msg, int64_t ldm, const float* __restrict__ att,
                                      int64_t lda, const int32_t* __restrict__ row_ptr, int64_t nq, int c, int mode,
                                      float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int64_t total = nq * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t q;
@@ -143,6 +150,7 @@ __global__ void seg_aggregate_kernel(const float* __restrict__ msg, int64_t ldm,
 __global__ void sgcnn_layer1_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ idx,
                                     int64_t n, int K, int c, int act, float slope, float* __restrict__ out,
                                     int64_t ldo) {
+    ccn_pdl_wait();
     const int G = K + 1;
     const int64_t total = n * (int64_t)G * c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -161,6 +169,7 @@ __global__ void sgcnn_layer1_kernel(const float* __restrict__ PQ, int64_t ldpq, 
 __global__ void edge_pair_layer1_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ erow,
                                         const int32_t* __restrict__ ecol, int64_t E, int c, int act, float slope,
                                         float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int64_t total = E * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t e;
@@ -174,6 +183,7 @@ __global__ void edge_pair_layer1_kernel(const float* __restrict__ PQ, int64_t ld
 // max over the K+1 rows of every point, invalid rows count as -100 (dgcnn.py:187-189).
 __global__ void group_max_dense_kernel(const float* __restrict__ feat, int64_t ldf, const int32_t* __restrict__ idx,
                                        int64_t n, int K, int c, float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int G = K + 1;
     const int64_t total = n * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -217,6 +227,7 @@ __device__ __forceinline__ void st_planes4(const float4 y, __nv_bfloat16* o, int
 __global__ void group_max_dense_v4_kernel(const float* __restrict__ feat, int64_t ldf, const int32_t* __restrict__ idx,
                                           int64_t n, int K, int c4, float* __restrict__ out, int64_t ldo,
                                           __nv_bfloat16* __restrict__ planes, int64_t kpad, int64_t pstride, int npl) {
+    ccn_pdl_wait();
     const int G = K + 1;
     const int64_t total = n * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -240,6 +251,7 @@ __global__ void seg_aggregate_v4_kernel(const float* __restrict__ msg, int64_t l
                                         int64_t lda, const int32_t* __restrict__ row_ptr, int64_t nq, int c4, int mode,
                                         float* __restrict__ out, int64_t ldo, __nv_bfloat16* __restrict__ planes,
                                         int64_t kpad, int64_t pstride, int npl) {
+    ccn_pdl_wait();
     const int64_t total = nq * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t q;
@@ -320,6 +332,7 @@ __global__ void seg_aggregate_v4_kernel(const float* __restrict__ msg, int64_t l
 __global__ void interp_blend_kernel(const float* __restrict__ x, int64_t ldx, const int32_t* __restrict__ nbr,
                                     const float* __restrict__ wgt, int from_d2, int64_t n, int knn, int c,
                                     float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t i;
@@ -343,6 +356,7 @@ __global__ void interp_blend_v4_kernel(const float* __restrict__ x, int64_t ldx,
                                        const float* __restrict__ wgt, int from_d2, int64_t n, int knn, int c4,
                                        float* __restrict__ out, int64_t ldo, __nv_bfloat16* __restrict__ planes,
                                        int64_t kpad, int64_t pstride, int npl) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t i;
@@ -371,6 +385,7 @@ __global__ void edge_layer1_v4_kernel(const float* __restrict__ H, int64_t ldh, 
                                       const float* __restrict__ pos_dst, const int32_t* __restrict__ erow,
                                       const int32_t* __restrict__ ecol, int64_t E, int c, float inv_norm_is_div,
                                       float radius, int act, float slope, float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int c4 = c >> 2;
     const int64_t total = E * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -400,6 +415,7 @@ __global__ void edge_layer1_v4_kernel(const float* __restrict__ H, int64_t ldh, 
 __global__ void edge_pair_layer1_v4_kernel(const float* __restrict__ PQ, int64_t ldpq, const int32_t* __restrict__ erow,
                                            const int32_t* __restrict__ ecol, int64_t E, int c, int act, float slope,
                                            float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int c4 = c >> 2;
     const int64_t total = E * (int64_t)c4;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -439,6 +455,7 @@ __global__ void sgcnn_layer1_planes_kernel(const float* __restrict__ PQ, int64_t
                                            int64_t n, int K, int c, int act, float slope,
                                            __nv_bfloat16* __restrict__ planes, int64_t kpad, int64_t plane_stride,
                                            int n_planes) {
+    ccn_pdl_wait();
     const int G = K + 1, cg = c >> 3;
     const int64_t total = n * (int64_t)G * cg;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -465,6 +482,7 @@ __global__ void edge_pair_layer1_planes_kernel(const float* __restrict__ PQ, int
                                                const int32_t* __restrict__ ecol, int64_t E, int c, int act, float slope,
                                                __nv_bfloat16* __restrict__ planes, int64_t kpad, int64_t plane_stride,
                                                int n_planes) {
+    ccn_pdl_wait();
     const int cg = c >> 3;
     const int64_t total = E * (int64_t)cg;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -486,6 +504,7 @@ __global__ void edge_layer1_planes_kernel(const float* __restrict__ H, int64_t l
                                           const int32_t* __restrict__ ecol, int64_t E, int c, float inv_norm_is_div,
                                           float radius, int act, float slope, __nv_bfloat16* __restrict__ planes,
                                           int64_t kpad, int64_t plane_stride, int n_planes) {
+    ccn_pdl_wait();
     const int cg = c >> 3;
     const int64_t total = E * (int64_t)cg;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -531,11 +550,11 @@ extern "C" int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t*
     CCN_REQUIRE(n >= 0 && c > 0 && src && dst && lds >= c && ldd >= c);
     if (n == 0) return CCN_OK;
     if ((c & 3) == 0 && (lds & 3) == 0 && (ldd & 3) == 0 && ccn_al16(src) && ccn_al16(dst)) {
-        gather_rows_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, n, c >> 2, dst, ldd);
+        ccn_launch(gather_rows_v4_kernel, dim3(CCN_ELT_GRID(n * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, src, lds, idx, n, c >> 2, dst, ldd);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    gather_rows_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, n, c, dst, ldd);
+    ccn_launch(gather_rows_kernel, dim3(CCN_ELT_GRID(n * c)), dim3(256), 0, (cudaStream_t)stream, src, lds, idx, n, c, dst, ldd);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -543,7 +562,7 @@ extern "C" int ccn_gather_rows_f32(const float* src, int64_t lds, const int64_t*
 extern "C" int ccn_gather_i64(const int64_t* src, const int64_t* idx, int64_t n, int64_t* dst, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && src && idx && dst);
     if (n == 0) return CCN_OK;
-    gather_i64_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(src, idx, n, dst);
+    ccn_launch(gather_i64_kernel, dim3(ccn_blocks_exact(n, 256)), dim3(256), 0, (cudaStream_t)stream, src, idx, n, dst);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -554,6 +573,7 @@ __global__ void subset_gather_kernel(const float* __restrict__ pos, int64_t ldp,
                                      const int64_t* __restrict__ curve, const int64_t* __restrict__ idx, int64_t n,
                                      float* __restrict__ posq, int64_t* __restrict__ batchq, int64_t* __restrict__ curveq,
                                      __nv_bfloat16* __restrict__ planes, int64_t pstride, int npl) {
+    ccn_pdl_wait();
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t >= n) return;
     const int64_t i = idx[t];
@@ -585,7 +605,7 @@ extern "C" int ccn_subset_gather(const float* pos, int64_t ldp, const int64_t* b
     if (n == 0) return CCN_OK;
     CCN_REQUIRE(pos && batch && idx && posq && batchq && (!curve || curveq));
     CCN_REQUIRE(!pos_planes || (ccn_al16(pos_planes) && (n_planes == 1 || (n_planes == 2 && (plane_stride & 7) == 0))));
-    subset_gather_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(subset_gather_kernel, dim3(ccn_blocks_exact(n, 256)), dim3(256), 0, (cudaStream_t)stream, 
         pos, ldp, batch, curve, idx, n, posq, batchq, curveq, (__nv_bfloat16*)pos_planes, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -595,7 +615,7 @@ extern "C" int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int6
                                 int32_t* ecol, ccn_stream_t stream) {
     CCN_REQUIRE(nq >= 0 && K >= 1 && idx && row_ptr && erow && ecol);
     if (nq == 0) return CCN_OK;
-    dense_to_csr_kernel<<<ccn_blocks_exact(nq * K, 256), 256, 0, (cudaStream_t)stream>>>(idx, row_ptr, nq, K, erow, ecol);
+    ccn_launch(dense_to_csr_kernel, dim3(ccn_blocks_exact(nq * K, 256)), dim3(256), 0, (cudaStream_t)stream, idx, row_ptr, nq, K, erow, ecol);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -603,7 +623,7 @@ extern "C" int ccn_dense_to_csr(const int32_t* idx, const int32_t* row_ptr, int6
 extern "C" int ccn_csr_rows(const int32_t* row_ptr, int64_t nq, int32_t* erow, ccn_stream_t stream) {
     CCN_REQUIRE(nq >= 0 && row_ptr && erow);
     if (nq == 0) return CCN_OK;
-    csr_rows_kernel<<<ccn_blocks_exact(nq, 256), 256, 0, (cudaStream_t)stream>>>(row_ptr, nq, erow);
+    ccn_launch(csr_rows_kernel, dim3(ccn_blocks_exact(nq, 256)), dim3(256), 0, (cudaStream_t)stream, row_ptr, nq, erow);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -616,13 +636,13 @@ extern "C" int ccn_edge_layer1(const float* H, int64_t ldh, const float* wp, con
     if (E == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldo & 3) == 0 && ccn_al16(out) && ccn_al16(wp) && (!bias || ccn_al16(bias)) &&
         (!H || ((ldh & 3) == 0 && ccn_al16(H)))) {
-        edge_layer1_v4_kernel<<<CCN_ELT_GRID(E * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+        ccn_launch(edge_layer1_v4_kernel, dim3(CCN_ELT_GRID(E * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, 
             H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
             slope, out, ldo);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    edge_layer1_kernel<<<CCN_ELT_GRID(E * c), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(edge_layer1_kernel, dim3(CCN_ELT_GRID(E * c)), dim3(256), 0, (cudaStream_t)stream, 
         H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
         slope, out, ldo);
     CCN_CHECK_LAUNCH();
@@ -634,12 +654,12 @@ extern "C" int ccn_edge_pair_layer1(const float* PQ, int64_t ldpq, const int32_t
     CCN_REQUIRE(E >= 0 && c > 0 && PQ && erow && ecol && out && ldpq >= 2 * c && ldo >= c);
     if (E == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldpq & 3) == 0 && (ldo & 3) == 0 && ccn_al16(PQ) && ccn_al16(out)) {
-        edge_pair_layer1_v4_kernel<<<CCN_ELT_GRID(E * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, erow, ecol, E, c, act,
+        ccn_launch(edge_pair_layer1_v4_kernel, dim3(CCN_ELT_GRID(E * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, PQ, ldpq, erow, ecol, E, c, act,
                                                                                                   slope, out, ldo);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    edge_pair_layer1_kernel<<<CCN_ELT_GRID(E * c), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, erow, ecol, E, c, act,
+    ccn_launch(edge_pair_layer1_kernel, dim3(CCN_ELT_GRID(E * c)), dim3(256), 0, (cudaStream_t)stream, PQ, ldpq, erow, ecol, E, c, act,
                                                                                    slope, out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -652,12 +672,12 @@ extern "C" int ccn_seg_aggregate(const float* msg, int64_t ldm, const float* att
     if (nq == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) && ccn_al16(out) &&
         (!att || ((lda & 3) == 0 && ccn_al16(att)))) {
-        seg_aggregate_v4_kernel<<<CCN_ELT_GRID(nq * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq,
+        ccn_launch(seg_aggregate_v4_kernel, dim3(CCN_ELT_GRID(nq * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, msg, ldm, att, lda, row_ptr, nq,
                                                                                                 c >> 2, mode, out, ldo, nullptr, 0, 0, 0);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    seg_aggregate_kernel<<<CCN_ELT_GRID(nq * c), 256, 0, (cudaStream_t)stream>>>(msg, ldm, att, lda, row_ptr, nq, c,
+    ccn_launch(seg_aggregate_kernel, dim3(CCN_ELT_GRID(nq * c)), dim3(256), 0, (cudaStream_t)stream, msg, ldm, att, lda, row_ptr, nq, c,
                                                                                  mode, out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -667,7 +687,7 @@ extern "C" int ccn_sgcnn_layer1(const float* PQ, int64_t ldpq, const int32_t* id
                                 int32_t act, float slope, float* out, int64_t ldo, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && PQ && out && ldpq >= 2 * c && ldo >= c && (K == 0 || idx));
     if (n == 0) return CCN_OK;
-    sgcnn_layer1_kernel<<<CCN_ELT_GRID(n * (K + 1) * c), 256, 0, (cudaStream_t)stream>>>(PQ, ldpq, idx, n, K, c, act,
+    ccn_launch(sgcnn_layer1_kernel, dim3(CCN_ELT_GRID(n * (K + 1) * c)), dim3(256), 0, (cudaStream_t)stream, PQ, ldpq, idx, n, K, c, act,
                                                                                         slope, out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -678,12 +698,12 @@ extern "C" int ccn_group_max_dense(const float* feat, int64_t ldf, const int32_t
     CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && feat && out);
     if (n == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldf & 3) == 0 && (ldo & 3) == 0 && ccn_al16(feat) && ccn_al16(out)) {
-        group_max_dense_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(feat, ldf, idx, n, K, c >> 2,
+        ccn_launch(group_max_dense_v4_kernel, dim3(CCN_ELT_GRID(n * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, feat, ldf, idx, n, K, c >> 2,
                                                                                                  out, ldo, nullptr, 0, 0, 0);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    group_max_dense_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(feat, ldf, idx, n, K, c, out, ldo);
+    ccn_launch(group_max_dense_kernel, dim3(CCN_ELT_GRID(n * c)), dim3(256), 0, (cudaStream_t)stream, feat, ldf, idx, n, K, c, out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -693,12 +713,12 @@ extern "C" int ccn_interp_blend(const float* x, int64_t ldx, const int32_t* nbr,
     CCN_REQUIRE(n >= 0 && knn >= 1 && c > 0 && x && nbr && wgt && out);
     if (n == 0) return CCN_OK;
     if ((c & 3) == 0 && (ldx & 3) == 0 && (ldo & 3) == 0 && ccn_al16(x) && ccn_al16(out)) {
-        interp_blend_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn,
+        ccn_launch(interp_blend_v4_kernel, dim3(CCN_ELT_GRID(n * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, x, ldx, nbr, wgt, from_d2, n, knn,
                                                                                               c >> 2, out, ldo, nullptr, 0, 0, 0);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    interp_blend_kernel<<<CCN_ELT_GRID(n * c), 256, 0, (cudaStream_t)stream>>>(x, ldx, nbr, wgt, from_d2, n, knn, c,
+    ccn_launch(interp_blend_kernel, dim3(CCN_ELT_GRID(n * c)), dim3(256), 0, (cudaStream_t)stream, x, ldx, nbr, wgt, from_d2, n, knn, c,
                                                                                out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -719,7 +739,7 @@ extern "C" int ccn_seg_aggregate_both(const float* msg, int64_t ldm, const float
     CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldm & 3) == 0 && (ldo & 3) == 0 && ccn_al16(msg) &&
                 ccn_al16(out) && (!att || ((lda & 3) == 0 && ccn_al16(att))));
     if (nq == 0) return CCN_OK;
-    seg_aggregate_v4_kernel<<<CCN_ELT_GRID(nq * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(seg_aggregate_v4_kernel, dim3(CCN_ELT_GRID(nq * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, 
         msg, ldm, att, lda, row_ptr, nq, c >> 2, mode, out, ldo, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -732,7 +752,7 @@ extern "C" int ccn_group_max_dense_both(const float* feat, int64_t ldf, const in
     CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldf & 3) == 0 && (ldo & 3) == 0 && ccn_al16(feat) &&
                 ccn_al16(out));
     if (n == 0) return CCN_OK;
-    group_max_dense_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(group_max_dense_v4_kernel, dim3(CCN_ELT_GRID(n * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, 
         feat, ldf, idx, n, K, c >> 2, out, ldo, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -745,7 +765,7 @@ extern "C" int ccn_interp_blend_both(const float* x, int64_t ldx, const int32_t*
     CCN_REQUIRE(CCN_BOTH_OK(planes, kpad, plane_stride, n_planes, c) && (ldx & 3) == 0 && (ldo & 3) == 0 && ccn_al16(x) &&
                 ccn_al16(out));
     if (n == 0) return CCN_OK;
-    interp_blend_v4_kernel<<<CCN_ELT_GRID(n * (c >> 2)), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(interp_blend_v4_kernel, dim3(CCN_ELT_GRID(n * (c >> 2))), dim3(256), 0, (cudaStream_t)stream, 
         x, ldx, nbr, wgt, from_d2, n, knn, c >> 2, out, ldo, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -757,7 +777,7 @@ extern "C" int ccn_sgcnn_layer1_planes(const float* PQ, int64_t ldpq, const int3
     CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && PQ && ldpq >= 2 * c && (K == 0 || idx));
     CCN_REQUIRE(CCN_PLANES_OK(planes, kpad, plane_stride, n_planes, c) && kpad == c && ccn_al16(PQ) && (ldpq & 3) == 0);
     if (n == 0) return CCN_OK;
-    sgcnn_layer1_planes_kernel<<<CCN_ELT_GRID(n * (K + 1) * (c >> 3)), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(sgcnn_layer1_planes_kernel, dim3(CCN_ELT_GRID(n * (K + 1) * (c >> 3))), dim3(256), 0, (cudaStream_t)stream, 
         PQ, ldpq, idx, n, K, c, act, slope, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -769,7 +789,7 @@ extern "C" int ccn_edge_pair_layer1_planes(const float* PQ, int64_t ldpq, const 
     CCN_REQUIRE(E >= 0 && c > 0 && PQ && erow && ecol && ldpq >= 2 * c);
     CCN_REQUIRE(CCN_PLANES_OK(planes, kpad, plane_stride, n_planes, c) && kpad == c && ccn_al16(PQ) && (ldpq & 3) == 0);
     if (E == 0) return CCN_OK;
-    edge_pair_layer1_planes_kernel<<<CCN_ELT_GRID(E * (c >> 3)), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(edge_pair_layer1_planes_kernel, dim3(CCN_ELT_GRID(E * (c >> 3))), dim3(256), 0, (cudaStream_t)stream, 
         PQ, ldpq, erow, ecol, E, c, act, slope, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -784,7 +804,7 @@ extern "C" int ccn_edge_layer1_planes(const float* H, int64_t ldh, const float* 
     CCN_REQUIRE(CCN_PLANES_OK(planes, kpad, plane_stride, n_planes, c) && kpad == c && ccn_al16(wp) &&
                 (!bias || ccn_al16(bias)) && (!H || (ccn_al16(H) && (ldh & 3) == 0)));
     if (E == 0) return CCN_OK;
-    edge_layer1_planes_kernel<<<CCN_ELT_GRID(E * (c >> 3)), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(edge_layer1_planes_kernel, dim3(CCN_ELT_GRID(E * (c >> 3))), dim3(256), 0, (cudaStream_t)stream, 
         H, ldh, wp, bias, pos_src, pos_dst, erow, ecol, E, c, normalize_radius > 0.f ? 1.f : 0.f, normalize_radius, act,
         slope, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();

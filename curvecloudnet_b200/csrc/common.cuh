@@ -10,6 +10,38 @@ extern unsigned long long g_ccn_kernel_launches;   // version.cu; one increment 
 // gemm_tc.cu: CUtensorMap (128 bytes, 64-byte aligned, HOST memory) of a bf16 (n, kpad) row-major matrix, box 64 x box_n
 int ccn_encode_bf16_map(void* tmap_out_host, const void* base, int64_t n, int64_t kpad, int32_t box_n);
 
+// ------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  The per-scan forward is a chain of ~400 dependent launches of 3 - 30 us kernels, and a
+// plain stream-ordered launch boundary costs 3 - 4 us on B200 (tools/bench_pdl.cu, profiles/r02p_pdl_micro.txt: 3.07 us
+// between two one-wave kernels, 1.87 us with the attribute below).  EVERY kernel of this library is launched through
+// ccn_launch with cudaLaunchAttributeProgrammaticStreamSerialization and executes ccn_pdl_wait() (griddepcontrol.wait:
+// all prerequisite grids complete, their memory visible) before it touches global memory - as its first statement, or, in
+// the tensor-core kernels, after the prologue that does not depend on the previous kernel (barrier init, TMEM allocation,
+// descriptor prefetch).  Since every kernel waits, completion stays transitive along the stream.  No kernel triggers its
+// dependents early (measured: no gain).  ccn_set_dependent_launch(0) / CCN_PDL=0 launches without the attribute.
+// ------------------------------------------------------------------------------------------
+extern int g_ccn_pdl;                               // version.cu
+
+__device__ __forceinline__ void ccn_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+static inline cudaError_t ccn_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args&&... args) {
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_ccn_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+#endif
+
 #define CCN_CHECK_LAUNCH()                                 \
     do {                                                   \
         cudaError_t e__ = cudaGetLastError();              \

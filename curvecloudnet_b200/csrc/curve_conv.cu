@@ -15,6 +15,7 @@ __global__ void curve_feat_prep_kernel(const float* __restrict__ x, int64_t ldx,
                                        const float* __restrict__ pos, int with_xyz, int with_diff,
                                        const int32_t* __restrict__ ord, int64_t n,
                                        float* __restrict__ out, int64_t ldo) {
+    ccn_pdl_wait();
     const int c_in = cx + (with_xyz ? 3 : 0);
     const int64_t total = n * (int64_t)c_in;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
@@ -37,6 +38,7 @@ __global__ void curve_feat_prep_kernel(const float* __restrict__ x, int64_t ldx,
 }
 
 __global__ void row_map_kernel(const int32_t* __restrict__ ord, int64_t n, int pad, int32_t* __restrict__ row2pt) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i < n) row2pt[i + (int64_t)pad * (ord[i] + 1)] = (int32_t)i;
 }
@@ -52,6 +54,7 @@ __global__ void __launch_bounds__(256) curve_conv_layer_kernel(
     const float* __restrict__ in, int64_t ld_in, const float* __restrict__ w, const float* __restrict__ bias,
     float* __restrict__ out, int64_t ld_out, const int32_t* __restrict__ row2pt, int64_t rows,
     int cin, int cout, int in_mapped, int out_mapped, float slope) {
+    ccn_pdl_wait();
     constexpr int K = 2 * HALF + 1;
     constexpr int TROWS = kTR + 2 * HALF;
     __shared__ float tile[TROWS][kCK];
@@ -120,7 +123,7 @@ extern "C" int ccn_curve_feat_prep(const float* x, int64_t ldx, int32_t cx, cons
     CCN_REQUIRE(n >= 0 && c_in > 0 && out && (cx == 0 || x) && (!with_xyz || pos) && (!with_diff || curve_ord));
     CCN_REQUIRE(ldo >= (with_diff ? 2 : 1) * c_in);
     if (n == 0) return CCN_OK;
-    curve_feat_prep_kernel<<<ccn_grid(n * c_in, 256), 256, 0, (cudaStream_t)stream>>>(x, ldx, cx, pos, with_xyz,
+    ccn_launch(curve_feat_prep_kernel, dim3(ccn_grid(n * c_in, 256)), dim3(256), 0, (cudaStream_t)stream, x, ldx, cx, pos, with_xyz,
                                                                                      with_diff, curve_ord, n, out, ldo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -133,7 +136,7 @@ extern "C" int ccn_curve_row_map(const int32_t* curve_ord, int64_t n, int32_t n_
     cudaError_t e = cudaMemsetAsync(row2pt, 0xff, rows * sizeof(int32_t), (cudaStream_t)stream);
     if (e != cudaSuccess) return (int)e;
     if (n == 0) return CCN_OK;
-    row_map_kernel<<<ccn_blocks_exact(n, 256), 256, 0, (cudaStream_t)stream>>>(curve_ord, n, pad, row2pt);
+    ccn_launch(row_map_kernel, dim3(ccn_blocks_exact(n, 256)), dim3(256), 0, (cudaStream_t)stream, curve_ord, n, pad, row2pt);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -149,7 +152,7 @@ extern "C" int ccn_curve_conv_layer(const float* in, int64_t ld_in, const float*
     dim3 grid(ccn_blocks_exact(rows, kTR), (cout + 31) / 32);
     cudaStream_t s = (cudaStream_t)stream;
 #define CCN_LAUNCH_CONV(H)                                                                                     \
-    curve_conv_layer_kernel<H><<<grid, 256, 0, s>>>(in, ld_in, w, bias, out, ld_out, row2pt, rows, cin, cout, \
+    ccn_launch(curve_conv_layer_kernel<H>, dim3(grid), dim3(256), 0, s, in, ld_in, w, bias, out, ld_out, row2pt, rows, cin, cout, \
                                                     in_mapped, out_mapped, slope)
     switch (ksize / 2) {
         case 0: CCN_LAUNCH_CONV(0); break;

@@ -10,6 +10,7 @@ namespace {
 
 __global__ void beam_hist_kernel(const int64_t* __restrict__ beam, int64_t n, int n_beams, int32_t* __restrict__ count,
                                  int32_t* __restrict__ flags) {
+    ccn_pdl_wait();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t b = beam[i];
         if (b < 0 || b >= n_beams) { atomicOr(flags, 1); continue; }
@@ -21,6 +22,7 @@ __global__ void beam_hist_kernel(const int64_t* __restrict__ beam, int64_t n, in
 __global__ void __launch_bounds__(1024) beam_rank_kernel(const int64_t* __restrict__ beam, int64_t n,
                                                          const int32_t* __restrict__ count, int64_t* __restrict__ reorder,
                                                          int64_t* __restrict__ inv) {
+    ccn_pdl_wait();
     __shared__ int scan_smem[33];
     __shared__ int base_s;
     const int b = blockIdx.x;
@@ -48,6 +50,7 @@ __global__ void __launch_bounds__(1024) beam_rank_kernel(const int64_t* __restri
 
 // single-beam sweeps (KITTI): the stable sort is the identity
 __global__ void iota_i64_kernel(int64_t n, int64_t* __restrict__ a, int64_t* __restrict__ b) {
+    ccn_pdl_wait();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         a[i] = i;
         b[i] = i;
@@ -58,6 +61,7 @@ __global__ void iota_i64_kernel(int64_t n, int64_t* __restrict__ a, int64_t* __r
 __global__ void curve_split_kernel(const float* __restrict__ points, int64_t ldp, const int64_t* __restrict__ beam,
                                    const int64_t* __restrict__ reorder, int64_t n, float thresh,
                                    float* __restrict__ sorted_points, int32_t* __restrict__ split) {
+    ccn_pdl_wait();
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = reorder[j];
         const float x = points[i * ldp], y = points[i * ldp + 1], z = points[i * ldp + 2];
@@ -83,6 +87,7 @@ __global__ void curve_split_kernel(const float* __restrict__ points, int64_t ldp
 // curve_idxs[j] = inclusive running sum of split (single CTA, chunked block scan); *n_curves = last + 1
 __global__ void __launch_bounds__(1024) curve_cumsum_kernel(const int32_t* __restrict__ split, int64_t n,
                                                             int64_t* __restrict__ cid, int32_t* __restrict__ n_curves) {
+    ccn_pdl_wait();
     __shared__ int scan_smem[33];
     int running = 0;
     for (int64_t i0 = 0; i0 < n; i0 += blockDim.x) {
@@ -111,15 +116,15 @@ extern "C" int ccn_get_curves(const float* points, int64_t ldp, const int64_t* b
     if (n == 0) return CCN_OK;
     int32_t* count = scratch;
     int32_t* split = scratch + n_beams;
-    beam_hist_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(beam, n, n_beams, count, counts_out + 1);
+    ccn_launch(beam_hist_kernel, dim3(ccn_grid(n, 256, 148 * 8)), dim3(256), 0, s, beam, n, n_beams, count, counts_out + 1);
     CCN_CHECK_LAUNCH();
-    if (n_beams == 1) iota_i64_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(n, reorder, inv_reorder);
-    else beam_rank_kernel<<<n_beams, 1024, 0, s>>>(beam, n, count, reorder, inv_reorder);
+    if (n_beams == 1) ccn_launch(iota_i64_kernel, dim3(ccn_grid(n, 256, 148 * 8)), dim3(256), 0, s, n, reorder, inv_reorder);
+    else ccn_launch(beam_rank_kernel, dim3(n_beams), dim3(1024), 0, s, beam, n, count, reorder, inv_reorder);
     CCN_CHECK_LAUNCH();
-    curve_split_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(points, ldp, beam, reorder, n, curve_thresh,
+    ccn_launch(curve_split_kernel, dim3(ccn_grid(n, 256, 148 * 8)), dim3(256), 0, s, points, ldp, beam, reorder, n, curve_thresh,
                                                                   sorted_points, split);
     CCN_CHECK_LAUNCH();
-    curve_cumsum_kernel<<<1, 1024, 0, s>>>(split, n, curve_idxs, counts_out);
+    ccn_launch(curve_cumsum_kernel, dim3(1), dim3(1024), 0, s, split, n, curve_idxs, counts_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

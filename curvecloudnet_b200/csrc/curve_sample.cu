@@ -43,6 +43,7 @@ constexpr int kTile = 1024 * kItems;
 
 __global__ void __launch_bounds__(1024) cfps_tile_sum_kernel(const float* __restrict__ pos, const int32_t* __restrict__ ord,
                                                              int64_t n, double* __restrict__ tile_tot) {
+    ccn_pdl_wait();
     __shared__ double smd[33];
     const int64_t i0 = (int64_t)blockIdx.x * kTile + (int64_t)threadIdx.x * kItems;
     double local = 0.0;
@@ -56,6 +57,7 @@ __global__ void __launch_bounds__(1024) cfps_tile_sum_kernel(const float* __rest
 __global__ void __launch_bounds__(1024) cfps_run_kernel(const float* __restrict__ pos, const int32_t* __restrict__ ord,
                                                         int64_t n, const double* __restrict__ tile_tot,
                                                         float* __restrict__ run) {
+    ccn_pdl_wait();
     __shared__ double smd[33];
     __shared__ double s_carry;
     if (threadIdx.x == 0) {
@@ -106,6 +108,7 @@ __global__ void __launch_bounds__(1024) cfps_count_kernel(const float* __restric
                                                           const int32_t* __restrict__ cptr, int64_t n,
                                                           const float* __restrict__ u_ptr, float arclen,
                                                           int32_t* __restrict__ tile_cnt) {
+    ccn_pdl_wait();
     __shared__ int smi[33];
     int f[kItems];
     const int local = cfps_flags(run, ord, cptr, n, (int64_t)blockIdx.x * kTile + (int64_t)threadIdx.x * kItems, *u_ptr, arclen, f);
@@ -119,6 +122,7 @@ __global__ void __launch_bounds__(1024) cfps_compact_kernel(const float* __restr
                                                             const float* __restrict__ u_ptr, float arclen,
                                                             const int32_t* __restrict__ tile_cnt,
                                                             int64_t* __restrict__ idx_out, int32_t* __restrict__ count_out) {
+    ccn_pdl_wait();
     __shared__ int smi[33];
     int part = 0;
     for (int t = threadIdx.x; t < (int)blockIdx.x; t += blockDim.x) part += tile_cnt[t];
@@ -141,6 +145,7 @@ __global__ void __launch_bounds__(1024) cfps_compact_kernel(const float* __restr
 __global__ void __launch_bounds__(256) radius_1d_curve_stats_kernel(
     const float* __restrict__ pos, const int32_t* __restrict__ ord, const int32_t* __restrict__ cptr,
     int32_t n_curves, float radius, float* __restrict__ kc, int32_t* __restrict__ stats) {
+    ccn_pdl_wait();
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (c >= n_curves) return;
     const int lane = ccn_lane();
@@ -169,6 +174,7 @@ __global__ void radius_1d_group_kernel(const int64_t* __restrict__ idxs, int64_t
                                        int64_t n, int32_t n_curves, const float* __restrict__ kc,
                                        const int32_t* __restrict__ stats, int32_t* __restrict__ row_ptr,
                                        int32_t* __restrict__ col) {
+    ccn_pdl_wait();
     const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (q >= nq) return;
     const int64_t p = idxs[q];
@@ -211,6 +217,7 @@ __global__ void radius_1d_group_kernel(const int64_t* __restrict__ idxs, int64_t
 // also written to a[n] (CSR terminator).
 __global__ void __launch_bounds__(1024) excl_scan_i32_kernel(int32_t* __restrict__ a, int64_t n,
                                                              int32_t* __restrict__ total_out) {
+    ccn_pdl_wait();
     __shared__ int sm[33];
     int carry = 0;
     for (int64_t base = 0; base < n; base += 1024 * kItems) {
@@ -243,6 +250,7 @@ constexpr int kMaxKnn1d = 8;
 __global__ void knn_1d_superset_kernel(const float* __restrict__ pos, const int32_t* __restrict__ ord, int64_t n,
                                        const int64_t* __restrict__ idxs, int64_t nq, int knn,
                                        int32_t* __restrict__ nbr, float* __restrict__ wgt) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     // a = #sampled positions <= i  (cumsum of the hit mask, point_ops.py:203-205)
@@ -302,13 +310,13 @@ extern "C" int ccn_curve_fps(const float* pos, const int32_t* curve_ord, const i
     const int tiles = (int)((n + kTile - 1) / kTile);
     double* tile_tot = reinterpret_cast<double*>(idx_out);                    // consumed before idx_out is written
     int32_t* tile_cnt = reinterpret_cast<int32_t*>(run_scratch + n);          // the tail of run_scratch
-    cfps_tile_sum_kernel<<<tiles, 1024, 0, s>>>(pos, curve_ord, n, tile_tot);
+    ccn_launch(cfps_tile_sum_kernel, dim3(tiles), dim3(1024), 0, s, pos, curve_ord, n, tile_tot);
     CCN_CHECK_LAUNCH();
-    cfps_run_kernel<<<tiles, 1024, 0, s>>>(pos, curve_ord, n, tile_tot, run_scratch);
+    ccn_launch(cfps_run_kernel, dim3(tiles), dim3(1024), 0, s, pos, curve_ord, n, tile_tot, run_scratch);
     CCN_CHECK_LAUNCH();
-    cfps_count_kernel<<<tiles, 1024, 0, s>>>(run_scratch, curve_ord, curve_ptr, n, u, arclen, tile_cnt);
+    ccn_launch(cfps_count_kernel, dim3(tiles), dim3(1024), 0, s, run_scratch, curve_ord, curve_ptr, n, u, arclen, tile_cnt);
     CCN_CHECK_LAUNCH();
-    cfps_compact_kernel<<<tiles, 1024, 0, s>>>(run_scratch, curve_ord, curve_ptr, n, u, arclen, tile_cnt, idx_out, count_out);
+    ccn_launch(cfps_compact_kernel, dim3(tiles), dim3(1024), 0, s, run_scratch, curve_ord, curve_ptr, n, u, arclen, tile_cnt, idx_out, count_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -323,16 +331,16 @@ extern "C" int ccn_radius_1d_group_count(const float* pos, const int32_t* curve_
     cudaError_t e = cudaMemsetAsync(stats_scratch, 0, 2 * sizeof(int32_t), s);
     if (e != cudaSuccess) return (int)e;
     if (n_curves > 0) {
-        radius_1d_curve_stats_kernel<<<ccn_blocks_exact((int64_t)n_curves * 32, 256), 256, 0, s>>>(
+        ccn_launch(radius_1d_curve_stats_kernel, dim3(ccn_blocks_exact((int64_t)n_curves * 32, 256)), dim3(256), 0, s, 
             pos, curve_ord, curve_ptr, n_curves, radius, kc_scratch, stats_scratch);
         CCN_CHECK_LAUNCH();
     }
     if (nq > 0) {
-        radius_1d_group_kernel<false><<<ccn_blocks_exact(nq, 128), 128, 0, s>>>(
+        ccn_launch(radius_1d_group_kernel<false>, dim3(ccn_blocks_exact(nq, 128)), dim3(128), 0, s, 
             idxs, nq, curve_ord, curve_local, n, n_curves, kc_scratch, stats_scratch, row_ptr, nullptr);
         CCN_CHECK_LAUNCH();
     }
-    excl_scan_i32_kernel<<<1, 1024, 0, s>>>(row_ptr, nq, total_out);
+    ccn_launch(excl_scan_i32_kernel, dim3(1), dim3(1024), 0, s, row_ptr, nq, total_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -343,7 +351,7 @@ extern "C" int ccn_radius_1d_group_fill(const int32_t* curve_ord, const int64_t*
                                         ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && nq >= 0 && kc_scratch && stats_scratch && row_ptr && (col || nq == 0));
     if (nq == 0) return CCN_OK;
-    radius_1d_group_kernel<true><<<ccn_blocks_exact(nq, 128), 128, 0, (cudaStream_t)stream>>>(
+    ccn_launch(radius_1d_group_kernel<true>, dim3(ccn_blocks_exact(nq, 128)), dim3(128), 0, (cudaStream_t)stream, 
         idxs, nq, curve_ord, curve_local, n, n_curves, kc_scratch, stats_scratch, const_cast<int32_t*>(row_ptr), col);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -351,7 +359,7 @@ extern "C" int ccn_radius_1d_group_fill(const int32_t* curve_ord, const int64_t*
 
 extern "C" int ccn_excl_scan_i32(int32_t* a, int64_t n, int32_t* total_out, ccn_stream_t stream) {
     CCN_REQUIRE(a && n >= 0);
-    excl_scan_i32_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(a, n, total_out);
+    ccn_launch(excl_scan_i32_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, a, n, total_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -360,7 +368,7 @@ extern "C" int ccn_knn_1d_superset(const float* pos, const int32_t* curve_ord, i
                                    int64_t nq, int32_t knn, int32_t* nbr, float* wgt, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && nq >= 0 && knn >= 1 && knn <= kMaxKnn1d && nbr && wgt);
     if (n == 0) return CCN_OK;
-    knn_1d_superset_kernel<<<ccn_blocks_exact(n, 128), 128, 0, (cudaStream_t)stream>>>(pos, curve_ord, n, idxs, nq,
+    ccn_launch(knn_1d_superset_kernel, dim3(ccn_blocks_exact(n, 128)), dim3(128), 0, (cudaStream_t)stream, pos, curve_ord, n, idxs, nq,
                                                                                       knn, nbr, wgt);
     CCN_CHECK_LAUNCH();
     return CCN_OK;

@@ -35,6 +35,7 @@ __device__ __forceinline__ unsigned long long point_flags(const int64_t* __restr
 __global__ void __launch_bounds__(1024) tile_flags_kernel(const int64_t* __restrict__ batch, const int64_t* __restrict__ curve,
                                                           int64_t n, unsigned long long* __restrict__ tile_sum,
                                                           int32_t* __restrict__ counts) {
+    ccn_pdl_wait();
     __shared__ unsigned long long sm[33];
     const int64_t i0 = (int64_t)blockIdx.x * kTile + (int64_t)threadIdx.x * kItems;
     unsigned long long local = 0;
@@ -52,6 +53,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(
     const int64_t* __restrict__ batch, const int64_t* __restrict__ curve, int64_t n,
     const unsigned long long* __restrict__ tile_sum, int32_t* __restrict__ ord, int32_t* __restrict__ cptr,
     int32_t* __restrict__ sptr, int32_t* __restrict__ counts, int max_samples) {
+    ccn_pdl_wait();
     __shared__ unsigned long long sm[33];
     // carry of this tile = sum of the earlier tiles' totals
     unsigned long long part = 0;
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(
 __global__ void __launch_bounds__(1024) sample_offsets_kernel(const int64_t* __restrict__ curve, int64_t n,
                                                               const int32_t* __restrict__ sptr, int64_t* __restrict__ soff,
                                                               int32_t* __restrict__ counts) {
+    ccn_pdl_wait();
     __shared__ long long sm[33];
     if (counts[2]) {                       // invalid topology: sptr is not trustworthy
         if (threadIdx.x == 0) counts[3] = 0;
@@ -122,6 +125,7 @@ __global__ void __launch_bounds__(1024) sample_offsets_kernel(const int64_t* __r
 __global__ void glob_ids_kernel(const int64_t* __restrict__ batch, const int64_t* __restrict__ curve, int64_t n,
                                 const int64_t* __restrict__ soff, const int32_t* __restrict__ counts,
                                 int64_t* __restrict__ glob) {
+    ccn_pdl_wait();
     if (counts[2]) return;
     const bool single = counts[0] == 1;     // point_ops.py:27-28: a single sample keeps its ids unchanged
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -132,6 +136,7 @@ __global__ void glob_ids_kernel(const int64_t* __restrict__ batch, const int64_t
 __global__ void __launch_bounds__(1024) sample_ptr_kernel(const int64_t* __restrict__ batch, int64_t n,
                                                           int32_t* __restrict__ sptr, int32_t* __restrict__ counts,
                                                           int max_samples) {
+    ccn_pdl_wait();
     __shared__ int sm[33];
     int carry = 0, err = 0;
     for (int64_t base = 0; base < n; base += 1024) {
@@ -181,13 +186,13 @@ extern "C" int ccn_curve_csr(const int64_t* batch, const int64_t* curve, int64_t
     }
     const int tiles = (int)((n + kTile - 1) / kTile);
     unsigned long long* tile_sum = reinterpret_cast<unsigned long long*>(curve_glob);
-    tile_flags_kernel<<<tiles, 1024, 0, s>>>(batch, curve, n, tile_sum, counts);
+    ccn_launch(tile_flags_kernel, dim3(tiles), dim3(1024), 0, s, batch, curve, n, tile_sum, counts);
     CCN_CHECK_LAUNCH();
-    tile_scan_kernel<<<tiles, 1024, 0, s>>>(batch, curve, n, tile_sum, curve_ord, curve_ptr, sample_ptr, counts, max_samples);
+    ccn_launch(tile_scan_kernel, dim3(tiles), dim3(1024), 0, s, batch, curve, n, tile_sum, curve_ord, curve_ptr, sample_ptr, counts, max_samples);
     CCN_CHECK_LAUNCH();
-    sample_offsets_kernel<<<1, 1024, 0, s>>>(curve, n, sample_ptr, sample_curve_off, counts);
+    ccn_launch(sample_offsets_kernel, dim3(1), dim3(1024), 0, s, curve, n, sample_ptr, sample_curve_off, counts);
     CCN_CHECK_LAUNCH();
-    glob_ids_kernel<<<ccn_grid(n, 256, 148LL * 8), 256, 0, s>>>(batch, curve, n, sample_curve_off, counts, curve_glob);
+    ccn_launch(glob_ids_kernel, dim3(ccn_grid(n, 256, 148LL * 8)), dim3(256), 0, s, batch, curve, n, sample_curve_off, counts, curve_glob);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -195,7 +200,7 @@ extern "C" int ccn_curve_csr(const int64_t* batch, const int64_t* curve, int64_t
 extern "C" int ccn_sample_ptr(const int64_t* batch, int64_t n, int32_t* sample_ptr, int32_t* counts,
                               int32_t max_samples, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && n < 0x7fffffff && max_samples > 0 && batch && sample_ptr && counts);
-    sample_ptr_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(batch, n, sample_ptr, counts, max_samples);
+    ccn_launch(sample_ptr_kernel, dim3(1), dim3(1024), 0, (cudaStream_t)stream, batch, n, sample_ptr, counts, max_samples);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -207,6 +212,7 @@ namespace {
 __global__ void subset_sample_ptr_kernel(const int64_t* __restrict__ batch, const int64_t* __restrict__ idx,
                                          const int32_t* __restrict__ count_ptr, int32_t n_samples,
                                          int32_t* __restrict__ sptr) {
+    ccn_pdl_wait();
     const int count = *count_ptr;
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t == 0) sptr[n_samples] = count;
@@ -222,7 +228,7 @@ __global__ void subset_sample_ptr_kernel(const int64_t* __restrict__ batch, cons
 extern "C" int ccn_subset_sample_ptr(const int64_t* batch, const int64_t* idx, const int32_t* count_ptr,
                                      int64_t capacity, int32_t n_samples, int32_t* sptr_out, ccn_stream_t stream) {
     CCN_REQUIRE(batch && idx && count_ptr && sptr_out && capacity >= 0 && n_samples >= 1);
-    subset_sample_ptr_kernel<<<ccn_blocks_exact(capacity > 0 ? capacity : 1, 256), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(subset_sample_ptr_kernel, dim3(ccn_blocks_exact(capacity > 0 ? capacity : 1, 256)), dim3(256), 0, (cudaStream_t)stream, 
         batch, idx, count_ptr, n_samples, sptr_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;

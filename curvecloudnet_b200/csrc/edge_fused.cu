@@ -176,6 +176,7 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
         mbar_init(acc_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    ccn_pdl_wait();      // global memory (biases included: the optimizer's kernels may precede a forward) from here on
     for (int t = threadIdx.x; t < p.L * kMaxWidth; t += kThreads) {
         const int l = t / kMaxWidth, c = t % kMaxWidth;
         bias_s[l][c] = (p.ly[l].bias && c < p.ly[l].N) ? __ldg(p.ly[l].bias + c) : 0.f;
@@ -570,6 +571,7 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
 // CSR tiling: tile t owns the targets whose first edge lies in [S t, S (t+1)) - at most S - 1 + max_degree = 128 edge rows,
 // whole segments only; targets without edges belong to the tile of their offset.  One thread per tile, two binary searches.
 __global__ void csr_tiles_kernel(const int32_t* __restrict__ row_ptr, int nq, int S, int n_tiles, int4* __restrict__ tiles) {
+    ccn_pdl_wait();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_tiles) return;
     const int lo_v = S * t, hi_v = lo_v + S;
@@ -620,6 +622,7 @@ template <int P>
 __global__ void __launch_bounds__(kStreamThreads, 1) sgcnn_stream_kernel(const __grid_constant__ CUtensorMap w_hi,
                                                                          const __grid_constant__ CUtensorMap w_lo,
                                                                          const __grid_constant__ StreamParams p) {
+    ccn_pdl_wait();
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];     // full[S], empty[S], tfull[2], tempty[2]
     __shared__ uint32_t tmem_base_slot;
@@ -914,7 +917,7 @@ int launch_chain(const ccn_chain_t* ch, const ChainParams& p, int smem, cudaStre
     const int grid = p.n_tiles < 148 * per_sm ? p.n_tiles : 148 * per_sm;
     const CUtensorMap* whi = (const CUtensorMap*)ch->w_hi_tmap;
     const CUtensorMap* wlo = P == 2 ? (const CUtensorMap*)ch->w_lo_tmap : whi;
-    edge_chain_kernel<P, FORM><<<grid, kThreads, smem, s>>>(*whi, *wlo, p);
+    ccn_launch(edge_chain_kernel<P, FORM>, dim3(grid), dim3(kThreads), smem, s, *whi, *wlo, p);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -929,7 +932,7 @@ int launch_stream_t(const StreamParams& p, const ccn_chain_t* ch, int smem, int 
     }
     const CUtensorMap* whi = (const CUtensorMap*)ch->w_hi_tmap;
     const CUtensorMap* wlo = P == 2 ? (const CUtensorMap*)ch->w_lo_tmap : whi;
-    sgcnn_stream_kernel<P><<<grid, kStreamThreads, smem, s>>>(*whi, *wlo, p);
+    ccn_launch(sgcnn_stream_kernel<P>, dim3(grid), dim3(kStreamThreads), smem, s, *whi, *wlo, p);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -1024,7 +1027,7 @@ extern "C" int ccn_pointconv_fused(const float* H, int64_t ldh, const float* wp,
     p.out = out; p.ldo = ldo; p.planes = (__nv_bfloat16*)planes; p.kpad = kpad; p.pstride = plane_stride; p.npl = n_planes;
     cudaStream_t s = (cudaStream_t)stream;
     p.tiles = reinterpret_cast<const int4*>(tile_scratch);
-    csr_tiles_kernel<<<(p.n_tiles + 127) / 128, 128, 0, s>>>(row_ptr, p.nq, p.S, p.n_tiles, reinterpret_cast<int4*>(tile_scratch));
+    ccn_launch(csr_tiles_kernel, dim3((p.n_tiles + 127) / 128), dim3(128), 0, s, row_ptr, p.nq, p.S, p.n_tiles, reinterpret_cast<int4*>(tile_scratch));
     CCN_CHECK_LAUNCH();
     if (pair) return P == 2 ? launch_chain<2, FORM_PAIR>(chain_host, p, smem, s) : launch_chain<1, FORM_PAIR>(chain_host, p, smem, s);
     return P == 2 ? launch_chain<2, FORM_POINT>(chain_host, p, smem, s) : launch_chain<1, FORM_POINT>(chain_host, p, smem, s);

@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_slot;
+    ccn_pdl_wait();      // barrier init + TMEM allocation overlapped the previous kernel's tail; global memory from here on
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
@@ -327,6 +328,7 @@ struct PackSrc {
 
 __global__ void pack_planes_kernel(const PackSrc s, int64_t n, int ctot, __nv_bfloat16* __restrict__ planes,
                                    int64_t kpad, int64_t plane_stride, int n_planes) {
+    ccn_pdl_wait();
     const int groups = (int)(kpad >> 3);
     const int64_t total = n * groups;
     const int e0 = s.c[0], e1 = e0 + s.c[1], e2 = e1 + s.c[2];
@@ -396,7 +398,7 @@ extern "C" int ccn_pack_planes(const float* s0, int64_t ld0, int32_t c0, const i
     s.idx[0] = i0; s.idx[1] = i1; s.idx[2] = i2; s.idx[3] = i3;
     s.ld[0] = ld0; s.ld[1] = ld1; s.ld[2] = ld2; s.ld[3] = ld3;
     s.c[0] = c0; s.c[1] = c1; s.c[2] = c2; s.c[3] = c3;
-    pack_planes_kernel<<<ccn_grid(n * (kpad >> 3), 256, 148LL * 32), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(pack_planes_kernel, dim3(ccn_grid(n * (kpad >> 3), 256, 148LL * 32)), dim3(256), 0, (cudaStream_t)stream, 
         s, n, ctot, (__nv_bfloat16*)planes, kpad, plane_stride, n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -497,10 +499,10 @@ static int launch_planes(const void* const* ap, const int64_t* ald, const int64_
         attr[which] = true;
     }
     switch (which) {
-        case 0: linear_planes_kernel<1, false><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
-        case 1: linear_planes_kernel<1, true><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
-        case 2: linear_planes_kernel<3, false><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
-        default: linear_planes_kernel<3, true><<<grid, kThreads, smem, s>>>(am, *whi, *wlo, p, out_map); break;
+        case 0: ccn_launch(linear_planes_kernel<1, false>, dim3(grid), dim3(kThreads), smem, s, am, *whi, *wlo, p, out_map); break;
+        case 1: ccn_launch(linear_planes_kernel<1, true>, dim3(grid), dim3(kThreads), smem, s, am, *whi, *wlo, p, out_map); break;
+        case 2: ccn_launch(linear_planes_kernel<3, false>, dim3(grid), dim3(kThreads), smem, s, am, *whi, *wlo, p, out_map); break;
+        default: ccn_launch(linear_planes_kernel<3, true>, dim3(grid), dim3(kThreads), smem, s, am, *whi, *wlo, p, out_map); break;
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;

@@ -14,6 +14,7 @@ __global__ void __launch_bounds__(256) linear_f32_kernel(const float* __restrict
                                                          const float* __restrict__ W, int64_t ldw,
                                                          const float* __restrict__ bias, float* __restrict__ Y,
                                                          int64_t ldy, int M, int N, int K, int act, float slope) {
+    ccn_pdl_wait();
     constexpr int BM = 16 * TM, BN = 16 * TN;
     constexpr int PA = BM / 16, PB = BN / 16;     // rows loaded per thread per k-tile
     __shared__ __align__(16) float As[2][kBK][BM + 4];
@@ -114,10 +115,10 @@ extern "C" int ccn_linear_f32(const float* A, int64_t lda, const float* W, int64
     const int64_t big_tiles = ((M + 127) / 128) * ((N + 127) / 128);
     if (big_tiles >= 148) {
         dim3 grid((N + 127) / 128, (unsigned)((M + 127) / 128));
-        linear_f32_kernel<8, 8><<<grid, 256, 0, s>>>(A, lda, W, ldw, bias, Y, ldy, (int)M, N, K, act, slope);
+        ccn_launch(linear_f32_kernel<8, 8>, dim3(grid), dim3(256), 0, s, A, lda, W, ldw, bias, Y, ldy, (int)M, N, K, act, slope);
     } else {
         dim3 grid((N + 63) / 64, (unsigned)((M + 63) / 64));
-        linear_f32_kernel<4, 4><<<grid, 256, 0, s>>>(A, lda, W, ldw, bias, Y, ldy, (int)M, N, K, act, slope);
+        ccn_launch(linear_f32_kernel<4, 4>, dim3(grid), dim3(256), 0, s, A, lda, W, ldw, bias, Y, ldy, (int)M, N, K, act, slope);
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;

@@ -35,6 +35,7 @@ __global__ void __launch_bounds__(kThreads) linear_tc_kernel(
     const float* __restrict__ A, int64_t lda, const __grid_constant__ CUtensorMap w_hi,
     const __grid_constant__ CUtensorMap w_lo, const float* __restrict__ bias, float* __restrict__ Y, int64_t ldy,
     int M, int N, int K, int BN, int stages, int act, float slope) {
+    ccn_pdl_wait();
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * 8 + 1];     // full[8], empty[8], tmem_full
     __shared__ uint32_t tmem_base_slot;
@@ -204,6 +205,7 @@ __global__ void __launch_bounds__(kThreads) linear_tc_kernel(
 // fp32 (N, K) -> bf16 hi (N, Kpad) and residual lo = bf16(w - hi), zero padded along K.
 __global__ void split_bf16_kernel(const float* __restrict__ w, int64_t ldw, int n, int k, int kpad,
                                   __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+    ccn_pdl_wait();
     const int64_t total = (int64_t)n * kpad;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t r = t / kpad;
@@ -220,7 +222,7 @@ __global__ void split_bf16_kernel(const float* __restrict__ w, int64_t ldw, int 
 extern "C" int ccn_split_bf16(const float* w, int64_t ldw, int32_t n, int32_t k, int32_t kpad, void* hi, void* lo,
                               ccn_stream_t stream) {
     CCN_REQUIRE(w && hi && n > 0 && k > 0 && kpad >= k && (kpad % kBK) == 0 && ldw >= k);
-    split_bf16_kernel<<<ccn_grid((int64_t)n * kpad, 256), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(split_bf16_kernel, dim3(ccn_grid((int64_t)n * kpad, 256)), dim3(256), 0, (cudaStream_t)stream, 
         w, ldw, n, k, kpad, (__nv_bfloat16*)hi, (__nv_bfloat16*)lo);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -287,7 +289,7 @@ extern "C" int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_
             if (e != cudaSuccess) return (int)e;
             attr3 = true;
         }
-        linear_tc_kernel<3><<<grid, kThreads, smem, s>>>(A, lda, *hi, *lo, bias, Y, ldy, (int)M, N, K, box_n, stages, act, slope);
+        ccn_launch(linear_tc_kernel<3>, dim3(grid), dim3(kThreads), smem, s, A, lda, *hi, *lo, bias, Y, ldy, (int)M, N, K, box_n, stages, act, slope);
     } else {
         static bool attr1 = false;
         if (!attr1) {
@@ -295,7 +297,7 @@ extern "C" int ccn_linear_tc(const float* A, int64_t lda, const void* w_hi_tmap_
             if (e != cudaSuccess) return (int)e;
             attr1 = true;
         }
-        linear_tc_kernel<1><<<grid, kThreads, smem, s>>>(A, lda, *hi, *lo, bias, Y, ldy, (int)M, N, K, box_n, stages, act, slope);
+        ccn_launch(linear_tc_kernel<1>, dim3(grid), dim3(kThreads), smem, s, A, lda, *hi, *lo, bias, Y, ldy, (int)M, N, K, box_n, stages, act, slope);
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;

@@ -55,6 +55,7 @@ template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1) wgrad_tc_kernel(
     const __grid_constant__ CUtensorMap dy_hi, const __grid_constant__ CUtensorMap dy_lo,
     const __grid_constant__ CUtensorMap x_hi, const __grid_constant__ CUtensorMap x_lo, const WgradParams p) {
+    ccn_pdl_wait();
     constexpr int P = MODE == 3 ? 2 : 1;
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 1];     // full[S], empty[S], tfull
@@ -176,6 +177,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_tc_kernel(
 // out[c] += sum_r src[r][c]   (bias gradient)
 __global__ void __launch_bounds__(256) col_sum_kernel(const float* __restrict__ src, int64_t ld, int64_t M, int C,
                                                       int64_t rows_per_cta, float* __restrict__ out) {
+    ccn_pdl_wait();
     const int cw = C >= 256 ? 256 : C;
     const int lanes = 256 / cw;
     const int col = blockIdx.y * 256 + (threadIdx.x % cw);
@@ -203,7 +205,7 @@ extern "C" int ccn_col_sum(const float* src, int64_t ld, int64_t M, int32_t C, f
     if (gx < 1) gx = 1;
     const int64_t rpc = (M + gx - 1) / gx;
     gx = (M + rpc - 1) / rpc;
-    col_sum_kernel<<<dim3((unsigned)gx, (unsigned)gy), 256, 0, (cudaStream_t)stream>>>(src, ld, M, C, rpc, out);
+    ccn_launch(col_sum_kernel, dim3(dim3((unsigned)gx, (unsigned)gy)), dim3(256), 0, (cudaStream_t)stream, src, ld, M, C, rpc, out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -257,7 +259,7 @@ extern "C" int ccn_linear_wgrad_tc(const void* dy_planes, int64_t dy_ld, int64_t
             if (e != cudaSuccess) return (int)e;
             attr3 = true;
         }
-        wgrad_tc_kernel<3><<<grid, kThreads, smem, s>>>(maps[0], maps[1], maps[2], maps[3], p);
+        ccn_launch(wgrad_tc_kernel<3>, dim3(grid), dim3(kThreads), smem, s, maps[0], maps[1], maps[2], maps[3], p);
     } else {
         static bool attr1 = false;
         if (!attr1) {
@@ -265,7 +267,7 @@ extern "C" int ccn_linear_wgrad_tc(const void* dy_planes, int64_t dy_ld, int64_t
             if (e != cudaSuccess) return (int)e;
             attr1 = true;
         }
-        wgrad_tc_kernel<1><<<grid, kThreads, smem, s>>>(maps[0], maps[1], maps[2], maps[3], p);
+        ccn_launch(wgrad_tc_kernel<1>, dim3(grid), dim3(kThreads), smem, s, maps[0], maps[1], maps[2], maps[3], p);
     }
     CCN_CHECK_LAUNCH();
     return CCN_OK;

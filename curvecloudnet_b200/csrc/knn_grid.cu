@@ -29,12 +29,14 @@ __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i
 
 // meta (int32[16]): [0..2] min xyz (ordered ints), [3..5] max xyz, [6] open-query count, [8] h bits, [9] 1/h bits
 __global__ void kg_init_kernel(int32_t* meta) {
+    ccn_pdl_wait();
     if (threadIdx.x < 3) meta[threadIdx.x] = 0x7fffffff;
     else if (threadIdx.x < 6) meta[threadIdx.x] = (int)0x80000000;
     else if (threadIdx.x < 16) meta[threadIdx.x] = 0;
 }
 
 __global__ void kg_bbox_kernel(const float* __restrict__ pos, int64_t n, int32_t* meta) {
+    ccn_pdl_wait();
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
 #pragma unroll
@@ -58,6 +60,7 @@ __global__ void kg_bbox_kernel(const float* __restrict__ pos, int64_t n, int32_t
 }
 
 __global__ void kg_cell_kernel(int32_t* meta, int64_t n2, float cell_given) {
+    ccn_pdl_wait();
     float h = cell_given;
     if (!(h > 0.f)) {
         float e[3];
@@ -79,6 +82,7 @@ __global__ void kg_cell_kernel(int32_t* meta, int64_t n2, float cell_given) {
 __global__ void kg_count_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int64_t n,
                                 const int32_t* __restrict__ meta, unsigned mask, int32_t* __restrict__ cell_cnt,
                                 int32_t* __restrict__ slot) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float inv_cell = __int_as_float(meta[9]);
@@ -90,6 +94,7 @@ __global__ void kg_count_kernel(const float* __restrict__ pos, const int64_t* __
 __global__ void kg_fill_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int64_t n,
                                const int32_t* __restrict__ meta, unsigned mask, const int32_t* __restrict__ cell_off,
                                const int32_t* __restrict__ slot, float4* __restrict__ sorted) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float inv_cell = __int_as_float(meta[9]);
@@ -118,6 +123,7 @@ __global__ void __launch_bounds__(128) kg_search_kernel(
     const int32_t* __restrict__ cell_off, const int32_t* __restrict__ sptr2, int32_t* __restrict__ meta, unsigned mask,
     int Kout, int32_t* __restrict__ open_list, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
     int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
     const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (q >= n1) return;
     const float h = __int_as_float(meta[8]), inv_cell = __int_as_float(meta[9]);
@@ -172,6 +178,7 @@ __global__ void __launch_bounds__(256) kg_open_kernel(
     const float* __restrict__ p1, const int64_t* __restrict__ batch1, const float* __restrict__ p2,
     const int32_t* __restrict__ sptr2, const int32_t* __restrict__ meta, const int32_t* __restrict__ open_list, int Kout,
     int zero_fill, int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
     const int n_open = meta[6];
     const int lane = threadIdx.x & 31;
     for (int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < n_open; w += (gridDim.x * blockDim.x) >> 5) {
@@ -214,10 +221,10 @@ template <int K>
 int launch_search(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const float4* sorted,
                   const int32_t* cell_off, const int32_t* sptr2, int32_t* meta, unsigned mask, int Kout, int zero_fill,
                   int32_t* open_list, int32_t* idx_out, float* d2_out, int32_t* cnt_out, cudaStream_t s) {
-    kg_search_kernel<K><<<ccn_blocks_exact(n1, 128), 128, 0, s>>>(pos1, batch1, n1, sorted, cell_off, sptr2, meta, mask, Kout,
+    ccn_launch(kg_search_kernel<K>, dim3(ccn_blocks_exact(n1, 128)), dim3(128), 0, s, pos1, batch1, n1, sorted, cell_off, sptr2, meta, mask, Kout,
                                                                   open_list, idx_out, d2_out, cnt_out);
     CCN_CHECK_LAUNCH();
-    kg_open_kernel<K><<<148 * 4, 256, 0, s>>>(pos1, batch1, pos2, sptr2, meta, open_list, Kout, zero_fill, idx_out, d2_out, cnt_out);
+    ccn_launch(kg_open_kernel<K>, dim3(148 * 4), dim3(256), 0, s, pos1, batch1, pos2, sptr2, meta, open_list, Kout, zero_fill, idx_out, d2_out, cnt_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -238,27 +245,27 @@ extern "C" int ccn_knn_grid(const float* pos1, const int64_t* batch1, int64_t n1
     int32_t* meta = open_scratch;                 // 16 ints, then the open-query list (n1 ints)
     int32_t* open_list = open_scratch + 16;
     const unsigned mask = (unsigned)(num_cells - 1);
-    kg_init_kernel<<<1, 32, 0, s>>>(meta);
+    ccn_launch(kg_init_kernel, dim3(1), dim3(32), 0, s, meta);
     CCN_CHECK_LAUNCH();
     cudaError_t e = cudaMemsetAsync(cell_off, 0, (num_cells + 1) * sizeof(int32_t), s);
     if (e != cudaSuccess) return (int)e;
     if (n2 > 0) {
         if (!(cell > 0.f)) {
-            kg_bbox_kernel<<<ccn_grid(n2, 256, 148LL * 4), 256, 0, s>>>(pos2, n2, meta);
+            ccn_launch(kg_bbox_kernel, dim3(ccn_grid(n2, 256, 148LL * 4)), dim3(256), 0, s, pos2, n2, meta);
             CCN_CHECK_LAUNCH();
         }
-        kg_cell_kernel<<<1, 1, 0, s>>>(meta, n2, cell);
+        ccn_launch(kg_cell_kernel, dim3(1), dim3(1), 0, s, meta, n2, cell);
         CCN_CHECK_LAUNCH();
-        kg_count_kernel<<<ccn_blocks_exact(n2, 256), 256, 0, s>>>(pos2, batch2, n2, meta, mask, cell_off, slot_scratch);
+        ccn_launch(kg_count_kernel, dim3(ccn_blocks_exact(n2, 256)), dim3(256), 0, s, pos2, batch2, n2, meta, mask, cell_off, slot_scratch);
         CCN_CHECK_LAUNCH();
     } else {
-        kg_cell_kernel<<<1, 1, 0, s>>>(meta, 1, 1.f);
+        ccn_launch(kg_cell_kernel, dim3(1), dim3(1), 0, s, meta, 1, 1.f);
         CCN_CHECK_LAUNCH();
     }
     const int rc = ccn_excl_scan_i32(cell_off, num_cells, nullptr, stream);
     if (rc) return rc;
     if (n2 > 0) {
-        kg_fill_kernel<<<ccn_blocks_exact(n2, 256), 256, 0, s>>>(pos2, batch2, n2, meta, mask, cell_off, slot_scratch,
+        ccn_launch(kg_fill_kernel, dim3(ccn_blocks_exact(n2, 256)), dim3(256), 0, s, pos2, batch2, n2, meta, mask, cell_off, slot_scratch,
                                                                 (float4*)sorted_xyzi);
         CCN_CHECK_LAUNCH();
     }

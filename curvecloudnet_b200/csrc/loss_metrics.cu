@@ -27,6 +27,7 @@ __device__ __forceinline__ float row_lse(const float* row, int C) {
 __global__ void lovasz_keys_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target,
                                    int64_t n, int C, int64_t ignore, int64_t npad, unsigned long long* __restrict__ keys,
                                    int32_t* __restrict__ fg_count, float* __restrict__ lse) {
+    ccn_pdl_wait();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < npad; i += (int64_t)gridDim.x * blockDim.x) {
         if (i >= n) {
             for (int c = 0; c < C; ++c) keys[(int64_t)c * npad + i] = 0ull;
@@ -58,6 +59,7 @@ __device__ __forceinline__ void cmp_swap(unsigned long long& a, unsigned long lo
 // One CTA per class: bitonic sort (descending) of npad keys in global memory.
 __global__ void __launch_bounds__(kSortThreads) lovasz_sort_kernel(unsigned long long* __restrict__ keys, int64_t npad,
                                                                    const int32_t* __restrict__ fg_count) {
+    ccn_pdl_wait();
     __shared__ unsigned long long tile[kTile];
     const int c = blockIdx.x;
     if (fg_count[c] == 0) return;                       // class absent: skipped like classes='present'
@@ -125,6 +127,7 @@ __global__ void __launch_bounds__(kSortThreads) lovasz_scan_kernel(const unsigne
                                                                    int64_t npad, const int32_t* __restrict__ fg_count,
                                                                    float* __restrict__ grad,
                                                                    int64_t n, double* __restrict__ acc) {
+    ccn_pdl_wait();
     __shared__ int scan_smem[33];
     __shared__ double red[kSortThreads / 32];
     const int c = blockIdx.x;
@@ -170,6 +173,7 @@ __global__ void __launch_bounds__(kSortThreads) lovasz_scan_kernel(const unsigne
 }
 
 __global__ void lovasz_finish_kernel(const double* __restrict__ acc, float* __restrict__ loss) {
+    ccn_pdl_wait();
     loss[0] = acc[1] > 0.0 ? (float)(acc[0] / acc[1]) : 0.f;
 }
 
@@ -179,6 +183,7 @@ __global__ void lovasz_bwd_kernel(const float* __restrict__ logits, int64_t ld, 
                                   const float* __restrict__ grad, const int32_t* __restrict__ fg_count,
                                   const double* __restrict__ acc, const float* __restrict__ gscale,
                                   float* __restrict__ dlogits, int64_t ldd, int accumulate) {
+    ccn_pdl_wait();
     const float sc = acc[1] > 0.0 ? gscale[0] / (float)acc[1] : 0.f;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t y = target[i];
@@ -216,6 +221,7 @@ __global__ void lovasz_bwd_kernel(const float* __restrict__ logits, int64_t ld, 
 __global__ void confusion_hist_kernel(const float* __restrict__ scores, int64_t ld, int C, const int64_t* __restrict__ pred_in,
                                       const int64_t* __restrict__ target, int64_t n, int ncls, int col_offset,
                                       int64_t* __restrict__ pred_out, unsigned long long* __restrict__ hist) {
+    ccn_pdl_wait();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         int64_t p;
         if (scores) {
@@ -236,6 +242,7 @@ __global__ void confusion_hist_kernel(const float* __restrict__ scores, int64_t 
 
 // out = [sx * x, sy * y, z]                                     (the flips / scales of val(), nuscenes_seg.py:93-104)
 __global__ void scale_xy_kernel(const float* __restrict__ pos, int64_t n, float sx, float sy, float* __restrict__ out) {
+    ccn_pdl_wait();
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < 3 * n; t += (int64_t)gridDim.x * blockDim.x) {
         const int a = (int)(t % 3);
         const float v = pos[t];
@@ -246,6 +253,7 @@ __global__ void scale_xy_kernel(const float* __restrict__ pos, int64_t n, float 
 // acc (+)= src                                                  (sum(outs) of the augmented forwards)
 __global__ void accumulate_kernel(const float* __restrict__ src, int64_t lds, int64_t n, int C, float* __restrict__ acc,
                                   int64_t lda, int first) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)C;
     for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         int64_t r;
@@ -259,6 +267,7 @@ __global__ void accumulate_kernel(const float* __restrict__ src, int64_t lds, in
 // out = log_softmax(acc * scale, dim=-1); pred = arg-max              (out = sum(outs) / 12; F.log_softmax; argmax)
 __global__ void mean_logsoftmax_kernel(const float* __restrict__ acc, int64_t lda, int64_t n, int C, float scale,
                                        float* __restrict__ out, int64_t ldo, int64_t* __restrict__ pred) {
+    ccn_pdl_wait();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         const float* row = acc + i * lda;
         float m = -INFINITY;
@@ -297,14 +306,14 @@ extern "C" int ccn_lovasz_softmax_fwd(const float* logits, int64_t ld, const int
     if (e == cudaSuccess) e = cudaMemsetAsync(acc, 0, 2 * sizeof(double), S_);
     if (e == cudaSuccess) e = cudaMemsetAsync(grad, 0, (size_t)C * n * sizeof(float), S_);
     if (e != cudaSuccess) return (int)e;
-    lovasz_keys_kernel<<<PT_GRID(npad), 128, 0, S_>>>(logits, ld, target, n, C, ignore_index, npad,
+    ccn_launch(lovasz_keys_kernel, dim3(PT_GRID(npad)), dim3(128), 0, S_, logits, ld, target, n, C, ignore_index, npad,
                                                       (unsigned long long*)keys, fg_count, lse);
     CCN_CHECK_LAUNCH();
-    lovasz_sort_kernel<<<C, kSortThreads, 0, S_>>>((unsigned long long*)keys, npad, fg_count);
+    ccn_launch(lovasz_sort_kernel, dim3(C), dim3(kSortThreads), 0, S_, (unsigned long long*)keys, npad, fg_count);
     CCN_CHECK_LAUNCH();
-    lovasz_scan_kernel<<<C, kSortThreads, 0, S_>>>((const unsigned long long*)keys, npad, fg_count, grad, n, acc);
+    ccn_launch(lovasz_scan_kernel, dim3(C), dim3(kSortThreads), 0, S_, (const unsigned long long*)keys, npad, fg_count, grad, n, acc);
     CCN_CHECK_LAUNCH();
-    lovasz_finish_kernel<<<1, 1, 0, S_>>>(acc, loss);
+    ccn_launch(lovasz_finish_kernel, dim3(1), dim3(1), 0, S_, acc, loss);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -315,7 +324,7 @@ extern "C" int ccn_lovasz_softmax_bwd(const float* logits, int64_t ld, const int
                                       int32_t accumulate, ccn_stream_t stream) {
     CCN_REQUIRE(n > 0 && C > 0 && logits && target && lse && grad && fg_count && acc && gscale && dlogits && ld >= C &&
                 ldd >= C);
-    lovasz_bwd_kernel<<<PT_GRID(n), 128, 0, S_>>>(logits, ld, target, n, C, ignore_index, lse, grad, fg_count, acc, gscale,
+    ccn_launch(lovasz_bwd_kernel, dim3(PT_GRID(n)), dim3(128), 0, S_, logits, ld, target, n, C, ignore_index, lse, grad, fg_count, acc, gscale,
                                                   dlogits, ldd, accumulate);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -328,7 +337,7 @@ extern "C" int ccn_confusion_hist(const float* scores, int64_t ld, int32_t C, co
     CCN_REQUIRE(n >= 0 && (scores || pred_in) && (!scores || (C > 0 && ld >= C && col_offset >= 0 && col_offset < C)));
     CCN_REQUIRE((!hist || (target && ncls > 0)) && (hist || pred_out));
     if (n == 0) return CCN_OK;
-    confusion_hist_kernel<<<PT_GRID(n), 128, 0, S_>>>(scores, ld, C, pred_in, target, n, ncls, col_offset, pred_out,
+    ccn_launch(confusion_hist_kernel, dim3(PT_GRID(n)), dim3(128), 0, S_, scores, ld, C, pred_in, target, n, ncls, col_offset, pred_out,
                                                       (unsigned long long*)hist);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -337,7 +346,7 @@ extern "C" int ccn_confusion_hist(const float* scores, int64_t ld, int32_t C, co
 extern "C" int ccn_scale_xy(const float* pos, int64_t n, float sx, float sy, float* out, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && (n == 0 || (pos && out)));
     if (n == 0) return CCN_OK;
-    scale_xy_kernel<<<ccn_grid(3 * n, 256, 148 * 8), 256, 0, S_>>>(pos, n, sx, sy, out);
+    ccn_launch(scale_xy_kernel, dim3(ccn_grid(3 * n, 256, 148 * 8)), dim3(256), 0, S_, pos, n, sx, sy, out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -346,7 +355,7 @@ extern "C" int ccn_accumulate(const float* src, int64_t lds, int64_t n, int32_t 
                               ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && C > 0 && (n == 0 || (src && acc)) && lds >= C && lda >= C);
     if (n == 0) return CCN_OK;
-    accumulate_kernel<<<ccn_grid(n * C, 256, 148 * 8), 256, 0, S_>>>(src, lds, n, C, acc, lda, first);
+    ccn_launch(accumulate_kernel, dim3(ccn_grid(n * C, 256, 148 * 8)), dim3(256), 0, S_, src, lds, n, C, acc, lda, first);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -355,7 +364,7 @@ extern "C" int ccn_mean_logsoftmax(const float* acc, int64_t lda, int64_t n, int
                                    int64_t ldo, int64_t* pred, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && C > 0 && (n == 0 || (acc && out)) && lda >= C && ldo >= C);
     if (n == 0) return CCN_OK;
-    mean_logsoftmax_kernel<<<PT_GRID(n), 128, 0, S_>>>(acc, lda, n, C, scale, out, ldo, pred);
+    ccn_launch(mean_logsoftmax_kernel, dim3(PT_GRID(n)), dim3(128), 0, S_, acc, lda, n, C, scale, out, ldo, pred);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

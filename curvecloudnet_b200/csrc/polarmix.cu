@@ -30,6 +30,7 @@ __device__ __forceinline__ bool in_sector(float x, float y, float lo, float hi) 
 __global__ void pm_flags_kernel(const float* __restrict__ pos1, int64_t n1, const float* __restrict__ pos2,
                                 const int64_t* __restrict__ cid2, int64_t n2, int do_swap, float lo, float hi,
                                 int32_t* __restrict__ keep1, int32_t* __restrict__ take2, int32_t* __restrict__ start2) {
+    ccn_pdl_wait();
     const int64_t n = n1 > n2 ? n1 : n2;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         if (i < n1) keep1[i] = !(do_swap && in_sector(pos1[3 * i], pos1[3 * i + 1], lo, hi));
@@ -46,6 +47,7 @@ __global__ void pm_flags_kernel(const float* __restrict__ pos1, int64_t n1, cons
 __global__ void pm_curve_count_kernel(const int64_t* __restrict__ y2, const int32_t* __restrict__ start2,
                                       const int32_t* __restrict__ n_curves2, ClassPos cp, int do_paste,
                                       int32_t* __restrict__ icnt, int64_t cap) {
+    ccn_pdl_wait();
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t C = *n_curves2;
@@ -80,6 +82,7 @@ __global__ void pm_emit_swap_kernel(const float* __restrict__ pos1, const float*
                                     const float* __restrict__ pos2, const float* __restrict__ x2,
                                     const int64_t* __restrict__ y2, const int64_t* __restrict__ cid2, int64_t n2,
                                     const int32_t* __restrict__ keep1, const int32_t* __restrict__ take2, PmOut o) {
+    ccn_pdl_wait();
     const int64_t n = n1 > n2 ? n1 : n2;
     const int64_t K1 = keep1[n1];
     const int64_t off2 = n1 > 0 ? cid1[n1 - 1] : 0;                    // curve_idxs2 += max(curve_idxs_orig)
@@ -105,6 +108,7 @@ __global__ void pm_emit_paste_kernel(const float* __restrict__ pos2, const float
                                      const int32_t* __restrict__ keep1, const int32_t* __restrict__ take2,
                                      ClassPos cp, int n_cls, double c0, double s0, double c1, double s1, PmOut o,
                                      int64_t cap) {
+    ccn_pdl_wait();
     const int lane = threadIdx.x & 31;
     const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5, nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t C = *n_curves2;
@@ -158,6 +162,7 @@ __global__ void pm_change_flags_kernel(const int64_t* __restrict__ cid, const in
                                        const int32_t* __restrict__ take2, int64_t n2, const int32_t* __restrict__ ioff,
                                        int64_t cap, int do_paste, int32_t* __restrict__ flag, int64_t n_max,
                                        int32_t* __restrict__ n_out) {
+    ccn_pdl_wait();
     const int64_t N = (int64_t)keep1[n1] + take2[n2] + (do_paste ? 3 * (int64_t)ioff[cap] : 0);
     if (blockIdx.x == 0 && threadIdx.x == 0) *n_out = (int32_t)N;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n_max; i += (int64_t)gridDim.x * blockDim.x)
@@ -166,6 +171,7 @@ __global__ void pm_change_flags_kernel(const int64_t* __restrict__ cid, const in
 
 __global__ void pm_dense_ids_kernel(const int32_t* __restrict__ flag, int64_t n_max, const int32_t* __restrict__ n_out,
                                     int64_t* __restrict__ cid, int32_t* __restrict__ n_curves_out) {
+    ccn_pdl_wait();
     // flag holds the EXCLUSIVE scan of the change flags: inclusive = exclusive of the next element
     const int64_t N = *n_out;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
@@ -182,6 +188,7 @@ struct Augment {
 
 __global__ void augment_points_kernel(const float* __restrict__ in, int64_t n, int on, Augment a, float pos_div,
                                       float* __restrict__ out) {
+    ccn_pdl_wait();
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
         float px = in[3 * j], py = in[3 * j + 1], pz = in[3 * j + 2];
         if (on) {
@@ -229,31 +236,31 @@ extern "C" int ccn_polarmix(const float* pos1, const float* x1, const int64_t* y
     int32_t* start2 = take2 + (n2 + 1);                       // [n2 + 1]
     int32_t* icnt = start2 + (n2 + 2);                        // [n2 + 1]
     int32_t* flag = icnt + (n2 + 2);                          // [n_max + 1]
-    pm_flags_kernel<<<ccn_grid(n1 > n2 ? n1 : n2, 256, 148 * 8), 256, 0, s>>>(pos1, n1, pos2, cid2, n2, do_swap, alpha, beta,
+    ccn_launch(pm_flags_kernel, dim3(ccn_grid(n1 > n2 ? n1 : n2, 256, 148 * 8)), dim3(256), 0, s, pos1, n1, pos2, cid2, n2, do_swap, alpha, beta,
                                                                                keep1, take2, start2);
     CCN_CHECK_LAUNCH();
-    pm_curve_count_kernel<<<ccn_grid(cap * 32, 256, 148 * 8), 256, 0, s>>>(y2, start2, n_curves2, cp, do_paste, icnt, cap);
+    ccn_launch(pm_curve_count_kernel, dim3(ccn_grid(cap * 32, 256, 148 * 8)), dim3(256), 0, s, y2, start2, n_curves2, cp, do_paste, icnt, cap);
     CCN_CHECK_LAUNCH();
     int rc = ccn_excl_scan_i32(keep1, n1, nullptr, stream);
     if (rc == CCN_OK) rc = ccn_excl_scan_i32(take2, n2, nullptr, stream);
     if (rc == CCN_OK) rc = ccn_excl_scan_i32(icnt, cap, nullptr, stream);
     if (rc != CCN_OK) return rc;
     PmOut o{pos_out, x_out, y_out, cid_out};
-    pm_emit_swap_kernel<<<ccn_grid(n1 > n2 ? n1 : n2, 256, 148 * 8), 256, 0, s>>>(pos1, x1, y1, cid1, n1, pos2, x2, y2, cid2,
+    ccn_launch(pm_emit_swap_kernel, dim3(ccn_grid(n1 > n2 ? n1 : n2, 256, 148 * 8)), dim3(256), 0, s, pos1, x1, y1, cid1, n1, pos2, x2, y2, cid2,
                                                                                    n2, keep1, take2, o);
     CCN_CHECK_LAUNCH();
     if (do_paste) {
-        pm_emit_paste_kernel<<<ccn_grid(cap * 32, 256, 148 * 8), 256, 0, s>>>(
+        ccn_launch(pm_emit_paste_kernel, dim3(ccn_grid(cap * 32, 256, 148 * 8)), dim3(256), 0, s, 
             pos2, x2, y2, cid2, n2, cid1, n1, start2, n_curves2, icnt, keep1, take2, cp, n_classes, cos(omega0), sin(omega0),
             cos(omega1), sin(omega1), o, cap);
         CCN_CHECK_LAUNCH();
     }
-    pm_change_flags_kernel<<<ccn_grid(n_max, 256, 148 * 8), 256, 0, s>>>(cid_out, keep1, n1, take2, n2, icnt, cap, do_paste,
+    ccn_launch(pm_change_flags_kernel, dim3(ccn_grid(n_max, 256, 148 * 8)), dim3(256), 0, s, cid_out, keep1, n1, take2, n2, icnt, cap, do_paste,
                                                                           flag, n_max, counts_out);
     CCN_CHECK_LAUNCH();
     rc = ccn_excl_scan_i32(flag, n_max, nullptr, stream);
     if (rc != CCN_OK) return rc;
-    pm_dense_ids_kernel<<<ccn_grid(n_max, 256, 148 * 8), 256, 0, s>>>(flag, n_max, counts_out, cid_out, counts_out + 1);
+    ccn_launch(pm_dense_ids_kernel, dim3(ccn_grid(n_max, 256, 148 * 8)), dim3(256), 0, s, flag, n_max, counts_out, cid_out, counts_out + 1);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -266,7 +273,7 @@ extern "C" int ccn_augment_points(const float* pos_in, int64_t n, int32_t augmen
     CCN_REQUIRE(pos_in && pos_out);
     Augment a;
     a.c = rot_c; a.s = rot_s; a.flip = flip_type; a.scale = scale; a.tx = tx; a.ty = ty; a.tz = tz;
-    augment_points_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(pos_in, n, augment, a, pos_div, pos_out);
+    ccn_launch(augment_points_kernel, dim3(ccn_grid(n, 256, 148 * 8)), dim3(256), 0, (cudaStream_t)stream, pos_in, n, augment, a, pos_div, pos_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

@@ -22,6 +22,7 @@ __global__ void voxel_insert_kernel(const float* __restrict__ pos, const int64_t
                                     float voxel, const float* __restrict__ noise, unsigned long long tmask,
                                     unsigned long long* __restrict__ tkeys, unsigned long long* __restrict__ tmin,
                                     int32_t* __restrict__ err) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     // pos / voxel, floor, |floor - pos/voxel| + noise * voxel / 4   (fps_ops.py:52-57)
@@ -56,6 +57,7 @@ __global__ void voxel_compact_kernel(const unsigned long long* __restrict__ tkey
                                      const unsigned long long* __restrict__ tmin, int64_t slots,
                                      unsigned long long* __restrict__ ukeys, int32_t* __restrict__ uwin,
                                      int32_t* __restrict__ count) {
+    ccn_pdl_wait();
     const int64_t s = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (s >= slots) return;
     const unsigned long long k = tkeys[s];
@@ -70,6 +72,7 @@ constexpr int kRankChunk = 2048;
 __global__ void __launch_bounds__(256) rank_keys_kernel(const unsigned long long* __restrict__ keys,
                                                         const int32_t* __restrict__ count_ptr,
                                                         int32_t* __restrict__ rank) {
+    ccn_pdl_wait();
     __shared__ unsigned long long tile[256];
     const int n = *count_ptr;
     const int i = blockIdx.x * 256 + threadIdx.x;
@@ -90,6 +93,7 @@ __global__ void __launch_bounds__(256) rank_keys_kernel(const unsigned long long
 
 __global__ void scatter_by_rank_kernel(const int32_t* __restrict__ rank, const int32_t* __restrict__ uwin,
                                        const int32_t* __restrict__ count_ptr, int64_t* __restrict__ idx_out) {
+    ccn_pdl_wait();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < *count_ptr) idx_out[rank[i]] = uwin[i];
 }
@@ -112,6 +116,7 @@ __global__ void __launch_bounds__(THREADS) fps_kernel(const float* __restrict__ 
                                                           const int32_t* __restrict__ start,
                                                           float* __restrict__ closest_scratch,
                                                           int32_t* __restrict__ sel_cnt) {
+    ccn_pdl_wait();
     __shared__ FpsPartial part[2][THREADS / 32];
     const int b = blockIdx.x;
     const int lo = sptr[b], len = sptr[b + 1] - lo;
@@ -184,6 +189,7 @@ __global__ void __launch_bounds__(THREADS) fps_kernel(const float* __restrict__ 
 __global__ void __launch_bounds__(1024) expand_counts_kernel(const int32_t* __restrict__ cnt, int64_t n,
                                                              int64_t* __restrict__ idx_out,
                                                              int32_t* __restrict__ total_out) {
+    ccn_pdl_wait();
     __shared__ int sm[33];
     int carry = 0;
     for (int64_t base = 0; base < n; base += 1024) {
@@ -219,18 +225,18 @@ extern "C" int ccn_voxel_fps(const float* pos, const int64_t* batch, int64_t n, 
     if ((e = cudaMemsetAsync(rank, 0, (n > 0 ? n : 1) * 4, s)) != cudaSuccess) return (int)e;
     if ((e = cudaMemsetAsync(counts, 0, 2 * 4, s)) != cudaSuccess) return (int)e;
     if (n == 0) return CCN_OK;
-    voxel_insert_kernel<<<ccn_blocks_exact(n, 256), 256, 0, s>>>(pos, batch, n, voxel, noise, (unsigned long long)(slots - 1),
+    ccn_launch(voxel_insert_kernel, dim3(ccn_blocks_exact(n, 256)), dim3(256), 0, s, pos, batch, n, voxel, noise, (unsigned long long)(slots - 1),
                                                                 (unsigned long long*)table_keys,
                                                                 (unsigned long long*)table_min, counts + 1);
     CCN_CHECK_LAUNCH();
-    voxel_compact_kernel<<<ccn_blocks_exact(slots, 256), 256, 0, s>>>((unsigned long long*)table_keys,
+    ccn_launch(voxel_compact_kernel, dim3(ccn_blocks_exact(slots, 256)), dim3(256), 0, s, (unsigned long long*)table_keys,
                                                                      (unsigned long long*)table_min, slots,
                                                                      (unsigned long long*)ukeys, uwin, counts);
     CCN_CHECK_LAUNCH();
     dim3 grid(ccn_blocks_exact(n, 256), ccn_blocks_exact(n, kRankChunk));
-    rank_keys_kernel<<<grid, 256, 0, s>>>((unsigned long long*)ukeys, counts, rank);
+    ccn_launch(rank_keys_kernel, dim3(grid), dim3(256), 0, s, (unsigned long long*)ukeys, counts, rank);
     CCN_CHECK_LAUNCH();
-    scatter_by_rank_kernel<<<ccn_blocks_exact(n, 256), 256, 0, s>>>(rank, uwin, counts, idx_out);
+    ccn_launch(scatter_by_rank_kernel, dim3(ccn_blocks_exact(n, 256)), dim3(256), 0, s, rank, uwin, counts, idx_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -243,7 +249,7 @@ extern "C" int ccn_fps(const float* pos, const int32_t* sample_ptr, int32_t n_sa
     cudaError_t e = cudaMemsetAsync(sel_cnt_scratch, 0, (n > 0 ? n : 1) * 4, s);
     if (e != cudaSuccess) return (int)e;
     if (n_samples > 0 && n > 0) {
-#define CCN_FPS_LAUNCH(PPT, T) fps_kernel<PPT, T><<<n_samples, T, 0, s>>>(pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch)
+#define CCN_FPS_LAUNCH(PPT, T) ccn_launch(fps_kernel<PPT, T>, dim3(n_samples), dim3(T), 0, s, pos, sample_ptr, ksel, start, closest_scratch, sel_cnt_scratch)
         // measured (tools/bench_fps.py, profiles/r02o_fps_variants.txt): a round costs ~0.5 us whatever the split - 4 warps x 16
         // points 0.95 us, 32 warps x 2 points 0.60 us, 16 warps x 4 points 0.50 us (kept): the round is the latency chain
         // distance -> warp argmax -> shared memory -> barrier -> block argmax, not arithmetic, so a CTA cluster per cloud (a
@@ -259,7 +265,7 @@ extern "C" int ccn_fps(const float* pos, const int32_t* sample_ptr, int32_t n_sa
 #undef CCN_FPS_LAUNCH
         CCN_CHECK_LAUNCH();
     }
-    expand_counts_kernel<<<1, 1024, 0, s>>>(sel_cnt_scratch, n, idx_out, total_out);
+    ccn_launch(expand_counts_kernel, dim3(1), dim3(1024), 0, s, sel_cnt_scratch, n, idx_out, total_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

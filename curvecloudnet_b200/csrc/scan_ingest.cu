@@ -24,6 +24,7 @@ struct Augment {
 };
 
 __global__ void ring_ids_kernel(const float* __restrict__ raw, int64_t n, int rec, int64_t* __restrict__ beam) {
+    ccn_pdl_wait();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         beam[i] = rec >= 5 ? (int64_t)raw[i * rec + 4] : 0;
 }
@@ -33,6 +34,7 @@ __global__ void ingest_finish_kernel(const float* __restrict__ raw, int rec, con
                                      const int64_t* __restrict__ reorder, const float* __restrict__ sorted_points,
                                      int64_t n, Augment a, float pos_div, float* __restrict__ pos, float* __restrict__ x,
                                      int64_t* __restrict__ y, int32_t* __restrict__ flags) {
+    ccn_pdl_wait();
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = reorder[j];
         x[j] = raw[i * rec + 3];
@@ -88,7 +90,7 @@ extern "C" int ccn_ingest_scan(const float* raw, int64_t n, int32_t rec, const v
     if (n > 0) CCN_REQUIRE(raw && beam_tmp && sorted_tmp && pos && x && y);
     cudaStream_t s = (cudaStream_t)stream;
     if (n > 0) {
-        ring_ids_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(raw, n, rec, beam_tmp);
+        ccn_launch(ring_ids_kernel, dim3(ccn_grid(n, 256, 148 * 8)), dim3(256), 0, s, raw, n, rec, beam_tmp);
         CCN_CHECK_LAUNCH();
     }
     const int rc = ccn_get_curves(raw, rec, beam_tmp, n, n_beams, curve_thresh, scratch, reorder, inv_reorder, sorted_tmp,
@@ -96,7 +98,7 @@ extern "C" int ccn_ingest_scan(const float* raw, int64_t n, int32_t rec, const v
     if (rc != CCN_OK || n == 0) return rc;
     Augment a;
     a.on = augment; a.c = rot_c; a.s = rot_s; a.flip = flip_type; a.scale = scale; a.tx = tx; a.ty = ty; a.tz = tz;
-    ingest_finish_kernel<<<ccn_grid(n, 256, 148 * 8), 256, 0, s>>>(raw, rec, labels, label_bytes, (uint32_t)label_mask, lut, lut_size,
+    ccn_launch(ingest_finish_kernel, dim3(ccn_grid(n, 256, 148 * 8)), dim3(256), 0, s, raw, rec, labels, label_bytes, (uint32_t)label_mask, lut, lut_size,
                                                                     reorder, sorted_tmp, n, a, pos_div, pos, x, y,
                                                                     counts_out + 1);
     CCN_CHECK_LAUNCH();

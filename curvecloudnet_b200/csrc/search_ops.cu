@@ -29,6 +29,7 @@ __device__ __forceinline__ int cell_of(float v, float inv_cell) { return __float
 __global__ void grid_count_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int64_t n,
                                   float inv_cell, unsigned mask, int32_t* __restrict__ cell_cnt,
                                   int32_t* __restrict__ slot) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const unsigned h = cell_hash((int)batch[i], cell_of(pos[3 * i], inv_cell), cell_of(pos[3 * i + 1], inv_cell),
@@ -39,6 +40,7 @@ __global__ void grid_count_kernel(const float* __restrict__ pos, const int64_t* 
 __global__ void grid_fill_kernel(const float* __restrict__ pos, const int64_t* __restrict__ batch, int64_t n,
                                  float inv_cell, unsigned mask, const int32_t* __restrict__ cell_off,
                                  const int32_t* __restrict__ slot, float4* __restrict__ sorted) {
+    ccn_pdl_wait();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float x = pos[3 * i], y = pos[3 * i + 1], z = pos[3 * i + 2];
@@ -77,6 +79,7 @@ __global__ void __launch_bounds__(256) frnn_knn_kernel(
     const float4* __restrict__ sorted, const int32_t* __restrict__ cell_off, const int32_t* __restrict__ sptr2,
     float inv_cell, unsigned mask, float r2, int K, int32_t* __restrict__ idx_out, float* __restrict__ d2_out,
     int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= n1) return;
     const int lane = ccn_lane();
@@ -134,6 +137,7 @@ __global__ void __launch_bounds__(256) knn_exact_kernel(
     const float* __restrict__ p1, const int64_t* __restrict__ batch1, int64_t n1, const float* __restrict__ p2,
     const int32_t* __restrict__ sptr2, int K, int zero_fill, int32_t* __restrict__ idx_out,
     float* __restrict__ d2_out, int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= n1) return;
     const int lane = ccn_lane();
@@ -196,6 +200,7 @@ __global__ void __launch_bounds__(256) knn_small_kernel(
     const float* __restrict__ p1, const int64_t* __restrict__ batch1, int64_t n1, const float* __restrict__ p2,
     const int32_t* __restrict__ sptr2, int Kout, int zero_fill, int32_t* __restrict__ idx_out,
     float* __restrict__ d2_out, int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
     __shared__ float sx[kSmallTile], sy[kSmallTile], sz[kSmallTile];
     __shared__ int s_lo, s_hi;
     const int sub = threadIdx.x & 7;
@@ -266,6 +271,7 @@ __global__ void __launch_bounds__(256) ball_query_kernel(
     const float* __restrict__ p1, const int64_t* __restrict__ batch1, int64_t n1, const float* __restrict__ p2,
     const int32_t* __restrict__ sptr2, float r2, int K, int32_t* __restrict__ idx_out,
     int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= n1) return;
     const int lane = ccn_lane();
@@ -307,14 +313,14 @@ extern "C" int ccn_grid_build(const float* pos2, const int64_t* batch2, int64_t 
     const float inv_cell = 1.f / (radius * 1.0001f);
     const unsigned mask = (unsigned)(num_cells - 1);
     if (n2 > 0) {
-        grid_count_kernel<<<ccn_blocks_exact(n2, 256), 256, 0, s>>>(pos2, batch2, n2, inv_cell, mask, cell_off,
+        ccn_launch(grid_count_kernel, dim3(ccn_blocks_exact(n2, 256)), dim3(256), 0, s, pos2, batch2, n2, inv_cell, mask, cell_off,
                                                                    slot_scratch);
         CCN_CHECK_LAUNCH();
     }
     int rc = ccn_excl_scan_i32(cell_off, num_cells, nullptr, stream);
     if (rc) return rc;
     if (n2 > 0) {
-        grid_fill_kernel<<<ccn_blocks_exact(n2, 256), 256, 0, s>>>(pos2, batch2, n2, inv_cell, mask, cell_off,
+        ccn_launch(grid_fill_kernel, dim3(ccn_blocks_exact(n2, 256)), dim3(256), 0, s, pos2, batch2, n2, inv_cell, mask, cell_off,
                                                                   slot_scratch, (float4*)sorted_xyzi);
         CCN_CHECK_LAUNCH();
     }
@@ -329,7 +335,7 @@ extern "C" int ccn_frnn_knn(const float* pos1, const int64_t* batch1, int64_t n1
     if (n1 == 0) return CCN_OK;
     const float inv_cell = 1.f / (radius * 1.0001f);
     const float r2 = radius * radius;      // f32 product, as frnn.py computes r2s = rs * rs
-    frnn_knn_kernel<<<ccn_blocks_exact(n1 * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(frnn_knn_kernel, dim3(ccn_blocks_exact(n1 * 32, 256)), dim3(256), 0, (cudaStream_t)stream, 
         pos1, batch1, n1, (const float4*)sorted_xyzi, cell_off, sample_ptr2, inv_cell, (unsigned)(num_cells - 1), r2, K,
         idx_out, d2_out, cnt_out);
     CCN_CHECK_LAUNCH();
@@ -344,18 +350,18 @@ extern "C" int ccn_knn_exact(const float* pos1, const int64_t* batch1, int64_t n
     if (K <= 4) {
         const unsigned blocks = ccn_blocks_exact(n1, 32);
         if (K <= 2)
-            knn_small_kernel<2><<<blocks, 256, 0, (cudaStream_t)stream>>>(pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
+            ccn_launch(knn_small_kernel<2>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
                                                                           idx_out, d2_out, cnt_out);
         else if (K == 3)
-            knn_small_kernel<3><<<blocks, 256, 0, (cudaStream_t)stream>>>(pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
+            ccn_launch(knn_small_kernel<3>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
                                                                           idx_out, d2_out, cnt_out);
         else
-            knn_small_kernel<4><<<blocks, 256, 0, (cudaStream_t)stream>>>(pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
+            ccn_launch(knn_small_kernel<4>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill,
                                                                           idx_out, d2_out, cnt_out);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    knn_exact_kernel<<<ccn_blocks_exact(n1 * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(knn_exact_kernel, dim3(ccn_blocks_exact(n1 * 32, 256)), dim3(256), 0, (cudaStream_t)stream, 
         pos1, batch1, n1, pos2, sample_ptr2, K, zero_fill, idx_out, d2_out, cnt_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -367,7 +373,7 @@ extern "C" int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t 
     CCN_REQUIRE(n1 >= 0 && K >= 1 && idx_out && sample_ptr2);
     if (n1 == 0) return CCN_OK;
     const float r2 = radius * radius;
-    ball_query_kernel<<<ccn_blocks_exact(n1 * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+    ccn_launch(ball_query_kernel, dim3(ccn_blocks_exact(n1 * 32, 256)), dim3(256), 0, (cudaStream_t)stream, 
         pos1, batch1, n1, pos2, sample_ptr2, r2, K, idx_out, cnt_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;

@@ -45,6 +45,7 @@ __device__ __forceinline__ float act_fwd(float y, int act, float slope) {
 // dst[r] = idx[r] >= 0 ? src[idx[r]] : 0
 __global__ void gather_rows_i32_kernel(const float* __restrict__ src, int64_t lds, const int32_t* __restrict__ idx,
                                        int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
         int64_t r;
@@ -59,6 +60,7 @@ __global__ void gather_rows_i32_kernel(const float* __restrict__ src, int64_t ld
 template <typename IdxT>
 __global__ void scatter_add_rows_kernel(const float* __restrict__ src, int64_t lds, const IdxT* __restrict__ idx,
                                         int64_t n, int c, float* __restrict__ dst, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
         int64_t r;
@@ -72,6 +74,7 @@ __global__ void scatter_add_rows_kernel(const float* __restrict__ src, int64_t l
 // float4 forms (c % 4 == 0, 16-byte aligned rows): one thread per (row, 4 channels); the scatter uses one 16-byte reduction
 __global__ void gather_rows_i32_v4_kernel(const float* __restrict__ src, int64_t lds, const int32_t* __restrict__ idx,
                                           int64_t n, int c4, float* __restrict__ dst, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c4;
     GRID_STRIDE(t, total) {
         int64_t r;
@@ -86,6 +89,7 @@ __global__ void gather_rows_i32_v4_kernel(const float* __restrict__ src, int64_t
 template <typename IdxT>
 __global__ void scatter_add_rows_v4_kernel(const float* __restrict__ src, int64_t lds, const IdxT* __restrict__ idx,
                                            int64_t n, int c4, float* __restrict__ dst, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c4;
     GRID_STRIDE(t, total) {
         int64_t r;
@@ -106,6 +110,7 @@ static inline bool rows_v4_ok(const float* a, int64_t lda, const float* b, int64
 // dst[i] (+)= sum of the G consecutive rows i*G .. i*G+G-1 of src
 __global__ void group_sum_rows_kernel(const float* __restrict__ src, int64_t lds, int64_t n, int G, int c,
                                       float* __restrict__ dst, int64_t ldd, int accumulate) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
         int64_t i;
@@ -129,6 +134,7 @@ __global__ void __launch_bounds__(256) linear_wgrad_kernel(const float* __restri
                                                            const float* __restrict__ X, int64_t ldx, int64_t M, int N,
                                                            int K, int64_t rows_per_split, float* __restrict__ dW,
                                                            int64_t lddw, float* __restrict__ db) {
+    ccn_pdl_wait();
     __shared__ float sy[WG_R][WG_T + 4];
     __shared__ float sx[WG_R][WG_T + 4];
     const int k0 = blockIdx.x * WG_T, n0 = blockIdx.y * WG_T;
@@ -184,6 +190,7 @@ __global__ void __launch_bounds__(256) linear_wgrad_kernel(const float* __restri
 // ------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__ z, int64_t ld, int64_t M, int C,
                                                        int64_t rows_per_cta, double* __restrict__ sums) {
+    ccn_pdl_wait();
     // thread = one column (c = threadIdx.x + 256*blockIdx.y handled by grid.y), rows split over grid.x; for
     // narrow C several row lanes share a column: lanes = 256 / Cw
     const int cw = C >= 256 ? 256 : C;                   // columns handled by this CTA row of threads
@@ -219,6 +226,7 @@ struct ColRed {
 
 template <int MODE>
 __global__ void __launch_bounds__(256) col_reduce_v4_kernel(const ColRed p) {
+    ccn_pdl_wait();
     constexpr int NS = MODE == 0 ? 4 : 8;              // statistics per thread
     constexpr int UNR = MODE == 2 ? 2 : 4;             // rows in flight per thread
     __shared__ double red[256 * NS];
@@ -312,7 +320,7 @@ static int launch_col_reduce_v4(ColRed p, cudaStream_t s) {
     if (gx < 1) gx = 1;
     p.rows_per_cta = (p.M + gx - 1) / gx;
     gx = (p.M + p.rows_per_cta - 1) / p.rows_per_cta;
-    col_reduce_v4_kernel<MODE><<<dim3((unsigned)gx, (unsigned)gy), 256, 0, s>>>(p);
+    ccn_launch(col_reduce_v4_kernel<MODE>, dim3(dim3((unsigned)gx, (unsigned)gy)), dim3(256), 0, s, p);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -322,6 +330,7 @@ static int launch_col_reduce_v4(ColRed p, cudaStream_t s) {
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, int64_t M, int C, float eps, float momentum,
                                    float* __restrict__ mean, float* __restrict__ invstd,
                                    float* __restrict__ running_mean, float* __restrict__ running_var) {
+    ccn_pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const double mu = sums[c] / (double)M;
@@ -341,6 +350,7 @@ __global__ void bn_apply_kernel(const float* __restrict__ z, int64_t ldz, int64_
                                 const float* __restrict__ mean, const float* __restrict__ invstd,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, int act, float slope,
                                 float* __restrict__ y, int64_t ldy, const PlanesOut po) {
+    ccn_pdl_wait();
     const int W = po.p ? (int)po.kpad : C;               // with planes: the pad columns are written too (zeros)
     const int64_t total = M * (int64_t)W;
     GRID_STRIDE(t, total) {
@@ -366,6 +376,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
                                                             const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, int act, float slope,
                                                             int64_t rows_per_cta, double* __restrict__ sums) {
+    ccn_pdl_wait();
     const int cw = C >= 256 ? 256 : C;
     const int lanes = 256 / cw;
     const int col = blockIdx.y * 256 + (threadIdx.x % cw);
@@ -393,6 +404,7 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ dy, int64_t lddy, 
                                     const double* __restrict__ sums, float* __restrict__ dz, int64_t lddz,
                                     float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dzsum,
                                     const PlanesOut po) {
+    ccn_pdl_wait();
     if (gamma && blockIdx.x == 0) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             if (dbeta) dbeta[c] = (float)sums[c];
@@ -449,6 +461,7 @@ __global__ void __launch_bounds__(256) bn_apply_v4_kernel(const float* __restric
                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
                                                           int act, float slope, float* __restrict__ y, int64_t ldy,
                                                           const PlanesOut po) {
+    ccn_pdl_wait();
     const int G = (po.p ? (int)po.kpad : C) >> 2;
     const int tg = G < 256 ? G : 256, rows_pb = 256 / tg;
     const int rl = threadIdx.x / tg, cg0 = threadIdx.x - rl * tg;
@@ -481,6 +494,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_v4_kernel(
     const float* __restrict__ beta, int act, float slope, int batch_stats, const double* __restrict__ sums,
     float* __restrict__ dz, int64_t lddz, float* __restrict__ dgamma, float* __restrict__ dbeta,
     float* __restrict__ dzsum, const PlanesOut po) {
+    ccn_pdl_wait();
     if (gamma && blockIdx.x == 0) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             if (dbeta) dbeta[c] = (float)sums[c];
@@ -547,6 +561,7 @@ __global__ void seg_aggregate_bwd_kernel(const float* __restrict__ msg, int64_t 
                                          int64_t lda, const int32_t* __restrict__ row_ptr, int64_t nq, int c, int mode,
                                          const float* __restrict__ dout, int64_t ldo, float* __restrict__ dmsg,
                                          int64_t lddm, float* __restrict__ datt, int64_t ldda) {
+    ccn_pdl_wait();
     const int64_t total = nq * (int64_t)c;
     GRID_STRIDE(t, total) {
         int64_t q;
@@ -593,6 +608,7 @@ __global__ void seg_aggregate_bwd_kernel(const float* __restrict__ msg, int64_t 
 __global__ void group_max_dense_bwd_kernel(const float* __restrict__ feat, int64_t ldf, const int32_t* __restrict__ idx,
                                            int64_t n, int K, int c, const float* __restrict__ dout, int64_t ldo,
                                            float* __restrict__ dfeat, int64_t lddf) {
+    ccn_pdl_wait();
     const int G = K + 1;
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
@@ -615,6 +631,7 @@ __global__ void group_max_dense_bwd_kernel(const float* __restrict__ feat, int64
 __global__ void interp_blend_bwd_kernel(const int32_t* __restrict__ nbr, const float* __restrict__ wgt, int from_d2,
                                         int64_t n, int knn, int c, const float* __restrict__ dout, int64_t ldo,
                                         float* __restrict__ dx, int64_t lddx) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     GRID_STRIDE(t, total) {
         int64_t i;
@@ -643,6 +660,7 @@ __global__ void interp_blend_bwd_kernel(const int32_t* __restrict__ nbr, const f
 __global__ void curve_feat_prep_bwd_kernel(const float* __restrict__ x, int64_t ldx, int cx, int c_in, int with_diff,
                                            const int32_t* __restrict__ ord, int64_t n, const float* __restrict__ dout,
                                            int64_t ldo, float* __restrict__ dx, int64_t lddx) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)cx;
     GRID_STRIDE(t, total) {
         int64_t i;
@@ -675,6 +693,7 @@ __global__ void curve_feat_prep_bwd_kernel(const float* __restrict__ x, int64_t 
 __global__ void edge_rel_pos_kernel(const float* __restrict__ pos_src, const float* __restrict__ pos_dst,
                                     const int32_t* __restrict__ erow, const int32_t* __restrict__ ecol, int64_t E,
                                     float radius, float* __restrict__ rel) {
+    ccn_pdl_wait();
     const int64_t total = E * 3;
     GRID_STRIDE(t, total) {
         int64_t e;
@@ -693,6 +712,7 @@ __global__ void edge_rel_pos_kernel(const float* __restrict__ pos_src, const flo
 __global__ void nll_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int64_t* __restrict__ target,
                                const float* __restrict__ cw, int64_t n, int C, int64_t ignore, float* __restrict__ lse,
                                double* __restrict__ acc, float* __restrict__ perpoint) {
+    ccn_pdl_wait();
     double ls = 0.0, ws = 0.0;
     GRID_STRIDE(i, n) {
         const float* row = logits + i * ld;
@@ -721,6 +741,7 @@ __global__ void nll_fwd_kernel(const float* __restrict__ logits, int64_t ld, con
 }
 
 __global__ void nll_finish_kernel(const double* __restrict__ acc, float* __restrict__ loss) {
+    ccn_pdl_wait();
     loss[0] = (float)(acc[0] / acc[1]);
 }
 
@@ -729,6 +750,7 @@ __global__ void nll_bwd_kernel(const float* __restrict__ logits, int64_t ld, con
                                const float* __restrict__ cw, int64_t n, int C, int64_t ignore,
                                const float* __restrict__ lse, const double* __restrict__ acc,
                                const float* __restrict__ gscale, float* __restrict__ dlogits, int64_t ldd) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)C;
     const float gs = gscale[0] / (float)acc[1];
     GRID_STRIDE(t, total) {
@@ -748,6 +770,7 @@ __global__ void nll_bwd_kernel(const float* __restrict__ logits, int64_t ld, con
 // y = u >= p ? x / (1 - p) : 0   (F.dropout with the uniform draws u supplied by the caller; its own backward)
 __global__ void dropout_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ u, int64_t n, int c,
                                float p, float* __restrict__ y, int64_t ldy) {
+    ccn_pdl_wait();
     const int64_t total = n * (int64_t)c;
     const float sc = 1.f / (1.f - p);
     GRID_STRIDE(t, total) {
@@ -777,11 +800,11 @@ extern "C" int ccn_gather_rows_i32(const float* src, int64_t lds, const int32_t*
     CCN_REQUIRE(n >= 0 && c > 0 && src && idx && dst && lds >= c && ldd >= c);
     if (n == 0) return CCN_OK;
     if (rows_v4_ok(src, lds, dst, ldd, c)) {
-        gather_rows_i32_v4_kernel<<<ELT_GRID(n * (c >> 2)), 256, 0, S_>>>(src, lds, idx, n, c >> 2, dst, ldd);
+        ccn_launch(gather_rows_i32_v4_kernel, dim3(ELT_GRID(n * (c >> 2))), dim3(256), 0, S_, src, lds, idx, n, c >> 2, dst, ldd);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    gather_rows_i32_kernel<<<ELT_GRID(n * c), 256, 0, S_>>>(src, lds, idx, n, c, dst, ldd);
+    ccn_launch(gather_rows_i32_kernel, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, src, lds, idx, n, c, dst, ldd);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -791,11 +814,11 @@ extern "C" int ccn_scatter_add_rows_i32(const float* src, int64_t lds, const int
     CCN_REQUIRE(n >= 0 && c > 0 && src && idx && dst && lds >= c && ldd >= c);
     if (n == 0) return CCN_OK;
     if (rows_v4_ok(src, lds, dst, ldd, c)) {
-        scatter_add_rows_v4_kernel<int32_t><<<ELT_GRID(n * (c >> 2)), 256, 0, S_>>>(src, lds, idx, n, c >> 2, dst, ldd);
+        ccn_launch(scatter_add_rows_v4_kernel<int32_t>, dim3(ELT_GRID(n * (c >> 2))), dim3(256), 0, S_, src, lds, idx, n, c >> 2, dst, ldd);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    scatter_add_rows_kernel<int32_t><<<ELT_GRID(n * c), 256, 0, S_>>>(src, lds, idx, n, c, dst, ldd);
+    ccn_launch(scatter_add_rows_kernel<int32_t>, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, src, lds, idx, n, c, dst, ldd);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -805,11 +828,11 @@ extern "C" int ccn_scatter_add_rows_i64(const float* src, int64_t lds, const int
     CCN_REQUIRE(n >= 0 && c > 0 && src && idx && dst && lds >= c && ldd >= c);
     if (n == 0) return CCN_OK;
     if (rows_v4_ok(src, lds, dst, ldd, c)) {
-        scatter_add_rows_v4_kernel<int64_t><<<ELT_GRID(n * (c >> 2)), 256, 0, S_>>>(src, lds, idx, n, c >> 2, dst, ldd);
+        ccn_launch(scatter_add_rows_v4_kernel<int64_t>, dim3(ELT_GRID(n * (c >> 2))), dim3(256), 0, S_, src, lds, idx, n, c >> 2, dst, ldd);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    scatter_add_rows_kernel<int64_t><<<ELT_GRID(n * c), 256, 0, S_>>>(src, lds, idx, n, c, dst, ldd);
+    ccn_launch(scatter_add_rows_kernel<int64_t>, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, src, lds, idx, n, c, dst, ldd);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -818,7 +841,7 @@ extern "C" int ccn_group_sum_rows(const float* src, int64_t lds, int64_t n, int3
                                   int64_t ldd, int32_t accumulate, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && G >= 1 && c > 0 && src && dst && lds >= c && ldd >= c);
     if (n == 0) return CCN_OK;
-    group_sum_rows_kernel<<<ELT_GRID(n * c), 256, 0, S_>>>(src, lds, n, G, c, dst, ldd, accumulate);
+    ccn_launch(group_sum_rows_kernel, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, src, lds, n, G, c, dst, ldd, accumulate);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -838,7 +861,7 @@ extern "C" int ccn_linear_wgrad(const float* dY, int64_t lddy, const float* X, i
     rps = (rps + WG_R - 1) / WG_R * WG_R;
     splits = (M + rps - 1) / rps;
     dim3 grid(tk, tn, (unsigned)splits);
-    linear_wgrad_kernel<<<grid, 256, 0, S_>>>(dY, lddy, X, ldx, M, N, K, rps, dW, lddw, db);
+    ccn_launch(linear_wgrad_kernel, dim3(grid), dim3(256), 0, S_, dY, lddy, X, ldx, M, N, K, rps, dW, lddw, db);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -871,10 +894,10 @@ extern "C" int ccn_bn_stats(const float* z, int64_t ldz, int64_t M, int32_t C, f
         dim3 grid;
         int64_t rpc;
         bn_grid(M, C, &grid, &rpc);
-        bn_stats_kernel<<<grid, 256, 0, S_>>>(z, ldz, M, C, rpc, sums);
+        ccn_launch(bn_stats_kernel, dim3(grid), dim3(256), 0, S_, z, ldz, M, C, rpc, sums);
         CCN_CHECK_LAUNCH();
     }
-    bn_finalize_kernel<<<(C + 255) / 256, 256, 0, S_>>>(sums, M, C, eps, momentum, mean, invstd, running_mean,
+    ccn_launch(bn_finalize_kernel, dim3((C + 255) / 256), dim3(256), 0, S_, sums, M, C, eps, momentum, mean, invstd, running_mean,
                                                         running_var);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -894,12 +917,12 @@ extern "C" int ccn_bn_apply(const float* z, int64_t ldz, int64_t M, int32_t C, c
     const PlanesOut po = {(__nv_bfloat16*)y_planes, yp_ld, yp_plane_stride, n_planes};
     if ((C & 3) == 0 && (ldz & 3) == 0 && (ldy & 3) == 0 && al16(z) && al16(y) && (!gamma || (al16(mean) && al16(invstd) && al16(gamma) && al16(beta))) &&
         (!y_planes || ((yp_ld & 3) == 0 && (yp_plane_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(y_planes) & 7) == 0))) {
-        bn_apply_v4_kernel<<<bn_v4_grid(M, (int)(y_planes ? yp_ld : C)), 256, 0, S_>>>(z, ldz, M, C, mean, invstd, gamma, beta,
+        ccn_launch(bn_apply_v4_kernel, dim3(bn_v4_grid(M, (int)(y_planes ? yp_ld : C))), dim3(256), 0, S_, z, ldz, M, C, mean, invstd, gamma, beta,
                                                                                      act, slope, y, ldy, po);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    bn_apply_kernel<<<ELT_GRID(M * (y_planes ? yp_ld : C)), 256, 0, S_>>>(z, ldz, M, C, mean, invstd, gamma, beta, act,
+    ccn_launch(bn_apply_kernel, dim3(ELT_GRID(M * (y_planes ? yp_ld : C))), dim3(256), 0, S_, z, ldz, M, C, mean, invstd, gamma, beta, act,
                                                                           slope, y, ldy, po);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -928,7 +951,7 @@ extern "C" int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, in
             dim3 grid;
             int64_t rpc;
             bn_grid(M, C, &grid, &rpc);
-            bn_bwd_reduce_kernel<<<grid, 256, 0, S_>>>(dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, rpc,
+            ccn_launch(bn_bwd_reduce_kernel, dim3(grid), dim3(256), 0, S_, dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, rpc,
                                                        sums);
             CCN_CHECK_LAUNCH();
         }
@@ -936,12 +959,12 @@ extern "C" int ccn_bn_backward(const float* dy, int64_t lddy, const float* z, in
     const PlanesOut po = {(__nv_bfloat16*)dz_planes, dzp_ld, dzp_plane_stride, n_planes};
     if ((C & 3) == 0 && (ldz & 3) == 0 && (lddy & 3) == 0 && (lddz & 3) == 0 && al16(z) && al16(dy) && al16(dz) &&
         (!dz_planes || ((dzp_ld & 3) == 0 && (dzp_plane_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(dz_planes) & 7) == 0))) {
-        bn_bwd_apply_v4_kernel<<<bn_v4_grid(M, (int)(dz_planes ? dzp_ld : C)), 256, 0, S_>>>(
+        ccn_launch(bn_bwd_apply_v4_kernel, dim3(bn_v4_grid(M, (int)(dz_planes ? dzp_ld : C))), dim3(256), 0, S_, 
             dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, batch_stats, sums, dz, lddz, dgamma, dbeta, dzsum, po);
         CCN_CHECK_LAUNCH();
         return CCN_OK;
     }
-    bn_bwd_apply_kernel<<<ELT_GRID(M * (dz_planes ? dzp_ld : C)), 256, 0, S_>>>(
+    ccn_launch(bn_bwd_apply_kernel, dim3(ELT_GRID(M * (dz_planes ? dzp_ld : C))), dim3(256), 0, S_, 
         dy, lddy, z, ldz, M, C, mean, invstd, gamma, beta, act, slope, batch_stats, sums, dz, lddz, dgamma, dbeta, dzsum, po);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -955,7 +978,7 @@ extern "C" int ccn_seg_aggregate_bwd(const float* msg, int64_t ldm, const float*
     CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || (att && datt && msg));
     CCN_REQUIRE(mode != CCN_AGG_MAX || msg);
     if (nq == 0) return CCN_OK;
-    seg_aggregate_bwd_kernel<<<ELT_GRID(nq * c), 256, 0, S_>>>(msg, ldm, att, lda, row_ptr, nq, c, mode, dout, ldo,
+    ccn_launch(seg_aggregate_bwd_kernel, dim3(ELT_GRID(nq * c)), dim3(256), 0, S_, msg, ldm, att, lda, row_ptr, nq, c, mode, dout, ldo,
                                                                dmsg, lddm, datt, ldda);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -966,7 +989,7 @@ extern "C" int ccn_group_max_dense_bwd(const float* feat, int64_t ldf, const int
                                        ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && K >= 0 && c > 0 && feat && dout && dfeat && (K == 0 || idx));
     if (n == 0) return CCN_OK;
-    group_max_dense_bwd_kernel<<<ELT_GRID(n * c), 256, 0, S_>>>(feat, ldf, idx, n, K, c, dout, ldo, dfeat, lddf);
+    ccn_launch(group_max_dense_bwd_kernel, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, feat, ldf, idx, n, K, c, dout, ldo, dfeat, lddf);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -976,7 +999,7 @@ extern "C" int ccn_interp_blend_bwd(const int32_t* nbr, const float* wgt, int32_
                                     ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && knn >= 1 && c > 0 && nbr && wgt && dout && dx);
     if (n == 0) return CCN_OK;
-    interp_blend_bwd_kernel<<<ELT_GRID(n * c), 256, 0, S_>>>(nbr, wgt, from_d2, n, knn, c, dout, ldo, dx, lddx);
+    ccn_launch(interp_blend_bwd_kernel, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, nbr, wgt, from_d2, n, knn, c, dout, ldo, dx, lddx);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -987,7 +1010,7 @@ extern "C" int ccn_curve_feat_prep_bwd(const float* x, int64_t ldx, int32_t cx, 
     CCN_REQUIRE(n >= 0 && cx > 0 && x && dout && dx && (!with_diff || curve_ord));
     if (n == 0) return CCN_OK;
     const int c_in = cx + (with_xyz ? 3 : 0);
-    curve_feat_prep_bwd_kernel<<<ELT_GRID(n * cx), 256, 0, S_>>>(x, ldx, cx, c_in, with_diff, curve_ord, n, dout, ldo,
+    ccn_launch(curve_feat_prep_bwd_kernel, dim3(ELT_GRID(n * cx)), dim3(256), 0, S_, x, ldx, cx, c_in, with_diff, curve_ord, n, dout, ldo,
                                                                  dx, lddx);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -997,7 +1020,7 @@ extern "C" int ccn_edge_rel_pos(const float* pos_src, const float* pos_dst, cons
                                 int64_t E, float normalize_radius, float* rel, ccn_stream_t stream) {
     CCN_REQUIRE(E >= 0 && pos_src && pos_dst && erow && ecol && rel);
     if (E == 0) return CCN_OK;
-    edge_rel_pos_kernel<<<ELT_GRID(E * 3), 256, 0, S_>>>(pos_src, pos_dst, erow, ecol, E, normalize_radius, rel);
+    ccn_launch(edge_rel_pos_kernel, dim3(ELT_GRID(E * 3)), dim3(256), 0, S_, pos_src, pos_dst, erow, ecol, E, normalize_radius, rel);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -1008,10 +1031,10 @@ extern "C" int ccn_nll_loss_fwd(const float* logits, int64_t ld, const int64_t* 
     CCN_REQUIRE(n > 0 && C > 0 && logits && target && lse && acc && loss && ld >= C);
     cudaError_t e = cudaMemsetAsync(acc, 0, 2 * sizeof(double), S_);
     if (e != cudaSuccess) return (int)e;
-    nll_fwd_kernel<<<ccn_grid(n, 128, 148 * 8), 128, 0, S_>>>(logits, ld, target, class_weight, n, C, ignore_index, lse,
+    ccn_launch(nll_fwd_kernel, dim3(ccn_grid(n, 128, 148 * 8)), dim3(128), 0, S_, logits, ld, target, class_weight, n, C, ignore_index, lse,
                                                               acc, perpoint);
     CCN_CHECK_LAUNCH();
-    nll_finish_kernel<<<1, 1, 0, S_>>>(acc, loss);
+    ccn_launch(nll_finish_kernel, dim3(1), dim3(1), 0, S_, acc, loss);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
@@ -1020,7 +1043,7 @@ extern "C" int ccn_nll_loss_bwd(const float* logits, int64_t ld, const int64_t* 
                                 int64_t n, int32_t C, int64_t ignore_index, const float* lse, const double* acc,
                                 const float* gscale, float* dlogits, int64_t ldd, ccn_stream_t stream) {
     CCN_REQUIRE(n > 0 && C > 0 && logits && target && lse && acc && gscale && dlogits && ld >= C && ldd >= C);
-    nll_bwd_kernel<<<ELT_GRID(n * C), 256, 0, S_>>>(logits, ld, target, class_weight, n, C, ignore_index, lse, acc,
+    ccn_launch(nll_bwd_kernel, dim3(ELT_GRID(n * C)), dim3(256), 0, S_, logits, ld, target, class_weight, n, C, ignore_index, lse, acc,
                                                     gscale, dlogits, ldd);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
@@ -1030,7 +1053,7 @@ extern "C" int ccn_dropout(const float* x, int64_t ldx, const float* u, int64_t 
                            int64_t ldy, ccn_stream_t stream) {
     CCN_REQUIRE(n >= 0 && c > 0 && x && u && y && p >= 0.f && p < 1.f);
     if (n == 0) return CCN_OK;
-    dropout_kernel<<<ELT_GRID(n * c), 256, 0, S_>>>(x, ldx, u, n, c, p, y, ldy);
+    ccn_launch(dropout_kernel, dim3(ELT_GRID(n * c)), dim3(256), 0, S_, x, ldx, u, n, c, p, y, ldy);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

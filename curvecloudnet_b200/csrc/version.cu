@@ -1,4 +1,17 @@
 #include "common.cuh"
+
+#include <cstdlib>
+
 unsigned long long g_ccn_kernel_launches = 0;
-extern "C" int ccn_version(void) { return 100; }
+// programmatic dependent launch of every kernel (common.cuh ccn_launch): on unless CCN_PDL=0 in the environment
+int g_ccn_pdl = [] {
+    const char* e = std::getenv("CCN_PDL");
+    return !(e && e[0] == '0');
+}();
+extern "C" int ccn_version(void) { return 101; }
 extern "C" int64_t ccn_kernel_launches(void) { return (int64_t)g_ccn_kernel_launches; }
+extern "C" int ccn_set_dependent_launch(int32_t on) {
+    const int prev = g_ccn_pdl;
+    if (on >= 0) g_ccn_pdl = on != 0;
+    return prev;
+}

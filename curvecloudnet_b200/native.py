@@ -223,6 +223,11 @@ def kernel_launches() -> int:
     return int(load().ccn_kernel_launches())
 
 
+def set_dependent_launch(on: int = -1) -> int:
+    """ccn_set_dependent_launch: programmatic dependent launch of the library's kernels (1 / 0; -1 queries) -> previous."""
+    return int(load().ccn_set_dependent_launch(int(on)))
+
+
 def grid_num_cells(n2: int) -> int:
     return int(load().ccn_grid_num_cells(int(n2)))
 

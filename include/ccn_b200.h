@@ -58,6 +58,10 @@ typedef struct CUstream_st* ccn_stream_t;
 int ccn_version(void);
 /* number of kernels this library has launched in this process (bench.py reports it as gpu_launches). */
 int64_t ccn_kernel_launches(void);
+/* Programmatic dependent launch of every kernel of this library (cudaLaunchAttributeProgrammaticStreamSerialization + a
+ * griddepcontrol.wait before the kernel's first global access): on by default (CCN_PDL=0 in the environment turns it off);
+ * on = 1 / 0 sets it, on < 0 only queries.  Returns the previous setting.  Results do not depend on it. */
+int ccn_set_dependent_launch(int32_t on);
 
 /* ---- curve / sample topology -------------------------------------------------------------------
  * replaces curveidx_local2global + batch2ptr + is_sorted asserts

@@ -130,3 +130,30 @@ def test_mlp_chain_setting_does_not_change_the_logits(native, precision):
     assert torch.equal(outs["auto"], outs[True]) and torch.equal(outs["auto"], outs[False])
     if not native:           # the python executor's launches go through ops.call
         assert chained[False] == 0 and chained["auto"] >= 2 and chained[True] > chained["auto"]
+
+
+@pytest.mark.parametrize("native", [True, False])
+def test_dependent_launch_setting_does_not_change_the_logits(native):
+    """ccn_set_dependent_launch: every kernel launched with the programmatic-stream-serialization attribute (and waiting on
+    its predecessor before its first global access) against plain stream-ordered launches - bit-identical logits, several
+    forwards in a row so that a missing wait would race with the previous kernel's tail."""
+    from curvecloudnet_b200 import native as nat
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    data = driving_scan_batch([4]).to("cuda")
+    model = randomize_model_(build_model(ModelBase, "nuscenes", precision="bf16x3", native_executor=native), 1234).cuda().eval()
+    prev = nat.set_dependent_launch(-1)
+    outs = {}
+    try:
+        for on in (1, 0, 1):
+            nat.set_dependent_launch(on)
+            assert nat.set_dependent_launch(-1) == on
+            for rep in range(3):
+                with torch.no_grad():
+                    torch.manual_seed(5)
+                    y = model(data)
+                outs.setdefault(on, y)
+                assert torch.equal(y, outs[on]) and torch.equal(y, outs[1])
+    finally:
+        nat.set_dependent_launch(prev)
