@@ -10,13 +10,14 @@
 // as deep as shared memory allows.  Producers (this kernel's epilogue, ccn_pack_planes, the edge-layer
 // kernels) write planes; the last layer of a chain writes fp32.
 //
-// One persistent CTA per SM, 192 threads:
+// One persistent CTA per SM, 320 threads:
 //   warp 0   lane 0: TMA producer.  Weights (bf16 hi [+ lo]) are loaded ONCE per CTA when the CTA's N-slice of W
 //            fits in shared memory next to a >= 3-stage ring ("resident": every big-M layer of the path), else
 //            they stream through the ring with A.  A tiles: 128 rows x 64 bf16 per plane per stage.
 //   warp 1   lane 0: tcgen05.mma kind::f16 issuer, fp32 accumulators in TMEM, DOUBLE-BUFFERED (2 x BN columns)
 //            so the epilogue of tile t overlaps the MMAs of tile t+1.  x3 mode: A_hi W_hi + A_lo W_hi + A_hi W_lo.
-//   warps 2-5 epilogue: tcgen05.ld (32 lanes x 32 columns), bias + activation, then fp32 rows and/or bf16 planes.
+//   warps 2-9 epilogue: tcgen05.ld (32 lanes x 32 columns), bias + activation, then fp32 rows and/or bf16 planes;
+//            two warps per TMEM lane quarter, alternating 32-column chunks.
 // Tile order: tile t -> (m = t / tiles_n, n = t % tiles_n); the grid is a multiple of tiles_n in resident mode, so
 // a CTA keeps one N-slice and the CTAs sharing an A tile run concurrently (second read served by L2).
 #include <type_traits>
@@ -31,7 +32,8 @@ using namespace ccn_tc;
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kATile = kBM * kBK * 2;     // 16 KB per plane per stage
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;          // warp 0: TMA producer, warp 1: MMA issuer, warps 2..9: epilogue
+constexpr int kEpiThreads = kThreads - 64;
 constexpr int kMaxStages = 8;
 constexpr int kSmemLimit = 227 * 1024;
 
@@ -126,7 +128,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
         mbar_init(wfull, 1);
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull0 + 8 * b, 1);
-            mbar_init(tempty0 + 8 * b, 4);
+            mbar_init(tempty0 + 8 * b, kEpiThreads / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -221,20 +223,25 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
             }
         }
     } else {
-        // ------------------------------------------------------------------ epilogue (warps 2..5)
+        // ------------------------------------------------------------------ epilogue (warps 2..9)
+        // Two warps per TMEM lane quarter (= per scheduler), taking alternate 32-column chunks of the accumulator: with one
+        // warp per scheduler the chunk loop (tcgen05.ld -> bias / activation / bf16 split -> 32-byte stores, ~10 dependent
+        // instructions per element) ran unhidden and bounded every K <= 256 layer at ~3.5 us per 128 x 128 tile against
+        // 1.4 us of MMA (ncu source view, profiles/r02q_linear_epilogue.txt)
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
+        const int half = (warp - 2) >> 2;               // which of the quarter's two warps
         const bool vecy = p.Y && ((p.ldy & 7) == 0) && ((reinterpret_cast<uintptr_t>(p.Y) & 31) == 0);
         int it = 0, bias_n0 = -1;
         const float* bs = bias_s;
-        const int et = threadIdx.x - 64;                // 0..127 over the four epilogue warps
+        const int et = threadIdx.x - 64;                // 0..255 over the eight epilogue warps
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
             const int m0 = (t / p.tiles_n) * kBM, n0 = (t % p.tiles_n) * BN;
             const int mma_n = min(BN, ((p.N - n0) + 15) & ~15);
             const int buf = it & 1;
             if (n0 != bias_n0) {                        // once per CTA in resident mode
-                asm volatile("bar.sync 1, 128;" ::: "memory");      // everyone is done with the previous slice
-                for (int j = et; j < BN; j += 128) bias_s[j] = (p.bias && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");      // everyone is done with the previous slice
+                for (int j = et; j < BN; j += kEpiThreads) bias_s[j] = (p.bias && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 bias_n0 = n0;
             }
             mbar_wait(tfull0 + 8 * buf, (it >> 1) & 1);
@@ -295,7 +302,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     }
                 }
             };
-            for (int c0 = 0; c0 < mma_n; c0 += 32) {
+            for (int c0 = half * 32; c0 < mma_n; c0 += 64) {
                 uint32_t v[32];
                 tmem_ld32(tbase + (uint32_t)c0, v);
                 emit(v, c0);

@@ -82,6 +82,40 @@ def main():
     for name, (n, us) in sorted(per.items(), key=lambda kv: -kv[1][1])[:40]:
         print("  %-70s %4d  %8.1f us  avg %6.2f" % (name, n, us, us / n))
     report.update({"main_busy_us": busy, "main_idle_us": tot_gap, "n_main": len(lst)})
+    # every Linear launch with its shape: the python executor issues the same C-ABI calls in the same order, so its
+    # ccn_linear_planes / ccn_conv_planes argument lists line up with the linear_planes_kernel records of the native run
+    from curvecloudnet_b200 import ops
+    shapes, real_call = [], ops.call
+
+    def spy(name, *a):
+        if name == "ccn_linear_planes":
+            shapes.append(("lin", a[24], a[25], a[3] + a[7] + a[11] + a[15], a[26], 1 + (a[7] > 0) + (a[11] > 0) + (a[15] > 0)))
+        elif name == "ccn_conv_planes":
+            shapes.append(("conv", 0))
+        return real_call(name, *a)
+    pym = randomize_model_(build_model(ModelBase, "nuscenes", precision=precision, native_executor=False), 1234).cuda().eval()
+    ops.call = spy
+    try:
+        with torch.no_grad():
+            torch.manual_seed(2)
+            pym(scans[2])
+    finally:
+        ops.call = real_call
+    lin = [k for k in last if "linear_planes_kernel" in k[2]]
+    print("linear launches in order (%d kernels, %d python-side calls):" % (len(lin), len(shapes)))
+    if len(lin) == len(shapes):
+        tot = 0.0
+        for k, sh in zip(lin, shapes):
+            d = k[1] - k[0]
+            tot += d
+            if sh[0] == "lin":
+                _, M, N, K, box, nseg = sh
+                fl = 2.0 * M * N * K
+                print("  t=%7.1f  M=%6d N=%5d K=%5d box=%3d segs=%d  %6.1f us  %6.1f TF/s alg  tiles=%d" %
+                      (k[0] - t0, M, N, K, box, nseg, d, fl / d * 1e-6, ((M + 127) // 128) * ((N + box - 1) // box)))
+            else:
+                print("  t=%7.1f  conv layer %s  %6.1f us" % (k[0] - t0, sh[1:2], d))
+        print("  total %.1f us" % tot)
     if out_json:
         report["kernels"] = [(k[0] - t0, k[1] - k[0], k[2][:60], str(k[3])) for k in last]
         json.dump(report, open(out_json, "w"))
