@@ -359,10 +359,10 @@ int level_sptr(Exec& ex, Level* lv) {                 // nn.ForwardCache.sample_
     int32_t* tail = ex.alloc_n<int32_t>(kMaxSamples + 1 + 4);
     if (ex.oom) return CCN_OK;
     EX_CALL(ccn_sample_ptr(lv->batch, lv->n, tail, tail + kMaxSamples + 1, kMaxSamples, (ccn_stream_t)ex.stream));
-    EX_CALL(ex.readback(tail + kMaxSamples + 1, 4));
-    const int B = ex.pinned[0], flags = ex.pinned[2];
+    EX_CALL(ex.readback(tail, kMaxSamples + 1 + 4));      // sample CSR and its header in ONE round trip (4 KB)
+    const int32_t* hd = ex.pinned + kMaxSamples + 1;
+    const int B = hd[0], flags = hd[2];
     if (flags) { ex.topo_flags = flags; return CCN_ETOPOLOGY; }
-    EX_CALL(ex.readback(tail, B + 1));
     lv->sptr.assign(ex.pinned, ex.pinned + B + 1);
     lv->sptr_dev = tail;
     lv->has_sptr = true;
@@ -380,11 +380,11 @@ int level_topo(Exec& ex, Level* lv) {                 // nn.ForwardCache.topolog
     if (ex.oom) return CCN_OK;
     EX_CALL(ccn_curve_csr(lv->batch, lv->curve, n, ord, cptr, tail, soff, glob, tail + kMaxSamples + 1, kMaxSamples,
                           (ccn_stream_t)ex.stream));
-    EX_CALL(ex.readback(tail + kMaxSamples + 1, 4));
-    const int B = ex.pinned[0], n_curves = ex.pinned[1], flags = ex.pinned[2], max_glob = ex.pinned[3];
+    EX_CALL(ex.readback(tail, kMaxSamples + 1 + 4));      // one round trip
+    const int32_t* hd = ex.pinned + kMaxSamples + 1;
+    const int B = hd[0], n_curves = hd[1], flags = hd[2], max_glob = hd[3];
     if (flags) { ex.topo_flags = flags; return CCN_ETOPOLOGY; }
     if (!lv->has_sptr) {
-        EX_CALL(ex.readback(tail, B + 1));
         lv->sptr.assign(ex.pinned, ex.pinned + B + 1);
         lv->sptr_dev = tail;
         lv->has_sptr = true;
@@ -665,11 +665,15 @@ int fps_downsample(Exec& ex, Level* lv, float ratio, Level* ch, int64_t** idx_ou
 // Right after step `si` has created level `lv` (its gathers are queued on the main stream): sample - and gather - the levels
 // of the following FPS `sa` steps on the side stream.  Their sizes are host arithmetic, their draws are the next draws of
 // the reference's sequence (no step in between draws), so nothing but the overlap changes.
-int presample_ahead(Exec& ex, int si, Level* lv) {
+// `ready`: an event recorded on the main stream when the level was complete (null: record one now).
+int presample_ahead(Exec& ex, int si, Level* lv, cudaEvent_t ready = nullptr) {
     if (!ex.use_side || ex.prof || !ex.side || ex.fps_next[si] < 0 || ex.oom) return CCN_OK;
     if (ex.pre[ex.fps_next[si]].done) return CCN_OK;      // already sampled as part of an earlier step's look-ahead chain
-    EX_CUDA(cudaEventRecord(ex.lvl_ready, ex.stream));
-    EX_CUDA(cudaStreamWaitEvent(ex.side, ex.lvl_ready, 0));
+    if (!ready) {
+        EX_CUDA(cudaEventRecord(ex.lvl_ready, ex.stream));
+        ready = ex.lvl_ready;
+    }
+    EX_CUDA(cudaStreamWaitEvent(ex.side, ready, 0));
     cudaStream_t main_stream = ex.stream;
     ex.stream = ex.side;
     int rc = CCN_OK;
@@ -705,10 +709,13 @@ int presample_ahead(Exec& ex, int si, Level* lv) {
 // Step `si` has created level `ch` from `lv` (sampled indices `idx`): queue, on the geometry stream, (1) the interpolation
 // table of the fp / fp-geo step that will pop this down step and (2) the kNN tables of the sgcnn steps that run on `ch` before
 // the next level change.  The main stream joins through events at first use.
-int geometry_ahead(Exec& ex, int si, Level* lv, Level* ch, const int64_t* idx) {
+int geometry_ahead(Exec& ex, int si, Level* lv, Level* ch, const int64_t* idx, cudaEvent_t ready = nullptr) {
     if (!ex.use_side || ex.prof || !ex.geo || ex.oom || ch->n == 0) return CCN_OK;
-    cudaEvent_t start = ex.geo_event();
-    EX_CUDA(cudaEventRecord(start, ex.stream));            // the level's positions / batch are queued on the main (or sampling) stream
+    cudaEvent_t start = ready;
+    if (!start) {
+        start = ex.geo_event();
+        EX_CUDA(cudaEventRecord(start, ex.stream));        // the level's positions / batch are queued on the main (or sampling) stream
+    }
     EX_CUDA(cudaStreamWaitEvent(ex.geo, start, 0));
     cudaStream_t saved = ex.stream;
     ex.stream = ex.geo;
@@ -1167,24 +1174,37 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     }
                     e = Edges{buf, erow, col, E, nq, max_deg};
                     if (!presampled) EX_CALL(subset_level(ex, lv, idx, ch));
-                    EX_CALL(presample_ahead(ex, (int)si, ch));
-                    EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx));
                     pc_iv = iv + 2;
                     if (cur.x) xparts[nxp++] = cur.x;
                     if (iv[0] || !cur.x) xparts[nxp++] = &lv->pos;
                 } else {
-                    const int K = (int)iv[1];
                     if (!presampled || ex.pre[si].voxel) EX_CALL(subset_level(ex, lv, idx, ch));
-                    EX_CALL(presample_ahead(ex, (int)si, ch));
-                    EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx));
-                    int32_t *nbr = nullptr, *cnt = nullptr;
-                    EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));
-                    EX_CALL(dense_to_csr(ex, nbr, cnt, ch->n, K, &e));
                     pc_iv = iv + 2;
                     if (cur.x) xparts[nxp++] = cur.x;
                 }
+                // The look-ahead work (next levels' samplers on the side stream, neighbour tables on the geometry stream) is
+                // HOST work too - the draw callbacks, a dozen launches, for a voxel sampler 70 us of noise generation - and used to
+                // run before this step's own launches, with the main stream idle meanwhile (160 us after sa-geo, 50 us after
+                // every sa: tools/timeline.py).  The level is complete here: mark it, queue this step's kernels, then look ahead.
+                cudaEvent_t lvl_done = nullptr;
+                if (ex.use_side && !ex.prof && !ex.oom) {
+                    lvl_done = ex.geo_event();
+                    EX_CUDA(cudaEventRecord(lvl_done, ex.stream));
+                }
                 Feat* o = nullptr;
-                EX_CALL(pointconv(ex, pc_iv, pc_fv, xparts, nxp, lv, ch, e, &o));
+                if (s.kind == ST_SA_GEO) {
+                    EX_CALL(pointconv(ex, pc_iv, pc_fv, xparts, nxp, lv, ch, e, &o));     // no host wait inside: all queued
+                    EX_CALL(presample_ahead(ex, (int)si, ch, lvl_done));
+                    EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx, lvl_done));
+                } else {
+                    const int K = (int)iv[1];
+                    int32_t *nbr = nullptr, *cnt = nullptr;
+                    EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));
+                    EX_CALL(presample_ahead(ex, (int)si, ch, lvl_done));                  // while the search runs
+                    EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx, lvl_done));
+                    EX_CALL(dense_to_csr(ex, nbr, cnt, ch->n, K, &e));                    // host waits for the edge count
+                    EX_CALL(pointconv(ex, pc_iv, pc_fv, xparts, nxp, lv, ch, e, &o));
+                }
                 outp.x = o;
                 outp.lv = ch;
                 if (s.kind == ST_SA_GEO) didx = idx;
