@@ -6,6 +6,8 @@
 // the per-voxel argmin as one atomicMin on a packed (score, index) key, and only the occupied
 // voxels (N2 << N) are ordered.  FPS is one CTA per cloud with points and running distances in
 // registers and a 2-instruction (redux.sync) warp argmax per round.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -269,3 +271,46 @@ extern "C" int ccn_fps(const float* pos, const int32_t* sample_ptr, int32_t n_sa
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// ccn_fps_static: ccn_fps with its scratch in a file-scope device array - no allocation anywhere on the call path (no
+// counterpart in the reference; for callers under CUDA graph capture / serving loops that may not call cudaMalloc).
+// Layout: [0, 4 MAX) the running squared distances (float, read only by the > 8192-point variant), [4 MAX, 8 MAX) the
+// selection flags (int32, cleared by ccn_fps at every call).  One array per device that loads the library; every call on a
+// device shares it, calls that overlap on the GPU race (include/ccn_b200.h).
+// In HOST code `g_fps_static_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once
+// per device, with that device current, through cudaGetSymbolAddress.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_fps_static_scratch[(size_t)CCN_FPS_STATIC_MAX_POINTS * 8];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_fps_static_mutex;
+void* g_fps_static_addr[kMaxDevices] = {};
+}  // namespace
+
+extern "C" int ccn_fps_static(const float* pos, const int32_t* sample_ptr, int32_t n_samples, int64_t n, const int32_t* ksel,
+                              const int32_t* start, int32_t max_len, int64_t* idx_out, int32_t* total_out, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0);
+    if (n > CCN_FPS_STATIC_MAX_POINTS) return CCN_ESCRATCH_LIMIT;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    CCN_REQUIRE(dev >= 0 && dev < kMaxDevices);
+    void* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_fps_static_mutex);
+        if (!g_fps_static_addr[dev]) {                       // set-up, once per device, with that device current
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_fps_static_scratch);
+            if (e != cudaSuccess) return (int)e;
+            if (!p) return CCN_EINVAL;
+            g_fps_static_addr[dev] = p;
+        }
+        base = g_fps_static_addr[dev];
+    }
+    float* closest = reinterpret_cast<float*>(base);
+    int32_t* sel_cnt = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(base) + (size_t)CCN_FPS_STATIC_MAX_POINTS * 4);
+    return ccn_fps(pos, sample_ptr, n_samples, n, ksel, start, max_len, closest, sel_cnt, idx_out, total_out, stream);
+}
+

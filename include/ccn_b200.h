@@ -38,6 +38,7 @@ typedef struct CUstream_st* ccn_stream_t;
 #define CCN_ETOPOLOGY (-3)    /* batch / curve ids not sorted (the reference asserts, point_ops.py:31,49): ccn_exec_topology_flags */
 #define CCN_EVOXEL_RANGE (-4) /* VoxelFPS: voxel coordinates out of the supported range */
 #define CCN_ENOMEM (-5)       /* ccn_forward_run: the arena is too small (*arena_needed = bytes used when it ran out) */
+#define CCN_ESCRATCH_LIMIT (-6) /* ccn_fps_static: the input is larger than the library's built-in scratch array */
 
 #define CCN_ACT_NONE 0
 #define CCN_ACT_RELU 1
@@ -135,6 +136,21 @@ int ccn_voxel_fps(const float* pos, const int64_t* batch, int64_t n, float voxel
 int ccn_fps(const float* pos, const int32_t* sample_ptr, int32_t n_samples, int64_t n, const int32_t* ksel,
             const int32_t* start, int32_t max_len, float* closest_scratch, int32_t* sel_cnt_scratch, int64_t* idx_out,
             int32_t* total_out, ccn_stream_t stream);
+
+/* fps_static: ccn_fps WITHOUT caller-supplied scratch and without any allocation.  No counterpart in the reference: added
+ *            for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ *            tight serving loops, harnesses that forbid allocation).  The two scratch vectors of ccn_fps (running distances,
+ *            selection flags) live in a file-scope `static __device__` array of the library: CCN_FPS_STATIC_MAX_POINTS points,
+ *            8 bytes each = 2 MiB, held by every GPU that loads the library until the process exits.  Same arguments otherwise,
+ *            same result as ccn_fps bit for bit.  n > CCN_FPS_STATIC_MAX_POINTS -> CCN_ESCRATCH_LIMIT, nothing is launched.
+ *            The call path contains no cudaMalloc / cudaFree / allocating library routine (the array's device address is
+ *            looked up once per device with cudaGetSymbolAddress; the flags are cleared with cudaMemsetAsync on `stream`).
+ *            EVERY call on a device shares the one array and finds the previous call's contents in it: the entry point
+ *            clears what must start at zero, and calls that overlap on the GPU (different streams, no ordering between
+ *            them) RACE - order them, or use ccn_fps with scratch of your own. */
+#define CCN_FPS_STATIC_MAX_POINTS 262144
+int ccn_fps_static(const float* pos, const int32_t* sample_ptr, int32_t n_samples, int64_t n, const int32_t* ksel,
+                   const int32_t* start, int32_t max_len, int64_t* idx_out, int32_t* total_out, ccn_stream_t stream);
 
 /* ---- neighbour search ------------------------------------------------------------------------------
  * grid_build + frnn_knn: frnn.frnn_grid_points (third_party/FRNN/frnn/frnn.py:210-347) = _C.insert_points_cuda +
