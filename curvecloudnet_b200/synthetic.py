@@ -241,3 +241,75 @@ def randomize_model_(model: torch.nn.Module, seed: int = 1234) -> torch.nn.Modul
             else:  # bias
                 t.copy_((torch.rand(t.shape, generator=g) * 2 - 1) * 0.1)
     return model
+
+
+# ----------------------------------------------------------------------------------------------
+# Synthetic triangle meshes for the scanning simulator (curvecloudnet_b200/simulator.py): the ShapeNet / Kortx meshes the
+# reference's generator reads (scanning_simulator/shapenet_seg/generate_shapenet.py) are not available offline.  Objects fit
+# a sphere of radius ~0.3 around the origin (the camera sits at distance 1, sampling.py:16,37), every triangle is present in
+# both windings (the rasteriser culls one winding, rasterizer_kernel.cu:194-198), so every view sees a closed surface.
+# ----------------------------------------------------------------------------------------------
+def _grid_faces(nu: int, nv: int, wrap_u: bool, wrap_v: bool):
+    import numpy as np
+    iu = np.arange(nu if wrap_u else nu - 1)
+    iv = np.arange(nv if wrap_v else nv - 1)
+    a, b = np.meshgrid(iu, iv, indexing="ij")
+    a1, b1 = (a + 1) % nu, (b + 1) % nv
+    v00, v10, v01, v11 = a * nv + b, a1 * nv + b, a * nv + b1, a1 * nv + b1
+    return np.concatenate([np.stack([v00, v10, v11], -1).reshape(-1, 3), np.stack([v00, v11, v01], -1).reshape(-1, 3)], 0)
+
+
+def _box(lo, hi):
+    import numpy as np
+    lo, hi = np.asarray(lo, float), np.asarray(hi, float)
+    c = np.array([[x, y, z] for x in (lo[0], hi[0]) for y in (lo[1], hi[1]) for z in (lo[2], hi[2])])
+    quads = [(0, 1, 3, 2), (4, 6, 7, 5), (0, 4, 5, 1), (2, 3, 7, 6), (0, 2, 6, 4), (1, 5, 7, 3)]
+    f = np.array([[q[0], q[1], q[2]] for q in quads] + [[q[0], q[2], q[3]] for q in quads])
+    return c, f
+
+
+def synthetic_mesh(kind: str = "blob", seed: int = 0, detail: int = 64):
+    """-> vertices (nv, 3) float32, faces (nf, 3) int32 (CPU tensors).  kind: "sphere" | "blob" (sphere with seeded radial
+    harmonics: self-occlusion, silhouettes) | "torus" | "table" (few LARGE triangles: a top and four legs)."""
+    import numpy as np
+    rng = np.random.RandomState(seed)
+    if kind in ("sphere", "blob"):
+        nu, nv = detail, 2 * detail
+        th = np.linspace(0.02, np.pi - 0.02, nu)[:, None]
+        ph = (np.arange(nv) * (2 * np.pi / nv))[None, :]
+        r = 0.28 * np.ones((nu, nv))
+        if kind == "blob":
+            for _ in range(4):
+                a, b, p1, p2 = rng.randint(1, 5), rng.randint(1, 5), rng.rand() * 6.28, rng.rand() * 6.28
+                r = r + 0.03 * np.sin(a * th + p1) * np.cos(b * ph + p2)
+        v = np.stack([r * np.sin(th) * np.cos(ph), r * np.cos(th) + 0 * ph, r * np.sin(th) * np.sin(ph)], -1).reshape(-1, 3)
+        f = _grid_faces(nu, nv, False, True)
+    elif kind == "torus":
+        nu, nv = 2 * detail, detail
+        u = (np.arange(nu) * (2 * np.pi / nu))[:, None]
+        w = (np.arange(nv) * (2 * np.pi / nv))[None, :]
+        R0, r0 = 0.2, 0.08
+        v = np.stack([(R0 + r0 * np.cos(w)) * np.cos(u), r0 * np.sin(w) + 0 * u, (R0 + r0 * np.cos(w)) * np.sin(u)], -1).reshape(-1, 3)
+        f = _grid_faces(nu, nv, True, True)
+    elif kind == "table":
+        parts = [_box([-0.28, 0.10, -0.2], [0.28, 0.13, 0.2])]
+        for sx in (-1, 1):
+            for sz in (-1, 1):
+                parts.append(_box([sx * 0.25 - 0.02, -0.2, sz * 0.17 - 0.02], [sx * 0.25 + 0.02, 0.10, sz * 0.17 + 0.02]))
+        vs, fs, off = [], [], 0
+        for c, ff in parts:
+            vs.append(c)
+            fs.append(ff + off)
+            off += c.shape[0]
+        v, f = np.concatenate(vs, 0), np.concatenate(fs, 0)
+    else:
+        raise KeyError(kind)
+    # a seeded rigid tilt, so that no face is axis-aligned with the image grid
+    ax = rng.randn(3)
+    ax /= np.linalg.norm(ax)
+    ang = 0.5 * rng.rand() + 0.2
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    Rm = np.eye(3) + np.sin(ang) * K + (1 - np.cos(ang)) * K @ K
+    v = v @ Rm.T
+    f = np.concatenate([f, f[:, ::-1]], 0)
+    return torch.tensor(v, dtype=torch.float32), torch.tensor(np.ascontiguousarray(f), dtype=torch.int32)

@@ -515,6 +515,20 @@ int ccn_forward_run(ccn_exec_t* exec, const float* x, int64_t ldx, const float* 
                     const int64_t* curve_idxs, int64_t n, void* arena, int64_t arena_bytes, ccn_draw_fn draw,
                     void* draw_user, float* logits, int64_t ld_logits, int64_t* arena_needed_host, ccn_stream_t stream);
 
+/* ---- scanning simulator (csrc/sim_raster.cu, csrc/sim_scan.cu): mesh -> curve cloud, plain CUDA ----
+ * sim_rasterize: scanning_simulator/utils/minimal_rasterizer.py:14-51 `rasterize` = vertices @ R^T + t, Pinhole2D.project_ndc
+ *            (third_party/minimal_pytorch_rasterizer/minimal_pytorch_rasterizer/camera.py:38-61; fx = fy = res, cx = cy = res/2),
+ *            estimate_normals_cuda (.../cuda/rasterizer_kernel.cu:80-225 z-buffer, :335-465 point + face normal of the
+ *            closest face, back-facing windings culled by the inside test :194-198), mask = z_cam > 0, then the scene frame
+ *            (p - t) @ R, n @ R.  vertices (nv, 3) f32 scene frame; faces (nf, 3) i32; R (3, 3) row-major, t (3): DEVICE
+ *            pointers.  Out: coords / normals (res, res, 3) f32 [row i = image y, column j = image x], mask (res, res) u8,
+ *            depth_or_null (res, res) f32 camera depth (1e10 where nothing was hit).  Scratch: cam / ndc (nv, 3) f32,
+ *            keys res^2 u64, list (nf + 1) i32.  Where several faces lie within 1e-5 of the closest depth the reference
+ *            keeps whichever face's thread wrote last; here the closest face wins, equal depths -> lowest face index. */
+int ccn_sim_rasterize(const float* vertices, int64_t nv, const int32_t* faces, int64_t nf, const float* R, const float* t,
+                      int32_t res, float* cam_scratch, float* ndc_scratch, uint64_t* key_scratch, int32_t* list_scratch,
+                      float* coords, float* normals, uint8_t* mask, float* depth_or_null, ccn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
