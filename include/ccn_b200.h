@@ -529,6 +529,38 @@ int ccn_sim_rasterize(const float* vertices, int64_t nv, const int32_t* faces, i
                       int32_t res, float* cam_scratch, float* ndc_scratch, uint64_t* key_scratch, int32_t* list_scratch,
                       float* coords, float* normals, uint8_t* mask, float* depth_or_null, ccn_stream_t stream);
 
+/* sim_scan_lines: ONE attempt of ScanLineGenerator.generate_linear_scan_lines' while loop (scanning_simulator/utils/scanlines.py:24-76,
+ *            sample_line_points :133-144).  border (B, L, 2, 2) f64 = the attempt's line end points [line][end][u, v] (drawn on
+ *            the host like the reference: numpy RNG); sample k of a line = trunc((b1 - b0) * (k / ts + offset) + b0), in float32
+ *            when f32_math (integer borders of direction 'random') else float64 ('parallel' / 'grid'); offset = the
+ *            torch.rand(1) / ts draw.  A sample is kept when it is the first of its line on its pixel, masks[b][u][v] != 0 and
+ *            the mesh holds fewer than N points; kept samples go to uv (B, N, 3) i64 = (u, v, line_base + line) from position
+ *            npoints[b] on, in (line, sample) order; npoints (B) i32 running totals, updated (zero them before attempt 0).
+ * sim_scan_finish: scanlines.py:78-88 (line ids -> 0 .. lines-with-points - 1 per mesh, in place) and the pixel look-up of
+ *            SampleMeshes._sample_curves (scanning_simulator/utils/sampling.py:76-80): points / point_normals (B, N, 3) f32 =
+ *            coords / normals (B, res, res, 3) at (u, v); pass null for both to skip the look-up.  Call when every mesh has N. */
+int ccn_sim_scan_lines(const double* border, int32_t B, int32_t L, int32_t ts, float offset, int32_t f32_math, int32_t res,
+                       const uint8_t* masks, int32_t N, int32_t line_base, int32_t* npoints, int64_t* uv, ccn_stream_t stream);
+int ccn_sim_scan_finish(int64_t* uv, int32_t B, int32_t N, int32_t res, const float* coords, const float* normals,
+                        float* points_or_null, float* point_normals_or_null, ccn_stream_t stream);
+/* sim_curve_split: CurveClouds.compute_3d_curve_idxs (scanning_simulator/utils/curve_cloud.py:40-47): points (B, N, 3) f32;
+ *            curve_idx (B, N) i32 = number of edges longer than thresh (float64 norm; CURVE_SPLIT_THRESH = 0.01) before the
+ *            point; cstart / cend (B, N) i32: point range [cstart[c], cend[c]) of curve c (first ncurves[b] entries valid).
+ * sim_anti_alias: CurveClouds._anti_alias (curve_cloud.py:168-190): vals (B, N, 3) f32 -> out (B, N, 3) f64, the 7-tap
+ *            ANTI_ALIAS_KERNEL [1, 2, 3, 3, 3, 2, 2] along every curve divided by the same filter over the curve's extent.
+ * sim_curvature: CurveClouds.compute_curvature_new -> estimate_curvature_and_grads(points, X = points, curve ids, k)
+ *            (scanning_simulator/utils/curvature_approx.py:14-146; k nearest points of the own curve, Gaussian weights of width
+ *            kernel_width x mean within-curve edge length in arc length, weighted quadratic fit with hinge_reg on the constant
+ *            term): points (B, N, 3) f64 -> curvature (B, N, 3) f64 (curve normal x curvature), gradients (B, N, 3, 3) f64
+ *            (or null).  k <= 16.  Scratch: geo_raw / geo (B, N) f64, mean_edge (B) f64.  Float64 results agree with the
+ *            reference to summation order (its torch.linalg.solve / conv1d reduce in library order). */
+int ccn_sim_curve_split(const float* points, int32_t B, int32_t N, double thresh, int32_t* curve_idx, int32_t* cstart,
+                        int32_t* cend, int32_t* ncurves, ccn_stream_t stream);
+int ccn_sim_anti_alias(const float* vals, const int32_t* curve_idx, int32_t B, int32_t N, double* out, ccn_stream_t stream);
+int ccn_sim_curvature(const double* points, const int32_t* curve_idx, const int32_t* cstart, const int32_t* cend, int32_t B,
+                      int32_t N, int32_t k, double kernel_width, double hinge_reg, double* geo_raw_scratch, double* geo_scratch,
+                      double* mean_edge_scratch, double* curvature, double* gradients_or_null, ccn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
