@@ -210,6 +210,21 @@ struct Exec {
         h2d_off += (bytes + 15) & ~(size_t)15;
         return e == cudaSuccess ? CCN_OK : (int)e;
     }
+    // split read-back of <= 8 ints: `begin` queues the copy and marks it with an event, the caller queues whatever does not
+    // depend on the values, `end` waits for the EVENT only - the stream keeps running the work queued in between
+    cudaEvent_t rb_event = nullptr;
+    int readback_begin(const void* dev, int n_ints) {
+        if (oom) return CCN_ENOMEM;
+        if (n_ints > 8) return CCN_EINVAL;
+        if (!rb_event) EX_CUDA(cudaEventCreateWithFlags(&rb_event, cudaEventDisableTiming));
+        EX_CUDA(cudaMemcpyAsync(pinned + kMaxSamples + 8, dev, 4 * (size_t)n_ints, cudaMemcpyDeviceToHost, stream));
+        EX_CUDA(cudaEventRecord(rb_event, stream));
+        return CCN_OK;
+    }
+    int readback_end(const int32_t** vals) {
+        *vals = pinned + kMaxSamples + 8;
+        return sync_event(rb_event);
+    }
     int readback(const void* dev, int n_ints) {      // blocking read of n_ints int32 into `pinned`
         if (oom) return CCN_ENOMEM;
         EX_CUDA(cudaMemcpyAsync(pinned, dev, 4 * (size_t)n_ints, cudaMemcpyDeviceToHost, stream));
@@ -487,8 +502,17 @@ int knn_exact(Exec& ex, Level* fine, Level* coarse, int knn, int32_t* nbr, float
 struct Edges { int32_t *row_ptr, *erow, *ecol; int64_t E, nq; int max_degree; };
 
 // PointNetConv2.forward_edges (inference): decomposed first layer, fused chain kernel or the unfused launches
-int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts, int nxp, Level* src, Level* dst,
-              const Edges& e, Feat** out) {
+// The per-POINT half of the decomposed first layer, H = x_src W_x: it does not depend on the edge list, so the sa / sa-geo steps
+// queue it BEFORE they wait for the data-dependent edge count - the device works through it while the host is blocked.
+int pointconv_pre(Exec& ex, const int64_t* iv, Feat* const* xparts, int nxp, Feat** H) {
+    *H = nullptr;
+    if (iv[0] < 0) return CCN_OK;
+    Seg segs[4];
+    EX_CALL(segs_of(ex, xparts, nxp, segs));
+    return linear_planes(ex, ex.lins[iv[0]], segs, nxp, xparts[0]->n, 0, H, nullptr);
+}
+
+int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* H, Level* src, Level* dst, const Edges& e, Feat** out) {
     // iv: lin_x, wp_ptr, bias0_ptr, c1, act0, agg, chain (-1: none), n_local (layers after the first), local lin ids[n_local],
     //     n_att, attend lin ids[n_att];  fv: slope0, normalize_radius (0: none)
     const Linear* lin_x = iv[0] >= 0 ? &ex.lins[iv[0]] : nullptr;
@@ -499,12 +523,7 @@ int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts
     const int n_att = (int)iv[8 + n_local];
     const int64_t* att_ids = iv + 9 + n_local;
     const float slope0 = (float)fv[0], nradius = (float)fv[1];
-    Feat* H = nullptr;
-    if (lin_x) {
-        Seg segs[4];
-        EX_CALL(segs_of(ex, xparts, nxp, segs));
-        EX_CALL(linear_planes(ex, *lin_x, segs, nxp, xparts[0]->n, 0, &H, nullptr));
-    }
+    if ((lin_x != nullptr) != (H != nullptr) && !ex.oom) return CCN_EINVAL;
     const bool att = agg == CCN_AGG_ATTEND || agg == CCN_AGG_WSUM;
     if (chain >= 0 && e.max_degree <= 64) {
         const Chain& ch = ex.chains[chain];
@@ -569,11 +588,19 @@ int pointconv(Exec& ex, const int64_t* iv, const double* fv, Feat* const* xparts
 }
 
 // ops.dense_to_csr: (nq, K) table + per-row counts -> CSR (one read-back for E)
-int dense_to_csr(Exec& ex, int32_t* idx, int32_t* cnt, int64_t nq, int K, Edges* e) {
-    if (ex.oom) { *e = Edges{cnt, nullptr, nullptr, 0, nq, K}; return CCN_OK; }
+// in two halves: `begin` queues the scan of the counts and the read-back of their total, `end` waits for it and expands the
+// table - the caller queues the edge-independent part of the step in between
+int dense_to_csr_begin(Exec& ex, int32_t* cnt, int64_t nq) {
+    if (ex.oom) return CCN_OK;
     EX_CALL(ccn_excl_scan_i32(cnt, nq, cnt + nq + 1, (ccn_stream_t)ex.stream));
-    EX_CALL(ex.readback(cnt + nq + 1, 1));
-    const int64_t E = ex.pinned[0];
+    return ex.readback_begin(cnt + nq + 1, 1);
+}
+
+int dense_to_csr_end(Exec& ex, int32_t* idx, int32_t* cnt, int64_t nq, int K, Edges* e) {
+    if (ex.oom) { *e = Edges{cnt, nullptr, nullptr, 0, nq, K}; return CCN_OK; }
+    const int32_t* vals = nullptr;
+    EX_CALL(ex.readback_end(&vals));
+    const int64_t E = vals[0];
     int32_t* erow = ex.alloc_n<int32_t>(E);
     int32_t* ecol = ex.alloc_n<int32_t>(E);
     *e = Edges{cnt, erow, ecol, E, nq, K};
@@ -856,6 +883,7 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
 
 extern "C" void ccn_exec_destroy(ccn_exec_t* h) {
     if (!h) return;
+    if (h->ex.rb_event) cudaEventDestroy(h->ex.rb_event);
     if (h->ex.pinned) cudaFreeHost(h->ex.pinned);
     if (h->ex.h2d_ring) cudaFreeHost(h->ex.h2d_ring);
     if (h->ex.pinned_side) cudaFreeHost(h->ex.pinned_side);
@@ -1144,10 +1172,13 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     EX_CALL(fps_downsample(ex, lv, (float)fv[1], ch, &idx));
                 }
                 if (ex.oom) return CCN_ENOMEM;
-                const int64_t* pc_iv;
+                const int64_t* pc_iv = iv + 2;
                 const double* pc_fv = fv + 3;
                 Feat* xparts[2];
                 int nxp = 0;
+                if (cur.x) xparts[nxp++] = cur.x;
+                if (s.kind == ST_SA_GEO && (iv[0] || !cur.x)) xparts[nxp++] = &lv->pos;
+                Feat* H = nullptr;
                 if (s.kind == ST_SA_GEO) {
                     // ops.radius_1d_group
                     const int64_t nq = ch->n;
@@ -1158,11 +1189,15 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     if (!ex.oom) {
                         EX_CALL(ccn_radius_1d_group_count(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->curve, lv->n, lv->n_curves, idx, nq,
                                                           radius, kc, buf + nq + 2, buf, buf + nq + 1, st));
-                        EX_CALL(ex.readback(buf + nq + 1, 3));
-                        E = ex.pinned[0];
+                        EX_CALL(ex.readback_begin(buf + nq + 1, 3));
+                        EX_CALL(pointconv_pre(ex, pc_iv, xparts, nxp, &H));    // queued behind the copy: runs while the host waits
+                        if (ex.oom) return CCN_ENOMEM;
+                        const int32_t* vals = nullptr;
+                        EX_CALL(ex.readback_end(&vals));
+                        E = vals[0];
                         float kf, nf;
-                        std::memcpy(&kf, &ex.pinned[1], 4);
-                        std::memcpy(&nf, &ex.pinned[2], 4);
+                        std::memcpy(&kf, &vals[1], 4);
+                        std::memcpy(&nf, &vals[2], 4);
                         const float m = kf < nf ? kf : nf;
                         max_deg = m >= 1.f ? (int)m : 1;
                     }
@@ -1174,13 +1209,8 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     }
                     e = Edges{buf, erow, col, E, nq, max_deg};
                     if (!presampled) EX_CALL(subset_level(ex, lv, idx, ch));
-                    pc_iv = iv + 2;
-                    if (cur.x) xparts[nxp++] = cur.x;
-                    if (iv[0] || !cur.x) xparts[nxp++] = &lv->pos;
                 } else {
                     if (!presampled || ex.pre[si].voxel) EX_CALL(subset_level(ex, lv, idx, ch));
-                    pc_iv = iv + 2;
-                    if (cur.x) xparts[nxp++] = cur.x;
                 }
                 // The look-ahead work (next levels' samplers on the side stream, neighbour tables on the geometry stream) is
                 // HOST work too - the draw callbacks, a dozen launches, for a voxel sampler 70 us of noise generation - and used to
@@ -1193,17 +1223,21 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 }
                 Feat* o = nullptr;
                 if (s.kind == ST_SA_GEO) {
-                    EX_CALL(pointconv(ex, pc_iv, pc_fv, xparts, nxp, lv, ch, e, &o));     // no host wait inside: all queued
+                    if (ex.oom) return CCN_ENOMEM;
+                    EX_CALL(pointconv(ex, pc_iv, pc_fv, H, lv, ch, e, &o));               // no host wait inside: all queued
                     EX_CALL(presample_ahead(ex, (int)si, ch, lvl_done));
                     EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx, lvl_done));
                 } else {
                     const int K = (int)iv[1];
                     int32_t *nbr = nullptr, *cnt = nullptr;
                     EX_CALL(frnn(ex, ch, lv, K, radius, true, &nbr, &cnt));
+                    EX_CALL(dense_to_csr_begin(ex, cnt, ch->n));                          // scan + read-back of the edge count, queued
+                    EX_CALL(pointconv_pre(ex, pc_iv, xparts, nxp, &H));                   // independent of the edges: behind the copy
                     EX_CALL(presample_ahead(ex, (int)si, ch, lvl_done));                  // while the search runs
                     EX_CALL(geometry_ahead(ex, (int)si, lv, ch, idx, lvl_done));
-                    EX_CALL(dense_to_csr(ex, nbr, cnt, ch->n, K, &e));                    // host waits for the edge count
-                    EX_CALL(pointconv(ex, pc_iv, pc_fv, xparts, nxp, lv, ch, e, &o));
+                    EX_CALL(dense_to_csr_end(ex, nbr, cnt, ch->n, K, &e));                // host waits for the copy's event only
+                    if (ex.oom) return CCN_ENOMEM;
+                    EX_CALL(pointconv(ex, pc_iv, pc_fv, H, lv, ch, e, &o));
                 }
                 outp.x = o;
                 outp.lv = ch;
