@@ -20,6 +20,7 @@
 //            two warps per TMEM lane quarter, alternating 32-column chunks.
 // Tile order: tile t -> (m = t / tiles_n, n = t % tiles_n); the grid is a multiple of tiles_n in resident mode, so
 // a CTA keeps one N-slice and the CTAs sharing an A tile run concurrently (second read served by L2).
+#include <cstdlib>
 #include <type_traits>
 
 #include "common.cuh"
@@ -141,19 +142,24 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        // converged warp, one elected lane issues (see the MMA issuer below); ring slot and phase are carried, not divided out
+        {
             if (p.resident) {
                 const int n0 = (blockIdx.x % p.tiles_n) * BN;
-                mbar_arrive_expect_tx(wfull, (uint32_t)(nk * P * wtile));
-                for (int kc = 0; kc < nk; ++kc) {
-                    load_w_tile(w_res + (kc * P) * wtile, &w_hi, kc, n0, BN, p.b_mn, wfull);
-                    if (P == 2) load_w_tile(w_res + (kc * P + 1) * wtile, &w_lo, kc, n0, BN, p.b_mn, wfull);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(wfull, (uint32_t)(nk * P * wtile));
+                    for (int kc = 0; kc < nk; ++kc) {
+                        load_w_tile(w_res + (kc * P) * wtile, &w_hi, kc, n0, BN, p.b_mn, wfull);
+                        if (P == 2) load_w_tile(w_res + (kc * P + 1) * wtile, &w_lo, kc, n0, BN, p.b_mn, wfull);
+                    }
                 }
+                __syncwarp();
             }
-            uint32_t cnt = 0;
+            int slot = 0;
+            uint32_t phase = 1;                                         // parity to wait for on `empty`: slots start free
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 const int m0 = (t / p.tiles_n) * kBM, n0 = (t % p.tiles_n) * BN;
-                for (int kc = 0; kc < nk; ++kc, ++cnt) {
+                for (int kc = 0; kc < nk; ++kc) {
                     const CUtensorMap *mh, *ml;
                     int ka;                                             // column inside the segment's planes
                     int roff = 0;                                       // row shift of a convolution tap
@@ -165,27 +171,34 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                     else if (kc < p.sc2) { mh = &am.hi[1]; ml = &am.lo[1]; ka = (kc - p.sc1) * kBK; }
                     else if (kc < p.sc3) { mh = &am.hi[2]; ml = &am.lo[2]; ka = (kc - p.sc2) * kBK; }
                     else { mh = &am.hi[3]; ml = &am.lo[3]; ka = (kc - p.sc3) * kBK; }
-                    const int s = cnt % stages;
-                    mbar_wait(empty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
-                    const uint32_t dst = ring0 + s * stage_bytes;
-                    mbar_arrive_expect_tx(full0 + 8 * s, (uint32_t)stage_bytes);
-                    tma_load_2d(dst, mh, ka, m0 + roff, full0 + 8 * s);      // rows outside [0, M) arrive as zeros
-                    if (P == 2) tma_load_2d(dst + kATile, ml, ka, m0 + roff, full0 + 8 * s);
-                    if (!p.resident) {
-                        load_w_tile(dst + P * kATile, &w_hi, kc, n0, BN, p.b_mn, full0 + 8 * s);
-                        if (P == 2) load_w_tile(dst + P * kATile + wtile, &w_lo, kc, n0, BN, p.b_mn, full0 + 8 * s);
+                    mbar_wait(empty0 + 8 * slot, phase);
+                    const uint32_t dst = ring0 + slot * stage_bytes;
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(full0 + 8 * slot, (uint32_t)stage_bytes);
+                        tma_load_2d(dst, mh, ka, m0 + roff, full0 + 8 * slot);      // rows outside [0, M) arrive as zeros
+                        if (P == 2) tma_load_2d(dst + kATile, ml, ka, m0 + roff, full0 + 8 * slot);
+                        if (!p.resident) {
+                            load_w_tile(dst + P * kATile, &w_hi, kc, n0, BN, p.b_mn, full0 + 8 * slot);
+                            if (P == 2) load_w_tile(dst + P * kATile + wtile, &w_lo, kc, n0, BN, p.b_mn, full0 + 8 * slot);
+                        }
                     }
+                    __syncwarp();
+                    if (++slot == stages) { slot = 0; phase ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
+        // The whole warp runs the control flow (converged); ONE lane, chosen by elect.sync, issues.  Under `if (lane == 0)`
+        // ptxas cannot prove the region single-threaded and wraps every tcgen05.mma in a per-lane loop
+        // (ELECT ... @P0 BRA.U.ANY, ~7 extra instructions per MMA on the thread that bounds the narrow-tile layers).
+        {
             if (p.resident) {
                 mbar_wait(wfull, 0);
                 tc_fence_after();
             }
-            uint32_t cnt = 0;
+            int slot = 0;
+            uint32_t phase = 0;                                         // parity to wait for on `full`
             int it = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
                 const int n0 = (t % p.tiles_n) * BN;
@@ -197,29 +210,50 @@ __global__ void __launch_bounds__(kThreads, 1) linear_planes_kernel(
                 mbar_wait(tempty0 + 8 * buf, ((it >> 1) & 1) ^ 1);     // epilogue has drained this accumulator
                 tc_fence_after();
                 const uint32_t acc = tmem_base + (uint32_t)(buf * BN);
-                for (int kc = 0; kc < nk; ++kc, ++cnt) {
-                    const int s = cnt % stages;
-                    mbar_wait(full0 + 8 * s, (cnt / stages) & 1);
+                for (int kc = 0; kc < nk; ++kc) {
+                    const int s = slot;
+                    mbar_wait(full0 + 8 * s, phase);
                     tc_fence_after();
                     const uint32_t a_hi_s = ring0 + s * stage_bytes;
                     const uint32_t a_lo_s = a_hi_s + kATile;
                     const uint32_t w_hi_s = p.resident ? w_res + (kc * P) * wtile : a_hi_s + P * kATile;
                     const uint32_t w_lo_s = w_hi_s + wtile;
+                    // The issuing thread is the bottleneck of the narrow-tile layers (12 MMAs per chunk, ~14 SASS instructions of
+                    // descriptor arithmetic each = 0.65 us per chunk whatever the tile width, tools/bench_linear2.py small): the
+                    // descriptors of a stage are built ONCE, a k-step of 16 bf16 = 32 bytes = +2 in their 16-byte address field
+                    // (tiles are 1024-byte aligned: no carry out of the field)
+                    const uint64_t da_hi = umma_desc_sw128(a_hi_s), da_lo = umma_desc_sw128(a_lo_s);
+                    if (elect_one()) {
+                    if (!p.b_mn) {
+                        const uint64_t dw_hi = umma_desc_sw128(w_hi_s), dw_lo = umma_desc_sw128(w_lo_s);
 #pragma unroll
-                    for (int k = 0; k < kBK / 16; ++k) {
-                        const uint32_t ko = k * 32;     // 16 bf16 = 32 bytes inside the 128-byte swizzle row
-                        // MN-major B: 16 reduction rows of 128 bytes further down the box
-                        const uint64_t dwh = p.b_mn ? umma_desc_mn_sw128(w_hi_s + k * 2048, kBoxBytes) : umma_desc_sw128(w_hi_s + ko);
-                        umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), dwh, idesc, (kc | k) ? 1u : 0u);
-                        if (P == 2) {
-                            const uint64_t dwl = p.b_mn ? umma_desc_mn_sw128(w_lo_s + k * 2048, kBoxBytes) : umma_desc_sw128(w_lo_s + ko);
-                            umma_bf16(acc, umma_desc_sw128(a_lo_s + ko), dwh, idesc, 1u);
-                            umma_bf16(acc, umma_desc_sw128(a_hi_s + ko), dwl, idesc, 1u);
+                        for (int k = 0; k < kBK / 16; ++k) {
+                            umma_bf16(acc, da_hi + 2 * k, dw_hi + 2 * k, idesc, (kc | k) ? 1u : 0u);
+                            if (P == 2) {
+                                umma_bf16(acc, da_lo + 2 * k, dw_hi + 2 * k, idesc, 1u);
+                                umma_bf16(acc, da_hi + 2 * k, dw_lo + 2 * k, idesc, 1u);
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < kBK / 16; ++k) {
+                            // MN-major B: 16 reduction rows of 128 bytes further down the box
+                            const uint64_t dwh = umma_desc_mn_sw128(w_hi_s + k * 2048, kBoxBytes);
+                            umma_bf16(acc, da_hi + 2 * k, dwh, idesc, (kc | k) ? 1u : 0u);
+                            if (P == 2) {
+                                const uint64_t dwl = umma_desc_mn_sw128(w_lo_s + k * 2048, kBoxBytes);
+                                umma_bf16(acc, da_lo + 2 * k, dwh, idesc, 1u);
+                                umma_bf16(acc, da_hi + 2 * k, dwl, idesc, 1u);
+                            }
                         }
                     }
                     umma_commit(empty0 + 8 * s);        // stage reusable once these MMAs have read it
+                    }
+                    __syncwarp();
+                    if (++slot == stages) { slot = 0; phase ^= 1u; }
                 }
-                umma_commit(tfull0 + 8 * buf);          // accumulator of this tile complete
+                if (elect_one()) umma_commit(tfull0 + 8 * buf);          // accumulator of this tile complete
+                __syncwarp();
             }
         }
     } else {

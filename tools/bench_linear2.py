@@ -17,6 +17,9 @@ npl = cnn.n_planes()
 SHAPES = [(111783, 128, 128, "f32"), (63177, 128, 128, "planes"), (63177, 128, 128, "both"), (92638, 256, 256, "planes"),
           (92638, 256, 192, "both"), (30420, 256, 256, "planes"), (40278, 256, 256, "f32"), (15251, 512, 512, "planes"),
           (3633, 1024, 1024, "planes"), (17287, 128, 128, "planes"), (32226, 128, 128, "both")]
+if len(sys.argv) > 2 and sys.argv[2] == "small":        # the level 4 / 5 layers: M of one or a few row tiles, wide N and K
+    SHAPES = [(173, 2048, 3072, "planes"), (173, 2048, 1024, "planes"), (173, 1024, 2048, "both"), (576, 1024, 2051, "planes"),
+              (576, 1024, 1024, "planes"), (576, 512, 1024, "both"), (1918, 512, 512, "planes"), (1918, 256, 512, "both")]
 REPS = 12
 
 
@@ -56,7 +59,7 @@ for M, N, K, out in SHAPES:
     As = [ops.pack_planes([torch.randn(M, K, device="cuda")], npl) for _ in range(4)]
     auto = tw.pick_box_planes(M, npl)
     byts = M * K * 2 * npl + N * K * 2 * npl + M * N * ((4 if out != "planes" else 0) + (2 * npl if out != "f32" else 0))
-    for box in (256, 128, 64):
+    for box in (256, 128, 64, 32):
         if box // 2 >= N and box != 32:
             continue
         try:

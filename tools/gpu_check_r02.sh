@@ -22,17 +22,23 @@ cut -c1-300 $O/${TAG}_bench_reference.json
 python tools/host_profile.py > $O/${TAG}_host_profile.txt 2>&1
 head -4 $O/${TAG}_host_profile.txt
 python tools/bench_fused.py bf16x3 > $O/${TAG}_fused_bf16x3.txt 2>&1; python tools/bench_fused.py bf16 > $O/${TAG}_fused_bf16.txt 2>&1
-python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant > $O/${TAG}_plain.log 2>&1 &&
+python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant --no-train-variant > $O/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $O/${TAG}_launches.csv \
-    python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant > $O/${TAG}_ncu.log 2>&1
+    python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant --no-train-variant > $O/${TAG}_ncu.log 2>&1
 echo "ncu exit $?"
 python tools/summarize_launches.py $O/${TAG}_launches.csv > $O/${TAG}_launches_summary.txt 2>&1
 gzip -f $O/${TAG}_launches.csv
-ncu --set full --clock-control none --import-source on -k regex:linear_planes_kernel -s 60 -c 6 -f -o $O/${TAG}_linear_planes \
-    python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant > $O/${TAG}_ncu_full.log 2>&1
+# EVERY linear_planes launch of one forward (73: the third forward of tools/ncu_forward.py), so that the mean DRAM bytes per
+# launch (bench.py's roofline.traffic) is over the same population as the algorithmic bytes per launch it is compared with
+python tools/ncu_forward.py > $O/${TAG}_ncu_forward_plain.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:linear_planes_kernel -s 146 -c 73 -f -o $O/${TAG}_linear_planes \
+    python tools/ncu_forward.py > $O/${TAG}_ncu_full.log 2>&1
 ncu -i $O/${TAG}_linear_planes.ncu-rep --page raw --csv > $O/${TAG}_linear_planes_raw.csv 2>/dev/null
+python tools/timeline.py bf16x3 > $O/${TAG}_timeline.txt 2>&1
+python tools/bench_simulator.py > $O/${TAG}_simulator.txt 2>&1
+python tools/bench_linear2.py bf16x3 > $O/${TAG}_linear2.txt 2>&1
 ncu --set full --clock-control none --import-source on -k regex:edge_chain_kernel -s 2 -c 2 -f -o $O/${TAG}_edge_chain \
-    python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant > $O/${TAG}_ncu_full2.log 2>&1
+    python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-batched-variant --no-train-variant > $O/${TAG}_ncu_full2.log 2>&1
 ncu -i $O/${TAG}_edge_chain.ncu-rep --page raw --csv > $O/${TAG}_edge_chain_raw.csv 2>/dev/null
 rm -f $O/${TAG}_linear_planes.ncu-rep $O/${TAG}_edge_chain.ncu-rep
 echo done
