@@ -197,22 +197,27 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer: the weight stream
-        if (lane == 0) {
-            uint32_t cnt = 0;
+        // (converged warp, one elected lane issues; ring slot / phase carried - see gemm_planes.cu)
+        {
+            int s = 0;
+            uint32_t ph = 1;
             for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
                 for (int l = 0; l < p.L; ++l) {
                     const int N = p.ly[l].N, nk = p.ly[l].K >> 6, wrow = p.ly[l].w_row;
                     for (int n0 = 0; n0 < N; n0 += 128) {
                         const int mma_n = (min(128, N - n0) + 63) & ~63;     // whole 64-row boxes (rows past the matrix: zeros)
-                        for (int kc = 0; kc < nk; ++kc, ++cnt) {
-                            const int s = cnt % stages;
-                            mbar_wait(wempty0 + 8 * s, ((cnt / stages) & 1) ^ 1);
+                        for (int kc = 0; kc < nk; ++kc) {
+                            mbar_wait(wempty0 + 8 * s, ph);
                             const uint32_t dst = ring0 + s * stage_bytes;
-                            mbar_arrive_expect_tx(wfull0 + 8 * s, (uint32_t)(P * mma_n * 128));
-                            for (int b = 0; b < mma_n; b += 64) {
-                                tma_load_2d(dst + b * 128, &w_hi, kc * 64, wrow + n0 + b, wfull0 + 8 * s);
-                                if (P == 2) tma_load_2d(dst + p.w_plane_bytes + b * 128, &w_lo, kc * 64, wrow + n0 + b, wfull0 + 8 * s);
+                            if (elect_one()) {
+                                mbar_arrive_expect_tx(wfull0 + 8 * s, (uint32_t)(P * mma_n * 128));
+                                for (int b = 0; b < mma_n; b += 64) {
+                                    tma_load_2d(dst + b * 128, &w_hi, kc * 64, wrow + n0 + b, wfull0 + 8 * s);
+                                    if (P == 2) tma_load_2d(dst + p.w_plane_bytes + b * 128, &w_lo, kc * 64, wrow + n0 + b, wfull0 + 8 * s);
+                                }
                             }
+                            __syncwarp();
+                            if (++s == stages) { s = 0; ph ^= 1u; }
                         }
                     }
                 }
@@ -220,8 +225,9 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer
-        if (lane == 0) {
-            uint32_t cnt = 0, aphase = 0;
+        {
+            uint32_t aphase = 0, ph = 0;
+            int s = 0;
             for (int t = blockIdx.x; t < p.n_tiles; t += gridDim.x) {
                 for (int l = 0; l < p.L; ++l) {
                     const int N = p.ly[l].N, nk = p.ly[l].K >> 6;
@@ -234,25 +240,31 @@ __global__ void __launch_bounds__(kThreads, 2) edge_chain_kernel(const __grid_co
                         // instruction descriptor: D=f32, A=B=bf16, K-major both, N>>3 at bit 17, M>>4 at bit 24
                         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(mma_n >> 3) << 17) |
                                                ((uint32_t)(kRows >> 4) << 24);
-                        for (int kc = 0; kc < nk; ++kc, ++cnt) {
-                            const int s = cnt % stages;
-                            mbar_wait(wfull0 + 8 * s, (cnt / stages) & 1);
+                        for (int kc = 0; kc < nk; ++kc) {
+                            mbar_wait(wfull0 + 8 * s, ph);
                             tc_fence_after();
                             const uint32_t a_hi = res0 + (uint32_t)(kc * P) * kChunkBytes, a_lo = a_hi + kChunkBytes;
                             const uint32_t b_hi = ring0 + s * stage_bytes, b_lo = b_hi + p.w_plane_bytes;
+                            // descriptors once per chunk; a k-step of 16 bf16 = 32 bytes = +2 in the 16-byte address field
+                            const uint64_t da_hi = umma_desc_sw128(a_hi), da_lo = umma_desc_sw128(a_lo);
+                            const uint64_t db_hi = umma_desc_sw128(b_hi), db_lo = umma_desc_sw128(b_lo);
+                            if (elect_one()) {
 #pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const uint32_t ko = k * 32;         // 16 bf16 = 32 bytes inside the 128-byte swizzle row
-                                umma_bf16(acc + n0, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_hi + ko), idesc, (kc | k) ? 1u : 0u);
-                                if (P == 2) {
-                                    umma_bf16(acc + n0, umma_desc_sw128(a_lo + ko), umma_desc_sw128(b_hi + ko), idesc, 1u);
-                                    umma_bf16(acc + n0, umma_desc_sw128(a_hi + ko), umma_desc_sw128(b_lo + ko), idesc, 1u);
+                                for (int k = 0; k < 4; ++k) {
+                                    umma_bf16(acc + n0, da_hi + 2 * k, db_hi + 2 * k, idesc, (kc | k) ? 1u : 0u);
+                                    if (P == 2) {
+                                        umma_bf16(acc + n0, da_lo + 2 * k, db_hi + 2 * k, idesc, 1u);
+                                        umma_bf16(acc + n0, da_hi + 2 * k, db_lo + 2 * k, idesc, 1u);
+                                    }
                                 }
+                                umma_commit(wempty0 + 8 * s);       // ring slot reusable once these MMAs have read it
                             }
-                            umma_commit(wempty0 + 8 * s);           // ring slot reusable once these MMAs have read it
+                            __syncwarp();
+                            if (++s == stages) { s = 0; ph ^= 1u; }
                         }
                     }
-                    umma_commit(acc_full);                          // accumulator complete, A operand no longer read
+                    if (elect_one()) umma_commit(acc_full);         // accumulator complete, A operand no longer read
+                    __syncwarp();
                 }
             }
         }
