@@ -90,52 +90,64 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_tc_kernel(
 
     if (c_end > c_beg) {
         if (warp == 0) {
-            if (lane == 0) {
-                uint32_t cnt = 0;
-                for (int c = c_beg; c < c_end; ++c, ++cnt) {
-                    const int s = cnt % p.stages;
-                    mbar_wait(empty0 + 8 * s, ((cnt / p.stages) & 1) ^ 1);
+            // converged warp, one elected lane issues; ring slot / phase carried (see gemm_planes.cu)
+            {
+                int s = 0;
+                uint32_t ph = 1;
+                for (int c = c_beg; c < c_end; ++c) {
+                    mbar_wait(empty0 + 8 * s, ph);
                     const uint32_t dst = ring0 + s * stage_bytes;
                     const uint32_t fb = full0 + 8 * s;
                     const int m0 = c * kRows;
-                    mbar_arrive_expect_tx(fb, (uint32_t)stage_bytes);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(fb, (uint32_t)stage_bytes);
 #pragma unroll
-                    for (int pl = 0; pl < P; ++pl) {
-                        const CUtensorMap* my = pl ? &dy_lo : &dy_hi;
-                        const CUtensorMap* mx = pl ? &x_lo : &x_hi;
-                        tma_load_2d(dst + pl * a_plane, my, n0, m0, fb);
-                        tma_load_2d(dst + pl * a_plane + kBoxBytes, my, n0 + 64, m0, fb);
-                        const uint32_t bdst = dst + P * a_plane + pl * b_plane;
-                        for (int j = 0; j < nb; ++j) tma_load_2d(bdst + j * kBoxBytes, mx, k0 + 64 * j, m0 + p.x_row_off, fb);
+                        for (int pl = 0; pl < P; ++pl) {
+                            const CUtensorMap* my = pl ? &dy_lo : &dy_hi;
+                            const CUtensorMap* mx = pl ? &x_lo : &x_hi;
+                            tma_load_2d(dst + pl * a_plane, my, n0, m0, fb);
+                            tma_load_2d(dst + pl * a_plane + kBoxBytes, my, n0 + 64, m0, fb);
+                            const uint32_t bdst = dst + P * a_plane + pl * b_plane;
+                            for (int j = 0; j < nb; ++j) tma_load_2d(bdst + j * kBoxBytes, mx, k0 + 64 * j, m0 + p.x_row_off, fb);
+                        }
                     }
+                    __syncwarp();
+                    if (++s == p.stages) { s = 0; ph ^= 1u; }
                 }
             }
         } else if (warp == 1) {
-            if (lane == 0) {
+            {
                 // D = f32, A = B = bf16, both MN-major (bits 15, 16), N >> 3 at bit 17, M >> 4 at bit 24
                 const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                                        ((uint32_t)(p.BKc >> 3) << 17) | ((uint32_t)(kWM >> 4) << 24);
-                uint32_t cnt = 0;
-                for (int c = c_beg; c < c_end; ++c, ++cnt) {
-                    const int s = cnt % p.stages;
-                    mbar_wait(full0 + 8 * s, (cnt / p.stages) & 1);
+                int s = 0;
+                uint32_t ph = 0;
+                bool first = true;
+                for (int c = c_beg; c < c_end; ++c) {
+                    mbar_wait(full0 + 8 * s, ph);
                     tc_fence_after();
                     const uint32_t a_hi = ring0 + s * stage_bytes, a_lo = a_hi + a_plane;
                     const uint32_t b_hi = a_hi + P * a_plane, b_lo = b_hi + b_plane;
+                    if (elect_one()) {
 #pragma unroll
-                    for (int ks = 0; ks < kRows / 16; ++ks) {
-                        const uint32_t ko = ks * 16 * 128;                 // 16 K-rows of 128 bytes
-                        const uint64_t da = umma_desc_mn_sw128(a_hi + ko, kBoxBytes);
-                        const uint64_t db = umma_desc_mn_sw128(b_hi + ko, kBoxBytes);
-                        umma_bf16(tmem_base, da, db, idesc, (cnt | ks) ? 1u : 0u);
-                        if (P == 2) {
-                            umma_bf16(tmem_base, umma_desc_mn_sw128(a_lo + ko, kBoxBytes), db, idesc, 1u);
-                            umma_bf16(tmem_base, da, umma_desc_mn_sw128(b_lo + ko, kBoxBytes), idesc, 1u);
+                        for (int ks = 0; ks < kRows / 16; ++ks) {
+                            const uint32_t ko = ks * 16 * 128;             // 16 K-rows of 128 bytes
+                            const uint64_t da = umma_desc_mn_sw128(a_hi + ko, kBoxBytes);
+                            const uint64_t db = umma_desc_mn_sw128(b_hi + ko, kBoxBytes);
+                            umma_bf16(tmem_base, da, db, idesc, (first && ks == 0) ? 0u : 1u);
+                            if (P == 2) {
+                                umma_bf16(tmem_base, umma_desc_mn_sw128(a_lo + ko, kBoxBytes), db, idesc, 1u);
+                                umma_bf16(tmem_base, da, umma_desc_mn_sw128(b_lo + ko, kBoxBytes), idesc, 1u);
+                            }
                         }
+                        umma_commit(empty0 + 8 * s);
                     }
-                    umma_commit(empty0 + 8 * s);
+                    __syncwarp();
+                    first = false;
+                    if (++s == p.stages) { s = 0; ph ^= 1u; }
                 }
-                umma_commit(tfull);
+                if (elect_one()) umma_commit(tfull);
+                __syncwarp();
             }
         } else {
             const int q = warp & 3;
