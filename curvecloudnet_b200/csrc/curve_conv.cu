@@ -6,6 +6,8 @@
 // (three host syncs).  Here the padded signal exists only as an index map (row2pt); every layer is
 // one kernel: tap-shifted FMA over a shared-memory tile of the signal, BatchNorm (eval) folded into
 // the mirrored weights, LeakyReLU in the epilogue, pad rows skipped on the last layer.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace {
@@ -34,6 +36,57 @@ __global__ void curve_feat_prep_kernel(const float* __restrict__ x, int64_t ldx,
             const float den = fmaxf((vf ? 1.f : 0.f) + (vb ? 1.f : 0.f), 1.f);
             out[i * ldo + c_in + c] = fabsf(__fdiv_rn(__fadd_rn(ef, eb), den));
         }
+    }
+}
+
+// feat_prep + row gather + plane packing in one pass: the bf16 planes of the padded signal rows [x, pos, |diff|] that the
+// first tensor-core conv layer reads, without the fp32 feature matrix (n x 2 c_in), its gathered copy (rows x 2 c_in) and
+// the pack kernel's read of it.  Same fp32 values as curve_feat_prep_kernel, same split as ccn_pack_planes: bit-identical.
+// One thread per (row, 8 output columns); pad rows (row2pt < 0) and pad columns are zeros.
+__global__ void curve_feat_planes_kernel(const float* __restrict__ x, int64_t ldx, int cx, const float* __restrict__ pos,
+                                         int with_xyz, int with_diff, const int32_t* __restrict__ ord, int64_t n,
+                                         const int32_t* __restrict__ row2pt, int64_t rows, __nv_bfloat16* __restrict__ planes,
+                                         int64_t kpad, int64_t plane_stride, int n_planes) {
+    ccn_pdl_wait();
+    const int c_in = cx + (with_xyz ? 3 : 0), C = with_diff ? 2 * c_in : c_in;
+    const int groups = (int)(kpad >> 3);
+    const int64_t total = rows * groups;
+    for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r;
+        int g;
+        ccn_divmod(t, groups, r, g);
+        const int64_t i = row2pt[r];
+        float y[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y[e] = 0.f;
+        if (i >= 0) {
+            const int o = with_diff ? ord[i] : 0;
+            const bool vb = with_diff && i > 0 && ord[i - 1] == o;
+            const bool vf = with_diff && i + 1 < n && ord[i + 1] == o;
+            const float den = fmaxf((vf ? 1.f : 0.f) + (vb ? 1.f : 0.f), 1.f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int col = 8 * g + e;
+                if (col >= C) break;
+                const int c = col < c_in ? col : col - c_in;
+                auto feat = [&](int64_t q) -> float { return c < cx ? x[q * ldx + c] : pos[q * 3 + (c - cx)]; };
+                const float v = feat(i);
+                if (col < c_in) { y[e] = v; continue; }
+                const float eb = vb ? __fsub_rn(v, feat(i - 1)) : 0.f;
+                const float ef = vf ? __fsub_rn(feat(i + 1), v) : 0.f;
+                y[e] = fabsf(__fdiv_rn(__fadd_rn(ef, eb), den));
+            }
+        }
+        __nv_bfloat162 h[4], l[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            h[e] = __floats2bfloat162_rn(y[2 * e], y[2 * e + 1]);
+            const float2 f = __bfloat1622float2(h[e]);
+            l[e] = __floats2bfloat162_rn(y[2 * e] - f.x, y[2 * e + 1] - f.y);
+        }
+        __nv_bfloat16* op = planes + r * kpad + 8 * g;
+        *reinterpret_cast<uint4*>(op) = *reinterpret_cast<uint4*>(h);
+        if (n_planes == 2) *reinterpret_cast<uint4*>(op + plane_stride) = *reinterpret_cast<uint4*>(l);
     }
 }
 
@@ -125,6 +178,21 @@ extern "C" int ccn_curve_feat_prep(const float* x, int64_t ldx, int32_t cx, cons
     if (n == 0) return CCN_OK;
     ccn_launch(curve_feat_prep_kernel, dim3(ccn_grid(n * c_in, 256)), dim3(256), 0, (cudaStream_t)stream, x, ldx, cx, pos, with_xyz,
                                                                                      with_diff, curve_ord, n, out, ldo);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_curve_feat_planes(const float* x, int64_t ldx, int32_t cx, const float* pos, int32_t with_xyz, int32_t with_diff,
+                                     const int32_t* curve_ord, int64_t n, const int32_t* row2pt, int64_t rows, void* planes,
+                                     int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream) {
+    const int c_in = cx + (with_xyz ? 3 : 0);
+    CCN_REQUIRE(n >= 0 && rows >= 0 && c_in > 0 && planes && row2pt && (cx == 0 || x) && (!with_xyz || pos) && (!with_diff || curve_ord));
+    CCN_REQUIRE((kpad & 7) == 0 && kpad >= (with_diff ? 2 : 1) * c_in && (n_planes == 1 || (n_planes == 2 && (plane_stride & 7) == 0)) &&
+                (reinterpret_cast<uintptr_t>(planes) & 15) == 0);
+    if (rows == 0) return CCN_OK;
+    ccn_launch(curve_feat_planes_kernel, dim3(ccn_grid(rows * (kpad >> 3), 256, 148LL * 32)), dim3(256), 0, (cudaStream_t)stream, x, ldx,
+               (int)cx, pos, (int)with_xyz, (int)with_diff, curve_ord, n, row2pt, rows, (__nv_bfloat16*)planes, kpad, plane_stride,
+               (int)n_planes);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

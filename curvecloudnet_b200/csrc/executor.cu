@@ -1013,23 +1013,33 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 const int64_t np = lv->n;
                 const int cx = cur.x ? cur.x->c : 0;
                 const int c_in = cx + (with_xyz ? 3 : 0);
-                Feat* feats = ex.new_feat(np, c_in * (with_diff ? 2 : 1));
-                if (!ex.oom)
-                    EX_CALL(ccn_curve_feat_prep(cur.x ? cur.x->f : nullptr, cur.x ? cur.x->ld : 0, cx, lv->pos.f, with_xyz, with_diff,
-                                                lv->curve_ord, np, feats->f, feats->ld, st));
                 const int pad = ksize > 1 ? (ksize / 2) * nl : 0;
                 const int64_t rows = np + (int64_t)(lv->n_curves + 1) * pad;
+                const int tcf = rows > 0 ? tc_from : nl;
+                // every layer on the tensor cores: the signal planes are formed in ONE pass (ccn_curve_feat_planes) - the fp32
+                // feature matrix, its gathered copy and the pack kernel's read of it (78 us at the decoder's 32 k x 262) are skipped
+                const bool direct = tcf == 0 && nl > 0;
+                Feat* feats = direct ? nullptr : ex.new_feat(np, c_in * (with_diff ? 2 : 1));
+                if (!direct && !ex.oom)
+                    EX_CALL(ccn_curve_feat_prep(cur.x ? cur.x->f : nullptr, cur.x ? cur.x->ld : 0, cx, lv->pos.f, with_xyz, with_diff,
+                                                lv->curve_ord, np, feats->f, feats->ld, st));
                 int32_t* row2pt = ex.alloc_n<int32_t>(rows);
                 if (!ex.oom) EX_CALL(ccn_curve_row_map(lv->curve_ord, np, lv->n_curves, pad, row2pt, st));
-                const int tcf = rows > 0 ? tc_from : nl;
                 Feat* sig = feats;
                 Planes sigp;
                 bool have_p = false;
+                if (direct) {
+                    sigp = ex.alloc_planes(rows, c_in * (with_diff ? 2 : 1));
+                    have_p = true;
+                    if (!ex.oom)
+                        EX_CALL(ccn_curve_feat_planes(cur.x ? cur.x->f : nullptr, cur.x ? cur.x->ld : 0, cx, lv->pos.f, with_xyz, with_diff,
+                                                      lv->curve_ord, np, row2pt, rows, sigp.buf, sigp.kpad, sigp.pstride, ex.npl, st));
+                }
                 for (int li = 0; li < nl; ++li) {
                     const Conv& cv = ex.convs[iv[5 + li]];
                     const bool first = li == 0, last = li == nl - 1;
                     if (li >= tcf) {
-                        if (first) {
+                        if (first && !direct) {
                             Feat* g = ex.new_feat(rows, feats->c);
                             if (!ex.oom && rows)
                                 EX_CALL(ccn_gather_rows_i32(feats->f, feats->ld, row2pt, rows, feats->c, g->f, g->ld, st));

@@ -91,6 +91,11 @@ int ccn_subset_sample_ptr(const int64_t* batch, const int64_t* idx, const int32_
  *            (ksize, cin, cout) = mirrored weight (fast_conv1d.py:173-184) with BatchNorm(eval) folded.
  *            in_mapped: input rows are points addressed through row2pt (pad rows read zeros);
  *            out_mapped: only rows with row2pt >= 0 are written, to out[row2pt[r]]. */
+/* feat_planes: feat_prep + the gather to the padded signal rows (row2pt of row_map) + ccn_pack_planes in one pass: the
+ *            split-bf16 planes (rows, kpad) the first tensor-core conv layer reads; bit-identical to the three calls. */
+int ccn_curve_feat_planes(const float* x, int64_t ldx, int32_t cx, const float* pos, int32_t with_xyz, int32_t with_diff,
+                          const int32_t* curve_ord, int64_t n, const int32_t* row2pt, int64_t rows, void* planes,
+                          int64_t kpad, int64_t plane_stride, int32_t n_planes, ccn_stream_t stream);
 int ccn_curve_feat_prep(const float* x, int64_t ldx, int32_t cx, const float* pos, int32_t with_xyz,
                         int32_t with_diff, const int32_t* curve_ord, int64_t n, float* out, int64_t ldo,
                         ccn_stream_t stream);

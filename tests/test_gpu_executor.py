@@ -157,3 +157,28 @@ def test_dependent_launch_setting_does_not_change_the_logits(native):
                 assert torch.equal(y, outs[on]) and torch.equal(y, outs[1])
     finally:
         nat.set_dependent_launch(prev)
+
+
+@pytest.mark.parametrize("npl", [2, 1])
+@pytest.mark.parametrize("cx,with_xyz,with_diff,pad", [(128, True, True, 6), (1, True, True, 2), (0, True, False, 0), (21, False, True, 4)])
+def test_curve_feat_planes_equals_prep_gather_pack(cx, with_xyz, with_diff, pad, npl):
+    """ccn_curve_feat_planes (the native executor's one-pass signal planes of a curve-conv step) against the three calls it
+    replaces - ccn_curve_feat_prep -> ccn_gather_rows_i32 (padded rows) -> ccn_pack_planes: bit-identical planes."""
+    from curvecloudnet_b200 import ops
+    from curvecloudnet_b200.native import call
+    from curvecloudnet_b200.synthetic import driving_scan_batch
+    data = driving_scan_batch([5, 6], subsample=4000).to("cuda")
+    topo = ops.curve_csr(data.batch, data.curve_idxs)
+    n = data.pos.shape[0]
+    gen = torch.Generator().manual_seed(cx)
+    x = torch.randn(n, cx, generator=gen).cuda() if cx else None
+    feats = ops.curve_feat_prep(x, data.pos, with_xyz, with_diff, topo.curve_ord)
+    row2pt = ops.curve_row_map(topo, pad)
+    want = ops.pack_planes([ops.gather_rows_i32(feats, row2pt)], npl)
+    rows = row2pt.shape[0]
+    got = ops.alloc_planes(rows, feats.shape[1], npl, data.pos)
+    got.buf.fill_(7.0)
+    call("ccn_curve_feat_planes", x if x is not None else 0, x.stride(0) if x is not None else 0, cx, data.pos.contiguous(), int(with_xyz),
+         int(with_diff), topo.curve_ord, n, row2pt, rows, got.buf, got.kpad, got.plane_stride, npl)
+    assert rows > n or pad == 0
+    assert torch.equal(got.buf[:, :rows], want.buf[:, :rows])
