@@ -345,6 +345,38 @@ extern "C" int ccn_radius_1d_group_count(const float* pos, const int32_t* curve_
     return CCN_OK;
 }
 
+// The two halves of ccn_radius_1d_group_count for callers that overlap them: the per-curve statistics depend on the level's
+// positions and curve layout only (not on the sampled queries), so the native executor computes them on its geometry stream
+// while the main stream is still busy with the step before.
+extern "C" int ccn_radius_1d_curve_stats(const float* pos, const int32_t* curve_ord, const int32_t* curve_ptr, int32_t n_curves,
+                                         float radius, float* kc_scratch, int32_t* stats_scratch, ccn_stream_t stream) {
+    CCN_REQUIRE(n_curves >= 0 && kc_scratch && stats_scratch);
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(stats_scratch, 0, 2 * sizeof(int32_t), s);
+    if (e != cudaSuccess) return (int)e;
+    if (n_curves > 0) {
+        ccn_launch(radius_1d_curve_stats_kernel, dim3(ccn_blocks_exact((int64_t)n_curves * 32, 256)), dim3(256), 0, s, pos, curve_ord,
+                   curve_ptr, n_curves, radius, kc_scratch, stats_scratch);
+        CCN_CHECK_LAUNCH();
+    }
+    return CCN_OK;
+}
+
+extern "C" int ccn_radius_1d_group_count_ready(const int32_t* curve_ord, const int64_t* curve_local, int64_t n, int32_t n_curves,
+                                               const int64_t* idxs, int64_t nq, const float* kc_ready, const int32_t* stats_ready,
+                                               int32_t* row_ptr, int32_t* total_out, ccn_stream_t stream) {
+    CCN_REQUIRE(n >= 0 && nq >= 0 && n_curves >= 0 && kc_ready && stats_ready && row_ptr && total_out);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (nq > 0) {
+        ccn_launch(radius_1d_group_kernel<false>, dim3(ccn_blocks_exact(nq, 128)), dim3(128), 0, s, idxs, nq, curve_ord, curve_local, n,
+                   n_curves, kc_ready, stats_ready, row_ptr, nullptr);
+        CCN_CHECK_LAUNCH();
+    }
+    ccn_launch(excl_scan_i32_kernel, dim3(1), dim3(1024), 0, s, row_ptr, nq, total_out);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
 extern "C" int ccn_radius_1d_group_fill(const int32_t* curve_ord, const int64_t* curve_local, int64_t n,
                                         int32_t n_curves, const int64_t* idxs, int64_t nq, const float* kc_scratch,
                                         const int32_t* stats_scratch, const int32_t* row_ptr, int32_t* col,

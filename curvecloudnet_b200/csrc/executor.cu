@@ -94,6 +94,8 @@ struct Level {                 // one point set of the pyramid
     int32_t *curve_ord = nullptr, *curve_ptr = nullptr;
     std::vector<Grid> grids;
     std::vector<KnnMemo> knn;
+    // per-curve statistics of radius_1d_group (ccn_radius_1d_curve_stats), computed ahead on the geometry stream
+    float* kc = nullptr; int32_t* kstats = nullptr; float kc_radius = 0.f; cudaEvent_t kc_ready = nullptr;
 };
 
 struct Exec {
@@ -150,6 +152,8 @@ struct Exec {
     bool on_main() const { return stream != side && stream != geo; }
     ccn_draw_fn draw = nullptr;
     void* draw_user = nullptr;
+    bool early_u_valid = false;         // the CurveFPS phase, when it is the forward's first draw, is taken at entry
+    float early_u = 0.f;
     int topo_flags = 0;
     // host-side accounting of the last forward: wall time of ccn_forward_run, time blocked in stream / event synchronisation
     double host_total_ms = 0, host_blocked_ms = 0;
@@ -975,6 +979,19 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
     for (Exec::UpMemo& u : ex.up) u.valid = false;
     ex.geo_used = 0;
     ccn_stream_t st = (ccn_stream_t)ex.stream;
+    // the first draw of the forward: when it is the CurveFPS phase (sa-geo before any other sampling step) it is taken NOW - the
+    // callback into python (~20 us) otherwise sits between the curve conv and the sampler with the device idle
+    ex.early_u_valid = false;
+    for (const Step& s0 : ex.steps) {
+        if (s0.kind == ST_SA) break;
+        if (s0.kind == ST_SA_GEO) {
+            if (s0.iv[1] && ex.use_side && !ex.prof) {
+                ex.draw(ex.draw_user, DRAW_CURVE_PHASE, 1, &ex.early_u);
+                ex.early_u_valid = true;
+            }
+            break;
+        }
+    }
 
     ex.levels.emplace_back();
     Level* lv0 = &ex.levels.back();
@@ -1010,6 +1027,25 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 const int with_xyz = (int)iv[0], with_diff = (int)iv[1], ksize = (int)iv[2], nl = (int)iv[3], tc_from = (int)iv[4];
                 Level* lv = cur.lv;
                 EX_CALL(level_topo(ex, lv));
+                if (si + 1 < ex.steps.size() && ex.steps[si + 1].kind == ST_SA_GEO && ex.use_side && !ex.prof && ex.geo && !ex.oom &&
+                    lv->n_curves > 0 && !lv->kc) {
+                    // the next step groups along the curves of THIS level: its per-curve statistics (a strictly ordered f32 sum per
+                    // curve, 28 us at 32 k points) run on the geometry stream behind the topology, beside this step's kernels
+                    lv->kc = ex.alloc_n<float>(lv->n_curves);
+                    lv->kstats = ex.alloc_n<int32_t>(2);
+                    lv->kc_radius = (float)ex.steps[si + 1].fv[2];
+                    if (!ex.oom) {
+                        cudaEvent_t topo_done = ex.geo_event();
+                        EX_CUDA(cudaEventRecord(topo_done, ex.stream));
+                        EX_CUDA(cudaStreamWaitEvent(ex.geo, topo_done, 0));
+                        EX_CALL(ccn_radius_1d_curve_stats(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->n_curves, lv->kc_radius, lv->kc,
+                                                          lv->kstats, (ccn_stream_t)ex.geo));
+                        lv->kc_ready = ex.geo_event();
+                        EX_CUDA(cudaEventRecord(lv->kc_ready, ex.geo));
+                    } else {
+                        lv->kc = nullptr;
+                    }
+                }
                 const int64_t np = lv->n;
                 const int cx = cur.x ? cur.x->c : 0;
                 const int c_in = cx + (with_xyz ? 3 : 0);
@@ -1202,8 +1238,9 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     EX_CUDA(cudaStreamWaitEvent(ex.stream, ex.pre[si].ready, 0));
                 } else if (curve_fps) {
                     // ops.curve_fps
-                    float u = 0.f;
-                    ex.draw(ex.draw_user, DRAW_CURVE_PHASE, 1, &u);
+                    float u = ex.early_u;
+                    if (!ex.early_u_valid) ex.draw(ex.draw_user, DRAW_CURVE_PHASE, 1, &u);
+                    ex.early_u_valid = false;
                     float* run = ex.alloc_n<float>((lv->n > 0 ? lv->n : 1) + (lv->n + 4095) / 4096);
                     idx = ex.alloc_n<int64_t>(lv->n);
                     int32_t* cnt = ex.alloc_n<int32_t>(1);
@@ -1235,11 +1272,20 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 if (s.kind == ST_SA_GEO) {
                     // ops.radius_1d_group
                     const int64_t nq = ch->n;
-                    float* kc = ex.alloc_n<float>(lv->n_curves);
+                    const bool stats_ahead = lv->kc && lv->kc_radius == radius;
+                    float* kc = stats_ahead ? lv->kc : ex.alloc_n<float>(lv->n_curves);
                     int32_t* buf = ex.alloc_n<int32_t>(nq + 4);
+                    int32_t* kstats = stats_ahead ? lv->kstats : buf + nq + 2;
                     int64_t E = 0;
                     int max_deg = 1;
                     if (!ex.oom) {
+                        if (stats_ahead) {
+                            if (lv->kc_ready) { EX_CUDA(cudaStreamWaitEvent(ex.stream, lv->kc_ready, 0)); lv->kc_ready = nullptr; }
+                            EX_CALL(ccn_radius_1d_group_count_ready(lv->curve_ord, lv->curve, lv->n, lv->n_curves, idx, nq, kc, kstats, buf,
+                                                                    buf + nq + 1, st));
+                            // the read-back below takes {E, max k_c, max #points}: the statistics follow E in buf
+                            EX_CUDA(cudaMemcpyAsync(buf + nq + 2, kstats, 8, cudaMemcpyDeviceToDevice, ex.stream));
+                        } else
                         EX_CALL(ccn_radius_1d_group_count(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->curve, lv->n, lv->n_curves, idx, nq,
                                                           radius, kc, buf + nq + 2, buf, buf + nq + 1, st));
                         EX_CALL(ex.readback_begin(buf + nq + 1, 3));
@@ -1257,7 +1303,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     int32_t* col = ex.alloc_n<int32_t>(E);
                     int32_t* erow = ex.alloc_n<int32_t>(E);
                     if (!ex.oom) {
-                        EX_CALL(ccn_radius_1d_group_fill(lv->curve_ord, lv->curve, lv->n, lv->n_curves, idx, nq, kc, buf + nq + 2, buf, col, st));
+                        EX_CALL(ccn_radius_1d_group_fill(lv->curve_ord, lv->curve, lv->n, lv->n_curves, idx, nq, kc, kstats, buf, col, st));
                         EX_CALL(ccn_csr_rows(buf, nq, erow, st));
                     }
                     e = Edges{buf, erow, col, E, nq, max_deg};

@@ -115,6 +115,14 @@ int ccn_curve_conv_layer(const float* in, int64_t ld_in, const float* w, const f
  *            344-355): nbr (n,knn) sampled ORDINALS (-1 padded) by (distance, candidate order), wgt = 1/clamp(d^2,1e-16). */
 int ccn_curve_fps(const float* pos, const int32_t* curve_ord, const int32_t* curve_ptr, int64_t n, const float* u,
                   float arclen, float* run_scratch, int64_t* idx_out, int32_t* count_out, ccn_stream_t stream);
+/* radius_1d_curve_stats + radius_1d_group_count_ready = ccn_radius_1d_group_count in two calls: the per-curve statistics
+ *            (point_ops.py:149-167; kc, stats) need the level only, not the queries - a caller can compute them early, on
+ *            another stream - and count_ready then does the per-query part with them. */
+int ccn_radius_1d_curve_stats(const float* pos, const int32_t* curve_ord, const int32_t* curve_ptr, int32_t n_curves,
+                              float radius, float* kc_scratch, int32_t* stats_scratch, ccn_stream_t stream);
+int ccn_radius_1d_group_count_ready(const int32_t* curve_ord, const int64_t* curve_local, int64_t n, int32_t n_curves,
+                                    const int64_t* idxs, int64_t nq, const float* kc_ready, const int32_t* stats_ready,
+                                    int32_t* row_ptr, int32_t* total_out, ccn_stream_t stream);
 int ccn_radius_1d_group_count(const float* pos, const int32_t* curve_ord, const int32_t* curve_ptr,
                               const int64_t* curve_local, int64_t n, int32_t n_curves, const int64_t* idxs, int64_t nq,
                               float radius, float* kc_scratch, int32_t* stats_scratch, int32_t* row_ptr,
