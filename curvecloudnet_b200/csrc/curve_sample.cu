@@ -214,28 +214,62 @@ __global__ void radius_1d_group_kernel(const int64_t* __restrict__ idxs, int64_t
 }
 
 // Exclusive scan of an int32 array in place (single CTA, running carry); total -> *total_out,
-// also written to a[n] (CSR terminator).
+// also written to a[n] (CSR terminator).  16 items per thread and round (the rounds are a load -> block scan -> store latency
+// chain: 17 k row counts are 2 rounds instead of 5, the 262 k cell counts of a level-1 grid 16 instead of 64); the next
+// round's items are loaded before this round's scan.
+constexpr int kScanItems = 16;
 __global__ void __launch_bounds__(1024) excl_scan_i32_kernel(int32_t* __restrict__ a, int64_t n,
                                                              int32_t* __restrict__ total_out) {
     ccn_pdl_wait();
     __shared__ int sm[33];
     int carry = 0;
-    for (int64_t base = 0; base < n; base += 1024 * kItems) {
-        const int64_t i0 = base + (int64_t)threadIdx.x * kItems;
-        int v[kItems], local = 0;
+    const bool vec = (reinterpret_cast<uintptr_t>(a) & 15) == 0;
+    int v[kScanItems], nx[kScanItems];
+    auto load = [&](int64_t base, int (&dst)[kScanItems]) {
+        const int64_t i0 = base + (int64_t)threadIdx.x * kScanItems;
+        if (vec && i0 + kScanItems <= n) {
 #pragma unroll
-        for (int k = 0; k < kItems; ++k) {
-            v[k] = (i0 + k < n) ? a[i0 + k] : 0;
-            local += v[k];
+            for (int k = 0; k < kScanItems; k += 4) {
+                const int4 q = *reinterpret_cast<const int4*>(a + i0 + k);
+                dst[k] = q.x; dst[k + 1] = q.y; dst[k + 2] = q.z; dst[k + 3] = q.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kScanItems; ++k) dst[k] = (i0 + k < n) ? a[i0 + k] : 0;
         }
+    };
+    if (n > 0) load(0, v);
+    for (int64_t base = 0; base < n; base += 1024 * kScanItems) {
+        const int64_t i0 = base + (int64_t)threadIdx.x * kScanItems;
+        const bool more = base + 1024 * kScanItems < n;
+        if (more) load(base + 1024 * kScanItems, nx);          // rows of the next round: not written by this one
+        int local = 0;
+#pragma unroll
+        for (int k = 0; k < kScanItems; ++k) local += v[k];
         int total;
         int run = carry + ccn_block_excl_scan<int>(local, sm, &total);
+        if (vec && i0 + kScanItems <= n) {
 #pragma unroll
-        for (int k = 0; k < kItems; ++k) {
-            if (i0 + k < n) a[i0 + k] = run;
-            run += v[k];
+            for (int k = 0; k < kScanItems; k += 4) {
+                int4 q;
+                q.x = run; run += v[k];
+                q.y = run; run += v[k + 1];
+                q.z = run; run += v[k + 2];
+                q.w = run; run += v[k + 3];
+                *reinterpret_cast<int4*>(a + i0 + k) = q;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kScanItems; ++k) {
+                if (i0 + k < n) a[i0 + k] = run;
+                run += v[k];
+            }
         }
         carry += total;
+        if (more) {
+#pragma unroll
+            for (int k = 0; k < kScanItems; ++k) v[k] = nx[k];
+        }
     }
     if (threadIdx.x == 0) {
         a[n] = carry;

@@ -1032,7 +1032,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                     // the next step groups along the curves of THIS level: its per-curve statistics (a strictly ordered f32 sum per
                     // curve, 28 us at 32 k points) run on the geometry stream behind the topology, beside this step's kernels
                     lv->kc = ex.alloc_n<float>(lv->n_curves);
-                    lv->kstats = ex.alloc_n<int32_t>(2);
+                    lv->kstats = ex.alloc_n<int32_t>(4) + 1;          // [E | max k_c, max #points]: one read-back takes all three
                     lv->kc_radius = (float)ex.steps[si + 1].fv[2];
                     if (!ex.oom) {
                         cudaEvent_t topo_done = ex.geo_event();
@@ -1282,13 +1282,11 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                         if (stats_ahead) {
                             if (lv->kc_ready) { EX_CUDA(cudaStreamWaitEvent(ex.stream, lv->kc_ready, 0)); lv->kc_ready = nullptr; }
                             EX_CALL(ccn_radius_1d_group_count_ready(lv->curve_ord, lv->curve, lv->n, lv->n_curves, idx, nq, kc, kstats, buf,
-                                                                    buf + nq + 1, st));
-                            // the read-back below takes {E, max k_c, max #points}: the statistics follow E in buf
-                            EX_CUDA(cudaMemcpyAsync(buf + nq + 2, kstats, 8, cudaMemcpyDeviceToDevice, ex.stream));
+                                                                    kstats - 1, st));
                         } else
                         EX_CALL(ccn_radius_1d_group_count(lv->pos.f, lv->curve_ord, lv->curve_ptr, lv->curve, lv->n, lv->n_curves, idx, nq,
                                                           radius, kc, buf + nq + 2, buf, buf + nq + 1, st));
-                        EX_CALL(ex.readback_begin(buf + nq + 1, 3));
+                        EX_CALL(ex.readback_begin(stats_ahead ? kstats - 1 : buf + nq + 1, 3));
                         EX_CALL(pointconv_pre(ex, pc_iv, xparts, nxp, &H));    // queued behind the copy: runs while the host waits
                         if (ex.oom) return CCN_ENOMEM;
                         const int32_t* vals = nullptr;
