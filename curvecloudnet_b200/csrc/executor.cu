@@ -139,11 +139,6 @@ struct Exec {
     std::vector<int> fp_partner;        // per down step: the fp / fp-geo step that pops it (-1: none)
     struct UpMemo { bool valid = false; int32_t* nbr = nullptr; float* wgt = nullptr; cudaEvent_t ready = nullptr; };
     std::vector<UpMemo> up;             // per fp step: its interpolation table, if computed ahead
-    // large exact 3-NN tables (>= kDeferPairs query-source pairs) are needed in the decoder only: launched beside the encoder
-    // step that creates their level they take every SM for ~100 us and triple the time of that step's own FRNN query (30 -> 94
-    // us); they are queued instead when the main stream has reached a level 16x smaller, whose kernels leave most SMs idle
-    struct Deferred { int j; Level* lv; Level* ch; };
-    std::vector<Deferred> deferred;
     std::vector<cudaEvent_t> geo_events;
     size_t geo_used = 0;
     cudaEvent_t geo_event() {
@@ -777,42 +772,6 @@ int collect_voxel_early(Exec& ex) {
     return CCN_OK;
 }
 
-constexpr double kDeferPairs = 2e7;
-
-// The deferred interpolation tables whose turn has come (`all`: every one - the decoder starts): queued on the geometry stream
-// behind what the main stream has queued so far.
-int flush_deferred(Exec& ex, int64_t cur_n, bool all) {
-    if (ex.deferred.empty() || ex.oom) return CCN_OK;
-    cudaEvent_t start = nullptr;
-    cudaStream_t saved = ex.stream;
-    int rc = CCN_OK;
-    for (size_t d = 0; d < ex.deferred.size() && rc == CCN_OK && !ex.oom;) {
-        const Exec::Deferred job = ex.deferred[d];
-        if (!all && cur_n * 16 > job.lv->n) { ++d; continue; }
-        if (!start) {
-            start = ex.geo_event();
-            EX_CUDA(cudaEventRecord(start, saved));
-            EX_CUDA(cudaStreamWaitEvent(ex.geo, start, 0));
-        }
-        const int knn = (int)ex.steps[job.j].iv[0];
-        int32_t* nbr = ex.alloc_n<int32_t>(job.lv->n * knn);
-        float* wgt = ex.alloc_n<float>(job.lv->n * knn);
-        if (!ex.oom) {
-            ex.stream = ex.geo;
-            rc = knn_exact(ex, job.lv, job.ch, knn, nbr, wgt);
-            ex.stream = saved;
-            if (rc == CCN_OK) {
-                Exec::UpMemo& u = ex.up[job.j];
-                u.valid = true; u.nbr = nbr; u.wgt = wgt; u.ready = ex.geo_event();
-                if (cudaEventRecord(u.ready, ex.geo) != cudaSuccess) rc = CCN_EINVAL;
-            }
-        }
-        ex.deferred.erase(ex.deferred.begin() + d);
-    }
-    ex.stream = saved;
-    return rc;
-}
-
 // Step `si` has created level `ch` from `lv` (sampled indices `idx`): queue, on the geometry stream, (1) the interpolation
 // table of the fp / fp-geo step that will pop this down step and (2) the kNN tables of the sgcnn steps that run on `ch` before
 // the next level change.  The main stream joins through events at first use.
@@ -829,9 +788,7 @@ int geometry_ahead(Exec& ex, int si, Level* lv, Level* ch, const int64_t* idx, c
     int rc = CCN_OK;
     bool any = false;
     const int j = ex.fp_partner[si];
-    if (j >= 0 && ch->has_sptr && ex.steps[j].kind == ST_FP && (double)lv->n * (double)ch->n >= kDeferPairs) {
-        ex.deferred.push_back(Exec::Deferred{j, lv, ch});
-    } else if (j >= 0 && ch->has_sptr) {
+    if (j >= 0 && ch->has_sptr) {
         const Step& fp = ex.steps[j];
         const int knn = (int)fp.iv[0];
         int32_t* nbr = ex.alloc_n<int32_t>(lv->n * knn);
@@ -1020,7 +977,6 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
     ex.prof_used = 0;
     for (Exec::Pre& pr : ex.pre) { pr.done = false; pr.ch = nullptr; pr.idx = nullptr; pr.parent = nullptr; pr.collected = false; }
     for (Exec::UpMemo& u : ex.up) u.valid = false;
-    ex.deferred.clear();
     ex.geo_used = 0;
     ccn_stream_t st = (ccn_stream_t)ex.stream;
     // the first draw of the forward: when it is the CurveFPS phase (sa-geo before any other sampling step) it is taken NOW - the
@@ -1064,7 +1020,6 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
         State outp = cur;
         int64_t* didx = nullptr;
         EX_CALL(collect_voxel_early(ex));
-        EX_CALL(flush_deferred(ex, cur.lv->n, s.kind == ST_FP || s.kind == ST_FP_GEO));
         if (ex.oom) return CCN_ENOMEM;
         switch (s.kind) {
             case ST_CONV_V2: {
