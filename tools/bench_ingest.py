@@ -4,8 +4,8 @@
 
 Prints one JSON line: sweeps/s and points/s of `ingest_scan` from host bytes (pinned staging + H2D + ccn_ingest_scan,
 training augmentation on), the device-only time of the C-ABI call (CUDA events), its algorithmic HBM bytes, and the CPU
-restatement of the reference's `get()` body (oracle/ccn_ingest.py) timed on this host for the same sweep.
-Development tool: it imports oracle/ for the CPU arm (allowed for tools that are not the product path).
+restatement of the reference's `get()` body timed on this host for the same sweep when --cpu-arm is given (that arm
+imports oracle/ccn_ingest.py: the oracle as a timed CPU baseline, like bench.py's cpu_baseline leg; off by default).
 """
 import argparse
 import json
@@ -24,11 +24,11 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--dataset", default="nuscenes")
     ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--cpu-arm", action="store_true", help="also time the CPU restatement (imports oracle/)")
     args = ap.parse_args()
     from curvecloudnet_b200 import native
     from curvecloudnet_b200.ingest import LearningMap, ScanAugmentation, ingest_scan
     from curvecloudnet_b200.synthetic import raycast_driving_scan
-    from oracle import ccn_ingest as oi
 
     nusc = args.dataset == "nuscenes"
     raws = []
@@ -68,11 +68,14 @@ def main():
     alg = n_mean * (rec_b + (1 if nusc else 4) + 12 + 4 + 8 + 8 + 8 + 8)
 
     rec, lab = raws[0]
-    t1 = time.perf_counter()
-    reps = 3
-    for _ in range(reps):
-        oi.ingest_scan(rec, lab, mapping, args.dataset, oi.draw_augmentation(args.dataset, rng))
-    cpu_sec = (time.perf_counter() - t1) / reps
+    cpu_sec = None
+    if args.cpu_arm:
+        from oracle import ccn_ingest as oi
+        t1 = time.perf_counter()
+        reps = 3
+        for _ in range(reps):
+            oi.ingest_scan(rec, lab, mapping, args.dataset, oi.draw_augmentation(args.dataset, rng))
+        cpu_sec = (time.perf_counter() - t1) / reps
     try:
         peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
@@ -81,8 +84,9 @@ def main():
         "metric": "sweeps/s ingest (raw host bytes -> Data in HBM, training augmentation)", "dataset": args.dataset,
         "value": args.steps / sec, "points_per_s": pts / sec, "points_per_sweep": n_mean, "ms_per_sweep": sec / args.steps * 1e3,
         "device_us_per_call": dev_us, "algorithmic_bytes_per_call": alg, "device_gbs": alg / dev_us / 1e3,
-        "hbm_peak_gbs": peak, "cpu_port_ms_per_sweep": cpu_sec * 1e3, "cpu_port_points_per_s": rec.shape[0] / cpu_sec,
-        "speedup_vs_cpu_port": cpu_sec / (sec / args.steps)}))
+        "hbm_peak_gbs": peak, "cpu_port_ms_per_sweep": cpu_sec * 1e3 if cpu_sec else None,
+        "cpu_port_points_per_s": rec.shape[0] / cpu_sec if cpu_sec else None,
+        "speedup_vs_cpu_port": cpu_sec / (sec / args.steps) if cpu_sec else None}))
 
 
 if __name__ == "__main__":
