@@ -47,7 +47,8 @@ def main():
              ("random", ["sphere", "torus"], 96, 2500, 0.25, 12, False),                      # many attempts: N close to the visible pixels
              ("random", ["table", "blob"], 384, 64, 0.5, 13, True),                 # the cut inside the first attempt, half density
              ("parallel", ["blob", "torus"], 400, 500, 1.0, 14, True),
-             ("grid", ["torus", "blob"], 512, 700, 1.0, 15, True)]
+             ("grid", ["torus", "blob"], 512, 700, 1.0, 15, True),
+             ("random", ["blob", "torus"], 640, 1500, 1.0, 16, True)]    # more points than one 1024-thread round of the scans
     for direction, kinds, res, N, density, seed, clouds in specs:
         coords, normals, masks = views(kinds, res, 0.4 * seed)
         B = len(kinds)
