@@ -81,12 +81,14 @@ class _Linear(Function):
         wd = w.detach().contiguous()
         bd = None if b is None else b.detach()
         ctx.xp = None
+        ctx.had_xp = False
         if mode == "fp32" or x.shape[0] == 0:
             ctx.save_for_backward(x, w)
             return ops.linear(x, wd, bd, ops.ACT_NONE)
         xp = _planes_of(x, _npl(mode)) or ops.pack_planes([x], _npl(mode))
         if _tc_wgrad_ok(wd.shape[0], wd.shape[1]):
             ctx.xp = xp
+            ctx.had_xp = True
             ctx.save_for_backward(None, w)
         else:
             ctx.save_for_backward(x, w)
@@ -108,9 +110,12 @@ class _Linear(Function):
             # dX = dY W straight from the forward weight's planes (MN-major B tiles): no transpose, no second split
             dx = ops.linear_planes_bt(dyp, ops.tc_weight_param(w))
         if need_w:
+            if ctx.had_xp and ctx.xp is None:
+                raise RuntimeError("second backward through a tensor-core Linear: its input planes were released after the first "
+                                   "(retain_graph=True is not supported on this path)")
             if ctx.xp is not None:
                 dW = wgrad_planes(dyp, ctx.xp)
-                db = (getattr(dy, "_ccn_colsum", None) if ctx.has_bias else None)
+                db = _colsum_of(dy) if ctx.has_bias else None
                 if ctx.has_bias and db is None:
                     db = col_sum(dy)
             else:
@@ -133,9 +138,24 @@ def _npl(mode: str) -> int:
 def _planes_of(t: torch.Tensor, npl: int):
     """Activation planes a producer kernel attached to `t` (same values, same shape), else None."""
     pl = getattr(t, "_ccn_planes", None)
-    if pl is not None and pl.n_planes == npl and pl.shape == tuple(t.shape):
+    if pl is not None and pl.n_planes == npl and pl.shape == tuple(t.shape) and _tag_ok(t):
         return pl
     return None
+
+
+def _tag(t: torch.Tensor):
+    """Stamp of the tensor contents the attached planes / column sums were computed from: an in-place accumulation into the
+    same TensorImpl (a second gradient contribution) bumps the version and invalidates them."""
+    t._ccn_tag = (t._version, t.data_ptr())
+
+
+def _tag_ok(t: torch.Tensor) -> bool:
+    return getattr(t, "_ccn_tag", None) == (t._version, t.data_ptr())
+
+
+def _colsum_of(t: torch.Tensor):
+    cs = getattr(t, "_ccn_colsum", None)
+    return cs if cs is not None and _tag_ok(t) else None
 
 
 class _BNAct(Function):
@@ -182,6 +202,7 @@ class _BNAct(Function):
         ctx.cfg = (act, float(slope), bool(batch_stats))
         if yp is not None:
             y._ccn_planes = yp
+            _tag(y)
         return y
 
     @staticmethod
@@ -205,6 +226,7 @@ class _BNAct(Function):
             dz._ccn_colsum = dzsum
         if dzp is not None:
             dz._ccn_planes = dzp
+        _tag(dz)
         if gamma is None:
             return dz, None, None, None, None, None, None, None
         return dz, dgamma, dbeta, None, None, None, None, None
