@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 
 #include <chrono>
+#include <cstdlib>
 #include <cmath>
 #include <cstring>
 #include <deque>
@@ -132,6 +133,10 @@ struct Exec {
     std::vector<Pre> pre;
     cudaEvent_t lvl_ready = nullptr;
     bool use_side = true;
+    // CCN_EXEC_LOOKAHEAD (read at ccn_exec_create; tests run both settings against the python executor): 0 = everything on the
+    // caller's stream in step order (no side / geometry streams), 1 = look-ahead streams but no early collection of voxel
+    // pre-samples, early first draw or curve statistics ahead, 2 (default) = all of it
+    bool early = true;
     // neighbour searches depend on positions only: as soon as a level exists, the kNN tables of the sgcnn steps that will run
     // on it and the interpolation table of the fp / fp-geo step that will return to its parent are computed on a second side
     // stream (`geo`), concurrently with the feature kernels of the main stream
@@ -747,7 +752,7 @@ int presample_ahead(Exec& ex, int si, Level* lv, cudaEvent_t ready = nullptr) {
 // chains: 0.5 us per selected point, 300 us for level 4) start that much earlier.  Same draws in the same order: no step
 // between the two points draws.
 int collect_voxel_early(Exec& ex) {
-    if (!ex.use_side || ex.prof || !ex.side || ex.oom) return CCN_OK;
+    if (!ex.use_side || !ex.early || ex.prof || !ex.side || ex.oom) return CCN_OK;
     for (size_t k = 0; k < ex.pre.size(); ++k) {
         Exec::Pre& pr = ex.pre[k];
         if (!pr.done || !pr.voxel || pr.collected) continue;
@@ -911,6 +916,12 @@ extern "C" int ccn_exec_create(const int64_t* iplan, int64_t n_i, const double* 
         delete h;
         return CCN_EINVAL;
     }
+    {
+        const char* env = std::getenv("CCN_EXEC_LOOKAHEAD");
+        const int level = env ? std::atoi(env) : 2;
+        ex.use_side = level >= 1;
+        ex.early = level >= 2;
+    }
     if (cudaStreamCreateWithFlags(&ex.side, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ex.lvl_ready, cudaEventDisableTiming) != cudaSuccess) {
         ex.side = nullptr;                       // no side stream: everything stays on the caller's stream
@@ -985,7 +996,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
     for (const Step& s0 : ex.steps) {
         if (s0.kind == ST_SA) break;
         if (s0.kind == ST_SA_GEO) {
-            if (s0.iv[1] && ex.use_side && !ex.prof) {
+            if (s0.iv[1] && ex.use_side && ex.early && !ex.prof) {
                 ex.draw(ex.draw_user, DRAW_CURVE_PHASE, 1, &ex.early_u);
                 ex.early_u_valid = true;
             }
@@ -1027,7 +1038,7 @@ int run_forward(Exec& ex, const float* x, int64_t ldx, const float* pos, const i
                 const int with_xyz = (int)iv[0], with_diff = (int)iv[1], ksize = (int)iv[2], nl = (int)iv[3], tc_from = (int)iv[4];
                 Level* lv = cur.lv;
                 EX_CALL(level_topo(ex, lv));
-                if (si + 1 < ex.steps.size() && ex.steps[si + 1].kind == ST_SA_GEO && ex.use_side && !ex.prof && ex.geo && !ex.oom &&
+                if (si + 1 < ex.steps.size() && ex.steps[si + 1].kind == ST_SA_GEO && ex.use_side && ex.early && !ex.prof && ex.geo && !ex.oom &&
                     lv->n_curves > 0 && !lv->kc) {
                     // the next step groups along the curves of THIS level: its per-curve statistics (a strictly ordered f32 sum per
                     // curve, 28 us at 32 k points) run on the geometry stream behind the topology, beside this step's kernels

@@ -182,3 +182,26 @@ def test_curve_feat_planes_equals_prep_gather_pack(cx, with_xyz, with_diff, pad,
          int(with_diff), topo.curve_ord, n, row2pt, rows, got.buf, got.kpad, got.plane_stride, npl)
     assert rows > n or pad == 0
     assert torch.equal(got.buf[:, :rows], want.buf[:, :rows])
+
+
+@pytest.mark.parametrize("name,seeds", [("nuscenes", [0]), ("kitti", [2, 3])])
+def test_lookahead_levels_do_not_change_the_logits(name, seeds, monkeypatch):
+    """CCN_EXEC_LOOKAHEAD = 0 (one stream, step order) / 1 (side + geometry streams) / 2 (default: also voxel pre-samples
+    collected at step boundaries, the first draw taken at entry, curve statistics ahead): the same kernels with the same
+    arguments and the same draws in the same order, whatever runs beside what - bit-identical logits, three forwards each
+    (whether a voxel read-back has landed at a step boundary is a matter of timing: both branches occur)."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    data = driving_scan_batch(seeds, kind=name).to("cuda")
+    outs = {}
+    for level in ("0", "1", "2"):
+        monkeypatch.setenv("CCN_EXEC_LOOKAHEAD", level)
+        model = randomize_model_(build_model(ModelBase, name, precision="bf16x3"), 1234).cuda().eval()
+        for rep in range(3):
+            with torch.no_grad():
+                torch.manual_seed(21)
+                y = model(data)
+            assert model.__dict__["_native"][1] is not None
+            outs.setdefault(level, y)
+            assert torch.equal(y, outs[level]) and torch.equal(y, outs["0"]), "look-ahead level %s, forward %d" % (level, rep)
