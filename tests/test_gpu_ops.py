@@ -351,3 +351,101 @@ def test_knn_grid_equals_brute_force(K):
             assert torch.equal(g[0][off1:off1 + l1].cpu().long(), ii[0] + off2), trial
             off1 += l1
             off2 += l2
+
+
+def _ragged_segments(nq, max_deg, gen):
+    """CSR rows with empty segments, single-row segments and a long one; returns (row_ptr i32, erow i64)."""
+    deg = torch.randint(0, max_deg + 1, (nq,), generator=gen)
+    deg[0], deg[nq // 2], deg[nq - 1] = 0, 1, 4 * max_deg          # an empty first, a single, a long last segment
+    row_ptr = torch.zeros(nq + 1, dtype=torch.int64)
+    row_ptr[1:] = deg.cumsum(0)
+    erow = torch.repeat_interleave(torch.arange(nq), deg)
+    return row_ptr.int(), erow
+
+
+@pytest.mark.parametrize("c", [7, 20, 64])                          # scalar kernel, float4 kernel, float4 + planes
+@pytest.mark.parametrize("mode", ["max", "mean", "sum", "attend", "weighted-sum", "weighted-sum-norm"])
+def test_seg_aggregate_against_oracle_scatter(mode, c):
+    """ccn_seg_aggregate(_both) against the oracle's torch_scatter / torch_geometric restatements on a ragged edge list
+    (point_conv.py:81-92, dgcnn.py:190-197, 240-244): empty segments give 0, 'attend' is softmax over the target's rows
+    with the 1e-16 of torch_geometric.utils.softmax.  Sums run in row order on both sides; fp32 tolerance 1e-5."""
+    from curvecloudnet_b200 import nn as N
+    from curvecloudnet_b200 import ops
+    from oracle import tp_ops as T
+    gen = torch.Generator().manual_seed(100 + c)
+    nq = 301
+    row_ptr, erow = _ragged_segments(nq, 9, gen)
+    E = erow.shape[0]
+    msg = torch.randn(E, c, generator=gen)
+    att = 3.0 * torch.randn(E, c, generator=gen)
+    if mode == "max":
+        want = T.scatter_max(msg, erow, 0, None, nq)[0]
+    elif mode == "mean":
+        want = T.scatter_mean(msg, erow, 0, None, nq)
+    elif mode == "sum":
+        want = T.scatter_add(msg, erow, 0, None, nq)
+    elif mode == "attend":
+        want = T.scatter_add(msg * T.segment_softmax(att, erow, nq), erow, 0, None, nq)
+    elif mode == "weighted-sum":
+        want = T.scatter_add(msg * torch.sigmoid(att), erow, 0, None, nq)
+    else:
+        w = torch.sigmoid(att)
+        tot = T.scatter_add(w, erow, 0, None, nq).clamp(min=1e-3)
+        want = T.scatter_add(msg * (w / tot[erow]), erow, 0, None, nq)
+    a = att.cuda() if mode in ("attend", "weighted-sum", "weighted-sum-norm") else None
+    got = ops.seg_aggregate(msg.cuda(), a, row_ptr.cuda(), nq, mode)
+    assert torch.equal(got[0].cpu(), torch.zeros(c)), "empty segment"
+    if mode == "max":
+        assert torch.equal(got.cpu(), want)
+    else:
+        assert rel_err(got.cpu(), want) <= 1e-5, mode
+    if c % 16 == 0:
+        cache = N.ForwardCache()
+        both = ops.seg_aggregate(msg.cuda(), a, row_ptr.cuda(), nq, mode, npl=2, cache=cache)
+        assert torch.equal(both, got)
+        pl = cache.planes_for(both, 2)
+        assert torch.equal(pl.buf, ops.pack_planes([got], 2).buf)
+    # a column slice of a wider buffer (leading dimension > c) gives the same rows
+    wide = torch.zeros(E, c + 12)
+    wide[:, 4:4 + c] = msg
+    got_ld = ops.seg_aggregate(wide.cuda()[:, 4:4 + c], a, row_ptr.cuda(), nq, mode)
+    assert torch.equal(got_ld, got)
+
+
+@pytest.mark.parametrize("c", [6, 64])
+def test_group_max_dense_and_interp_blend_against_formula(c):
+    """ccn_group_max_dense: max over the K+1 rows of every point with the rows of missing neighbours (idx < 0) counted as
+    -100 (dgcnn.py:187-189).  ccn_interp_blend: sum w x / sum w with w = 1 / clamp(d2, 1e-16) (point_ops.py:330-341) or
+    the given weights, missing neighbours skipped.  Both against plain fp32 torch on the CPU."""
+    from curvecloudnet_b200 import ops
+    gen = torch.Generator().manual_seed(7 + c)
+    n, K = 517, 9
+    idx = torch.randint(0, n, (n, K), generator=gen).int()
+    idx[torch.rand(n, K, generator=gen) < 0.3] = -1
+    idx[5] = -1
+    feat = 40.0 * torch.randn(n * (K + 1), c, generator=gen) - 90.0       # many rows below -100: the mask value matters
+    f3 = feat.view(n, K + 1, c).clone()
+    f3[:, 1:][idx < 0] = -100.0
+    want = f3.max(dim=1)[0]
+    got = ops.group_max_dense(feat.cuda(), idx.cuda())
+    assert torch.equal(got.cpu(), want)
+
+    ns, knn = 133, 3
+    x = torch.randn(ns, c, generator=gen)
+    nbr = torch.randint(0, ns, (n, knn), generator=gen).int()
+    nbr[torch.rand(n, knn, generator=gen) < 0.2] = -1
+    nbr[:, 0].clamp_(min=0)                                               # at least one neighbour per row
+    d2 = torch.rand(n, knn, generator=gen) ** 4
+    d2[3, 0] = 0.0                                                        # coincident point: the 1e-16 clamp
+    valid = (nbr >= 0).float()
+    for from_d2, given in ((True, d2), (False, d2 + 0.1)):
+        w = (1.0 / given.clamp(min=1e-16) if from_d2 else given) * valid
+        xs = x[nbr.clamp(min=0).long()]                                   # (n, knn, c)
+        num = torch.zeros(n, c)
+        den = torch.zeros(n)
+        for s in range(knn):                                              # the kernel's order of additions
+            num = num + xs[:, s] * w[:, s:s + 1]
+            den = den + w[:, s]
+        want = num / den[:, None]
+        got = ops.interp_blend(x.cuda(), nbr.cuda(), given.cuda(), from_d2)
+        assert rel_err(got.cpu(), want) <= 1e-6, from_d2
