@@ -44,3 +44,32 @@ def test_state_dict_roundtrip_with_oracle():
     src = build_model(OracleModel, "nuscenes")
     dst = build_model(ModelBase, "nuscenes")
     dst.load_state_dict(src.state_dict(), strict=True)
+
+
+@pytest.mark.parametrize("native_executor", [True, False])
+@pytest.mark.parametrize("n_points", [400, 120, 40])
+@pytest.mark.parametrize("name", ["nuscenes", "kitti"])
+def test_tiny_scans_match_oracle(name, n_points, native_executor):
+    """Scans far below the sizes the levels are tuned for (400 / 120 / 40 points: neighbourhoods larger than the cloud,
+    sampling levels that shrink to a handful of points, curves of one or two points): the reference's code path still
+    answers there (the oracle runs it on the CPU), so ours has to as well - same logits inside the north-star tolerance,
+    through both executors."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    data = driving_scan_batch([3], kind=name, subsample=n_points)
+    ref = randomize_model_(build_model(OracleModel, name), 1234).eval()
+    torch.manual_seed(5)
+    with torch.no_grad():
+        want = ref(data)
+    model = build_model(ModelBase, name, precision="bf16x3", native_executor=native_executor)
+    model.load_state_dict(ref.state_dict(), strict=True)
+    model = model.cuda().eval()
+    torch.manual_seed(5)
+    with torch.no_grad():
+        got = model(data.to("cuda"))
+    assert got.shape == want.shape and bool(torch.isfinite(got).all())
+    err = rel_err(got.cpu(), want)
+    print("%s %d points native=%s rel err %.3e" % (name, n_points, native_executor, err))
+    assert err <= 1e-4
