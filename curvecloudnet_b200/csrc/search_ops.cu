@@ -293,6 +293,69 @@ __global__ void __launch_bounds__(256) ball_query_kernel(
     if (cnt_out && lane == 0) cnt_out[q] = cnt;
 }
 
+// Neighbour search in FEATURE space (DynamicEdgeConv, dgcnn.py:64-89: the graph is rebuilt from the D-dimensional rows
+// [x, pos] of every layer).  One warp per query, brute force over the query's own cloud; squared distance accumulated
+// over the D columns in order, every operation rounded (no FMA) - oracle/tp_ops.py::_sqdist.
+//   mode 0: the FRNN contract (fast_knn with r = 0.25, point_ops.py:84-88): d2 <= r2, the K smallest by (d2, index)
+//   mode 1: ball_query (point_ops.py:81): d2 < r2, the first K in index order
+__device__ __forceinline__ float feat_sqdist(const float* __restrict__ a, const float* __restrict__ b, int dim) {
+    float t = __fsub_rn(a[0], b[0]);
+    float acc = __fmul_rn(t, t);
+    for (int d = 1; d < dim; ++d) {
+        t = __fsub_rn(a[d], b[d]);
+        acc = __fadd_rn(acc, __fmul_rn(t, t));
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(256) feat_neighbours_kernel(
+    const float* __restrict__ x1, int64_t ld1, const int64_t* __restrict__ batch1, int64_t n1,
+    const float* __restrict__ x2, int64_t ld2, const int32_t* __restrict__ sptr2, int dim, float r2, int K, int mode,
+    int32_t* __restrict__ idx_out, int32_t* __restrict__ cnt_out) {
+    ccn_pdl_wait();
+    const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (q >= n1) return;
+    const int lane = ccn_lane();
+    const float* qrow = x1 + q * ld1;
+    const int b = (int)batch1[q];
+    const int lo2 = sptr2[b], hi2 = sptr2[b + 1];
+    if (mode == 0) {
+        WarpTopK top;
+        top.init();
+        for (int j0 = lo2; j0 < hi2; j0 += 32) {
+            const int j = j0 + lane;
+            bool ok = false;
+            unsigned long long key = kKeyMax;
+            if (j < hi2) {
+                const float d2 = feat_sqdist(qrow, x2 + (int64_t)j * ld2, dim);
+                ok = d2 <= r2;
+                key = ccn_pack_key(d2, j);
+            }
+            top.offer(ok, key, K);
+        }
+        const bool have = top.held != kKeyMax;
+        if (lane < K) idx_out[q * K + lane] = have ? (int32_t)(top.held & 0xffffffffu) : -1;
+        if (cnt_out) {
+            const int cnt = __popc(__ballot_sync(0xffffffffu, have && lane < K));
+            if (lane == 0) cnt_out[q] = cnt;
+        }
+        return;
+    }
+    int cnt = 0;
+    for (int j0 = lo2; j0 < hi2 && cnt < K; j0 += 32) {
+        const int j = j0 + lane;
+        bool hit = false;
+        if (j < hi2) hit = feat_sqdist(qrow, x2 + (int64_t)j * ld2, dim) < r2;
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        const int at = cnt + __popc(m & ((1u << lane) - 1u));
+        if (hit && at < K) idx_out[q * K + at] = j;
+        cnt += __popc(m);
+    }
+    cnt = min(cnt, K);
+    for (int t = cnt + lane; t < K; t += 32) idx_out[q * K + t] = -1;
+    if (cnt_out && lane == 0) cnt_out[q] = cnt;
+}
+
 }  // namespace
 
 extern "C" int64_t ccn_grid_num_cells(int64_t n2) {
@@ -375,6 +438,19 @@ extern "C" int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t 
     const float r2 = radius * radius;
     ccn_launch(ball_query_kernel, dim3(ccn_blocks_exact(n1 * 32, 256)), dim3(256), 0, (cudaStream_t)stream, 
         pos1, batch1, n1, pos2, sample_ptr2, r2, K, idx_out, cnt_out);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}
+
+extern "C" int ccn_feat_neighbours(const float* x1, int64_t ld1, const int64_t* batch1, int64_t n1, const float* x2,
+                                   int64_t ld2, const int32_t* sample_ptr2, int32_t dim, float radius, int32_t K,
+                                   int32_t mode, int32_t* idx_out, int32_t* cnt_out, ccn_stream_t stream) {
+    CCN_REQUIRE(n1 >= 0 && dim >= 1 && ld1 >= dim && ld2 >= dim && K >= 1 && (mode == 0 || mode == 1) && idx_out && sample_ptr2);
+    CCN_REQUIRE(mode == 1 || K <= 32);
+    if (n1 == 0) return CCN_OK;
+    CCN_REQUIRE(x1 && x2 && batch1);
+    ccn_launch(feat_neighbours_kernel, dim3(ccn_blocks_exact(n1 * 32, 256)), dim3(256), 0, (cudaStream_t)stream,
+               x1, ld1, batch1, n1, x2, ld2, sample_ptr2, (int)dim, radius * radius, (int)K, (int)mode, idx_out, cnt_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

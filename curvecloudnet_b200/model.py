@@ -144,8 +144,10 @@ class ModelBase(torch.nn.Module):
             return M.CurveFPModule(kw["knn"][i], MLP(dims, act="leaky_relu", bias=b), with_xyz=kw["with_xyz"])
         if name == "mlp":
             return M.SharedMLP(dims, **kw)
-        if name in ("dgcnn", "dgcnn-rad"):
-            raise NotImplementedError("step %s: DynamicEdgeConv is not reached by any shipped CurveCloudNet config" % name)
+        if name == "dgcnn":                                                 # base.py:98-99
+            return M.DGCNNLayer(MLP(dims, bias=b), kw["knn"][i], with_xyz=kw["with_xyz"])
+        if name == "dgcnn-rad":                                             # base.py:100-101
+            return M.DGCNNLayerRadius(MLP(dims, bias=b), kw["radii"][i], with_xyz=kw["with_xyz"])
         raise NotImplementedError("Have not implemented step %s yet!" % name)
 
     # ------------------------------------------------------------------------------ forward

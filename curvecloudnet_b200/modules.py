@@ -427,7 +427,7 @@ class CurveFPModule(FPModule):
 
 
 # ----------------------------------------------------------------------------------------------
-# dgcnn.py (StaticEdgeConv / SGCNNLayer; the Dynamic* classes are reached by no shipped config)
+# dgcnn.py (StaticEdgeConv / SGCNNLayer; DynamicEdgeConv / DGCNNLayer / DGCNNLayerRadius below them)
 # ----------------------------------------------------------------------------------------------
 class SGCNNLayer(nn.Module):
     """dgcnn.py:130-266.  kNN graph in xyz space.
@@ -528,6 +528,76 @@ class SGCNNLayer(nn.Module):
             msg, msg_in = msg if both else (msg, msg)
             out = ops.seg_aggregate(msg, self.attend_nn(msg_in), edges.row_ptr, edges.nq, "attend", n_planes(), cache)
         return out, pos, batch, point2curveidx
+
+
+class _DynamicEdgeConv(nn.Module):
+    """DynamicEdgeConv (dgcnn.py:16-95): EdgeConv whose graph is rebuilt from the layer's own INPUT rows - here [x, pos] -
+    by a neighbour search in that feature space (knn_ball_group_pytorch3d on D-dimensional rows, point_ops.py:73-111):
+    use_knn: fast_knn, i.e. the fixed-radius kNN contract with the 0.25 the reference falls back to when no radius is given
+    (point_ops.py:84-87); else ball_query with K = 128.  message = nn([x_i, x_j - x_i]) (:91-92), default aggregation of
+    MessagePassing over the target's edges (max / mean / add).  Reached by no shipped configuration: the search is brute
+    force (ccn_feat_neighbours); everything behind it is the sparse SGCNN machinery (first Linear decomposed per point,
+    ccn_edge_pair_layer1, MLP, ccn_seg_aggregate)."""
+
+    KNN_FALLBACK_RADIUS = 0.25      # point_ops.py:85-87 "Not setting radius for Fast-KNN!"
+    BALL_K = 128                    # point_ops.py:81
+
+    def __init__(self, nn, k=None, radius=None, aggr="max", num_workers=1, use_knn=True, with_xyz=False, **kwargs):
+        super().__init__()
+        if aggr not in ("max", "mean", "add", "sum"):
+            raise NotImplementedError("DynamicEdgeConv aggregation %r" % (aggr,))
+        self.nn, self.k, self.r, self.aggr = nn, k, radius, aggr
+        self.num_workers, self.use_knn, self.with_xyz = num_workers, use_knn, with_xyz
+        self._dec, self._dec_src = None, None
+
+    def _decomposed(self):
+        layers = self.nn.layers()
+        if self._dec is None or self._dec_src is not layers:
+            l0 = layers[0]
+            c = l0.in_features // 2
+            wa, wb = l0.w[:, :c], l0.w[:, c:]
+            # nn([x_i, x_j - x_i]) first Linear: P (per source j) = Wb, Q (per target i) = Wa - Wb (+ bias)
+            wpq, bpq = torch.cat([wb, wa - wb], dim=0), torch.cat([torch.zeros_like(l0.b), l0.b])
+            self._dec, self._dec_src = (PreparedLinear(wpq.contiguous(), bpq.contiguous()), l0.act, l0.slope), layers
+        return self._dec
+
+    def search(self, xin, batch, sptr):
+        """-> (idx (n, K) int32 -1 padded, counts): the edge list of dgcnn.py:80-85, grouped by query."""
+        if self.use_knn:
+            return ops.feat_neighbours(xin, batch, xin, sptr, self.k, self.KNN_FALLBACK_RADIUS, "knn")
+        return ops.feat_neighbours(xin, batch, xin, sptr, self.BALL_K, self.r, "ball")
+
+    def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        if x is None and not self.with_xyz:
+            raise TypeError("DynamicEdgeConv needs node features (x is None and with_xyz is False)")   # dgcnn.py:68-72 fails on None
+        if self.training:
+            return T.dgcnn_layer(self, x, pos, batch, point2curveidx, **kwargs)
+        cache = get_cache(kwargs)
+        sptr = cache.sample_ptr(batch)
+        xin = x if not self.with_xyz else (pos if x is None else ops.concat_cols([x, pos]))
+        nbr, cnt = self.search(xin, batch, sptr)
+        edges = ops.dense_to_csr(nbr, cnt)
+        lin_pq, act0, slope0 = self._decomposed()
+        PQ = lin_pq(xin)
+        npl = n_planes() if self.nn.num_layers > 1 else 0
+        msg = self.nn.forward_from(ops.edge_pair_layer1(PQ, edges, act0, slope0, npl), 1)
+        mode = "sum" if self.aggr in ("add", "sum") else self.aggr
+        out = ops.seg_aggregate(msg, None, edges.row_ptr, edges.nq, mode, n_planes(), cache)
+        return out, pos, batch, point2curveidx
+
+
+class DGCNNLayer(_DynamicEdgeConv):
+    """dgcnn.py:98-111: k nearest rows of [x, pos] (within the fast-kNN fallback radius)."""
+
+    def __init__(self, nn, k, aggr="max", num_workers=1, with_xyz=False, **kwargs):
+        super().__init__(nn, k, None, aggr, num_workers, use_knn=True, with_xyz=with_xyz)
+
+
+class DGCNNLayerRadius(_DynamicEdgeConv):
+    """dgcnn.py:114-127: the first 128 rows of [x, pos] inside radius r."""
+
+    def __init__(self, nn, r, aggr="max", num_workers=1, with_xyz=False, **kwargs):
+        super().__init__(nn, None, r, aggr, num_workers, use_knn=False, with_xyz=with_xyz)
 
 
 # ----------------------------------------------------------------------------------------------

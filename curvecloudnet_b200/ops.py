@@ -385,6 +385,21 @@ def ball_query(pos1, batch1, pos2, sptr2: SamplePtr, radius: float, K: int = 128
     return idx, cnt
 
 
+def feat_neighbours(x1, batch1, x2, sptr2: SamplePtr, K: int, radius: float, mode: str):
+    """Neighbours in FEATURE space (DynamicEdgeConv, dgcnn.py:64-89): mode "knn" = fixed-radius kNN by (d2, index)
+    (fast_knn on D-dimensional rows, K <= 32), "ball" = first K in index order inside the radius (ball_query)."""
+    x1, ld1 = _rows(x1)
+    x2, ld2 = _rows(x2)
+    if x1.shape[1] != x2.shape[1]:
+        raise ValueError("dimension mismatch: points1 of dimension %d while points2 of dimension %d" % (x1.shape[1], x2.shape[1]))
+    n1 = x1.shape[0]
+    idx = _empty((n1, K), torch.int32, x1)
+    cnt = _empty((n1 + 2,), torch.int32, x1)
+    call("ccn_feat_neighbours", x1, ld1, _i64(batch1), n1, x2, ld2, sptr2.dev, x1.shape[1], float(radius), K,
+         {"knn": 0, "ball": 1}[mode], idx, cnt)
+    return idx, cnt
+
+
 def dense_to_csr(idx: torch.Tensor, cnt: torch.Tensor) -> EdgeCSR:
     """(nq, K) table with leading valid entries + per-row counts (nq+2 buffer) -> CSR (one host sync for E)."""
     nq, K = idx.shape

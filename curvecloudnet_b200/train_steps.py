@@ -207,6 +207,27 @@ def sgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
     return out, pos, batch, curve
 
 
+def dgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
+    """DynamicEdgeConv in training form (dgcnn.py:64-92): the graph comes from the detached input rows (index selection
+    carries no gradient in the reference either), the message MLP runs in training mode over the edge list."""
+    cache = get_cache(kwargs)
+    sptr = cache.sample_ptr(batch)
+    x = cat_xyz(x, pos, mod.with_xyz)
+    nbr, cnt = mod.search(x.detach(), batch, sptr)
+    edges = ops.dense_to_csr(nbr, cnt)
+    mlp = mod.nn
+    lin0 = mlp.lins[0]
+    W = lin0.weight
+    c = W.shape[1] // 2
+    wa, wb = W[:, :c], W[:, c:]
+    wpq = torch.cat([wb, wa - wb], dim=0)
+    bpq = torch.cat([torch.zeros_like(lin0.bias), lin0.bias]) if lin0.bias is not None else None
+    PQ = A.linear(x, wpq, bpq)
+    msg = A.mlp_train(mlp, _first_hidden(mlp, A.edge_pair(PQ, edges)), first=1)
+    mode = "sum" if mod.aggr in ("add", "sum") else mod.aggr
+    return A.seg_aggregate(msg, None, edges.row_ptr, edges.nq, mode), pos, batch, curve
+
+
 # ---------------------------------------------------------------------------------------------- mlp.py / skip_connect.py
 def shared_mlp(mod, x, pos, batch, curve=None, **kwargs):
     return A.mlp_train(mod.mlp, cat_xyz(x, pos, mod.with_xyz)), pos, batch, curve

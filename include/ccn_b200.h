@@ -191,6 +191,17 @@ int ccn_knn_grid(const float* pos1, const int64_t* batch1, int64_t n1, const flo
                  int32_t* cnt_out, ccn_stream_t stream);
 int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t n1, const float* pos2, const int32_t* sample_ptr2,
                    float radius, int32_t K, int32_t* idx_out, int32_t* cnt_out, ccn_stream_t stream);
+/* Neighbour search in FEATURE space - the graph of DynamicEdgeConv (src/models/modules/dgcnn.py:64-89: DGCNNLayer :98-111,
+ * DGCNNLayerRadius :114-127), which the reference rebuilds from the rows [x, pos] of every layer through
+ * knn_ball_group_pytorch3d (point_ops.py:73-111).  x1 (n1, dim) / x2 (n2, dim) fp32 rows with leading dimensions ld1 / ld2;
+ * a query searches the cloud sample_ptr2[batch1[q]] .. of x2; squared distance summed over the columns in order, every
+ * operation rounded.  mode 0: fixed-radius kNN, d2 <= radius^2, the K <= 32 smallest by (d2, index) (fast_knn,
+ * point_ops.py:84-88, frnn.frnn_grid_points on dim-D points); mode 1: d2 < radius^2, the first K in index order
+ * (pytorch3d.ops.ball_query, point_ops.py:81, K = 128 there).  idx_out (n1, K) global row indices of x2, -1 padded;
+ * cnt_out (n1) or null.  Brute force, O(n1 * cloud * dim): no shipped configuration reaches these steps. */
+int ccn_feat_neighbours(const float* x1, int64_t ld1, const int64_t* batch1, int64_t n1, const float* x2, int64_t ld2,
+                        const int32_t* sample_ptr2, int32_t dim, float radius, int32_t K, int32_t mode, int32_t* idx_out,
+                        int32_t* cnt_out, ccn_stream_t stream);
 
 /* ---- gathers and segmented aggregation ---------------------------------------------------------------
  * replace x[idx] / torch_scatter / torch_geometric.utils.softmax / frnn_gather on the path

@@ -90,6 +90,10 @@ class ModelBase(torch.nn.Module):
             return M.SAModule(kw["ratios"][i], kw["radii"][i], MLP(dims, bias=b), attend_nn=att, k=kw["knn"][i], **kw)
         if name == "sa-global":
             return M.GlobalSAModule(MLP(dims, bias=b), **kw)
+        if name == "dgcnn":                                                # base.py:98-99
+            return M.DGCNNLayer(MLP(dims, bias=b), kw["knn"][i], with_xyz=kw["with_xyz"])
+        if name == "dgcnn-rad":                                            # base.py:100-101
+            return M.DGCNNLayerRadius(MLP(dims, bias=b), kw["radii"][i], with_xyz=kw["with_xyz"])
         if name == "sgcnn":
             return M.SGCNNLayer(MLP(dims, bias=b), kw["knn"][i], r=kw["radii"][i],
                                 attend_nn=self._attend(dims[-1], kw, False), **kw)

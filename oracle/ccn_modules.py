@@ -306,7 +306,7 @@ class CurveFPModule(FPModule):
 
 
 # ----------------------------------------------------------------------------------
-# dgcnn.py (StaticEdgeConv / SGCNNLayer only - the Dynamic* classes are dead in all configs)
+# dgcnn.py (StaticEdgeConv / SGCNNLayer; DynamicEdgeConv / DGCNNLayer / DGCNNLayerRadius - reached by no shipped config)
 # ----------------------------------------------------------------------------------
 class SGCNNLayer(nn.Module):
     """dgcnn.py:130-266.  kNN graph in xyz.
@@ -366,6 +366,54 @@ class SGCNNLayer(nn.Module):
         if self.aggr_type == "max":
             return tp.scatter_max(msg, i, 0, None, n)[0]
         return tp.scatter_add(msg * tp.segment_softmax(self.attend_nn(msg), i), i, 0)
+
+
+class DynamicEdgeConv(nn.Module):
+    """dgcnn.py:16-95: the graph is rebuilt from the input rows x (= [x, pos] in the two layers below) with
+    knn_ball_group_pytorch3d on D-dimensional points (:80-83: fast kNN with the 0.25 fallback radius, or ball-group);
+    edge_index = flip([row, col]) (:84-85): source j = neighbour, target i = query; message nn([x_i, x_j - x_i]) (:91-92);
+    MessagePassing's own aggregation over the target (max / mean / add; empty targets give 0)."""
+
+    def __init__(self, nn, k=None, radius=None, aggr="max", num_workers=1, use_knn=True, **kwargs):
+        super().__init__()
+        self.nn, self.k, self.r, self.aggr, self.use_knn = nn, k, radius, aggr, use_knn
+
+    def edge_conv(self, x, batch):
+        if self.use_knn:
+            row, col = po.knn_ball_group(x, x, batch, batch, operation="knn", knn=self.k)
+        else:
+            row, col = po.knn_ball_group(x, x, batch, batch, operation="ball-group", radius=self.r)
+        i, j = row, col
+        msg = self.nn(torch.cat([x[i], x[j] - x[i]], dim=-1))
+        n = x.shape[0]
+        if self.aggr == "max":
+            return tp.scatter_max(msg, i, 0, None, n)[0]
+        if self.aggr == "mean":
+            return tp.scatter_mean(msg, i, 0, None, n)
+        assert self.aggr in ("add", "sum")
+        return tp.scatter_add(msg, i, 0, None, n)
+
+
+class DGCNNLayer(DynamicEdgeConv):
+    """dgcnn.py:98-111."""
+
+    def __init__(self, nn, k, aggr="max", num_workers=1, with_xyz=False, **kwargs):
+        super().__init__(nn, k, None, aggr, num_workers)
+        self.with_xyz = with_xyz
+
+    def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        return self.edge_conv(_cat_xyz(x, pos, self.with_xyz), batch), pos, batch, point2curveidx
+
+
+class DGCNNLayerRadius(DynamicEdgeConv):
+    """dgcnn.py:114-127."""
+
+    def __init__(self, nn, r, aggr="max", num_workers=1, with_xyz=False, **kwargs):
+        super().__init__(nn, None, r, aggr, num_workers, use_knn=False)
+        self.with_xyz = with_xyz
+
+    def forward(self, x, pos, batch, point2curveidx=None, **kwargs):
+        return self.edge_conv(_cat_xyz(x, pos, self.with_xyz), batch), pos, batch, point2curveidx
 
 
 # ----------------------------------------------------------------------------------

@@ -310,6 +310,47 @@ def make_models_extra(rbase):
     return out
 
 
+def make_dgcnn(rbase):
+    """DynamicEdgeConv (dgcnn.py:16-127) through the REAL reference classes: DGCNNLayer / DGCNNLayerRadius with every
+    default aggregation, and a whole ModelBase whose step list uses `dgcnn` twice (no shipped config does)."""
+    import src.models.modules.dgcnn as rdg
+    from torch_geometric.nn import MLP
+    from curvecloudnet_b200.synthetic import object_scan_batch, randomize_model_
+    data = object_scan_batch([71, 72], n_points=600)
+    gen = torch.Generator().manual_seed(3)
+    x = 0.2 * torch.randn(data.pos.shape[0], 5, generator=gen)
+    out = {"pos": data.pos, "batch": data.batch, "curve": data.curve_idxs, "x": x, "layers": {}}
+    for tag, mk in {
+        "knn_max": lambda nn_: rdg.DGCNNLayer(nn_, 8, with_xyz=True),
+        "knn_mean": lambda nn_: rdg.DGCNNLayer(nn_, 12, aggr="mean", with_xyz=True),
+        "knn_add_posonly": lambda nn_: rdg.DGCNNLayer(nn_, 6, aggr="add", with_xyz=True),
+        "ball_max": lambda nn_: rdg.DGCNNLayerRadius(nn_, 0.3, with_xyz=True),
+        "ball_mean_noxyz": lambda nn_: rdg.DGCNNLayerRadius(nn_, 0.35, aggr="mean", with_xyz=False),
+    }.items():
+        feat = None if tag.endswith("posonly") else x
+        d = (0 if feat is None else 5) + (0 if tag.endswith("noxyz") else 3)
+        mod = mk(MLP([2 * d, 32, 48]))
+        randomize_model_(mod, 900 + len(out["layers"]))
+        mod.eval()
+        with torch.no_grad():
+            y = mod(feat, data.pos, data.batch, data.curve_idxs)[0]
+        out["layers"][tag] = {"state": {k: v.clone() for k, v in mod.state_dict().items()}, "out": y, "dims": [2 * d, 32, 48]}
+        print("dgcnn", tag, tuple(y.shape), float(y.abs().max()))
+    model = rbase.ModelBase(in_dim=4, n_out=6, steps=["dgcnn", "dgcnn", "mlp"], feat_dims=[[32, 32], [32, 64], [64]],
+                            out_mlp={"dims": [32]}, knn=[10, 6, None], radii=[None, None, None], with_xyz=True)
+    randomize_model_(model, 1234)
+    model.eval()
+    data.x = x[:, :1].contiguous()
+    torch.manual_seed(81)
+    with torch.no_grad():
+        logits = model(data)
+    out["model"] = {"kwargs": dict(in_dim=4, n_out=6, steps=["dgcnn", "dgcnn", "mlp"], feat_dims=[[32, 32], [32, 64], [64]],
+                                   out_mlp={"dims": [32]}, knn=[10, 6, None], radii=[None, None, None], with_xyz=True),
+                    "x": data.x, "weight_seed": 1234, "logits": logits}
+    print("dgcnn model", tuple(logits.shape), float(logits.abs().max()))
+    return out
+
+
 def _reference_class(relpath: str, class_name: str, names):
     """A stand-in class whose methods are compiled from the reference's own source text (the module itself cannot be
     imported here: nuscenes-devkit / cv2 / mitsuba / torch_geometric.data are absent)."""
@@ -504,6 +545,10 @@ def main():
         print("polarmix.pt", os.path.getsize(os.path.join(OUT, "polarmix.pt")) // 1024, "KiB")
         return
     rpo, rbase, rconv, rfps = _import_reference()
+    if len(sys.argv) > 1 and sys.argv[1] == "dgcnn":      # only the DynamicEdgeConv fixture
+        torch.save(_compact(make_dgcnn(rbase)), os.path.join(OUT, "dgcnn.pt"))
+        print("dgcnn.pt", os.path.getsize(os.path.join(OUT, "dgcnn.pt")) // 1024, "KiB")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "models_extra":
         torch.save(_compact(make_models_extra(rbase)), os.path.join(OUT, "models_extra.pt"))
         print("models_extra.pt", os.path.getsize(os.path.join(OUT, "models_extra.pt")) // 1024, "KiB")

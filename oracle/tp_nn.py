@@ -172,3 +172,15 @@ class MessagePassing(torch.nn.Module):
                     n_dst = val[1].shape[0]
         out = self.message(**margs)
         return self.aggregate(out, dst, ptr=None, dim_size=n_dst)
+
+    def aggregate(self, inputs, index, ptr=None, dim_size=None):
+        """torch_geometric 2.3.0 default aggregation for a string `aggr` (DynamicEdgeConv, dgcnn.py:49, relies on it):
+        torch_scatter reductions over the target index; a target without edges gets 0."""
+        from . import tp_ops as tp
+        if self.aggr == "max":
+            return tp.scatter_max(inputs, index, 0, None, dim_size)[0]
+        if self.aggr == "mean":
+            return tp.scatter_mean(inputs, index, 0, None, dim_size)
+        if self.aggr in ("add", "sum"):
+            return tp.scatter_add(inputs, index, 0, None, dim_size)
+        raise NotImplementedError("aggr %r" % (self.aggr,))

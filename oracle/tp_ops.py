@@ -167,7 +167,7 @@ def ball_query(p1, p2, lengths1, lengths2, K, radius):
             continue
         for s in range(0, l1, 2048):
             q = p1[n, s:min(s + 2048, l1)]
-            inside = sqdist3(q[:, None, :], p2[n, None, :l2, :]) < r2
+            inside = _sqdist(q[:, None, :], p2[n, None, :l2, :]) < r2     # any D (sqdist3 for D = 3)
             rank = torch.cumsum(inside, dim=1)  # 1-based ordinal among hits
             keep = inside & (rank <= K)
             rows, cols = torch.nonzero(keep, as_tuple=True)

@@ -131,3 +131,43 @@ def test_oracle_training_step_matches_reference(name, mode):
     loss.backward()
     # the restatement runs the same CPU torch kernels as the reference did: agreement to rounding
     check_train_golden(model, logits, loss, g[mode], 1e-5, 1e-4 if mode == "frozen_bn" else 1e-3, "%s %s oracle" % (name, mode))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# DynamicEdgeConv (dgcnn.py:16-127; reached by no shipped config) against the REAL reference classes (dgcnn.pt)
+# ---------------------------------------------------------------------------------------------------------------
+DGCNN_LAYERS = {
+    "knn_max": lambda Mo, nn_: Mo.DGCNNLayer(nn_, 8, with_xyz=True),
+    "knn_mean": lambda Mo, nn_: Mo.DGCNNLayer(nn_, 12, aggr="mean", with_xyz=True),
+    "knn_add_posonly": lambda Mo, nn_: Mo.DGCNNLayer(nn_, 6, aggr="add", with_xyz=True),
+    "ball_max": lambda Mo, nn_: Mo.DGCNNLayerRadius(nn_, 0.3, with_xyz=True),
+    "ball_mean_noxyz": lambda Mo, nn_: Mo.DGCNNLayerRadius(nn_, 0.35, aggr="mean", with_xyz=False),
+}
+
+
+@pytest.mark.parametrize("tag", list(DGCNN_LAYERS))
+def test_dgcnn_layers(tag):
+    from oracle.tp_nn import MLP
+    g = load("dgcnn.pt")
+    rec = g["layers"][tag]
+    mod = DGCNN_LAYERS[tag](M, MLP(rec["dims"]))
+    mod.load_state_dict(rec["state"], strict=True)
+    mod.eval()
+    x = None if tag.endswith("posonly") else g["x"]
+    with torch.no_grad():
+        out = mod(x, g["pos"], g["batch"], g["curve"])[0]
+    assert out.shape == rec["out"].shape
+    assert rel_err(out, rec["out"]) < 2e-6
+
+
+def test_dgcnn_model_logits():
+    from curvecloudnet_b200.synthetic import ScanBatch, randomize_model_
+    from oracle.ccn_model import ModelBase
+    g = load("dgcnn.pt")
+    rec = g["model"]
+    model = ModelBase(**rec["kwargs"])
+    randomize_model_(model, rec["weight_seed"])
+    model.eval()
+    with torch.no_grad():
+        logits = model(ScanBatch(rec["x"], g["pos"], g["batch"], g["curve"], None, None))
+    assert rel_err(logits, rec["logits"]) < 2e-6
