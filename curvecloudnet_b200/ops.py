@@ -251,6 +251,27 @@ def radius_1d_group(pos: torch.Tensor, topo: CurveTopology, idxs: torch.Tensor, 
     return EdgeCSR(row_ptr[:nq + 1], erow[:E], col[:E], E, nq, max_deg)
 
 
+def knn_1d_group(curve_glob: torch.Tensor, idxs: torch.Tensor, knn: int) -> EdgeCSR:
+    """knn_1d_group_subset (point_ops.py:114-140) as CSR over the queries (one host sync for E)."""
+    curve_glob, idxs = _i64(curve_glob), _i64(idxs)
+    nq = idxs.shape[0]
+    W = 2 * knn + 1
+    idx = _empty((nq, W), torch.int32, curve_glob)
+    cnt = _empty((nq + 2,), torch.int32, curve_glob)
+    call("ccn_knn_1d_group", curve_glob, curve_glob.shape[0], idxs, nq, knn, idx, cnt)
+    return dense_to_csr(idx, cnt)
+
+
+def group_first_k(values: torch.Tensor, batch: torch.Tensor, n_groups: int, kmax: int):
+    """First kmax rows of every group id in order of appearance -> (out (n_groups, kmax, d) zero padded, counts (n_groups,))."""
+    values, ldv = _rows(values)
+    d = values.shape[1]
+    out = _empty((n_groups, kmax, d), torch.float32, values)
+    cnt = _empty((max(n_groups, 1),), torch.int32, values)
+    call("ccn_group_first_k", values, ldv, _i64(batch), values.shape[0], d, n_groups, kmax, out, cnt)
+    return out, cnt[:n_groups]
+
+
 def knn_1d_superset(pos: torch.Tensor, curve_ord: torch.Tensor, idxs: torch.Tensor, knn: int):
     pos, idxs = _f32(pos), _i64(idxs)
     n = pos.shape[0]

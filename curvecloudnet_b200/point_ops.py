@@ -121,6 +121,15 @@ def radius_1d_group_subset(points, idxs, point2curveidx, batch, radius):
     return e.erow.to(torch.int64), e.ecol.to(torch.int64)
 
 
+def knn_1d_group_subset(points, idxs, point2curveidx, batch, knn):
+    """point_ops.py:114-140 -> (row = query ordinal, col = point index): up to knn points around each query along the point
+    order and on its curve, the query itself first.  (The reference forms the candidate indices in float32; identical below
+    2^24 points.)"""
+    _need_cuda(points, "knn_1d_group_subset")
+    e = ops.knn_1d_group(curveidx_local2global(point2curveidx, batch), idxs, int(knn))
+    return e.erow.to(torch.int64), e.ecol.to(torch.int64)
+
+
 def knn_1d_group_superset(points, idxs, point2curveidx, batch, knn):
     """point_ops.py:196-260 -> (row = point index, col = sampled ORDINAL)."""
     _need_cuda(points, "knn_1d_group_superset")
@@ -193,3 +202,43 @@ def get_curves(points, beam_ids, labels=None, reflectance=None, curve_thresh: fl
                                        if labels.dtype == torch.int64 else labels[reorder])
     ref = None if reflectance is None else ops.gather_rows(reflectance.reshape(reflectance.shape[0], -1).float(), reorder)
     return pts, cid, lab, ref, inv
+
+
+def dense2padded_pyg(x: torch.Tensor, batch: torch.Tensor):
+    """point_ops.py:264-284 -> (x_padded (B, Nmax, C), mask (B, Nmax), lengths (B,), offsets (B-1,))."""
+    x_padded, mask = to_batch_padded(x, batch)
+    lengths = mask.sum(dim=-1)
+    return x_padded, mask, lengths, torch.cumsum(lengths, dim=0)[:-1]
+
+
+def pytorch3didx2pyg(idx: torch.Tensor, mask: torch.Tensor, offsets: torch.Tensor) -> torch.Tensor:
+    """point_ops.py:287-290: padded (B, P, K) local indices -> flat global indices of the entries selected by mask
+    (shifts idx in place, as the reference does)."""
+    idx[1:, :] += offsets.view(-1, 1, 1)
+    return idx[mask].flatten()
+
+
+def is_sorted(t: torch.Tensor) -> torch.Tensor:
+    """point_ops.py:464-465, quirk kept: `all(diff) >= 0` compares the BOOLEAN all-differences-nonzero with 0, so the result
+    is always True (the assert of curveidx_local2global, :31, never fires upstream either)."""
+    return torch.all(t[1:] - t[:-1]) >= 0
+
+
+def group_first_k_values(values: torch.Tensor, batch: torch.Tensor, k):
+    """point_ops.py:384-428 -> (grouped (num_batches, k_max[, D]) zero padded, mask (num_batches, k_max)): the first k values of
+    every batch id that occurs, in order of appearance; k an int or a per-batch tensor (the limit of batch p is k[p], the
+    width k.max()).  Host syncs: the largest id and the per-id counts (the reference synchronises in torch.unique)."""
+    _need_cuda(values, "group_first_k_values")
+    if values.dtype != torch.float32:
+        raise TypeError("group_first_k_values: float32 values (got %s)" % values.dtype)
+    one_d = values.dim() == 1
+    v2 = values.view(values.shape[0], -1)
+    k_max = int(torch.max(k).item()) if torch.is_tensor(k) else int(k)
+    n_ids = int(batch.max().item()) + 1 if batch.numel() else 0                # host sync
+    out, cnt = ops.group_first_k(v2, batch, n_ids, k_max)
+    present = cnt > 0
+    out, cnt = out[present], cnt[present].to(torch.int64)                          # ids that do not occur vanish (torch.unique)
+    lim = torch.clamp(cnt, max=k.to(cnt.device) if torch.is_tensor(k) else k_max)
+    mask = torch.arange(k_max, device=values.device).unsqueeze(0) < lim.unsqueeze(1)
+    out = torch.where(mask.unsqueeze(-1), out, torch.zeros_like(out))
+    return (out.squeeze(-1) if one_d else out), mask

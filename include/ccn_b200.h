@@ -132,6 +132,18 @@ int ccn_radius_1d_group_fill(const int32_t* curve_ord, const int64_t* curve_loca
                              const int32_t* row_ptr, int32_t* col, ccn_stream_t stream);
 int ccn_knn_1d_superset(const float* pos, const int32_t* curve_ord, int64_t n, const int64_t* idxs, int64_t nq,
                         int32_t knn, int32_t* nbr, float* wgt, ccn_stream_t stream);
+/* knn_1d_group_subset (src/models/utils/point_ops.py:114-140; called by no shipped configuration): for query q the points
+ * idxs[q], -1, +1, -2, +2, ... along the point order that lie inside the array and on the query's curve (curve_glob =
+ * curveidx_local2global), the first knn of them, the query included.  idx_out (nq, 2 knn + 1) leading valid entries, -1
+ * padded; cnt_out (nq + 2) counts (the layout ccn_dense_to_csr takes). */
+int ccn_knn_1d_group(const int64_t* curve_glob, int64_t n, const int64_t* idxs, int64_t nq, int32_t knn, int32_t* idx_out,
+                     int32_t* cnt_out, ccn_stream_t stream);
+/* group_first_k_values (src/models/utils/point_ops.py:384-428; caller: scanning_simulator/utils/curve_cloud.py:223): the first
+ * kmax rows of every group id 0 .. n_groups-1 in the order of appearance (= torch.sort(batch, stable=True)), zero padded.
+ * values (n, d) fp32 rows; out (n_groups, kmax, d); count_out (n_groups) = min(rows of the group, kmax).  Ids that do not
+ * occur give an all-zero block with count 0 (the reference drops them: the python wrapper does). */
+int ccn_group_first_k(const float* values, int64_t ldv, const int64_t* batch, int64_t n, int32_t d, int32_t n_groups,
+                      int32_t kmax, float* out, int32_t* count_out, ccn_stream_t stream);
 /* in-place exclusive scan of a[0..n), a[n] = total (replaces prefix_sum.prefix_sum_cuda, prefix_sum.h:6-20). */
 int ccn_excl_scan_i32(int32_t* a, int64_t n, int32_t* total_out, ccn_stream_t stream);
 

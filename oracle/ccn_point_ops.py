@@ -265,6 +265,44 @@ def radius_1d_group_subset(points, idxs, curve, batch, radius: float):
     return row, cand[ok]
 
 
+def knn_1d_group_subset(points, idxs, curve, batch, knn: int):
+    """point_ops.py:114-140 (reached by no shipped config), stated as a plain loop - small cases only: for query q the
+    candidates idxs[q] + [0, -1, +1, ..., -knn, +knn] that are inside the array and on the query's (global) curve, the first
+    knn of them in that order (the query itself counts, :133).  Returns (row = query ordinal, col = point index)."""
+    glob = curve_ids_global(curve, batch).tolist()
+    n = len(glob)
+    rows, cols = [], []
+    for q, c in enumerate(idxs.tolist()):
+        kept = 0
+        for s in range(2 * knn + 1):
+            j = c + (0 if s == 0 else (-((s + 1) // 2) if s % 2 else s // 2))
+            if 0 <= j < n and glob[j] == glob[c] and kept < knn:
+                rows.append(q)
+                cols.append(j)
+                kept += 1
+    return torch.tensor(rows, dtype=torch.int64), torch.tensor(cols, dtype=torch.int64)
+
+
+def group_first_k_values(values, batch, k):
+    """point_ops.py:384-428 (caller: scanning_simulator/utils/curve_cloud.py:223), stated as a plain loop - small cases only:
+    for every batch id that occurs (ascending) its first min(count, k) values in order of appearance, zero padded to
+    k_max = k or k.max(); k a per-occurring-batch tensor or an int.  Returns (grouped, mask)."""
+    ids = batch.tolist()
+    present = sorted(set(ids))
+    per_batch = torch.is_tensor(k)
+    k_max = int(k.max()) if per_batch else int(k)
+    v2 = values.reshape(values.shape[0], -1)
+    out = torch.zeros((len(present), k_max, v2.shape[1]), dtype=values.dtype)
+    mask = torch.zeros((len(present), k_max), dtype=torch.bool)
+    for p, g in enumerate(present):
+        members = [i for i, b in enumerate(ids) if b == g]
+        lim = min(len(members), int(k[p]) if per_batch else k_max)
+        for t in range(lim):
+            out[p, t] = v2[members[t]]
+            mask[p, t] = True
+    return (out.squeeze(-1) if values.dim() == 1 else out), mask
+
+
 def knn_1d_group_superset(points, idxs, curve, batch, knn: int):
     """point_ops.py:196-260.  For every point i: a_i = #sampled points at positions <= i; the
     candidates are the sampled ordinals a_i + [0,-1,+1,...,-(knn+1),+(knn+1)] that exist and

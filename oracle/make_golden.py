@@ -351,6 +351,33 @@ def make_dgcnn(rbase):
     return out
 
 
+def make_helpers(rpo):
+    """The two grouping helpers of point_ops.py that no shipped config calls, through the REAL functions."""
+    from curvecloudnet_b200.synthetic import object_scan_batch
+    data = object_scan_batch([91, 92], n_points=300)
+    n = data.pos.shape[0]
+    gen = torch.Generator().manual_seed(17)
+    out = {"pos": data.pos, "batch": data.batch, "curve": data.curve_idxs, "knn_1d": {}, "first_k": {}}
+    idxs = torch.sort(torch.randperm(n, generator=gen)[:97])[0]
+    idxs[0], idxs[-1] = 0, n - 1
+    out["idxs"] = idxs
+    for knn in (1, 3, 8):
+        row, col = rpo.knn_1d_group_subset(data.pos, idxs.clone(), data.curve_idxs, data.batch, knn)
+        out["knn_1d"][knn] = {"row": row, "col": col}
+        print("knn_1d_group_subset", knn, row.shape[0])
+    # group_first_k_values: unsorted ids with a gap (id 3 never occurs), 1-D and 2-D values, int and per-batch k
+    ids = torch.tensor([2, 0, 0, 5, 2, 2, 1, 0, 5, 2, 4, 4, 0, 2, 1, 2, 2, 0, 5, 4, 2, 0, 0, 2])
+    v1 = torch.randn(ids.shape[0], generator=gen)
+    v2 = torch.randn(ids.shape[0], 3, generator=gen)
+    out["first_k_ids"], out["first_k_v1"], out["first_k_v2"] = ids, v1, v2
+    for tag, vals, k in (("v1_k4", v1, 4), ("v2_k3", v2, 3), ("v2_k12", v2, 12),
+                         ("v1_ktensor", v1, torch.tensor([3, 1, 6, 2, 2])), ("v2_ktensor", v2, torch.tensor([1, 5, 2, 4, 3]))):
+        grouped, mask = rpo.group_first_k_values(vals.clone(), ids.clone(), k.clone() if torch.is_tensor(k) else k)
+        out["first_k"][tag] = {"k": k, "grouped": grouped, "mask": mask}
+        print("group_first_k_values", tag, tuple(grouped.shape))
+    return out
+
+
 def _reference_class(relpath: str, class_name: str, names):
     """A stand-in class whose methods are compiled from the reference's own source text (the module itself cannot be
     imported here: nuscenes-devkit / cv2 / mitsuba / torch_geometric.data are absent)."""
@@ -545,6 +572,10 @@ def main():
         print("polarmix.pt", os.path.getsize(os.path.join(OUT, "polarmix.pt")) // 1024, "KiB")
         return
     rpo, rbase, rconv, rfps = _import_reference()
+    if len(sys.argv) > 1 and sys.argv[1] == "helpers":    # only the unused grouping helpers of point_ops.py
+        torch.save(_compact(make_helpers(rpo)), os.path.join(OUT, "helpers.pt"))
+        print("helpers.pt", os.path.getsize(os.path.join(OUT, "helpers.pt")) // 1024, "KiB")
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "dgcnn":      # only the DynamicEdgeConv fixture
         torch.save(_compact(make_dgcnn(rbase)), os.path.join(OUT, "dgcnn.pt"))
         print("dgcnn.pt", os.path.getsize(os.path.join(OUT, "dgcnn.pt")) // 1024, "KiB")

@@ -449,3 +449,30 @@ def test_group_max_dense_and_interp_blend_against_formula(c):
         want = num / den[:, None]
         got = ops.interp_blend(x.cuda(), nbr.cuda(), given.cuda(), from_d2)
         assert rel_err(got.cpu(), want) <= 1e-6, from_d2
+
+
+def test_unused_grouping_helpers_match_reference():
+    """knn_1d_group_subset (point_ops.py:114-140) and group_first_k_values (:384-428) - called by no shipped configuration -
+    against the outputs of the REAL functions (tests/golden/helpers.pt): index results bit-exact, values bit-exact (copies);
+    plus the layout helpers dense2padded_pyg / pytorch3didx2pyg / is_sorted of the same file."""
+    from curvecloudnet_b200 import point_ops as po
+    g = load("helpers.pt")
+    pos, batch, curve = dev(g["pos"]), dev(g["batch"]), dev(g["curve"])
+    for knn, rec in g["knn_1d"].items():
+        row, col = po.knn_1d_group_subset(pos, dev(g["idxs"]), curve, batch, int(knn))
+        assert row.dtype == torch.int64 and torch.equal(row.cpu(), rec["row"]) and torch.equal(col.cpu(), rec["col"]), knn
+    ids = dev(g["first_k_ids"])
+    for tag, rec in g["first_k"].items():
+        vals = dev(g["first_k_v1"] if tag.startswith("v1") else g["first_k_v2"])
+        k = dev(rec["k"]) if torch.is_tensor(rec["k"]) else rec["k"]
+        grouped, mask = po.group_first_k_values(vals, ids, k)
+        assert grouped.shape == rec["grouped"].shape, tag
+        assert torch.equal(mask.cpu(), rec["mask"]) and torch.equal(grouped.cpu(), rec["grouped"]), tag
+    xp, mask, lengths, offsets = po.dense2padded_pyg(pos, batch)
+    lens = torch.bincount(g["batch"])
+    assert xp.shape == (2, int(lens.max()), 3) and torch.equal(lengths.cpu(), lens) and torch.equal(offsets.cpu(), lens.cumsum(0)[:-1])
+    assert torch.equal(xp[mask].cpu(), g["pos"]) and float(xp[~mask].abs().sum()) == 0.0
+    local = torch.arange(int(lens.max())).view(1, -1, 1).repeat(2, 1, 1).cuda()
+    flat = po.pytorch3didx2pyg(local, mask.unsqueeze(-1), offsets)
+    assert torch.equal(flat.cpu(), torch.arange(g["pos"].shape[0]))
+    assert bool(po.is_sorted(batch)) and bool(po.is_sorted(torch.tensor([3, 1, 2]).cuda()))     # upstream quirk: always True

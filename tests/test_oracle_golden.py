@@ -171,3 +171,17 @@ def test_dgcnn_model_logits():
     with torch.no_grad():
         logits = model(ScanBatch(rec["x"], g["pos"], g["batch"], g["curve"], None, None))
     assert rel_err(logits, rec["logits"]) < 2e-6
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the two grouping helpers of point_ops.py that no shipped config calls, against the REAL functions (helpers.pt)
+# ---------------------------------------------------------------------------------------------------------------
+def test_unused_grouping_helpers():
+    g = load("helpers.pt")
+    for knn, rec in g["knn_1d"].items():
+        row, col = po.knn_1d_group_subset(g["pos"], g["idxs"], g["curve"], g["batch"], int(knn))
+        assert torch.equal(row, rec["row"]) and torch.equal(col, rec["col"]), knn
+    for tag, rec in g["first_k"].items():
+        vals = g["first_k_v1"] if tag.startswith("v1") else g["first_k_v2"]
+        grouped, mask = po.group_first_k_values(vals, g["first_k_ids"], rec["k"])
+        assert torch.equal(mask, rec["mask"]) and torch.equal(grouped, rec["grouped"]), tag
