@@ -21,6 +21,7 @@ import numpy as np
 import torch
 
 from . import native
+from . import ops
 from .model import Batch
 
 POS_NORMALIZE = 20.0          # nuscenes_dataset.py:18, kitti_dataset.py:17
@@ -243,6 +244,59 @@ def ingest_scan_polarmix(sweep1: dict, sweep2: dict, mix: PolarMixDraw, learning
         raise ValueError("ingest_scan_polarmix: ring id out of range or unmapped label (flags %d)" % flags)
     out.pos = augment_points(out.pos, augmentation)
     return out
+
+
+@dataclass
+class A2D2Augmentation:
+    """The draws of SemA2D2._training_augmentation (audi_dataset.py:81-90): flip of the y axis, one scale for x and y."""
+    flip_y: int
+    scale: float
+
+    @classmethod
+    def draw(cls, rng=np.random) -> "A2D2Augmentation":
+        flip = int(rng.choice(2, 1)[0])
+        return cls(flip, float(rng.uniform(0.95, 1.05)))
+
+
+A2D2_POS_NORMALIZE = 30.0        # audi_dataset.py:21
+
+
+def ingest_a2d2_frame(frame: dict, labels=None, augmentation: Optional[A2D2Augmentation] = None, device="cuda",
+                      check: bool = True) -> Batch:
+    """SemA2D2.get (audi_dataset.py:120-141) after `_load_frame`: frame = the npz fields {"points" (n,3) f32, "reflectance"
+    (n,) f32, "timestamp" (n,) i64, "lidar_id" (n,) i64} as numpy arrays or tensors; labels = per-point class ids (the
+    reference reads them off the undistorted label image on the host, :92-117 - file and image decoding stay with the
+    caller).  Curves come from ccn_a2d2_curves (kNN graph per lidar -> components -> time order -> cuts), positions are
+    divided by 30 and, for training, y-flipped and x, y-scaled - all on the device.  -> Batch(x, pos, y, curve_idxs, reorder
+    = index of every output point in the input, counts = {curves, error flags})."""
+    native.load()
+    pts = np.ascontiguousarray(frame["points"], dtype=np.float32) if isinstance(frame["points"], np.ndarray) else frame["points"]
+    n = int(pts.shape[0])
+    ptd = _as_device(pts, torch.float32, device).view(n, 3)
+    lid = _as_device(_np_i64(frame["lidar_id"]), torch.int64, device)
+    tsd = _as_device(_np_i64(frame["timestamp"]), torch.int64, device)
+    refd = _as_device(frame["reflectance"] if torch.is_tensor(frame["reflectance"])
+                      else np.ascontiguousarray(frame["reflectance"], dtype=np.float32), torch.float32, device)
+    labd = _as_device(_np_i64(labels), torch.int64, device) if labels is not None else None
+    reorder, cid, sorted_pts, counts = ops.a2d2_curves(ptd, lid, tsd)
+    x = torch.empty((n, 1), dtype=torch.float32, device=ptd.device)
+    y = torch.empty((n,), dtype=torch.int64, device=ptd.device)
+    native.call("ccn_a2d2_finish", refd, labd if labd is not None else 0, reorder, n, 255.0, x, y)
+    pos = augment_points(sorted_pts, None, A2D2_POS_NORMALIZE)                      # points /= 30 (:137)
+    if augmentation is not None:                                                    # then flip / scale (:140-141)
+        a = ScanAugmentation(1.0, 0.0, 2 if augmentation.flip_y == 1 else 0, augmentation.scale, (0.0, 0.0, 0.0))
+        pos = augment_points(pos, a, 1.0)
+    if check:
+        flags = int(counts[1].item())                        # host sync
+        if flags & 1:
+            raise ValueError("ingest_a2d2_frame: lidar id outside [0, %d)" % len(ops.A2D2_KNN))
+        if flags & 2:
+            raise ValueError("ingest_a2d2_frame: timestamps span more than 2^30 ticks")
+    return Batch(x=x, pos=pos, y=y, curve_idxs=cid, reorder=reorder, counts=counts)
+
+
+def _np_i64(a):
+    return np.ascontiguousarray(a, dtype=np.int64) if isinstance(a, np.ndarray) else a
 
 
 def ingest_batch(sweeps: List[dict], learning_map: Optional[LearningMap] = None, dataset: str = "nuscenes",

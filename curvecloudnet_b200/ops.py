@@ -150,6 +150,37 @@ def get_curves(points: torch.Tensor, beam_ids: torch.Tensor, curve_thresh: float
     return reorder, inv, cid, sorted_pts, counts
 
 
+A2D2_KNN = (4, 4, 4, 3, 4)                       # audi_dataset.py:20
+A2D2_CURVE_THRESHES = (0.1, 0.17, 0.1, 0.12, 0.1)   # audi_dataset.py:19
+
+
+def a2d2_curves(points: torch.Tensor, lidar_id: torch.Tensor, timestamp: torch.Tensor, knn=A2D2_KNN,
+                curve_threshes=A2D2_CURVE_THRESHES):
+    """SemA2D2._get_curves (audi_dataset.py:156-243): -> (reorder i64 (n), curve_idxs i64 (n), sorted xyz f32 (n,3),
+    counts i32 [2] = {number of curves, error flags}); everything in the final (sensor-major) order."""
+    import ctypes
+    if points.dtype != torch.float32 or points.dim() != 2 or points.shape[1] < 3:
+        raise TypeError("points must be float32 (n, >=3)")
+    if len(knn) != len(curve_threshes):
+        raise ValueError("one k and one threshold per sensor")
+    points, ldp = _rows(points)
+    lidar_id, timestamp = _i64(lidar_id), _i64(timestamp)
+    n, ns = points.shape[0], len(knn)
+    nbytes = int(native.load().ccn_a2d2_scratch_bytes(n, ns))
+    if nbytes < 0:
+        raise native.CcnError("ccn_a2d2_scratch_bytes: invalid argument")
+    scratch = _empty((nbytes,), torch.uint8, points)
+    reorder = _empty((n,), torch.int64, points)
+    sorted_pts = _empty((n, 3), torch.float32, points)
+    cid = _empty((n,), torch.int64, points)
+    counts = _empty((2,), torch.int32, points)
+    k_host = (ctypes.c_int32 * ns)(*[int(k) for k in knn])
+    t_host = (ctypes.c_float * ns)(*[float(t) for t in curve_threshes])
+    call("ccn_a2d2_curves", points, ldp, lidar_id, timestamp, n, ns, ctypes.addressof(k_host), ctypes.addressof(t_host),
+         scratch, reorder, sorted_pts, cid, counts)
+    return reorder, cid, sorted_pts, counts
+
+
 def _finish_subset(parent_batch, idx_buf, count_dev, n_samples) -> Tuple[torch.Tensor, SamplePtr]:
     """Read back {sample_ptr of the selected level, count} with ONE host sync; trims idx."""
     out = _empty((n_samples + 1,), torch.int32, idx_buf)

@@ -82,6 +82,38 @@ def raycast_driving_scan(seed: int, beams=32, azimuth_steps=1085, elev_deg=(-30.
     return RawScan(points=pts, reflectance=refl, beam_ids=beam[keep].astype(np.float32))
 
 
+def a2d2_frame(seed: int, n_sensors: int = 5, beams: int = 16, azimuth_steps: int = 900, fov_deg: float = 60.0,
+               shuffle: bool = True) -> dict:
+    """An A2D2-shaped frame (src/data/audi_dataset.py:92-117 `_load_frame`: the npz keys points / reflectance / timestamp /
+    lidar_id): `n_sensors` 16-beam lidars at different mounts, each cut to the front camera's field of view, NO beam ids,
+    a timestamp per firing (all beams of a firing share it) and the points in shuffled file order.  Returns numpy arrays:
+    points f32 (n,3), reflectance f32 (n,), timestamp i64 (n,), lidar_id i64 (n,), label i64 (n,)."""
+    rng = np.random.default_rng(1000 + seed)
+    pts, refl, ts, ids = [], [], [], []
+    for sid in range(n_sensors):
+        lo = float(rng.uniform(-22.0, -12.0))
+        raw = raycast_driving_scan(100 * seed + sid, beams=beams, azimuth_steps=azimuth_steps, elev_deg=(lo, lo + 26.0),
+                                   n_boxes=30, drop=0.08)
+        p = raw.points
+        az = np.arctan2(p[:, 1], p[:, 0])
+        front = np.abs(az) < np.deg2rad(fov_deg)
+        p, az = p[front], az[front]
+        firing = np.round((az + np.pi) / (2 * np.pi) * azimuth_steps).astype(np.int64)
+        mount = np.array([rng.uniform(-0.5, 1.5), rng.uniform(-0.8, 0.8), rng.uniform(-0.2, 0.3)], dtype=np.float32)
+        pts.append(p + mount[None, :])
+        refl.append(raw.reflectance[front])
+        ts.append(1_554_000_000_000_000 + 37 * sid + 55 * firing)
+        ids.append(np.full(p.shape[0], sid, dtype=np.int64))
+    points = np.concatenate(pts).astype(np.float32)
+    out = {"points": points, "reflectance": np.concatenate(refl).astype(np.float32),
+           "timestamp": np.concatenate(ts).astype(np.int64), "lidar_id": np.concatenate(ids)}
+    out["label"] = rng.integers(0, 38, size=points.shape[0]).astype(np.int64)
+    if shuffle:
+        perm = rng.permutation(points.shape[0])
+        out = {k: np.ascontiguousarray(v[perm]) for k, v in out.items()}
+    return out
+
+
 def group_curves_host(points: torch.Tensor, beam_ids: torch.Tensor, curve_thresh: float = 0.08):
     """Host-side statement of the curve split used only by this generator: stable sort by
     beam, split where the beam changes or |p[i+1]-p[i]| (f64) > thresh*sqrt(|p[i+1].xy|).

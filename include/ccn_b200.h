@@ -404,6 +404,27 @@ int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t 
 int ccn_get_curves(const float* points, int64_t ldp, const int64_t* beam, int64_t n, int32_t n_beams, float curve_thresh,
                    int32_t* scratch, int64_t* reorder, int64_t* inv_reorder, float* sorted_points, int64_t* curve_idxs,
                    int32_t* counts_out, ccn_stream_t stream);
+/* Curve grouping of an A2D2 frame - SemA2D2._get_curves / _partition_curves_at_discontinuities
+ * (src/data/audi_dataset.py:156-243).  A2D2 carries no beam ids: per lidar (lidar_id, 5 sensors) the reference builds a kNN
+ * graph (torch_cluster.knn, k = KNN[id] <= 4, self included), keeps the edges shorter than CURVE_THRESHES[id] * sqrt(|p.xy|)
+ * of the query, takes connected components (scipy: numbered by their lowest point), orders the sensor's points by
+ * (component, timestamp) (np.lexsort, ties in file order), cuts again where the component changes or where the f64 edges to
+ * the previous AND the second-previous point both exceed 0.9 * CURVE_THRESHES[id] * sqrt(|p.xy|), offsets the ids of a sensor
+ * by the sum of the LARGEST ids of the sensors before (so neighbouring sensors share one id - upstream behaviour, kept) and
+ * compacts the ids (np.unique).  points (n, >= 3) f32 rows of stride ldp, lidar_id / timestamp int64 (n); knn_host /
+ * thresh_host: n_sensors HOST values; scratch: ccn_a2d2_scratch_bytes(n, n_sensors) bytes, 16-byte aligned.  Outputs in the
+ * final order (sensor-major): reorder (n) = index into the input, sorted_points (n, 3), curve_idxs (n); counts_out int32
+ * [2] = {number of curves, error flags (1: lidar id outside [0, n_sensors); 2: a timestamp more than 2^30 ticks after the
+ * frame's first)}.  n < 2^17 points per frame. */
+int64_t ccn_a2d2_scratch_bytes(int64_t n, int32_t n_sensors);
+int ccn_a2d2_curves(const float* points, int64_t ldp, const int64_t* lidar_id, const int64_t* timestamp, int64_t n,
+                    int32_t n_sensors, const int32_t* knn_host, const float* thresh_host, void* scratch, int64_t* reorder,
+                    float* sorted_points, int64_t* curve_idxs, int32_t* counts_out, ccn_stream_t stream);
+/* the rest of SemA2D2.get (audi_dataset.py:131-141): x_out[r] = reflectance[reorder[r]] / refl_div (255), y_out[r] =
+ * labels[reorder[r]] (labels null: zeros; y_out null: skipped).  Positions go through ccn_augment_points (/ 30, then the
+ * y flip and the x, y scale of _training_augmentation, :81-90). */
+int ccn_a2d2_finish(const float* reflectance, const int64_t* labels, const int64_t* reorder, int64_t n, float refl_div,
+                    float* x_out, int64_t* y_out, ccn_stream_t stream);
 
 /* Scan ingest - SemNuScenes.get / _load_frame / _get_curves / _training_augmentation
  * (src/data/nuscenes_dataset.py:42-149) and SemKITTI.get / ... (src/data/kitti_dataset.py:40-152) as ONE call per sweep:

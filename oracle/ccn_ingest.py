@@ -134,3 +134,106 @@ def polarmix(d1, d2, mix, instance_classes):
     dense = torch.unique(torch.from_numpy(rows[:, 4].copy()), return_inverse=True)[1]
     return {"pos": torch.from_numpy(rows[:, :3].copy()), "x": torch.from_numpy(rows[:, 3:4].copy()),
             "y": torch.from_numpy(labs).long(), "curve_idxs": dense.long()}
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# A2D2 (src/data/audi_dataset.py): no beam ids - curves from a kNN graph per lidar.  Pinned by tests/golden/a2d2.pt,
+# generated from SemA2D2.get / _get_curves / _partition_curves_at_discontinuities / _training_augmentation's own source text
+# (oracle/make_golden.py, mode `a2d2`; torch_cluster.knn is absent there and stands as exact (d2, index) kNN: unpinned).
+# ----------------------------------------------------------------------------------------------------------------------
+A2D2_CURVE_THRESHES = (0.1, 0.17, 0.1, 0.12, 0.1)    # audi_dataset.py:19
+A2D2_KNN = (4, 4, 4, 3, 4)                            # audi_dataset.py:20
+A2D2_POS_NORMALIZE = 30.0                            # audi_dataset.py:21
+
+
+def _components_by_lowest_point(n: int, src, dst) -> np.ndarray:
+    """Weakly connected components, numbered in the order of their lowest point (what scipy's connected_components returns:
+    it opens a new label at the first unlabelled node while walking 0..n-1).  Plain union-find."""
+    parent = list(range(n))
+
+    def find(a):
+        while parent[a] != a:
+            parent[a] = parent[parent[a]]
+            a = parent[a]
+        return a
+
+    for a, b in zip(src, dst):
+        ra, rb = find(a), find(b)
+        if ra != rb:
+            parent[max(ra, rb)] = min(ra, rb)
+    roots = [find(a) for a in range(n)]
+    label, out = {}, np.empty(n, dtype=np.int64)
+    for a in range(n):                      # a root is the lowest point of its component, so labels appear in that order
+        if roots[a] not in label:
+            label[roots[a]] = len(label)
+        out[a] = label[roots[a]]
+    return out
+
+
+def a2d2_partition(points: torch.Tensor, comp: torch.Tensor, thresh: float) -> torch.Tensor:
+    """audi_dataset.py:214-237: a cut where the component changes, or where the f64 edges to the previous AND to the
+    second-previous point (10 where there is none) both exceed thresh * sqrt(|p.xy|) (f32); ids = running count - 1."""
+    n = points.shape[0]
+    pd = points.double()
+    e1 = torch.full((n,), 10.0, dtype=torch.float64)
+    e2 = torch.full((n,), 10.0, dtype=torch.float64)
+    e1[1:] = torch.linalg.norm(pd[1:] - pd[:-1], dim=-1)
+    e2[2:] = torch.linalg.norm(pd[2:] - pd[:-2], dim=-1)
+    lim = thresh * torch.sqrt(torch.linalg.norm(points[:, :2], dim=-1))
+    cut = (e1 > lim) & (e2 > lim)
+    cut[1:] |= comp[1:] != comp[:-1]
+    return torch.cumsum(cut, dim=0) - 1
+
+
+def a2d2_get_curves(points: np.ndarray, lidar_id: np.ndarray, timestamp: np.ndarray, knn=A2D2_KNN,
+                    curve_threshes=A2D2_CURVE_THRESHES):
+    """audi_dataset.py:156-211 -> (reorder (n) into the input, curve_idxs (n) int64, sorted points (n,3)); see the header of
+    csrc/a2d2_curves.cu for the steps.  Quirks kept: a sensor's ids are offset by the sum of the LARGEST ids (not the
+    counts) of the sensors before it (:197,205), so its first curve takes the id of the previous sensor's last; the final
+    np.unique compaction."""
+    from . import tp_ops as tp
+    order_all, ids_all, total = [], [], 0
+    for sid in np.unique(lidar_id.astype(np.int64)):
+        sel = np.flatnonzero(lidar_id == sid)
+        p = torch.from_numpy(points[sel])
+        m = p.shape[0]
+        k = min(int(knn[sid]), m)
+        nbr = tp.knn_points(p[None], p[None], torch.tensor([m]), torch.tensor([m]), k)[1][0]            # (m, k), self included
+        q = torch.arange(m)[:, None].expand(-1, k)
+        elen = torch.norm(p[q.reshape(-1)] - p[nbr.reshape(-1)], dim=1)
+        lim = curve_threshes[sid] * torch.sqrt(torch.linalg.norm(p[:, :2], dim=-1))
+        keep = elen < lim[q.reshape(-1)]
+        comp = _components_by_lowest_point(m, q.reshape(-1)[keep].tolist(), nbr.reshape(-1)[keep].tolist())
+        order = np.lexsort((timestamp[sel], comp))                     # by component, then time, ties in file order
+        ids = torch.from_numpy(comp[order])
+        if m > 1:
+            ids = a2d2_partition(p[order], ids, 0.9 * curve_threshes[sid])
+        order_all.append(sel[order])
+        ids_all.append(ids.numpy() + total)
+        total += int(ids.max())
+    reorder = np.concatenate(order_all)
+    cid = np.unique(np.concatenate(ids_all), return_inverse=True)[1]
+    return reorder, torch.from_numpy(cid.astype(np.int64)), points[reorder]
+
+
+def a2d2_draw_augmentation(rng=np.random):
+    """The draws of SemA2D2._training_augmentation in its call order (audi_dataset.py:81-90)."""
+    return {"flip_y": int(rng.choice(2, 1)[0]), "scale": float(rng.uniform(0.95, 1.05))}
+
+
+def a2d2_ingest_frame(frame: dict, aug=None):
+    """SemA2D2.get (audi_dataset.py:120-141) after _load_frame: curves, positions / 30, reflectance / 255, the optional
+    y flip and x, y scale -> dict(pos, x, reorder, curve_idxs)."""
+    reorder, cid, pts = a2d2_get_curves(frame["points"], frame["lidar_id"], frame["timestamp"])
+    pos = torch.from_numpy(pts.copy())
+    pos /= A2D2_POS_NORMALIZE
+    x = torch.from_numpy(frame["reflectance"][reorder]).view(-1, 1) / 255
+    if aug is not None:
+        xyz = pos.numpy()
+        if aug["flip_y"] == 1:
+            xyz[:, 1] = -xyz[:, 1]
+        sc = np.float32(aug["scale"])
+        xyz[:, 0] = sc * xyz[:, 0]
+        xyz[:, 1] = sc * xyz[:, 1]
+        pos = torch.from_numpy(xyz).float()
+    return {"pos": pos.float(), "x": x, "reorder": torch.from_numpy(reorder), "curve_idxs": cid}

@@ -378,13 +378,15 @@ def make_helpers(rpo):
     return out
 
 
-def _reference_class(relpath: str, class_name: str, names):
+def _reference_class(relpath: str, class_name: str, names, extra=None):
     """A stand-in class whose methods are compiled from the reference's own source text (the module itself cannot be
-    imported here: nuscenes-devkit / cv2 / mitsuba / torch_geometric.data are absent)."""
+    imported here: nuscenes-devkit / cv2 / mitsuba / torch_geometric.data are absent).  extra: further module-level names
+    the methods use."""
     import numpy as np
     src = open(os.path.join(REF, relpath)).read()
     tree = ast.parse(src)
     ns = {"torch": torch, "np": np, "os": os, "Data": lambda **kw: kw}
+    ns.update(extra or {})
     body = {}
     for node in ast.walk(tree):
         if isinstance(node, ast.ClassDef) and node.name == class_name:
@@ -392,13 +394,75 @@ def _reference_class(relpath: str, class_name: str, names):
                 if isinstance(item, ast.FunctionDef) and item.name in names:
                     code = textwrap.dedent(ast.get_source_segment(src, item))
                     exec(compile(code, "%s:%s" % (relpath, item.name), "exec"), ns)
-                    body[item.name] = ns[item.name]
+                    static = any(isinstance(d, ast.Name) and d.id == "staticmethod" for d in item.decorator_list)
+                    body[item.name] = staticmethod(ns[item.name]) if static else ns[item.name]
                 elif isinstance(item, ast.Assign) and isinstance(item.targets[0], ast.Name):
                     body[item.targets[0].id] = eval(compile(ast.Expression(item.value), relpath, "eval"), ns)
     missing = set(names) - set(body)
     if missing:
         raise RuntimeError("not found in %s: %s" % (relpath, sorted(missing)))
     return type(class_name + "FromSource", (), body)
+
+
+def a2d2_frames():
+    """The A2D2-shaped fixtures: a full synthetic frame, a small one, and the small one with sensor 2 absent and a single
+    point of sensor 4 (np.unique over the ids that occur, audi_dataset.py:162; the `> 1` guard of :195)."""
+    import numpy as np
+    from curvecloudnet_b200.synthetic import a2d2_frame
+    full = a2d2_frame(1)
+    small = a2d2_frame(2, azimuth_steps=150)
+    keep = small["lidar_id"] != 2
+    one = np.flatnonzero(small["lidar_id"] == 4)[1:]
+    keep[one] = False
+    ragged = {k: np.ascontiguousarray(v[keep]) for k, v in small.items()}
+    return {"full": full, "small": small, "ragged": ragged}
+
+
+def make_a2d2():
+    """SemA2D2.get / _get_curves / _partition_curves_at_discontinuities / _training_augmentation (src/data/audi_dataset.py)
+    compiled from source; _load_frame (npz + label image through cv2) is replaced by the synthetic frame.  torch_cluster.knn
+    and torch_geometric.utils.to_scipy_sparse_matrix are absent: knn = the oracle's exact (d2, index) kNN, the sparse matrix
+    is built with scipy directly; scipy's connected_components is the real one."""
+    import numpy as np
+    import scipy.sparse as sp
+    import scipy.sparse.csgraph  # noqa: F401
+    sys.path.insert(0, ROOT)
+    from oracle import tp_ops as tp
+
+    def knn(x, y, k, batch_x=None, batch_y=None):
+        lx, ly = torch.tensor([x.shape[0]]), torch.tensor([y.shape[0]])
+        kk = min(k, x.shape[0])
+        idx = tp.knn_points(y[None].float(), x[None].float(), ly, lx, kk)[1][0]          # (ny, kk), ascending (d2, index)
+        rows = torch.arange(y.shape[0])[:, None].expand(-1, kk)
+        return torch.stack([rows.reshape(-1), idx.reshape(-1)], dim=0)
+
+    def to_scipy_sparse_matrix(edge_index, num_nodes=None):
+        r, c = edge_index[0].numpy(), edge_index[1].numpy()
+        return sp.coo_matrix((np.ones(r.shape[0]), (r, c)), shape=(num_nodes, num_nodes))
+
+    cls = _reference_class("src/data/audi_dataset.py", "SemA2D2",
+                           ["get", "_get_curves", "_partition_curves_at_discontinuities", "_training_augmentation"],
+                           extra={"knn": knn, "to_scipy_sparse_matrix": to_scipy_sparse_matrix, "sp": sp})
+    out = {}
+    for tag, frame in a2d2_frames().items():
+        n = frame["points"].shape[0]
+        rec = {k: torch.from_numpy(v) for k, v in frame.items()}
+        base = int(frame["timestamp"].min())              # the fixture stores int32: timestamps as offsets from the first
+        rec["timestamp"] = rec["timestamp"] - base
+        rec["timestamp_base"] = base
+        ds = cls()
+        ds.split = "val"
+        ds._load_frame = lambda idx, f=frame, m=n: ({k: v.copy() for k, v in f.items()}, np.arange(m))
+        d = ds.get(0)                                   # labels = arange(n): the permutation the reference applied
+        rec["val"] = {"pos": d["pos"], "x": d["x"], "reorder": d["y"], "curve_idxs": d["curve_idxs"]}
+        ds.split = "train"
+        np.random.seed(11)
+        d = ds.get(0)
+        assert torch.equal(d["curve_idxs"], rec["val"]["curve_idxs"])
+        rec["train"] = {"pos": d["pos"], "seed": 11}
+        out[tag] = rec
+        print("a2d2", tag, n, "points", int(d["curve_idxs"].max()) + 1, "curves")
+    return out
 
 
 def make_ingest():
@@ -565,6 +629,11 @@ def main():
         sys.path.insert(0, ROOT)
         torch.save(_compact(make_ingest()), os.path.join(OUT, "ingest.pt"))
         print("ingest.pt", os.path.getsize(os.path.join(OUT, "ingest.pt")) // 1024, "KiB")
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "a2d2":       # only the A2D2 curve-builder fixture
+        sys.path.insert(0, ROOT)
+        torch.save(_compact(make_a2d2()), os.path.join(OUT, "a2d2.pt"))
+        print("a2d2.pt", os.path.getsize(os.path.join(OUT, "a2d2.pt")) // 1024, "KiB")
         return
     if len(sys.argv) > 1 and sys.argv[1] == "polarmix":   # only the PolarMix fixture (the real data_utils.polarmix)
         sys.path.insert(0, ROOT)

@@ -291,3 +291,103 @@ def test_polarmix_degenerate_cases():
         assert got.pos.shape[0] == want["pos"].shape[0]
         assert torch.equal(got.y.cpu(), want["y"]) and torch.equal(got.curve_idxs.cpu(), want["curve_idxs"])
         assert torch.equal(got.x.cpu(), want["x"]) and _ulp_close(got.pos.cpu(), want["pos"])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# A2D2 (audi_dataset.py:120-243): curves from a kNN graph per lidar.  tests/golden/a2d2.pt = SemA2D2's own get /
+# _get_curves / _partition_curves_at_discontinuities / _training_augmentation on synthetic frames (CPU pin of the
+# oracle: tests/test_oracle_golden.py::test_a2d2_curve_builder)
+# ---------------------------------------------------------------------------------------------------------------
+def _a2d2_frame(g):
+    return {"points": g["points"].numpy(), "reflectance": g["reflectance"].numpy(), "lidar_id": g["lidar_id"].numpy(),
+            "timestamp": g["timestamp"].numpy() + int(g["timestamp_base"])}
+
+
+def test_a2d2_augmentation_draws_replay_the_reference_order():
+    from curvecloudnet_b200.ingest import A2D2Augmentation
+    from oracle import ccn_ingest as I
+    np.random.seed(5)
+    a = A2D2Augmentation.draw()
+    np.random.seed(5)
+    b = I.a2d2_draw_augmentation()
+    assert (a.flip_y, a.scale) == (b["flip_y"], b["scale"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["full", "small", "ragged"])
+def test_a2d2_ingest_matches_reference_golden(tag):
+    """ccn_a2d2_curves + ccn_a2d2_finish + ccn_augment_points against the reference's own `get()`: the permutation, the
+    curve ids, reflectance and positions bit-exact (validation and training split; no rotation in this augmentation, so
+    nothing is left to a BLAS summation order)."""
+    from curvecloudnet_b200.ingest import A2D2Augmentation, ingest_a2d2_frame
+    g = load("a2d2.pt")[tag]
+    frame = _a2d2_frame(g)
+    n = frame["points"].shape[0]
+    d = ingest_a2d2_frame(frame, labels=np.arange(n, dtype=np.int64))
+    assert torch.equal(d.reorder.cpu(), g["val"]["reorder"]) and torch.equal(d.y.cpu(), g["val"]["reorder"])
+    assert torch.equal(d.curve_idxs.cpu(), g["val"]["curve_idxs"])
+    assert int(d.counts[0]) == int(g["val"]["curve_idxs"].max()) + 1 and int(d.counts[1]) == 0
+    assert torch.equal(d.x.cpu(), g["val"]["x"]) and torch.equal(d.pos.cpu(), g["val"]["pos"])
+    np.random.seed(int(g["train"]["seed"]))
+    t = ingest_a2d2_frame(frame, augmentation=A2D2Augmentation.draw())
+    assert torch.equal(t.pos.cpu(), g["train"]["pos"])
+    assert torch.equal(t.curve_idxs, d.curve_idxs)
+
+
+@pytest.mark.gpu
+def test_a2d2_ingest_fresh_frames_match_oracle_and_errors():
+    """Frames the fixture does not hold (other seeds, points in acquisition order, one sensor only, duplicate points, a
+    handful of points) against the CPU oracle; a lidar id out of range is reported."""
+    from curvecloudnet_b200.ingest import ingest_a2d2_frame
+    from curvecloudnet_b200.synthetic import a2d2_frame
+    from oracle import ccn_ingest as I
+    frames = [a2d2_frame(7, azimuth_steps=400), a2d2_frame(8, azimuth_steps=300, shuffle=False)]
+    one = a2d2_frame(9, azimuth_steps=200)
+    keep = one["lidar_id"] == 3
+    frames.append({k: np.ascontiguousarray(v[keep]) for k, v in one.items()})
+    dup = a2d2_frame(10, azimuth_steps=120)
+    dup["points"][5:40] = dup["points"][4]                       # coincident points: distance ties in the kNN graph
+    dup["lidar_id"][5:40] = dup["lidar_id"][4]
+    frames.append(dup)
+    frames.append({k: np.ascontiguousarray(v[:3]) for k, v in one.items()})
+    for f in frames:
+        want = I.a2d2_ingest_frame(f)
+        got = ingest_a2d2_frame(f)
+        assert torch.equal(got.reorder.cpu(), want["reorder"]), f["points"].shape
+        assert torch.equal(got.curve_idxs.cpu(), want["curve_idxs"])
+        assert torch.equal(got.pos.cpu(), want["pos"]) and torch.equal(got.x.cpu(), want["x"])
+    bad = {k: v.copy() for k, v in frames[0].items()}
+    bad["lidar_id"][3] = 9
+    with pytest.raises(ValueError, match="lidar id"):
+        ingest_a2d2_frame(bad)
+    empty = {k: v[:0] for k, v in frames[0].items()}
+    e = ingest_a2d2_frame(empty)
+    assert e.pos.shape == (0, 3) and e.curve_idxs.numel() == 0 and int(e.counts[0]) == 0
+
+
+@pytest.mark.gpu
+def test_a2d2_frame_feeds_the_model():
+    """An ingested A2D2-shaped frame runs through the A2D2 step list (configs 'a2d2') and matches the oracle model fed with
+    the oracle's ingest of the same frame."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.ingest import ingest_a2d2_frame
+    from curvecloudnet_b200.model import Batch, ModelBase
+    from curvecloudnet_b200.synthetic import ScanBatch, a2d2_frame, randomize_model_
+    from golden_utils import rel_err
+    from oracle import ccn_ingest as I
+    from oracle.ccn_model import ModelBase as OracleModel
+    f = a2d2_frame(12, azimuth_steps=250)
+    want_in = I.a2d2_ingest_frame(f)
+    n = want_in["pos"].shape[0]
+    ref = randomize_model_(build_model(OracleModel, "a2d2"), 1234).eval()
+    torch.manual_seed(3)
+    with torch.no_grad():
+        want = ref(ScanBatch(want_in["x"], want_in["pos"], torch.zeros(n, dtype=torch.int64), want_in["curve_idxs"], None, None))
+    d = ingest_a2d2_frame(f)
+    model = build_model(ModelBase, "a2d2", precision="bf16x3")
+    model.load_state_dict(ref.state_dict(), strict=True)
+    model = model.cuda().eval()
+    torch.manual_seed(3)
+    with torch.no_grad():
+        got = model(Batch.from_data_list([d]))
+    assert rel_err(got.cpu(), want) <= 1e-4

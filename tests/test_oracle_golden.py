@@ -185,3 +185,22 @@ def test_unused_grouping_helpers():
         vals = g["first_k_v1"] if tag.startswith("v1") else g["first_k_v2"]
         grouped, mask = po.group_first_k_values(vals, g["first_k_ids"], rec["k"])
         assert torch.equal(mask, rec["mask"]) and torch.equal(grouped, rec["grouped"]), tag
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# A2D2 curve builder (audi_dataset.py:120-243) against SemA2D2's own methods (a2d2.pt)
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["full", "small", "ragged"])
+def test_a2d2_curve_builder(tag):
+    import numpy as np
+    from oracle import ccn_ingest as I
+    g = load("a2d2.pt")[tag]
+    frame = {"points": g["points"].numpy(), "reflectance": g["reflectance"].numpy(), "lidar_id": g["lidar_id"].numpy(),
+             "timestamp": g["timestamp"].numpy() + int(g["timestamp_base"])}
+    got = I.a2d2_ingest_frame(frame)
+    assert torch.equal(got["reorder"], g["val"]["reorder"])
+    assert torch.equal(got["curve_idxs"], g["val"]["curve_idxs"])
+    assert torch.equal(got["pos"], g["val"]["pos"]) and torch.equal(got["x"], g["val"]["x"])
+    np.random.seed(int(g["train"]["seed"]))
+    aug = I.a2d2_draw_augmentation()
+    assert torch.equal(I.a2d2_ingest_frame(frame, aug)["pos"], g["train"]["pos"])
