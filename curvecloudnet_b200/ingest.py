@@ -282,6 +282,8 @@ def ingest_a2d2_frame(frame: dict, labels=None, augmentation: Optional[A2D2Augme
     x = torch.empty((n, 1), dtype=torch.float32, device=ptd.device)
     y = torch.empty((n,), dtype=torch.int64, device=ptd.device)
     native.call("ccn_a2d2_finish", refd, labd if labd is not None else 0, reorder, n, 255.0, x, y)
+    if n == 0:
+        return Batch(x=x, pos=sorted_pts, y=y, curve_idxs=cid, reorder=reorder, counts=counts)
     pos = augment_points(sorted_pts, None, A2D2_POS_NORMALIZE)                      # points /= 30 (:137)
     if augmentation is not None:                                                    # then flip / scale (:140-141)
         a = ScanAugmentation(1.0, 0.0, 2 if augmentation.flip_y == 1 else 0, augmentation.scale, (0.0, 0.0, 0.0))

@@ -174,6 +174,9 @@ def a2d2_curves(points: torch.Tensor, lidar_id: torch.Tensor, timestamp: torch.T
     sorted_pts = _empty((n, 3), torch.float32, points)
     cid = _empty((n,), torch.int64, points)
     counts = _empty((2,), torch.int32, points)
+    if n == 0:
+        counts.zero_()
+        return reorder, cid, sorted_pts, counts
     k_host = (ctypes.c_int32 * ns)(*[int(k) for k in knn])
     t_host = (ctypes.c_float * ns)(*[float(t) for t in curve_threshes])
     call("ccn_a2d2_curves", points, ldp, lidar_id, timestamp, n, ns, ctypes.addressof(k_host), ctypes.addressof(t_host),
