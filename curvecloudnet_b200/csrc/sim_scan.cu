@@ -423,3 +423,161 @@ extern "C" int ccn_sim_curvature(const double* points, const int32_t* curve_idx,
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// CurveClouds.compute_intersections (scanning_simulator/utils/curve_cloud.py:114-166) + line_seg_dists (:285-331), ONE curve
+// cloud (the reference's second scatter_min only broadcasts for B = 1, which is how generate_shapenet.py calls it):
+// every pair of polyline edges (i, j): mua_ij = parameter on edge i of the point closest to the LINE through edge j (0 for
+// parallel pairs, clipped to [0, 1]); dist(i, j) = |closest_ij - closest_ji|; pairs with an edge that joins two curves or
+// with both edges on one curve count as 1.0 (= 100 * thresh).  min over the rows of a curve, then over the columns of a
+// curve (lowest index among equals) -> curve pairs closer than thresh -> the two edges -> the nearer end point of each.
+// All in f64 like upstream, products and sums rounded separately.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+__device__ __forceinline__ double dot3_rn(double ax, double ay, double az, double bx, double by, double bz) {
+    return __dadd_rn(__dadd_rn(__dmul_rn(ax, bx), __dmul_rn(ay, by)), __dmul_rn(az, bz));
+}
+
+// mua of edge a against the line of edge b, and the closest point on a
+__device__ __forceinline__ double seg_mua(const double* __restrict__ p, int a, int b, double* cx, double* cy, double* cz) {
+    const double p1x = p[3 * a], p1y = p[3 * a + 1], p1z = p[3 * a + 2];
+    const double ux = __dsub_rn(p[3 * a + 3], p1x), uy = __dsub_rn(p[3 * a + 4], p1y), uz = __dsub_rn(p[3 * a + 5], p1z);
+    const double p3x = p[3 * b], p3y = p[3 * b + 1], p3z = p[3 * b + 2];
+    const double vx = __dsub_rn(p[3 * b + 3], p3x), vy = __dsub_rn(p[3 * b + 4], p3y), vz = __dsub_rn(p[3 * b + 5], p3z);
+    const double wx = __dsub_rn(p1x, p3x), wy = __dsub_rn(p1y, p3y), wz = __dsub_rn(p1z, p3z);
+    const double d1343 = dot3_rn(wx, wy, wz, vx, vy, vz), d4321 = dot3_rn(ux, uy, uz, vx, vy, vz);
+    const double d1321 = dot3_rn(wx, wy, wz, ux, uy, uz), d4343 = dot3_rn(vx, vy, vz, vx, vy, vz);
+    const double d2121 = dot3_rn(ux, uy, uz, ux, uy, uz);
+    const double denom = __dsub_rn(__dmul_rn(d2121, d4343), __dmul_rn(d4321, d4321));
+    const double num = __dsub_rn(__dmul_rn(d1343, d4321), __dmul_rn(d1321, d4343));
+    double mua = denom < 1e-8 ? 0.0 : __ddiv_rn(num, denom);
+    mua = fmin(fmax(mua, 0.0), 1.0);
+    *cx = __dadd_rn(p1x, __dmul_rn(mua, ux));
+    *cy = __dadd_rn(p1y, __dmul_rn(mua, uy));
+    *cz = __dadd_rn(p1z, __dmul_rn(mua, uz));
+    return mua;
+}
+
+__device__ __forceinline__ double seg_pair_dist(const double* __restrict__ p, const int32_t* __restrict__ cidx, int i, int j,
+                                                double masked) {
+    if (cidx[i + 1] != cidx[i] || cidx[j + 1] != cidx[j] || cidx[i] == cidx[j]) return masked;
+    double ax, ay, az, bx, by, bz;
+    seg_mua(p, i, j, &ax, &ay, &az);
+    seg_mua(p, j, i, &bx, &by, &bz);
+    const double dx = __dsub_rn(ax, bx), dy = __dsub_rn(ay, by), dz = __dsub_rn(az, bz);
+    return sqrt(__dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz)));
+}
+
+// cptr[g] = first point of curve g (curve ids are 0, 1, 2, ... along the points); cptr[n_curves] = n
+__global__ void sim_curve_ptr_kernel(const int32_t* __restrict__ cidx, int n, int n_curves, int32_t* __restrict__ cptr) {
+    ccn_pdl_wait();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        if (i == 0 || cidx[i] != cidx[i - 1]) cptr[cidx[i]] = i;
+    if (blockIdx.x == 0 && threadIdx.x == 0) cptr[n_curves] = n;
+}
+
+// (g, j): min over the edges i of curve g of dist(i, j), lowest i among equals (scatter_min over the rows, :145)
+__global__ void sim_isect_rows_kernel(const double* __restrict__ p, const int32_t* __restrict__ cidx,
+                                      const int32_t* __restrict__ cptr, int n_edges, int n_groups, double masked,
+                                      double* __restrict__ min1, int32_t* __restrict__ arg1) {
+    ccn_pdl_wait();
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (t >= (int64_t)n_groups * n_edges) return;
+    const int g = (int)(t / n_edges), j = (int)(t - (int64_t)g * n_edges);
+    const int lo = cptr[g], hi = min(cptr[g + 1], n_edges);          // edges of curve g = its points that have a successor
+    double best = 0.0;
+    int at = -1;
+    for (int i = lo; i < hi; ++i) {
+        const double d = seg_pair_dist(p, cidx, i, j, masked);
+        if (at < 0 || d < best) { best = d; at = i; }
+    }
+    min1[t] = best;
+    arg1[t] = at;
+}
+
+// (g, h): min over the edges j of curve h of min1[g][j], lowest j among equals (scatter_min over the columns, :146);
+// flag = closer than thresh
+__global__ void sim_isect_cols_kernel(const double* __restrict__ min1, const int32_t* __restrict__ cptr, int n_edges,
+                                      int n_groups, double thresh, int32_t* __restrict__ arg2, int32_t* __restrict__ flag,
+                                      int32_t* __restrict__ slot) {
+    ccn_pdl_wait();
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_groups * n_groups) return;
+    const int g = t / n_groups, h = t - g * n_groups;
+    const int lo = cptr[h], hi = min(cptr[h + 1], n_edges);
+    const bool g_has_edges = cptr[g] < min(cptr[g + 1], n_edges);    // a last curve of one point owns no edge: not a group upstream
+    double best = 0.0;
+    int at = -1;
+    for (int j = lo; j < hi; ++j) {
+        const double d = min1[(int64_t)g * n_edges + j];
+        if (at < 0 || d < best) { best = d; at = j; }
+    }
+    arg2[t] = at;
+    const int f = (g_has_edges && at >= 0 && best < thresh) ? 1 : 0;
+    flag[t] = f;
+    slot[t] = f;
+}
+
+// curve pair k (row-major over (g, h)): the two edges, each moved to its end point when the closest approach lies in the
+// edge's second half (:153-160; the second look-up uses the already shifted first index, as upstream)
+__global__ void sim_isect_fill_kernel(const double* __restrict__ p, const int32_t* __restrict__ arg1,
+                                      const int32_t* __restrict__ arg2, const int32_t* __restrict__ flag,
+                                      const int32_t* __restrict__ slot, int n_edges, int n_groups, int64_t n_out,
+                                      int64_t* __restrict__ pairs, int32_t* __restrict__ err) {
+    ccn_pdl_wait();
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_groups * n_groups || !flag[t]) return;
+    const int g = t / n_groups;
+    int e2 = arg2[t];
+    int e1 = arg1[(int64_t)g * n_edges + e2];
+    double cx, cy, cz;
+    if (seg_mua(p, e1, e2, &cx, &cy, &cz) > 0.5) e1 += 1;
+    if (e1 >= n_edges) { atomicOr(err, 1); e1 = n_edges - 1; }      // upstream indexes past the matrix here and raises
+    if (seg_mua(p, e2, e1, &cx, &cy, &cz) > 0.5) e2 += 1;
+    const int k = slot[t];
+    pairs[k] = e1;
+    pairs[n_out + k] = e2;
+}
+
+}  // namespace
+
+extern "C" int ccn_sim_intersections_count(const double* points, const int32_t* curve_idx, int32_t n, int32_t n_curves,
+                                           double thresh, int32_t* cptr_scratch, double* min1_scratch, int32_t* arg1_scratch,
+                                           int32_t* arg2_scratch, int32_t* flag_scratch, int32_t* slot_scan,
+                                           ccn_stream_t stream) {
+    // scratch: cptr n_curves + 1 ints; min1 / arg1 n_curves * (n - 1); arg2 / flag n_curves^2; slot_scan n_curves^2 + 1 ints:
+    // on return the exclusive scan of the pair flags, the number of intersections in its last entry
+    CCN_REQUIRE(n >= 2 && n_curves >= 1 && points && curve_idx && cptr_scratch && min1_scratch && arg1_scratch && arg2_scratch &&
+                flag_scratch && slot_scan);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int n_edges = n - 1;
+    ccn_launch(sim_curve_ptr_kernel, dim3(ccn_grid(n, 256, 148 * 4)), dim3(256), 0, st, curve_idx, (int)n, (int)n_curves, cptr_scratch);
+    CCN_CHECK_LAUNCH();
+    const int64_t work = (int64_t)n_curves * n_edges;
+    ccn_launch(sim_isect_rows_kernel, dim3(ccn_blocks_exact(work, 128)), dim3(128), 0, st, points, curve_idx,
+               (const int32_t*)cptr_scratch, n_edges, (int)n_curves, 100.0 * thresh, min1_scratch, arg1_scratch);
+    CCN_CHECK_LAUNCH();
+    ccn_launch(sim_isect_cols_kernel, dim3(ccn_blocks_exact((int64_t)n_curves * n_curves, 128)), dim3(128), 0, st,
+               (const double*)min1_scratch, (const int32_t*)cptr_scratch, n_edges, (int)n_curves, thresh, arg2_scratch, flag_scratch,
+               slot_scan);
+    CCN_CHECK_LAUNCH();
+    return ccn_excl_scan_i32(slot_scan, (int64_t)n_curves * n_curves, nullptr, stream);
+}
+
+extern "C" int ccn_sim_intersections_fill(const double* points, int32_t n, int32_t n_curves, const int32_t* arg1_scratch,
+                                          const int32_t* arg2_scratch, const int32_t* flag_scratch, const int32_t* slot_scan,
+                                          int64_t n_out, int64_t* pairs_out, int32_t* err_out, ccn_stream_t stream) {
+    // pairs_out (2, n_out) int64: point indices (first row: on the row curve, second: on the column curve), curve pairs in
+    // row-major order; err_out: 1 when a shifted first index left the edge range (upstream raises an IndexError there)
+    CCN_REQUIRE(n >= 2 && n_curves >= 1 && n_out >= 0 && points && arg1_scratch && arg2_scratch && flag_scratch && slot_scan &&
+                err_out);
+    cudaError_t e = cudaMemsetAsync(err_out, 0, sizeof(int32_t), (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+    if (n_out == 0) return CCN_OK;
+    CCN_REQUIRE(pairs_out);
+    ccn_launch(sim_isect_fill_kernel, dim3(ccn_blocks_exact((int64_t)n_curves * n_curves, 128)), dim3(128), 0, (cudaStream_t)stream,
+               points, arg1_scratch, arg2_scratch, flag_scratch, slot_scan, (int)(n - 1), (int)n_curves, n_out, pairs_out, err_out);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}

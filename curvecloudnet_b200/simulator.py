@@ -162,7 +162,8 @@ class CurveClouds:
     """scanning_simulator/utils/curve_cloud.py:8-190: polylines -> 3-D curves (split at jumps), anti-aliased points / normals,
     per-point curvature vectors and position gradients.  Attributes as the reference's: points / normals (B, N, 3) float64,
     uv, point2uvcurve_idxs, point2curve_idxs (B, N) float32, curvature (B, N, 3) float64, gradients (B, N, 3, 3) float64.
-    `with_intersections` (curve_cloud.py:113-165, an O(N^2) segment-pair search nothing downstream stores) is not provided."""
+    `with_intersections` (curve_cloud.py:113-165, an O(N^2) segment-pair search; sampling.py:85 asks for it, nothing downstream
+    stores it): intersections (2, K) int64 and intersection2batch_idxs (K,), one curve cloud at a time like upstream."""
     CURVE_SPLIT_THRESH = 0.01
     INTERSECTION_DIST_THRESH = 0.01
     ANTI_ALIAS_KERNEL = [1, 2, 3, 3, 3, 2, 2]
@@ -171,8 +172,6 @@ class CurveClouds:
                  curvature_knn=10):
         if not points.is_cuda:
             raise native.CcnError("CurveClouds: CUDA tensors only (no CPU path exists)")
-        if with_intersections:
-            raise NotImplementedError("CurveClouds(with_intersections=True) is outside the B200 path (DESIGN.md 3g)")
         B, N = points.shape[0], points.shape[1]
         dev = points.device
         p32 = points.to(torch.float32).contiguous()
@@ -198,6 +197,40 @@ class CurveClouds:
         self.curvature, self.gradients = self.compute_curvature_new()
         self.intersections = None
         self.intersection2batch_idxs = None
+        if with_intersections:
+            self.intersections, self.intersection2batch_idxs = self.compute_intersections()
+
+    def compute_intersections(self):
+        """curve_cloud.py:114-166 -> (pairs (2, K) int64 point indices, batch (K,) int64): for every ordered pair of curves
+        whose polylines come closer than INTERSECTION_DIST_THRESH, the point of each at the closest approach.  One curve cloud
+        only: upstream's second scatter_min (:146) cannot broadcast its index for B > 1 and raises - so does this."""
+        B, N = self.points.shape[0], self.points.shape[1]
+        dev = self.points.device
+        if B != 1:
+            raise RuntimeError("CurveClouds.compute_intersections: one curve cloud at a time (B = %d; the reference's "
+                               "scatter_min over the columns fails to broadcast for B > 1)" % B)
+        if N < 2:
+            return torch.zeros((2, 0), dtype=torch.int64, device=dev), torch.zeros((0,), dtype=torch.int64, device=dev)
+        G = int(self._ncurves[0].item())                                   # host sync
+        E = N - 1
+        pts = self.points[0].contiguous()
+        cidx = self._curve_idx_i32[0].contiguous()
+        i32 = dict(dtype=torch.int32, device=dev)
+        cptr = torch.empty((G + 1,), **i32)
+        min1 = torch.empty((G, E), dtype=torch.float64, device=dev)
+        arg1 = torch.empty((G, E), **i32)
+        arg2 = torch.empty((G * G,), **i32)
+        flag = torch.empty((G * G,), **i32)
+        slot = torch.empty((G * G + 1,), **i32)
+        call("ccn_sim_intersections_count", pts, cidx, N, G, float(self.INTERSECTION_DIST_THRESH), cptr, min1, arg1, arg2, flag, slot)
+        K = int(slot[G * G].item())                                        # host sync
+        pairs = torch.empty((2, K), dtype=torch.int64, device=dev)
+        err = torch.empty((1,), **i32)
+        call("ccn_sim_intersections_fill", pts, N, G, arg1, arg2, flag, slot, K, pairs if K else 0, err)
+        if K and int(err.item()):
+            raise IndexError("CurveClouds.compute_intersections: a closest approach at the far end of the last edge "
+                             "(upstream indexes past its distance matrix here)")
+        return pairs, torch.zeros((K,), dtype=torch.int64, device=dev)
 
     def compute_curvature_new(self):
         B, N = self.points.shape[0], self.points.shape[1]
@@ -217,6 +250,9 @@ class CurveClouds:
     def to(self, device):
         for name in ("points", "normals", "uv", "point2uvcurve_idxs", "point2curve_idxs", "curvature", "gradients"):
             setattr(self, name, getattr(self, name).to(device))
+        if self.intersections is not None:
+            self.intersections = self.intersections.to(device)
+            self.intersection2batch_idxs = self.intersection2batch_idxs.to(device)
 
 
 class SampleMeshes:
@@ -252,6 +288,7 @@ class SampleMeshes:
         success, scans_uv, pts, nrm = self.scan_lines_gen.generate_scan_lines(B, self.npoints, masks, coords, normals)
         if not success:
             return None
-        # the reference passes with_intersections=True (sampling.py:83-84); nothing downstream reads the intersections
-        return CurveClouds(pts, nrm, scans_uv[:, :, :2], scans_uv[:, :, 2], anti_alias=True, with_intersections=False,
+        # the reference passes with_intersections=True (sampling.py:83-84), which only works for ONE mesh (every shipped caller's
+        # case, generate_shapenet.py:69,83); for several meshes - where upstream raises - the intersections are left out
+        return CurveClouds(pts, nrm, scans_uv[:, :, :2], scans_uv[:, :, 2], anti_alias=True, with_intersections=(B == 1),
                            curvature_knn=self.curvature_knn)

@@ -617,6 +617,20 @@ int ccn_sim_anti_alias(const float* vals, const int32_t* curve_idx, int32_t B, i
 int ccn_sim_curvature(const double* points, const int32_t* curve_idx, const int32_t* cstart, const int32_t* cend, int32_t B,
                       int32_t N, int32_t k, double kernel_width, double hinge_reg, double* geo_raw_scratch, double* geo_scratch,
                       double* mean_edge_scratch, double* curvature, double* gradients_or_null, ccn_stream_t stream);
+/* CurveClouds.compute_intersections + line_seg_dists (scanning_simulator/utils/curve_cloud.py:114-166, 285-331) for ONE curve
+ * cloud (upstream's second scatter_min only broadcasts for B = 1 - how generate_shapenet.py calls it): all pairs of polyline
+ * edges in f64, closest approach of edge i to the line of edge j (mua clipped to [0,1], 0 for parallel pairs), pairs across a
+ * curve boundary or on one curve masked to 100 * thresh, min over the rows then over the columns of a curve (lowest index among
+ * equals), curve pairs closer than thresh.  Two calls around one host read-back of the count: _count leaves the exclusive
+ * scan of the pair flags in slot_scan (last entry = number of intersections), _fill writes pairs_out (2, n_out) int64 point
+ * indices, each edge moved to its far end point when its mua > 0.5.  points (n,3) f64; curve_idx (n) int32 0,1,2,.. along the
+ * points; scratch sizes: cptr n_curves+1, min1 / arg1 n_curves*(n-1), arg2 / flag n_curves^2, slot_scan n_curves^2+1. */
+int ccn_sim_intersections_count(const double* points, const int32_t* curve_idx, int32_t n, int32_t n_curves, double thresh,
+                                int32_t* cptr_scratch, double* min1_scratch, int32_t* arg1_scratch, int32_t* arg2_scratch,
+                                int32_t* flag_scratch, int32_t* slot_scan, ccn_stream_t stream);
+int ccn_sim_intersections_fill(const double* points, int32_t n, int32_t n_curves, const int32_t* arg1_scratch,
+                               const int32_t* arg2_scratch, const int32_t* flag_scratch, const int32_t* slot_scan, int64_t n_out,
+                               int64_t* pairs_out, int32_t* err_out, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }

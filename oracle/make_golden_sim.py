@@ -7,7 +7,7 @@ What runs from the reference tree, unmodified: scanning_simulator/utils/scanline
 (CurveClouds: curve split, anti-alias, compute_curvature_new) and curvature_approx.py.  Their third-party imports resolve to
 oracle/shims (torch_scatter is imported but unused without intersections; torch_geometric.nn.knn = torch_cluster.knn restated
 by brute force).  Two documented deviations: `np.int` (removed in numpy >= 1.24, used by the 'parallel' / 'grid' directions,
-scanlines.py:106,122) is set to `int`; CurveClouds is built with with_intersections=False (nothing downstream stores them).
+scanlines.py:106,122) is set to `int`; CurveClouds is built per mesh with with_intersections=True (sampling.py:85).
 The rasterised views the lines run over come from oracle/sim_raster.c (the reference rasteriser is CUDA-only; it is compared
 with ours directly on the GPU box, tests/test_gpu_simulator.py).
 """
@@ -75,11 +75,15 @@ def main():
             # one mesh per CurveClouds, as every caller in the reference does (generate_shapenet.py:69,83: a list of ONE model):
             # with several meshes its batchdense2curvepadded (curve_cloud.py:200-214) offsets the curve ids by the INCLUSIVE
             # running curve count, so the ids of a mesh with fewer curves than its predecessor collide with the predecessor's
+            # with_intersections=True as sampling.py:85 passes it (the result is only ever visualised): it works for one mesh
+            # only - the second scatter_min of curve_cloud.py:146 cannot broadcast its index for B > 1
             ccs = [CurveClouds(pts[b:b + 1], nrm[b:b + 1], uv[b:b + 1, :, :2], uv[b:b + 1, :, 2], anti_alias=True,
-                               with_intersections=False, curvature_knn=10) for b in range(B)]
+                               with_intersections=True, curvature_knn=10) for b in range(B)]
             cat = lambda name: torch.cat([getattr(c, name) for c in ccs], dim=0)
             case.update({"curve_idx": cat("point2curve_idxs").to(torch.int16), "points": cat("points"), "normals": cat("normals"),
-                         "curvature": cat("curvature"), "gradients": cat("gradients") if N <= 500 else None})
+                         "curvature": cat("curvature"), "gradients": cat("gradients") if N <= 500 else None,
+                         "intersections": [c.intersections.to(torch.int16) for c in ccs],
+                         "intersection_batch": [c.intersection2batch_idxs.to(torch.int16) for c in ccs]})
         cases.append(case)
         print(direction, kinds, "res", res, "N", N, "lines", case["lines"],
               "curves %d" % (int(case["curve_idx"].max()) + 1) if clouds else "")

@@ -308,7 +308,14 @@ def scatter_max(src, index, dim=0, out=None, dim_size=None):
 
 
 def scatter_min(src, index, dim=0, out=None, dim_size=None):
-    """torch_scatter.scatter_min -> (values, argmin); ties -> lowest row (fps_ops.py:59)."""
+    """torch_scatter.scatter_min -> (values, argmin); ties -> lowest row (fps_ops.py:59).  dim = 1 of a matrix (the second
+    reduction of curve_cloud.py:146; a 1-D index broadcasts over the rows): the same along the transposed matrix."""
+    if src.dim() == 2 and dim in (1, -1):
+        if index.dim() != 1 or index.shape[0] != src.shape[1]:
+            raise RuntimeError("The expanded size of the tensor (%d) must match the existing size (%d) at non-singleton "
+                               "dimension 1" % (src.shape[1], index.shape[0]))      # torch_scatter.utils.broadcast's failure
+        val, arg = _scatter_ext(src.t().contiguous(), index, dim_size, False)
+        return val.t().contiguous(), arg.t().contiguous()
     return _scatter_ext(src, index, dim_size, False)
 
 
