@@ -581,3 +581,48 @@ extern "C" int ccn_sim_intersections_fill(const double* points, int32_t n, int32
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Label transfer of the dataset generators (scanning_simulator/shapenet_seg/generate_shapenet.py:88-89,
+// kortx/generate_shapenet.py: `argmin(cdist(points.double(), pos.double()), dim=1)`, then `y[closest]`): for every sampled
+// point the nearest labelled point in f64 (lowest index among equals) and its label.  Warp per query, the labelled cloud
+// streamed by the lanes; squared distances (monotone in the distance cdist compares).
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) sim_nearest_kernel(const double* __restrict__ q, int64_t nq, const double* __restrict__ r,
+                                                          int64_t nr, const int64_t* __restrict__ labels,
+                                                          int64_t* __restrict__ idx_out, int64_t* __restrict__ label_out) {
+    ccn_pdl_wait();
+    const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (w >= nq) return;
+    const int lane = ccn_lane();
+    const double x = q[3 * w], y = q[3 * w + 1], z = q[3 * w + 2];
+    double best = 1e300;
+    long long at = 0x7fffffffffffffffll;
+    for (int64_t j = lane; j < nr; j += 32) {
+        const double dx = x - r[3 * j], dy = y - r[3 * j + 1], dz = z - r[3 * j + 2];
+        const double d = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+        if (d < best) { best = d; at = j; }                  // ascending j per lane: the first minimum stays
+    }
+    for (int o = 16; o; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const long long oa = __shfl_xor_sync(0xffffffffu, at, o);
+        if (ob < best || (ob == best && oa < at)) { best = ob; at = oa; }
+    }
+    if (lane == 0) {
+        idx_out[w] = at;
+        if (label_out) label_out[w] = labels[at];
+    }
+}
+}  // namespace
+
+extern "C" int ccn_sim_nearest_label(const double* points, int64_t nq, const double* ref_points, int64_t nr,
+                                     const int64_t* ref_labels, int64_t* idx_out, int64_t* label_out, ccn_stream_t stream) {
+    CCN_REQUIRE(nq >= 0 && nr >= 1 && ref_points && idx_out && (!label_out || ref_labels));
+    if (nq == 0) return CCN_OK;
+    CCN_REQUIRE(points);
+    ccn_launch(sim_nearest_kernel, dim3(ccn_blocks_exact(nq * 32, 256)), dim3(256), 0, (cudaStream_t)stream, points, nq, ref_points, nr,
+               ref_labels, idx_out, label_out);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}

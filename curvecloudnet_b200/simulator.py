@@ -255,6 +255,20 @@ class CurveClouds:
             self.intersection2batch_idxs = self.intersection2batch_idxs.to(device)
 
 
+def transfer_labels(points: torch.Tensor, ref_points: torch.Tensor, ref_labels: torch.Tensor):
+    """generate_shapenet.py:88-89 (`closest = argmin(cdist(points.double(), pos.double()), dim=1); y[closest]`): labels of a
+    sampled curve cloud (N, 3) from the labelled point cloud (M, 3) / (M,) of the same model -> (labels (N,), closest (N,))."""
+    if not points.is_cuda:
+        raise native.CcnError("transfer_labels: CUDA tensors only (no CPU path exists)")
+    q = points.to(torch.float64).contiguous()
+    r = ref_points.to(torch.float64).contiguous()
+    lab = ref_labels.to(torch.int64).contiguous()
+    idx = torch.empty((q.shape[0],), dtype=torch.int64, device=q.device)
+    out = torch.empty((q.shape[0],), dtype=torch.int64, device=q.device)
+    call("ccn_sim_nearest_label", q, q.shape[0], r, r.shape[0], lab, idx, out)
+    return out.to(ref_labels.dtype), idx
+
+
 class SampleMeshes:
     """scanning_simulator/utils/sampling.py:13-85: batches of meshes -> CurveClouds of `npoints` points each."""
 

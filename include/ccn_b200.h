@@ -631,6 +631,11 @@ int ccn_sim_intersections_count(const double* points, const int32_t* curve_idx, 
 int ccn_sim_intersections_fill(const double* points, int32_t n, int32_t n_curves, const int32_t* arg1_scratch,
                                const int32_t* arg2_scratch, const int32_t* flag_scratch, const int32_t* slot_scan, int64_t n_out,
                                int64_t* pairs_out, int32_t* err_out, ccn_stream_t stream);
+/* Label transfer of the dataset generators (scanning_simulator/shapenet_seg/generate_shapenet.py:88-89:
+ * argmin(cdist(points.double(), pos.double()), dim=1), y[closest]): idx_out[i] = nearest of the nr labelled points to sampled
+ * point i in f64 (lowest index among equals), label_out[i] = ref_labels[idx_out[i]] (label_out / ref_labels may be null). */
+int ccn_sim_nearest_label(const double* points, int64_t nq, const double* ref_points, int64_t nr, const int64_t* ref_labels,
+                          int64_t* idx_out, int64_t* label_out, ccn_stream_t stream);
 
 #ifdef __cplusplus
 }
