@@ -368,3 +368,76 @@ extern "C" int ccn_mean_logsoftmax(const float* acc, int64_t lda, int64_t n, int
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Part IoU of the object-segmentation runs (src/run/shapenet_seg.py:88-99): per object, the arg-max over the score columns of
+// the object's category (torch_geometric ShapeNet.seg_classes), the target mapped to its position in that part list, and
+// torchmetrics' jaccard_index(num_classes = #parts, absent_score): per part intersection / union from the confusion matrix,
+// absent_score where the union is empty, mean over the parts.  The reference loops over the objects on the host with one
+// .item() each; here one CTA per object, one launch per batch.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kMaxParts = 16;
+
+__global__ void __launch_bounds__(256) part_iou_kernel(const float* __restrict__ scores, int64_t ld,
+                                                       const int64_t* __restrict__ target, const int32_t* __restrict__ sptr,
+                                                       const int64_t* __restrict__ category, const int32_t* __restrict__ parts,
+                                                       const int32_t* __restrict__ parts_ptr, int n_categories, float absent,
+                                                       float* __restrict__ iou_out, int64_t* __restrict__ pred_out,
+                                                       int32_t* __restrict__ flags) {
+    ccn_pdl_wait();
+    __shared__ int conf[kMaxParts * kMaxParts];
+    __shared__ int plist[kMaxParts];
+    const int b = blockIdx.x;
+    const int64_t cat = category[b];
+    if (cat < 0 || cat >= n_categories) {
+        if (threadIdx.x == 0) { atomicOr(flags, 1); iou_out[b] = 0.f; }
+        return;
+    }
+    const int p0 = parts_ptr[cat], P = parts_ptr[cat + 1] - p0;
+    for (int t = threadIdx.x; t < kMaxParts * kMaxParts; t += blockDim.x) conf[t] = 0;
+    if (threadIdx.x < P) plist[threadIdx.x] = parts[p0 + threadIdx.x];
+    __syncthreads();
+    for (int i = sptr[b] + threadIdx.x; i < sptr[b + 1]; i += blockDim.x) {
+        const float* row = scores + (int64_t)i * ld;
+        int best = 0;
+        float bv = row[plist[0]];
+        for (int k = 1; k < P; ++k) {
+            const float v = row[plist[k]];
+            if (v > bv) { bv = v; best = k; }               // first maximum, like torch.argmax
+        }
+        if (pred_out) pred_out[i] = best;
+        const int64_t y = target[i];
+        int tk = -1;
+        for (int k = 0; k < P; ++k) tk = (plist[k] == y) ? k : tk;
+        if (tk < 0) { atomicOr(flags, 2); continue; }       // a label outside the category's parts (upstream reads a stale map)
+        atomicAdd(&conf[tk * kMaxParts + best], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float sum = 0.f;
+        for (int c = 0; c < P; ++c) {
+            int row = 0, col = 0;
+            for (int k = 0; k < P; ++k) { row += conf[c * kMaxParts + k]; col += conf[k * kMaxParts + c]; }
+            const int inter = conf[c * kMaxParts + c], uni = row + col - inter;
+            sum = __fadd_rn(sum, uni == 0 ? absent : __fdiv_rn((float)inter, (float)uni));
+        }
+        iou_out[b] = __fdiv_rn(sum, (float)P);
+    }
+}
+}  // namespace
+
+extern "C" int ccn_part_iou(const float* scores, int64_t ld, const int64_t* target, const int32_t* sample_ptr,
+                            const int64_t* category, int32_t n_objects, const int32_t* parts, const int32_t* parts_ptr,
+                            int32_t n_categories, int32_t max_parts, float absent_score, float* iou_out, int64_t* pred_out,
+                            int32_t* flags_out, ccn_stream_t stream) {
+    CCN_REQUIRE(n_objects >= 0 && n_categories >= 1 && max_parts >= 1 && max_parts <= kMaxParts && flags_out);
+    cudaError_t e = cudaMemsetAsync(flags_out, 0, sizeof(int32_t), S_);
+    if (e != cudaSuccess) return (int)e;
+    if (n_objects == 0) return CCN_OK;
+    CCN_REQUIRE(scores && target && sample_ptr && category && parts && parts_ptr && iou_out);
+    ccn_launch(part_iou_kernel, dim3((unsigned)n_objects), dim3(256), 0, S_, scores, ld, target, sample_ptr, category, parts,
+               parts_ptr, (int)n_categories, absent_score, iou_out, pred_out, flags_out);
+    CCN_CHECK_LAUNCH();
+    return CCN_OK;
+}

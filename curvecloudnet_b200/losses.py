@@ -88,6 +88,76 @@ def per_class_iu(hist: torch.Tensor) -> torch.Tensor:
     return d / (h.sum(1) + h.sum(0) - d)
 
 
+# ---------------------------------------------------------------------------------------------------- object runs
+SHAPENET_CATEGORY_NAMES = ['Airplane', 'Bag', 'Cap', 'Car', 'Chair', 'Earphone', 'Guitar', 'Knife', 'Lamp', 'Laptop',
+                           'Motorbike', 'Mug', 'Pistol', 'Rocket', 'Skateboard', 'Table']        # src/run/globals.py:88-89
+# torch_geometric.datasets.ShapeNet.seg_classes (the part labels of every category, used at shapenet_seg.py:93)
+SHAPENET_SEG_CLASSES = {'Airplane': [0, 1, 2, 3], 'Bag': [4, 5], 'Cap': [6, 7], 'Car': [8, 9, 10, 11], 'Chair': [12, 13, 14, 15],
+                        'Earphone': [16, 17, 18], 'Guitar': [19, 20, 21], 'Knife': [22, 23], 'Lamp': [24, 25, 26, 27],
+                        'Laptop': [28, 29], 'Motorbike': [30, 31, 32, 33, 34, 35], 'Mug': [36, 37], 'Pistol': [38, 39, 40],
+                        'Rocket': [41, 42, 43], 'Skateboard': [44, 45, 46], 'Table': [47, 48, 49]}
+_part_tables = {}
+
+
+def object_seg_loss(pred: torch.Tensor, gt: torch.Tensor):
+    """seg_loss of src/run/shapenet_seg.py:182-186 on raw logits: log_softmax, per-point NLL, its mean -> (loss, per-point)."""
+    return seg_loss(pred, gt, ignore=-100)
+
+
+def part_iou(scores: torch.Tensor, y: torch.Tensor, ptr: torch.Tensor, categories, seg_classes=None, names=None,
+             absent_score: float = 1.0) -> torch.Tensor:
+    """The per-object loop of shapenet_seg.py:88-99 as one launch: for object b (points ptr[b]..ptr[b+1], category
+    categories[b]) jaccard_index(scores[:, part].argmax(-1), y_map[y], num_classes=len(part), absent_score) -> (B,) float32
+    on the device (the reference appends `iou.item()` per object: one host sync each)."""
+    seg_classes = SHAPENET_SEG_CLASSES if seg_classes is None else seg_classes
+    names = SHAPENET_CATEGORY_NAMES if names is None else names
+    dev = scores.device
+    key = (id(seg_classes), tuple(names), str(dev))
+    if key not in _part_tables:
+        flat, pp = [], [0]
+        for nme in names:
+            flat += list(seg_classes[nme])
+            pp.append(len(flat))
+        _part_tables[key] = (torch.tensor(flat, dtype=torch.int32, device=dev), torch.tensor(pp, dtype=torch.int32, device=dev),
+                             max(pp[i + 1] - pp[i] for i in range(len(names))))
+    parts, parts_ptr, pmax = _part_tables[key]
+    sc, ld = ops._rows(scores)
+    cat = torch.as_tensor(categories, dtype=torch.int64, device=dev)
+    B = cat.shape[0]
+    out = torch.empty((B,), dtype=torch.float32, device=dev)
+    flags = torch.empty((1,), dtype=torch.int32, device=dev)
+    call("ccn_part_iou", sc, ld, ops._i64(y), ptr.to(torch.int32), cat, B, parts, parts_ptr, len(names), pmax, float(absent_score),
+         out, 0, flags)
+    return out
+
+
+def category_iou_summary(ious: torch.Tensor, categories: torch.Tensor):
+    """shapenet_seg.py:103-111 on the collected per-object IoUs (host-size vectors): per-category mean (scatter mean sized
+    max category + 1), instance mean, class mean, median."""
+    cat = categories.to(torch.int64)
+    n = int(cat.max()) + 1 if cat.numel() else 0
+    tot = torch.zeros(n, dtype=ious.dtype, device=ious.device).scatter_add_(0, cat, ious)
+    cnt = torch.zeros(n, dtype=ious.dtype, device=ious.device).scatter_add_(0, cat, torch.ones_like(ious)).clamp(min=1)
+    per_cat = tot / cnt
+    return {"per_category": per_cat, "inst_iou": float(ious.mean()), "mean_iou": float(per_cat.mean()),
+            "median_iou": float(per_cat.median())}
+
+
+def classification_metrics(log_probs: torch.Tensor, labels: torch.Tensor, n_classes: int):
+    """The epilogue of src/run/shapenet_classification.py:77-93 for a batch / a whole split: NLL loss on log-probabilities,
+    the confusion histogram of the arg-max (fused kernel), accuracy (= sklearn accuracy_score) and class-mean accuracy
+    (= sklearn balanced_accuracy_score: mean recall over the classes that occur).  -> dict with the histogram on the device."""
+    hist = torch.zeros((n_classes, n_classes), dtype=torch.int64, device=log_probs.device)
+    sc, ld = ops._rows(log_probs)
+    call("ccn_confusion_hist", sc, ld, n_classes, 0, ops._i64(labels), sc.shape[0], n_classes, 0, 0, hist)
+    h = hist.double()
+    support = h.sum(1)
+    diag = torch.diagonal(h)
+    seen = support > 0
+    return {"hist": hist, "accuracy": float(diag.sum() / h.sum().clamp(min=1)),
+            "class_accuracy": float((diag[seen] / support[seen]).mean()) if bool(seen.any()) else 0.0}
+
+
 # ---------------------------------------------------------------------------------------------------- val() TTA
 TTA_FLIPS = ((1.0, 1.0), (-1.0, 1.0), (1.0, -1.0), (-1.0, -1.0))       # nuscenes_seg.py:93-98
 TTA_SCALES = (1.0, 0.95, 1.05)                                         # :100-103

@@ -482,6 +482,15 @@ int ccn_lovasz_softmax_bwd(const float* logits, int64_t ld, const int64_t* targe
  * accumulated into) [target][pred]; pred_out optional; scores == NULL: predictions are given in pred_in. */
 int ccn_confusion_hist(const float* scores, int64_t ld, int32_t C, const int64_t* pred_in, const int64_t* target, int64_t n,
                        int32_t ncls, int32_t col_offset, int64_t* pred_out, int64_t* hist, ccn_stream_t stream);
+/* Part IoU of the object-segmentation runs (src/run/shapenet_seg.py:88-99), all objects of a batch in one launch: per object b
+ * (points sample_ptr[b] .. sample_ptr[b+1]) the arg-max over the score columns parts[parts_ptr[c] .. parts_ptr[c+1]) of its
+ * category c = category[b] (torch_geometric ShapeNet.seg_classes), the target mapped to its position in that list, and
+ * torchmetrics.functional.jaccard_index(num_classes = #parts, absent_score): intersection / union per part from the confusion
+ * matrix, absent_score where the union is empty, mean over the parts -> iou_out (n_objects) f32.  pred_out (optional): the
+ * per-point arg-max position.  flags_out: 1 category out of range, 2 a label outside its category's parts.  max_parts <= 16. */
+int ccn_part_iou(const float* scores, int64_t ld, const int64_t* target, const int32_t* sample_ptr, const int64_t* category,
+                 int32_t n_objects, const int32_t* parts, const int32_t* parts_ptr, int32_t n_categories, int32_t max_parts,
+                 float absent_score, float* iou_out, int64_t* pred_out, int32_t* flags_out, ccn_stream_t stream);
 /* test-time augmentation of val() (src/run/nuscenes_seg.py:86-116): out = [sx x, sy y, z]; acc (+)= src;
  * out = log_softmax(acc * scale), pred = arg-max. */
 int ccn_scale_xy(const float* pos, int64_t n, float sx, float sy, float* out, ccn_stream_t stream);

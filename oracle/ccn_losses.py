@@ -126,3 +126,30 @@ def tta_forward_stacked(model, data, group):
             total = out[g * n:(g + 1) * n] if total is None else total + out[g * n:(g + 1) * n]
     out = F.log_softmax(total / len(factors), dim=-1)
     return out, torch.argmax(out, dim=-1)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# object runs: src/run/shapenet_seg.py:88-111 (part IoU per object) - torchmetrics is absent here, its jaccard_index is
+# restated from its published definition (confusion matrix; intersection / union per class, absent_score where the union is
+# empty, mean over the classes): parity unpinned for that one function
+# ----------------------------------------------------------------------------------------------------------------------
+def jaccard_index(pred, target, num_classes, absent_score=0.0):
+    conf = torch.zeros((num_classes, num_classes), dtype=torch.int64)
+    conf.index_put_((target.long(), pred.long()), torch.ones_like(target, dtype=torch.int64), accumulate=True)
+    inter = torch.diagonal(conf)
+    union = conf.sum(0) + conf.sum(1) - inter
+    scores = inter.float() / union.float()
+    scores[union == 0] = absent_score
+    return scores.mean()
+
+
+def part_iou_loop(out, y, ptr, categories, seg_classes, names, n_seg_classes=50):
+    """The object loop of shapenet_seg.py:88-99 -> list of per-object IoUs."""
+    y_map = torch.zeros(n_seg_classes, dtype=torch.int64)
+    sizes = (ptr[1:] - ptr[:-1]).tolist()
+    ious = []
+    for o, t, c in zip(out.split(sizes), y.split(sizes), categories):
+        part = torch.tensor(seg_classes[names[int(c)]])
+        y_map[part] = torch.arange(part.shape[0])
+        ious.append(float(jaccard_index(o[:, part].argmax(dim=-1), y_map[t], num_classes=part.shape[0], absent_score=1.0)))
+    return ious

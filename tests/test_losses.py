@@ -139,3 +139,54 @@ def test_cuda_tta_forward_stacked_matches_oracle():
     assert st.batch.cpu().tolist() == data2.batch.tolist() + (data2.batch + 2).tolist()
     assert torch.equal(st.pos[:n].cpu(), data2.pos)
     assert torch.equal(st.pos[n:, 2].cpu(), data2.pos[:, 2]) and torch.equal(st.curve_idxs[n:].cpu(), data2.curve_idxs)
+
+
+@pytest.mark.gpu
+def test_part_iou_and_object_epilogues():
+    """Object-run epilogues: ccn_part_iou against the reference's per-object loop (shapenet_seg.py:88-99, oracle restatement;
+    parts absent from an object -> absent_score 1, an object whose every point is wrong, first-maximum ties), the loss of
+    :182-186, the category summary of :103-111, and the classification metrics of shapenet_classification.py:77-93 against
+    sklearn's accuracy_score / balanced_accuracy_score."""
+    import torch.nn.functional as F
+    from sklearn import metrics
+    from curvecloudnet_b200 import losses as L
+    from oracle import ccn_losses as OL
+    gen = torch.Generator().manual_seed(12)
+    cats = [0, 10, 1, 15, 4, 10, 7, 3]
+    sizes = [700, 650, 300, 2048, 512, 37, 1, 900]
+    ptr = torch.tensor([0] + sizes).cumsum(0)
+    n = int(ptr[-1])
+    out = torch.randn(n, 50, generator=gen)
+    y = torch.empty(n, dtype=torch.int64)
+    for b, c in enumerate(cats):
+        part = L.SHAPENET_SEG_CLASSES[L.SHAPENET_CATEGORY_NAMES[c]]
+        lo, hi = int(ptr[b]), int(ptr[b + 1])
+        y[lo:hi] = torch.tensor(part)[torch.randint(0, len(part) - (1 if b == 1 else 0), (hi - lo,), generator=gen)]
+        if b % 2 == 0:                                   # make the prediction mostly right on every second object
+            out[lo:hi].scatter_(1, y[lo:hi, None], 4.0 + torch.rand(hi - lo, 1, generator=gen))
+    out[int(ptr[3]):int(ptr[3]) + 50, 47:50] = 0.25                      # equal scores: the first part wins
+    lp = F.log_softmax(out, dim=-1)
+    want = OL.part_iou_loop(lp, y, ptr, cats, L.SHAPENET_SEG_CLASSES, L.SHAPENET_CATEGORY_NAMES)
+    got = L.part_iou(lp.cuda(), y.cuda(), ptr.cuda(), cats)
+    assert got.dtype == torch.float32 and torch.allclose(got.cpu(), torch.tensor(want), rtol=0, atol=1e-7), (got.tolist(), want)
+    loss, per = L.object_seg_loss(out.cuda(), y.cuda())
+    ref = F.nll_loss(lp, y, reduction="none")
+    assert abs(float(loss) - float(ref.mean())) <= 1e-5 * float(ref.mean()) and torch.allclose(per.cpu(), ref, rtol=1e-5, atol=1e-6)
+    summ = L.category_iou_summary(got, torch.tensor(cats).cuda())
+    ious, cat = torch.tensor(want), torch.tensor(cats)
+    per_cat = torch.zeros(16).scatter_add_(0, cat, ious) / torch.zeros(16).scatter_add_(0, cat, torch.ones(8)).clamp(min=1)
+    assert torch.allclose(summ["per_category"].cpu(), per_cat, atol=1e-6) and abs(summ["inst_iou"] - float(ious.mean())) < 1e-6
+    assert abs(summ["mean_iou"] - float(per_cat.mean())) < 1e-6 and abs(summ["median_iou"] - float(per_cat.median())) < 1e-6
+    # classification
+    logits = torch.randn(500, 16, generator=gen)
+    labels = torch.randint(0, 13, (500,), generator=gen)                 # three classes never occur
+    logits.scatter_(1, labels[:, None], 1.5, reduce="add")
+    clp = F.log_softmax(logits, dim=-1)
+    m = L.classification_metrics(clp.cuda(), labels.cuda(), 16)
+    pred = clp.argmax(dim=-1)
+    assert abs(m["accuracy"] - metrics.accuracy_score(labels.numpy(), pred.numpy())) < 1e-12
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        assert abs(m["class_accuracy"] - metrics.balanced_accuracy_score(labels.numpy(), pred.numpy())) < 1e-12
+    assert int(m["hist"].sum()) == 500
