@@ -297,6 +297,39 @@ def ingest_a2d2_frame(frame: dict, labels=None, augmentation: Optional[A2D2Augme
     return Batch(x=x, pos=pos, y=y, curve_idxs=cid, reorder=reorder, counts=counts)
 
 
+@dataclass
+class ObjectAugmentation:
+    """The draws of the shapenet-seg training transform (object_datasets.py:31-36), one object: RandomScale's
+    `random.uniform(0.95, 1.05)` (python's generator) and `(torch.rand((1, 3)) - 0.5) * 0.05` (torch's)."""
+    scale: float
+    shift: Sequence[float]
+
+    @classmethod
+    def draw(cls) -> "ObjectAugmentation":
+        import random
+        scale = random.uniform(0.95, 1.05)
+        shift = ((torch.rand((1, 3)) - 0.5) * 0.05)[0]
+        return cls(float(scale), tuple(float(v) for v in shift))
+
+
+def ingest_object_scans(pos: torch.Tensor, batch: torch.Tensor, augmentations: Optional[List[ObjectAugmentation]] = None):
+    """CurvesInMemoryDataset.get (object_datasets.py:21-38) for a batch of stored objects: positions (N, 3) with their object
+    ids -> normalised (and, for the shapenet-seg training split, transformed) positions.  Loading the `.pth` file is the
+    caller's; curve ids, normals and labels pass through unchanged."""
+    native.load()
+    pos = pos.to(torch.float32).contiguous()
+    sptr = ops.sample_ptr(batch)
+    B = sptr.n_samples
+    out = torch.empty_like(pos)
+    aug = 0
+    if augmentations is not None:
+        if len(augmentations) != B:
+            raise ValueError("one ObjectAugmentation per object")
+        aug = torch.tensor([[a.scale, a.shift[0], a.shift[1], a.shift[2]] for a in augmentations], dtype=torch.float32).to(pos.device)
+    native.call("ccn_object_normalize", pos, sptr.dev, B, aug, out)
+    return out
+
+
 def _np_i64(a):
     return np.ascontiguousarray(a, dtype=np.int64) if isinstance(a, np.ndarray) else a
 

@@ -462,6 +462,12 @@ int ccn_polarmix(const float* pos1, const float* x1, const int64_t* y1, const in
  * entry, for the PolarMix path where the mix sits between the grouping and the augmentation). */
 int ccn_augment_points(const float* pos_in, int64_t n, int32_t augment, double rot_c, double rot_s, int32_t flip_type,
                        float scale, double tx, double ty, double tz, float pos_div, float* pos_out, ccn_stream_t stream);
+/* Object scans - CurvesInMemoryDataset.get (src/data/object_datasets.py:21-38) for a batch of objects (points of object b:
+ * sample_ptr[b] .. sample_ptr[b+1]): pc_normalize (:61-66: minus the mean, divided by the largest norm); with aug
+ * ((n_objects, 4) f32 = {scale, shift xyz}) also the shapenet-seg training transform: torch_geometric NormalizeScale (centre,
+ * * 0.999999 / max |coordinate|), RandomScale (one factor), pos += shift (:31-36).  The means are f64 sums rounded once. */
+int ccn_object_normalize(const float* pos, const int32_t* sample_ptr, int32_t n_objects, const float* aug, float* pos_out,
+                         ccn_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------------------------
  * Loss / metrics epilogue of the segmentation runs (csrc/loss_metrics.cu).

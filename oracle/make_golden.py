@@ -465,6 +465,43 @@ def make_a2d2():
     return out
 
 
+def make_objects():
+    """Object scans: `pc_normalize` compiled from its source text (src/data/object_datasets.py:61-66) and the body of
+    CurvesInMemoryDataset.get (:21-38) around it.  torch_geometric.transforms is absent: Center / NormalizeScale / RandomScale
+    are stated from their 2.3.0 definitions (pos - mean; * 0.999999 / max|pos|; * random.uniform) - unpinned third party."""
+    import random
+    from curvecloudnet_b200.synthetic import object_scan_batch
+    src = open(os.path.join(REF, "src/data/object_datasets.py")).read()
+    tree = ast.parse(src)
+    ns = {"torch": torch}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name == "pc_normalize":
+            exec(compile(textwrap.dedent(ast.get_source_segment(src, node)), "object_datasets.py:pc_normalize", "exec"), ns)
+    pc_normalize = ns["pc_normalize"]
+    data = object_scan_batch([31, 32, 33], n_points=768)
+    gen = torch.Generator().manual_seed(4)
+    raw = data.pos * 3.7 + torch.tensor([0.4, -1.1, 2.0]) + 0.01 * torch.randn(data.pos.shape, generator=gen)   # un-normalised
+    out = {"seeds": [31, 32, 33], "raw": raw, "batch": data.batch, "val": [], "train": [], "draws": []}
+    random.seed(21)
+    torch.manual_seed(21)
+    for b in range(3):
+        p = raw[data.batch == b].float()
+        v = pc_normalize(p)
+        out["val"].append(v)
+        t = v - v.mean(dim=-2, keepdim=True)                      # T.NormalizeScale = Center + scale
+        t = t * ((1 / t.abs().max()) * 0.999999)
+        scale = random.uniform(0.95, 1.05)                        # T.RandomScale((0.95, 1.05))
+        t = t * scale
+        shift = (torch.rand((1, 3)) - 0.5) * 0.05                 # object_datasets.py:36
+        t = t + shift
+        out["train"].append(t)
+        out["draws"].append([scale] + shift[0].tolist())
+    out["val"], out["train"] = torch.cat(out["val"]), torch.cat(out["train"])
+    out["draws"] = torch.tensor(out["draws"], dtype=torch.float64)
+    print("objects", tuple(out["val"].shape), float(out["val"].norm(dim=1).max()), float(out["train"].abs().max()))
+    return out
+
+
 def make_ingest():
     """Scan ingest: SemNuScenes.get / SemKITTI.get with their own _load_frame, _get_curves and
     _training_augmentation, compiled from source and run on synthetic raw files written to a temp directory."""
@@ -629,6 +666,11 @@ def main():
         sys.path.insert(0, ROOT)
         torch.save(_compact(make_ingest()), os.path.join(OUT, "ingest.pt"))
         print("ingest.pt", os.path.getsize(os.path.join(OUT, "ingest.pt")) // 1024, "KiB")
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "objects":    # only the object-scan normalisation fixture
+        sys.path.insert(0, ROOT)
+        torch.save(_compact(make_objects()), os.path.join(OUT, "objects.pt"))
+        print("objects.pt", os.path.getsize(os.path.join(OUT, "objects.pt")) // 1024, "KiB")
         return
     if len(sys.argv) > 1 and sys.argv[1] == "a2d2":       # only the A2D2 curve-builder fixture
         sys.path.insert(0, ROOT)

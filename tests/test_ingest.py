@@ -391,3 +391,36 @@ def test_a2d2_frame_feeds_the_model():
     with torch.no_grad():
         got = model(Batch.from_data_list([d]))
     assert rel_err(got.cpu(), want) <= 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# object scans: CurvesInMemoryDataset.get / pc_normalize (src/data/object_datasets.py:21-66); tests/golden/objects.pt holds
+# pc_normalize's own output (compiled from source) and the shapenet-seg training transform around it
+# ---------------------------------------------------------------------------------------------------------------
+def test_object_augmentation_draws_replay_the_reference_order():
+    import random
+    from curvecloudnet_b200.ingest import ObjectAugmentation
+    g = load("objects.pt")
+    random.seed(21)
+    torch.manual_seed(21)
+    for b in range(3):
+        a = ObjectAugmentation.draw()
+        assert abs(a.scale - float(g["draws"][b, 0])) < 1e-15
+        assert torch.allclose(torch.tensor(a.shift, dtype=torch.float64), g["draws"][b, 1:], atol=1e-9)
+
+
+@pytest.mark.gpu
+def test_object_scans_match_reference_golden():
+    """ccn_object_normalize against pc_normalize (and the training transform): 1e-6 relative to the unit scale of the result -
+    the means are f64 sums here, f32 pairwise sums upstream."""
+    from curvecloudnet_b200.ingest import ObjectAugmentation, ingest_object_scans
+    g = load("objects.pt")
+    raw, batch = g["raw"].cuda(), g["batch"].cuda()
+    val = ingest_object_scans(raw, batch)
+    assert float((val.cpu() - g["val"]).abs().max()) <= 1e-6
+    augs = [ObjectAugmentation(float(d[0]), tuple(float(v) for v in d[1:])) for d in g["draws"]]
+    tr = ingest_object_scans(raw, batch, augs)
+    assert float((tr.cpu() - g["train"]).abs().max()) <= 1e-6
+    for b in range(3):                                       # what pc_normalize promises: centred, the farthest point at 1
+        v = val[batch == b]
+        assert float(v.mean(0).abs().max()) < 1e-6 and abs(float(v.norm(dim=1).max()) - 1.0) < 1e-6
