@@ -330,6 +330,33 @@ def ingest_object_scans(pos: torch.Tensor, batch: torch.Tensor, augmentations: O
     return out
 
 
+def ingest_kortx_scan(points, raw_curve_idxs, segmentation=None, npoints: int = 2048, samples_per_scan: int = 5,
+                      capture_setting: str = "table", device="cuda"):
+    """The per-file body of scanning_simulator/kortx/generate_kortx.py:38-75 on the device: one long scan (the CSV's columns
+    0-2 xyz in f64, 4 raw curve counter, 5 segmentation) -> `fix_curve_idxs`, `cut_curves` (threshold 0.2 for 'table'
+    captures, else 1.0), `samples_per_scan` windows of `npoints` points scaled into the unit cube's half, curve ids renumbered
+    per window.  -> dict(pos (S, npoints, 3) f64, curve_idxs (S, npoints) i64, y (S, npoints) i64 or None, all_curve_idxs (n,)).
+    Reading the CSV / info.json stays with the caller."""
+    native.load()
+    pts = _as_device(np.ascontiguousarray(points, dtype=np.float64) if isinstance(points, np.ndarray) else points.to(torch.float64),
+                     torch.float64, device).view(-1, 3)
+    n = pts.shape[0]
+    if n < npoints:
+        raise ValueError("ingest_kortx_scan: %d points, fewer than one window of %d" % (n, npoints))
+    raw = _as_device(_np_i64(raw_curve_idxs), torch.int64, device)
+    seg = _as_device(_np_i64(segmentation), torch.int64, device) if segmentation is not None else None
+    dev = pts.device
+    scratch = torch.empty((2 * n,), dtype=torch.int32, device=dev)
+    curve = torch.empty((n,), dtype=torch.int64, device=dev)
+    native.call("ccn_kortx_curves", pts, raw, n, 0.2 if capture_setting == "table" else 1.0, scratch, curve)
+    S = int(samples_per_scan)
+    pos = torch.empty((S, npoints, 3), dtype=torch.float64, device=dev)
+    cid = torch.empty((S, npoints), dtype=torch.int64, device=dev)
+    y = torch.empty((S, npoints), dtype=torch.int64, device=dev) if seg is not None else None
+    native.call("ccn_kortx_windows", pts, curve, seg if seg is not None else 0, n, int(npoints), S, pos, cid, y if y is not None else 0)
+    return {"pos": pos, "curve_idxs": cid, "y": y, "all_curve_idxs": curve}
+
+
 def _np_i64(a):
     return np.ascontiguousarray(a, dtype=np.int64) if isinstance(a, np.ndarray) else a
 

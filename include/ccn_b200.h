@@ -404,6 +404,17 @@ int ccn_conv_planes(const void* a, int64_t ld, int64_t ps, int32_t cin, int32_t 
 int ccn_get_curves(const float* points, int64_t ldp, const int64_t* beam, int64_t n, int32_t n_beams, float curve_thresh,
                    int32_t* scratch, int64_t* reorder, int64_t* inv_reorder, float* sorted_points, int64_t* curve_idxs,
                    int32_t* counts_out, ccn_stream_t stream);
+/* Kortx scans (scanning_simulator/kortx/generate_kortx.py:38-75): ccn_kortx_curves = fix_curve_idxs (:94-104: a curve start
+ * directly followed by another start is dropped; ids = running count of the remaining starts) then cut_curves (:107-117: new
+ * curve where the id grows or the f64 edge exceeds cut_thresh - 0.2 for 'table' captures, else 1.0; ids from 0).  points (n,3)
+ * f64, raw_curve (n) int64 (the file's column 4); scratch int32 [2 n]; curve_out (n) int64.
+ * ccn_kortx_windows: n_windows windows of npoints consecutive points, window w starting at w * ((n - npoints) / n_windows)
+ * (:40-42): pos_out (n_windows, npoints, 3) f64 = points / (2 max |coordinate| of the window) (:57-59), curve_out the ids
+ * renumbered from 0 per window (torch.unique(return_inverse) of a non-decreasing sequence, :63), seg_out the labels. */
+int ccn_kortx_curves(const double* points, const int64_t* raw_curve, int64_t n, double cut_thresh, int32_t* scratch,
+                     int64_t* curve_out, ccn_stream_t stream);
+int ccn_kortx_windows(const double* points, const int64_t* curve, const int64_t* segmentation, int64_t n, int32_t npoints,
+                      int32_t n_windows, double* pos_out, int64_t* curve_out, int64_t* seg_out, ccn_stream_t stream);
 /* Curve grouping of an A2D2 frame - SemA2D2._get_curves / _partition_curves_at_discontinuities
  * (src/data/audi_dataset.py:156-243).  A2D2 carries no beam ids: per lidar (lidar_id, 5 sensors) the reference builds a kNN
  * graph (torch_cluster.knn, k = KNN[id] <= 4, self included), keeps the edges shorter than CURVE_THRESHES[id] * sqrt(|p.xy|)

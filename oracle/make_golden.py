@@ -502,6 +502,77 @@ def make_objects():
     return out
 
 
+def kortx_scan(seed: int, n: int = 9000):
+    """A Kortx-shaped raw scan: points along ~70 laser lines of a height field (f64, 0.5 m extent), a raw curve counter that
+    grows at every line change - with spurious single-point increments the way the real files have them - a time stamp and a
+    part label per point."""
+    import numpy as np
+    rng = np.random.default_rng(500 + seed)
+    lines = 70
+    per = n // lines
+    pts, raw, cur = [], [], 0
+    for li in range(lines):
+        m = per + (n - per * lines if li == lines - 1 else 0)
+        s = np.linspace(-0.25, 0.25, m)
+        th = rng.uniform(0, np.pi)
+        off = rng.uniform(-0.2, 0.2)
+        xy = off * np.array([-np.sin(th), np.cos(th)])[None] + s[:, None] * np.array([np.cos(th), np.sin(th)])[None]
+        z = 0.08 * np.sin(9 * xy[:, 0]) * np.cos(7 * xy[:, 1])
+        hole = rng.integers(0, m - 40)
+        z[hole:hole + rng.integers(0, 30)] += 0.35                      # a jump: cut_curves splits here ('table' threshold 0.2)
+        pts.append(np.concatenate([xy, z[:, None]], axis=1))
+        ids = np.full(m, cur)
+        for k in rng.integers(1, m - 2, size=3):                       # spurious +1, +1 on consecutive points
+            ids[k:] += 1
+            ids[k + 1:] += 1
+        raw.append(ids)
+        cur = ids[-1] + 1
+    pts = np.concatenate(pts).astype(np.float64)
+    raw = np.concatenate(raw).astype(np.int64)
+    t = (np.arange(pts.shape[0]) * 13).astype(np.int64)
+    seg = rng.integers(12, 16, size=pts.shape[0]).astype(np.int64)
+    return pts, t, raw, seg
+
+
+def make_kortx():
+    """scanning_simulator/kortx/generate_kortx.py run AS A SCRIPT MODULE (its main(), fix_curve_idxs and cut_curves; pandas is
+    here) over a temp directory holding one synthetic instance with two views; its visualisation import is stubbed."""
+    import json
+    import tempfile
+    import types
+    import numpy as np
+    import pandas as pd
+    for p in (ROOT, os.path.join(ROOT, "oracle", "shims"), REF):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    viz = types.ModuleType("scanning_simulator.utils.visualization")
+    viz.visualize_kortx_test_pc = viz.visualize_kortx_test_pc_mitsuba = lambda *a, **k: None
+    sys.modules["scanning_simulator.utils.visualization"] = viz
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_generate_kortx", os.path.join(REF, "scanning_simulator/kortx/generate_kortx.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = {}
+    for tag, setting, seed, n in (("table", "table", 1, 9000), ("handheld", "handheld", 2, 12345)):
+        tmp = tempfile.mkdtemp(prefix="ccn_kortx_")
+        os.makedirs(os.path.join(tmp, "inst"))
+        with open(os.path.join(tmp, "inst", "info.json"), "w") as f:
+            json.dump({"object-class": "chair", "capture-setting": setting}, f)
+        pts, t, raw, seg = kortx_scan(seed, n)
+        pd.DataFrame(np.concatenate([pts, t[:, None], raw[:, None], seg[:, None]], axis=1)).to_csv(
+            os.path.join(tmp, "inst", "view0.csv"), header=False, index=False, float_format="%.17g")
+        args = types.SimpleNamespace(data_path=tmp, npoints=2048, samples_per_scan=5, viz=False,
+                                     outfile=os.path.join(tmp, "out.pth"))
+        mod.main(args, "cpu")
+        batch = torch.load(args.outfile, weights_only=False)
+        out[tag] = {"points": torch.from_numpy(pts), "raw": torch.from_numpy(raw), "seg": torch.from_numpy(seg),
+                    "setting": setting, "pos": batch.pos.view(5, 2048, 3), "curve_idxs": batch.curve_idxs.view(5, 2048),
+                    "y": batch.y.view(5, 2048), "label": int(batch.labels[0])}
+        print("kortx", tag, n, "points ->", tuple(out[tag]["pos"].shape), "curves per window",
+              [int(c.max()) + 1 for c in out[tag]["curve_idxs"]])
+    return out
+
+
 def make_ingest():
     """Scan ingest: SemNuScenes.get / SemKITTI.get with their own _load_frame, _get_curves and
     _training_augmentation, compiled from source and run on synthetic raw files written to a temp directory."""
@@ -671,6 +742,10 @@ def main():
         sys.path.insert(0, ROOT)
         torch.save(_compact(make_objects()), os.path.join(OUT, "objects.pt"))
         print("objects.pt", os.path.getsize(os.path.join(OUT, "objects.pt")) // 1024, "KiB")
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "kortx":      # only the Kortx raw-scan fixture (the real generate_kortx.py)
+        torch.save(_compact(make_kortx()), os.path.join(OUT, "kortx.pt"))
+        print("kortx.pt", os.path.getsize(os.path.join(OUT, "kortx.pt")) // 1024, "KiB")
         return
     if len(sys.argv) > 1 and sys.argv[1] == "a2d2":       # only the A2D2 curve-builder fixture
         sys.path.insert(0, ROOT)

@@ -424,3 +424,22 @@ def test_object_scans_match_reference_golden():
     for b in range(3):                                       # what pc_normalize promises: centred, the farthest point at 1
         v = val[batch == b]
         assert float(v.mean(0).abs().max()) < 1e-6 and abs(float(v.norm(dim=1).max()) - 1.0) < 1e-6
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Kortx raw scans: tests/golden/kortx.pt = the output file of the REAL scanning_simulator/kortx/generate_kortx.py (main,
+# fix_curve_idxs, cut_curves) run over a synthetic instance directory (oracle/make_golden.py kortx)
+# ---------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["table", "handheld"])
+def test_kortx_scan_matches_the_reference_script(tag):
+    from curvecloudnet_b200.ingest import ingest_kortx_scan
+    g = load("kortx.pt")[tag]
+    d = ingest_kortx_scan(g["points"].numpy(), g["raw"].numpy(), g["seg"].numpy(), npoints=2048, samples_per_scan=5,
+                          capture_setting=g["setting"])
+    assert d["pos"].dtype == torch.float64 and torch.equal(d["pos"].cpu(), g["pos"])          # f64 division: bit-exact
+    assert torch.equal(d["curve_idxs"].cpu(), g["curve_idxs"]) and torch.equal(d["y"].cpu(), g["y"])
+    c = d["all_curve_idxs"]
+    assert int(c[0]) == 0 and bool((c[1:] - c[:-1] >= 0).all()) and bool((c[1:] - c[:-1] <= 1).all())
+    with pytest.raises(ValueError, match="fewer than one window"):
+        ingest_kortx_scan(g["points"].numpy()[:100], g["raw"].numpy()[:100], None)
