@@ -561,6 +561,8 @@ def make_kortx():
         pts, t, raw, seg = kortx_scan(seed, n)
         pd.DataFrame(np.concatenate([pts, t[:, None], raw[:, None], seg[:, None]], axis=1)).to_csv(
             os.path.join(tmp, "inst", "view0.csv"), header=False, index=False, float_format="%.17g")
+        # what the script will read: pandas' default float parser is not round-trip exact, so the fixture keeps ITS values
+        pts = pd.read_csv(os.path.join(tmp, "inst", "view0.csv"), header=None).iloc[:, :3].to_numpy().copy()
         args = types.SimpleNamespace(data_path=tmp, npoints=2048, samples_per_scan=5, viz=False,
                                      outfile=os.path.join(tmp, "out.pth"))
         mod.main(args, "cpu")
