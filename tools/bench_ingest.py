@@ -1,6 +1,6 @@
 """Scan ingest timing: raw records in host memory -> Data fields in HBM.
 
-    python tools/bench_ingest.py [--dataset nuscenes|kitti] [--steps 200]
+    python tools/bench_ingest.py [--dataset nuscenes|kitti|a2d2] [--steps 200]
 
 Prints one JSON line: sweeps/s and points/s of `ingest_scan` from host bytes (pinned staging + H2D + ccn_ingest_scan,
 training augmentation on), the device-only time of the C-ABI call (CUDA events), its algorithmic HBM bytes, and the CPU
@@ -20,12 +20,41 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def a2d2(args):
+    """A2D2-shaped frames (5 lidars, no beam ids): ingest_a2d2_frame = ccn_a2d2_curves + ccn_a2d2_finish + ccn_augment_points."""
+    from curvecloudnet_b200.ingest import A2D2Augmentation, ingest_a2d2_frame
+    from curvecloudnet_b200.synthetic import a2d2_frame
+    frames = [a2d2_frame(20 + s) for s in range(4)]
+    np.random.seed(1)
+    for i in range(8):
+        ingest_a2d2_frame(frames[i % 4], frames[i % 4]["label"], A2D2Augmentation.draw(), check=False)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        ingest_a2d2_frame(frames[i % 4], frames[i % 4]["label"], A2D2Augmentation.draw(), check=False)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / args.steps
+    pts = float(np.mean([f["points"].shape[0] for f in frames]))
+    line = {"metric": "A2D2 frame ingest (kNN-graph curve builder + normalisation + augmentation)", "frames_per_s": 1.0 / dt,
+            "points_per_s": pts / dt, "ms_per_frame": dt * 1e3, "points_per_frame": pts, "steps": args.steps}
+    if args.cpu_arm:
+        from oracle import ccn_ingest as I
+        t0 = time.perf_counter()
+        for i in range(4):
+            I.a2d2_ingest_frame(frames[i], I.a2d2_draw_augmentation())
+        line["cpu_ms_per_frame"] = (time.perf_counter() - t0) / 4 * 1e3
+        line["cpu_kind"] = "oracle port of SemA2D2.get (torch CPU + numpy, one thread of python)"
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--dataset", default="nuscenes")
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--cpu-arm", action="store_true", help="also time the CPU restatement (imports oracle/)")
     args = ap.parse_args()
+    if args.dataset == "a2d2":
+        return a2d2(args)
     from curvecloudnet_b200 import native
     from curvecloudnet_b200.ingest import LearningMap, ScanAugmentation, ingest_scan
     from curvecloudnet_b200.synthetic import raycast_driving_scan
