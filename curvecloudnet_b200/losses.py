@@ -112,7 +112,7 @@ def part_iou(scores: torch.Tensor, y: torch.Tensor, ptr: torch.Tensor, categorie
     seg_classes = SHAPENET_SEG_CLASSES if seg_classes is None else seg_classes
     names = SHAPENET_CATEGORY_NAMES if names is None else names
     dev = scores.device
-    key = (id(seg_classes), tuple(names), str(dev))
+    key = (tuple((nme, tuple(seg_classes[nme])) for nme in names), str(dev))
     if key not in _part_tables:
         flat, pp = [], [0]
         for nme in names:
