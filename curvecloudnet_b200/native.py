@@ -64,7 +64,32 @@ def load():
         fn.argtypes = [_c[ch] for ch in sig]
         fn.restype = _RETURNS[name]
     _lib = lib
+    _load_fast()
     return lib
+
+
+_fast = None                # the cffi extension's `lib` (thin C wrappers, see _fastcall_build.py) or None: ctypes only
+BINDING = "ctypes"
+
+
+def _load_fast():
+    """Use the generated CPython extension for the Python -> C hop when it is present and was built from this header
+    (CCN_BINDING=ctypes keeps ctypes).  Only the binding differs: both reach the same entry points of libccn_b200.so."""
+    global _fast, BINDING
+    if os.environ.get("CCN_BINDING", "") == "ctypes":
+        return
+    try:
+        from . import _ccn_cffi
+        from ._fastcall_build import header_hash
+        mod_hash = _ccn_cffi.ffi.string(_ccn_cffi.lib.w_header_hash()).decode()
+        if mod_hash != header_hash():
+            import warnings
+            warnings.warn("curvecloudnet_b200: _ccn_cffi was built from another include/ccn_b200.h - using ctypes "
+                          "(run __graft_entry__.build())")
+            return
+        _fast, BINDING = _ccn_cffi.lib, "cffi"
+    except ImportError:
+        _fast = None
 
 
 class CcnError(RuntimeError):
@@ -165,7 +190,8 @@ _fns = {}                   # name -> (foreign function, indices of the pointer 
 def _bind(name):
     lib = _lib if _lib is not None else load()
     sig = SIGNATURES[name]
-    ent = (getattr(lib, name), tuple(i for i, ch in enumerate(sig[:-1]) if ch == "p"))
+    fn = getattr(_fast, "w_" + name, None) if _fast is not None else None
+    ent = (fn if fn is not None else getattr(lib, name), tuple(i for i, ch in enumerate(sig[:-1]) if ch == "p"))
     _fns[name] = ent
     return ent
 

@@ -37,6 +37,24 @@ def test_every_declared_symbol_is_exported(lib):
     assert native.kernel_launches() == 0 or native.kernel_launches() > 0
 
 
+def test_fast_binding_wraps_every_entry_point(lib):
+    """The generated CPython extension (curvecloudnet_b200/_fastcall_build.py): built from THIS header, one wrapper per
+    entry point, and an argument error comes back through it exactly as through ctypes (no GPU call is reached)."""
+    from curvecloudnet_b200 import _fastcall_build
+    so = [f for f in os.listdir(os.path.dirname(native.LIB_PATH)) if f.startswith("_ccn_cffi.") and f.endswith(".so")]
+    if not so:
+        _fastcall_build.build()
+    from curvecloudnet_b200 import _ccn_cffi
+    assert _ccn_cffi.ffi.string(_ccn_cffi.lib.w_header_hash()).decode() == _fastcall_build.header_hash()
+    for name in native.SIGNATURES:
+        assert hasattr(_ccn_cffi.lib, "w_" + name), name
+    args = (0, 64, 0, 100, 9, 64, 0, 64, 0)                  # feat = NULL: rejected by the argument check
+    assert _ccn_cffi.lib.w_ccn_group_max_dense(*args) == lib.ccn_group_max_dense(*args) == -1
+    assert _ccn_cffi.lib.w_ccn_grid_num_cells(1000) == 2048
+    if os.environ.get("CCN_BINDING", "") != "ctypes":
+        assert native.BINDING == "cffi"
+
+
 def test_library_has_sm100a_code_only(lib):
     out = subprocess.run(["cuobjdump", "--list-elf", native.LIB_PATH], capture_output=True, text=True)
     if out.returncode != 0:
