@@ -311,7 +311,7 @@ __device__ __forceinline__ float feat_sqdist(const float* __restrict__ a, const 
 __global__ void __launch_bounds__(256) feat_neighbours_kernel(
     const float* __restrict__ x1, int64_t ld1, const int64_t* __restrict__ batch1, int64_t n1,
     const float* __restrict__ x2, int64_t ld2, const int32_t* __restrict__ sptr2, int dim, float r2, int K, int mode,
-    int32_t* __restrict__ idx_out, int32_t* __restrict__ cnt_out) {
+    int32_t* __restrict__ idx_out, float* __restrict__ d2_out, int32_t* __restrict__ cnt_out) {
     ccn_pdl_wait();
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= n1) return;
@@ -334,7 +334,10 @@ __global__ void __launch_bounds__(256) feat_neighbours_kernel(
             top.offer(ok, key, K);
         }
         const bool have = top.held != kKeyMax;
-        if (lane < K) idx_out[q * K + lane] = have ? (int32_t)(top.held & 0xffffffffu) : -1;
+        if (lane < K) {
+            idx_out[q * K + lane] = have ? (int32_t)(top.held & 0xffffffffu) : -1;
+            if (d2_out) d2_out[q * K + lane] = have ? __uint_as_float((unsigned)(top.held >> 32)) : -1.f;
+        }
         if (cnt_out) {
             const int cnt = __popc(__ballot_sync(0xffffffffu, have && lane < K));
             if (lane == 0) cnt_out[q] = cnt;
@@ -444,13 +447,14 @@ extern "C" int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t 
 
 extern "C" int ccn_feat_neighbours(const float* x1, int64_t ld1, const int64_t* batch1, int64_t n1, const float* x2,
                                    int64_t ld2, const int32_t* sample_ptr2, int32_t dim, float radius, int32_t K,
-                                   int32_t mode, int32_t* idx_out, int32_t* cnt_out, ccn_stream_t stream) {
+                                   int32_t mode, int32_t* idx_out, float* d2_out, int32_t* cnt_out, ccn_stream_t stream) {
     CCN_REQUIRE(n1 >= 0 && dim >= 1 && ld1 >= dim && ld2 >= dim && K >= 1 && (mode == 0 || mode == 1) && idx_out && sample_ptr2);
     CCN_REQUIRE(mode == 1 || K <= 32);
+    CCN_REQUIRE(mode == 0 || !d2_out);                      // the ball query keeps index order and reports no distances
     if (n1 == 0) return CCN_OK;
     CCN_REQUIRE(x1 && x2 && batch1);
     ccn_launch(feat_neighbours_kernel, dim3(ccn_blocks_exact(n1 * 32, 256)), dim3(256), 0, (cudaStream_t)stream,
-               x1, ld1, batch1, n1, x2, ld2, sample_ptr2, (int)dim, radius * radius, (int)K, (int)mode, idx_out, cnt_out);
+               x1, ld1, batch1, n1, x2, ld2, sample_ptr2, (int)dim, radius * radius, (int)K, (int)mode, idx_out, d2_out, cnt_out);
     CCN_CHECK_LAUNCH();
     return CCN_OK;
 }

@@ -29,7 +29,7 @@ def _flatten(points, lengths):
     else:
         lens = [int(v) for v in lengths.tolist()]
     if all(l == P for l in lens):
-        flat = points.reshape(N * P, 3)
+        flat = points.reshape(N * P, points.shape[2])
     else:
         flat = torch.cat([points[b, :lens[b]] for b in range(N)])
     batch = torch.repeat_interleave(torch.arange(N, device=points.device), torch.tensor(lens, device=points.device))
@@ -45,8 +45,9 @@ def frnn_grid_points(points1: torch.Tensor, points2: torch.Tensor, lengths1: Opt
         raise TypeError("frnn_grid_points only supports CUDA tensors")
     if points1.shape[0] != points2.shape[0]:
         raise ValueError("points1 and points2 must have the same batch dimension")
-    if points1.shape[2] != 3 or points2.shape[2] != 3:
-        raise NotImplementedError("only D = 3 (the CurveCloudNet path)")
+    if points1.shape[2] != points2.shape[2]:
+        raise ValueError("dimension mismatch: points1 of dimension %d while points2 of dimension %d"
+                         % (points1.shape[2], points2.shape[2]))                      # frnn.py:286-289
     if K <= 0 or K > 32:
         raise ValueError("K must be in [1, 32]")                      # the reference kernels are instantiated for K <= 32
     if torch.is_tensor(r):
@@ -68,7 +69,12 @@ def frnn_grid_points(points1: torch.Tensor, points2: torch.Tensor, lengths1: Opt
     dists = torch.full((N, P1, K), -1.0, dtype=torch.float32, device=points1.device)
     idxs = torch.full((N, P1, K), -1, dtype=torch.int64, device=points1.device)
     if p1.shape[0] and p2.shape[0]:
-        idx, d2, _ = ops.frnn_knn(p1, b1, p2, b2, s2, K, float(r), want_d2=True, cache=cache)
+        if points1.shape[2] == 3:
+            idx, d2, _ = ops.frnn_knn(p1, b1, p2, b2, s2, K, float(r), want_d2=True, cache=cache)
+        else:
+            # D != 3 (upstream's N-D kernels, grid.h:27-34; reached only by DynamicEdgeConv): brute force in feature space,
+            # same result contract (d2 <= r^2, ascending by (d2, index)); no grid object comes back
+            idx, _, d2 = ops.feat_neighbours(p1, b1, p2, s2, K, float(r), "knn", want_d2=True)
         off1 = off2 = 0
         for b in range(N):
             blk = idx[off1:off1 + l1[b]].to(torch.int64)

@@ -440,7 +440,7 @@ def ball_query(pos1, batch1, pos2, sptr2: SamplePtr, radius: float, K: int = 128
     return idx, cnt
 
 
-def feat_neighbours(x1, batch1, x2, sptr2: SamplePtr, K: int, radius: float, mode: str):
+def feat_neighbours(x1, batch1, x2, sptr2: SamplePtr, K: int, radius: float, mode: str, want_d2: bool = False):
     """Neighbours in FEATURE space (DynamicEdgeConv, dgcnn.py:64-89): mode "knn" = fixed-radius kNN by (d2, index)
     (fast_knn on D-dimensional rows, K <= 32), "ball" = first K in index order inside the radius (ball_query)."""
     x1, ld1 = _rows(x1)
@@ -450,9 +450,10 @@ def feat_neighbours(x1, batch1, x2, sptr2: SamplePtr, K: int, radius: float, mod
     n1 = x1.shape[0]
     idx = _empty((n1, K), torch.int32, x1)
     cnt = _empty((n1 + 2,), torch.int32, x1)
+    d2 = _empty((n1, K), torch.float32, x1) if want_d2 else None
     call("ccn_feat_neighbours", x1, ld1, _i64(batch1), n1, x2, ld2, sptr2.dev, x1.shape[1], float(radius), K,
-         {"knn": 0, "ball": 1}[mode], idx, cnt)
-    return idx, cnt
+         {"knn": 0, "ball": 1}[mode], idx, d2 if d2 is not None else 0, cnt)
+    return (idx, cnt, d2) if want_d2 else (idx, cnt)
 
 
 def dense_to_csr(idx: torch.Tensor, cnt: torch.Tensor) -> EdgeCSR:

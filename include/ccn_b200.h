@@ -210,10 +210,11 @@ int ccn_ball_query(const float* pos1, const int64_t* batch1, int64_t n1, const f
  * operation rounded.  mode 0: fixed-radius kNN, d2 <= radius^2, the K <= 32 smallest by (d2, index) (fast_knn,
  * point_ops.py:84-88, frnn.frnn_grid_points on dim-D points); mode 1: d2 < radius^2, the first K in index order
  * (pytorch3d.ops.ball_query, point_ops.py:81, K = 128 there).  idx_out (n1, K) global row indices of x2, -1 padded;
- * cnt_out (n1) or null.  Brute force, O(n1 * cloud * dim): no shipped configuration reaches these steps. */
+ * d2_out (n1, K) squared distances, -1 padded (mode 0 only, or null); cnt_out (n1) or null.  Brute force,
+ * O(n1 * cloud * dim): no shipped configuration reaches these steps. */
 int ccn_feat_neighbours(const float* x1, int64_t ld1, const int64_t* batch1, int64_t n1, const float* x2, int64_t ld2,
                         const int32_t* sample_ptr2, int32_t dim, float radius, int32_t K, int32_t mode, int32_t* idx_out,
-                        int32_t* cnt_out, ccn_stream_t stream);
+                        float* d2_out, int32_t* cnt_out, ccn_stream_t stream);
 
 /* ---- gathers and segmented aggregation ---------------------------------------------------------------
  * replace x[idx] / torch_scatter / torch_geometric.utils.softmax / frnn_gather on the path

@@ -62,3 +62,23 @@ def test_frnn_grid_points_matches_reference_golden():
     _, idxs, _, _ = frnn.frnn_grid_points(p1, p2, m1.sum(1), m2.sum(1), 16, rec["knn_radius"])
     want = rec["frnn_dense"]
     assert torch.equal(idxs[:, :want.shape[1]].cpu(), want)
+
+
+@pytest.mark.parametrize("dim", [2, 5, 17])
+def test_frnn_grid_points_other_dimensions(dim):
+    """frnn_grid_points on D != 3 points (upstream's N-D kernels, grid.h:27-34; what DynamicEdgeConv feeds it): same result
+    contract as D = 3 - d2 <= r^2, ascending by (d2, index), -1 padded - against the oracle's D-dimensional statement."""
+    from curvecloudnet_b200 import frnn
+    from oracle import tp_ops as T
+    gen = torch.Generator().manual_seed(dim)
+    lens = torch.tensor([61, 40])
+    pts = 0.3 * torch.randn(2, 61, dim, generator=gen)
+    pts[0, 7] = pts[0, 3]
+    K, r = 9, 0.22 * dim ** 0.5
+    want_d, want_i = T.frnn_grid_points(pts, pts, lens, lens, K, r)
+    d, i, nn, grid = frnn.frnn_grid_points(pts.cuda(), pts.cuda(), lens.cuda(), lens.cuda(), K, r, return_nn=True)
+    assert torch.equal(i.cpu(), want_i) and torch.equal(d.cpu(), want_d) and grid is None
+    g = T.frnn_gather(pts, want_i, lens)
+    assert torch.equal(nn.cpu(), g)
+    with pytest.raises(ValueError, match="dimension mismatch"):
+        frnn.frnn_grid_points(pts.cuda(), pts[:, :, :dim - 1].contiguous().cuda(), lens.cuda(), lens.cuda(), K, r)
