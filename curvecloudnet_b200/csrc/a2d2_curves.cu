@@ -231,7 +231,9 @@ __global__ void a2d2_offset_kernel(const int32_t* __restrict__ local_id, const i
         for (int s = 0; s < n_sensors; ++s) { off[s] = run; if (sptr[s + 1] > sptr[s]) run += sensor_max[s]; }
     }
     __syncthreads();
+    const int n_valid = sptr[n_sensors];        // < n only when a lidar id was out of range (flag 1): those slots hold no point
     for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        if (r >= n_valid) { gid[r] = -1; continue; }
         const int g = local_id[r] + off[sensor[r]];
         gid[r] = g;
         presence[g + 1] = 1;
