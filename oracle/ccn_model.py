@@ -165,6 +165,6 @@ class ModelBase(torch.nn.Module):
 
         feat = cur[0]
         if "shapenet-categories" in kwargs and hasattr(self, "lin_categorical"):   # base.py:150-153
-            cats = F.one_hot(kwargs["shapenet-categories"], num_classes=16).float()
+            cats = F.one_hot(kwargs["shapenet-categories"], num_classes=16).to(feat.dtype)
             feat = torch.cat([feat, self.lin_categorical(cats)[batch0]], dim=1)
         return self.mlp(feat)

@@ -37,7 +37,7 @@ def feature_diffs(x, curve, batch):
     e = torch.where(same[:, None], x[1:] - x[:-1], torch.zeros_like(x[1:]))
     z = torch.zeros((1, x.shape[1]), dtype=x.dtype)
     e = torch.cat([z, e, z], dim=0)
-    v = torch.cat([torch.zeros(1, dtype=torch.bool), same, torch.zeros(1, dtype=torch.bool)]).float()
+    v = torch.cat([torch.zeros(1, dtype=torch.bool), same, torch.zeros(1, dtype=torch.bool)]).to(x.dtype)
     den = torch.clip(v[1:] + v[:-1], min=1)
     return torch.abs((e[1:] + e[:-1]) / den[:, None])
 
@@ -61,7 +61,7 @@ class SymmetricConv1d(nn.Module):
         return w
 
     def forward(self, x):  # x (1?, C_in, L)
-        return F.conv1d(x, self.full_weight(), self.bias, padding="same")
+        return F.conv1d(x.to(self.weight.dtype), self.full_weight(), self.bias, padding="same")
 
 
 def _pad_layout(glob, n_points, pad, with_ends):
@@ -109,7 +109,7 @@ class SymmetricCurve1DConvV2(_CurveConvBase):
         n_rows, valid = _pad_layout(glob, x.shape[0], pad if self.kernel_size > 1 else 0, with_ends=True)
         if self.with_diff:
             x = torch.cat([x, feature_diffs(x, point2curveidx, batch)], dim=1)
-        sig = torch.zeros((n_rows, x.shape[1]))
+        sig = torch.zeros((n_rows, x.shape[1]), dtype=x.dtype)
         sig[valid] = x
         for conv, norm in zip(self.conv_modules, self.norm_modules):
             sig = conv(sig.t()).t()
@@ -135,7 +135,7 @@ class SymmetricCurve1DConvFastV1(_CurveConvBase):
         for conv, norm in zip(self.conv_modules, self.norm_modules):
             if self.with_diff:
                 x = torch.cat([x, feature_diffs(x, point2curveidx, batch)], dim=1)
-            sig = torch.zeros((n_rows, x.shape[1]))
+            sig = torch.zeros((n_rows, x.shape[1]), dtype=x.dtype)
             sig[valid] = x
             x = conv(sig.t()).t()[valid]
             x = F.leaky_relu(norm(x))

@@ -79,6 +79,7 @@ class MLP(torch.nn.Module):
                 n.reset_parameters()
 
     def forward(self, x, *args, **kwargs):
+        x = x.to(self.lins[0].weight.dtype)       # no-op in f32; lets tests run the FEATURE arithmetic in f64 (positions stay f32)
         for i, (lin, norm) in enumerate(zip(self.lins, self.norms)):
             x = lin(x)
             if self.act is not None and self.act_first:
