@@ -73,3 +73,35 @@ def test_tiny_scans_match_oracle(name, n_points, native_executor):
     err = rel_err(got.cpu(), want)
     print("%s %d points native=%s rel err %.3e" % (name, n_points, native_executor, err))
     assert err <= 1e-4
+
+
+@pytest.mark.parametrize("name", ["nuscenes", "shapenet-seg", "a2d2"])
+def test_inference_against_f64_oracle(name):
+    """How far each precision mode is from an (almost) exact answer: the oracle with its feature arithmetic in f64 (same
+    weights, positions and index decisions).  The f32 oracle - i.e. the reference's own arithmetic - is ~1e-6 away from it;
+    fp32 must sit at the same distance (3x), bf16x3 inside the 1e-4 north-star budget, bf16 inside 2e-2 - measured against the
+    exact answer, not against another f32 run."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, object_scan_batch, randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    data = driving_scan_batch([4], subsample=2500) if name in ("nuscenes", "a2d2") else object_scan_batch([5, 6])
+    ref = randomize_model_(build_model(OracleModel, name), 1234).eval()
+    state = {k: v.clone() for k, v in ref.state_dict().items()}
+    outs = {}
+    for dt in (torch.float32, torch.float64):
+        torch.manual_seed(9)
+        with torch.no_grad():
+            outs[dt] = ref.to(dt)(data).float()
+    truth = outs[torch.float64]
+    base = rel_err(outs[torch.float32], truth)
+    for precision, bound in (("fp32", max(3 * base, 2e-6)), ("bf16x3", 1e-4), ("bf16", 2e-2)):
+        model = build_model(ModelBase, name, precision=precision)
+        model.load_state_dict(state, strict=True)
+        model = model.cuda().eval()
+        torch.manual_seed(9)
+        with torch.no_grad():
+            got = model(data.to("cuda"))
+        err = rel_err(got.cpu(), truth)
+        print("%s %s vs f64 oracle: %.3e (f32 oracle %.3e)" % (name, precision, err, base))
+        assert err <= bound, (precision, err, bound)
