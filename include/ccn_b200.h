@@ -269,7 +269,9 @@ int ccn_linear_f32(const float* A, int64_t lda, const float* W, int64_t ldw, con
  *   ccn_split_bf16         W fp32 (n,k) -> bf16 hi (n,kpad) [+ residual lo], kpad % 64 == 0, zero padded;
  *   ccn_weight_tensor_map  HOST call: fills a 128-byte CUtensorMap (host memory) for such a weight, box = 64 x box_n;
  *   ccn_linear_tc          mode 1: bf16 (2e-2 budget); mode 3: split-bf16 x3 (A_hi W_hi + A_lo W_hi + A_hi W_lo, fp32-class
- *                          accuracy for the 1e-4 budget).  A and Y stay fp32 in HBM; box_n in {32, 64, 128, 256}. */
+ *                          accuracy for the 1e-4 budget).  A and Y stay fp32 in HBM; box_n in {32, 64, 128, 256}.
+ * ccn_linear_tc is the STAND-ALONE form for a caller that binds only this layer and keeps fp32 activations; the model path of
+ * this library does not use it (its activations travel as split-bf16 planes: ccn_linear_planes / ccn_mlp_chain below). */
 int ccn_split_bf16(const float* w, int64_t ldw, int32_t n, int32_t k, int32_t kpad, void* hi, void* lo,
                    ccn_stream_t stream);
 int ccn_weight_tensor_map(void* tmap_out_host, const void* w_bf16, int32_t n, int32_t kpad, int32_t box_n);
