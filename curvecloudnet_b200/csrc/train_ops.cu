@@ -554,7 +554,7 @@ static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) 
 // One thread per (segment, channel); the forward is recomputed from msg / att.
 //   max       : the gradient goes to the first edge (lowest index) attaining the maximum
 //   mean/sum  : dmsg = dout / max(count, 1)   |   dmsg = dout
-//   weighted  : s = sigmoid(a); dmsg = s dout; datt = s (1 - s) msg dout
+//   weighted  : s = sigmoid(a); dmsg = s dout; datt = s (1 - s) msg dout   (normalised form: see the branch)
 //   attend    : s = softmax_seg(a); dmsg = s dout; datt = s (msg - sum_e s_e msg_e) dout
 // ------------------------------------------------------------------------------------------------------------
 __global__ void seg_aggregate_bwd_kernel(const float* __restrict__ msg, int64_t ldm, const float* __restrict__ att,
@@ -586,6 +586,21 @@ __global__ void seg_aggregate_bwd_kernel(const float* __restrict__ msg, int64_t 
                 const float s = 1.f / (1.f + expf(-att[(int64_t)j * lda + k]));
                 dmsg[(int64_t)j * lddm + k] = s * g;
                 datt[(int64_t)j * ldda + k] = s * (1.f - s) * msg[(int64_t)j * ldm + k] * g;
+            }
+        } else if (mode == CCN_AGG_WSUM_NORM) {
+            // out = sum_j m_j w_j / D, w = sigmoid(a), D = clamp(sum w, 1e-3) (dgcnn.py:190-197): the clamp passes the
+            // gradient of the sum only where it is not active
+            float tot = 0.f, o = 0.f;
+            for (int j = b; j < e; ++j) tot += 1.f / (1.f + expf(-att[(int64_t)j * lda + k]));
+            const bool free_sum = tot > 1e-3f;
+            const float den = fmaxf(tot, 1e-3f);
+            for (int j = b; j < e; ++j)
+                o += msg[(int64_t)j * ldm + k] * ((1.f / (1.f + expf(-att[(int64_t)j * lda + k]))) / den);
+            for (int j = b; j < e; ++j) {
+                const float s = 1.f / (1.f + expf(-att[(int64_t)j * lda + k]));
+                const float m = msg[(int64_t)j * ldm + k];
+                dmsg[(int64_t)j * lddm + k] = (s / den) * g;
+                datt[(int64_t)j * ldda + k] = s * (1.f - s) * ((free_sum ? m - o : m) / den) * g;
             }
         } else {
             float m = -INFINITY;

@@ -187,11 +187,29 @@ def sgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
         x = A.append_zero_rows(x, n_pad)
     PQ = A.linear(x, wpq, bpq)
     if not mod.use_sparse_feat_agg:
-        if mod.aggr_type != "max":
-            raise NotImplementedError("dense SGCNN path: only 'max' aggregation occurs in the shipped configs")
-        nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, mod.k, mod.r, cache=cache)
+        if mod.aggr_type == "max":
+            nbr, _, _ = ops.frnn_knn(pos, batch, pos, batch, sptr, mod.k, mod.r, cache=cache)
+            h = A.mlp_train(mlp, _first_hidden(mlp, A.sgcnn_layer1(PQ, _pad_nbr(nbr, n_pad))), first=1)
+            return A.group_max_dense(h, nbr), pos, batch, curve
+        # mean / attend / weighted-sum (dgcnn.py:182-203): the MLPs - and their batch statistics - run over ALL rows of the
+        # padded (B, N_max, K+1) table; the reduction then takes the valid rows of every point (its self loop and its found
+        # neighbours, the leading slots of the FRNN table)
+        nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, mod.k, mod.r, want_cnt=True, cache=cache)
+        n, G = pos.shape[0], mod.k + 1
         h = A.mlp_train(mlp, _first_hidden(mlp, A.sgcnn_layer1(PQ, _pad_nbr(nbr, n_pad))), first=1)
-        return A.group_max_dense(h, nbr), pos, batch, curve
+        att_all = A.mlp_train(mod.attend_nn, h) if mod.aggr_type in ("attend", "weighted-sum") else None
+        ext = torch.cat([torch.arange(n, dtype=torch.int32, device=pos.device).view(n, 1), nbr], dim=1).contiguous()
+        cnt = cnt.clone()
+        cnt[:n] += 1
+        edges = ops.dense_to_csr(ext, cnt)
+        slot = torch.arange(edges.E, device=pos.device, dtype=torch.int64) - edges.row_ptr[:n].to(torch.int64)[edges.erow.to(torch.int64)]
+        rows = edges.erow.to(torch.int64) * G + slot                    # dense row of every valid (point, slot): index plumbing
+        msg = A.gather_rows(h, rows)
+        if mod.aggr_type == "mean":
+            return A.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "mean"), pos, batch, curve
+        att = A.gather_rows(att_all, rows)
+        mode = "attend" if mod.aggr_type == "attend" else "weighted-sum-norm"
+        return A.seg_aggregate(msg, att, edges.row_ptr, edges.nq, mode), pos, batch, curve
     if mod.use_fast_knn:
         nbr, _, cnt = ops.frnn_knn(pos, batch, pos, batch, sptr, mod.k, mod.r, want_cnt=True, cache=cache)
     else:
@@ -200,10 +218,10 @@ def sgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
     msg = A.mlp_train(mlp, _first_hidden(mlp, A.edge_pair(PQ, edges)), first=1)
     if mod.aggr_type == "max":
         out = A.seg_aggregate(msg, None, edges.row_ptr, edges.nq, "max")
-    elif mod.aggr_type == "attend":
+    else:                                # dgcnn.py:240-244: everything but 'max' takes the softmax branch
+        if mod.attend_nn is None:
+            raise UnboundLocalError("attend_nn")                  # the reference dereferences self.attend_nn (dgcnn.py:242)
         out = A.seg_aggregate(msg, A.mlp_train(mod.attend_nn, msg), edges.row_ptr, edges.nq, "attend")
-    else:
-        raise NotImplementedError("sparse SGCNN path: aggregation %r" % mod.aggr_type)
     return out, pos, batch, curve
 
 

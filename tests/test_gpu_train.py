@@ -538,3 +538,47 @@ def test_eval_after_train_forward_refolds_batchnorm(precision):
         want = fresh(data)
     assert not torch.equal(before, after), "the train-mode forward did not change the running statistics"
     assert torch.equal(after, want), "stale folded BatchNorm: eval after a train forward differs from a fresh fold"
+
+
+@pytest.mark.parametrize("aggr", ["mean", "attend", "weighted-sum"])
+def test_dense_sgcnn_training_aggregations(aggr):
+    """StaticEdgeConv.forward_fast in TRAINING mode with the aggregations no shipped config uses (dgcnn.py:182-203): the MLPs'
+    batch statistics run over the whole padded (B, N_max, K+1) table (two samples of different length: padding rows and
+    missing neighbours take part), the reduction over each point's valid rows; output, input and parameter gradients against
+    the oracle's autograd.  Also the sparse path's "everything but max is the softmax branch" (:240-244)."""
+    from curvecloudnet_b200 import modules as M
+    from curvecloudnet_b200 import nn as N
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle import ccn_modules as OM
+    from oracle.tp_nn import MLP as OMLP
+    data = driving_scan_batch([1, 2], subsample=700)
+    gen = torch.Generator().manual_seed(4)
+    x0 = torch.randn(data.pos.shape[0], 13, generator=gen)
+    dims = [2 * (13 + 3), 48, 64]
+    att = aggr in ("attend", "weighted-sum")
+    for sparse in (False, True):
+        if sparse and aggr == "mean":
+            continue                                            # no attend_nn: the reference dereferences None there
+        kw = dict(r=0.12, with_xyz=True, aggr_type=aggr, use_sparse_feat_agg=sparse)
+        ref = OM.SGCNNLayer(OMLP(dims), 9, attend_nn=OMLP([64, 64, 64], act="leaky_relu") if att else None, **kw)
+        randomize_model_(ref, 77)
+        ref.train()
+        xr = x0.clone().requires_grad_()
+        out_r = ref(xr, data.pos, data.batch)[0]
+        gout = torch.randn(out_r.shape, generator=gen)
+        out_r.backward(gout)
+        mod = M.SGCNNLayer(N.MLP(dims), 9, attend_nn=N.MLP([64, 64, 64], act="leaky_relu") if att else None, **kw)
+        mod.load_state_dict(ref.state_dict(), strict=True)
+        mod = mod.cuda().train()
+        xg = x0.cuda().requires_grad_()
+        out = mod(xg, data.pos.cuda(), data.batch.cuda(), cache=N.ForwardCache())[0]
+        out.backward(gout.cuda())
+        assert rel_err(out.detach().cpu(), out_r.detach()) <= 1e-4, (aggr, sparse)
+        gmax = max(float(q.grad.abs().max()) for q in ref.parameters())
+        for (k, p), (_, q) in zip(mod.named_parameters(), ref.named_parameters()):
+            assert p.grad is not None, k
+            if k.endswith("lins.0.bias") or (k.endswith(".bias") and "lins" in k and not k.endswith("lins.%d.bias" % (len(dims) - 2))):
+                continue                                        # in front of a batch-statistics BatchNorm: zero up to rounding
+            err = float((p.grad.cpu().double() - q.grad.double()).abs().max()) / max(float(q.grad.abs().max()), 1e-3 * gmax)
+            assert err <= 1e-2, (aggr, sparse, k, err)
+        assert rel_err(xg.grad.cpu(), xr.grad) <= 5e-3, (aggr, sparse)
