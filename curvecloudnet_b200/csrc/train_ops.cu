@@ -989,8 +989,8 @@ extern "C" int ccn_seg_aggregate_bwd(const float* msg, int64_t ldm, const float*
                                      const int32_t* row_ptr, int64_t nq, int32_t c, int32_t mode, const float* dout,
                                      int64_t ldo, float* dmsg, int64_t lddm, float* datt, int64_t ldda,
                                      ccn_stream_t stream) {
-    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && dout && dmsg && mode >= 0 && mode <= 4);
-    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND) || (att && datt && msg));
+    CCN_REQUIRE(nq >= 0 && c > 0 && row_ptr && dout && dmsg && mode >= 0 && mode <= 5);
+    CCN_REQUIRE((mode != CCN_AGG_WSUM && mode != CCN_AGG_ATTEND && mode != CCN_AGG_WSUM_NORM) || (att && datt && msg));
     CCN_REQUIRE(mode != CCN_AGG_MAX || msg);
     if (nq == 0) return CCN_OK;
     ccn_launch(seg_aggregate_bwd_kernel, dim3(ELT_GRID(nq * c)), dim3(256), 0, S_, msg, ldm, att, lda, row_ptr, nq, c, mode, dout, ldo,

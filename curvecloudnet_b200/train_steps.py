@@ -202,7 +202,7 @@ def sgcnn_layer(mod, x, pos, batch, curve=None, **kwargs):
         cnt = cnt.clone()
         cnt[:n] += 1
         edges = ops.dense_to_csr(ext, cnt)
-        slot = torch.arange(edges.E, device=pos.device, dtype=torch.int64) - edges.row_ptr[:n].to(torch.int64)[edges.erow.to(torch.int64)]
+        slot = torch.arange(edges.n_edges, device=pos.device, dtype=torch.int64) - edges.row_ptr[:n].to(torch.int64)[edges.erow.to(torch.int64)]
         rows = edges.erow.to(torch.int64) * G + slot                    # dense row of every valid (point, slot): index plumbing
         msg = A.gather_rows(h, rows)
         if mod.aggr_type == "mean":
