@@ -105,3 +105,29 @@ def test_inference_against_f64_oracle(name):
         err = rel_err(got.cpu(), truth)
         print("%s %s vs f64 oracle: %.3e (f32 oracle %.3e)" % (name, precision, err, base))
         assert err <= bound, (precision, err, bound)
+
+
+@pytest.mark.parametrize("native_executor", [True, False])
+def test_mixed_size_batch_matches_oracle(native_executor):
+    """One batch holding a 6000-point scan, a 40-point scan and a 900-point scan (levels of the small scans shrink to a few
+    points while the large one is still dense; per-sample pointers, FPS counts and neighbour tables all become ragged):
+    logits against the oracle through both executors."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import _collate, driving_scan_sample, randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    data = _collate([driving_scan_sample(5, subsample=6000), driving_scan_sample(6, subsample=40),
+                     driving_scan_sample(7, subsample=900)], with_x=True)
+    ref = randomize_model_(build_model(OracleModel, "nuscenes"), 1234).eval()
+    torch.manual_seed(6)
+    with torch.no_grad():
+        want = ref(data)
+    model = build_model(ModelBase, "nuscenes", precision="bf16x3", native_executor=native_executor)
+    model.load_state_dict(ref.state_dict(), strict=True)
+    model = model.cuda().eval()
+    torch.manual_seed(6)
+    with torch.no_grad():
+        got = model(data.to("cuda"))
+    err = rel_err(got.cpu(), want)
+    print("mixed batch native=%s rel err %.3e" % (native_executor, err))
+    assert got.shape == want.shape and err <= 1e-4
