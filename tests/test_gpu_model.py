@@ -131,3 +131,31 @@ def test_mixed_size_batch_matches_oracle(native_executor):
     err = rel_err(got.cpu(), want)
     print("mixed batch native=%s rel err %.3e" % (native_executor, err))
     assert got.shape == want.shape and err <= 1e-4
+
+
+@pytest.mark.parametrize("native_executor", [True, False])
+@pytest.mark.parametrize("structure", ["singletons", "one_curve"])
+def test_degenerate_curve_structures_match_oracle(structure, native_executor):
+    """Curve ids at the two extremes - every point its own curve (no neighbour along any curve: the convolution sees pads only,
+    CurveFPS keeps every point, the 1-D groupings are self loops) and one single curve through the whole scan - against the
+    oracle, both executors."""
+    from curvecloudnet_b200.configs import build_model
+    from curvecloudnet_b200.model import ModelBase
+    from curvecloudnet_b200.synthetic import driving_scan_batch, randomize_model_
+    from oracle.ccn_model import ModelBase as OracleModel
+    data = driving_scan_batch([8], subsample=800)
+    n = data.pos.shape[0]
+    data.curve_idxs = torch.arange(n) if structure == "singletons" else torch.zeros(n, dtype=torch.int64)
+    ref = randomize_model_(build_model(OracleModel, "nuscenes"), 1234).eval()
+    torch.manual_seed(1)
+    with torch.no_grad():
+        want = ref(data)
+    model = build_model(ModelBase, "nuscenes", precision="bf16x3", native_executor=native_executor)
+    model.load_state_dict(ref.state_dict(), strict=True)
+    model = model.cuda().eval()
+    torch.manual_seed(1)
+    with torch.no_grad():
+        got = model(data.to("cuda"))
+    err = rel_err(got.cpu(), want)
+    print("%s native=%s rel err %.3e" % (structure, native_executor, err))
+    assert err <= 1e-4
