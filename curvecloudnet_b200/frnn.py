@@ -50,12 +50,25 @@ def frnn_grid_points(points1: torch.Tensor, points2: torch.Tensor, lengths1: Opt
                          % (points1.shape[2], points2.shape[2]))                      # frnn.py:286-289
     if K <= 0 or K > 32:
         raise ValueError("K must be in [1, 32]")                      # the reference kernels are instantiated for K <= 32
-    if torch.is_tensor(r):
-        rv = r.reshape(-1).tolist()
-        if any(abs(v - rv[0]) > 0 for v in rv):
-            raise NotImplementedError("one radius per batch (every reference call site passes a scalar)")
-        r = float(rv[0])
     N, P1, _ = points1.shape
+    if torch.is_tensor(r):
+        rv = [float(v) for v in r.reshape(-1).tolist()]
+        if len(rv) not in (1, N):
+            raise ValueError("r: one radius, or one per cloud")                              # frnn.py:319
+        if any(v != rv[0] for v in rv):
+            # a radius per cloud (frnn.py:316-323; no reference call site uses it): one search per cloud at the boundary
+            l1 = [P1] * N if lengths1 is None else [int(v) for v in lengths1.tolist()]
+            l2 = [points2.shape[1]] * N if lengths2 is None else [int(v) for v in lengths2.tolist()]
+            dists = torch.full((N, P1, K), -1.0, dtype=torch.float32, device=points1.device)
+            idxs = torch.full((N, P1, K), -1, dtype=torch.int64, device=points1.device)
+            for b in range(N):
+                if l1[b] == 0 or l2[b] == 0:
+                    continue
+                d, i, _, _ = frnn_grid_points(points1[b:b + 1, :l1[b]].contiguous(), points2[b:b + 1, :l2[b]].contiguous(), None, None,
+                                              K, rv[b], None, False, return_sorted, radius_cell_ratio)
+                dists[b, :l1[b]], idxs[b, :l1[b]] = d[0], i[0]
+            return dists, idxs, (frnn_gather(points2, idxs, lengths2) if return_nn else None), None
+        r = rv[0]
     p1, b1, l1 = _flatten(points1, lengths1)
     gp = grid.grid_params if grid is not None and isinstance(grid.grid_params, dict) else None
     if gp is not None and gp["key"] == (tuple(points2.shape), float(r)):

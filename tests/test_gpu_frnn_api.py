@@ -82,3 +82,16 @@ def test_frnn_grid_points_other_dimensions(dim):
     assert torch.equal(nn.cpu(), g)
     with pytest.raises(ValueError, match="dimension mismatch"):
         frnn.frnn_grid_points(pts.cuda(), pts[:, :, :dim - 1].contiguous().cuda(), lens.cuda(), lens.cuda(), K, r)
+
+
+def test_frnn_grid_points_radius_per_cloud():
+    """r as an (N,) tensor (frnn.py:316-323; no reference call site passes one): every cloud searched with its own radius."""
+    from curvecloudnet_b200 import frnn
+    from oracle import tp_ops as T
+    gen = torch.Generator().manual_seed(3)
+    lens = torch.tensor([200, 150, 90])
+    pts = torch.rand(3, 200, 3, generator=gen)
+    r = torch.tensor([0.08, 0.2, 0.12])
+    want_d, want_i = T.frnn_grid_points(pts, pts, lens, lens, 8, r)
+    d, i, _, grid = frnn.frnn_grid_points(pts.cuda(), pts.cuda(), lens.cuda(), lens.cuda(), 8, r.cuda())
+    assert torch.equal(i.cpu(), want_i) and torch.equal(d.cpu(), want_d) and grid is None
